@@ -1,0 +1,157 @@
+/*
+ * fls_format.h — on-disk / in-HBM container read by the B200 FastLanes decode engine.
+ *
+ * Why a container of our own: the reference extension (sebastiaan-dev/duckdb-fastlanes) delegates the
+ * .fls byte layout to a third-party library that is not vendored (reference CMakeLists.txt:56-62), so the
+ * true footer/segment bytes cannot be known here.  What IS pinned by the reference is the logical model:
+ *   table -> row groups (64 vectors x 1024 values, reference src/include/writer/fls_writer.hpp:14)
+ *         -> one column chunk per (row group, column), each with ONE encoding expression
+ *         -> per-vector entry points into segments (reference src/reader/fls_reader.cpp:448,458: get_chunk /
+ *            PointTo(vec_idx)).
+ * This header states that model as plain C structs.  It is a FORMAT contract shared by the product encoder,
+ * the CUDA decoder and the CPU oracle; it contains no algorithm.
+ *
+ * All integers little-endian.  All segment starts are 128-byte aligned relative to the file start so that a
+ * staged copy in HBM (256-byte aligned base) satisfies the 16-byte alignment of TMA bulk copies.
+ */
+#ifndef FLS_FORMAT_H
+#define FLS_FORMAT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLS_MAGIC "FLSB2001"
+#define FLS_VERSION 1u
+#define FLS_VEC_SZ 1024u            /* fastlanes::CFG::VEC_SZ */
+#define FLS_DEFAULT_VEC_PER_RG 64u  /* row group = 65 536 tuples, reference fls_writer.hpp:14 */
+#define FLS_ALIGN 128u
+
+/* Mirrors the names of fastlanes::DataType that the reference maps (src/reader/translation_utils.cpp:5-48,
+ * src/writer/translation_utils.cpp:6-70). */
+typedef enum fls_data_type {
+	FLS_TYPE_INVALID = 0,
+	FLS_TYPE_INT8 = 1,
+	FLS_TYPE_INT16 = 2,
+	FLS_TYPE_INT32 = 3,
+	FLS_TYPE_INT64 = 4,
+	FLS_TYPE_UINT8 = 5,
+	FLS_TYPE_UINT16 = 6,
+	FLS_TYPE_UINT32 = 7,
+	FLS_TYPE_UINT64 = 8,
+	FLS_TYPE_FLOAT = 9,
+	FLS_TYPE_DOUBLE = 10,
+	FLS_TYPE_BOOLEAN = 11, /* u8 view, reference fls_view_writer.cpp:63-64 */
+	FLS_TYPE_DATE = 12,    /* int32 days */
+	FLS_TYPE_TIMESTAMP = 13, /* int64 microseconds */
+	FLS_TYPE_DECIMAL = 14, /* physical INT16/32/64 chosen by precision; fix_me_decimal_type in the reference */
+	FLS_TYPE_FLS_STR = 15, /* VARCHAR */
+	FLS_TYPE_BYTE_ARRAY = 16
+} fls_data_type;
+
+/* One encoding expression per column chunk (the final operator of the reference's PhysicalExpr,
+ * src/reader/fls_reader.cpp:459; operator structs listed in SURVEY.md section 2.2). */
+typedef enum fls_encoding {
+	FLS_ENC_UNCOMPRESSED = 0, /* dec_uncompressed_opr */
+	FLS_ENC_CONSTANT = 1,     /* dec_constant_opr */
+	FLS_ENC_FFOR = 2,         /* dec_unffor_opr: bit-unpack + frame of reference */
+	FLS_ENC_DELTA = 3,        /* dec_unffor -> rsum -> dec_transpose_opr */
+	FLS_ENC_DICT = 4,         /* dec_dict_opr<KEY,IDX>: codes FFOR-packed in IDX lanes */
+	FLS_ENC_RLE = 5,          /* dec_rle_map_opr<KEY,u16>: run values + DELTA-coded run index */
+	FLS_ENC_ALP = 6,          /* dec_alp_opr */
+	FLS_ENC_ALP_RD = 7,       /* dec_alp_rd_opr */
+	FLS_ENC_CROSS_RLE = 8,    /* dec_cross_rle_opr: row-group wide (value,length) runs */
+	FLS_ENC_FREQUENCY = 9,    /* dec_frequency_opr: frequent value + exceptions */
+	FLS_ENC_SLPATCH = 10,     /* dec_slpatch_opr: FFOR at reduced width + patches */
+	FLS_ENC_DICT_STR = 11,    /* dec_dict_opr<fls_string_t,IDX> */
+	FLS_ENC_COUNT = 12
+} fls_encoding;
+
+/* Segment slots inside a column chunk. */
+enum {
+	FLS_SEG_META = 0, /* fls_vec_meta[n_vec] */
+	FLS_SEG_DATA = 1, /* per-vector packed blobs, addressed by fls_vec_meta.data_off16 */
+	FLS_SEG_AUX0 = 2, /* DICT keys | RLE run values | exception values | CROSS_RLE values | string bytes */
+	FLS_SEG_AUX1 = 3, /* exception positions (u16) | CROSS_RLE lengths (u32) | string end offsets (u32) */
+	FLS_SEG_COUNT = 4
+};
+
+typedef struct fls_file_header { /* 64 bytes at offset 0 */
+	char magic[8];
+	uint32_t version;
+	uint32_t n_columns;
+	uint32_t n_rowgroups;
+	uint32_t vec_per_rowgroup;
+	uint64_t n_tuples;
+	uint64_t footer_offset; /* fls_column_desc[n_columns], fls_rowgroup_desc[n_rowgroups],
+	                           fls_chunk_desc[n_rowgroups*n_columns] (row-group major) */
+	uint64_t footer_size;
+	uint8_t reserved[16];
+} fls_file_header;
+
+typedef struct fls_column_desc { /* 80 bytes */
+	char name[64];
+	uint8_t data_type;  /* fls_data_type */
+	uint8_t phys_bits;  /* 8/16/32/64: width T of the stored integers / IEEE words */
+	uint8_t is_signed;  /* integer interpretation of the physical words */
+	uint8_t is_float;   /* 1: FLOAT/DOUBLE payload */
+	uint8_t decimal_precision;
+	uint8_t decimal_scale;
+	uint8_t reserved[10];
+} fls_column_desc;
+
+typedef struct fls_rowgroup_desc { /* 24 bytes */
+	uint64_t first_tuple; /* file_row_number of tuple 0 of this row group */
+	uint32_t n_tuples;
+	uint32_t n_vec;
+	uint64_t reserved;
+} fls_rowgroup_desc;
+
+typedef struct fls_chunk_desc { /* 144 bytes */
+	uint64_t offset; /* from file start, 128-aligned */
+	uint64_t size;
+	uint64_t seg_off[FLS_SEG_COUNT]; /* from chunk start, 128-aligned */
+	uint64_t seg_size[FLS_SEG_COUNT];
+	uint64_t const_val; /* CONSTANT: the value (zero-extended physical word) */
+	uint64_t min_val;   /* zone map, physical word (sign-extended to 64 for signed, raw IEEE for floats) */
+	uint64_t max_val;
+	uint32_t n_vec;
+	uint32_t n_tuples;
+	uint32_t aux_count;  /* DICT: #keys; RLE/CROSS_RLE: total #runs; patched encodings: total #exceptions */
+	uint8_t encoding;    /* fls_encoding */
+	uint8_t phys_bits;   /* T */
+	uint8_t idx_bits;    /* DICT: lane width of the codes (8/16/32); RLE: 16 */
+	uint8_t max_width;   /* max fls_vec_meta.width(+width2) over the chunk: sizes the shared-memory stage */
+	uint8_t has_stats;
+	uint8_t reserved8[3];
+	uint16_t rd_dict[8]; /* ALP_RD: left-part dictionary (alprd_constants.hpp MAX_DICTIONARY_SIZE = 8) */
+	uint32_t reserved32;
+} fls_chunk_desc;
+
+/* Per-vector entry point + parameters: what PointTo(vec_idx) resolves in the reference. */
+typedef struct fls_vec_meta { /* 32 bytes */
+	uint64_t base;       /* FFOR/SLPATCH/ALP: frame of reference; FREQUENCY: frequent value */
+	uint32_t data_off16; /* blob offset from the DATA segment start, 16-byte units */
+	uint32_t aux_off;    /* first exception / first run value of this vector in AUX0 (and AUX1), in elements */
+	uint16_t aux_cnt;    /* #exceptions | #runs of this vector */
+	uint8_t width;       /* packed bit width W in [0,T] */
+	uint8_t width2;      /* ALP_RD: bit width of the left-part codes */
+	uint8_t e;           /* ALP exponent */
+	uint8_t f;           /* ALP factor */
+	uint16_t n_valid;    /* tuples of this vector that exist (last vector of a row group may be partial) */
+	uint64_t reserved;
+} fls_vec_meta;
+
+/* Per-vector blob layout in the DATA segment (sizes in bytes, every blob is a multiple of 128):
+ *   FFOR / SLPATCH / ALP / DICT codes / FREQUENCY(W=0): [128*W packed]
+ *   DELTA, RLE index:                                   [128 lane bases][128*W packed deltas]
+ *   ALP_RD:                                             [128*W right parts][128*W2 left codes]  (both in T lanes)
+ *   UNCOMPRESSED:                                       [1024*T/8 natural order]
+ */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLS_FORMAT_H */
