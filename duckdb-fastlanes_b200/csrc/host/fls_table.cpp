@@ -1,0 +1,275 @@
+// fls_table.cpp — flsgpu_table_open*/info/close: container parsing and validation (host C++).
+#include "flsgpu.h"
+#include "fls_error.hpp"
+#include "fls_table.hpp"
+
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+
+static thread_local std::string g_last_error;
+
+int fls_set_error(int status, const char* msg) {
+	g_last_error = msg ? msg : "";
+	return status;
+}
+
+static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
+	switch (c.encoding) {
+	case FLS_ENC_UNCOMPRESSED: return 1024u * c.phys_bits / 8;
+	case FLS_ENC_DELTA:
+	case FLS_ENC_RLE: return 128u + 128u * m.width;
+	case FLS_ENC_ALP_RD: return 128u * (m.width + m.width2);
+	case FLS_ENC_CONSTANT:
+	case FLS_ENC_CROSS_RLE: return 0;
+	default: return 128u * m.width;
+	}
+}
+
+int fls_table_parse(flsgpu_table* t) {
+	char msg[256];
+	if (t->size < sizeof(fls_file_header)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "file smaller than its header");
+	}
+	std::memcpy(&t->header, t->bytes, sizeof(fls_file_header));
+	const fls_file_header& h = t->header;
+	if (std::memcmp(h.magic, FLS_MAGIC, 8) != 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "bad magic: not an flsgpu container");
+	}
+	if (h.version != FLS_VERSION) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "unsupported container version");
+	}
+	if (h.n_columns == 0 || h.vec_per_rowgroup == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "container declares zero columns or zero vectors per row group");
+	}
+	const uint64_t need = (uint64_t)h.n_columns * sizeof(fls_column_desc) + (uint64_t)h.n_rowgroups * sizeof(fls_rowgroup_desc) +
+	                      (uint64_t)h.n_rowgroups * h.n_columns * sizeof(fls_chunk_desc);
+	if (h.footer_offset > t->size || h.footer_size != need || h.footer_offset + need > t->size || (h.footer_offset % 8)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "footer out of bounds or of unexpected size");
+	}
+	const uint8_t* f = t->bytes + h.footer_offset;
+	t->columns = reinterpret_cast<const fls_column_desc*>(f);
+	f += (uint64_t)h.n_columns * sizeof(fls_column_desc);
+	t->rowgroups = reinterpret_cast<const fls_rowgroup_desc*>(f);
+	f += (uint64_t)h.n_rowgroups * sizeof(fls_rowgroup_desc);
+	t->chunks = reinterpret_cast<const fls_chunk_desc*>(f);
+
+	uint64_t tuples = 0;
+	t->n_vectors = 0;
+	for (uint32_t r = 0; r < h.n_rowgroups; ++r) {
+		const fls_rowgroup_desc& rg = t->rowgroups[r];
+		if (rg.n_tuples == 0 || rg.n_vec != (rg.n_tuples + FLS_VEC_SZ - 1) / FLS_VEC_SZ || rg.n_vec > h.vec_per_rowgroup ||
+		    rg.first_tuple != tuples) {
+			std::snprintf(msg, sizeof(msg), "row group %u: inconsistent tuple/vector counts", r);
+			return fls_set_error(FLSGPU_ERR_INVALID, msg);
+		}
+		if (r + 1 < h.n_rowgroups && rg.n_vec != h.vec_per_rowgroup) {
+			std::snprintf(msg, sizeof(msg), "row group %u: only the last row group may be short", r);
+			return fls_set_error(FLSGPU_ERR_INVALID, msg);
+		}
+		tuples += rg.n_tuples;
+		t->n_vectors += rg.n_vec;
+		for (uint32_t c = 0; c < h.n_columns; ++c) {
+			const fls_chunk_desc& ch = t->chunk(r, c);
+			const fls_column_desc& col = t->columns[c];
+			std::snprintf(msg, sizeof(msg), "chunk (rg %u, col %u): ", r, c);
+			const size_t ml = std::strlen(msg);
+			auto fail = [&](const char* what) {
+				std::snprintf(msg + ml, sizeof(msg) - ml, "%s", what);
+				return fls_set_error(FLSGPU_ERR_INVALID, msg);
+			};
+			if (ch.offset % FLS_ALIGN || ch.offset + ch.size > h.footer_offset || ch.offset + ch.size < ch.offset) {
+				return fail("extent outside the data region");
+			}
+			if (ch.encoding >= FLS_ENC_COUNT || ch.phys_bits != col.phys_bits || ch.n_vec != rg.n_vec || ch.n_tuples != rg.n_tuples) {
+				return fail("descriptor disagrees with the row group / column");
+			}
+			for (int s = 0; s < FLS_SEG_COUNT; ++s) {
+				if (ch.seg_off[s] % FLS_ALIGN || ch.seg_off[s] + ch.seg_size[s] > ch.size) {
+					return fail("segment outside the chunk");
+				}
+			}
+			if (ch.seg_size[FLS_SEG_META] != (uint64_t)ch.n_vec * sizeof(fls_vec_meta)) {
+				return fail("meta segment has the wrong size");
+			}
+			const unsigned T = ch.phys_bits, esz = T / 8;
+			const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_META]);
+			const bool patched = ch.encoding == FLS_ENC_FFOR || ch.encoding == FLS_ENC_SLPATCH || ch.encoding == FLS_ENC_FREQUENCY ||
+			                     ch.encoding == FLS_ENC_ALP || ch.encoding == FLS_ENC_ALP_RD;
+			unsigned lanes_T = T;
+			if (ch.encoding == FLS_ENC_DICT) {
+				lanes_T = ch.idx_bits;
+				if (lanes_T != 8 && lanes_T != 16 && lanes_T != 32) {
+					return fail("DICT idx_bits must be 8, 16 or 32");
+				}
+				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.aux_count == 0) {
+					return fail("dictionary segment has the wrong size");
+				}
+			} else if (ch.encoding == FLS_ENC_RLE) {
+				lanes_T = 16;
+				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz) {
+					return fail("run value segment has the wrong size");
+				}
+			} else if (ch.encoding == FLS_ENC_CROSS_RLE) {
+				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.seg_size[FLS_SEG_AUX1] != (uint64_t)ch.aux_count * 4) {
+					return fail("CROSS_RLE segments have the wrong size");
+				}
+				const uint32_t* lens = reinterpret_cast<const uint32_t*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX1]);
+				uint64_t sum = 0;
+				for (uint32_t i = 0; i < ch.aux_count; ++i) {
+					sum += lens[i];
+				}
+				if (sum != (uint64_t)ch.n_vec * FLS_VEC_SZ) {
+					return fail("CROSS_RLE run lengths do not cover the chunk");
+				}
+			} else if (patched) {
+				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.seg_size[FLS_SEG_AUX1] != (uint64_t)ch.aux_count * 2) {
+					return fail("exception segments have the wrong size");
+				}
+			}
+			if ((ch.encoding == FLS_ENC_ALP || ch.encoding == FLS_ENC_ALP_RD) && !(col.is_float && T >= 32)) {
+				return fail("ALP encodings need a FLOAT/DOUBLE column");
+			}
+			const uint16_t* exc_pos = reinterpret_cast<const uint16_t*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX1]);
+			for (uint32_t v = 0; v < ch.n_vec; ++v) {
+				const fls_vec_meta& m = meta[v];
+				if (m.width > lanes_T || (ch.encoding == FLS_ENC_ALP_RD && (m.width2 == 0 || m.width2 > 3 || m.width + m.width2 > 64 + 3))) {
+					return fail("vector bit width out of range");
+				}
+				if ((uint64_t)m.data_off16 * 16 + blob_bytes(ch, m) > ch.seg_size[FLS_SEG_DATA]) {
+					return fail("vector entry point outside the data segment");
+				}
+				if (m.n_valid == 0 || m.n_valid > FLS_VEC_SZ) {
+					return fail("vector n_valid out of range");
+				}
+				if (patched || ch.encoding == FLS_ENC_RLE) {
+					if ((uint64_t)m.aux_off + m.aux_cnt > ch.aux_count || m.aux_cnt > FLS_VEC_SZ) {
+						return fail("vector aux range outside the aux segments");
+					}
+				}
+				if (patched) {
+					for (uint32_t k = 0; k < m.aux_cnt; ++k) {
+						if (exc_pos[m.aux_off + k] >= FLS_VEC_SZ) {
+							return fail("exception position out of range");
+						}
+					}
+				}
+				if (ch.encoding == FLS_ENC_ALP && (m.e > (T == 64 ? 18 : 10) || m.f > m.e)) {
+					return fail("ALP exponent/factor out of range");
+				}
+				if (ch.encoding == FLS_ENC_RLE && m.aux_cnt == 0) {
+					return fail("RLE vector without runs");
+				}
+			}
+		}
+	}
+	if (tuples != h.n_tuples) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "row group tuple counts do not add up to the table's");
+	}
+	return FLSGPU_OK;
+}
+
+extern "C" {
+
+const char* flsgpu_last_error(void) {
+	return g_last_error.c_str();
+}
+const char* flsgpu_version(void) {
+	return "flsgpu 0.1 (sm_100a)";
+}
+
+int flsgpu_table_open_memory(const void* bytes, uint64_t size, int copy, flsgpu_table** out) {
+	if (!bytes || !out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_open_memory: null argument");
+	}
+	auto t = std::make_unique<flsgpu_table>();
+	if (copy) {
+		t->owned.assign(static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + size);
+		t->bytes = t->owned.data();
+	} else {
+		t->bytes = static_cast<const uint8_t*>(bytes);
+	}
+	t->size = size;
+	const int rc = fls_table_parse(t.get());
+	if (rc) {
+		return rc;
+	}
+	*out = t.release();
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_open(const char* path, flsgpu_table** out) {
+	if (!path || !out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_open: null argument");
+	}
+	FILE* fp = std::fopen(path, "rb");
+	if (!fp) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open file: ") + path).c_str());
+	}
+	std::fseek(fp, 0, SEEK_END);
+	const long sz = std::ftell(fp);
+	std::fseek(fp, 0, SEEK_SET);
+	auto t = std::make_unique<flsgpu_table>();
+	t->owned.resize(sz > 0 ? (size_t)sz : 0);
+	const size_t n = sz > 0 ? std::fread(t->owned.data(), 1, (size_t)sz, fp) : 0;
+	std::fclose(fp);
+	if (sz < 0 || n != (size_t)sz) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("short read: ") + path).c_str());
+	}
+	t->bytes = t->owned.data();
+	t->size = (uint64_t)sz;
+	const int rc = fls_table_parse(t.get());
+	if (rc) {
+		return rc;
+	}
+	*out = t.release();
+	return FLSGPU_OK;
+}
+
+void flsgpu_table_close(flsgpu_table* t) {
+	if (t) {
+		fls_device_release(t);
+		delete t;
+	}
+}
+
+int flsgpu_table_info_get(const flsgpu_table* t, flsgpu_table_info* out) {
+	if (!t || !out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_info_get: null argument");
+	}
+	out->n_columns = t->header.n_columns;
+	out->n_rowgroups = t->header.n_rowgroups;
+	out->vec_per_rowgroup = t->header.vec_per_rowgroup;
+	out->reserved = 0;
+	out->n_tuples = t->header.n_tuples;
+	out->n_vectors = t->n_vectors;
+	out->file_bytes = t->size;
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_column(const flsgpu_table* t, uint32_t col, fls_column_desc* out) {
+	if (!t || !out || col >= t->header.n_columns) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_column: column index out of range");
+	}
+	*out = t->columns[col];
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_rowgroup(const flsgpu_table* t, uint32_t rg, fls_rowgroup_desc* out) {
+	if (!t || !out || rg >= t->header.n_rowgroups) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_rowgroup: row group index out of range");
+	}
+	*out = t->rowgroups[rg];
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_chunk(const flsgpu_table* t, uint32_t rg, uint32_t col, fls_chunk_desc* out) {
+	if (!t || !out || rg >= t->header.n_rowgroups || col >= t->header.n_columns) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_chunk: index out of range");
+	}
+	*out = t->chunk(rg, col);
+	return FLSGPU_OK;
+}
+
+} // extern "C"

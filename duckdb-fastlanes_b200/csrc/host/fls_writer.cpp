@@ -1,0 +1,272 @@
+// fls_writer.cpp — flsgpu_writer_*: row-group buffering + container assembly (host C++).
+// Mirrors FastLanesFileWriter (reference src/writer/fls_writer.cpp): rows are buffered until a row group is
+// full (:46-102), each column of a full row group goes through WriteColumn (:14-39), Finalize flushes the tail
+// (:332-347).
+#include "flsgpu.h"
+#include "fls_encoder.hpp"
+#include "fls_error.hpp"
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+using namespace flshost;
+
+struct flsgpu_writer {
+	std::vector<fls_column_desc> cols;
+	std::vector<ColumnType> types;
+	std::vector<int> force;
+	uint32_t vec_per_rg = FLS_DEFAULT_VEC_PER_RG;
+	uint64_t rg_tuples = 0;
+	std::vector<std::vector<uint8_t>> pending; // per column, < rg_tuples rows
+	uint64_t pending_rows = 0;
+	std::vector<fls_rowgroup_desc> rgs;
+	std::vector<std::unique_ptr<EncodedChunk>> chunks; // row-group major
+	uint64_t n_tuples = 0;
+	bool finished = false;
+	std::vector<uint8_t> image;
+};
+
+static int encode_rowgroups(flsgpu_writer* w, const std::vector<const uint8_t*>& col_ptrs, uint64_t n_rows, int n_threads) {
+	// n_rows covers k full row groups, or one partial tail row group
+	const uint64_t n_rg = (n_rows + w->rg_tuples - 1) / w->rg_tuples;
+	const size_t n_cols = w->cols.size();
+	const size_t first_chunk = w->chunks.size();
+	w->chunks.resize(first_chunk + n_rg * n_cols);
+	for (uint64_t r = 0; r < n_rg; ++r) {
+		fls_rowgroup_desc rd {};
+		rd.first_tuple = w->n_tuples + r * w->rg_tuples;
+		rd.n_tuples = (uint32_t)std::min<uint64_t>(w->rg_tuples, n_rows - r * w->rg_tuples);
+		rd.n_vec = (rd.n_tuples + FLS_VEC_SZ - 1) / FLS_VEC_SZ;
+		w->rgs.push_back(rd);
+	}
+	std::atomic<uint64_t> next {0};
+	std::atomic<bool> failed {false};
+	std::string fail_msg;
+	std::mutex* mu = new std::mutex();
+	auto work = [&]() {
+		for (;;) {
+			const uint64_t task = next.fetch_add(1);
+			if (task >= n_rg * n_cols || failed.load()) {
+				return;
+			}
+			const uint64_t r = task / n_cols, c = task % n_cols;
+			const uint32_t nt = (uint32_t)std::min<uint64_t>(w->rg_tuples, n_rows - r * w->rg_tuples);
+			const size_t esz = w->types[c].phys_bits / 8;
+			auto ch = std::make_unique<EncodedChunk>();
+			const char* err = "";
+			if (!encode_chunk(w->types[c], col_ptrs[c] + r * w->rg_tuples * esz, nt, w->force[c], *ch, &err)) {
+				std::lock_guard<std::mutex> g(*mu);
+				failed = true;
+				fail_msg = std::string("column '") + w->cols[c].name + "': " + err;
+				return;
+			}
+			w->chunks[first_chunk + task] = std::move(ch);
+		}
+	};
+	const int nt = std::max(1, std::min<int>(n_threads, (int)(n_rg * n_cols)));
+	if (nt == 1) {
+		work();
+	} else {
+		std::vector<std::thread> th;
+		for (int i = 0; i < nt; ++i) {
+			th.emplace_back(work);
+		}
+		for (auto& t : th) {
+			t.join();
+		}
+	}
+	delete mu;
+	if (failed) {
+		w->chunks.resize(first_chunk);
+		w->rgs.resize(w->rgs.size() - n_rg);
+		return fls_set_error(FLSGPU_ERR_INVALID, fail_msg.c_str());
+	}
+	w->n_tuples += n_rows;
+	return FLSGPU_OK;
+}
+
+extern "C" {
+
+int flsgpu_writer_create(uint32_t n_columns, const flsgpu_column_spec* cols, uint32_t vec_per_rowgroup, flsgpu_writer** out) {
+	if (!out || !cols || n_columns == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_create: null argument or zero columns");
+	}
+	auto w = std::make_unique<flsgpu_writer>();
+	w->vec_per_rg = vec_per_rowgroup ? vec_per_rowgroup : FLS_DEFAULT_VEC_PER_RG;
+	w->rg_tuples = (uint64_t)w->vec_per_rg * FLS_VEC_SZ;
+	for (uint32_t i = 0; i < n_columns; ++i) {
+		const ColumnType t = column_type_of(cols[i].data_type, cols[i].decimal_precision);
+		if (!t.phys_bits) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_writer_create: unsupported column data type");
+		}
+		fls_column_desc d {};
+		std::snprintf(d.name, sizeof(d.name), "%s", cols[i].name ? cols[i].name : "");
+		d.data_type = t.data_type;
+		d.phys_bits = t.phys_bits;
+		d.is_signed = t.is_signed;
+		d.is_float = t.is_float;
+		d.decimal_precision = (uint8_t)cols[i].decimal_precision;
+		d.decimal_scale = (uint8_t)cols[i].decimal_scale;
+		w->cols.push_back(d);
+		w->types.push_back(t);
+		w->force.push_back(cols[i].force_encoding);
+	}
+	w->pending.resize(n_columns);
+	*out = w.release();
+	return FLSGPU_OK;
+}
+
+int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t n_tuples, int n_threads) {
+	if (!w || !columns) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_append: null argument");
+	}
+	if (w->finished) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_append: writer already finished");
+	}
+	const size_t n_cols = w->cols.size();
+	uint64_t consumed = 0;
+	// 1. top up the pending buffer to a full row group
+	if (w->pending_rows) {
+		const uint64_t take = std::min<uint64_t>(n_tuples, w->rg_tuples - w->pending_rows);
+		for (size_t c = 0; c < n_cols; ++c) {
+			const size_t esz = w->types[c].phys_bits / 8;
+			const uint8_t* src = static_cast<const uint8_t*>(columns[c]);
+			w->pending[c].insert(w->pending[c].end(), src, src + take * esz);
+		}
+		w->pending_rows += take;
+		consumed = take;
+		if (w->pending_rows == w->rg_tuples) {
+			std::vector<const uint8_t*> ptrs(n_cols);
+			for (size_t c = 0; c < n_cols; ++c) {
+				ptrs[c] = w->pending[c].data();
+			}
+			const int rc = encode_rowgroups(w, ptrs, w->rg_tuples, n_threads);
+			if (rc) {
+				return rc;
+			}
+			for (auto& p : w->pending) {
+				p.clear();
+			}
+			w->pending_rows = 0;
+		}
+	}
+	// 2. encode full row groups straight from the caller's arrays
+	const uint64_t full = (n_tuples - consumed) / w->rg_tuples * w->rg_tuples;
+	if (full) {
+		std::vector<const uint8_t*> ptrs(n_cols);
+		for (size_t c = 0; c < n_cols; ++c) {
+			ptrs[c] = static_cast<const uint8_t*>(columns[c]) + consumed * (w->types[c].phys_bits / 8);
+		}
+		const int rc = encode_rowgroups(w, ptrs, full, n_threads);
+		if (rc) {
+			return rc;
+		}
+		consumed += full;
+	}
+	// 3. keep the remainder
+	if (consumed < n_tuples) {
+		const uint64_t rest = n_tuples - consumed;
+		for (size_t c = 0; c < n_cols; ++c) {
+			const size_t esz = w->types[c].phys_bits / 8;
+			const uint8_t* src = static_cast<const uint8_t*>(columns[c]) + consumed * esz;
+			w->pending[c].insert(w->pending[c].end(), src, src + rest * esz);
+		}
+		w->pending_rows += rest;
+	}
+	return FLSGPU_OK;
+}
+
+int flsgpu_writer_finish(flsgpu_writer* w) {
+	if (!w) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_finish: null writer");
+	}
+	if (w->finished) {
+		return FLSGPU_OK;
+	}
+	if (w->pending_rows) {
+		std::vector<const uint8_t*> ptrs(w->cols.size());
+		for (size_t c = 0; c < w->cols.size(); ++c) {
+			ptrs[c] = w->pending[c].data();
+		}
+		const int rc = encode_rowgroups(w, ptrs, w->pending_rows, 1);
+		if (rc) {
+			return rc;
+		}
+		w->pending_rows = 0;
+		for (auto& p : w->pending) {
+			p.clear();
+			p.shrink_to_fit();
+		}
+	}
+	// lay out: header | chunks (128-aligned) | footer
+	uint64_t off = FLS_ALIGN; // header occupies the first 128 bytes
+	for (auto& ch : w->chunks) {
+		ch->desc.offset = off;
+		off += ch->desc.size;
+	}
+	const uint64_t footer_off = off;
+	const uint64_t footer_size = w->cols.size() * sizeof(fls_column_desc) + w->rgs.size() * sizeof(fls_rowgroup_desc) +
+	                             w->chunks.size() * sizeof(fls_chunk_desc);
+	w->image.assign(footer_off + footer_size, 0);
+	fls_file_header h {};
+	std::memcpy(h.magic, FLS_MAGIC, 8);
+	h.version = FLS_VERSION;
+	h.n_columns = (uint32_t)w->cols.size();
+	h.n_rowgroups = (uint32_t)w->rgs.size();
+	h.vec_per_rowgroup = w->vec_per_rg;
+	h.n_tuples = w->n_tuples;
+	h.footer_offset = footer_off;
+	h.footer_size = footer_size;
+	std::memcpy(w->image.data(), &h, sizeof(h));
+	uint8_t* f = w->image.data() + footer_off;
+	std::memcpy(f, w->cols.data(), w->cols.size() * sizeof(fls_column_desc));
+	f += w->cols.size() * sizeof(fls_column_desc);
+	std::memcpy(f, w->rgs.data(), w->rgs.size() * sizeof(fls_rowgroup_desc));
+	f += w->rgs.size() * sizeof(fls_rowgroup_desc);
+	for (auto& ch : w->chunks) {
+		std::memcpy(w->image.data() + ch->desc.offset, ch->bytes.data(), ch->bytes.size());
+		std::memcpy(f, &ch->desc, sizeof(fls_chunk_desc));
+		f += sizeof(fls_chunk_desc);
+		ch->bytes.clear();
+		ch->bytes.shrink_to_fit();
+	}
+	w->finished = true;
+	return FLSGPU_OK;
+}
+
+int flsgpu_writer_image(const flsgpu_writer* w, const void** bytes, uint64_t* size) {
+	if (!w || !w->finished || !bytes || !size) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_image: writer not finished");
+	}
+	*bytes = w->image.data();
+	*size = w->image.size();
+	return FLSGPU_OK;
+}
+
+int flsgpu_writer_save(const flsgpu_writer* w, const char* path) {
+	if (!w || !w->finished || !path) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_save: writer not finished");
+	}
+	FILE* fp = std::fopen(path, "wb");
+	if (!fp) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open for writing: ") + path).c_str());
+	}
+	const size_t n = std::fwrite(w->image.data(), 1, w->image.size(), fp);
+	std::fclose(fp);
+	if (n != w->image.size()) {
+		return fls_set_error(FLSGPU_ERR_IO, "short write");
+	}
+	return FLSGPU_OK;
+}
+
+void flsgpu_writer_destroy(flsgpu_writer* w) {
+	delete w;
+}
+
+} // extern "C"

@@ -1,0 +1,271 @@
+"""ctypes binding of libflsgpu.so (the C ABI in include/flsgpu.h).
+
+This is the Python test/bench driver over the same entry points the DuckDB extension's C++ reader calls; it adds
+no decode logic of its own.  There is no CPU fallback: if the shared library is missing the import fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.environ.get("FLSGPU_LIB", os.path.join(os.path.dirname(_HERE), "libflsgpu.so"))
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: build it with `python __graft_entry__.py build` "
+        "(flsgpu has no CPU fallback and will not run without its CUDA library)"
+    )
+lib = C.CDLL(LIB_PATH)
+
+# ---- enums (include/fls_format.h, include/flsgpu.h) -------------------------------------------------------------
+TYPE = dict(INT8=1, INT16=2, INT32=3, INT64=4, UINT8=5, UINT16=6, UINT32=7, UINT64=8, FLOAT=9, DOUBLE=10,
+            BOOLEAN=11, DATE=12, TIMESTAMP=13, DECIMAL=14)
+ENC = dict(UNCOMPRESSED=0, CONSTANT=1, FFOR=2, DELTA=3, DICT=4, RLE=5, ALP=6, ALP_RD=7, CROSS_RLE=8, FREQUENCY=9,
+           SLPATCH=10)
+ENC_NAME = {v: k for k, v in ENC.items()}
+OUT = dict(NATIVE=0, I8=1, I16=2, I32=3, I64=4, U8=5, U16=6, U32=7, U64=8, F32=9, F64=10)
+OUT_NP = {1: np.int8, 2: np.int16, 3: np.int32, 4: np.int64, 5: np.uint8, 6: np.uint16, 7: np.uint32, 8: np.uint64,
+          9: np.float32, 10: np.float64}
+_NP_OF_TYPE = {1: np.int8, 2: np.int16, 3: np.int32, 4: np.int64, 5: np.uint8, 6: np.uint16, 7: np.uint32,
+               8: np.uint64, 9: np.float32, 10: np.float64, 11: np.uint8, 12: np.int32, 13: np.int64}
+VEC = 1024
+
+
+class ColumnSpec(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("data_type", C.c_int32), ("decimal_precision", C.c_int32),
+                ("decimal_scale", C.c_int32), ("force_encoding", C.c_int32)]
+
+
+class ColumnDesc(C.Structure):
+    _fields_ = [("name", C.c_char * 64), ("data_type", C.c_uint8), ("phys_bits", C.c_uint8), ("is_signed", C.c_uint8),
+                ("is_float", C.c_uint8), ("decimal_precision", C.c_uint8), ("decimal_scale", C.c_uint8),
+                ("reserved", C.c_uint8 * 10)]
+
+
+class RowgroupDesc(C.Structure):
+    _fields_ = [("first_tuple", C.c_uint64), ("n_tuples", C.c_uint32), ("n_vec", C.c_uint32), ("reserved", C.c_uint64)]
+
+
+class ChunkDesc(C.Structure):
+    _fields_ = [("offset", C.c_uint64), ("size", C.c_uint64), ("seg_off", C.c_uint64 * 4), ("seg_size", C.c_uint64 * 4),
+                ("const_val", C.c_uint64), ("min_val", C.c_uint64), ("max_val", C.c_uint64), ("n_vec", C.c_uint32),
+                ("n_tuples", C.c_uint32), ("aux_count", C.c_uint32), ("encoding", C.c_uint8), ("phys_bits", C.c_uint8),
+                ("idx_bits", C.c_uint8), ("max_width", C.c_uint8), ("has_stats", C.c_uint8), ("reserved8", C.c_uint8 * 3),
+                ("rd_dict", C.c_uint16 * 8), ("reserved32", C.c_uint32)]
+
+
+class TableInfo(C.Structure):
+    _fields_ = [("n_columns", C.c_uint32), ("n_rowgroups", C.c_uint32), ("vec_per_rowgroup", C.c_uint32),
+                ("reserved", C.c_uint32), ("n_tuples", C.c_uint64), ("n_vectors", C.c_uint64), ("file_bytes", C.c_uint64)]
+
+
+class AggResult(C.Structure):
+    _fields_ = [("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("count", C.c_uint64), ("min_val", C.c_int64),
+                ("max_val", C.c_int64), ("fsum", C.c_double), ("reserved", C.c_uint64 * 2)]
+
+
+assert C.sizeof(ColumnDesc) == 80 and C.sizeof(RowgroupDesc) == 24 and C.sizeof(ChunkDesc) == 144
+assert C.sizeof(AggResult) == 64
+
+lib.flsgpu_last_error.restype = C.c_char_p
+lib.flsgpu_version.restype = C.c_char_p
+lib.flsgpu_launch_count.restype = C.c_uint64
+for _n in ("flsgpu_table_close", "flsgpu_writer_destroy"):
+    getattr(lib, _n).restype = None
+
+# every symbol include/flsgpu.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "flsgpu_last_error", "flsgpu_version", "flsgpu_init", "flsgpu_device_count", "flsgpu_writer_create",
+    "flsgpu_writer_append", "flsgpu_writer_finish", "flsgpu_writer_image", "flsgpu_writer_save",
+    "flsgpu_writer_destroy", "flsgpu_table_open", "flsgpu_table_open_memory", "flsgpu_table_close",
+    "flsgpu_table_info_get", "flsgpu_table_column", "flsgpu_table_rowgroup", "flsgpu_table_chunk",
+    "flsgpu_table_stage", "flsgpu_table_unstage", "flsgpu_table_resident_bytes", "flsgpu_decode_column",
+    "flsgpu_rowgroup_decode", "flsgpu_aggregate_column", "flsgpu_agg_reset", "flsgpu_scan_column_to_host",
+    "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
+]
+
+
+class FlsError(RuntimeError):
+    def __init__(self, status, where):
+        msg = lib.flsgpu_last_error().decode(errors="replace")
+        super().__init__(f"{where}: status {status}: {msg}")
+        self.status = status
+
+
+def _check(rc, where):
+    if rc != 0:
+        raise FlsError(rc, where)
+
+
+def _vp(x):
+    return C.c_void_p(int(x) if x else 0)
+
+
+class Writer:
+    """COPY ... (FORMAT fls): flsgpu_writer_* (reference src/writer/fls_writer.cpp)."""
+
+    def __init__(self, columns, vec_per_rowgroup=64):
+        # columns: list of (name, type_name, force_encoding_name|None[, precision, scale])
+        self._names = [c[0].encode() for c in columns]
+        specs = (ColumnSpec * len(columns))()
+        self.np_types = []
+        for i, c in enumerate(columns):
+            prec, scale = (c[3], c[4]) if len(c) > 3 else (0, 0)
+            specs[i] = ColumnSpec(self._names[i], TYPE[c[1]], prec, scale, -1 if c[2] is None else ENC[c[2]])
+            if c[1] == "DECIMAL":
+                self.np_types.append(np.int16 if prec <= 4 else np.int32 if prec <= 9 else np.int64)
+            else:
+                self.np_types.append(_NP_OF_TYPE[TYPE[c[1]]])
+        self._h = C.c_void_p()
+        _check(lib.flsgpu_writer_create(len(columns), specs, vec_per_rowgroup, C.byref(self._h)), "writer_create")
+
+    def append(self, arrays, n_threads=None):
+        n = len(arrays[0])
+        keep = [np.ascontiguousarray(a, dtype=t) for a, t in zip(arrays, self.np_types)]
+        assert all(len(a) == n for a in keep)
+        ptrs = (C.c_void_p * len(keep))(*[a.ctypes.data for a in keep])
+        _check(lib.flsgpu_writer_append(self._h, ptrs, C.c_uint64(n), n_threads or (os.cpu_count() or 1)), "writer_append")
+
+    def finish(self):
+        _check(lib.flsgpu_writer_finish(self._h), "writer_finish")
+        p, n = C.c_void_p(), C.c_uint64()
+        _check(lib.flsgpu_writer_image(self._h, C.byref(p), C.byref(n)), "writer_image")
+        # zero-copy view; valid until close()
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,))
+
+    def save(self, path):
+        _check(lib.flsgpu_writer_save(self._h, os.fsencode(path)), "writer_save")
+
+    def close(self):
+        if self._h:
+            lib.flsgpu_writer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        self.close()
+
+
+def write_table(columns, arrays, vec_per_rowgroup=64, n_threads=None):
+    """Encode arrays into a container image (numpy uint8 copy)."""
+    w = Writer(columns, vec_per_rowgroup)
+    w.append(arrays, n_threads)
+    img = w.finish().copy()
+    w.close()
+    return img
+
+
+class Table:
+    """TableMetadata + row-group readers: flsgpu_table_* (reference src/reader/table_metadata.cpp, fls_reader.cpp)."""
+
+    def __init__(self, image=None, path=None, copy=False):
+        self._h = C.c_void_p()
+        self._image = None
+        if path is not None:
+            _check(lib.flsgpu_table_open(os.fsencode(path), C.byref(self._h)), "table_open")
+        else:
+            self._image = np.ascontiguousarray(image, dtype=np.uint8)
+            _check(lib.flsgpu_table_open_memory(_vp(self._image.ctypes.data), C.c_uint64(self._image.size), int(copy),
+                                                C.byref(self._h)), "table_open_memory")
+        info = TableInfo()
+        _check(lib.flsgpu_table_info_get(self._h, C.byref(info)), "table_info")
+        self.info = info
+        self.n_columns, self.n_rowgroups = info.n_columns, info.n_rowgroups
+        self.vec_per_rowgroup, self.n_tuples = info.vec_per_rowgroup, info.n_tuples
+
+    def column(self, col):
+        d = ColumnDesc()
+        _check(lib.flsgpu_table_column(self._h, col, C.byref(d)), "table_column")
+        return d
+
+    def rowgroup(self, rg):
+        d = RowgroupDesc()
+        _check(lib.flsgpu_table_rowgroup(self._h, rg, C.byref(d)), "table_rowgroup")
+        return d
+
+    def chunk(self, rg, col):
+        d = ChunkDesc()
+        _check(lib.flsgpu_table_chunk(self._h, rg, col, C.byref(d)), "table_chunk")
+        return d
+
+    def native_dtype(self, col):
+        d = self.column(col)
+        if d.is_float:
+            return np.float32 if d.phys_bits == 32 else np.float64
+        return np.dtype(f"{'i' if d.is_signed else 'u'}{d.phys_bits // 8}").type
+
+    def out_elems(self, n_rg):
+        return n_rg * self.vec_per_rowgroup * VEC
+
+    def stage(self, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_table_stage(self._h, rg_begin, n_rg, _vp(stream)), "table_stage")
+
+    def unstage(self):
+        _check(lib.flsgpu_table_unstage(self._h), "table_unstage")
+
+    def resident_bytes(self):
+        n = C.c_uint64()
+        _check(lib.flsgpu_table_resident_bytes(self._h, C.byref(n)), "resident_bytes")
+        return n.value
+
+    def decode_column(self, col, out_ptr, out_bytes, rg_begin=0, n_rg=None, out_type=0, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_decode_column(self._h, col, rg_begin, n_rg, out_type, _vp(out_ptr), C.c_uint64(out_bytes),
+                                        _vp(stream)), "decode_column")
+
+    def rowgroup_decode(self, rg, cols, out_ptrs, out_types=None, stream=0):
+        n = len(cols)
+        ca = (C.c_uint32 * n)(*cols)
+        pa = (C.c_void_p * n)(*[int(p) for p in out_ptrs])
+        ta = (C.c_int32 * n)(*(out_types or [0] * n))
+        _check(lib.flsgpu_rowgroup_decode(self._h, rg, ca, n, pa, ta, _vp(stream)), "rowgroup_decode")
+
+    def aggregate_column(self, col, result_ptr, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_aggregate_column(self._h, col, rg_begin, n_rg, _vp(result_ptr), _vp(stream)), "aggregate_column")
+
+    def scan_column_to_host(self, col, out_host_ptr, out_bytes, rg_begin=0, n_rg=None, out_type=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_scan_column_to_host(self._h, col, rg_begin, n_rg, out_type, _vp(out_host_ptr),
+                                              C.c_uint64(out_bytes)), "scan_column_to_host")
+
+    def valid_mask_slices(self, rg_begin=0, n_rg=None):
+        """(start, stop) element ranges of real tuples in the decode_column output layout."""
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        stride = self.vec_per_rowgroup * VEC
+        return [(r * stride, r * stride + self.rowgroup(rg_begin + r).n_tuples) for r in range(n_rg)]
+
+    def close(self):
+        if self._h:
+            lib.flsgpu_table_close(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        self.close()
+
+
+def init(device_ids=(0,)):
+    arr = (C.c_int * len(device_ids))(*device_ids)
+    _check(lib.flsgpu_init(len(device_ids), arr), "init")
+
+
+def agg_reset(ptr, stream=0):
+    _check(lib.flsgpu_agg_reset(_vp(ptr), _vp(stream)), "agg_reset")
+
+
+def sync(stream=0):
+    _check(lib.flsgpu_sync(_vp(stream)), "sync")
+
+
+def host_alloc(nbytes):
+    p = C.c_void_p()
+    _check(lib.flsgpu_host_alloc(C.c_uint64(nbytes), C.byref(p)), "host_alloc")
+    return p.value
+
+
+def host_free(ptr):
+    _check(lib.flsgpu_host_free(_vp(ptr)), "host_free")
+
+
+def launch_count():
+    return int(lib.flsgpu_launch_count())

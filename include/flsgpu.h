@@ -1,0 +1,144 @@
+/*
+ * flsgpu.h — C ABI of the B200 FastLanes decode engine (libflsgpu.so).
+ *
+ * This library sits UNDER the read_fls table function of the DuckDB extension: it replaces the absent
+ * third-party FastLanes library (reference CMakeLists.txt:56-67) plus the extension's materializer
+ * (reference src/include/reader/materializer/ **), i.e. layers L0+L1 of SURVEY.md section 1.  Every entry
+ * point cites the reference interface it stands in for.  POD only, no exceptions cross this boundary, every
+ * call returns 0 on success or a negative flsgpu_status; flsgpu_last_error() gives the message (thread local).
+ * There is no CPU fallback: decode entry points fail with FLSGPU_ERR_CUDA when no device is usable.
+ */
+#ifndef FLSGPU_H
+#define FLSGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "fls_format.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum flsgpu_status {
+	FLSGPU_OK = 0,
+	FLSGPU_ERR_INVALID = -1, /* bad argument / malformed container  (reference: InternalException, BinderException) */
+	FLSGPU_ERR_IO = -2,      /* file could not be read/written      (reference: std::runtime_error) */
+	FLSGPU_ERR_CUDA = -3,    /* CUDA runtime error, or no device */
+	FLSGPU_ERR_UNSUPPORTED = -4, /* encoding/type combination not implemented (reference fls_kernel.hpp:24-34) */
+	FLSGPU_ERR_CONVERSION = -5   /* destination type cannot hold the column   (reference fls_type_resolver.hpp:75-82) */
+} flsgpu_status;
+
+typedef struct flsgpu_table flsgpu_table;   /* replaces TableMetadata + fastlanes::TableReader (table_metadata.cpp:13-35) */
+typedef struct flsgpu_writer flsgpu_writer; /* replaces fastlanes::FileWriter/RowGroupWriter (fls_writer.cpp:271-284) */
+
+const char* flsgpu_last_error(void);
+const char* flsgpu_version(void);
+
+/* ---- device ------------------------------------------------------------------------------------------ */
+/* Select the devices this process will use (one process per GPU: n_devices = 1).  No reference counterpart. */
+int flsgpu_init(int n_devices, const int* device_ids);
+int flsgpu_device_count(int* out);
+
+/* ---- writer: COPY ... (FORMAT fls), reference src/writer/fls_writer.cpp -------------------------------- */
+typedef struct flsgpu_column_spec {
+	const char* name;
+	int32_t data_type;         /* fls_data_type */
+	int32_t decimal_precision; /* DECIMAL only; physical width INT16/32/64 by precision (writer/translation_utils.cpp:46-58) */
+	int32_t decimal_scale;
+	int32_t force_encoding;    /* fls_encoding, or -1: choose the smallest (encoding selection lives in the absent lib) */
+} flsgpu_column_spec;
+
+/* WithSchema/WithRowGroupSize (fls_writer.cpp:271-284); vec_per_rowgroup 0 -> 64 (fls_writer.hpp:14). */
+int flsgpu_writer_create(uint32_t n_columns, const flsgpu_column_spec* cols, uint32_t vec_per_rowgroup,
+                         flsgpu_writer** out);
+/* Sink (fls_writer.cpp:46-102): columns[i] points at n_tuples values of column i's PHYSICAL type.  Rows are
+ * buffered until a full row group exists; full row groups are encoded on n_threads host threads. */
+int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t n_tuples, int n_threads);
+/* Finalize (fls_writer.cpp:332-347): flush the tail row group and build the footer. */
+int flsgpu_writer_finish(flsgpu_writer* w);
+int flsgpu_writer_image(const flsgpu_writer* w, const void** bytes, uint64_t* size); /* valid until destroy */
+int flsgpu_writer_save(const flsgpu_writer* w, const char* path);
+void flsgpu_writer_destroy(flsgpu_writer* w);
+
+/* ---- table metadata: TableMetadata / SchemaBuilder / RowGroupStatistics ------------------------------- */
+int flsgpu_table_open(const char* path, flsgpu_table** out);                         /* table_metadata.cpp:13-16 */
+int flsgpu_table_open_memory(const void* bytes, uint64_t size, int copy, flsgpu_table** out);
+void flsgpu_table_close(flsgpu_table* t);
+
+typedef struct flsgpu_table_info {
+	uint32_t n_columns;
+	uint32_t n_rowgroups;
+	uint32_t vec_per_rowgroup;
+	uint32_t reserved;
+	uint64_t n_tuples;
+	uint64_t n_vectors;
+	uint64_t file_bytes;
+} flsgpu_table_info;
+int flsgpu_table_info_get(const flsgpu_table* t, flsgpu_table_info* out);
+int flsgpu_table_column(const flsgpu_table* t, uint32_t col, fls_column_desc* out);            /* schema_builder.cpp:179-243 */
+int flsgpu_table_rowgroup(const flsgpu_table* t, uint32_t rg, fls_rowgroup_desc* out);         /* fls_reader.cpp:129-138 */
+int flsgpu_table_chunk(const flsgpu_table* t, uint32_t rg, uint32_t col, fls_chunk_desc* out); /* row_group_statistics.cpp:60-127 */
+
+/* ---- staging: get_rowgroup_reader (fls_reader.cpp:615-618) -------------------------------------------- */
+/* Copy the compressed image of row groups [rg_begin, rg_begin+n_rg) to HBM (pinned host -> device, async on
+ * `stream`) and build the device descriptor tables.  No-op for row groups already resident. */
+int flsgpu_table_stage(flsgpu_table* t, uint32_t rg_begin, uint32_t n_rg, void* cuda_stream);
+int flsgpu_table_unstage(flsgpu_table* t);
+int flsgpu_table_resident_bytes(const flsgpu_table* t, uint64_t* out);
+
+/* ---- decode: DecodePhysicalColumns (fls_reader.cpp:436-472) + KernelTraits<Op>::Decode ------------------ */
+/* Destination physical type of a decoded column = DuckDB PhysicalType the materializer writes
+ * (fls_type_resolver.hpp:42-83).  Same-width copy or widening static_cast (CastNumeric, :22-33). */
+typedef enum flsgpu_out_type {
+	FLSGPU_OUT_NATIVE = 0, /* the column's own physical width */
+	FLSGPU_OUT_I8 = 1, FLSGPU_OUT_I16 = 2, FLSGPU_OUT_I32 = 3, FLSGPU_OUT_I64 = 4,
+	FLSGPU_OUT_U8 = 5, FLSGPU_OUT_U16 = 6, FLSGPU_OUT_U32 = 7, FLSGPU_OUT_U64 = 8,
+	FLSGPU_OUT_F32 = 9, FLSGPU_OUT_F64 = 10
+} flsgpu_out_type;
+
+/* Decode column `col` of row groups [rg_begin, rg_begin+n_rg) in ONE launch into out_dev (device memory,
+ * 16-byte aligned).  Row group r's vector v lands at element ((r-rg_begin)*vec_per_rowgroup + v)*1024: whole
+ * vectors are written, the caller exposes only n_tuples of each row group (fls_reader.cpp:429-431).
+ * out_capacity_bytes must cover n_rg*vec_per_rowgroup*1024 elements. Asynchronous on `stream`. */
+int flsgpu_decode_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type,
+                         void* out_dev, uint64_t out_capacity_bytes, void* cuda_stream);
+
+/* Per-row-group form used by the reader's TryInitializeScan (one row group per worker, fls_reader.cpp:337-355).
+ * out_ptrs[i] receives column col_ids[i]; pointers may be device memory or pinned host memory mapped for the
+ * device. */
+int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids, uint32_t n_cols,
+                           void* const* out_ptrs, const int32_t* out_types, void* cuda_stream);
+
+/* ---- fused decode + aggregate (SUM/COUNT/MIN/MAX over a scan) ---------------------------- */
+typedef struct flsgpu_agg_result { /* written to device memory, 64 bytes */
+	uint64_t sum_lo;  /* 128-bit two's complement sum (HUGEINT / DECIMAL(38) semantics, sum.cpp:161-210) */
+	uint64_t sum_hi;
+	uint64_t count;
+	int64_t min_val;  /* physical order of the column (signed or unsigned 64, raw IEEE for floats) */
+	int64_t max_val;
+	double fsum;      /* FLOAT/DOUBLE columns: sum in double (not order-stable, reported only) */
+	uint64_t reserved[2];
+} flsgpu_agg_result;
+/* Accumulates into *result_dev (caller zero-initialises with flsgpu_agg_reset). Asynchronous. */
+int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg,
+                            flsgpu_agg_result* result_dev, void* cuda_stream);
+int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream);
+
+/* ---- end to end from host buffers: what FastLanesReader::Scan hands to DuckDB -------------------------- */
+/* Stage (H2D) + decode + copy back (D2H) into pinned/pageable host memory `out_host`, pipelined in slabs of
+ * row groups over two streams.  Synchronous: returns when out_host is complete. */
+int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type,
+                               void* out_host, uint64_t out_capacity_bytes);
+
+int flsgpu_sync(void* cuda_stream);
+/* Pinned host allocations for staging / results (cudaHostAlloc). */
+int flsgpu_host_alloc(uint64_t bytes, void** out);
+int flsgpu_host_free(void* p);
+
+/* Launch counter: number of decode/aggregate kernels this process has launched (bench.py gpu_launches). */
+uint64_t flsgpu_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLSGPU_H */

@@ -1,0 +1,318 @@
+/*
+ * fls_oracle_scan.c — materializer, column decode, reference-shaped scan and aggregates of the CPU oracle.
+ * TEST INFRASTRUCTURE ONLY (see fls_oracle.h).
+ */
+#include "fls_oracle.h"
+
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* same numbering as flsgpu_out_type */
+enum { OUT_NATIVE = 0, OUT_I8, OUT_I16, OUT_I32, OUT_I64, OUT_U8, OUT_U16, OUT_U32, OUT_U64, OUT_F32, OUT_F64 };
+
+static int out_bits(int out_type, const fls_column_desc* c) {
+	switch (out_type) {
+	case OUT_NATIVE: return c->phys_bits;
+	case OUT_I8: case OUT_U8: return 8;
+	case OUT_I16: case OUT_U16: return 16;
+	case OUT_I32: case OUT_U32: case OUT_F32: return 32;
+	default: return 64;
+	}
+}
+
+static inline uint64_t load_src(const void* p, unsigned T, unsigned i, int is_signed) {
+	switch (T) {
+	case 8: return is_signed ? (uint64_t)(int64_t)((const int8_t*)p)[i] : ((const uint8_t*)p)[i];
+	case 16: return is_signed ? (uint64_t)(int64_t)((const int16_t*)p)[i] : ((const uint16_t*)p)[i];
+	case 32: return is_signed ? (uint64_t)(int64_t)((const int32_t*)p)[i] : ((const uint32_t*)p)[i];
+	default: return ((const uint64_t*)p)[i];
+	}
+}
+
+/*
+ * KernelTraits<Op>::Decode -> NumericHelper::{CopyVector,UntransposeBlock} (fls_type_resolver.hpp:120-165):
+ * same physical type -> fastlanes::copy; otherwise CastNumeric's plain static_cast loop (:22-33), with integer
+ * columns of signed src_type viewed as signed first (unffor_kernel.hpp:16-25) so that widening sign-extends.
+ * A transposed scratch goes through untranspose_i, via a 1024-element temporary when a cast follows (:206-222).
+ */
+int fls_oracle_materialize(const fls_oracle_table* t, uint32_t col, const void* scratch, int is_transposed, int out_type,
+                           void* out) {
+	const fls_column_desc* c = &t->columns[col];
+	const unsigned T = c->phys_bits;
+	const int ob = out_bits(out_type, c);
+	const int out_float = out_type == OUT_F32 || out_type == OUT_F64 || (out_type == OUT_NATIVE && c->is_float);
+	uint64_t tmp[1024];
+	const void* src = scratch;
+	if (is_transposed) {
+		if ((unsigned)ob == T && out_float == c->is_float) {
+			fls_oracle_untranspose(scratch, T, out);
+			return 0;
+		}
+		fls_oracle_untranspose(scratch, T, tmp);
+		src = tmp;
+	}
+	if ((unsigned)ob == T && out_float == c->is_float) {
+		memcpy(out, src, 1024u * T / 8);
+		return 0;
+	}
+	if ((unsigned)ob < T) {
+		return -5; /* narrowing is never requested by the reader: the bound type is the promoted one */
+	}
+	if (c->is_float) {
+		if (T == 32 && out_type == OUT_F64) {
+			for (unsigned i = 0; i < 1024; ++i) {
+				((double*)out)[i] = (double)((const float*)src)[i];
+			}
+			return 0;
+		}
+		return -5;
+	}
+	if (out_float) {
+		for (unsigned i = 0; i < 1024; ++i) {
+			const uint64_t v = load_src(src, T, i, c->is_signed);
+			const double d = c->is_signed ? (double)(int64_t)v : (double)v;
+			if (ob == 32) {
+				((float*)out)[i] = c->is_signed ? (float)(int64_t)v : (float)v;
+			} else {
+				((double*)out)[i] = d;
+			}
+		}
+		return 0;
+	}
+	for (unsigned i = 0; i < 1024; ++i) {
+		const uint64_t v = load_src(src, T, i, c->is_signed);
+		switch (ob) {
+		case 16: ((uint16_t*)out)[i] = (uint16_t)v; break;
+		case 32: ((uint32_t*)out)[i] = (uint32_t)v; break;
+		default: ((uint64_t*)out)[i] = v; break;
+		}
+	}
+	return 0;
+}
+
+/* ---- threaded drivers ---------------------------------------------------------------------------------- */
+typedef struct job {
+	const fls_oracle_table* t;
+	const uint32_t* cols;
+	uint32_t n_cols, rg_begin, n_rg;
+	int out_type;
+	uint8_t* out; /* decode_column only */
+	int mode;     /* 0: decode column into out; 1: reference-shaped scan */
+	volatile uint32_t* next;
+	int rc;
+	uint64_t bytes, checksum;
+} job;
+
+static uint64_t fold(const uint64_t* p, size_t n_words, uint64_t h) {
+	for (size_t i = 0; i < n_words; ++i) {
+		h = (h ^ p[i]) * 0x100000001B3ull;
+	}
+	return h;
+}
+
+static void* worker(void* arg) {
+	job* j = (job*)arg;
+	const fls_oracle_table* t = j->t;
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	uint64_t scratch[1024];
+	/* one 2048-row DuckDB chunk buffer per projected column (vector_size.hpp:16) */
+	uint64_t* chunkbuf = j->mode ? (uint64_t*)malloc((size_t)j->n_cols * 2048 * 8) : NULL;
+	for (;;) {
+		/* TryAssignNextRowGroup: row groups are handed out one at a time (fls_reader.cpp:337-355) */
+		const uint32_t r = __atomic_fetch_add(j->next, 1, __ATOMIC_RELAXED);
+		if (r >= j->n_rg) {
+			break;
+		}
+		const uint32_t rg = j->rg_begin + r;
+		const uint32_t n_vec = t->rowgroups[rg].n_vec;
+		if (!j->mode) {
+			const fls_column_desc* c = &t->columns[j->cols[0]];
+			const size_t esz = (size_t)out_bits(j->out_type, c) / 8;
+			for (uint32_t v = 0; v < n_vec; ++v) {
+				int tr = 0;
+				int rc = fls_oracle_decode_vector(t, rg, j->cols[0], v, scratch, &tr);
+				if (!rc) {
+					rc = fls_oracle_materialize(t, j->cols[0], scratch, tr, j->out_type,
+					                            j->out + ((size_t)r * vpr + v) * 1024 * esz);
+				}
+				if (rc) {
+					j->rc = rc;
+					return NULL;
+				}
+			}
+		} else {
+			/* Scan: GetScanBatch takes <= 2 vectors per call (fls_reader.cpp:422-434), DecodePhysicalColumns visits
+			 * every projected column per vector (:436-472) with Pass::First / Pass::Second destinations */
+			for (uint32_t v0 = 0; v0 < n_vec; v0 += 2) {
+				const uint32_t nv = n_vec - v0 < 2 ? n_vec - v0 : 2;
+				for (uint32_t b = 0; b < nv; ++b) {
+					for (uint32_t ci = 0; ci < j->n_cols; ++ci) {
+						const fls_column_desc* c = &t->columns[j->cols[ci]];
+						const size_t esz = (size_t)c->phys_bits / 8;
+						uint8_t* dst = (uint8_t*)(chunkbuf + (size_t)ci * 2048) + (size_t)b * 1024 * esz;
+						int tr = 0;
+						int rc = fls_oracle_decode_vector(t, rg, j->cols[ci], v0 + b, scratch, &tr);
+						if (!rc) {
+							rc = fls_oracle_materialize(t, j->cols[ci], scratch, tr, OUT_NATIVE, dst);
+						}
+						if (rc) {
+							j->rc = rc;
+							free(chunkbuf);
+							return NULL;
+						}
+					}
+				}
+				for (uint32_t ci = 0; ci < j->n_cols; ++ci) {
+					const size_t esz = (size_t)t->columns[j->cols[ci]].phys_bits / 8;
+					const size_t nbytes = (size_t)nv * 1024 * esz;
+					j->checksum = fold(chunkbuf + (size_t)ci * 2048, nbytes / 8, j->checksum);
+					j->bytes += nbytes;
+				}
+			}
+		}
+	}
+	free(chunkbuf);
+	return NULL;
+}
+
+static int run_jobs(job* proto, int n_threads) {
+	if (n_threads < 1) {
+		n_threads = 1;
+	}
+	volatile uint32_t next = 0;
+	job* jobs = (job*)calloc((size_t)n_threads, sizeof(job));
+	pthread_t* th = (pthread_t*)calloc((size_t)n_threads, sizeof(pthread_t));
+	for (int i = 0; i < n_threads; ++i) {
+		jobs[i] = *proto;
+		jobs[i].next = &next;
+		jobs[i].checksum = 0xcbf29ce484222325ull + (uint64_t)i;
+		if (n_threads > 1) {
+			pthread_create(&th[i], NULL, worker, &jobs[i]);
+		}
+	}
+	if (n_threads == 1) {
+		worker(&jobs[0]);
+	}
+	int rc = 0;
+	proto->bytes = 0;
+	proto->checksum = 0;
+	for (int i = 0; i < n_threads; ++i) {
+		if (n_threads > 1) {
+			pthread_join(th[i], NULL);
+		}
+		if (jobs[i].rc) {
+			rc = jobs[i].rc;
+		}
+		proto->bytes += jobs[i].bytes;
+		proto->checksum ^= jobs[i].checksum;
+	}
+	free(jobs);
+	free(th);
+	return rc;
+}
+
+int fls_oracle_decode_column(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int out_type,
+                             void* out, int n_threads) {
+	if (col >= t->header.n_columns || rg_begin + n_rg > t->header.n_rowgroups) {
+		return -1;
+	}
+	job j;
+	memset(&j, 0, sizeof(j));
+	j.t = t;
+	j.cols = &col;
+	j.n_cols = 1;
+	j.rg_begin = rg_begin;
+	j.n_rg = n_rg;
+	j.out_type = out_type;
+	j.out = (uint8_t*)out;
+	j.mode = 0;
+	return run_jobs(&j, n_threads);
+}
+
+int fls_oracle_scan(const fls_oracle_table* t, const uint32_t* cols, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg,
+                    int n_threads, uint64_t* decoded_bytes, uint64_t* checksum) {
+	if (rg_begin + n_rg > t->header.n_rowgroups) {
+		return -1;
+	}
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		if (cols[i] >= t->header.n_columns) {
+			return -1;
+		}
+	}
+	job j;
+	memset(&j, 0, sizeof(j));
+	j.t = t;
+	j.cols = cols;
+	j.n_cols = n_cols;
+	j.rg_begin = rg_begin;
+	j.n_rg = n_rg;
+	j.mode = 1;
+	const int rc = run_jobs(&j, n_threads);
+	if (decoded_bytes) {
+		*decoded_bytes = j.bytes;
+	}
+	if (checksum) {
+		*checksum = j.checksum;
+	}
+	return rc;
+}
+
+/* SUM as 128-bit two's complement (DuckDB SUM(BIGINT)->HUGEINT, sum.cpp:161-210), COUNT, MIN, MAX over the valid
+ * tuples of the range. */
+int fls_oracle_aggregate(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* sum_lo,
+                         uint64_t* sum_hi, uint64_t* count, int64_t* min_val, int64_t* max_val, double* fsum) {
+	if (col >= t->header.n_columns || rg_begin + n_rg > t->header.n_rowgroups) {
+		return -1;
+	}
+	const fls_column_desc* c = &t->columns[col];
+	const unsigned T = c->phys_bits;
+	unsigned __int128 acc = 0;
+	uint64_t n = 0;
+	int first = 1;
+	int64_t mn = 0, mx = 0;
+	double fs = 0.0;
+	uint64_t scratch[1024], nat[1024];
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		const uint32_t rg = rg_begin + r;
+		uint32_t left = t->rowgroups[rg].n_tuples;
+		for (uint32_t v = 0; v < t->rowgroups[rg].n_vec; ++v) {
+			int tr = 0;
+			int rc = fls_oracle_decode_vector(t, rg, col, v, scratch, &tr);
+			if (!rc) {
+				rc = fls_oracle_materialize(t, col, scratch, tr, OUT_NATIVE, nat);
+			}
+			if (rc) {
+				return rc;
+			}
+			const uint32_t valid = left < 1024 ? left : 1024;
+			left -= valid;
+			for (uint32_t i = 0; i < valid; ++i) {
+				if (c->is_float) {
+					double x = T == 32 ? (double)((const float*)nat)[i] : ((const double*)nat)[i];
+					fs += x;
+					continue;
+				}
+				const uint64_t u = load_src(nat, T, i, c->is_signed);
+				if (c->is_signed) {
+					acc += (unsigned __int128)(__int128)(int64_t)u;
+					if (first || (int64_t)u < mn) mn = (int64_t)u;
+					if (first || (int64_t)u > mx) mx = (int64_t)u;
+				} else {
+					acc += u;
+					if (first || u < (uint64_t)mn) mn = (int64_t)u;
+					if (first || u > (uint64_t)mx) mx = (int64_t)u;
+				}
+				first = 0;
+			}
+			n += valid;
+		}
+	}
+	*sum_lo = (uint64_t)acc;
+	*sum_hi = (uint64_t)(acc >> 64);
+	*count = n;
+	*min_val = mn;
+	*max_val = mx;
+	*fsum = fs;
+	return 0;
+}

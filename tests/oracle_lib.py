@@ -1,0 +1,85 @@
+"""ctypes wrapper of oracle/liboracle.so — the CPU restatement used as the CHECKER in tests (never by the product)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+LIB = os.path.join(ORACLE_DIR, "liboracle.so")
+
+
+def build():
+    srcs = ["fls_oracle.c", "fls_oracle_scan.c", "fls_oracle_tmpl.h", "fls_oracle.h"]
+    stale = not os.path.exists(LIB) or any(
+        os.path.getmtime(os.path.join(ORACLE_DIR, s)) > os.path.getmtime(LIB) for s in srcs)
+    if stale:
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
+
+
+build()
+lib = C.CDLL(LIB)
+
+
+class OracleTable(C.Structure):
+    _fields_ = [("bytes", C.c_void_p), ("size", C.c_uint64), ("header", C.c_uint8 * 64), ("columns", C.c_void_p),
+                ("rowgroups", C.c_void_p), ("chunks", C.c_void_p)]
+
+
+lib.fls_oracle_alp_decode_f64.restype = C.c_double
+lib.fls_oracle_alp_decode_f64.argtypes = [C.c_int64, C.c_int, C.c_int]
+lib.fls_oracle_alp_decode_f32.restype = C.c_float
+lib.fls_oracle_alp_decode_f32.argtypes = [C.c_int32, C.c_int, C.c_int]
+
+
+class Oracle:
+    def __init__(self, image):
+        self.image = np.ascontiguousarray(image, dtype=np.uint8)
+        self.t = OracleTable()
+        rc = lib.fls_oracle_open(C.c_void_p(self.image.ctypes.data), C.c_uint64(self.image.size), C.byref(self.t))
+        if rc:
+            raise RuntimeError(f"fls_oracle_open failed: {rc}")
+
+    def decode_column(self, col, rg_begin, n_rg, out_type, out_dtype, vec_per_rg, n_threads=1):
+        out = np.zeros(n_rg * vec_per_rg * 1024, dtype=out_dtype)
+        rc = lib.fls_oracle_decode_column(C.byref(self.t), col, rg_begin, n_rg, out_type, C.c_void_p(out.ctypes.data),
+                                          n_threads)
+        if rc:
+            raise RuntimeError(f"fls_oracle_decode_column failed: {rc}")
+        return out
+
+    def scan(self, cols, rg_begin, n_rg, n_threads):
+        ca = (C.c_uint32 * len(cols))(*cols)
+        nbytes, cks = C.c_uint64(), C.c_uint64()
+        rc = lib.fls_oracle_scan(C.byref(self.t), ca, len(cols), rg_begin, n_rg, n_threads, C.byref(nbytes), C.byref(cks))
+        if rc:
+            raise RuntimeError(f"fls_oracle_scan failed: {rc}")
+        return nbytes.value, cks.value
+
+    def aggregate(self, col, rg_begin, n_rg):
+        lo, hi, cnt = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        mn, mx, fs = C.c_int64(), C.c_int64(), C.c_double()
+        rc = lib.fls_oracle_aggregate(C.byref(self.t), col, rg_begin, n_rg, C.byref(lo), C.byref(hi), C.byref(cnt),
+                                      C.byref(mn), C.byref(mx), C.byref(fs))
+        if rc:
+            raise RuntimeError(f"fls_oracle_aggregate failed: {rc}")
+        s = (hi.value << 64) | lo.value
+        if s >= 1 << 127:
+            s -= 1 << 128
+        return dict(sum=s, count=cnt.value, min=mn.value, max=mx.value, fsum=fs.value)
+
+
+def fl_index(row, lane):
+    return lib.fls_oracle_index(row, lane)
+
+
+def fl_transpose(pos):
+    return lib.fls_oracle_transpose(pos)
+
+
+def unpack(packed, T, W):
+    packed = np.ascontiguousarray(packed)
+    out = np.zeros(1024, dtype=np.dtype(f"u{T // 8}"))
+    lib.fls_oracle_unpack(C.c_void_p(packed.ctypes.data), T, W, C.c_void_p(out.ctypes.data))
+    return out
