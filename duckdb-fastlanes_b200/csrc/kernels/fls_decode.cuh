@@ -1,0 +1,207 @@
+// fls_decode.cuh — the fused decode kernels (sm_100a).
+//
+// Work unit: one warp decodes one 1024-value vector end to end: TMA bulk copy of the packed blob into the warp's
+// shared-memory slot -> register unpack specialised on the bit width -> encoding epilogue (FOR base, per-lane
+// running sum + transposition, ALP multiply, ALP-RD glue, patches) -> coalesced / 128-bit stores.  This fuses what
+// the reference does in two passes (FastLanes library decode into scratch, then the materializer's copy / cast /
+// untranspose: reference src/reader/fls_reader.cpp:436-472, src/include/reader/materializer/kernels/*.hpp).
+//
+// Kernels are persistent: each warp walks vectors gw, gw + n_warps, ... in batches of 32; lane k of the warp
+// fetches the descriptor (chunk + fls_vec_meta entry point) of the batch's k-th vector so that descriptor latency
+// is paid once per 32 vectors, and the warp keeps n_slots TMA copies in flight ahead of the vector it is decoding.
+#pragma once
+#include "fls_device.h"
+#include "fls_store.cuh"
+
+namespace flsk {
+
+__constant__ double c_fact_d[19] = {1e0, 1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,
+                                    1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18};
+__constant__ double c_frac_d[21] = {1.0,
+                                    0.1,
+                                    0.01,
+                                    0.001,
+                                    0.0001,
+                                    0.00001,
+                                    0.000001,
+                                    0.0000001,
+                                    0.00000001,
+                                    0.000000001,
+                                    0.0000000001,
+                                    0.00000000001,
+                                    0.000000000001,
+                                    0.0000000000001,
+                                    0.00000000000001,
+                                    0.000000000000001,
+                                    0.0000000000000001,
+                                    0.00000000000000001,
+                                    0.000000000000000001,
+                                    0.0000000000000000001,
+                                    0.00000000000000000001};
+__constant__ float c_fact_f[11] = {1.0F,       10.0F,       100.0F,       1000.0F,       10000.0F,      100000.0F,
+                                   1000000.0F, 10000000.0F, 100000000.0F, 1000000000.0F, 10000000000.0F};
+__constant__ float c_frac_f[11] = {1.0F,      0.1F,       0.01F,       0.001F,       0.0001F,      0.00001F,
+                                   0.000001F, 0.0000001F, 0.00000001F, 0.000000001F, 0.0000000001F};
+
+constexpr int kWarpsPerCta = 8;
+
+// Everything a warp needs to decode one vector; filled per lane, broadcast with shuffles.
+struct VecDesc {
+	const uint8_t* blob;
+	const FlsChunkDev* ch;
+	uint64_t base;
+	uint32_t aux_off;
+	uint32_t bytes; // TMA bytes of the blob (0: nothing to copy)
+	uint32_t misc;  // aux_cnt | width << 16 | encoding << 24
+	uint32_t misc2; // width2 | e << 8 | f << 16 | vec_in_chunk << 24 (low 8 bits only, CROSS_RLE uses full value below)
+	uint32_t vec_in_chunk;
+};
+
+__device__ __forceinline__ VecDesc shfl_desc(const VecDesc& d, int src) {
+	VecDesc r;
+	r.blob = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)d.blob, src);
+	r.ch = (const FlsChunkDev*)__shfl_sync(0xffffffffu, (unsigned long long)d.ch, src);
+	r.base = __shfl_sync(0xffffffffu, (unsigned long long)d.base, src);
+	r.aux_off = __shfl_sync(0xffffffffu, d.aux_off, src);
+	r.bytes = __shfl_sync(0xffffffffu, d.bytes, src);
+	r.misc = __shfl_sync(0xffffffffu, d.misc, src);
+	r.misc2 = __shfl_sync(0xffffffffu, d.misc2, src);
+	r.vec_in_chunk = __shfl_sync(0xffffffffu, d.vec_in_chunk, src);
+	return r;
+}
+
+template <int T>
+__device__ __forceinline__ uint32_t blob_bytes(uint32_t enc, uint32_t w, uint32_t w2) {
+	switch (enc) {
+	case FLS_ENC_UNCOMPRESSED: return 128u * T;
+	case FLS_ENC_CONSTANT:
+	case FLS_ENC_CROSS_RLE: return 0u;
+	case FLS_ENC_DELTA:
+	case FLS_ENC_RLE: return 128u + 128u * w;
+	case FLS_ENC_ALP_RD: return 128u * (w + w2);
+	default: return 128u * w;
+	}
+}
+
+// Lane-parallel descriptor fetch for vector v (v >= total or not of this kernel's family -> bytes = 0, ch = null).
+template <int T>
+__device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
+	VecDesc d;
+	d.blob = nullptr;
+	d.ch = nullptr;
+	d.base = 0;
+	d.aux_off = d.bytes = d.misc = d.misc2 = d.vec_in_chunk = 0;
+	if (v < L.total_vecs) {
+		const uint32_t r = v / L.vec_per_rg, vi = v - r * L.vec_per_rg;
+		const FlsChunkDev* ch = L.chunks + (size_t)r * L.chunk_stride;
+		const uint32_t enc = ch->encoding;
+		if (vi < ch->n_vec && ((L.family_mask >> enc) & 1u)) {
+			const uint4* mp = reinterpret_cast<const uint4*>(ch->meta + vi);
+			const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
+			// fls_vec_meta: base(8) data_off16(4) aux_off(4) | aux_cnt(2) width(1) width2(1) e(1) f(1) n_valid(2) reserved(8)
+			d.base = ((uint64_t)m0.y << 32) | m0.x;
+			d.aux_off = m0.w;
+			const uint32_t aux_cnt = m1.x & 0xffffu, w = (m1.x >> 16) & 0xffu, w2 = m1.x >> 24;
+			d.misc = aux_cnt | (w << 16) | (enc << 24);
+			d.misc2 = w2 | ((m1.y & 0xffffu) << 8);
+			d.vec_in_chunk = vi;
+			d.bytes = blob_bytes<T>(enc, w, w2);
+			d.blob = ch->data + (size_t)m0.z * 16;
+			d.ch = ch;
+		}
+	}
+	return d;
+}
+
+template <int T>
+__device__ __forceinline__ void load_elem(const uint8_t* base, uint32_t idx, uint32_t& lo, uint32_t& hi) {
+	hi = 0;
+	if constexpr (T == 8) {
+		lo = __ldg(base + idx);
+	} else if constexpr (T == 16) {
+		lo = __ldg(reinterpret_cast<const uint16_t*>(base) + idx);
+	} else if constexpr (T == 32) {
+		lo = __ldg(reinterpret_cast<const uint32_t*>(base) + idx);
+	} else {
+		const uint2 q = __ldg(reinterpret_cast<const uint2*>(base) + idx);
+		lo = q.x;
+		hi = q.y;
+	}
+}
+
+// out[pos[k]] = exception[k]  (alp.hpp:401-404; slpatch / frequency patches)
+template <int T, int OB>
+__device__ __forceinline__ void patch_exceptions(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv) {
+	const uint32_t n = d.misc & 0xffffu;
+	if (n == 0) {
+		return;
+	}
+	__syncwarp();
+	const uint16_t* pos = reinterpret_cast<const uint16_t*>(d.ch->aux1) + d.aux_off;
+	for (uint32_t k = lane; k < n; k += 32) {
+		uint32_t lo, hi;
+		load_elem<T>(d.ch->aux0, d.aux_off + k, lo, hi);
+		store_one<T, OB>(out_vec, __ldg(pos + k), lo, hi, conv);
+	}
+}
+
+// logical start of the chain that FastLanes lane `lane` decodes in a DELTA vector
+__device__ __forceinline__ int chain_l0(int lane) {
+	return (lane & 15) * 64 + fl_order((lane >> 4) & 7) * 8;
+}
+
+template <int T, int OB>
+__device__ __forceinline__ void fill_constant(uint8_t* out_vec, int lane, uint32_t lo, uint32_t hi, uint32_t conv) {
+	convert_val<T, OB>(lo, hi, conv);
+	uint32_t w[4];
+	if constexpr (OB == 8) {
+		w[0] = w[2] = lo;
+		w[1] = w[3] = hi;
+	} else if constexpr (OB == 4) {
+		w[0] = w[1] = w[2] = w[3] = lo;
+	} else if constexpr (OB == 2) {
+		w[0] = w[1] = w[2] = w[3] = (lo & 0xffffu) * 0x00010001u;
+	} else {
+		w[0] = w[1] = w[2] = w[3] = (lo & 0xffu) * 0x01010101u;
+	}
+#pragma unroll
+	for (int it = 0; it < OB * 2; ++it) { // 1024*OB bytes / 16 / 32
+		st_cs_v4(out_vec + (size_t)(it * 32 + lane) * 16, w[0], w[1], w[2], w[3]);
+	}
+}
+
+// dec_cross_rle_opr: starts[] is the exclusive prefix sum of the run lengths (built at stage time).
+template <int T, int OB>
+__device__ __forceinline__ void decode_cross_rle(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv) {
+	const uint32_t* starts = reinterpret_cast<const uint32_t*>(d.ch->aux1);
+	const uint32_t n_runs = d.ch->aux_count;
+	const uint32_t g0 = d.vec_in_chunk * 1024u;
+	// first run of this vector (uniform binary search): largest r with starts[r] <= g0
+	uint32_t lo_r = 0, hi_r = n_runs;
+	while (hi_r - lo_r > 1) {
+		const uint32_t mid = (lo_r + hi_r) >> 1;
+		if (__ldg(starts + mid) <= g0) {
+			lo_r = mid;
+		} else {
+			hi_r = mid;
+		}
+	}
+	const uint32_t r_first = lo_r;
+	for (int it = 0; it < 32; ++it) {
+		const uint32_t gi = g0 + it * 32 + lane;
+		uint32_t a = r_first, b = min(n_runs, r_first + 1025u);
+		while (b - a > 1) {
+			const uint32_t mid = (a + b) >> 1;
+			if (__ldg(starts + mid) <= gi) {
+				a = mid;
+			} else {
+				b = mid;
+			}
+		}
+		uint32_t lo, hi;
+		load_elem<T>(d.ch->aux0, a, lo, hi);
+		store_one<T, OB>(out_vec, it * 32 + lane, lo, hi, conv);
+	}
+}
+
+} // namespace flsk

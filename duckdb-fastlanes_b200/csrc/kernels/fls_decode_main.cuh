@@ -1,0 +1,279 @@
+// fls_decode_main.cuh — per-vector decode bodies of the main kernel family (T-lane encodings) and the kernel itself.
+#pragma once
+#include "fls_decode.cuh"
+#include "fls_decode_gather.cuh"
+
+namespace flsk {
+
+// ---- T in {8,16,32} ------------------------------------------------------------------------------------------------------
+template <int T, int OB>
+__device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane,
+                                              uint32_t conv) {
+	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
+	constexpr uint32_t TMASK = T == 32 ? 0xffffffffu : ((1u << (T & 31)) - 1u);
+	switch (enc) {
+	case FLS_ENC_UNCOMPRESSED: copy_out_linear<T, OB, false>(slot, out_vec, lane, conv); return;
+	case FLS_ENC_CONSTANT: fill_constant<T, OB>(out_vec, lane, (uint32_t)d.ch->const_val, 0, conv); return;
+	case FLS_ENC_CROSS_RLE: decode_cross_rle<T, OB>(out_vec, d, lane, conv); return;
+	default: break;
+	}
+	uint32_t v[32];
+	const uint32_t base = (uint32_t)d.base;
+	if (enc == FLS_ENC_DELTA) {
+		// [128 B lane bases][packed deltas]: per-lane running sum (no cross-lane dependency), then transposition
+		const uint32_t* s32 = reinterpret_cast<const uint32_t*>(slot);
+		unpack_small_dispatch<T>((int)W, s32 + 32, lane, v);
+		const uint32_t bw = s32[lane];
+		uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
+		if constexpr (T == 32) {
+			uint32_t acc = bw;
+#pragma unroll
+			for (int j = 0; j < 32; ++j) {
+				acc += v[j] + base;
+				v[j] = acc;
+			}
+			const int g0 = chain_l0(lane) >> 2; // 4 elements per 16-byte granule
+#pragma unroll
+			for (int q = 0; q < 8; ++q) {
+				*reinterpret_cast<uint4*>(stage + (size_t)swz<T>(g0 + q) * 16) =
+				    make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+			}
+		} else if constexpr (T == 16) {
+#pragma unroll
+			for (int h = 0; h < 2; ++h) {
+				uint32_t acc = (bw >> (16 * h)) & 0xffffu;
+#pragma unroll
+				for (int row = 0; row < 16; ++row) {
+					acc += v[2 * row + h] + base;
+					v[2 * row + h] = acc & 0xffffu;
+				}
+				const int g0 = chain_l0(2 * lane + h) >> 3; // 8 elements per granule
+#pragma unroll
+				for (int q = 0; q < 2; ++q) {
+					uint32_t w4[4];
+#pragma unroll
+					for (int m = 0; m < 4; ++m) {
+						w4[m] = v[2 * (8 * q + 2 * m) + h] | (v[2 * (8 * q + 2 * m + 1) + h] << 16);
+					}
+					*reinterpret_cast<uint4*>(stage + (size_t)swz<T>(g0 + q) * 16) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+				}
+			}
+		} else {
+#pragma unroll
+			for (int b = 0; b < 4; ++b) {
+				uint32_t acc = (bw >> (8 * b)) & 0xffu;
+				uint32_t w2[2] = {0, 0};
+#pragma unroll
+				for (int row = 0; row < 8; ++row) {
+					acc += v[4 * row + b] + base;
+					w2[row >> 2] |= (acc & 0xffu) << (8 * (row & 3));
+				}
+				const int l0 = chain_l0(4 * lane + b); // byte offset == element offset
+				*reinterpret_cast<uint2*>(stage + (size_t)swz<T>(l0 >> 4) * 16 + (l0 & 8)) = make_uint2(w2[0], w2[1]);
+			}
+		}
+		(void)st32;
+		__syncwarp();
+		copy_out_linear<T, OB, true>(stage, out_vec, lane, conv);
+		return;
+	}
+	// FFOR family / ALP / ALP_RD: packed blob starts at the slot
+	unpack_small_dispatch<T>((int)W, reinterpret_cast<const uint32_t*>(slot), lane, v);
+	if constexpr (T == 32) {
+		if (enc == FLS_ENC_ALP) { // alp.hpp:129-134: (float)digit * (float)FACT[f] * FRAC[e], two roundings, no FMA
+			const float fa = c_fact_f[(d.misc2 >> 16) & 0xffu], fr = c_frac_f[(d.misc2 >> 8) & 0xffu];
+#pragma unroll
+			for (int j = 0; j < 32; ++j) {
+				const float x = __int2float_rn((int32_t)(v[j] + base));
+				v[j] = __float_as_uint(__fmul_rn(__fmul_rn(x, fa), fr));
+			}
+		} else if (enc == FLS_ENC_ALP_RD) { // alprd.hpp:222-226
+			uint32_t left[32];
+			const uint32_t W2 = d.misc2 & 0xffu;
+			unpack_small_dispatch<T>((int)W2, reinterpret_cast<const uint32_t*>(slot) + 32 * W, lane, left);
+			const uint4 dq = *reinterpret_cast<const uint4*>(d.ch->rd_dict);
+			const uint32_t dw[4] = {dq.x, dq.y, dq.z, dq.w};
+#pragma unroll
+			for (int j = 0; j < 32; ++j) {
+				const uint32_t code = left[j] & 7u;
+				const uint32_t pair = code < 4 ? (code < 2 ? dw[0] : dw[1]) : (code < 6 ? dw[2] : dw[3]);
+				const uint32_t key = (code & 1u) ? (pair >> 16) : (pair & 0xffffu);
+				v[j] |= key << W;
+			}
+		} else {
+#pragma unroll
+			for (int j = 0; j < 32; ++j) {
+				v[j] += base;
+			}
+		}
+	} else {
+#pragma unroll
+		for (int j = 0; j < 32; ++j) {
+			v[j] = (v[j] + base) & TMASK;
+		}
+	}
+	store_direct<T, OB>(out_vec, lane, v, conv);
+	patch_exceptions<T, OB>(out_vec, d, lane, conv);
+}
+
+// ---- T = 64 --------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane) {
+	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
+	switch (enc) {
+	case FLS_ENC_UNCOMPRESSED: copy_out_linear<64, 8, false>(slot, out_vec, lane, 0); return;
+	case FLS_ENC_CONSTANT:
+		fill_constant<64, 8>(out_vec, lane, (uint32_t)d.ch->const_val, (uint32_t)(d.ch->const_val >> 32), 0);
+		return;
+	case FLS_ENC_CROSS_RLE: decode_cross_rle<64, 8>(out_vec, d, lane, 0); return;
+	default: break;
+	}
+	uint32_t lo[32], hi[32];
+	const uint32_t blo = (uint32_t)d.base, bhi = (uint32_t)(d.base >> 32);
+	if (enc == FLS_ENC_DELTA) {
+		unpack_64_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot) + 32, lane, lo, hi);
+		// thread (l = lane&15, h = lane>>4) owns rows 32h..32h+31 of lane l: local sums, one shuffle to stitch halves
+		uint64_t sum = 0;
+#pragma unroll
+		for (int j = 0; j < 32; ++j) {
+			sum += (((uint64_t)hi[j] << 32) | lo[j]) + d.base;
+		}
+		const uint64_t lane_base = reinterpret_cast<const uint64_t*>(slot)[lane & 15];
+		const uint64_t first_half = __shfl_sync(0xffffffffu, sum, lane & 15);
+		uint64_t acc = lane_base + ((lane >> 4) ? first_half : 0ull);
+		const int g0 = (chain_l0(lane & 15) + 32 * (lane >> 4)) >> 1; // 2 elements per granule
+#pragma unroll
+		for (int q = 0; q < 16; ++q) {
+			acc += (((uint64_t)hi[2 * q] << 32) | lo[2 * q]) + d.base;
+			const uint64_t a0 = acc;
+			acc += (((uint64_t)hi[2 * q + 1] << 32) | lo[2 * q + 1]) + d.base;
+			*reinterpret_cast<uint4*>(stage + (size_t)swz<64>(g0 + q) * 16) =
+			    make_uint4((uint32_t)a0, (uint32_t)(a0 >> 32), (uint32_t)acc, (uint32_t)(acc >> 32));
+		}
+		__syncwarp();
+		copy_out_linear<64, 8, true>(stage, out_vec, lane, 0);
+		return;
+	}
+	unpack_64_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot), lane, lo, hi);
+	if (enc == FLS_ENC_ALP) { // (double)digit * (double)FACT[f] * FRAC[e]
+		const double fa = c_fact_d[(d.misc2 >> 16) & 0xffu], fr = c_frac_d[(d.misc2 >> 8) & 0xffu];
+#pragma unroll
+		for (int j = 0; j < 32; ++j) {
+			const uint64_t u = ((((uint64_t)hi[j]) << 32) | lo[j]) + d.base;
+			const double x = __dmul_rn(__dmul_rn(__ll2double_rn((long long)u), fa), fr);
+			const long long b = __double_as_longlong(x);
+			lo[j] = (uint32_t)b;
+			hi[j] = (uint32_t)(b >> 32);
+		}
+	} else if (enc == FLS_ENC_ALP_RD) {
+		uint32_t llo[32], lhi[32];
+		const uint32_t W2 = d.misc2 & 0xffu;
+		unpack_64_dispatch((int)W2, reinterpret_cast<const uint32_t*>(slot) + 32 * W, lane, llo, lhi);
+		const uint4 dq = *reinterpret_cast<const uint4*>(d.ch->rd_dict);
+		const uint32_t dw[4] = {dq.x, dq.y, dq.z, dq.w};
+#pragma unroll
+		for (int j = 0; j < 32; ++j) {
+			const uint32_t code = llo[j] & 7u;
+			const uint32_t pair = code < 4 ? (code < 2 ? dw[0] : dw[1]) : (code < 6 ? dw[2] : dw[3]);
+			const uint64_t key = (code & 1u) ? (pair >> 16) : (pair & 0xffffu);
+			const uint64_t u = ((((uint64_t)hi[j]) << 32) | lo[j]) | (key << W);
+			lo[j] = (uint32_t)u;
+			hi[j] = (uint32_t)(u >> 32);
+		}
+		(void)lhi;
+	} else {
+#pragma unroll
+		for (int j = 0; j < 32; ++j) {
+			const uint64_t u = ((((uint64_t)hi[j]) << 32) | lo[j]) + d.base;
+			lo[j] = (uint32_t)u;
+			hi[j] = (uint32_t)(u >> 32);
+		}
+	}
+	(void)blo;
+	(void)bhi;
+	store_direct64(out_vec, lane, lo, hi);
+	patch_exceptions<64, 8>(out_vec, d, lane, 0);
+}
+
+// ---- the persistent kernel -----------------------------------------------------------------------------------------------
+// MODE 0: main family (T = physical lane width = VT); MODE 1: DICT (T = code lane width, VT = key width);
+// MODE 2: RLE (T = 16: run-index lanes, VT = value width).
+template <int MODE, int T, int VT, int OB>
+__global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const FlsLaunch L) {
+	extern __shared__ __align__(128) uint8_t smem[];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const uint32_t n_slots = L.n_slots;
+	uint64_t* bars = reinterpret_cast<uint64_t*>(smem) + warp * n_slots;
+	const uint32_t bar_bytes = (kWarpsPerCta * n_slots * 8 + 127u) & ~127u;
+	const uint32_t warp_bytes = n_slots * L.slot_bytes + L.stage_bytes;
+	uint8_t* slots = smem + bar_bytes + (size_t)warp * warp_bytes;
+	uint8_t* stage = slots + (size_t)n_slots * L.slot_bytes;
+
+	if (lane == 0) {
+		for (uint32_t s = 0; s < n_slots; ++s) {
+			mbar_init(bars + s, 1);
+		}
+		fence_mbar_init();
+	}
+	__syncwarp();
+
+	const uint32_t n_warps = gridDim.x * kWarpsPerCta;
+	const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
+	uint32_t phases = 0; // bit s: parity to wait for on slot s
+	uint32_t n_done = 0; // vectors processed by this warp (slot = n_done % n_slots)
+	uint8_t* const out = static_cast<uint8_t*>(L.out);
+
+	for (uint64_t b0 = gw; b0 < L.total_vecs; b0 += (uint64_t)32 * n_warps) {
+		const uint64_t my_v64 = b0 + (uint64_t)lane * n_warps;
+		const VecDesc mine = fetch_desc<T>(L, my_v64 < L.total_vecs ? (uint32_t)my_v64 : 0xffffffffu);
+		uint32_t todo = __ballot_sync(0xffffffffu, mine.ch != nullptr);
+		uint32_t to_issue = todo;
+		// prologue: fill the pipeline
+		uint32_t slot_i = n_done % n_slots;
+		for (uint32_t s = 0; s < n_slots && to_issue; ++s) {
+			const int k = __ffs(to_issue) - 1;
+			to_issue &= to_issue - 1;
+			const uint8_t* src = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)mine.blob, k);
+			const uint32_t bytes = __shfl_sync(0xffffffffu, mine.bytes, k);
+			if (lane == 0 && bytes) {
+				mbar_expect_tx(bars + slot_i, bytes);
+				tma_load_1d(slots + (size_t)slot_i * L.slot_bytes, src, bytes, bars + slot_i);
+			}
+			slot_i = slot_i + 1 == n_slots ? 0 : slot_i + 1;
+		}
+		while (todo) {
+			const int k = __ffs(todo) - 1;
+			todo &= todo - 1;
+			const VecDesc d = shfl_desc(mine, k);
+			const uint32_t slot = n_done % n_slots;
+			if (d.bytes) {
+				mbar_wait(bars + slot, (phases >> slot) & 1u);
+				phases ^= 1u << slot;
+			}
+			uint8_t* out_vec = out + (size_t)(b0 + (uint64_t)k * n_warps) * 1024u * OB;
+			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
+			if constexpr (MODE == 1) {
+				process_dict<T, VT, OB>(d, sp, out_vec, lane, L.conv);
+			} else if constexpr (MODE == 2) {
+				process_rle<VT, OB>(d, sp, stage, out_vec, lane, L.conv);
+			} else if constexpr (T == 64) {
+				process_64(d, sp, stage, out_vec, lane);
+			} else {
+				process_small<T, OB>(d, sp, stage, out_vec, lane, L.conv);
+			}
+			__syncwarp(); // all lanes are done reading the slot (and the staging area)
+			if (to_issue) {
+				const int kn = __ffs(to_issue) - 1;
+				to_issue &= to_issue - 1;
+				const uint8_t* src = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)mine.blob, kn);
+				const uint32_t bytes = __shfl_sync(0xffffffffu, mine.bytes, kn);
+				if (lane == 0 && bytes) {
+					mbar_expect_tx(bars + slot, bytes);
+					tma_load_1d(slots + (size_t)slot * L.slot_bytes, src, bytes, bars + slot);
+				}
+			}
+			++n_done;
+		}
+	}
+}
+
+} // namespace flsk

@@ -1,0 +1,41 @@
+// fls_device.h — structs shared by the host launcher and the kernels.
+#pragma once
+#include <stdint.h>
+#include "fls_format.h"
+
+// Device-side view of one column chunk (64 bytes, built at stage time from fls_chunk_desc).
+struct alignas(16) FlsChunkDev {
+	const uint8_t* data;      // DATA segment
+	const fls_vec_meta* meta; // META segment
+	const uint8_t* aux0;      // dictionary keys | run values | exception values | CROSS_RLE values
+	const uint8_t* aux1;      // exception positions (u16) | CROSS_RLE run STARTS (u32 exclusive prefix, n_runs+1)
+	uint64_t const_val;
+	uint32_t aux_count;
+	uint16_t n_vec;
+	uint8_t encoding;
+	uint8_t idx_bits;
+	uint16_t rd_dict[8];
+};
+static_assert(sizeof(FlsChunkDev) == 64, "FlsChunkDev must be 64 bytes");
+
+// Launch parameters of one decode launch: column `col` of row groups [rg_begin, rg_begin + n_rg).
+struct FlsLaunch {
+	const FlsChunkDev* chunks; // &chunk_dev[rg_begin * n_cols + col]
+	uint32_t chunk_stride;     // n_cols
+	uint32_t vec_per_rg;
+	uint32_t total_vecs;       // n_rg * vec_per_rg (vectors beyond a chunk's n_vec are skipped)
+	uint32_t slot_bytes;       // shared-memory bytes per pipeline slot (multiple of 128)
+	uint32_t stage_bytes;      // per-warp staging area for transposition (0 if no chunk needs it)
+	uint32_t n_slots;          // pipeline depth per warp
+	uint32_t conv;             // 0: zero-extend / same width, 1: sign-extend, 2: f32 -> f64
+	uint32_t family_mask;      // bit e set: this kernel handles encoding e
+	void* out;
+};
+
+// Encoding families (which kernel template handles which fls_encoding)
+#define FLS_FAMILY_MAIN                                                                                                \
+	((1u << FLS_ENC_UNCOMPRESSED) | (1u << FLS_ENC_CONSTANT) | (1u << FLS_ENC_FFOR) | (1u << FLS_ENC_DELTA) |          \
+	 (1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD) | (1u << FLS_ENC_CROSS_RLE) | (1u << FLS_ENC_FREQUENCY) |            \
+	 (1u << FLS_ENC_SLPATCH))
+#define FLS_FAMILY_DICT (1u << FLS_ENC_DICT)
+#define FLS_FAMILY_RLE (1u << FLS_ENC_RLE)
