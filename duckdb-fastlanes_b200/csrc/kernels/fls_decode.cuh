@@ -95,7 +95,7 @@ __device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
 		const uint32_t r = v / L.vec_per_rg, vi = v - r * L.vec_per_rg;
 		const FlsChunkDev* ch = L.chunks + (size_t)r * L.chunk_stride;
 		const uint32_t enc = ch->encoding;
-		if (vi < ch->n_vec && ((L.family_mask >> enc) & 1u)) {
+		if (vi < ch->n_vec && ((L.family_mask >> enc) & 1u) && (L.idx_bits == 0 || ch->idx_bits == L.idx_bits)) {
 			const uint4* mp = reinterpret_cast<const uint4*>(ch->meta + vi);
 			const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
 			// fls_vec_meta: base(8) data_off16(4) aux_off(4) | aux_cnt(2) width(1) width2(1) e(1) f(1) n_valid(2) reserved(8)

@@ -1,0 +1,690 @@
+// flsgpu_device.cu — device side of the C ABI (include/flsgpu.h): staging of compressed row groups into HBM, launch
+// planning for the decode kernel families, the pipelined host-to-host scan, pinned allocations.
+//
+// Replaces, for the read_fls scan path, what the reference does per worker thread in
+// FastLanesReader::TryInitializeScan / DecodePhysicalColumns (reference src/reader/fls_reader.cpp:337-355,436-472):
+// get_rowgroup_reader (-> stage), get_chunk + PointTo + KernelTraits<Op>::Decode (-> one fused kernel launch over
+// every vector of the requested row groups).
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "fls_error.hpp"
+#include "fls_launch.hpp"
+#include "fls_table.hpp"
+#include "flsgpu.h"
+
+namespace {
+
+std::atomic<uint64_t> g_launches {0};
+std::mutex g_mu; // guards device selection + per-function attribute cache
+int g_device = -1;
+int g_n_sms = 0;
+std::map<const void*, int> g_func_ready;                  // fn -> 1 once the smem opt-in is set
+std::map<std::pair<const void*, uint32_t>, int> g_occ;    // (fn, smem) -> resident CTAs per SM
+
+constexpr uint32_t kMaxSmemPerCta = 227u * 1024u;
+
+int cuda_fail(cudaError_t e, const char* where) {
+	char msg[256];
+	std::snprintf(msg, sizeof(msg), "%s: %s", where, cudaGetErrorString(e));
+	return fls_set_error(FLSGPU_ERR_CUDA, msg);
+}
+#define FLS_CUDA(call)                                                                                               \
+	do {                                                                                                             \
+		const cudaError_t e_ = (call);                                                                               \
+		if (e_ != cudaSuccess) {                                                                                     \
+			return cuda_fail(e_, #call);                                                                             \
+		}                                                                                                            \
+	} while (0)
+
+int ensure_device() {
+	std::lock_guard<std::mutex> g(g_mu);
+	if (g_device < 0) {
+		int n = 0;
+		const cudaError_t e = cudaGetDeviceCount(&n);
+		if (e != cudaSuccess || n == 0) {
+			return fls_set_error(FLSGPU_ERR_CUDA, "no CUDA device available (flsgpu has no CPU fallback)");
+		}
+		g_device = 0;
+	}
+	FLS_CUDA(cudaSetDevice(g_device));
+	if (g_n_sms == 0) {
+		FLS_CUDA(cudaDeviceGetAttribute(&g_n_sms, cudaDevAttrMultiProcessorCount, g_device));
+	}
+	return FLSGPU_OK;
+}
+
+} // namespace
+
+// ---- per-table device state ---------------------------------------------------------------------------------------
+struct FlsColumnPlan { // what a decode launch over (col, rg range) needs to know about the chunks it covers
+	bool has_main = false, has_rle = false, has_dict[3] = {false, false, false};
+	bool main_needs_stage = false;
+	uint32_t main_slot = 0, rle_slot = 0, dict_slot[3] = {0, 0, 0};
+};
+
+struct FlsDeviceState {
+	int device = 0;
+	uint8_t* d_image = nullptr; // bytes [0, footer_offset) of the container, same offsets as the file
+	uint64_t image_bytes = 0;
+	FlsChunkDev* d_chunks = nullptr; // [rg * n_columns + col]
+	uint32_t* d_run_starts = nullptr; // CROSS_RLE: exclusive prefix sums of the run lengths, all chunks back to back
+	std::vector<uint8_t> chunk_resident; // [rg * n_columns + col]
+	uint64_t resident_bytes = 0;
+	bool host_pinned_tried = false;
+	bool host_registered = false;
+	std::map<std::tuple<uint32_t, uint32_t, uint32_t>, FlsColumnPlan> plans;
+	// pipelined scan (flsgpu_scan_column_to_host)
+	cudaStream_t scan_streams[2] = {nullptr, nullptr};
+	void* scan_out[2] = {nullptr, nullptr};
+	uint64_t scan_out_bytes = 0;
+	std::mutex mu;
+};
+
+void fls_device_release(flsgpu_table* t) {
+	FlsDeviceState* d = t->dev;
+	if (!d) {
+		return;
+	}
+	cudaSetDevice(d->device);
+	for (int i = 0; i < 2; ++i) {
+		if (d->scan_streams[i]) {
+			cudaStreamSynchronize(d->scan_streams[i]);
+			cudaStreamDestroy(d->scan_streams[i]);
+		}
+		cudaFree(d->scan_out[i]);
+	}
+	cudaDeviceSynchronize();
+	cudaFree(d->d_image);
+	cudaFree(d->d_chunks);
+	cudaFree(d->d_run_starts);
+	if (d->host_registered) {
+		cudaHostUnregister(const_cast<uint8_t*>(t->bytes));
+	}
+	delete d;
+	t->dev = nullptr;
+}
+
+namespace {
+
+// Allocate the HBM arena + device chunk table on first use.  Pointers in the chunk table are final from the start
+// (arena offsets equal file offsets); residency only says whether the bytes behind them have been copied.
+int device_state(flsgpu_table* t, FlsDeviceState** out) {
+	if (t->dev) {
+		*out = t->dev;
+		return cudaSetDevice(t->dev->device) == cudaSuccess ? FLSGPU_OK : fls_set_error(FLSGPU_ERR_CUDA, "cudaSetDevice failed");
+	}
+	const int rc = ensure_device();
+	if (rc) {
+		return rc;
+	}
+	auto d = new FlsDeviceState();
+	t->dev = d; // released by fls_device_release on any later failure path through flsgpu_table_close
+	d->device = g_device;
+	const fls_file_header& h = t->header;
+	const uint64_t n_chunks = (uint64_t)h.n_rowgroups * h.n_columns;
+	d->image_bytes = h.footer_offset;
+	d->chunk_resident.assign(n_chunks, 0);
+	FLS_CUDA(cudaMalloc(&d->d_image, d->image_bytes + 256));
+
+	// CROSS_RLE run starts (reference cross_rle_kernel.hpp:8-21 rescans run lengths per vector; here the prefix sums
+	// are built once so that a vector finds its first run by binary search)
+	std::vector<uint64_t> starts_off(n_chunks, ~0ull);
+	uint64_t n_starts = 0;
+	for (uint64_t i = 0; i < n_chunks; ++i) {
+		if (t->chunks[i].encoding == FLS_ENC_CROSS_RLE) {
+			starts_off[i] = n_starts;
+			n_starts += (uint64_t)t->chunks[i].aux_count + 1;
+		}
+	}
+	if (n_starts) {
+		std::vector<uint32_t> starts(n_starts);
+		for (uint64_t i = 0; i < n_chunks; ++i) {
+			if (starts_off[i] == ~0ull) {
+				continue;
+			}
+			const fls_chunk_desc& c = t->chunks[i];
+			const uint32_t* lens = reinterpret_cast<const uint32_t*>(t->bytes + c.offset + c.seg_off[FLS_SEG_AUX1]);
+			uint32_t acc = 0;
+			uint32_t* s = starts.data() + starts_off[i];
+			for (uint32_t r = 0; r < c.aux_count; ++r) {
+				s[r] = acc;
+				acc += lens[r];
+			}
+			s[c.aux_count] = acc;
+		}
+		FLS_CUDA(cudaMalloc(&d->d_run_starts, n_starts * sizeof(uint32_t)));
+		FLS_CUDA(cudaMemcpy(d->d_run_starts, starts.data(), n_starts * sizeof(uint32_t), cudaMemcpyHostToDevice));
+	}
+
+	std::vector<FlsChunkDev> host_chunks(n_chunks);
+	for (uint64_t i = 0; i < n_chunks; ++i) {
+		const fls_chunk_desc& c = t->chunks[i];
+		FlsChunkDev& o = host_chunks[i];
+		const uint8_t* base = d->d_image + c.offset;
+		o.data = base + c.seg_off[FLS_SEG_DATA];
+		o.meta = reinterpret_cast<const fls_vec_meta*>(base + c.seg_off[FLS_SEG_META]);
+		o.aux0 = base + c.seg_off[FLS_SEG_AUX0];
+		o.aux1 = c.encoding == FLS_ENC_CROSS_RLE ? reinterpret_cast<const uint8_t*>(d->d_run_starts + starts_off[i])
+		                                         : base + c.seg_off[FLS_SEG_AUX1];
+		o.const_val = c.const_val;
+		o.aux_count = c.aux_count;
+		o.n_vec = (uint16_t)c.n_vec;
+		o.encoding = c.encoding;
+		o.idx_bits = c.idx_bits;
+		std::memcpy(o.rd_dict, c.rd_dict, sizeof(o.rd_dict));
+	}
+	FLS_CUDA(cudaMalloc(&d->d_chunks, n_chunks * sizeof(FlsChunkDev)));
+	FLS_CUDA(cudaMemcpy(d->d_chunks, host_chunks.data(), n_chunks * sizeof(FlsChunkDev), cudaMemcpyHostToDevice));
+	*out = d;
+	return FLSGPU_OK;
+}
+
+// Page-lock the container image once so that H2D staging runs at PCIe speed and asynchronously.  Failure is not an
+// error (the image may already be pinned by flsgpu_host_alloc, or be a read-only mapping): copies then fall back to
+// the driver's pageable path.
+void pin_image(flsgpu_table* t, FlsDeviceState* d) {
+	if (d->host_pinned_tried) {
+		return;
+	}
+	d->host_pinned_tried = true;
+	cudaPointerAttributes attr {};
+	if (cudaPointerGetAttributes(&attr, t->bytes) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
+		return; // already pinned
+	}
+	cudaGetLastError();
+	if (cudaHostRegister(const_cast<uint8_t*>(t->bytes), t->size, cudaHostRegisterDefault) == cudaSuccess) {
+		d->host_registered = true;
+	} else {
+		cudaGetLastError();
+	}
+}
+
+// Copy the chunks of `col` (or of every column when col == ALL) of row groups [rg_begin, rg_begin+n_rg) that are not
+// resident yet.  Adjacent chunks are merged into one cudaMemcpyAsync.
+constexpr uint32_t kAllColumns = 0xffffffffu;
+
+int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t n_rg, uint32_t col, cudaStream_t stream) {
+	pin_image(t, d);
+	const uint32_t n_cols = t->header.n_columns;
+	uint64_t run_begin = 0, run_end = 0; // pending merged copy [begin, end) in file offsets
+	auto flush = [&]() -> int {
+		if (run_end > run_begin) {
+			FLS_CUDA(cudaMemcpyAsync(d->d_image + run_begin, t->bytes + run_begin, run_end - run_begin, cudaMemcpyHostToDevice,
+			                         stream));
+			d->resident_bytes += run_end - run_begin;
+		}
+		run_begin = run_end = 0;
+		return FLSGPU_OK;
+	};
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		const uint32_t c0 = col == kAllColumns ? 0 : col, c1 = col == kAllColumns ? n_cols : col + 1;
+		for (uint32_t c = c0; c < c1; ++c) {
+			const uint64_t i = (uint64_t)r * n_cols + c;
+			if (d->chunk_resident[i]) {
+				continue;
+			}
+			d->chunk_resident[i] = 1;
+			const fls_chunk_desc& ch = t->chunks[i];
+			if (run_end == ch.offset && run_end > run_begin) {
+				run_end = ch.offset + ch.size;
+			} else {
+				const int rc = flush();
+				if (rc) {
+					return rc;
+				}
+				run_begin = ch.offset;
+				run_end = ch.offset + ch.size;
+			}
+		}
+	}
+	return flush();
+}
+
+uint32_t blob_bytes_max(const fls_chunk_desc& c) {
+	switch (c.encoding) {
+	case FLS_ENC_UNCOMPRESSED: return 128u * c.phys_bits;
+	case FLS_ENC_CONSTANT:
+	case FLS_ENC_CROSS_RLE: return 0;
+	case FLS_ENC_DELTA:
+	case FLS_ENC_RLE: return 128u + 128u * c.max_width;
+	default: return 128u * c.max_width; // ALP_RD: max_width = max(width + width2)
+	}
+}
+
+const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg) {
+	const auto key = std::make_tuple(col, rg_begin, n_rg);
+	auto it = d->plans.find(key);
+	if (it != d->plans.end()) {
+		return it->second;
+	}
+	FlsColumnPlan p;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		const fls_chunk_desc& c = t->chunk(r, col);
+		const uint32_t bytes = blob_bytes_max(c);
+		if (c.encoding == FLS_ENC_DICT) {
+			const int k = c.idx_bits == 8 ? 0 : c.idx_bits == 16 ? 1 : 2;
+			p.has_dict[k] = true;
+			p.dict_slot[k] = std::max(p.dict_slot[k], bytes);
+		} else if (c.encoding == FLS_ENC_RLE) {
+			p.has_rle = true;
+			p.rle_slot = std::max(p.rle_slot, bytes);
+		} else {
+			p.has_main = true;
+			p.main_slot = std::max(p.main_slot, bytes);
+			p.main_needs_stage |= c.encoding == FLS_ENC_DELTA;
+		}
+	}
+	if (d->plans.size() > 4096) {
+		d->plans.clear();
+	}
+	return d->plans.emplace(key, p).first->second;
+}
+
+// Pick pipeline depth / grid for `fn` and launch it.
+int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t stage_bytes, cudaStream_t stream) {
+	if (!fn) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "no kernel instantiation for this (lane width, value width, output width)");
+	}
+	L.slot_bytes = std::max<uint32_t>(128u, (slot_bytes + 127u) & ~127u);
+	L.stage_bytes = stage_bytes;
+	// shared memory: aim for two resident CTAs per SM (~104 KB each) unless a single slot pair needs more
+	const uint32_t per_warp_budget = 13u * 1024u;
+	uint32_t n_slots = L.stage_bytes < per_warp_budget ? (per_warp_budget - L.stage_bytes) / L.slot_bytes : 0;
+	n_slots = std::max(2u, std::min(6u, n_slots));
+	L.n_slots = n_slots;
+	const uint32_t bar_bytes = (kFlsWarpsPerCta * n_slots * 8u + 127u) & ~127u;
+	const uint32_t smem = bar_bytes + kFlsWarpsPerCta * (n_slots * L.slot_bytes + L.stage_bytes);
+	if (smem > kMaxSmemPerCta) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "vector blob too large for the shared-memory pipeline");
+	}
+	int occ = 0;
+	{
+		std::lock_guard<std::mutex> g(g_mu);
+		if (!g_func_ready.count(fn)) {
+			FLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmemPerCta));
+			g_func_ready[fn] = 1;
+		}
+		const auto key = std::make_pair(fn, smem);
+		auto it = g_occ.find(key);
+		if (it == g_occ.end()) {
+			FLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kFlsWarpsPerCta * 32, smem));
+			g_occ[key] = occ;
+		} else {
+			occ = it->second;
+		}
+	}
+	if (occ < 1) {
+		return fls_set_error(FLSGPU_ERR_CUDA, "decode kernel cannot be resident with the requested shared memory");
+	}
+	const uint64_t want = ((uint64_t)L.total_vecs + kFlsWarpsPerCta - 1) / kFlsWarpsPerCta;
+	const uint32_t grid = (uint32_t)std::min<uint64_t>(want, (uint64_t)occ * g_n_sms);
+	void* args[] = {&L};
+	FLS_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(kFlsWarpsPerCta * 32), args, smem, stream));
+	g_launches.fetch_add(1, std::memory_order_relaxed);
+	return FLSGPU_OK;
+}
+
+struct OutSpec {
+	int ob = 0;        // bytes per output value
+	uint32_t conv = 0; // 0 zero-extend / same width, 1 sign-extend, 2 f32 -> f64
+};
+
+// Destination type rules of the materializer (reference fls_type_resolver.hpp:22-33,120-131: same physical type ->
+// copy, otherwise static_cast from the source viewed with the column's signedness, unffor_kernel.hpp:16-25).
+int resolve_out(const fls_column_desc& col, int32_t out_type, OutSpec* o) {
+	const int T = col.phys_bits;
+	if (out_type == FLSGPU_OUT_NATIVE) {
+		o->ob = T / 8;
+		o->conv = 0;
+		return FLSGPU_OK;
+	}
+	int ob = 0;
+	bool out_float = false;
+	switch (out_type) {
+	case FLSGPU_OUT_I8:
+	case FLSGPU_OUT_U8: ob = 1; break;
+	case FLSGPU_OUT_I16:
+	case FLSGPU_OUT_U16: ob = 2; break;
+	case FLSGPU_OUT_I32:
+	case FLSGPU_OUT_U32: ob = 4; break;
+	case FLSGPU_OUT_I64:
+	case FLSGPU_OUT_U64: ob = 8; break;
+	case FLSGPU_OUT_F32: ob = 4; out_float = true; break;
+	case FLSGPU_OUT_F64: ob = 8; out_float = true; break;
+	default: return fls_set_error(FLSGPU_ERR_INVALID, "unknown flsgpu_out_type");
+	}
+	if ((bool)col.is_float != out_float) {
+		return fls_set_error(FLSGPU_ERR_CONVERSION, "integer <-> floating point materialisation is not supported");
+	}
+	if (ob * 8 < T) {
+		return fls_set_error(FLSGPU_ERR_CONVERSION, "destination type is narrower than the column's physical type");
+	}
+	o->ob = ob;
+	o->conv = ob * 8 == T ? 0u : col.is_float ? 2u : col.is_signed ? 1u : 0u;
+	return FLSGPU_OK;
+}
+
+int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const OutSpec& os,
+                       void* out_dev, cudaStream_t stream) {
+	const fls_file_header& h = t->header;
+	const int T = t->columns[col].phys_bits;
+	FlsColumnPlan p;
+	{
+		std::lock_guard<std::mutex> g(d->mu);
+		p = plan_for(t, d, col, rg_begin, n_rg);
+	}
+	FlsLaunch L {};
+	L.chunks = d->d_chunks + (uint64_t)rg_begin * h.n_columns + col;
+	L.chunk_stride = h.n_columns;
+	L.vec_per_rg = h.vec_per_rowgroup;
+	L.total_vecs = n_rg * h.vec_per_rowgroup;
+	L.conv = os.conv;
+	L.out = out_dev;
+	int rc = FLSGPU_OK;
+	if (p.has_main) {
+		L.family_mask = FLS_FAMILY_MAIN;
+		L.idx_bits = 0;
+		rc = launch_family(fls_kernel_main(T, os.ob), L, p.main_slot, p.main_needs_stage ? 128u * T : 0u, stream);
+	}
+	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {
+		if (p.has_dict[k]) {
+			const int it = 8 << k;
+			L.family_mask = FLS_FAMILY_DICT;
+			L.idx_bits = (uint32_t)it;
+			rc = launch_family(fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream);
+		}
+	}
+	if (p.has_rle && rc == FLSGPU_OK) {
+		L.family_mask = FLS_FAMILY_RLE;
+		L.idx_bits = 0;
+		rc = launch_family(fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream);
+	}
+	return rc;
+}
+
+int check_range(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const char* who) {
+	if (!t || col >= t->header.n_columns || n_rg == 0 || rg_begin >= t->header.n_rowgroups ||
+	    n_rg > t->header.n_rowgroups - rg_begin) {
+		char msg[160];
+		std::snprintf(msg, sizeof(msg), "%s: column or row-group range out of bounds", who);
+		return fls_set_error(FLSGPU_ERR_INVALID, msg);
+	}
+	return FLSGPU_OK;
+}
+
+int check_resident(const flsgpu_table* t, const FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg) {
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		if (!d->chunk_resident[(uint64_t)r * t->header.n_columns + col]) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "row group not staged: call flsgpu_table_stage first");
+		}
+	}
+	return FLSGPU_OK;
+}
+
+} // namespace
+
+// ---- C ABI ---------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int flsgpu_init(int n_devices, const int* device_ids) {
+	int n = 0;
+	const cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) {
+		return fls_set_error(FLSGPU_ERR_CUDA, "flsgpu_init: no CUDA device available (flsgpu has no CPU fallback)");
+	}
+	// one process per GPU: the first listed device becomes this process's device
+	const int dev = (n_devices > 0 && device_ids) ? device_ids[0] : 0;
+	if (dev < 0 || dev >= n) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_init: device id out of range");
+	}
+	{
+		std::lock_guard<std::mutex> g(g_mu);
+		g_device = dev;
+		g_n_sms = 0;
+	}
+	return ensure_device();
+}
+
+int flsgpu_device_count(int* out) {
+	if (!out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_device_count: null argument");
+	}
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) {
+		cudaGetLastError();
+		n = 0;
+	}
+	*out = n;
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_stage(flsgpu_table* t, uint32_t rg_begin, uint32_t n_rg, void* cuda_stream) {
+	int rc = check_range(t, 0, rg_begin, n_rg, "flsgpu_table_stage");
+	if (rc) {
+		return rc;
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	std::lock_guard<std::mutex> g(d->mu);
+	return stage_range(t, d, rg_begin, n_rg, kAllColumns, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int flsgpu_table_evict(flsgpu_table* t) {
+	if (!t) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_evict: null table");
+	}
+	if (t->dev) {
+		FLS_CUDA(cudaSetDevice(t->dev->device));
+		FLS_CUDA(cudaDeviceSynchronize());
+		std::lock_guard<std::mutex> g(t->dev->mu);
+		std::fill(t->dev->chunk_resident.begin(), t->dev->chunk_resident.end(), 0);
+		t->dev->resident_bytes = 0;
+	}
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_unstage(flsgpu_table* t) {
+	if (!t) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_unstage: null table");
+	}
+	fls_device_release(t);
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_resident_bytes(const flsgpu_table* t, uint64_t* out) {
+	if (!t || !out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_resident_bytes: null argument");
+	}
+	*out = t->dev ? t->dev->resident_bytes : 0;
+	return FLSGPU_OK;
+}
+
+int flsgpu_decode_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type, void* out_dev,
+                         uint64_t out_capacity_bytes, void* cuda_stream) {
+	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_decode_column");
+	if (rc) {
+		return rc;
+	}
+	OutSpec os;
+	rc = resolve_out(t->columns[col], out_type, &os);
+	if (rc) {
+		return rc;
+	}
+	const uint64_t need = (uint64_t)n_rg * t->header.vec_per_rowgroup * FLS_VEC_SZ * os.ob;
+	if (!out_dev || (reinterpret_cast<uintptr_t>(out_dev) & 15u) || out_capacity_bytes < need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_column: output buffer null, misaligned or too small");
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	rc = check_resident(t, d, col, rg_begin, n_rg);
+	if (rc) {
+		return rc;
+	}
+	return decode_column_impl(t, d, col, rg_begin, n_rg, os, out_dev, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids, uint32_t n_cols, void* const* out_ptrs,
+                           const int32_t* out_types, void* cuda_stream) {
+	if (!t || !col_ids || !out_ptrs || n_cols == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_rowgroup_decode: null argument");
+	}
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		int rc = check_range(t, col_ids[i], rg, 1, "flsgpu_rowgroup_decode");
+		if (rc) {
+			return rc;
+		}
+		OutSpec os;
+		rc = resolve_out(t->columns[col_ids[i]], out_types ? out_types[i] : FLSGPU_OUT_NATIVE, &os);
+		if (rc) {
+			return rc;
+		}
+		if (!out_ptrs[i] || (reinterpret_cast<uintptr_t>(out_ptrs[i]) & 15u)) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_rowgroup_decode: output pointer null or not 16-byte aligned");
+		}
+	}
+	FlsDeviceState* d = nullptr;
+	int rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		rc = check_resident(t, d, col_ids[i], rg, 1);
+		if (rc) {
+			return rc;
+		}
+		OutSpec os;
+		resolve_out(t->columns[col_ids[i]], out_types ? out_types[i] : FLSGPU_OUT_NATIVE, &os);
+		rc = decode_column_impl(t, d, col_ids[i], rg, 1, os, out_ptrs[i], static_cast<cudaStream_t>(cuda_stream));
+		if (rc) {
+			return rc;
+		}
+	}
+	return FLSGPU_OK;
+}
+
+int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type, void* out_host,
+                               uint64_t out_capacity_bytes) {
+	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_scan_column_to_host");
+	if (rc) {
+		return rc;
+	}
+	OutSpec os;
+	rc = resolve_out(t->columns[col], out_type, &os);
+	if (rc) {
+		return rc;
+	}
+	const uint64_t rg_bytes = (uint64_t)t->header.vec_per_rowgroup * FLS_VEC_SZ * os.ob;
+	if (!out_host || out_capacity_bytes < rg_bytes * n_rg) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_column_to_host: output buffer null or too small");
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	// slabs of ~32 MiB decoded: deep enough to hide launch latency, small enough that H2D, decode and D2H of
+	// neighbouring slabs overlap on the two streams
+	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (32ull << 20) / rg_bytes));
+	const uint64_t slab_bytes = rg_bytes * slab_rg;
+	if (d->scan_out_bytes < slab_bytes) {
+		for (int i = 0; i < 2; ++i) {
+			if (d->scan_streams[i]) {
+				FLS_CUDA(cudaStreamSynchronize(d->scan_streams[i]));
+			}
+			FLS_CUDA(cudaFree(d->scan_out[i]));
+			d->scan_out[i] = nullptr;
+			FLS_CUDA(cudaMalloc(&d->scan_out[i], slab_bytes));
+		}
+		d->scan_out_bytes = slab_bytes;
+	}
+	for (int i = 0; i < 2; ++i) {
+		if (!d->scan_streams[i]) {
+			FLS_CUDA(cudaStreamCreateWithFlags(&d->scan_streams[i], cudaStreamNonBlocking));
+		}
+	}
+	uint32_t slab = 0;
+	for (uint32_t r = 0; r < n_rg; r += slab_rg, ++slab) {
+		const uint32_t n = std::min(slab_rg, n_rg - r);
+		cudaStream_t s = d->scan_streams[slab & 1];
+		{
+			std::lock_guard<std::mutex> g(d->mu);
+			rc = stage_range(t, d, rg_begin + r, n, col, s);
+		}
+		if (rc) {
+			return rc;
+		}
+		rc = decode_column_impl(t, d, col, rg_begin + r, n, os, d->scan_out[slab & 1], s);
+		if (rc) {
+			return rc;
+		}
+		FLS_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(out_host) + (uint64_t)r * rg_bytes, d->scan_out[slab & 1], rg_bytes * n,
+		                         cudaMemcpyDeviceToHost, s));
+	}
+	FLS_CUDA(cudaStreamSynchronize(d->scan_streams[0]));
+	FLS_CUDA(cudaStreamSynchronize(d->scan_streams[1]));
+	return FLSGPU_OK;
+}
+
+int flsgpu_sync(void* cuda_stream) {
+	const int rc = ensure_device();
+	if (rc) {
+		return rc;
+	}
+	FLS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(cuda_stream)));
+	return FLSGPU_OK;
+}
+
+int flsgpu_host_alloc(uint64_t bytes, void** out) {
+	if (!out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_host_alloc: null argument");
+	}
+	const int rc = ensure_device();
+	if (rc) {
+		return rc;
+	}
+	FLS_CUDA(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+	return FLSGPU_OK;
+}
+
+int flsgpu_host_free(void* p) {
+	if (p) {
+		FLS_CUDA(cudaFreeHost(p));
+	}
+	return FLSGPU_OK;
+}
+
+uint64_t flsgpu_launch_count(void) {
+	return g_launches.load(std::memory_order_relaxed);
+}
+
+int flsgpu_aggregate_column(flsgpu_table*, uint32_t, uint32_t, uint32_t, flsgpu_agg_result*, void*) {
+	return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_aggregate_column: not built yet");
+}
+int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {
+	if (!result_dev) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_agg_reset: null argument");
+	}
+	const int rc = ensure_device();
+	if (rc) {
+		return rc;
+	}
+	FLS_CUDA(cudaMemsetAsync(result_dev, 0, sizeof(flsgpu_agg_result), static_cast<cudaStream_t>(cuda_stream)));
+	return FLSGPU_OK;
+}
+
+} // extern "C"

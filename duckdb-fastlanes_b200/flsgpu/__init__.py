@@ -79,7 +79,7 @@ ABI_SYMBOLS = [
     "flsgpu_writer_append", "flsgpu_writer_finish", "flsgpu_writer_image", "flsgpu_writer_save",
     "flsgpu_writer_destroy", "flsgpu_table_open", "flsgpu_table_open_memory", "flsgpu_table_close",
     "flsgpu_table_info_get", "flsgpu_table_column", "flsgpu_table_rowgroup", "flsgpu_table_chunk",
-    "flsgpu_table_stage", "flsgpu_table_unstage", "flsgpu_table_resident_bytes", "flsgpu_decode_column",
+    "flsgpu_table_stage", "flsgpu_table_evict", "flsgpu_table_unstage", "flsgpu_table_resident_bytes", "flsgpu_decode_column",
     "flsgpu_rowgroup_decode", "flsgpu_aggregate_column", "flsgpu_agg_reset", "flsgpu_scan_column_to_host",
     "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
 ]
@@ -199,6 +199,9 @@ class Table:
     def stage(self, rg_begin=0, n_rg=None, stream=0):
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_table_stage(self._h, rg_begin, n_rg, _vp(stream)), "table_stage")
+
+    def evict(self):
+        _check(lib.flsgpu_table_evict(self._h), "table_evict")
 
     def unstage(self):
         _check(lib.flsgpu_table_unstage(self._h), "table_unstage")

@@ -83,6 +83,9 @@ int flsgpu_table_chunk(const flsgpu_table* t, uint32_t rg, uint32_t col, fls_chu
 /* Copy the compressed image of row groups [rg_begin, rg_begin+n_rg) to HBM (pinned host -> device, async on
  * `stream`) and build the device descriptor tables.  No-op for row groups already resident. */
 int flsgpu_table_stage(flsgpu_table* t, uint32_t rg_begin, uint32_t n_rg, void* cuda_stream);
+/* Forget residency but keep the HBM arena (the next stage copies again): used to time host-fed scans. */
+int flsgpu_table_evict(flsgpu_table* t);
+/* Free every device resource of the table. */
 int flsgpu_table_unstage(flsgpu_table* t);
 int flsgpu_table_resident_bytes(const flsgpu_table* t, uint64_t* out);
 
