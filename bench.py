@@ -1,0 +1,444 @@
+#!/usr/bin/env python
+"""bench.py — read_fls scan throughput of the B200 FastLanes decode engine (BASELINE.json metric).
+
+A step = one full scan of the all_types table (BASELINE.json configs[1]: 100 M rows; TINYINT .. TIMESTAMP, DOUBLE via
+ALP, VARCHAR via dictionary codes): every column of every row group is decoded through the C ABI
+(flsgpu_decode_column), one fused kernel launch per column.
+
+  value : decoded GB/s with the compressed container resident in HBM (CUDA events, max over ranks)
+  e2e   : the same scan through flsgpu_scan_column_to_host: pinned host container -> H2D -> decode -> D2H into pinned
+          host column buffers, every step
+  roofline : the kernel template that takes the largest share of the step, algorithmic bytes / its
+          CUDA-event time, against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline / --impl reference : oracle/liboracle.so's reference-shaped scan (2048-row chunks, one row group per
+          thread) on the host cores.  The reference's own binary cannot be built here (its FastLanes library is an
+          un-vendored dependency), so kind = "port".
+
+Multi-GPU: one process per GPU (torchrun); every rank scans its own shard of row groups (an all_types table of
+--rows rows per rank: weak scaling, no data-path collective); rank 0 gathers the per-rank times and the reduced
+scan results (row counts + checksums) with one NCCL all_reduce.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, "duckdb-fastlanes_b200"), os.path.join(ROOT, "tests"), ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "read_fls_decoded_GBps"
+UNIT = "GB/s"
+WORKLOAD = "all_types_100M"
+
+# name, fls type, forced encoding (None: the writer's own selection), numpy generator over row ids i = first..first+n
+COLUMNS = [
+    ("tiny", "INT8", None, lambda i: ((i % 256) - 128).astype(np.int8)),
+    ("small", "INT16", None, lambda i: ((i % 65536) - 32768).astype(np.int16)),
+    ("int", "INT32", None, lambda i: i.astype(np.int32)),
+    ("big", "INT64", None, lambda i: i * 10),
+    ("ubig", "UINT64", None, lambda i: (i * 10).astype(np.uint64)),
+    ("flt", "FLOAT", None, lambda i: i.astype(np.float32) / np.float32(100)),
+    ("dbl", "DOUBLE", None, lambda i: i / 1000.0),
+    ("dec", "DECIMAL", None, lambda i: (i % 10_000_000) * 100, 10, 2),
+    ("date", "DATE", None, lambda i: (8116 + (i % 10000)).astype(np.int32)),
+    ("ts", "TIMESTAMP", None, lambda i: 1_735_689_600_000_000 + i * 1_000_000),
+    # VARCHAR 'Value ' || (i % 1000): a 1000-key dictionary; the scan decodes the codes (the reference emits a
+    # DICTIONARY_VECTOR = selection vector over a per-row-group dictionary, dictionary_kernel.hpp:89-100)
+    ("varchar_codes", "UINT16", "DICT", lambda i: (i % 1000).astype(np.uint16)),
+]
+
+
+def build_table_image(n_rows, threads, batch_rows=64 * 65536):
+    """Encode the all_types table with the product writer (host C++), batch by batch so the raw columns never exist
+    in full.  Returns the container image as a numpy uint8 array."""
+    import flsgpu
+    specs = []
+    for c in COLUMNS:
+        specs.append((c[0], c[1], c[2]) + tuple(c[4:6]))
+    w = flsgpu.Writer(specs, 64)
+    done = 0
+    while done < n_rows:
+        n = min(batch_rows, n_rows - done)
+        i = np.arange(done + 1, done + n + 1, dtype=np.int64)
+        w.append([c[3](i) for c in COLUMNS], threads)
+        done += n
+    img = w.finish()
+    return w, img
+
+
+META_DT = np.dtype([("base", "<u8"), ("data_off16", "<u4"), ("aux_off", "<u4"), ("aux_cnt", "<u2"), ("width", "u1"),
+                    ("width2", "u1"), ("e", "u1"), ("f", "u1"), ("n_valid", "<u2"), ("reserved", "<u8")])
+assert META_DT.itemsize == 32
+
+
+def algorithmic_bytes(t, img, col):
+    """SURVEY.md 8(d), per 1024-value vector: C = compressed bytes read, D = 1024*sizeof(T_out) written.
+    FFOR-like: 128*W + sizeof(T) + 1; DELTA: + 128 (lane bases); DICT: 128*W_code + 1 (+ |dict|*sizeof(T) once per row
+    group); RLE: 128*W_idx + 128 + 1 + n_runs*sizeof(T); ALP: 128*W + 8 + 1 + 2 + 2 + n_exc*(sizeof(T)+2);
+    ALP_RD: 128*(W_r + W_l) + 2 + 16 + 2 + n_exc*4; CONSTANT: sizeof(T); UNCOMPRESSED: 1024*sizeof(T);
+    + 4 B per vector for the entry point."""
+    cd = t.column(col)
+    sz = cd.phys_bits // 8
+    read = 0
+    written = 0
+    for r in range(t.n_rowgroups):
+        ch = t.chunk(r, col)
+        off = ch.offset + ch.seg_off[0]
+        m = np.frombuffer(img, dtype=META_DT, count=ch.n_vec, offset=off)
+        w = m["width"].astype(np.int64)
+        w2 = m["width2"].astype(np.int64)
+        nx = m["aux_cnt"].astype(np.int64)
+        enc = ch.encoding
+        nv = ch.n_vec
+        if enc == 0:      # UNCOMPRESSED
+            c = nv * 1024 * sz
+        elif enc == 1:    # CONSTANT
+            c = nv * sz
+        elif enc == 3:    # DELTA
+            c = int((128 * w).sum()) + nv * (128 + sz + 1)
+        elif enc == 4:    # DICT
+            c = int((128 * w).sum()) + nv * 1 + ch.aux_count * sz
+        elif enc == 5:    # RLE
+            c = int((128 * w).sum()) + nv * (128 + 1) + int(nx.sum()) * sz
+        elif enc == 6:    # ALP
+            c = int((128 * w).sum()) + nv * (8 + 1 + 2 + 2) + int(nx.sum()) * (sz + 2)
+        elif enc == 7:    # ALP_RD
+            c = int((128 * (w + w2)).sum()) + nv * (2 + 16 + 2) + int(nx.sum()) * 4
+        elif enc == 8:    # CROSS_RLE
+            c = ch.aux_count * (sz + 4)
+        else:             # FFOR, FREQUENCY, SLPATCH
+            c = int((128 * w).sum()) + nv * (sz + 1) + int(nx.sum()) * (sz + 2)
+        read += c + 4 * nv
+        written += nv * 1024 * sz
+    return read, written
+
+
+class ClockSampler:
+    """SM clock + throttle reasons DURING the timed region, polled through NVML every few ms (the timed region of a
+    resident scan is tens of ms, shorter than nvidia-smi's start-up)."""
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.sm, self.reasons = [], set()
+        self.stop_flag = threading.Event()
+        self.thread = None
+        self.max_mhz = None
+        self.err = None
+
+    def _run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.idx)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+            while not self.stop_flag.is_set():
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                for name, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.002)
+        except Exception as e:  # NVML missing: report it, never fake a clock
+            self.err = f"{type(e).__name__}: {e}"
+
+    def start(self):
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+        time.sleep(0.05)
+        self.sm.clear()
+
+    def stop(self):
+        self.stop_flag.set()
+        self.thread.join(timeout=2)
+        out = {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+               "reasons": sorted(self.reasons), "samples": len(self.sm)}
+        if self.err:
+            out["error"] = self.err
+        return out
+
+
+def bench_config(rows, n_cols, extra=None):
+    cfg = {"workload": WORKLOAD, "rows_per_gpu": rows, "columns": n_cols, "rowgroup_rows": 65536,
+           "sharding": "row groups, one table shard per rank"}
+    cfg.update(extra or {})
+    return cfg
+
+
+def timed_cpu_scan(o, cols, n_rg, threads, target_seconds):
+    """Repeat the bounded oracle scan until ~target_seconds of CPU work have been timed."""
+    total_b, total_t, passes = 0, 0.0, 0
+    while total_t < target_seconds and passes < 1000:
+        t0 = time.perf_counter()
+        nb, _ = o.scan(cols, 0, n_rg, threads)
+        total_t += time.perf_counter() - t0
+        total_b += nb
+        passes += 1
+    return total_b, total_t, passes
+
+
+def cpu_scan(img, n_rowgroups, n_cols, threads, target_seconds):
+    """Oracle scan (reference-shaped: 2048-row chunks, a row group per thread) over a bounded prefix of the row
+    groups.  Returns (decoded GB/s, sample description, seconds per pass, rg count)."""
+    import oracle_lib
+    o = oracle_lib.Oracle(img)
+    cols = list(range(n_cols))
+    probe = min(n_rowgroups, max(threads * 2, 32))
+    t0 = time.perf_counter()
+    nb, _ = o.scan(cols, 0, probe, threads)
+    dt = time.perf_counter() - t0
+    rate = nb / dt
+    per_rg = nb / probe
+    n_rg = int(min(n_rowgroups, max(probe, target_seconds * rate / per_rg)))
+    return o, cols, n_rg
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU path on the host cores (oracle port; the reference binary is unbuildable here)."""
+    if rank != 0:
+        return
+    import flsgpu  # the WRITER lives in the product library; the timed decode below is oracle-only
+    threads = os.cpu_count() or 1
+    w, img = build_table_image(args.rows, threads)
+    t = flsgpu.Table(img)
+    o, cols, n_rg = cpu_scan(img, t.n_rowgroups, t.n_columns, threads, args.cpu_seconds / max(1, args.steps))
+    for _ in range(args.warmup):
+        o.scan(cols, 0, min(n_rg, 64), threads)
+    total_b, total_t = 0, 0.0
+    per_step = args.cpu_seconds / max(1, args.steps)
+    passes = 0
+    for _ in range(args.steps):
+        b_, t_, p_ = timed_cpu_scan(o, cols, n_rg, threads, per_step)
+        total_b += b_
+        total_t += t_
+        passes += p_
+    gbps = total_b / total_t / 1e9
+    sample = (f"{passes} passes over the first {n_rg} of {t.n_rowgroups} row groups x {t.n_columns} columns, "
+              f"{total_t:.1f} s, oracle scan, one row group per thread")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gbps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_t / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": bench_config(args.rows, t.n_columns, {"note": "CPU restatement of the reference scan (oracle port); the reference's own FastLanes library is not vendored"}),
+        "cpu_baseline": {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": gbps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    t.close()
+    w.close()
+
+
+def kernel_name(t, col):
+    """Which kernel template decodes this column (for grouping launches in the roofline)."""
+    import flsgpu
+    encs = sorted({flsgpu.ENC_NAME[t.chunk(r, col).encoding] for r in range(0, t.n_rowgroups, max(1, t.n_rowgroups // 64))})
+    T = t.column(col).phys_bits
+    fam = "dict" if encs == ["DICT"] else "rle" if encs == ["RLE"] else "main"
+    return f"fls_decode_kernel<{fam},T={T}>", encs
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import flsgpu
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    flsgpu.init((local_rank,))
+    threads = max(1, (os.cpu_count() or 1) // max(1, world))
+    t_build = time.perf_counter()
+    w, img = build_table_image(args.rows, threads)
+    t = flsgpu.Table(img)  # zero-copy view of the writer's image; page-locked on first stage
+    build_s = time.perf_counter() - t_build
+    n_cols = t.n_columns
+    stream = torch.cuda.current_stream().cuda_stream
+    t.stage(stream=stream)
+    torch.cuda.synchronize()
+
+    widths = [t.column(c).phys_bits // 8 for c in range(n_cols)]
+    out_elems = t.out_elems(t.n_rowgroups)
+    outs = [torch.empty(out_elems * wd, dtype=torch.uint8, device="cuda") for wd in widths]
+    decoded_bytes = sum(t.n_tuples * wd for wd in widths)  # real tuples only (padding of the last vector excluded)
+    compressed_bytes = t.resident_bytes()
+
+    def scan_step(events=None):
+        for c in range(n_cols):
+            if events is not None:
+                events[c][0].record()
+            t.decode_column(c, outs[c].data_ptr(), outs[c].numel(), stream=stream)
+            if events is not None:
+                events[c][1].record()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        scan_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = flsgpu.launch_count()
+    ev = [[(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_cols)]
+          for _ in range(args.steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for s in range(args.steps):
+        scan_step(ev[s])
+    e1.record()
+    barrier()
+    launches = flsgpu.launch_count() - launches0
+    total_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    col_ms = [float(np.mean([ev[s][c][0].elapsed_time(ev[s][c][1]) for s in range(args.steps)])) for c in range(n_cols)]
+
+    # ---- end to end: pinned host container -> H2D -> decode -> D2H into pinned host buffers, every step
+    host_outs = [flsgpu.host_alloc(out_elems * wd) for wd in widths]
+    e2e_times = []
+    for s in range(1 + args.steps):
+        t.evict()
+        barrier()
+        t0 = time.perf_counter()
+        for c in range(n_cols):
+            t.scan_column_to_host(c, host_outs[c], out_elems * widths[c])
+        dt = time.perf_counter() - t0
+        if s > 0:
+            e2e_times.append(dt)
+    e2e_s = float(np.sum(e2e_times))
+    # PCIe limit of this box, measured the plain way: one 1 GiB pinned<->device copy each direction
+    probe_dev = torch.empty(1 << 30, dtype=torch.uint8, device="cuda")
+    probe_host = torch.empty(1 << 30, dtype=torch.uint8).pin_memory()
+    pcie = {}
+    for name, (dst, src) in {"d2h": (probe_host, probe_dev), "h2d": (probe_dev, probe_host)}.items():
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        dst.copy_(src, non_blocking=True)
+        p1.record()
+        torch.cuda.synchronize()
+        pcie[name + "_GBps"] = round((1 << 30) / p0.elapsed_time(p1) / 1e6, 1)
+    del probe_dev, probe_host
+    # spot check of the e2e result against the generator (first and last rows of two columns)
+    big = np.ctypeslib.as_array((__import__("ctypes").c_int64 * 4).from_address(host_outs[3]))
+    assert list(big) == [10, 20, 30, 40], "e2e scan returned wrong data"
+
+    # ---- reduce over ranks: time = max, bytes = sum; reduced scan result (COUNT, SUM(int)) via NCCL
+    tm = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device="cuda")
+    by = torch.tensor([float(decoded_bytes), float(t.n_tuples)], dtype=torch.float64, device="cuda")
+    int_col = outs[2].view(torch.int32)
+    partial = torch.stack([int_col[: min(t.n_tuples, 65536)].to(torch.int64).sum(),
+                           torch.tensor(t.n_tuples, device="cuda", dtype=torch.int64)])
+    if dist is not None:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(by, op=dist.ReduceOp.SUM)
+        dist.all_reduce(partial, op=dist.ReduceOp.SUM)
+    total_ms, e2e_s = tm.tolist()
+    all_bytes, all_rows = by.tolist()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    value = all_bytes * args.steps / (total_ms / 1e3) / 1e9
+    e2e_value = all_bytes * args.steps / e2e_s / 1e9
+
+    # ---- roofline of the dominant kernel template
+    groups = {}
+    per_column = []
+    for c in range(n_cols):
+        name, encs = kernel_name(t, c)
+        rd, wr = algorithmic_bytes(t, img, c)
+        g = groups.setdefault(name, {"ms": 0.0, "bytes": 0, "launches": 0})
+        g["ms"] += col_ms[c]
+        g["bytes"] += rd + wr
+        g["launches"] += 1
+        per_column.append({"column": COLUMNS[c][0], "kernel": name, "encodings": encs, "ms": round(col_ms[c], 4),
+                           "alg_read_MB": round(rd / 1e6, 2), "alg_write_MB": round(wr / 1e6, 2),
+                           "alg_GBps": round((rd + wr) / col_ms[c] / 1e6, 1)})
+    dom = max(groups, key=lambda k: groups[k]["ms"])
+    g = groups[dom]
+    achieved = g["bytes"] / g["ms"] / 1e6  # GB/s
+    peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peak = float(json.load(f)["hbm_gbs"])
+            peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        pass
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(dom)
+    except (OSError, ValueError):
+        pass
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                "launches_per_step": g["launches"], "alg_bytes_per_launch": g["bytes"] // g["launches"],
+                "avg_launch_ms": round(g["ms"] / g["launches"], 4), "share_of_step": round(g["ms"] / sum(col_ms), 3)}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        o, cols, n_rg = cpu_scan(img, t.n_rowgroups, n_cols, cores, args.cpu_seconds)
+        nb, dt, passes = timed_cpu_scan(o, cols, n_rg, cores, args.cpu_seconds)
+        cpu = {"value": round(nb / dt / 1e9, 3), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{passes} passes over the first {n_rg} of {t.n_rowgroups} row groups x {n_cols} columns, {dt:.1f} s, oracle scan, one row group per thread"}
+
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+        "config": bench_config(args.rows, n_cols, {
+            "row_groups_per_gpu": t.n_rowgroups, "compressed_MB_per_gpu": round(compressed_bytes / 1e6, 1),
+            "decoded_MB_per_gpu": round(decoded_bytes / 1e6, 1),
+            "l2": "inputs + outputs per step exceed L2 (126 MB); no explicit flush", "table_build_s": round(build_s, 1)}),
+        "values_per_s": round(all_rows * n_cols * args.steps / (total_ms / 1e3), 1),
+        "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(compressed_bytes),
+                "d2h_bytes_per_step": int(sum(out_elems * wd for wd in widths)), "ms_per_step": round(e2e_s / args.steps * 1e3, 2), "pcie_measured": pcie},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        "per_column": per_column, "reduced_scan": {"count": int(partial[1].item()), "sum_int_prefix": int(partial[0].item())},
+    }
+    print(json.dumps(line), flush=True)
+    for p in host_outs:
+        flsgpu.host_free(p)
+    t.close()
+    w.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="flsgpu", choices=["flsgpu", "reference"])
+    ap.add_argument("--rows", type=int, default=100_000_000, help="rows of the all_types table per GPU")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU baseline sample budget")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
