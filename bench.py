@@ -312,8 +312,7 @@ def run_gpu(args, rank, world, local_rank):
         t.evict()
         barrier()
         t0 = time.perf_counter()
-        for c in range(n_cols):
-            t.scan_column_to_host(c, host_outs[c], out_elems * widths[c])
+        t.scan_columns_to_host(list(range(n_cols)), host_outs, [out_elems * wd for wd in widths])
         dt = time.perf_counter() - t0
         if s > 0:
             e2e_times.append(dt)

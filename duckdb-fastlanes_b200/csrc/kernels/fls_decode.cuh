@@ -13,7 +13,7 @@
 #include "fls_device.h"
 #include "fls_store.cuh"
 
-namespace flsk {
+namespace FLS_NS {
 
 __constant__ double c_fact_d[19] = {1e0, 1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,
                                     1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18};
@@ -53,8 +53,8 @@ struct VecDesc {
 	uint32_t aux_off;
 	uint32_t bytes; // TMA bytes of the blob (0: nothing to copy)
 	uint32_t misc;  // aux_cnt | width << 16 | encoding << 24
-	uint32_t misc2; // width2 | e << 8 | f << 16 | vec_in_chunk << 24 (low 8 bits only, CROSS_RLE uses full value below)
-	uint32_t vec_in_chunk;
+	uint32_t misc2; // width2 | e << 8 | f << 16
+	uint32_t vec_in_chunk; // vector index inside its chunk | n_valid << 16
 };
 
 __device__ __forceinline__ VecDesc shfl_desc(const VecDesc& d, int src) {
@@ -104,7 +104,7 @@ __device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
 			const uint32_t aux_cnt = m1.x & 0xffffu, w = (m1.x >> 16) & 0xffu, w2 = m1.x >> 24;
 			d.misc = aux_cnt | (w << 16) | (enc << 24);
 			d.misc2 = w2 | ((m1.y & 0xffffu) << 8);
-			d.vec_in_chunk = vi;
+			d.vec_in_chunk = vi | (m1.y & 0xffff0000u);
 			d.bytes = blob_bytes<T>(enc, w, w2);
 			d.blob = ch->data + (size_t)m0.z * 16;
 			d.ch = ch;
@@ -175,7 +175,7 @@ template <int T, int OB>
 __device__ __forceinline__ void decode_cross_rle(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv) {
 	const uint32_t* starts = reinterpret_cast<const uint32_t*>(d.ch->aux1);
 	const uint32_t n_runs = d.ch->aux_count;
-	const uint32_t g0 = d.vec_in_chunk * 1024u;
+	const uint32_t g0 = (d.vec_in_chunk & 0xffffu) * 1024u;
 	// first run of this vector (uniform binary search): largest r with starts[r] <= g0
 	uint32_t lo_r = 0, hi_r = n_runs;
 	while (hi_r - lo_r > 1) {
@@ -204,4 +204,82 @@ __device__ __forceinline__ void decode_cross_rle(uint8_t* out_vec, const VecDesc
 	}
 }
 
-} // namespace flsk
+// ---- fused aggregates (SUM as 128-bit, COUNT, MIN, MAX; reference semantics: DuckDB SUM(BIGINT) -> HUGEINT,
+// SUM(DECIMAL(p,s)) -> DECIMAL(38,s), duckdb/extension/core_functions/aggregate/distributive/sum.cpp:161-210) -------------
+struct AggPartial {
+	unsigned long long lo = 0;   // low 64 bits of the running sum
+	long long hi = 0;            // carries out of `lo` minus the number of negative addends
+	unsigned long long cnt = 0;
+	unsigned long long kmin = ~0ull, kmax = 0ull; // order keys
+	double fs = 0.0;
+
+	// Fold the first n_valid values of the natural-order tile (VT-bit elements) into the partials.
+	template <int VT>
+	__device__ __forceinline__ void fold(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float) {
+		const unsigned long long flip = is_signed ? 0x8000000000000000ull : 0ull;
+#pragma unroll 4
+		for (uint32_t i = lane; i < 1024u; i += 32u) {
+			if (i >= n_valid) {
+				break;
+			}
+			unsigned long long u;
+			if constexpr (VT == 8) {
+				u = tile[i];
+				u = is_signed ? (unsigned long long)(long long)(int8_t)u : u;
+			} else if constexpr (VT == 16) {
+				u = reinterpret_cast<const uint16_t*>(tile)[i];
+				u = is_signed ? (unsigned long long)(long long)(int16_t)u : u;
+			} else if constexpr (VT == 32) {
+				const uint32_t w = reinterpret_cast<const uint32_t*>(tile)[i];
+				if (is_float) {
+					fs += (double)__uint_as_float(w);
+					continue;
+				}
+				u = is_signed ? (unsigned long long)(long long)(int32_t)w : w;
+			} else {
+				u = reinterpret_cast<const unsigned long long*>(tile)[i];
+				if (is_float) {
+					fs += __longlong_as_double((long long)u);
+					continue;
+				}
+			}
+			lo += u;
+			hi += (lo < u) ? 1 : 0;
+			hi -= (is_signed && (long long)u < 0) ? 1 : 0;
+			const unsigned long long key = u ^ flip;
+			kmin = key < kmin ? key : kmin;
+			kmax = key > kmax ? key : kmax;
+		}
+		cnt += n_valid > (uint32_t)lane ? (n_valid - lane + 31u) / 32u : 0u;
+	}
+
+	// Warp reduction, then one set of atomics per warp.
+	__device__ __forceinline__ void flush(flsgpu_agg_acc* acc, int lane, uint32_t is_float) {
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) {
+			const unsigned long long olo = __shfl_down_sync(0xffffffffu, lo, o);
+			const long long ohi = __shfl_down_sync(0xffffffffu, hi, o);
+			lo += olo;
+			hi += ohi + ((lo < olo) ? 1 : 0);
+			cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+			const unsigned long long omin = __shfl_down_sync(0xffffffffu, kmin, o), omax = __shfl_down_sync(0xffffffffu, kmax, o);
+			kmin = omin < kmin ? omin : kmin;
+			kmax = omax > kmax ? omax : kmax;
+			fs += __shfl_down_sync(0xffffffffu, fs, o);
+		}
+		if (lane == 0 && cnt) {
+			atomicAdd(&acc->count, cnt);
+			if (is_float) {
+				atomicAdd(&acc->fsum, fs);
+			} else {
+				const unsigned long long old = atomicAdd(&acc->sum_lo, lo);
+				const unsigned long long carry = (old + lo < old) ? 1ull : 0ull;
+				atomicAdd(&acc->sum_hi, (unsigned long long)hi + carry);
+				atomicMin(&acc->key_min, kmin);
+				atomicMax(&acc->key_max, kmax);
+			}
+		}
+	}
+};
+
+} // namespace FLS_NS

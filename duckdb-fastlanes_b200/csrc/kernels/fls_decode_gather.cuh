@@ -2,7 +2,7 @@
 #pragma once
 #include "fls_decode.cuh"
 
-namespace flsk {
+namespace FLS_NS {
 
 // dec_dict_opr<KEY, IDX> (reference dictionary_kernel.hpp:11-22): out[i] = keys[index[i]].
 // IT = lane width of the codes (8/16/32), VT = key width.  A thread's G = 32/IT adjacent codes give G adjacent
@@ -81,4 +81,4 @@ __device__ __forceinline__ void process_rle(const VecDesc& d, const uint8_t* slo
 	}
 }
 
-} // namespace flsk
+} // namespace FLS_NS

@@ -3,7 +3,7 @@
 #include "fls_decode.cuh"
 #include "fls_decode_gather.cuh"
 
-namespace flsk {
+namespace FLS_NS {
 
 // ---- T in {8,16,32} ------------------------------------------------------------------------------------------------------
 template <int T, int OB>
@@ -197,16 +197,23 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 // ---- the persistent kernel -----------------------------------------------------------------------------------------------
 // MODE 0: main family (T = physical lane width = VT); MODE 1: DICT (T = code lane width, VT = key width);
 // MODE 2: RLE (T = 16: run-index lanes, VT = value width).
-template <int MODE, int T, int VT, int OB>
+// AGG: the vector is decoded into the warp's shared-memory tile (FLS_SINK_SHARED translation unit) and folded into
+// per-thread partial aggregates instead of being written to HBM.
+template <int MODE, int T, int VT, int OB, bool AGG = false>
 __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const FlsLaunch L) {
 	extern __shared__ __align__(128) uint8_t smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const uint32_t n_slots = L.n_slots;
+	const uint32_t wpc = blockDim.x >> 5; // warps per CTA: kWarpsPerCta unless the launcher had to shrink the CTA to fit shared memory
 	uint64_t* bars = reinterpret_cast<uint64_t*>(smem) + warp * n_slots;
-	const uint32_t bar_bytes = (kWarpsPerCta * n_slots * 8 + 127u) & ~127u;
-	const uint32_t warp_bytes = n_slots * L.slot_bytes + L.stage_bytes;
+	const uint32_t bar_bytes = (wpc * n_slots * 8 + 127u) & ~127u;
+	constexpr uint32_t kTileBytes = AGG ? 1024u * OB : 0u;
+	const uint32_t warp_bytes = n_slots * L.slot_bytes + L.stage_bytes + kTileBytes;
 	uint8_t* slots = smem + bar_bytes + (size_t)warp * warp_bytes;
 	uint8_t* stage = slots + (size_t)n_slots * L.slot_bytes;
+	uint8_t* tile = stage + L.stage_bytes;
+	AggPartial part;
+	(void)tile;
 
 	if (lane == 0) {
 		for (uint32_t s = 0; s < n_slots; ++s) {
@@ -216,8 +223,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const Fls
 	}
 	__syncwarp();
 
-	const uint32_t n_warps = gridDim.x * kWarpsPerCta;
-	const uint32_t gw = blockIdx.x * kWarpsPerCta + warp;
+	const uint32_t n_warps = gridDim.x * wpc;
+	const uint32_t gw = blockIdx.x * wpc + warp;
 	uint32_t phases = 0; // bit s: parity to wait for on slot s
 	uint32_t n_done = 0; // vectors processed by this warp (slot = n_done % n_slots)
 	uint8_t* const out = static_cast<uint8_t*>(L.out);
@@ -249,7 +256,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const Fls
 				mbar_wait(bars + slot, (phases >> slot) & 1u);
 				phases ^= 1u << slot;
 			}
-			uint8_t* out_vec = out + (size_t)(b0 + (uint64_t)k * n_warps) * 1024u * OB;
+			uint8_t* out_vec = AGG ? tile : out + (size_t)(b0 + (uint64_t)k * n_warps) * 1024u * OB;
 			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
 			if constexpr (MODE == 1) {
 				process_dict<T, VT, OB>(d, sp, out_vec, lane, L.conv);
@@ -261,6 +268,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const Fls
 				process_small<T, OB>(d, sp, stage, out_vec, lane, L.conv);
 			}
 			__syncwarp(); // all lanes are done reading the slot (and the staging area)
+			if constexpr (AGG) {
+				part.template fold<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float);
+				__syncwarp();
+			}
 			if (to_issue) {
 				const int kn = __ffs(to_issue) - 1;
 				to_issue &= to_issue - 1;
@@ -274,6 +285,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const Fls
 			++n_done;
 		}
 	}
+	if constexpr (AGG) {
+		part.flush(L.agg, lane, L.agg_float);
+	}
 }
 
-} // namespace flsk
+} // namespace FLS_NS

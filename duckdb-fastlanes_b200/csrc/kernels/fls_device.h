@@ -18,6 +18,17 @@ struct alignas(16) FlsChunkDev {
 };
 static_assert(sizeof(FlsChunkDev) == 64, "FlsChunkDev must be 64 bytes");
 
+// Device-side accumulator of the fused aggregates; same 64 bytes as flsgpu_agg_result (include/flsgpu.h).  min/max are
+// kept as ORDER KEYS (value ^ sign bit for signed columns) in key_min/key_max so that a zeroed-then-reset accumulator
+// works for either signedness; flsgpu_aggregate_column's finalize step writes min_val/max_val from them.
+struct flsgpu_agg_acc {
+	unsigned long long sum_lo, sum_hi, count;
+	long long min_val, max_val;
+	double fsum;
+	unsigned long long key_min, key_max;
+};
+static_assert(sizeof(flsgpu_agg_acc) == 64, "flsgpu_agg_acc must mirror flsgpu_agg_result");
+
 // Launch parameters of one decode launch: column `col` of row groups [rg_begin, rg_begin + n_rg).
 struct FlsLaunch {
 	const FlsChunkDev* chunks; // &chunk_dev[rg_begin * n_cols + col]
@@ -31,6 +42,10 @@ struct FlsLaunch {
 	uint32_t family_mask;      // bit e set: this kernel handles encoding e
 	uint32_t idx_bits;         // DICT launches: only chunks whose codes sit in idx_bits-wide lanes (0: any)
 	void* out;
+	// fused aggregate launches (flsgpu_aggregate_column): out is unused, partials are folded into *agg
+	flsgpu_agg_acc* agg;
+	uint32_t agg_signed; // integer columns: 1 = two's complement values
+	uint32_t agg_float;  // 1 = FLOAT/DOUBLE column (fsum + count only)
 };
 
 // Encoding families (which kernel template handles which fls_encoding)

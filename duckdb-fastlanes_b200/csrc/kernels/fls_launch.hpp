@@ -13,4 +13,12 @@ const void* fls_kernel_rle(int VT, int OB);
 // Fused decode + aggregate (SUM/COUNT/MIN/MAX): same families, output replaced by a reduction.
 const void* fls_kernel_agg(int mode, int T, int VT);
 
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#endif
+#if defined(__CUDACC__) || defined(CUDART_VERSION)
+cudaError_t fls_agg_finalize(flsgpu_agg_acc* acc, uint32_t is_signed, cudaStream_t stream);
+cudaError_t fls_agg_reset(flsgpu_agg_acc* acc, cudaStream_t stream);
+#endif
+
 constexpr int kFlsWarpsPerCta = 8;

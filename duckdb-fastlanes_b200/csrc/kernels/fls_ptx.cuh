@@ -2,7 +2,11 @@
 #pragma once
 #include <stdint.h>
 
-namespace flsk {
+#ifndef FLS_NS
+#define FLS_NS flsk // see fls_unpack.cuh
+#endif
+
+namespace FLS_NS {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 	return (uint32_t)__cvta_generic_to_shared(p);
@@ -47,6 +51,24 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
 	             : "memory");
 }
 
+#if defined(FLS_SINK_SHARED)
+// Aggregate kernels: the "output vector" is the warp's shared-memory tile (generic pointer into shared memory).
+__device__ __forceinline__ void st_cs_u32(void* p, uint32_t a) {
+	asm volatile("st.shared.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(a) : "memory");
+}
+__device__ __forceinline__ void st_cs_v2(void* p, uint32_t a, uint32_t b) {
+	asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void st_cs_v4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+	asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void st_cs_u16(void* p, uint32_t a) {
+	asm volatile("st.shared.u16 [%0], %1;" ::"r"(smem_u32(p)), "h"((uint16_t)a) : "memory");
+}
+__device__ __forceinline__ void st_cs_u8(void* p, uint32_t a) {
+	*reinterpret_cast<uint8_t*>(p) = (uint8_t)a;
+}
+#else
 // streaming stores: decoded output is written once and not re-read by this kernel
 __device__ __forceinline__ void st_cs_u32(void* p, uint32_t a) {
 	asm volatile("st.global.cs.u32 [%0], %1;" ::"l"(p), "r"(a) : "memory");
@@ -64,4 +86,6 @@ __device__ __forceinline__ void st_cs_u8(void* p, uint32_t a) {
 	*reinterpret_cast<uint8_t*>(p) = (uint8_t)a;
 }
 
-} // namespace flsk
+#endif
+
+} // namespace FLS_NS

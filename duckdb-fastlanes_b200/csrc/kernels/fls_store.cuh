@@ -6,7 +6,7 @@
 #include "fls_ptx.cuh"
 #include "fls_unpack.cuh"
 
-namespace flsk {
+namespace FLS_NS {
 
 // (lo,hi) of one T-bit value -> OB-byte value
 template <int T, int OB>
@@ -144,4 +144,4 @@ __device__ __forceinline__ void copy_out_linear(const uint8_t* smem, uint8_t* ou
 	}
 }
 
-} // namespace flsk
+} // namespace FLS_NS

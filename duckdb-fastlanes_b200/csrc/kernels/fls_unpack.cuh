@@ -19,7 +19,13 @@
 #define FLS_HD inline
 #endif
 
-namespace flsk {
+// The aggregate translation unit re-instantiates every template with its stores aimed at shared memory
+// (FLS_SINK_SHARED); it does so in its own namespace so that the two sets of instantiations never alias.
+#ifndef FLS_NS
+#define FLS_NS flsk
+#endif
+
+namespace FLS_NS {
 
 FLS_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {
 #if defined(__CUDA_ARCH__)
@@ -205,4 +211,4 @@ FLS_HD void unpack_64_dispatch(int W, const uint32_t* s32, int tid, uint32_t (&l
 	}
 }
 
-} // namespace flsk
+} // namespace FLS_NS

@@ -208,13 +208,20 @@ void pin_image(flsgpu_table* t, FlsDeviceState* d) {
 	}
 }
 
-// Copy the chunks of `col` (or of every column when col == ALL) of row groups [rg_begin, rg_begin+n_rg) that are not
-// resident yet.  Adjacent chunks are merged into one cudaMemcpyAsync.
-constexpr uint32_t kAllColumns = 0xffffffffu;
+// Copy the chunks of the listed columns (every column when cols == nullptr) of row groups [rg_begin, rg_begin+n_rg)
+// that are not resident yet.  Chunks that are adjacent in the file - or separated by less than kMergeGap bytes of
+// chunks nobody asked for - are merged into one cudaMemcpyAsync: a copy call costs a few microseconds of PCIe time,
+// as much as ~256 KiB of payload.
+constexpr uint64_t kMergeGap = 256u << 10;
 
-int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t n_rg, uint32_t col, cudaStream_t stream) {
+int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t n_rg, const uint32_t* cols, uint32_t n_sel,
+                cudaStream_t stream) {
 	pin_image(t, d);
 	const uint32_t n_cols = t->header.n_columns;
+	std::vector<uint8_t> want(n_cols, cols ? 0 : 1);
+	for (uint32_t i = 0; cols && i < n_sel; ++i) {
+		want[cols[i]] = 1;
+	}
 	uint64_t run_begin = 0, run_end = 0; // pending merged copy [begin, end) in file offsets
 	auto flush = [&]() -> int {
 		if (run_end > run_begin) {
@@ -226,15 +233,14 @@ int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t 
 		return FLSGPU_OK;
 	};
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
-		const uint32_t c0 = col == kAllColumns ? 0 : col, c1 = col == kAllColumns ? n_cols : col + 1;
-		for (uint32_t c = c0; c < c1; ++c) {
+		for (uint32_t c = 0; c < n_cols; ++c) {
 			const uint64_t i = (uint64_t)r * n_cols + c;
-			if (d->chunk_resident[i]) {
+			if (!want[c] || d->chunk_resident[i]) {
 				continue;
 			}
 			d->chunk_resident[i] = 1;
 			const fls_chunk_desc& ch = t->chunks[i];
-			if (run_end == ch.offset && run_end > run_begin) {
+			if (run_end > run_begin && ch.offset >= run_end && ch.offset - run_end <= kMergeGap) {
 				run_end = ch.offset + ch.size;
 			} else {
 				const int rc = flush();
@@ -290,7 +296,8 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 }
 
 // Pick pipeline depth / grid for `fn` and launch it.
-int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t stage_bytes, cudaStream_t stream) {
+int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t stage_bytes, cudaStream_t stream,
+                  uint32_t tile_bytes = 0) {
 	if (!fn) {
 		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "no kernel instantiation for this (lane width, value width, output width)");
 	}
@@ -298,13 +305,20 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	L.stage_bytes = stage_bytes;
 	// shared memory: aim for two resident CTAs per SM (~104 KB each) unless a single slot pair needs more
 	const uint32_t per_warp_budget = 13u * 1024u;
-	uint32_t n_slots = L.stage_bytes < per_warp_budget ? (per_warp_budget - L.stage_bytes) / L.slot_bytes : 0;
+	const uint32_t fixed = L.stage_bytes + tile_bytes; // per-warp bytes besides the pipeline slots
+	uint32_t n_slots = fixed < per_warp_budget ? (per_warp_budget - fixed) / L.slot_bytes : 0;
 	n_slots = std::max(2u, std::min(6u, n_slots));
 	L.n_slots = n_slots;
-	const uint32_t bar_bytes = (kFlsWarpsPerCta * n_slots * 8u + 127u) & ~127u;
-	const uint32_t smem = bar_bytes + kFlsWarpsPerCta * (n_slots * L.slot_bytes + L.stage_bytes);
-	if (smem > kMaxSmemPerCta) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "vector blob too large for the shared-memory pipeline");
+	uint32_t wpc = kFlsWarpsPerCta, smem = 0;
+	for (;; wpc >>= 1) { // wide vectors (8 KiB blobs + staging + aggregate tile) may need a smaller CTA to fit 227 KiB
+		const uint32_t bar_bytes = (wpc * n_slots * 8u + 127u) & ~127u;
+		smem = bar_bytes + wpc * (n_slots * L.slot_bytes + fixed);
+		if (smem <= kMaxSmemPerCta) {
+			break;
+		}
+		if (wpc == 1) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "vector blob too large for the shared-memory pipeline");
+		}
 	}
 	int occ = 0;
 	{
@@ -313,10 +327,10 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 			FLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmemPerCta));
 			g_func_ready[fn] = 1;
 		}
-		const auto key = std::make_pair(fn, smem);
+		const auto key = std::make_pair(fn, smem ^ (wpc << 24));
 		auto it = g_occ.find(key);
 		if (it == g_occ.end()) {
-			FLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kFlsWarpsPerCta * 32, smem));
+			FLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, (int)wpc * 32, smem));
 			g_occ[key] = occ;
 		} else {
 			occ = it->second;
@@ -325,10 +339,10 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	if (occ < 1) {
 		return fls_set_error(FLSGPU_ERR_CUDA, "decode kernel cannot be resident with the requested shared memory");
 	}
-	const uint64_t want = ((uint64_t)L.total_vecs + kFlsWarpsPerCta - 1) / kFlsWarpsPerCta;
+	const uint64_t want = ((uint64_t)L.total_vecs + wpc - 1) / wpc;
 	const uint32_t grid = (uint32_t)std::min<uint64_t>(want, (uint64_t)occ * g_n_sms);
 	void* args[] = {&L};
-	FLS_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(kFlsWarpsPerCta * 32), args, smem, stream));
+	FLS_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(wpc * 32), args, smem, stream));
 	g_launches.fetch_add(1, std::memory_order_relaxed);
 	return FLSGPU_OK;
 }
@@ -374,7 +388,7 @@ int resolve_out(const fls_column_desc& col, int32_t out_type, OutSpec* o) {
 }
 
 int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const OutSpec& os,
-                       void* out_dev, cudaStream_t stream) {
+                       void* out_dev, cudaStream_t stream, flsgpu_agg_acc* agg = nullptr) {
 	const fls_file_header& h = t->header;
 	const int T = t->columns[col].phys_bits;
 	FlsColumnPlan p;
@@ -389,24 +403,29 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	L.total_vecs = n_rg * h.vec_per_rowgroup;
 	L.conv = os.conv;
 	L.out = out_dev;
+	L.agg = agg;
+	L.agg_signed = t->columns[col].is_signed;
+	L.agg_float = t->columns[col].is_float;
+	const uint32_t tile = agg ? 128u * T : 0u; // aggregate launches decode into a per-warp shared-memory tile
 	int rc = FLSGPU_OK;
 	if (p.has_main) {
 		L.family_mask = FLS_FAMILY_MAIN;
 		L.idx_bits = 0;
-		rc = launch_family(fls_kernel_main(T, os.ob), L, p.main_slot, p.main_needs_stage ? 128u * T : 0u, stream);
+		rc = launch_family(agg ? fls_kernel_agg(0, T, T) : fls_kernel_main(T, os.ob), L, p.main_slot,
+		                   p.main_needs_stage ? 128u * T : 0u, stream, tile);
 	}
 	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {
 		if (p.has_dict[k]) {
 			const int it = 8 << k;
 			L.family_mask = FLS_FAMILY_DICT;
 			L.idx_bits = (uint32_t)it;
-			rc = launch_family(fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream);
+			rc = launch_family(agg ? fls_kernel_agg(1, it, T) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile);
 		}
 	}
 	if (p.has_rle && rc == FLSGPU_OK) {
 		L.family_mask = FLS_FAMILY_RLE;
 		L.idx_bits = 0;
-		rc = launch_family(fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream);
+		rc = launch_family(agg ? fls_kernel_agg(2, 16, T) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
 	}
 	return rc;
 }
@@ -478,7 +497,7 @@ int flsgpu_table_stage(flsgpu_table* t, uint32_t rg_begin, uint32_t n_rg, void* 
 		return rc;
 	}
 	std::lock_guard<std::mutex> g(d->mu);
-	return stage_range(t, d, rg_begin, n_rg, kAllColumns, static_cast<cudaStream_t>(cuda_stream));
+	return stage_range(t, d, rg_begin, n_rg, nullptr, 0, static_cast<cudaStream_t>(cuda_stream));
 }
 
 int flsgpu_table_evict(flsgpu_table* t) {
@@ -577,30 +596,38 @@ int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids
 	return FLSGPU_OK;
 }
 
-int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type, void* out_host,
-                               uint64_t out_capacity_bytes) {
-	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_scan_column_to_host");
-	if (rc) {
-		return rc;
+int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg,
+                                const int32_t* out_types, void* const* out_hosts, const uint64_t* out_capacity_bytes) {
+	if (!t || !col_ids || !out_hosts || !out_capacity_bytes || n_cols == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_columns_to_host: null argument");
 	}
-	OutSpec os;
-	rc = resolve_out(t->columns[col], out_type, &os);
-	if (rc) {
-		return rc;
-	}
-	const uint64_t rg_bytes = (uint64_t)t->header.vec_per_rowgroup * FLS_VEC_SZ * os.ob;
-	if (!out_host || out_capacity_bytes < rg_bytes * n_rg) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_column_to_host: output buffer null or too small");
+	std::vector<OutSpec> os(n_cols);
+	std::vector<uint64_t> rg_bytes(n_cols);
+	uint64_t rg_bytes_all = 0;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		int rc = check_range(t, col_ids[i], rg_begin, n_rg, "flsgpu_scan_columns_to_host");
+		if (rc) {
+			return rc;
+		}
+		rc = resolve_out(t->columns[col_ids[i]], out_types ? out_types[i] : FLSGPU_OUT_NATIVE, &os[i]);
+		if (rc) {
+			return rc;
+		}
+		rg_bytes[i] = (uint64_t)t->header.vec_per_rowgroup * FLS_VEC_SZ * os[i].ob;
+		rg_bytes_all += rg_bytes[i];
+		if (!out_hosts[i] || out_capacity_bytes[i] < rg_bytes[i] * n_rg) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_columns_to_host: output buffer null or too small");
+		}
 	}
 	FlsDeviceState* d = nullptr;
-	rc = device_state(t, &d);
+	int rc = device_state(t, &d);
 	if (rc) {
 		return rc;
 	}
-	// slabs of ~32 MiB decoded: deep enough to hide launch latency, small enough that H2D, decode and D2H of
-	// neighbouring slabs overlap on the two streams
-	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (32ull << 20) / rg_bytes));
-	const uint64_t slab_bytes = rg_bytes * slab_rg;
+	// slabs of ~64 MiB decoded (all projected columns together): deep enough to hide launch latency, small enough
+	// that H2D, decode and D2H of neighbouring slabs overlap on the two streams
+	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (64ull << 20) / rg_bytes_all));
+	const uint64_t slab_bytes = rg_bytes_all * slab_rg;
 	if (d->scan_out_bytes < slab_bytes) {
 		for (int i = 0; i < 2; ++i) {
 			if (d->scan_streams[i]) {
@@ -623,21 +650,30 @@ int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin,
 		cudaStream_t s = d->scan_streams[slab & 1];
 		{
 			std::lock_guard<std::mutex> g(d->mu);
-			rc = stage_range(t, d, rg_begin + r, n, col, s);
+			rc = stage_range(t, d, rg_begin + r, n, col_ids, n_cols, s);
 		}
 		if (rc) {
 			return rc;
 		}
-		rc = decode_column_impl(t, d, col, rg_begin + r, n, os, d->scan_out[slab & 1], s);
-		if (rc) {
-			return rc;
+		uint8_t* dev = static_cast<uint8_t*>(d->scan_out[slab & 1]);
+		for (uint32_t i = 0; i < n_cols; ++i) {
+			rc = decode_column_impl(t, d, col_ids[i], rg_begin + r, n, os[i], dev, s);
+			if (rc) {
+				return rc;
+			}
+			FLS_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(out_hosts[i]) + (uint64_t)r * rg_bytes[i], dev, rg_bytes[i] * n,
+			                         cudaMemcpyDeviceToHost, s));
+			dev += rg_bytes[i] * slab_rg;
 		}
-		FLS_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(out_host) + (uint64_t)r * rg_bytes, d->scan_out[slab & 1], rg_bytes * n,
-		                         cudaMemcpyDeviceToHost, s));
 	}
 	FLS_CUDA(cudaStreamSynchronize(d->scan_streams[0]));
 	FLS_CUDA(cudaStreamSynchronize(d->scan_streams[1]));
 	return FLSGPU_OK;
+}
+
+int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type, void* out_host,
+                               uint64_t out_capacity_bytes) {
+	return flsgpu_scan_columns_to_host(t, &col, 1, rg_begin, n_rg, &out_type, &out_host, &out_capacity_bytes);
 }
 
 int flsgpu_sync(void* cuda_stream) {
@@ -672,9 +708,37 @@ uint64_t flsgpu_launch_count(void) {
 	return g_launches.load(std::memory_order_relaxed);
 }
 
-int flsgpu_aggregate_column(flsgpu_table*, uint32_t, uint32_t, uint32_t, flsgpu_agg_result*, void*) {
-	return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_aggregate_column: not built yet");
+int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, flsgpu_agg_result* result_dev,
+                            void* cuda_stream) {
+	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_aggregate_column");
+	if (rc) {
+		return rc;
+	}
+	if (!result_dev || (reinterpret_cast<uintptr_t>(result_dev) & 7u)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_aggregate_column: result pointer null or misaligned");
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	rc = check_resident(t, d, col, rg_begin, n_rg);
+	if (rc) {
+		return rc;
+	}
+	OutSpec os;
+	os.ob = t->columns[col].phys_bits / 8;
+	os.conv = 0;
+	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+	flsgpu_agg_acc* acc = reinterpret_cast<flsgpu_agg_acc*>(result_dev);
+	rc = decode_column_impl(t, d, col, rg_begin, n_rg, os, nullptr, s, acc);
+	if (rc) {
+		return rc;
+	}
+	FLS_CUDA(fls_agg_finalize(acc, t->columns[col].is_signed, s));
+	return FLSGPU_OK;
 }
+
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {
 	if (!result_dev) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_agg_reset: null argument");
@@ -683,7 +747,7 @@ int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {
 	if (rc) {
 		return rc;
 	}
-	FLS_CUDA(cudaMemsetAsync(result_dev, 0, sizeof(flsgpu_agg_result), static_cast<cudaStream_t>(cuda_stream)));
+	FLS_CUDA(fls_agg_reset(reinterpret_cast<flsgpu_agg_acc*>(result_dev), static_cast<cudaStream_t>(cuda_stream)));
 	return FLSGPU_OK;
 }
 

@@ -80,7 +80,7 @@ ABI_SYMBOLS = [
     "flsgpu_writer_destroy", "flsgpu_table_open", "flsgpu_table_open_memory", "flsgpu_table_close",
     "flsgpu_table_info_get", "flsgpu_table_column", "flsgpu_table_rowgroup", "flsgpu_table_chunk",
     "flsgpu_table_stage", "flsgpu_table_evict", "flsgpu_table_unstage", "flsgpu_table_resident_bytes", "flsgpu_decode_column",
-    "flsgpu_rowgroup_decode", "flsgpu_aggregate_column", "flsgpu_agg_reset", "flsgpu_scan_column_to_host",
+    "flsgpu_rowgroup_decode", "flsgpu_aggregate_column", "flsgpu_agg_reset", "flsgpu_scan_column_to_host", "flsgpu_scan_columns_to_host",
     "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
 ]
 
@@ -231,6 +231,15 @@ class Table:
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_scan_column_to_host(self._h, col, rg_begin, n_rg, out_type, _vp(out_host_ptr),
                                               C.c_uint64(out_bytes)), "scan_column_to_host")
+
+    def scan_columns_to_host(self, cols, out_host_ptrs, out_bytes, rg_begin=0, n_rg=None, out_types=None):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        n = len(cols)
+        ca = (C.c_uint32 * n)(*cols)
+        ta = (C.c_int32 * n)(*(out_types or [0] * n))
+        pa = (C.c_void_p * n)(*[int(p) for p in out_host_ptrs])
+        ba = (C.c_uint64 * n)(*out_bytes)
+        _check(lib.flsgpu_scan_columns_to_host(self._h, ca, n, rg_begin, n_rg, ta, pa, ba), "scan_columns_to_host")
 
     def valid_mask_slices(self, rg_begin=0, n_rg=None):
         """(start, stop) element ranges of real tuples in the decode_column output layout."""

@@ -133,6 +133,11 @@ int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream);
 int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type,
                                void* out_host, uint64_t out_capacity_bytes);
 
+/* Projection form (FastLanesReaderProjectionPlan, fls_multi_file_info.hpp:48-55): all projected columns of a slab are
+ * staged with merged copies, decoded and copied back together. out_hosts[i] receives column col_ids[i]. */
+int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg,
+                                const int32_t* out_types, void* const* out_hosts, const uint64_t* out_capacity_bytes);
+
 int flsgpu_sync(void* cuda_stream);
 /* Pinned host allocations for staging / results (cudaHostAlloc). */
 int flsgpu_host_alloc(uint64_t bytes, void** out);
