@@ -71,6 +71,12 @@ struct FlsColumnPlan { // what a decode launch over (col, rg range) needs to kno
 	uint32_t main_slot = 0, rle_slot = 0, dict_slot[3] = {0, 0, 0};
 };
 
+struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of neighbouring slabs overlap
+	cudaStream_t streams[2] = {nullptr, nullptr};
+	void* out[2] = {nullptr, nullptr};
+	uint64_t out_bytes = 0;
+};
+
 struct FlsDeviceState {
 	int device = 0;
 	uint8_t* d_image = nullptr; // bytes [0, footer_offset) of the container, same offsets as the file
@@ -82,10 +88,8 @@ struct FlsDeviceState {
 	bool host_pinned_tried = false;
 	bool host_registered = false;
 	std::map<std::tuple<uint32_t, uint32_t, uint32_t>, FlsColumnPlan> plans;
-	// pipelined scan (flsgpu_scan_column_to_host)
-	cudaStream_t scan_streams[2] = {nullptr, nullptr};
-	void* scan_out[2] = {nullptr, nullptr};
-	uint64_t scan_out_bytes = 0;
+	// pipelined scans (flsgpu_scan_columns_to_host): one scratch per concurrent caller, recycled through a free list
+	std::vector<FlsScanScratch*> scratch_all, scratch_free;
 	std::mutex mu;
 };
 
@@ -95,14 +99,16 @@ void fls_device_release(flsgpu_table* t) {
 		return;
 	}
 	cudaSetDevice(d->device);
-	for (int i = 0; i < 2; ++i) {
-		if (d->scan_streams[i]) {
-			cudaStreamSynchronize(d->scan_streams[i]);
-			cudaStreamDestroy(d->scan_streams[i]);
-		}
-		cudaFree(d->scan_out[i]);
-	}
 	cudaDeviceSynchronize();
+	for (FlsScanScratch* sc : d->scratch_all) {
+		for (int i = 0; i < 2; ++i) {
+			if (sc->streams[i]) {
+				cudaStreamDestroy(sc->streams[i]);
+			}
+			cudaFree(sc->out[i]);
+		}
+		delete sc;
+	}
 	cudaFree(d->d_image);
 	cudaFree(d->d_chunks);
 	cudaFree(d->d_run_starts);
@@ -117,7 +123,12 @@ namespace {
 
 // Allocate the HBM arena + device chunk table on first use.  Pointers in the chunk table are final from the start
 // (arena offsets equal file offsets); residency only says whether the bytes behind them have been copied.
+int device_state_create(flsgpu_table* t, FlsDeviceState* d);
+
+std::mutex g_create_mu; // serialises first-use creation: worker threads of one scan all arrive here at once
+
 int device_state(flsgpu_table* t, FlsDeviceState** out) {
+	std::lock_guard<std::mutex> g(g_create_mu);
 	if (t->dev) {
 		*out = t->dev;
 		return cudaSetDevice(t->dev->device) == cudaSuccess ? FLSGPU_OK : fls_set_error(FLSGPU_ERR_CUDA, "cudaSetDevice failed");
@@ -126,9 +137,25 @@ int device_state(flsgpu_table* t, FlsDeviceState** out) {
 	if (rc) {
 		return rc;
 	}
+	if (t->header.vec_per_rowgroup > 65535u) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "more than 65535 vectors per row group are not supported on the device");
+	}
 	auto d = new FlsDeviceState();
-	t->dev = d; // released by fls_device_release on any later failure path through flsgpu_table_close
 	d->device = g_device;
+	const int rc2 = device_state_create(t, d);
+	if (rc2) { // publish only fully built states
+		cudaFree(d->d_image);
+		cudaFree(d->d_chunks);
+		cudaFree(d->d_run_starts);
+		delete d;
+		return rc2;
+	}
+	t->dev = d;
+	*out = d;
+	return FLSGPU_OK;
+}
+
+int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 	const fls_file_header& h = t->header;
 	const uint64_t n_chunks = (uint64_t)h.n_rowgroups * h.n_columns;
 	d->image_bytes = h.footer_offset;
@@ -184,7 +211,6 @@ int device_state(flsgpu_table* t, FlsDeviceState** out) {
 	}
 	FLS_CUDA(cudaMalloc(&d->d_chunks, n_chunks * sizeof(FlsChunkDev)));
 	FLS_CUDA(cudaMemcpy(d->d_chunks, host_chunks.data(), n_chunks * sizeof(FlsChunkDev), cudaMemcpyHostToDevice));
-	*out = d;
 	return FLSGPU_OK;
 }
 
@@ -628,47 +654,64 @@ int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32
 	// that H2D, decode and D2H of neighbouring slabs overlap on the two streams
 	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (64ull << 20) / rg_bytes_all));
 	const uint64_t slab_bytes = rg_bytes_all * slab_rg;
-	if (d->scan_out_bytes < slab_bytes) {
-		for (int i = 0; i < 2; ++i) {
-			if (d->scan_streams[i]) {
-				FLS_CUDA(cudaStreamSynchronize(d->scan_streams[i]));
-			}
-			FLS_CUDA(cudaFree(d->scan_out[i]));
-			d->scan_out[i] = nullptr;
-			FLS_CUDA(cudaMalloc(&d->scan_out[i], slab_bytes));
+	FlsScanScratch* sc = nullptr;
+	{
+		std::lock_guard<std::mutex> g(d->mu);
+		if (!d->scratch_free.empty()) {
+			sc = d->scratch_free.back();
+			d->scratch_free.pop_back();
+		} else {
+			sc = new FlsScanScratch();
+			d->scratch_all.push_back(sc);
 		}
-		d->scan_out_bytes = slab_bytes;
+	}
+	struct Return { // hand the scratch back on every exit path
+		FlsDeviceState* d;
+		FlsScanScratch* sc;
+		~Return() {
+			std::lock_guard<std::mutex> g(d->mu);
+			d->scratch_free.push_back(sc);
+		}
+	} ret {d, sc};
+	if (sc->out_bytes < slab_bytes) {
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaFree(sc->out[i]));
+			sc->out[i] = nullptr;
+			FLS_CUDA(cudaMalloc(&sc->out[i], slab_bytes));
+		}
+		sc->out_bytes = slab_bytes;
 	}
 	for (int i = 0; i < 2; ++i) {
-		if (!d->scan_streams[i]) {
-			FLS_CUDA(cudaStreamCreateWithFlags(&d->scan_streams[i], cudaStreamNonBlocking));
+		if (!sc->streams[i]) {
+			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
 		}
 	}
 	uint32_t slab = 0;
-	for (uint32_t r = 0; r < n_rg; r += slab_rg, ++slab) {
+	int status = FLSGPU_OK;
+	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
 		const uint32_t n = std::min(slab_rg, n_rg - r);
-		cudaStream_t s = d->scan_streams[slab & 1];
+		cudaStream_t s = sc->streams[slab & 1];
 		{
 			std::lock_guard<std::mutex> g(d->mu);
-			rc = stage_range(t, d, rg_begin + r, n, col_ids, n_cols, s);
+			status = stage_range(t, d, rg_begin + r, n, col_ids, n_cols, s);
 		}
-		if (rc) {
-			return rc;
-		}
-		uint8_t* dev = static_cast<uint8_t*>(d->scan_out[slab & 1]);
-		for (uint32_t i = 0; i < n_cols; ++i) {
-			rc = decode_column_impl(t, d, col_ids[i], rg_begin + r, n, os[i], dev, s);
-			if (rc) {
-				return rc;
+		uint8_t* dev = static_cast<uint8_t*>(sc->out[slab & 1]);
+		for (uint32_t i = 0; i < n_cols && status == FLSGPU_OK; ++i) {
+			status = decode_column_impl(t, d, col_ids[i], rg_begin + r, n, os[i], dev, s);
+			if (status == FLSGPU_OK &&
+			    cudaMemcpyAsync(static_cast<uint8_t*>(out_hosts[i]) + (uint64_t)r * rg_bytes[i], dev, rg_bytes[i] * n,
+			                    cudaMemcpyDeviceToHost, s) != cudaSuccess) {
+				status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
 			}
-			FLS_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(out_hosts[i]) + (uint64_t)r * rg_bytes[i], dev, rg_bytes[i] * n,
-			                         cudaMemcpyDeviceToHost, s));
 			dev += rg_bytes[i] * slab_rg;
 		}
 	}
-	FLS_CUDA(cudaStreamSynchronize(d->scan_streams[0]));
-	FLS_CUDA(cudaStreamSynchronize(d->scan_streams[1]));
-	return FLSGPU_OK;
+	// always drain both streams before the scratch goes back to the pool
+	const cudaError_t e0 = cudaStreamSynchronize(sc->streams[0]), e1 = cudaStreamSynchronize(sc->streams[1]);
+	if (status == FLSGPU_OK && (e0 != cudaSuccess || e1 != cudaSuccess)) {
+		status = cuda_fail(e0 != cudaSuccess ? e0 : e1, "cudaStreamSynchronize");
+	}
+	return status;
 }
 
 int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type, void* out_host,

@@ -1,0 +1,174 @@
+// fls_reader_capi.cpp — see fls_reader_capi.h.
+#include "fls_reader_capi.h"
+
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "fls_reader.hpp"
+
+using namespace flsreader;
+
+struct flsreader_handle {
+	std::unique_ptr<FastLanesReader> reader;
+};
+
+static thread_local std::string g_err;
+const char* flsreader_last_error(void) {
+	return g_err.c_str();
+}
+
+#define FLSR_TRY(...)                                                                                                  \
+	try {                                                                                                              \
+		__VA_ARGS__;                                                                                                     \
+		return 0;                                                                                                      \
+	} catch (const ReaderError& e) {                                                                                   \
+		g_err = e.what();                                                                                              \
+		return e.status;                                                                                               \
+	} catch (const std::exception& e) {                                                                                \
+		g_err = e.what();                                                                                              \
+		return FLSGPU_ERR_INVALID;                                                                                     \
+	}
+
+int flsreader_open(const char* path, int file_row_number, uint64_t explicit_cardinality, uint64_t rowgroups_per_batch,
+                   flsreader_handle** out) {
+	FLSR_TRY({
+		FastLanesFileReaderOptions o;
+		o.file_row_number = file_row_number != 0;
+		o.has_explicit_cardinality = explicit_cardinality != 0;
+		o.explicit_cardinality = explicit_cardinality;
+		if (rowgroups_per_batch) {
+			o.rowgroups_per_batch = rowgroups_per_batch;
+		}
+		auto h = std::make_unique<flsreader_handle>();
+		h->reader = std::make_unique<FastLanesReader>(path, o);
+		*out = h.release();
+	})
+}
+void flsreader_close(flsreader_handle* h) {
+	delete h;
+}
+int flsreader_n_columns(const flsreader_handle* h) {
+	return (int)h->reader->GetColumns().size();
+}
+int flsreader_column(const flsreader_handle* h, int i, char* name64, int* type_id, int* physical_bytes, int* width, int* scale) {
+	const auto& cols = h->reader->GetColumns();
+	if (i < 0 || (size_t)i >= cols.size()) {
+		g_err = "column index out of range";
+		return FLSGPU_ERR_INVALID;
+	}
+	std::snprintf(name64, 64, "%s", cols[i].name.c_str());
+	*type_id = (int)cols[i].type.id;
+	*physical_bytes = cols[i].type.physical_bytes;
+	*width = cols[i].type.width;
+	*scale = cols[i].type.scale;
+	return 0;
+}
+uint64_t flsreader_cardinality(const flsreader_handle* h) {
+	return h->reader->GetCardinality();
+}
+uint64_t flsreader_max_threads(const flsreader_handle* h) {
+	return h->reader->MaxThreads();
+}
+uint64_t flsreader_total_tuples(const flsreader_handle* h) {
+	return h->reader->GetTotalTuples();
+}
+double flsreader_progress(const flsreader_handle* h) {
+	return h->reader->GetProgressInFile();
+}
+int flsreader_partition_stats(const flsreader_handle* h, uint64_t* row_start, uint64_t* count, uint64_t capacity, uint64_t* n) {
+	std::vector<PartitionStatistics> ps;
+	h->reader->GetPartitionStats(ps);
+	*n = ps.size();
+	for (size_t i = 0; i < ps.size() && i < capacity; ++i) {
+		row_start[i] = ps[i].row_start;
+		count[i] = ps[i].count;
+	}
+	return 0;
+}
+int flsreader_statistics(const flsreader_handle* h, const char* name, int* has_stats, int64_t* min_i, int64_t* max_i, double* min_d,
+                         double* max_d) {
+	FLSR_TRY({
+		NumericStats s;
+		*has_stats = h->reader->GetStatistics(name, s) ? 1 : 0;
+		*min_i = s.min_i;
+		*max_i = s.max_i;
+		*min_d = s.min_d;
+		*max_d = s.max_d;
+	})
+}
+
+int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, int n_threads, void* const* out_cols,
+                       uint64_t* rows_out, uint64_t* chunks_out, uint64_t* max_chunk_rows) {
+	FLSR_TRY({
+		FastLanesReader& reader = *h->reader;
+		// the driver appends file_row_number to the projection to know where each chunk belongs
+		reader.column_ids.assign(column_ids, column_ids + n_cols);
+		reader.column_ids.push_back(COLUMN_IDENTIFIER_FILE_ROW_NUMBER);
+		const auto& cols = reader.GetColumns();
+		std::vector<uint32_t> widths(n_cols);
+		for (uint32_t c = 0; c < n_cols; ++c) {
+			if (column_ids[c] >= cols.size()) {
+				throw ReaderError(FLSGPU_ERR_INVALID, "Projected column id out of range");
+			}
+			widths[c] = cols[column_ids[c]].type.physical_bytes;
+		}
+		FastLanesReadGlobalState gstate;
+		std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0};
+		std::mutex err_mu;
+		std::string err;
+		int err_status = 0;
+		const int nt = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)std::max(1, n_threads), reader.MaxThreads()));
+		auto worker = [&]() {
+			try {
+				FastLanesReadLocalState lstate;
+				DataChunk chunk;
+				for (;;) {
+					{
+						std::lock_guard<std::mutex> g(gstate.lock);
+						if (!reader.TryInitializeScan(gstate, lstate)) {
+							return;
+						}
+					}
+					for (;;) {
+						reader.Scan(gstate, lstate, chunk);
+						if (chunk.count == 0) {
+							break;
+						}
+						const int64_t row0 = static_cast<const int64_t*>(chunk.data[n_cols].data)[0];
+						for (uint32_t c = 0; c < n_cols; ++c) {
+							std::memcpy(static_cast<uint8_t*>(out_cols[c]) + (uint64_t)row0 * widths[c], chunk.data[c].data,
+							            chunk.count * widths[c]);
+						}
+						rows += chunk.count;
+						chunks += 1;
+						uint64_t m = maxrows.load();
+						while (chunk.count > m && !maxrows.compare_exchange_weak(m, chunk.count)) {
+						}
+					}
+				}
+			} catch (const ReaderError& e) {
+				std::lock_guard<std::mutex> g(err_mu);
+				err = e.what();
+				err_status = e.status;
+			} catch (const std::exception& e) {
+				std::lock_guard<std::mutex> g(err_mu);
+				err = e.what();
+				err_status = FLSGPU_ERR_INVALID;
+			}
+		};
+		std::vector<std::thread> th;
+		for (int i = 0; i < nt; ++i) {
+			th.emplace_back(worker);
+		}
+		for (auto& t : th) {
+			t.join();
+		}
+		if (err_status) {
+			throw ReaderError(err_status, err);
+		}
+		*rows_out = rows;
+		*chunks_out = chunks;
+		*max_chunk_rows = maxrows;
+	})
+}

@@ -1,0 +1,33 @@
+/* fls_reader_capi.h — C view of the reader mirror (csrc/reader/fls_reader.hpp) for the Python tests and the bench:
+ * an executor stand-in that drives TryInitializeScan/Scan on N worker threads the way DuckDB's MultiFileScan does
+ * (duckdb/src/include/duckdb/common/multi_file/multi_file_function.hpp:397-472,591-616).  Not part of the drop-in
+ * boundary (that is include/flsgpu.h); it exists so that the reader logic is testable without a DuckDB build. */
+#ifndef FLS_READER_CAPI_H
+#define FLS_READER_CAPI_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+typedef struct flsreader_handle flsreader_handle;
+const char* flsreader_last_error(void);
+int flsreader_open(const char* path, int file_row_number, uint64_t explicit_cardinality, uint64_t rowgroups_per_batch,
+                   flsreader_handle** out);
+void flsreader_close(flsreader_handle* h);
+int flsreader_n_columns(const flsreader_handle* h);
+/* type_id: flsreader::LogicalTypeId */
+int flsreader_column(const flsreader_handle* h, int i, char* name64, int* type_id, int* physical_bytes, int* width, int* scale);
+uint64_t flsreader_cardinality(const flsreader_handle* h);
+uint64_t flsreader_max_threads(const flsreader_handle* h);
+uint64_t flsreader_total_tuples(const flsreader_handle* h);
+double flsreader_progress(const flsreader_handle* h);
+int flsreader_partition_stats(const flsreader_handle* h, uint64_t* row_start, uint64_t* count, uint64_t capacity, uint64_t* n);
+int flsreader_statistics(const flsreader_handle* h, const char* name, int* has_stats, int64_t* min_i, int64_t* max_i, double* min_d,
+                         double* max_d);
+/* SELECT column_ids FROM read_fls(path): n_threads workers; chunk rows land in out_cols[c] at their file row number.
+ * column id == n_columns (with file_row_number enabled) selects the virtual column. */
+int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, int n_threads, void* const* out_cols,
+                       uint64_t* rows_out, uint64_t* chunks_out, uint64_t* max_chunk_rows);
+#ifdef __cplusplus
+}
+#endif
+#endif

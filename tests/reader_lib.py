@@ -1,0 +1,101 @@
+"""ctypes view of libflsreader.so: the C++ reader mirror (csrc/reader) + its executor stand-in."""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "duckdb-fastlanes_b200", "libflsreader.so")
+lib = C.CDLL(LIB)
+lib.flsreader_last_error.restype = C.c_char_p
+lib.flsreader_close.restype = None
+lib.flsreader_cardinality.restype = C.c_uint64
+lib.flsreader_max_threads.restype = C.c_uint64
+lib.flsreader_total_tuples.restype = C.c_uint64
+lib.flsreader_progress.restype = C.c_double
+
+TYPE_NAMES = ["INVALID", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UBIGINT", "FLOAT", "DOUBLE", "DATE",
+              "TIMESTAMP", "DECIMAL"]
+NP_OF = {"BOOLEAN": np.uint8, "TINYINT": np.int8, "SMALLINT": np.int16, "INTEGER": np.int32, "BIGINT": np.int64,
+         "UBIGINT": np.uint64, "FLOAT": np.float32, "DOUBLE": np.float64, "DATE": np.int32, "TIMESTAMP": np.int64}
+
+
+class ReaderError(RuntimeError):
+    def __init__(self, status):
+        super().__init__(f"status {status}: {lib.flsreader_last_error().decode(errors='replace')}")
+        self.status = status
+
+
+class Reader:
+    def __init__(self, path, file_row_number=False, explicit_cardinality=0, rowgroups_per_batch=0):
+        self._h = C.c_void_p()
+        rc = lib.flsreader_open(os.fsencode(path), int(file_row_number), C.c_uint64(explicit_cardinality),
+                                C.c_uint64(rowgroups_per_batch), C.byref(self._h))
+        if rc:
+            raise ReaderError(rc)
+        self.columns = []
+        for i in range(lib.flsreader_n_columns(self._h)):
+            name = C.create_string_buffer(64)
+            tid, pb, w, s = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+            lib.flsreader_column(self._h, i, name, C.byref(tid), C.byref(pb), C.byref(w), C.byref(s))
+            self.columns.append(dict(name=name.value.decode(), type=TYPE_NAMES[tid.value], bytes=pb.value, width=w.value,
+                                     scale=s.value))
+
+    def np_dtype(self, i):
+        c = self.columns[i]
+        if c["type"] == "DECIMAL":
+            return {2: np.int16, 4: np.int32, 8: np.int64}[c["bytes"]]
+        return NP_OF[c["type"]]
+
+    @property
+    def cardinality(self):
+        return lib.flsreader_cardinality(self._h)
+
+    @property
+    def max_threads(self):
+        return lib.flsreader_max_threads(self._h)
+
+    @property
+    def total_tuples(self):
+        return lib.flsreader_total_tuples(self._h)
+
+    @property
+    def progress(self):
+        return lib.flsreader_progress(self._h)
+
+    def partition_stats(self):
+        n = C.c_uint64()
+        lib.flsreader_partition_stats(self._h, None, None, C.c_uint64(0), C.byref(n))
+        a = (C.c_uint64 * n.value)()
+        b = (C.c_uint64 * n.value)()
+        lib.flsreader_partition_stats(self._h, a, b, n, C.byref(n))
+        return list(zip(a, b))
+
+    def statistics(self, name):
+        has, mi, ma, md, xd = C.c_int(), C.c_int64(), C.c_int64(), C.c_double(), C.c_double()
+        rc = lib.flsreader_statistics(self._h, name.encode(), C.byref(has), C.byref(mi), C.byref(ma), C.byref(md), C.byref(xd))
+        if rc:
+            raise ReaderError(rc)
+        return dict(has_stats=bool(has.value), min_i=mi.value, max_i=ma.value, min_d=md.value, max_d=xd.value)
+
+    def scan_all(self, column_ids=None, n_threads=1):
+        """SELECT cols FROM read_fls(path) -> (list of numpy columns in file row order, stats dict)."""
+        ids = list(range(len(self.columns))) if column_ids is None else list(column_ids)
+        n = self.total_tuples
+        # ids the reader does not know are passed through so that the C++ side reports them
+        outs = [np.zeros(n, dtype=self.np_dtype(i) if i < len(self.columns) else np.uint8) for i in ids]
+        ia = (C.c_uint64 * len(ids))(*ids)
+        pa = (C.c_void_p * len(ids))(*[o.ctypes.data for o in outs])
+        rows, chunks, mx = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        rc = lib.flsreader_scan_all(self._h, ia, len(ids), n_threads, pa, C.byref(rows), C.byref(chunks), C.byref(mx))
+        if rc:
+            raise ReaderError(rc)
+        return outs, dict(rows=rows.value, chunks=chunks.value, max_chunk_rows=mx.value)
+
+    def close(self):
+        if self._h:
+            lib.flsreader_close(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        self.close()
