@@ -44,6 +44,9 @@ __constant__ float c_frac_f[11] = {1.0F,      0.1F,       0.01F,       0.001F,  
                                    0.000001F, 0.0000001F, 0.00000001F, 0.000000001F, 0.0000000001F};
 
 constexpr int kWarpsPerCta = 8;
+#ifndef FLS_MIN_CTAS
+#define FLS_MIN_CTAS 1
+#endif
 
 // Everything a warp needs to decode one vector; filled per lane, broadcast with shuffles.
 struct VecDesc {
@@ -129,19 +132,42 @@ __device__ __forceinline__ void load_elem(const uint8_t* base, uint32_t idx, uin
 	}
 }
 
-// out[pos[k]] = exception[k]  (alp.hpp:401-404; slpatch / frequency patches)
+// out[pos[k]] = exception[k]  (alp.hpp:401-404; slpatch / frequency patches).
+// The first 32 exceptions of a vector (one per lane) are loaded BEFORE the vector is unpacked so that the global-load
+// latency hides behind the unpack + stores; they are written after the vector's own stores (ordered by __syncwarp).
+struct ExcPrefetch {
+	uint32_t lo, hi, pos;
+};
+
+template <int T>
+__device__ __forceinline__ ExcPrefetch prefetch_exceptions(const VecDesc& d, int lane) {
+	ExcPrefetch e;
+	e.lo = e.hi = e.pos = 0;
+	const uint32_t n = d.misc & 0xffffu;
+	if ((uint32_t)lane < n) {
+		e.pos = __ldg(reinterpret_cast<const uint16_t*>(d.ch->aux1) + d.aux_off + lane);
+		load_elem<T>(d.ch->aux0, d.aux_off + lane, e.lo, e.hi);
+	}
+	return e;
+}
+
 template <int T, int OB>
-__device__ __forceinline__ void patch_exceptions(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv) {
+__device__ __forceinline__ void patch_exceptions(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv, const ExcPrefetch& e) {
 	const uint32_t n = d.misc & 0xffffu;
 	if (n == 0) {
 		return;
 	}
 	__syncwarp();
-	const uint16_t* pos = reinterpret_cast<const uint16_t*>(d.ch->aux1) + d.aux_off;
-	for (uint32_t k = lane; k < n; k += 32) {
-		uint32_t lo, hi;
-		load_elem<T>(d.ch->aux0, d.aux_off + k, lo, hi);
-		store_one<T, OB>(out_vec, __ldg(pos + k), lo, hi, conv);
+	if ((uint32_t)lane < n) {
+		store_one<T, OB>(out_vec, e.pos, e.lo, e.hi, conv);
+	}
+	if (n > 32) {
+		const uint16_t* pos = reinterpret_cast<const uint16_t*>(d.ch->aux1) + d.aux_off;
+		for (uint32_t k = lane + 32; k < n; k += 32) {
+			uint32_t lo, hi;
+			load_elem<T>(d.ch->aux0, d.aux_off + k, lo, hi);
+			store_one<T, OB>(out_vec, __ldg(pos + k), lo, hi, conv);
+		}
 	}
 }
 

@@ -6,20 +6,29 @@
 namespace FLS_NS {
 
 // ---- T in {8,16,32} ------------------------------------------------------------------------------------------------------
-template <int T, int OB>
+// FAM: which encodings this instantiation carries (the launcher splits a column's chunks into a "light" launch, an
+// ALP launch and an ALP-RD launch so that the register budget of the heavy float paths does not cap the occupancy of
+// the integer paths).
+constexpr uint32_t kFamLight = FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD));
+constexpr uint32_t kFamAlp = 1u << FLS_ENC_ALP;
+constexpr uint32_t kFamAlpRd = 1u << FLS_ENC_ALP_RD;
+
+template <int T, int OB, uint32_t FAM>
 __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane,
                                               uint32_t conv) {
 	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
 	constexpr uint32_t TMASK = T == 32 ? 0xffffffffu : ((1u << (T & 31)) - 1u);
-	switch (enc) {
-	case FLS_ENC_UNCOMPRESSED: copy_out_linear<T, OB, false>(slot, out_vec, lane, conv); return;
-	case FLS_ENC_CONSTANT: fill_constant<T, OB>(out_vec, lane, (uint32_t)d.ch->const_val, 0, conv); return;
-	case FLS_ENC_CROSS_RLE: decode_cross_rle<T, OB>(out_vec, d, lane, conv); return;
-	default: break;
+	if constexpr ((FAM & kFamLight) != 0) {
+		switch (enc) {
+		case FLS_ENC_UNCOMPRESSED: copy_out_linear<T, OB, false>(slot, out_vec, lane, conv); return;
+		case FLS_ENC_CONSTANT: fill_constant<T, OB>(out_vec, lane, (uint32_t)d.ch->const_val, 0, conv); return;
+		case FLS_ENC_CROSS_RLE: decode_cross_rle<T, OB>(out_vec, d, lane, conv); return;
+		default: break;
+		}
 	}
 	uint32_t v[32];
 	const uint32_t base = (uint32_t)d.base;
-	if (enc == FLS_ENC_DELTA) {
+	if ((FAM & kFamLight) != 0 && enc == FLS_ENC_DELTA) {
 		// [128 B lane bases][packed deltas]: per-lane running sum (no cross-lane dependency), then transposition
 		const uint32_t* s32 = reinterpret_cast<const uint32_t*>(slot);
 		unpack_small_dispatch<T>((int)W, s32 + 32, lane, v);
@@ -78,16 +87,17 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		return;
 	}
 	// FFOR family / ALP / ALP_RD: packed blob starts at the slot
+	const ExcPrefetch exc = prefetch_exceptions<T>(d, lane);
 	unpack_small_dispatch<T>((int)W, reinterpret_cast<const uint32_t*>(slot), lane, v);
 	if constexpr (T == 32) {
-		if (enc == FLS_ENC_ALP) { // alp.hpp:129-134: (float)digit * (float)FACT[f] * FRAC[e], two roundings, no FMA
+		if ((FAM & kFamAlp) != 0 && (FAM == kFamAlp || enc == FLS_ENC_ALP)) { // alp.hpp:129-134: (float)digit * (float)FACT[f] * FRAC[e], two roundings, no FMA
 			const float fa = c_fact_f[(d.misc2 >> 16) & 0xffu], fr = c_frac_f[(d.misc2 >> 8) & 0xffu];
 #pragma unroll
 			for (int j = 0; j < 32; ++j) {
 				const float x = __int2float_rn((int32_t)(v[j] + base));
 				v[j] = __float_as_uint(__fmul_rn(__fmul_rn(x, fa), fr));
 			}
-		} else if (enc == FLS_ENC_ALP_RD) { // alprd.hpp:222-226
+		} else if ((FAM & kFamAlpRd) != 0 && (FAM == kFamAlpRd || enc == FLS_ENC_ALP_RD)) { // alprd.hpp:222-226
 			uint32_t left[32];
 			const uint32_t W2 = d.misc2 & 0xffu;
 			unpack_small_dispatch<T>((int)W2, reinterpret_cast<const uint32_t*>(slot) + 32 * W, lane, left);
@@ -113,23 +123,26 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		}
 	}
 	store_direct<T, OB>(out_vec, lane, v, conv);
-	patch_exceptions<T, OB>(out_vec, d, lane, conv);
+	patch_exceptions<T, OB>(out_vec, d, lane, conv, exc);
 }
 
 // ---- T = 64 --------------------------------------------------------------------------------------------------------------
+template <uint32_t FAM>
 __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane) {
 	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
-	switch (enc) {
-	case FLS_ENC_UNCOMPRESSED: copy_out_linear<64, 8, false>(slot, out_vec, lane, 0); return;
-	case FLS_ENC_CONSTANT:
-		fill_constant<64, 8>(out_vec, lane, (uint32_t)d.ch->const_val, (uint32_t)(d.ch->const_val >> 32), 0);
-		return;
-	case FLS_ENC_CROSS_RLE: decode_cross_rle<64, 8>(out_vec, d, lane, 0); return;
-	default: break;
+	if constexpr ((FAM & kFamLight) != 0) {
+		switch (enc) {
+		case FLS_ENC_UNCOMPRESSED: copy_out_linear<64, 8, false>(slot, out_vec, lane, 0); return;
+		case FLS_ENC_CONSTANT:
+			fill_constant<64, 8>(out_vec, lane, (uint32_t)d.ch->const_val, (uint32_t)(d.ch->const_val >> 32), 0);
+			return;
+		case FLS_ENC_CROSS_RLE: decode_cross_rle<64, 8>(out_vec, d, lane, 0); return;
+		default: break;
+		}
 	}
 	uint32_t lo[32], hi[32];
 	const uint32_t blo = (uint32_t)d.base, bhi = (uint32_t)(d.base >> 32);
-	if (enc == FLS_ENC_DELTA) {
+	if ((FAM & kFamLight) != 0 && enc == FLS_ENC_DELTA) {
 		unpack_64_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot) + 32, lane, lo, hi);
 		// thread (l = lane&15, h = lane>>4) owns rows 32h..32h+31 of lane l: local sums, one shuffle to stitch halves
 		uint64_t sum = 0;
@@ -153,8 +166,9 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 		copy_out_linear<64, 8, true>(stage, out_vec, lane, 0);
 		return;
 	}
+	const ExcPrefetch exc = prefetch_exceptions<64>(d, lane);
 	unpack_64_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot), lane, lo, hi);
-	if (enc == FLS_ENC_ALP) { // (double)digit * (double)FACT[f] * FRAC[e]
+	if ((FAM & kFamAlp) != 0 && (FAM == kFamAlp || enc == FLS_ENC_ALP)) { // (double)digit * (double)FACT[f] * FRAC[e]
 		const double fa = c_fact_d[(d.misc2 >> 16) & 0xffu], fr = c_frac_d[(d.misc2 >> 8) & 0xffu];
 #pragma unroll
 		for (int j = 0; j < 32; ++j) {
@@ -164,7 +178,7 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 			lo[j] = (uint32_t)b;
 			hi[j] = (uint32_t)(b >> 32);
 		}
-	} else if (enc == FLS_ENC_ALP_RD) {
+	} else if ((FAM & kFamAlpRd) != 0 && (FAM == kFamAlpRd || enc == FLS_ENC_ALP_RD)) {
 		uint32_t llo[32], lhi[32];
 		const uint32_t W2 = d.misc2 & 0xffu;
 		unpack_64_dispatch((int)W2, reinterpret_cast<const uint32_t*>(slot) + 32 * W, lane, llo, lhi);
@@ -191,16 +205,23 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 	(void)blo;
 	(void)bhi;
 	store_direct64(out_vec, lane, lo, hi);
-	patch_exceptions<64, 8>(out_vec, d, lane, 0);
+	patch_exceptions<64, 8>(out_vec, d, lane, 0, exc);
 }
 
 // ---- the persistent kernel -----------------------------------------------------------------------------------------------
 // MODE 0: main family (T = physical lane width = VT); MODE 1: DICT (T = code lane width, VT = key width);
 // MODE 2: RLE (T = 16: run-index lanes, VT = value width).
+// Register budget: two resident CTAs per SM (<= 128 registers) everywhere except the 64-bit integer kernel, which is
+// faster with one CTA of 8 warps and no spills (measured: profiles/r01_notes.md).
+template <int MODE, int T, bool AGG, uint32_t FAM>
+constexpr int min_ctas_per_sm() {
+	return (MODE == 0 && T == 64 && !AGG && FAM == kFamLight) ? 1 : FLS_MIN_CTAS;
+}
+
 // AGG: the vector is decoded into the warp's shared-memory tile (FLS_SINK_SHARED translation unit) and folded into
 // per-thread partial aggregates instead of being written to HBM.
-template <int MODE, int T, int VT, int OB, bool AGG = false>
-__global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const FlsLaunch L) {
+template <int MODE, int T, int VT, int OB, bool AGG = false, uint32_t FAM = FLS_FAMILY_MAIN>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AGG, FAM>()) fls_decode_kernel(const FlsLaunch L) {
 	extern __shared__ __align__(128) uint8_t smem[];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const uint32_t n_slots = L.n_slots;
@@ -229,8 +250,15 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const Fls
 	uint32_t n_done = 0; // vectors processed by this warp (slot = n_done % n_slots)
 	uint8_t* const out = static_cast<uint8_t*>(L.out);
 
-	for (uint64_t b0 = gw; b0 < L.total_vecs; b0 += (uint64_t)32 * n_warps) {
-		const uint64_t my_v64 = b0 + (uint64_t)lane * n_warps;
+	// Vector -> warp assignment: a warp takes runs of C = 2^run_shift consecutive vectors (same row group, same
+	// dictionary, adjacent output), runs are dealt round-robin over all warps of the grid; 32 vectors per batch.
+	const uint32_t cs = L.run_shift, cmask = (1u << cs) - 1u, runs_per_batch = 32u >> cs;
+	for (uint64_t it = 0;; ++it) {
+		const uint64_t run0 = it * runs_per_batch; // first run index (per warp) of this batch
+		if (((run0 * n_warps + gw) << cs) >= L.total_vecs) {
+			break;
+		}
+		const uint64_t my_v64 = (((run0 + ((uint32_t)lane >> cs)) * n_warps + gw) << cs) + ((uint32_t)lane & cmask);
 		const VecDesc mine = fetch_desc<T>(L, my_v64 < L.total_vecs ? (uint32_t)my_v64 : 0xffffffffu);
 		uint32_t todo = __ballot_sync(0xffffffffu, mine.ch != nullptr);
 		uint32_t to_issue = todo;
@@ -256,16 +284,17 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) fls_decode_kernel(const Fls
 				mbar_wait(bars + slot, (phases >> slot) & 1u);
 				phases ^= 1u << slot;
 			}
-			uint8_t* out_vec = AGG ? tile : out + (size_t)(b0 + (uint64_t)k * n_warps) * 1024u * OB;
+			const uint64_t vk = (((run0 + ((uint32_t)k >> cs)) * n_warps + gw) << cs) + ((uint32_t)k & cmask);
+			uint8_t* out_vec = AGG ? tile : out + (size_t)vk * 1024u * OB;
 			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
 			if constexpr (MODE == 1) {
 				process_dict<T, VT, OB>(d, sp, out_vec, lane, L.conv);
 			} else if constexpr (MODE == 2) {
 				process_rle<VT, OB>(d, sp, stage, out_vec, lane, L.conv);
 			} else if constexpr (T == 64) {
-				process_64(d, sp, stage, out_vec, lane);
+				process_64<FAM>(d, sp, stage, out_vec, lane);
 			} else {
-				process_small<T, OB>(d, sp, stage, out_vec, lane, L.conv);
+				process_small<T, OB, FAM>(d, sp, stage, out_vec, lane, L.conv);
 			}
 			__syncwarp(); // all lanes are done reading the slot (and the staging area)
 			if constexpr (AGG) {

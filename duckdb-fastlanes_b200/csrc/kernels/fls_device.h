@@ -40,6 +40,7 @@ struct FlsLaunch {
 	uint32_t n_slots;          // pipeline depth per warp
 	uint32_t conv;             // 0: zero-extend / same width, 1: sign-extend, 2: f32 -> f64
 	uint32_t family_mask;      // bit e set: this kernel handles encoding e
+	uint32_t run_shift;        // log2 of the run of consecutive vectors a warp takes (0..5)
 	uint32_t idx_bits;         // DICT launches: only chunks whose codes sit in idx_bits-wide lanes (0: any)
 	void* out;
 	// fused aggregate launches (flsgpu_aggregate_column): out is unused, partials are folded into *agg

@@ -5,13 +5,14 @@
 #include "fls_device.h"
 
 // MODE 0 (T-lane encodings): T = column physical bits, OB = output bytes per value (>= T/8).
-const void* fls_kernel_main(int T, int OB);
+// fam: 0 = light (integer encodings), 1 = ALP, 2 = ALP_RD
+const void* fls_kernel_main(int T, int OB, int fam);
 // MODE 1 (DICT): IT = code lane bits (8/16/32), VT = key bits, OB = output bytes (>= VT/8).
 const void* fls_kernel_dict(int IT, int VT, int OB);
 // MODE 2 (RLE, u16 run index): VT = run value bits.
 const void* fls_kernel_rle(int VT, int OB);
 // Fused decode + aggregate (SUM/COUNT/MIN/MAX): same families, output replaced by a reduction.
-const void* fls_kernel_agg(int mode, int T, int VT);
+const void* fls_kernel_agg(int mode, int T, int VT, int fam);
 
 #ifdef __CUDACC__
 #include <cuda_runtime.h>

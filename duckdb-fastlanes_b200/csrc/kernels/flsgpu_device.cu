@@ -8,7 +8,9 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -31,6 +33,13 @@ std::map<const void*, int> g_func_ready;                  // fn -> 1 once the sm
 std::map<std::pair<const void*, uint32_t>, int> g_occ;    // (fn, smem) -> resident CTAs per SM
 
 constexpr uint32_t kMaxSmemPerCta = 227u * 1024u;
+
+// tuning knobs (environment overrides are for experiments; defaults are the measured best)
+uint32_t env_u32(const char* name, uint32_t def) {
+	const char* v = std::getenv(name);
+	return v ? (uint32_t)std::strtoul(v, nullptr, 10) : def;
+}
+const uint32_t g_run_shift = std::min(5u, env_u32("FLSGPU_RUN_SHIFT", 0));
 
 int cuda_fail(cudaError_t e, const char* where) {
 	char msg[256];
@@ -66,9 +75,10 @@ int ensure_device() {
 
 // ---- per-table device state ---------------------------------------------------------------------------------------
 struct FlsColumnPlan { // what a decode launch over (col, rg range) needs to know about the chunks it covers
-	bool has_main = false, has_rle = false, has_dict[3] = {false, false, false};
+	bool has_main[3] = {false, false, false}; // 0: light (integer encodings), 1: ALP, 2: ALP_RD
+	bool has_rle = false, has_dict[3] = {false, false, false};
 	bool main_needs_stage = false;
-	uint32_t main_slot = 0, rle_slot = 0, dict_slot[3] = {0, 0, 0};
+	uint32_t main_slot[3] = {0, 0, 0}, rle_slot = 0, dict_slot[3] = {0, 0, 0};
 };
 
 struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of neighbouring slabs overlap
@@ -310,8 +320,9 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 			p.has_rle = true;
 			p.rle_slot = std::max(p.rle_slot, bytes);
 		} else {
-			p.has_main = true;
-			p.main_slot = std::max(p.main_slot, bytes);
+			const int f = c.encoding == FLS_ENC_ALP ? 1 : c.encoding == FLS_ENC_ALP_RD ? 2 : 0;
+			p.has_main[f] = true;
+			p.main_slot[f] = std::max(p.main_slot[f], bytes);
 			p.main_needs_stage |= c.encoding == FLS_ENC_DELTA;
 		}
 	}
@@ -429,29 +440,34 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	L.total_vecs = n_rg * h.vec_per_rowgroup;
 	L.conv = os.conv;
 	L.out = out_dev;
+	L.run_shift = g_run_shift;
 	L.agg = agg;
 	L.agg_signed = t->columns[col].is_signed;
 	L.agg_float = t->columns[col].is_float;
 	const uint32_t tile = agg ? 128u * T : 0u; // aggregate launches decode into a per-warp shared-memory tile
 	int rc = FLSGPU_OK;
-	if (p.has_main) {
-		L.family_mask = FLS_FAMILY_MAIN;
-		L.idx_bits = 0;
-		rc = launch_family(agg ? fls_kernel_agg(0, T, T) : fls_kernel_main(T, os.ob), L, p.main_slot,
-		                   p.main_needs_stage ? 128u * T : 0u, stream, tile);
+	static const uint32_t kFamMask[3] = {FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD)), 1u << FLS_ENC_ALP,
+	                                     1u << FLS_ENC_ALP_RD};
+	for (int f = 0; f < 3 && rc == FLSGPU_OK; ++f) {
+		if (p.has_main[f]) {
+			L.family_mask = kFamMask[f];
+			L.idx_bits = 0;
+			rc = launch_family(agg ? fls_kernel_agg(0, T, T, f) : fls_kernel_main(T, os.ob, f), L, p.main_slot[f],
+			                   (f == 0 && p.main_needs_stage) ? 128u * T : 0u, stream, tile);
+		}
 	}
 	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {
 		if (p.has_dict[k]) {
 			const int it = 8 << k;
 			L.family_mask = FLS_FAMILY_DICT;
 			L.idx_bits = (uint32_t)it;
-			rc = launch_family(agg ? fls_kernel_agg(1, it, T) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile);
+			rc = launch_family(agg ? fls_kernel_agg(1, it, T, 0) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile);
 		}
 	}
 	if (p.has_rle && rc == FLSGPU_OK) {
 		L.family_mask = FLS_FAMILY_RLE;
 		L.idx_bits = 0;
-		rc = launch_family(agg ? fls_kernel_agg(2, 16, T) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
+		rc = launch_family(agg ? fls_kernel_agg(2, 16, T, 0) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
 	}
 	return rc;
 }

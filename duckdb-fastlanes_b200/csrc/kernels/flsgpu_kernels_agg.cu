@@ -8,10 +8,19 @@
 
 using namespace flsk_agg;
 
-const void* fls_kernel_agg(int mode, int T, int VT) {
+const void* fls_kernel_agg(int mode, int T, int VT, int fam) {
+	if (mode == 0 && fam == 0) {
+#define FLS_KL(Tv) if (T == Tv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, Tv / 8, true, kFamLight>);
+		FLS_KL(8) FLS_KL(16) FLS_KL(32) FLS_KL(64)
+#undef FLS_KL
+	}
+	if (mode == 0 && fam != 0) {
+#define FLS_KL(Tv) if (T == Tv) return fam == 1 ? reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, Tv / 8, true, kFamAlp>) : reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, Tv / 8, true, kFamAlpRd>);
+		FLS_KL(32) FLS_KL(64)
+#undef FLS_KL
+	}
 #define FLS_K(M, Tv, VTv) \
 	if (mode == M && T == Tv && VT == VTv) return reinterpret_cast<const void*>(&fls_decode_kernel<M, Tv, VTv, VTv / 8, true>);
-	FLS_K(0, 8, 8) FLS_K(0, 16, 16) FLS_K(0, 32, 32) FLS_K(0, 64, 64)
 	FLS_K(1, 8, 8) FLS_K(1, 8, 16) FLS_K(1, 8, 32) FLS_K(1, 8, 64)
 	FLS_K(1, 16, 8) FLS_K(1, 16, 16) FLS_K(1, 16, 32) FLS_K(1, 16, 64)
 	FLS_K(1, 32, 8) FLS_K(1, 32, 16) FLS_K(1, 32, 32) FLS_K(1, 32, 64)

@@ -1,18 +1,24 @@
-// flsgpu_kernels_main.cu — instantiations of the main decode kernel family (UNCOMPRESSED, CONSTANT, FFOR, DELTA, ALP,
-// ALP_RD, CROSS_RLE, FREQUENCY, SLPATCH) for every (physical width, output width) pair the materializer allows
-// (reference fls_type_resolver.hpp:42-83,120-131: same width copy or widening static_cast).
+// flsgpu_kernels_main.cu — instantiations of the main decode kernel family (UNCOMPRESSED, CONSTANT, FFOR, DELTA,
+// CROSS_RLE, FREQUENCY, SLPATCH = "light"; ALP; ALP_RD) for every (physical width, output width) pair the materializer
+// allows (reference fls_type_resolver.hpp:42-83,120-131: same width copy or widening static_cast).
 #include "fls_decode_main.cuh"
 #include "fls_launch.hpp"
 
 using namespace flsk;
 
-const void* fls_kernel_main(int T, int OB) {
+// fam: 0 = light, 1 = ALP, 2 = ALP_RD
+const void* fls_kernel_main(int T, int OB, int fam) {
 #define FLS_K(Tv, OBv) \
-	if (T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv>);
+	if (fam == 0 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamLight>);
 	FLS_K(8, 1) FLS_K(8, 2) FLS_K(8, 4) FLS_K(8, 8)
 	FLS_K(16, 2) FLS_K(16, 4) FLS_K(16, 8)
 	FLS_K(32, 4) FLS_K(32, 8)
 	FLS_K(64, 8)
+#undef FLS_K
+#define FLS_K(Tv, OBv) \
+	if (fam == 1 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamAlp>); \
+	if (fam == 2 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamAlpRd>);
+	FLS_K(32, 4) FLS_K(32, 8) FLS_K(64, 8)
 #undef FLS_K
 	return nullptr;
 }
