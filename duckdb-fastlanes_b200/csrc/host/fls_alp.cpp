@@ -206,7 +206,7 @@ void encode_alp(const IntChunk<U>& c, EncodedChunk& out) {
 		m.n_valid = c.valid_in(v);
 		m.e = (uint8_t)cb.e;
 		m.f = (uint8_t)cb.f;
-		m.aux_off = n_exc_total;
+		VecExceptions<U> exc;
 		int64_t mn = 0, mx = 0, filler = 0;
 		int n_ok = 0;
 		for (int i = 0; i < kVec; ++i) {
@@ -225,14 +225,7 @@ void encode_alp(const IntChunk<U>& c, EncodedChunk& out) {
 		}
 		for (int i = 0; i < kVec; ++i) {
 			if (is_exc[i]) {
-				const size_t o0 = b.aux0.size();
-				b.aux0.resize(o0 + sizeof(U));
-				std::memcpy(b.aux0.data() + o0, &in[i], sizeof(U));
-				const uint16_t pos = (uint16_t)i;
-				const size_t o1 = b.aux1.size();
-				b.aux1.resize(o1 + 2);
-				std::memcpy(b.aux1.data() + o1, &pos, 2);
-				++m.aux_cnt;
+				exc.add(in[i], i);
 				digits[i] = filler;
 			}
 		}
@@ -250,6 +243,8 @@ void encode_alp(const IntChunk<U>& c, EncodedChunk& out) {
 		if (W) {
 			pack_vector<U>(reduced, W, reinterpret_cast<U*>(b.data.data() + old));
 		}
+		m.aux_cnt = (uint16_t)exc.vals.size();
+		exc.append_to(b);
 		n_exc_total += m.aux_cnt;
 		maxw = std::max(maxw, W);
 		b.meta.push_back(m);
@@ -314,7 +309,7 @@ void encode_alp_rd(const IntChunk<U>& c, EncodedChunk& out) {
 		const U* in = c.vals + (size_t)v * kVec;
 		fls_vec_meta m {};
 		m.n_valid = c.valid_in(v);
-		m.aux_off = n_exc_total;
+		VecExceptions<U> exc;
 		for (int i = 0; i < kVec; ++i) {
 			right[i] = in[i] & rmask;
 			const uint32_t lp = (uint32_t)(in[i] >> best_right);
@@ -326,14 +321,7 @@ void encode_alp_rd(const IntChunk<U>& c, EncodedChunk& out) {
 				}
 			}
 			if (code < 0) {
-				const size_t o0 = b.aux0.size();
-				b.aux0.resize(o0 + sizeof(U));
-				std::memcpy(b.aux0.data() + o0, &in[i], sizeof(U));
-				const uint16_t pos = (uint16_t)i;
-				const size_t o1 = b.aux1.size();
-				b.aux1.resize(o1 + 2);
-				std::memcpy(b.aux1.data() + o1, &pos, 2);
-				++m.aux_cnt;
+				exc.add(in[i], i);
 				code = 0;
 			}
 			left[i] = (U)code;
@@ -345,6 +333,8 @@ void encode_alp_rd(const IntChunk<U>& c, EncodedChunk& out) {
 		b.data.resize(old + (size_t)(best_right + lw) * 128);
 		pack_vector<U>(right, best_right, reinterpret_cast<U*>(b.data.data() + old));
 		pack_vector<U>(left, lw, reinterpret_cast<U*>(b.data.data() + old + (size_t)best_right * 128));
+		m.aux_cnt = (uint16_t)exc.vals.size();
+		exc.append_to(b);
 		n_exc_total += m.aux_cnt;
 		b.meta.push_back(m);
 	}

@@ -52,6 +52,16 @@ void ChunkBuilder::finish(EncodedChunk& out, fls_chunk_desc d) const {
 		d.seg_size[s] = segs[s]->size();
 		off += (segs[s]->size() + FLS_ALIGN - 1) / FLS_ALIGN * FLS_ALIGN;
 	}
+	// largest per-vector blob (blobs are appended in vector order, so a blob ends where the next one starts)
+	uint32_t max_blob = 0;
+	for (size_t v = 0; v < meta.size(); ++v) {
+		const size_t begin = (size_t)meta[v].data_off16 * 16;
+		const size_t end = v + 1 < meta.size() ? (size_t)meta[v + 1].data_off16 * 16 : data.size();
+		if (end > begin) {
+			max_blob = std::max<uint32_t>(max_blob, (uint32_t)(end - begin));
+		}
+	}
+	d.max_blob_bytes = max_blob;
 	// 128 bytes of slack so that 16-byte vector loads of the last aux elements never leave the chunk
 	off += FLS_ALIGN;
 	d.size = off;
@@ -103,16 +113,6 @@ static void append_packed(ChunkBuilder& b, const U* reduced, unsigned W) {
 }
 
 template <class U>
-static void append_exception(ChunkBuilder& b, U value, uint16_t pos) {
-	const size_t o0 = b.aux0.size();
-	b.aux0.resize(o0 + sizeof(U));
-	std::memcpy(b.aux0.data() + o0, &value, sizeof(U));
-	const size_t o1 = b.aux1.size();
-	b.aux1.resize(o1 + 2);
-	std::memcpy(b.aux1.data() + o1, &pos, 2);
-}
-
-template <class U>
 void encode_ffor_family(const IntChunk<U>& c, int enc, EncodedChunk& out) {
 	constexpr int T = sizeof(U) * 8;
 	const U flip = ord_flip<U>(c.is_signed);
@@ -126,7 +126,7 @@ void encode_ffor_family(const IntChunk<U>& c, int enc, EncodedChunk& out) {
 		fls_vec_meta m {};
 		m.n_valid = c.valid_in(v);
 		m.data_off16 = (uint32_t)(b.data.size() / 16);
-		m.aux_off = n_exc_total;
+		VecExceptions<U> exc;
 		U base;
 		unsigned W;
 		if (enc == FLS_ENC_FREQUENCY) {
@@ -134,8 +134,7 @@ void encode_ffor_family(const IntChunk<U>& c, int enc, EncodedChunk& out) {
 			W = 0;
 			for (int i = 0; i < kVec; ++i) {
 				if (in[i] != base) {
-					append_exception<U>(b, in[i], (uint16_t)i);
-					++m.aux_cnt;
+					exc.add(in[i], i);
 				}
 			}
 		} else {
@@ -165,8 +164,7 @@ void encode_ffor_family(const IntChunk<U>& c, int enc, EncodedChunk& out) {
 			for (int i = 0; i < kVec; ++i) {
 				const U r = (U)(in[i] - base);
 				if (r & (U)~mask) {
-					append_exception<U>(b, in[i], (uint16_t)i);
-					++m.aux_cnt;
+					exc.add(in[i], i);
 					reduced[i] = 0;
 				} else {
 					reduced[i] = r;
@@ -175,7 +173,9 @@ void encode_ffor_family(const IntChunk<U>& c, int enc, EncodedChunk& out) {
 		}
 		m.base = (uint64_t)base;
 		m.width = (uint8_t)W;
+		m.aux_cnt = (uint16_t)exc.vals.size();
 		append_packed<U>(b, reduced, W);
+		exc.append_to(b);
 		n_exc_total += m.aux_cnt;
 		maxw = std::max(maxw, W);
 		b.meta.push_back(m);

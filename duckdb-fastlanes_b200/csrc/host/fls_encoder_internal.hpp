@@ -1,6 +1,7 @@
 // fls_encoder_internal.hpp — shared pieces of the encoder translation units.
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <type_traits>
 #include <vector>
 #include "fls_encoder.hpp"
@@ -12,6 +13,27 @@ struct ChunkBuilder {
 	std::vector<fls_vec_meta> meta;
 	std::vector<uint8_t> data, aux0, aux1;
 	void finish(EncodedChunk& out, fls_chunk_desc d) const;
+};
+
+// Exceptions of ONE vector; appended behind the vector's packed data (see fls_format.h "exception tail").
+template <class U>
+struct VecExceptions {
+	std::vector<U> vals;
+	std::vector<uint16_t> pos;
+	void add(U v, int p) {
+		vals.push_back(v);
+		pos.push_back((uint16_t)p);
+	}
+	void append_to(ChunkBuilder& b) const {
+		if (vals.empty()) {
+			return;
+		}
+		const size_t n = vals.size(), o = b.data.size();
+		const size_t vb = FLS_PAD16(n * sizeof(U)), pb = FLS_PAD16(n * 2);
+		b.data.resize(o + vb + pb, 0);
+		std::memcpy(b.data.data() + o, vals.data(), n * sizeof(U));
+		std::memcpy(b.data.data() + o + vb, pos.data(), n * 2);
+	}
 };
 
 // A column chunk viewed as unsigned T-bit words, padded to whole vectors with its last value.

@@ -15,7 +15,12 @@ int fls_set_error(int status, const char* msg) {
 	return status;
 }
 
-static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
+static bool is_patched(unsigned enc) {
+	return enc == FLS_ENC_FFOR || enc == FLS_ENC_SLPATCH || enc == FLS_ENC_FREQUENCY || enc == FLS_ENC_ALP || enc == FLS_ENC_ALP_RD;
+}
+
+// packed part of a vector's blob (the exception tail follows it)
+static unsigned packed_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
 	switch (c.encoding) {
 	case FLS_ENC_UNCOMPRESSED: return 1024u * c.phys_bits / 8;
 	case FLS_ENC_DELTA:
@@ -25,6 +30,9 @@ static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
 	case FLS_ENC_CROSS_RLE: return 0;
 	default: return 128u * m.width;
 	}
+}
+static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
+	return packed_bytes(c, m) + (is_patched(c.encoding) ? FLS_EXC_TAIL_BYTES(m.aux_cnt, c.phys_bits / 8u) : 0u);
 }
 
 int fls_table_parse(flsgpu_table* t) {
@@ -95,8 +103,7 @@ int fls_table_parse(flsgpu_table* t) {
 			}
 			const unsigned T = ch.phys_bits, esz = T / 8;
 			const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_META]);
-			const bool patched = ch.encoding == FLS_ENC_FFOR || ch.encoding == FLS_ENC_SLPATCH || ch.encoding == FLS_ENC_FREQUENCY ||
-			                     ch.encoding == FLS_ENC_ALP || ch.encoding == FLS_ENC_ALP_RD;
+			const bool patched = is_patched(ch.encoding);
 			unsigned lanes_T = T;
 			if (ch.encoding == FLS_ENC_DICT) {
 				lanes_T = ch.idx_bits;
@@ -123,15 +130,12 @@ int fls_table_parse(flsgpu_table* t) {
 				if (sum != (uint64_t)ch.n_vec * FLS_VEC_SZ) {
 					return fail("CROSS_RLE run lengths do not cover the chunk");
 				}
-			} else if (patched) {
-				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.seg_size[FLS_SEG_AUX1] != (uint64_t)ch.aux_count * 2) {
-					return fail("exception segments have the wrong size");
-				}
 			}
 			if ((ch.encoding == FLS_ENC_ALP || ch.encoding == FLS_ENC_ALP_RD) && !(col.is_float && T >= 32)) {
 				return fail("ALP encodings need a FLOAT/DOUBLE column");
 			}
-			const uint16_t* exc_pos = reinterpret_cast<const uint16_t*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX1]);
+			const uint8_t* data_seg = t->bytes + ch.offset + ch.seg_off[FLS_SEG_DATA];
+			uint64_t n_exc_seen = 0;
 			for (uint32_t v = 0; v < ch.n_vec; ++v) {
 				const fls_vec_meta& m = meta[v];
 				if (m.width > lanes_T || (ch.encoding == FLS_ENC_ALP_RD && (m.width2 == 0 || m.width2 > 3 || m.width + m.width2 > 64 + 3))) {
@@ -140,20 +144,27 @@ int fls_table_parse(flsgpu_table* t) {
 				if ((uint64_t)m.data_off16 * 16 + blob_bytes(ch, m) > ch.seg_size[FLS_SEG_DATA]) {
 					return fail("vector entry point outside the data segment");
 				}
+				if (blob_bytes(ch, m) > ch.max_blob_bytes) {
+					return fail("vector blob larger than the chunk's max_blob_bytes");
+				}
 				if (m.n_valid == 0 || m.n_valid > FLS_VEC_SZ) {
 					return fail("vector n_valid out of range");
 				}
-				if (patched || ch.encoding == FLS_ENC_RLE) {
-					if ((uint64_t)m.aux_off + m.aux_cnt > ch.aux_count || m.aux_cnt > FLS_VEC_SZ) {
-						return fail("vector aux range outside the aux segments");
-					}
+				if (m.aux_cnt > FLS_VEC_SZ || (!patched && ch.encoding != FLS_ENC_RLE && m.aux_cnt != 0)) {
+					return fail("vector exception/run count out of range");
 				}
-				if (patched) {
+				if (ch.encoding == FLS_ENC_RLE && (uint64_t)m.aux_off + m.aux_cnt > ch.aux_count) {
+					return fail("vector run range outside the run value segment");
+				}
+				if (patched && m.aux_cnt) {
+					const uint16_t* exc_pos = reinterpret_cast<const uint16_t*>(data_seg + (uint64_t)m.data_off16 * 16 + packed_bytes(ch, m) +
+					                                                            FLS_PAD16((uint32_t)m.aux_cnt * esz));
 					for (uint32_t k = 0; k < m.aux_cnt; ++k) {
-						if (exc_pos[m.aux_off + k] >= FLS_VEC_SZ) {
+						if (exc_pos[k] >= FLS_VEC_SZ) {
 							return fail("exception position out of range");
 						}
 					}
+					n_exc_seen += m.aux_cnt;
 				}
 				if (ch.encoding == FLS_ENC_ALP && (m.e > (T == 64 ? 18 : 10) || m.f > m.e)) {
 					return fail("ALP exponent/factor out of range");
@@ -161,6 +172,9 @@ int fls_table_parse(flsgpu_table* t) {
 				if (ch.encoding == FLS_ENC_RLE && m.aux_cnt == 0) {
 					return fail("RLE vector without runs");
 				}
+			}
+			if (patched && n_exc_seen != ch.aux_count) {
+				return fail("exception count disagrees with the chunk descriptor");
 			}
 		}
 	}

@@ -58,6 +58,11 @@ struct VecDesc {
 	uint32_t misc;  // aux_cnt | width << 16 | encoding << 24
 	uint32_t misc2; // width2 | e << 8 | f << 16
 	uint32_t vec_in_chunk; // vector index inside its chunk | n_valid << 16
+	// chunk-level pointers, copied at descriptor-fetch time (lane-parallel, once per 32 vectors) so that no warp ever
+	// chases ch-> through global memory in the middle of a vector
+	const uint8_t* aux0; // dictionary keys | run values | exception values | CROSS_RLE values
+	const uint8_t* aux1; // exception positions | CROSS_RLE run starts
+	uint32_t aux_n;      // ch->aux_count (#keys, #runs)
 };
 
 __device__ __forceinline__ VecDesc shfl_desc(const VecDesc& d, int src) {
@@ -70,30 +75,36 @@ __device__ __forceinline__ VecDesc shfl_desc(const VecDesc& d, int src) {
 	r.misc = __shfl_sync(0xffffffffu, d.misc, src);
 	r.misc2 = __shfl_sync(0xffffffffu, d.misc2, src);
 	r.vec_in_chunk = __shfl_sync(0xffffffffu, d.vec_in_chunk, src);
+	r.aux0 = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)d.aux0, src);
+	r.aux1 = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)d.aux1, src);
+	r.aux_n = __shfl_sync(0xffffffffu, d.aux_n, src);
 	return r;
 }
 
-template <int T>
-__device__ __forceinline__ uint32_t blob_bytes(uint32_t enc, uint32_t w, uint32_t w2) {
+// Bytes of a vector's blob: packed part + exception tail (fls_format.h).  T = lane width of the packed data, VT = value width.
+template <int T, int VT>
+__device__ __forceinline__ uint32_t blob_bytes(uint32_t enc, uint32_t w, uint32_t w2, uint32_t n_exc) {
 	switch (enc) {
 	case FLS_ENC_UNCOMPRESSED: return 128u * T;
 	case FLS_ENC_CONSTANT:
 	case FLS_ENC_CROSS_RLE: return 0u;
 	case FLS_ENC_DELTA:
 	case FLS_ENC_RLE: return 128u + 128u * w;
-	case FLS_ENC_ALP_RD: return 128u * (w + w2);
-	default: return 128u * w;
+	case FLS_ENC_DICT: return 128u * w;
+	case FLS_ENC_ALP_RD: return 128u * (w + w2) + FLS_EXC_TAIL_BYTES(n_exc, VT / 8u);
+	default: return 128u * w + FLS_EXC_TAIL_BYTES(n_exc, VT / 8u); // FFOR, SLPATCH, FREQUENCY, ALP
 	}
 }
 
 // Lane-parallel descriptor fetch for vector v (v >= total or not of this kernel's family -> bytes = 0, ch = null).
-template <int T>
+template <int T, int VT>
 __device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
 	VecDesc d;
 	d.blob = nullptr;
 	d.ch = nullptr;
 	d.base = 0;
-	d.aux_off = d.bytes = d.misc = d.misc2 = d.vec_in_chunk = 0;
+	d.aux_off = d.bytes = d.misc = d.misc2 = d.vec_in_chunk = d.aux_n = 0;
+	d.aux0 = d.aux1 = nullptr;
 	if (v < L.total_vecs) {
 		const uint32_t r = v / L.vec_per_rg, vi = v - r * L.vec_per_rg;
 		const FlsChunkDev* ch = L.chunks + (size_t)r * L.chunk_stride;
@@ -108,9 +119,12 @@ __device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
 			d.misc = aux_cnt | (w << 16) | (enc << 24);
 			d.misc2 = w2 | ((m1.y & 0xffffu) << 8);
 			d.vec_in_chunk = vi | (m1.y & 0xffff0000u);
-			d.bytes = blob_bytes<T>(enc, w, w2);
+			d.bytes = blob_bytes<T, VT>(enc, w, w2, aux_cnt);
 			d.blob = ch->data + (size_t)m0.z * 16;
 			d.ch = ch;
+			d.aux0 = ch->aux0;
+			d.aux1 = ch->aux1;
+			d.aux_n = ch->aux_count;
 		}
 	}
 	return d;
@@ -132,42 +146,31 @@ __device__ __forceinline__ void load_elem(const uint8_t* base, uint32_t idx, uin
 	}
 }
 
-// out[pos[k]] = exception[k]  (alp.hpp:401-404; slpatch / frequency patches).
-// The first 32 exceptions of a vector (one per lane) are loaded BEFORE the vector is unpacked so that the global-load
-// latency hides behind the unpack + stores; they are written after the vector's own stores (ordered by __syncwarp).
-struct ExcPrefetch {
-	uint32_t lo, hi, pos;
-};
-
-template <int T>
-__device__ __forceinline__ ExcPrefetch prefetch_exceptions(const VecDesc& d, int lane) {
-	ExcPrefetch e;
-	e.lo = e.hi = e.pos = 0;
-	const uint32_t n = d.misc & 0xffffu;
-	if ((uint32_t)lane < n) {
-		e.pos = __ldg(reinterpret_cast<const uint16_t*>(d.ch->aux1) + d.aux_off + lane);
-		load_elem<T>(d.ch->aux0, d.aux_off + lane, e.lo, e.hi);
-	}
-	return e;
-}
-
+// out[pos[k]] = exception[k]  (alp.hpp:401-404; slpatch / frequency patches).  The exception tail was staged into the
+// vector's shared-memory slot by the same bulk copy as the packed data, so patching costs no global load; the scattered
+// stores land after the vector's own stores (ordered by __syncwarp).
 template <int T, int OB>
-__device__ __forceinline__ void patch_exceptions(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv, const ExcPrefetch& e) {
+__device__ __forceinline__ void patch_exceptions(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv, const uint8_t* tail) {
 	const uint32_t n = d.misc & 0xffffu;
 	if (n == 0) {
 		return;
 	}
 	__syncwarp();
-	if ((uint32_t)lane < n) {
-		store_one<T, OB>(out_vec, e.pos, e.lo, e.hi, conv);
-	}
-	if (n > 32) {
-		const uint16_t* pos = reinterpret_cast<const uint16_t*>(d.ch->aux1) + d.aux_off;
-		for (uint32_t k = lane + 32; k < n; k += 32) {
-			uint32_t lo, hi;
-			load_elem<T>(d.ch->aux0, d.aux_off + k, lo, hi);
-			store_one<T, OB>(out_vec, __ldg(pos + k), lo, hi, conv);
+	const uint16_t* pos = reinterpret_cast<const uint16_t*>(tail + FLS_PAD16(n * (T / 8u)));
+	for (uint32_t k = lane; k < n; k += 32) {
+		uint32_t lo, hi = 0;
+		if constexpr (T == 8) {
+			lo = tail[k];
+		} else if constexpr (T == 16) {
+			lo = reinterpret_cast<const uint16_t*>(tail)[k];
+		} else if constexpr (T == 32) {
+			lo = reinterpret_cast<const uint32_t*>(tail)[k];
+		} else {
+			const uint2 q = reinterpret_cast<const uint2*>(tail)[k];
+			lo = q.x;
+			hi = q.y;
 		}
+		store_one<T, OB>(out_vec, pos[k], lo, hi, conv);
 	}
 }
 
@@ -199,8 +202,8 @@ __device__ __forceinline__ void fill_constant(uint8_t* out_vec, int lane, uint32
 // dec_cross_rle_opr: starts[] is the exclusive prefix sum of the run lengths (built at stage time).
 template <int T, int OB>
 __device__ __forceinline__ void decode_cross_rle(uint8_t* out_vec, const VecDesc& d, int lane, uint32_t conv) {
-	const uint32_t* starts = reinterpret_cast<const uint32_t*>(d.ch->aux1);
-	const uint32_t n_runs = d.ch->aux_count;
+	const uint32_t* starts = reinterpret_cast<const uint32_t*>(d.aux1);
+	const uint32_t n_runs = d.aux_n;
 	const uint32_t g0 = (d.vec_in_chunk & 0xffffu) * 1024u;
 	// first run of this vector (uniform binary search): largest r with starts[r] <= g0
 	uint32_t lo_r = 0, hi_r = n_runs;
@@ -225,7 +228,7 @@ __device__ __forceinline__ void decode_cross_rle(uint8_t* out_vec, const VecDesc
 			}
 		}
 		uint32_t lo, hi;
-		load_elem<T>(d.ch->aux0, a, lo, hi);
+		load_elem<T>(d.aux0, a, lo, hi);
 		store_one<T, OB>(out_vec, it * 32 + lane, lo, hi, conv);
 	}
 }

@@ -13,8 +13,8 @@ __device__ __forceinline__ void process_dict(const VecDesc& d, const uint8_t* sl
 	uint32_t v[32];
 	unpack_small_dispatch<IT>((int)W, reinterpret_cast<const uint32_t*>(slot), lane, v);
 	const uint32_t base = (uint32_t)d.base;
-	const uint8_t* keys = d.ch->aux0;
-	const uint32_t n_keys = d.ch->aux_count;
+	const uint8_t* keys = d.aux0;
+	const uint32_t n_keys = d.aux_n;
 	constexpr int G = 32 / IT;
 #pragma unroll
 	for (int r = 0; r < 32 / G; ++r) {
@@ -59,7 +59,7 @@ __device__ __forceinline__ void process_rle(const VecDesc& d, const uint8_t* slo
 		}
 	}
 	__syncwarp();
-	const uint8_t* vals = d.ch->aux0;
+	const uint8_t* vals = d.aux0;
 	const uint32_t first = d.aux_off, n_runs = d.misc & 0xffffu;
 #pragma unroll
 	for (int it = 0; it < 4; ++it) { // 2 KB of u16 indexes = 128 granules of 8

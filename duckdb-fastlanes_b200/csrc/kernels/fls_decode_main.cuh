@@ -21,7 +21,7 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 	if constexpr ((FAM & kFamLight) != 0) {
 		switch (enc) {
 		case FLS_ENC_UNCOMPRESSED: copy_out_linear<T, OB, false>(slot, out_vec, lane, conv); return;
-		case FLS_ENC_CONSTANT: fill_constant<T, OB>(out_vec, lane, (uint32_t)d.ch->const_val, 0, conv); return;
+		case FLS_ENC_CONSTANT: fill_constant<T, OB>(out_vec, lane, (uint32_t)d.base, 0, conv); return;
 		case FLS_ENC_CROSS_RLE: decode_cross_rle<T, OB>(out_vec, d, lane, conv); return;
 		default: break;
 		}
@@ -87,8 +87,8 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		return;
 	}
 	// FFOR family / ALP / ALP_RD: packed blob starts at the slot
-	const ExcPrefetch exc = prefetch_exceptions<T>(d, lane);
 	unpack_small_dispatch<T>((int)W, reinterpret_cast<const uint32_t*>(slot), lane, v);
+	uint32_t packed = 128u * W; // bytes of the packed part; the exception tail follows
 	if constexpr (T == 32) {
 		if ((FAM & kFamAlp) != 0 && (FAM == kFamAlp || enc == FLS_ENC_ALP)) { // alp.hpp:129-134: (float)digit * (float)FACT[f] * FRAC[e], two roundings, no FMA
 			const float fa = c_fact_f[(d.misc2 >> 16) & 0xffu], fr = c_frac_f[(d.misc2 >> 8) & 0xffu];
@@ -100,8 +100,9 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		} else if ((FAM & kFamAlpRd) != 0 && (FAM == kFamAlpRd || enc == FLS_ENC_ALP_RD)) { // alprd.hpp:222-226
 			uint32_t left[32];
 			const uint32_t W2 = d.misc2 & 0xffu;
+			packed += 128u * W2;
+			const uint4 dq = __ldg(reinterpret_cast<const uint4*>(d.ch->rd_dict)); // issued before the unpack: latency overlaps it
 			unpack_small_dispatch<T>((int)W2, reinterpret_cast<const uint32_t*>(slot) + 32 * W, lane, left);
-			const uint4 dq = *reinterpret_cast<const uint4*>(d.ch->rd_dict);
 			const uint32_t dw[4] = {dq.x, dq.y, dq.z, dq.w};
 #pragma unroll
 			for (int j = 0; j < 32; ++j) {
@@ -123,7 +124,7 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		}
 	}
 	store_direct<T, OB>(out_vec, lane, v, conv);
-	patch_exceptions<T, OB>(out_vec, d, lane, conv, exc);
+	patch_exceptions<T, OB>(out_vec, d, lane, conv, slot + packed);
 }
 
 // ---- T = 64 --------------------------------------------------------------------------------------------------------------
@@ -134,7 +135,7 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 		switch (enc) {
 		case FLS_ENC_UNCOMPRESSED: copy_out_linear<64, 8, false>(slot, out_vec, lane, 0); return;
 		case FLS_ENC_CONSTANT:
-			fill_constant<64, 8>(out_vec, lane, (uint32_t)d.ch->const_val, (uint32_t)(d.ch->const_val >> 32), 0);
+			fill_constant<64, 8>(out_vec, lane, (uint32_t)d.base, (uint32_t)(d.base >> 32), 0);
 			return;
 		case FLS_ENC_CROSS_RLE: decode_cross_rle<64, 8>(out_vec, d, lane, 0); return;
 		default: break;
@@ -166,8 +167,8 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 		copy_out_linear<64, 8, true>(stage, out_vec, lane, 0);
 		return;
 	}
-	const ExcPrefetch exc = prefetch_exceptions<64>(d, lane);
 	unpack_64_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot), lane, lo, hi);
+	uint32_t packed = 128u * W; // bytes of the packed part; the exception tail follows
 	if ((FAM & kFamAlp) != 0 && (FAM == kFamAlp || enc == FLS_ENC_ALP)) { // (double)digit * (double)FACT[f] * FRAC[e]
 		const double fa = c_fact_d[(d.misc2 >> 16) & 0xffu], fr = c_frac_d[(d.misc2 >> 8) & 0xffu];
 #pragma unroll
@@ -181,8 +182,9 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 	} else if ((FAM & kFamAlpRd) != 0 && (FAM == kFamAlpRd || enc == FLS_ENC_ALP_RD)) {
 		uint32_t llo[32], lhi[32];
 		const uint32_t W2 = d.misc2 & 0xffu;
+		packed += 128u * W2;
+		const uint4 dq = __ldg(reinterpret_cast<const uint4*>(d.ch->rd_dict)); // issued before the unpack: latency overlaps it
 		unpack_64_dispatch((int)W2, reinterpret_cast<const uint32_t*>(slot) + 32 * W, lane, llo, lhi);
-		const uint4 dq = *reinterpret_cast<const uint4*>(d.ch->rd_dict);
 		const uint32_t dw[4] = {dq.x, dq.y, dq.z, dq.w};
 #pragma unroll
 		for (int j = 0; j < 32; ++j) {
@@ -205,7 +207,7 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 	(void)blo;
 	(void)bhi;
 	store_direct64(out_vec, lane, lo, hi);
-	patch_exceptions<64, 8>(out_vec, d, lane, 0, exc);
+	patch_exceptions<64, 8>(out_vec, d, lane, 0, slot + packed);
 }
 
 // ---- the persistent kernel -----------------------------------------------------------------------------------------------
@@ -259,7 +261,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			break;
 		}
 		const uint64_t my_v64 = (((run0 + ((uint32_t)lane >> cs)) * n_warps + gw) << cs) + ((uint32_t)lane & cmask);
-		const VecDesc mine = fetch_desc<T>(L, my_v64 < L.total_vecs ? (uint32_t)my_v64 : 0xffffffffu);
+		const VecDesc mine = fetch_desc<T, VT>(L, my_v64 < L.total_vecs ? (uint32_t)my_v64 : 0xffffffffu);
 		uint32_t todo = __ballot_sync(0xffffffffu, mine.ch != nullptr);
 		uint32_t to_issue = todo;
 		// prologue: fill the pipeline

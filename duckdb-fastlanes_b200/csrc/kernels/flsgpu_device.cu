@@ -292,14 +292,7 @@ int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t 
 }
 
 uint32_t blob_bytes_max(const fls_chunk_desc& c) {
-	switch (c.encoding) {
-	case FLS_ENC_UNCOMPRESSED: return 128u * c.phys_bits;
-	case FLS_ENC_CONSTANT:
-	case FLS_ENC_CROSS_RLE: return 0;
-	case FLS_ENC_DELTA:
-	case FLS_ENC_RLE: return 128u + 128u * c.max_width;
-	default: return 128u * c.max_width; // ALP_RD: max_width = max(width + width2)
-	}
+	return c.max_blob_bytes; // largest packed blob + exception tail of the chunk, recorded by the writer
 }
 
 const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg) {

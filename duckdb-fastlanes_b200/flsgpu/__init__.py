@@ -51,7 +51,7 @@ class ChunkDesc(C.Structure):
                 ("const_val", C.c_uint64), ("min_val", C.c_uint64), ("max_val", C.c_uint64), ("n_vec", C.c_uint32),
                 ("n_tuples", C.c_uint32), ("aux_count", C.c_uint32), ("encoding", C.c_uint8), ("phys_bits", C.c_uint8),
                 ("idx_bits", C.c_uint8), ("max_width", C.c_uint8), ("has_stats", C.c_uint8), ("reserved8", C.c_uint8 * 3),
-                ("rd_dict", C.c_uint16 * 8), ("reserved32", C.c_uint32)]
+                ("rd_dict", C.c_uint16 * 8), ("max_blob_bytes", C.c_uint32)]
 
 
 class TableInfo(C.Structure):

@@ -24,7 +24,7 @@ extern "C" {
 #endif
 
 #define FLS_MAGIC "FLSB2001"
-#define FLS_VERSION 1u
+#define FLS_VERSION 2u
 #define FLS_VEC_SZ 1024u            /* fastlanes::CFG::VEC_SZ */
 #define FLS_DEFAULT_VEC_PER_RG 64u  /* row group = 65 536 tuples, reference fls_writer.hpp:14 */
 #define FLS_ALIGN 128u
@@ -73,8 +73,8 @@ typedef enum fls_encoding {
 enum {
 	FLS_SEG_META = 0, /* fls_vec_meta[n_vec] */
 	FLS_SEG_DATA = 1, /* per-vector packed blobs, addressed by fls_vec_meta.data_off16 */
-	FLS_SEG_AUX0 = 2, /* DICT keys | RLE run values | exception values | CROSS_RLE values | string bytes */
-	FLS_SEG_AUX1 = 3, /* exception positions (u16) | CROSS_RLE lengths (u32) | string end offsets (u32) */
+	FLS_SEG_AUX0 = 2, /* DICT keys | RLE run values | CROSS_RLE values | string bytes */
+	FLS_SEG_AUX1 = 3, /* CROSS_RLE lengths (u32) | string end offsets (u32) */
 	FLS_SEG_COUNT = 4
 };
 
@@ -127,15 +127,15 @@ typedef struct fls_chunk_desc { /* 144 bytes */
 	uint8_t has_stats;
 	uint8_t reserved8[3];
 	uint16_t rd_dict[8]; /* ALP_RD: left-part dictionary (alprd_constants.hpp MAX_DICTIONARY_SIZE = 8) */
-	uint32_t reserved32;
+	uint32_t max_blob_bytes; /* largest per-vector blob of the chunk (packed data + exception tail): sizes the TMA slots */
 } fls_chunk_desc;
 
 /* Per-vector entry point + parameters: what PointTo(vec_idx) resolves in the reference. */
 typedef struct fls_vec_meta { /* 32 bytes */
 	uint64_t base;       /* FFOR/SLPATCH/ALP: frame of reference; FREQUENCY: frequent value */
 	uint32_t data_off16; /* blob offset from the DATA segment start, 16-byte units */
-	uint32_t aux_off;    /* first exception / first run value of this vector in AUX0 (and AUX1), in elements */
-	uint16_t aux_cnt;    /* #exceptions | #runs of this vector */
+	uint32_t aux_off;    /* RLE: first run value of this vector in AUX0, in elements */
+	uint16_t aux_cnt;    /* #exceptions (stored in the blob's tail) | #runs of this vector */
 	uint8_t width;       /* packed bit width W in [0,T] */
 	uint8_t width2;      /* ALP_RD: bit width of the left-part codes */
 	uint8_t e;           /* ALP exponent */
@@ -144,12 +144,18 @@ typedef struct fls_vec_meta { /* 32 bytes */
 	uint64_t reserved;
 } fls_vec_meta;
 
-/* Per-vector blob layout in the DATA segment (sizes in bytes, every blob is a multiple of 128):
- *   FFOR / SLPATCH / ALP / DICT codes / FREQUENCY(W=0): [128*W packed]
- *   DELTA, RLE index:                                   [128 lane bases][128*W packed deltas]
- *   ALP_RD:                                             [128*W right parts][128*W2 left codes]  (both in T lanes)
- *   UNCOMPRESSED:                                       [1024*T/8 natural order]
+/* Per-vector blob layout in the DATA segment (sizes in bytes, every blob is a multiple of 16 and starts 16-aligned):
+ *   FFOR / SLPATCH / ALP / FREQUENCY(W=0): [128*W packed][exception tail]
+ *   ALP_RD:                                [128*W right parts][128*W2 left codes][exception tail]  (both in T lanes)
+ *   DICT codes:                            [128*W packed]
+ *   DELTA, RLE index:                      [128 lane bases][128*W packed deltas]
+ *   UNCOMPRESSED:                          [1024*T/8 natural order]
+ * exception tail (aux_cnt = n > 0 only):   [n values of T bits, padded to 16 B][n positions u16, padded to 16 B]
+ * The exceptions travel with the vector so that ONE bulk copy stages everything a vector needs (out[pos[k]] = value[k]
+ * after the vector has been decoded: alp.hpp:401-404, slpatch / frequency patches).
  */
+#define FLS_PAD16(x) (((x) + 15u) & ~15u)
+#define FLS_EXC_TAIL_BYTES(n, elem_bytes) ((n) ? FLS_PAD16((uint32_t)(n) * (elem_bytes)) + FLS_PAD16((uint32_t)(n) * 2u) : 0u)
 
 #ifdef __cplusplus
 }

@@ -66,7 +66,11 @@ static void FN(untranspose_)(const U* restrict in, U* restrict out) {
 }
 
 /* exceptions: out[pos[k]] = val[k] (alp.hpp:401-404) */
-static void FN(patch_)(U* out, const U* vals, const uint16_t* pos, unsigned n) {
+/* out[pos[k]] = value[k] (alp.hpp:401-404).  The exception tail sits behind the packed part of the vector's blob:
+ * [n values, padded to 16 B][n positions u16, padded to 16 B] (fls_format.h). */
+static void FN(patch_)(U* out, const uint8_t* tail, unsigned n) {
+	const U* vals = (const U*)tail;
+	const uint16_t* pos = (const uint16_t*)(tail + FLS_PAD16(n * (unsigned)sizeof(U)));
 	for (unsigned k = 0; k < n; ++k) {
 		out[pos[k]] = vals[k];
 	}
@@ -98,7 +102,6 @@ static int FN(decode_vector_)(const uint8_t* chunk_base, const fls_chunk_desc* c
 	const fls_vec_meta* m = (const fls_vec_meta*)(chunk_base + ch->seg_off[FLS_SEG_META]) + vec;
 	const uint8_t* blob = chunk_base + ch->seg_off[FLS_SEG_DATA] + (size_t)m->data_off16 * 16;
 	const U* aux0 = (const U*)(chunk_base + ch->seg_off[FLS_SEG_AUX0]);
-	const uint16_t* aux1_16 = (const uint16_t*)(chunk_base + ch->seg_off[FLS_SEG_AUX1]);
 	*is_transposed = 0;
 	switch (ch->encoding) {
 	case FLS_ENC_UNCOMPRESSED: memcpy(out, blob, 1024 * sizeof(U)); return 0;
@@ -111,7 +114,7 @@ static int FN(decode_vector_)(const uint8_t* chunk_base, const fls_chunk_desc* c
 	case FLS_ENC_SLPATCH:
 	case FLS_ENC_FREQUENCY:
 		FN(unffor_)((const U*)blob, m->width, (U)m->base, out);
-		FN(patch_)(out, aux0 + m->aux_off, aux1_16 + m->aux_off, m->aux_cnt);
+		FN(patch_)(out, blob + 128u * m->width, m->aux_cnt);
 		return 0;
 	case FLS_ENC_DELTA: {
 		U deltas[1024];
@@ -165,7 +168,7 @@ static int FN(decode_vector_)(const uint8_t* chunk_base, const fls_chunk_desc* c
 		for (unsigned i = 0; i < 1024; ++i) {
 			out[i] = FN(alp_decode_)((S)out[i], m->e, m->f);
 		}
-		FN(patch_)(out, aux0 + m->aux_off, aux1_16 + m->aux_off, m->aux_cnt);
+		FN(patch_)(out, blob + 128u * m->width, m->aux_cnt);
 		return 0;
 	}
 	case FLS_ENC_ALP_RD: { /* alprd.hpp:203-236 */
@@ -175,7 +178,7 @@ static int FN(decode_vector_)(const uint8_t* chunk_base, const fls_chunk_desc* c
 		for (unsigned i = 0; i < 1024; ++i) {
 			out[i] = (U)(((U)ch->rd_dict[left[i] & 7] << m->width) | out[i]);
 		}
-		FN(patch_)(out, aux0 + m->aux_off, aux1_16 + m->aux_off, m->aux_cnt);
+		FN(patch_)(out, blob + 128u * (m->width + m->width2), m->aux_cnt);
 		return 0;
 	}
 #endif

@@ -86,8 +86,6 @@ def alprd_container(l, bits, seed):
     ch = t.chunk(0, 0)
     meta = np.frombuffer(img, dtype=META_DT, count=ch.n_vec, offset=ch.offset + ch.seg_off[0])
     data0 = ch.offset + ch.seg_off[1]
-    exc_vals = np.frombuffer(img, dtype=udt, count=ch.aux_count, offset=ch.offset + ch.seg_off[2])
-    exc_pos = np.frombuffer(img, dtype=np.uint16, count=ch.aux_count, offset=ch.offset + ch.seg_off[3])
     glue = l.ref_alprd_glue_u64 if bits == 64 else l.ref_alprd_glue_u32
     expected = np.zeros(2048, dtype=udt)
     for v in range(ch.n_vec):
@@ -97,8 +95,11 @@ def alprd_container(l, bits, seed):
         left = oracle_lib.unpack(np.frombuffer(img, dtype=np.uint8, count=128 * int(m["width2"]), offset=blob + 128 * int(m["width"])),
                                  bits, int(m["width2"]))
         out = np.array([glue(int(ch.rd_dict[int(c) & 7]), int(rt), int(m["width"])) for c, rt in zip(left, right)], dtype=udt)
-        a, n = int(m["aux_off"]), int(m["aux_cnt"])
-        out[exc_pos[a:a + n]] = exc_vals[a:a + n]  # exceptions are stored as whole words in this container
+        n = int(m["aux_cnt"])  # exception tail of the blob: [n whole words, padded to 16 B][n u16 positions]
+        tail = blob + 128 * (int(m["width"]) + int(m["width2"]))
+        exc_vals = np.frombuffer(img, dtype=udt, count=n, offset=tail)
+        exc_pos = np.frombuffer(img, dtype=np.uint16, count=n, offset=tail + (n * (bits // 8) + 15) // 16 * 16)
+        out[exc_pos] = exc_vals
         expected[v * 1024:(v + 1) * 1024] = out
     t.close()
     assert expected.tobytes() == x.tobytes(), "reference glue over the container's parts must reproduce the input"

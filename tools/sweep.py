@@ -18,7 +18,27 @@ from bench import algorithmic_bytes  # noqa: E402
 WIDTHS = [0, 1, 2, 3, 4, 6, 8, 10, 12, 16, 20, 24, 32, 40, 48, 56, 63, 64]
 
 
+def float_column(kind, tname, w, n, rng):
+    """ALP shapes: ALP0 = digits of w bits, no exceptions; ALPX = i/1000.0 (the bench's DOUBLE column, ~8 exceptions per
+    vector); ALPRD = full-entropy mantissas."""
+    fdt = np.float64 if tname == "DOUBLE" else np.float32
+    base_n = 1 << 20
+    if kind == "ALP0":
+        d = rng.integers(0, (1 << w) - 1, base_n, endpoint=True).astype(np.float64)
+        x = (d / 100.0).astype(fdt) if tname == "DOUBLE" else d.astype(fdt)
+        if tname == "DOUBLE":  # keep only values ALP round-trips exactly at (e=2,f=0): make them so by construction
+            x = (np.round(x * 100.0) / 100.0).astype(fdt)
+    elif kind == "ALPX":
+        i = np.arange(1, base_n + 1, dtype=np.int64) + (1 << w)
+        x = (i / 1000.0).astype(fdt) if tname == "DOUBLE" else (i.astype(np.float32) / np.float32(100))
+    else:
+        x = (rng.random(base_n) * 2 - 1).astype(fdt)
+    return np.tile(x, n // base_n)
+
+
 def column(kind, tname, w, n, rng):
+    if kind.startswith("ALP"):
+        return float_column(kind, tname, w, n, rng)
     dt = np.dtype({"INT64": np.int64, "INT32": np.int32, "INT16": np.int16, "INT8": np.int8}[tname])
     bits = dt.itemsize * 8
     udt = np.dtype(f"u{dt.itemsize}")
@@ -71,18 +91,23 @@ def main():
     rng = np.random.default_rng(42)
     rows = []
     for tname in args.types.split(","):
-        bits = {"INT64": 64, "INT32": 32, "INT16": 16, "INT8": 8}[tname]
+        bits = {"INT64": 64, "INT32": 32, "INT16": 16, "INT8": 8, "DOUBLE": 64, "FLOAT": 32}[tname]
         for kind in args.kinds.split(","):
             ws = [w for w in WIDTHS if w <= bits]
             if kind == "DICT":
                 ws = [1, 4, 8, 12, 16]
             if kind == "RLE":
                 ws = [1, 3, 6, 10]
+            if kind.startswith("ALP"):
+                ws = {"ALP0": [4, 10, 20], "ALPX": [10, 24], "ALPRD": [0]}[kind]
+            if kind.startswith("ALP") != (tname in ("DOUBLE", "FLOAT")):
+                continue
             for w in ws:
                 if kind == "DICT" and w >= bits:
                     continue
                 x = column(kind, tname, w, args.values, rng)
-                img = flsgpu.write_table([("c", tname, kind)], [x])
+                force = {"ALP0": "ALP", "ALPX": "ALP", "ALPRD": "ALP_RD"}.get(kind, kind)
+                img = flsgpu.write_table([("c", tname, force)], [x])
                 t = flsgpu.Table(img)
                 t.stage()
                 ms, rd, wr = measure(t, img, 0)
