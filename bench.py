@@ -341,13 +341,18 @@ def run_gpu(args, rank, world, local_rank):
     # reduced scan result: fused SUM/COUNT of the BIGINT column on every rank, combined with one NCCL all-reduce
     from flsgpu import sharding
     res = torch.zeros(64, dtype=torch.uint8, device="cuda")
-    flsgpu.agg_reset(res.data_ptr(), stream)
     ea0, ea1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(3):  # warm-up: first launch of a kernel pays lazy module loading
+        flsgpu.agg_reset(res.data_ptr(), stream)
+        t.aggregate_column(3, res.data_ptr(), stream=stream)
+    n_agg = 10
     ea0.record()
-    t.aggregate_column(3, res.data_ptr(), stream=stream)
+    for _ in range(n_agg):
+        flsgpu.agg_reset(res.data_ptr(), stream)
+        t.aggregate_column(3, res.data_ptr(), stream=stream)
     ea1.record()
     torch.cuda.synchronize()
-    agg_ms = ea0.elapsed_time(ea1)
+    agg_ms = ea0.elapsed_time(ea1) / n_agg
     r_ = flsgpu.AggResult.from_buffer_copy(res.cpu().numpy().tobytes())
     s128 = (r_.sum_hi << 64) | r_.sum_lo
     s128 -= (1 << 128) if s128 >= (1 << 127) else 0

@@ -239,13 +239,11 @@ struct AggPartial {
 	unsigned long long lo = 0;   // low 64 bits of the running sum
 	long long hi = 0;            // carries out of `lo` minus the number of negative addends
 	unsigned long long cnt = 0;
-	unsigned long long kmin = ~0ull, kmax = 0ull; // order keys
 	double fs = 0.0;
 
 	// Fold the first n_valid values of the natural-order tile (VT-bit elements) into the partials.
 	template <int VT>
 	__device__ __forceinline__ void fold(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float) {
-		const unsigned long long flip = is_signed ? 0x8000000000000000ull : 0ull;
 #pragma unroll 4
 		for (uint32_t i = lane; i < 1024u; i += 32u) {
 			if (i >= n_valid) {
@@ -275,11 +273,78 @@ struct AggPartial {
 			lo += u;
 			hi += (lo < u) ? 1 : 0;
 			hi -= (is_signed && (long long)u < 0) ? 1 : 0;
-			const unsigned long long key = u ^ flip;
-			kmin = key < kmin ? key : kmin;
-			kmax = key > kmax ? key : kmax;
 		}
 		cnt += n_valid > (uint32_t)lane ? (n_valid - lane + 31u) / 32u : 0u;
+	}
+
+	// ---- register fast path: the 32 values a thread holds right after decoding (vector complete, no exceptions) -------
+	// MIN/MAX are not computed here: flsgpu_aggregate_column folds the chunks' exact zone maps (fls_chunk_desc.min_val /
+	// max_val, written from the data by the writer) into the result instead, like a scan answering from statistics.
+	__device__ __forceinline__ void add_u128(unsigned long long u, long long sign_word) {
+		const unsigned long long before = lo;
+		lo += u;
+		hi += sign_word + ((lo < before) ? 1 : 0);
+	}
+	// T <= 32: values are T-bit fields held in 32-bit registers; 32 of them cannot overflow a 64-bit partial
+	template <int T>
+	__device__ __forceinline__ void add32(const uint32_t (&v)[32], uint32_t is_signed, uint32_t is_float) {
+		cnt += 32;
+		if (T == 32 && is_float) {
+			double f0 = 0.0, f1 = 0.0;
+#pragma unroll
+			for (int j = 0; j < 32; j += 2) {
+				f0 += (double)__uint_as_float(v[j]);
+				f1 += (double)__uint_as_float(v[j + 1]);
+			}
+			fs += f0 + f1;
+			return;
+		}
+		if (is_signed) {
+			long long s0 = 0, s1 = 0;
+#pragma unroll
+			for (int j = 0; j < 32; j += 2) {
+				s0 += T == 32 ? (int)v[j] : T == 16 ? (int)(short)v[j] : (int)(signed char)v[j];
+				s1 += T == 32 ? (int)v[j + 1] : T == 16 ? (int)(short)v[j + 1] : (int)(signed char)v[j + 1];
+			}
+			const long long s = s0 + s1;
+			add_u128((unsigned long long)s, s < 0 ? -1ll : 0ll);
+		} else {
+			unsigned long long s0 = 0, s1 = 0;
+#pragma unroll
+			for (int j = 0; j < 32; j += 2) {
+				s0 += v[j];
+				s1 += v[j + 1];
+			}
+			add_u128(s0 + s1, 0);
+		}
+	}
+	// 64-bit values as (lo, hi) halves: low and high words are summed separately (4 independent chains), negatives are
+	// counted, and the vector's total enters the 128-bit partial once: sum = S_lo + (S_hi << 32) - (n_neg << 64).
+	__device__ __forceinline__ void add64(const uint32_t (&l)[32], const uint32_t (&h)[32], uint32_t is_signed, uint32_t is_float) {
+		cnt += 32;
+		if (is_float) {
+			double f0 = 0.0, f1 = 0.0;
+#pragma unroll
+			for (int j = 0; j < 32; j += 2) {
+				f0 += __longlong_as_double((long long)(((unsigned long long)h[j] << 32) | l[j]));
+				f1 += __longlong_as_double((long long)(((unsigned long long)h[j + 1] << 32) | l[j + 1]));
+			}
+			fs += f0 + f1;
+			return;
+		}
+		unsigned long long sl0 = 0, sl1 = 0, sh0 = 0, sh1 = 0;
+		uint32_t neg = 0;
+#pragma unroll
+		for (int j = 0; j < 32; j += 2) {
+			sl0 += l[j];
+			sl1 += l[j + 1];
+			sh0 += h[j];
+			sh1 += h[j + 1];
+			neg += (h[j] >> 31) + (h[j + 1] >> 31);
+		}
+		const unsigned long long sl = sl0 + sl1, sh = sh0 + sh1; // each < 2^37
+		add_u128(sl, 0);
+		add_u128(sh << 32, (long long)(sh >> 32) - (is_signed ? (long long)neg : 0ll));
 	}
 
 	// Warp reduction, then one set of atomics per warp.
@@ -291,9 +356,6 @@ struct AggPartial {
 			lo += olo;
 			hi += ohi + ((lo < olo) ? 1 : 0);
 			cnt += __shfl_down_sync(0xffffffffu, cnt, o);
-			const unsigned long long omin = __shfl_down_sync(0xffffffffu, kmin, o), omax = __shfl_down_sync(0xffffffffu, kmax, o);
-			kmin = omin < kmin ? omin : kmin;
-			kmax = omax > kmax ? omax : kmax;
 			fs += __shfl_down_sync(0xffffffffu, fs, o);
 		}
 		if (lane == 0 && cnt) {
@@ -304,8 +366,6 @@ struct AggPartial {
 				const unsigned long long old = atomicAdd(&acc->sum_lo, lo);
 				const unsigned long long carry = (old + lo < old) ? 1ull : 0ull;
 				atomicAdd(&acc->sum_hi, (unsigned long long)hi + carry);
-				atomicMin(&acc->key_min, kmin);
-				atomicMax(&acc->key_max, kmax);
 			}
 		}
 	}

@@ -13,9 +13,12 @@ constexpr uint32_t kFamLight = FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << 
 constexpr uint32_t kFamAlp = 1u << FLS_ENC_ALP;
 constexpr uint32_t kFamAlpRd = 1u << FLS_ENC_ALP_RD;
 
-template <int T, int OB, uint32_t FAM>
+// AGG + part != nullptr: register fast path of the fused aggregates — the vector is complete (n_valid == 1024) and has
+// no exceptions, so its values are folded into the partials straight from registers instead of being written anywhere.
+template <int T, int OB, uint32_t FAM, bool AGG>
 __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane,
-                                              uint32_t conv) {
+                                              uint32_t conv, AggPartial& part, bool agg_fast, uint32_t agg_signed, uint32_t agg_float) {
+	const bool fast = AGG && agg_fast;
 	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
 	constexpr uint32_t TMASK = T == 32 ? 0xffffffffu : ((1u << (T & 31)) - 1u);
 	if constexpr ((FAM & kFamLight) != 0) {
@@ -43,7 +46,7 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 			}
 			const int g0 = chain_l0(lane) >> 2; // 4 elements per 16-byte granule
 #pragma unroll
-			for (int q = 0; q < 8; ++q) {
+			for (int q = 0; q < 8 && !fast; ++q) {
 				*reinterpret_cast<uint4*>(stage + (size_t)swz<T>(g0 + q) * 16) =
 				    make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
 			}
@@ -58,7 +61,7 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 				}
 				const int g0 = chain_l0(2 * lane + h) >> 3; // 8 elements per granule
 #pragma unroll
-				for (int q = 0; q < 2; ++q) {
+				for (int q = 0; q < 2 && !fast; ++q) {
 					uint32_t w4[4];
 #pragma unroll
 					for (int m = 0; m < 4; ++m) {
@@ -76,12 +79,23 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 				for (int row = 0; row < 8; ++row) {
 					acc += v[4 * row + b] + base;
 					w2[row >> 2] |= (acc & 0xffu) << (8 * (row & 3));
+					if constexpr (AGG) {
+						v[4 * row + b] = acc & 0xffu;
+					}
 				}
 				const int l0 = chain_l0(4 * lane + b); // byte offset == element offset
-				*reinterpret_cast<uint2*>(stage + (size_t)swz<T>(l0 >> 4) * 16 + (l0 & 8)) = make_uint2(w2[0], w2[1]);
+				if (!fast) {
+					*reinterpret_cast<uint2*>(stage + (size_t)swz<T>(l0 >> 4) * 16 + (l0 & 8)) = make_uint2(w2[0], w2[1]);
+				}
 			}
 		}
 		(void)st32;
+		if constexpr (AGG) {
+			if (fast) {
+				part.template add32<T>(v, agg_signed, agg_float);
+				return;
+			}
+		}
 		__syncwarp();
 		copy_out_linear<T, OB, true>(stage, out_vec, lane, conv);
 		return;
@@ -123,13 +137,21 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 			v[j] = (v[j] + base) & TMASK;
 		}
 	}
+	if constexpr (AGG) {
+		if (fast) {
+			part.template add32<T>(v, agg_signed, agg_float);
+			return;
+		}
+	}
 	store_direct<T, OB>(out_vec, lane, v, conv);
 	patch_exceptions<T, OB>(out_vec, d, lane, conv, slot + packed);
 }
 
 // ---- T = 64 --------------------------------------------------------------------------------------------------------------
-template <uint32_t FAM>
-__device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane) {
+template <uint32_t FAM, bool AGG>
+__device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane,
+                                           AggPartial& part, bool agg_fast, uint32_t agg_signed, uint32_t agg_float) {
+	const bool fast = AGG && agg_fast;
 	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
 	if constexpr ((FAM & kFamLight) != 0) {
 		switch (enc) {
@@ -160,8 +182,23 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 			acc += (((uint64_t)hi[2 * q] << 32) | lo[2 * q]) + d.base;
 			const uint64_t a0 = acc;
 			acc += (((uint64_t)hi[2 * q + 1] << 32) | lo[2 * q + 1]) + d.base;
+			if constexpr (AGG) {
+				if (fast) { // keep the decoded values in the registers the deltas came from
+					lo[2 * q] = (uint32_t)a0;
+					hi[2 * q] = (uint32_t)(a0 >> 32);
+					lo[2 * q + 1] = (uint32_t)acc;
+					hi[2 * q + 1] = (uint32_t)(acc >> 32);
+					continue;
+				}
+			}
 			*reinterpret_cast<uint4*>(stage + (size_t)swz<64>(g0 + q) * 16) =
 			    make_uint4((uint32_t)a0, (uint32_t)(a0 >> 32), (uint32_t)acc, (uint32_t)(acc >> 32));
+		}
+		if constexpr (AGG) {
+			if (fast) {
+				part.add64(lo, hi, agg_signed, agg_float);
+				return;
+			}
 		}
 		__syncwarp();
 		copy_out_linear<64, 8, true>(stage, out_vec, lane, 0);
@@ -206,6 +243,12 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 	}
 	(void)blo;
 	(void)bhi;
+	if constexpr (AGG) {
+		if (fast) {
+			part.add64(lo, hi, agg_signed, agg_float);
+			return;
+		}
+	}
 	store_direct64(out_vec, lane, lo, hi);
 	patch_exceptions<64, 8>(out_vec, d, lane, 0, slot + packed);
 }
@@ -217,7 +260,7 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 // faster with one CTA of 8 warps and no spills (measured: profiles/r01_notes.md).
 template <int MODE, int T, bool AGG, uint32_t FAM>
 constexpr int min_ctas_per_sm() {
-	return (MODE == 0 && T == 64 && !AGG && FAM == kFamLight) ? 1 : FLS_MIN_CTAS;
+	return (MODE == 0 && T == 64 && (AGG || FAM == kFamLight)) ? 1 : FLS_MIN_CTAS;
 }
 
 // AGG: the vector is decoded into the warp's shared-memory tile (FLS_SINK_SHARED translation unit) and folded into
@@ -289,19 +332,25 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			const uint64_t vk = (((run0 + ((uint32_t)k >> cs)) * n_warps + gw) << cs) + ((uint32_t)k & cmask);
 			uint8_t* out_vec = AGG ? tile : out + (size_t)vk * 1024u * OB;
 			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
+			// aggregate fast path: complete vector, no exceptions, an encoding whose values end up in registers
+			const uint32_t enc_k = d.misc >> 24;
+			const bool agg_fast = AGG && MODE == 0 && (d.vec_in_chunk >> 16) == 1024u && (d.misc & 0xffffu) == 0u &&
+			                      enc_k != FLS_ENC_UNCOMPRESSED && enc_k != FLS_ENC_CONSTANT && enc_k != FLS_ENC_CROSS_RLE;
 			if constexpr (MODE == 1) {
 				process_dict<T, VT, OB>(d, sp, out_vec, lane, L.conv);
 			} else if constexpr (MODE == 2) {
 				process_rle<VT, OB>(d, sp, stage, out_vec, lane, L.conv);
 			} else if constexpr (T == 64) {
-				process_64<FAM>(d, sp, stage, out_vec, lane);
+				process_64<FAM, AGG>(d, sp, stage, out_vec, lane, part, agg_fast, L.agg_signed, L.agg_float);
 			} else {
-				process_small<T, OB, FAM>(d, sp, stage, out_vec, lane, L.conv);
+				process_small<T, OB, FAM, AGG>(d, sp, stage, out_vec, lane, L.conv, part, agg_fast, L.agg_signed, L.agg_float);
 			}
 			__syncwarp(); // all lanes are done reading the slot (and the staging area)
 			if constexpr (AGG) {
-				part.template fold<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float);
-				__syncwarp();
+				if (!agg_fast) {
+					part.template fold<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float);
+					__syncwarp();
+				}
 			}
 			if (to_issue) {
 				const int kn = __ffs(to_issue) - 1;

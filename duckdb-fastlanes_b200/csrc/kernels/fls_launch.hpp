@@ -18,7 +18,8 @@ const void* fls_kernel_agg(int mode, int T, int VT, int fam);
 #include <cuda_runtime.h>
 #endif
 #if defined(__CUDACC__) || defined(CUDART_VERSION)
-cudaError_t fls_agg_finalize(flsgpu_agg_acc* acc, uint32_t is_signed, cudaStream_t stream);
+cudaError_t fls_agg_finalize(flsgpu_agg_acc* acc, uint32_t is_signed, unsigned long long key_min, unsigned long long key_max,
+                             cudaStream_t stream);
 cudaError_t fls_agg_reset(flsgpu_agg_acc* acc, cudaStream_t stream);
 #endif
 

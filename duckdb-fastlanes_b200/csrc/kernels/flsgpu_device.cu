@@ -337,7 +337,10 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	const uint32_t per_warp_budget = 13u * 1024u;
 	const uint32_t fixed = L.stage_bytes + tile_bytes; // per-warp bytes besides the pipeline slots
 	uint32_t n_slots = fixed < per_warp_budget ? (per_warp_budget - fixed) / L.slot_bytes : 0;
-	n_slots = std::max(2u, std::min(6u, n_slots));
+	// never fewer than ~4 KiB of blobs in flight per warp: a bulk copy takes about a microsecond to land, and narrow
+	// vectors (a few hundred bytes) are decoded much faster than that
+	n_slots = std::max(n_slots, std::min(8u, 4096u / L.slot_bytes));
+	n_slots = std::max(2u, std::min(8u, n_slots));
 	L.n_slots = n_slots;
 	uint32_t wpc = kFlsWarpsPerCta, smem = 0;
 	for (;; wpc >>= 1) { // wide vectors (8 KiB blobs + staging + aggregate tile) may need a smaller CTA to fit 227 KiB
@@ -787,7 +790,20 @@ int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, ui
 	if (rc) {
 		return rc;
 	}
-	FLS_CUDA(fls_agg_finalize(acc, t->columns[col].is_signed, s));
+	// MIN / MAX come from the chunks' zone maps (exact, written from the data: reference row_group_statistics.cpp:60-127);
+	// integer columns only, as order keys (value ^ sign bit) so that signed and unsigned columns merge the same way
+	unsigned long long key_min = ~0ull, key_max = 0ull;
+	if (!t->columns[col].is_float) {
+		const unsigned long long flip = t->columns[col].is_signed ? 0x8000000000000000ull : 0ull;
+		for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+			const fls_chunk_desc& c = t->chunk(r, col);
+			if (c.has_stats) {
+				key_min = std::min<unsigned long long>(key_min, c.min_val ^ flip);
+				key_max = std::max<unsigned long long>(key_max, c.max_val ^ flip);
+			}
+		}
+	}
+	FLS_CUDA(fls_agg_finalize(acc, t->columns[col].is_signed, key_min, key_max, s));
 	return FLSGPU_OK;
 }
 

@@ -30,8 +30,11 @@ const void* fls_kernel_agg(int mode, int T, int VT, int fam) {
 }
 
 // min_val / max_val of the public result are written from the order keys after every aggregate launch.
-__global__ void fls_agg_finalize_kernel(flsgpu_agg_acc* acc, uint32_t is_signed) {
+__global__ void fls_agg_finalize_kernel(flsgpu_agg_acc* acc, uint32_t is_signed, unsigned long long key_min, unsigned long long key_max) {
 	const unsigned long long flip = is_signed ? 0x8000000000000000ull : 0ull;
+	// merge the zone-map extremes of the chunks this call covered (order keys: value ^ sign bit)
+	acc->key_min = key_min < acc->key_min ? key_min : acc->key_min;
+	acc->key_max = key_max > acc->key_max ? key_max : acc->key_max;
 	if (acc->count && acc->key_min <= acc->key_max) {
 		acc->min_val = (long long)(acc->key_min ^ flip);
 		acc->max_val = (long long)(acc->key_max ^ flip);
@@ -46,8 +49,9 @@ __global__ void fls_agg_reset_kernel(flsgpu_agg_acc* acc) {
 	acc->key_max = 0ull;
 }
 
-cudaError_t fls_agg_finalize(flsgpu_agg_acc* acc, uint32_t is_signed, cudaStream_t stream) {
-	fls_agg_finalize_kernel<<<1, 1, 0, stream>>>(acc, is_signed);
+cudaError_t fls_agg_finalize(flsgpu_agg_acc* acc, uint32_t is_signed, unsigned long long key_min, unsigned long long key_max,
+                             cudaStream_t stream) {
+	fls_agg_finalize_kernel<<<1, 1, 0, stream>>>(acc, is_signed, key_min, key_max);
 	return cudaGetLastError();
 }
 
