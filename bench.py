@@ -248,9 +248,10 @@ def kernel_name(t, col):
         ch = t.chunk(r, col)
         e = flsgpu.ENC_NAME[ch.encoding]
         encs.add(e)
-        fams.add("dict%d" % ch.idx_bits if e == "DICT" else "rle" if e == "RLE" else "alp" if e == "ALP" else "alprd" if e == "ALP_RD" else "light")
+        fams.add("dict%d" % ch.idx_bits if e == "DICT" else "rle" if e == "RLE" else "alp" if e == "ALP" else "alprd" if e == "ALP_RD"
+                 else "delta" if e == "DELTA" and ch.phys_bits == 64 else "light")
     T = t.column(col).phys_bits
-    fams = sorted(fams)
+    fams = sorted(fams)  # "delta": 64-bit DELTA chunks have their own instantiation
     if len(fams) == 1:
         return f"fls_decode_kernel<{fams[0]},T={T}>", sorted(encs), 1
     return f"mixed({'+'.join(fams)}),T={T}", sorted(encs), len(fams)

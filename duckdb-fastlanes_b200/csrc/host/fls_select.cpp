@@ -253,7 +253,21 @@ static bool encode_typed(const ColumnType& type, const void* values, uint32_t n_
 	case FLS_ENC_FFOR:
 	case FLS_ENC_SLPATCH:
 	case FLS_ENC_FREQUENCY: encode_ffor_family<U>(c, enc, out); return true;
-	case FLS_ENC_DELTA: encode_delta<U>(c, out); return true;
+	case FLS_ENC_DELTA:
+		// The padding of a partial last vector is never exposed (n_valid).  For DELTA, continue the last step of the data
+		// instead of repeating the last value when the data ends on a constant step: a sorted / arithmetic column then
+		// keeps its delta width in the tail vector (a repeated value puts a 0 delta among constant non-zero deltas, and one
+		// wide vector sizes the decoder's shared-memory slots for the whole launch).
+		if (!padded.empty() && n_tuples % kVec >= 3) {
+			const U step = (U)(padded[n_tuples - 1] - padded[n_tuples - 2]);
+			if (step != 0 && step == (U)(padded[n_tuples - 2] - padded[n_tuples - 3])) {
+				for (size_t i = n_tuples; i < (size_t)n_vec * kVec; ++i) {
+					padded[i] = (U)(padded[i - 1] + step);
+				}
+			}
+		}
+		encode_delta<U>(c, out);
+		return true;
 	case FLS_ENC_DICT: return encode_dict<U>(c, out);
 	case FLS_ENC_RLE: return encode_rle<U>(c, out);
 	case FLS_ENC_CROSS_RLE: encode_cross_rle<U>(c, out); return true;

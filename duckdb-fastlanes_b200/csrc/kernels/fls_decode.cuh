@@ -65,19 +65,38 @@ struct VecDesc {
 	uint32_t aux_n;      // ch->aux_count (#keys, #runs)
 };
 
-__device__ __forceinline__ VecDesc shfl_desc(const VecDesc& d, int src) {
+// A batch's 32 descriptors live in the warp's shared memory (64 B each): lane k stores the one it fetched, every lane
+// then reads descriptor k with broadcast loads (same address across the warp = one wavefront) and only the fields the
+// instantiation uses.  (Broadcasting through shuffles kept ~18 registers live per thread across the whole decode body;
+// ptxas spilled them to local memory: 16 SHFL + ~12 LDL/STL per vector.)
+constexpr uint32_t kDescBytes = 64, kDescBytesPerWarp = 32 * kDescBytes;
+static_assert(kDescBytesPerWarp == FLS_DESC_BYTES_PER_WARP, "launcher and kernel disagree on the descriptor area");
+
+__device__ __forceinline__ void store_desc(uint8_t* descs, int lane, const VecDesc& d) {
+	uint4* p = reinterpret_cast<uint4*>(descs + (size_t)lane * kDescBytes);
+	const unsigned long long blob = (unsigned long long)d.blob, ch = (unsigned long long)d.ch;
+	const unsigned long long a0 = (unsigned long long)d.aux0, a1 = (unsigned long long)d.aux1;
+	p[0] = make_uint4((uint32_t)blob, (uint32_t)(blob >> 32), (uint32_t)d.base, (uint32_t)(d.base >> 32));
+	p[1] = make_uint4(d.bytes, d.misc, d.misc2, d.vec_in_chunk);
+	p[2] = make_uint4((uint32_t)a0, (uint32_t)(a0 >> 32), (uint32_t)a1, (uint32_t)(a1 >> 32));
+	p[3] = make_uint4((uint32_t)ch, (uint32_t)(ch >> 32), d.aux_off, d.aux_n);
+}
+
+__device__ __forceinline__ VecDesc load_desc(const uint8_t* descs, int k) {
+	const uint4* p = reinterpret_cast<const uint4*>(descs + (size_t)k * kDescBytes);
+	const uint4 q0 = p[0], q1 = p[1], q2 = p[2], q3 = p[3];
 	VecDesc r;
-	r.blob = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)d.blob, src);
-	r.ch = (const FlsChunkDev*)__shfl_sync(0xffffffffu, (unsigned long long)d.ch, src);
-	r.base = __shfl_sync(0xffffffffu, (unsigned long long)d.base, src);
-	r.aux_off = __shfl_sync(0xffffffffu, d.aux_off, src);
-	r.bytes = __shfl_sync(0xffffffffu, d.bytes, src);
-	r.misc = __shfl_sync(0xffffffffu, d.misc, src);
-	r.misc2 = __shfl_sync(0xffffffffu, d.misc2, src);
-	r.vec_in_chunk = __shfl_sync(0xffffffffu, d.vec_in_chunk, src);
-	r.aux0 = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)d.aux0, src);
-	r.aux1 = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)d.aux1, src);
-	r.aux_n = __shfl_sync(0xffffffffu, d.aux_n, src);
+	r.blob = (const uint8_t*)(((unsigned long long)q0.y << 32) | q0.x);
+	r.base = ((unsigned long long)q0.w << 32) | q0.z;
+	r.bytes = q1.x;
+	r.misc = q1.y;
+	r.misc2 = q1.z;
+	r.vec_in_chunk = q1.w;
+	r.aux0 = (const uint8_t*)(((unsigned long long)q2.y << 32) | q2.x);
+	r.aux1 = (const uint8_t*)(((unsigned long long)q2.w << 32) | q2.z);
+	r.ch = (const FlsChunkDev*)(((unsigned long long)q3.y << 32) | q3.x);
+	r.aux_off = q3.z;
+	r.aux_n = q3.w;
 	return r;
 }
 
@@ -157,6 +176,7 @@ __device__ __forceinline__ void patch_exceptions(uint8_t* out_vec, const VecDesc
 	}
 	__syncwarp();
 	const uint16_t* pos = reinterpret_cast<const uint16_t*>(tail + FLS_PAD16(n * (T / 8u)));
+#pragma unroll 1
 	for (uint32_t k = lane; k < n; k += 32) {
 		uint32_t lo, hi = 0;
 		if constexpr (T == 8) {
@@ -216,6 +236,7 @@ __device__ __forceinline__ void decode_cross_rle(uint8_t* out_vec, const VecDesc
 		}
 	}
 	const uint32_t r_first = lo_r;
+#pragma unroll 1
 	for (int it = 0; it < 32; ++it) {
 		const uint32_t gi = g0 + it * 32 + lane;
 		uint32_t a = r_first, b = min(n_runs, r_first + 1025u);

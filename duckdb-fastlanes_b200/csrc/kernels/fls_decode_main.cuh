@@ -12,6 +12,10 @@ namespace FLS_NS {
 constexpr uint32_t kFamLight = FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD));
 constexpr uint32_t kFamAlp = 1u << FLS_ENC_ALP;
 constexpr uint32_t kFamAlpRd = 1u << FLS_ENC_ALP_RD;
+// T = 64 only: DELTA gets its own instantiation.  With DELTA and the FFOR family in one kernel the compiler folds the four
+// switch(W) dispatches (two phases each) into one and needs > 200 registers; apart they fit 128 with no spills.
+constexpr uint32_t kFamDelta = 1u << FLS_ENC_DELTA;
+constexpr uint32_t kFamLight64 = kFamLight & ~kFamDelta;
 
 // AGG + part != nullptr: register fast path of the fused aggregates — the vector is complete (n_valid == 1024) and has
 // no exceptions, so its values are folded into the partials straight from registers instead of being written anywhere.
@@ -253,14 +257,168 @@ __device__ __forceinline__ void process_64(const VecDesc& d, const uint8_t* slot
 	patch_exceptions<64, 8>(out_vec, d, lane, 0, slot + packed);
 }
 
+// ---- T = 64, materialising kernels: two phases of 16 rows -------------------------------------------------------------
+// A thread owns 32 rows of a half lane; decoding them in two phases of 16 keeps 16 instead of 32 (lo, hi) pairs (and
+// half the packed words) live, so the kernel fits 128 registers and two CTAs (16 warps) stay resident per SM: the
+// single-phase body needed ~200 registers = 8 warps per SM, and was latency bound (ncu: 2 warps per scheduler, stall
+// "wait" + "short scoreboard" ~3.5 per issue).
+template <int J0>
+__device__ __forceinline__ void delta64_phase(uint32_t W, const uint32_t* pe, const uint32_t* po, uint64_t base, uint64_t& acc,
+                                              uint8_t* stage, int g0) {
+	uint32_t lo[16], hi[16];
+	unpack_64_part_dispatch<J0>((int)W, pe, po, lo, hi);
+#pragma unroll
+	for (int q = 0; q < 8; ++q) {
+#ifdef FLS_DELTA64_PAIRS
+		// pair sums: the serial chain is 8 additions long instead of 16
+		const uint64_t first = ((((uint64_t)hi[2 * q]) << 32) | lo[2 * q]) + base;
+		const uint64_t pair = first + ((((uint64_t)hi[2 * q + 1]) << 32) | lo[2 * q + 1]) + base;
+		const uint64_t a0 = acc + first;
+		acc += pair;
+#else
+		acc += ((((uint64_t)hi[2 * q]) << 32) | lo[2 * q]) + base;
+		const uint64_t a0 = acc;
+		acc += ((((uint64_t)hi[2 * q + 1]) << 32) | lo[2 * q + 1]) + base;
+#endif
+		*reinterpret_cast<uint4*>(stage + (size_t)swz<64>(g0 + J0 / 2 + q) * 16) =
+		    make_uint4((uint32_t)a0, (uint32_t)(a0 >> 32), (uint32_t)acc, (uint32_t)(acc >> 32));
+	}
+}
+
+struct Ffor64Ctx {
+	const uint32_t *pe, *po;   // packed values (right parts for ALP_RD)
+	const uint32_t *pe2, *po2; // ALP_RD left codes
+	uint64_t base;
+	double fa, fr;             // ALP
+	uint32_t dw[4];            // ALP_RD dictionary
+	uint32_t W, W2;
+};
+
+template <uint32_t FAM, int J0>
+__device__ __forceinline__ void ffor64_phase(const Ffor64Ctx& c, uint32_t enc, uint8_t* out_vec, int lane) {
+	uint32_t lo[16], hi[16];
+	unpack_64_part_dispatch<J0>((int)c.W, c.pe, c.po, lo, hi);
+	if ((FAM & kFamAlp) != 0 && (FAM == kFamAlp || enc == FLS_ENC_ALP)) { // (double)digit * (double)FACT[f] * FRAC[e]
+#pragma unroll
+		for (int j = 0; j < 16; ++j) {
+			const uint64_t u = ((((uint64_t)hi[j]) << 32) | lo[j]) + c.base;
+			const double x = __dmul_rn(__dmul_rn(__ll2double_rn((long long)u), c.fa), c.fr);
+			const long long b = __double_as_longlong(x);
+			lo[j] = (uint32_t)b;
+			hi[j] = (uint32_t)(b >> 32);
+		}
+	} else if ((FAM & kFamAlpRd) != 0 && (FAM == kFamAlpRd || enc == FLS_ENC_ALP_RD)) {
+		uint32_t llo[16], lhi[16];
+		unpack_64_part_dispatch<J0>((int)c.W2, c.pe2, c.po2, llo, lhi);
+#pragma unroll
+		for (int j = 0; j < 16; ++j) {
+			const uint32_t code = llo[j] & 7u;
+			const uint32_t pair = code < 4 ? (code < 2 ? c.dw[0] : c.dw[1]) : (code < 6 ? c.dw[2] : c.dw[3]);
+			const uint64_t key = (code & 1u) ? (pair >> 16) : (pair & 0xffffu);
+			const uint64_t u = ((((uint64_t)hi[j]) << 32) | lo[j]) | (key << c.W);
+			lo[j] = (uint32_t)u;
+			hi[j] = (uint32_t)(u >> 32);
+		}
+		(void)lhi;
+	} else {
+#pragma unroll
+		for (int j = 0; j < 16; ++j) {
+			const uint64_t u = ((((uint64_t)hi[j]) << 32) | lo[j]) + c.base;
+			lo[j] = (uint32_t)u;
+			hi[j] = (uint32_t)(u >> 32);
+		}
+	}
+#pragma unroll
+	for (int j = 0; j < 16; ++j) {
+		st_cs_v2(out_vec + (size_t)value_pos<64>(lane, J0 + j) * 8, lo[j], hi[j]);
+	}
+}
+
+template <uint32_t FAM>
+__device__ __forceinline__ void process_64_2ph(const VecDesc& d, const uint8_t* slot, uint8_t* stage, uint8_t* out_vec, int lane) {
+	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
+	if constexpr ((FAM & kFamLight64) != 0) {
+		switch (enc) {
+		case FLS_ENC_UNCOMPRESSED: copy_out_linear<64, 8, false>(slot, out_vec, lane, 0); return;
+		case FLS_ENC_CONSTANT:
+			fill_constant<64, 8>(out_vec, lane, (uint32_t)d.base, (uint32_t)(d.base >> 32), 0);
+			return;
+		case FLS_ENC_CROSS_RLE: decode_cross_rle<64, 8>(out_vec, d, lane, 0); return;
+		default: break;
+		}
+	}
+	const uint32_t* s32 = reinterpret_cast<const uint32_t*>(slot);
+	if ((FAM & kFamDelta) != 0 && (FAM == kFamDelta || enc == FLS_ENC_DELTA)) {
+		// thread (l = lane&15, h = lane>>4) owns rows 32h..32h+31 of lane l = 32 logically consecutive values.  The second
+		// half starts its running sum at 0; the first half's end value (totals[l]) is added while the vector is copied out
+		const uint32_t *pe, *po;
+		stream64_bases(s32 + 32, lane, (int)W, pe, po);
+		const int h = lane >> 4;
+		uint64_t acc = h ? 0ull : reinterpret_cast<const uint64_t*>(slot)[lane & 15];
+		const int g0 = (chain_l0(lane & 15) + 32 * h) >> 1; // 2 elements per granule
+		uint64_t* totals = reinterpret_cast<uint64_t*>(stage + 8192);
+		delta64_phase<0>(W, pe, po, d.base, acc, stage, g0);
+		delta64_phase<16>(W, pe, po, d.base, acc, stage, g0);
+		if (!h) {
+			totals[lane] = acc;
+		}
+		__syncwarp();
+		// copy-out in two batches of 8 granules per thread: all loads of a batch are issued before its stores so that
+		// eight 16-byte stores per thread are in flight (a load -> add -> store chain per granule recycles three
+		// register quads and stalls on the store's source registers: ncu long-scoreboard on the copy-out)
+#pragma unroll
+		for (int half = 0; half < 2; ++half) {
+			uint4 q[8];
+			uint64_t add[8];
+#pragma unroll
+			for (int j = 0; j < 8; ++j) { // granule g = it*32 + lane: FastLanes lane `it`, half `h`
+				const int it = half * 8 + j;
+				q[j] = *reinterpret_cast<const uint4*>(stage + (size_t)swz<64>(it * 32 + lane) * 16);
+				add[j] = h ? totals[it] : 0ull;
+			}
+#pragma unroll
+			for (int j = 0; j < 8; ++j) {
+				const int it = half * 8 + j;
+				const uint64_t a = ((((uint64_t)q[j].y) << 32) | q[j].x) + add[j], b = ((((uint64_t)q[j].w) << 32) | q[j].z) + add[j];
+				st_cs_v4(out_vec + (size_t)(it * 32 + lane) * 16, (uint32_t)a, (uint32_t)(a >> 32), (uint32_t)b, (uint32_t)(b >> 32));
+			}
+		}
+		return;
+	}
+	if constexpr (FAM != kFamDelta) {
+	Ffor64Ctx c;
+	c.W = W;
+	c.W2 = d.misc2 & 0xffu;
+	c.base = d.base;
+	stream64_bases(s32, lane, (int)W, c.pe, c.po);
+	uint32_t packed = 128u * W; // bytes of the packed part; the exception tail follows
+	if ((FAM & kFamAlp) != 0 && (FAM == kFamAlp || enc == FLS_ENC_ALP)) {
+		c.fa = c_fact_d[(d.misc2 >> 16) & 0xffu];
+		c.fr = c_frac_d[(d.misc2 >> 8) & 0xffu];
+	}
+	if ((FAM & kFamAlpRd) != 0 && (FAM == kFamAlpRd || enc == FLS_ENC_ALP_RD)) {
+		const uint4 dq = __ldg(reinterpret_cast<const uint4*>(d.ch->rd_dict));
+		c.dw[0] = dq.x;
+		c.dw[1] = dq.y;
+		c.dw[2] = dq.z;
+		c.dw[3] = dq.w;
+		stream64_bases(s32 + 32 * W, lane, (int)c.W2, c.pe2, c.po2);
+		packed += 128u * c.W2;
+	}
+	ffor64_phase<FAM, 0>(c, enc, out_vec, lane);
+	ffor64_phase<FAM, 16>(c, enc, out_vec, lane);
+	patch_exceptions<64, 8>(out_vec, d, lane, 0, slot + packed);
+	}
+}
+
 // ---- the persistent kernel -----------------------------------------------------------------------------------------------
 // MODE 0: main family (T = physical lane width = VT); MODE 1: DICT (T = code lane width, VT = key width);
 // MODE 2: RLE (T = 16: run-index lanes, VT = value width).
-// Register budget: two resident CTAs per SM (<= 128 registers) everywhere except the 64-bit integer kernel, which is
-// faster with one CTA of 8 warps and no spills (measured: profiles/r01_notes.md).
+// Register budget: two resident CTAs per SM (<= 128 registers) everywhere except the 64-bit fused-aggregate kernel, which
+// keeps all 32 (lo, hi) pairs of a thread in registers (one CTA of 8 warps, no spills).
 template <int MODE, int T, bool AGG, uint32_t FAM>
 constexpr int min_ctas_per_sm() {
-	return (MODE == 0 && T == 64 && (AGG || FAM == kFamLight)) ? 1 : FLS_MIN_CTAS;
+	return (MODE == 0 && T == 64 && AGG) ? 1 : FLS_MIN_CTAS;
 }
 
 // AGG: the vector is decoded into the warp's shared-memory tile (FLS_SINK_SHARED translation unit) and folded into
@@ -274,8 +432,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 	uint64_t* bars = reinterpret_cast<uint64_t*>(smem) + warp * n_slots;
 	const uint32_t bar_bytes = (wpc * n_slots * 8 + 127u) & ~127u;
 	constexpr uint32_t kTileBytes = AGG ? 1024u * OB : 0u;
-	const uint32_t warp_bytes = n_slots * L.slot_bytes + L.stage_bytes + kTileBytes;
-	uint8_t* slots = smem + bar_bytes + (size_t)warp * warp_bytes;
+	const uint32_t warp_bytes = kDescBytesPerWarp + n_slots * L.slot_bytes + L.stage_bytes + kTileBytes;
+	uint8_t* descs = smem + bar_bytes + (size_t)warp * warp_bytes;
+	uint8_t* slots = descs + kDescBytesPerWarp;
 	uint8_t* stage = slots + (size_t)n_slots * L.slot_bytes;
 	uint8_t* tile = stage + L.stage_bytes;
 	AggPartial part;
@@ -304,26 +463,52 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			break;
 		}
 		const uint64_t my_v64 = (((run0 + ((uint32_t)lane >> cs)) * n_warps + gw) << cs) + ((uint32_t)lane & cmask);
-		const VecDesc mine = fetch_desc<T, VT>(L, my_v64 < L.total_vecs ? (uint32_t)my_v64 : 0xffffffffu);
-		uint32_t todo = __ballot_sync(0xffffffffu, mine.ch != nullptr);
+		uint32_t todo;
+		{
+			const VecDesc mine = fetch_desc<T, VT>(L, my_v64 < L.total_vecs ? (uint32_t)my_v64 : 0xffffffffu);
+			store_desc(descs, lane, mine);
+			todo = __ballot_sync(0xffffffffu, mine.ch != nullptr);
+			// The blobs of the NEXT batch (all 32 at once; for the first batch also its own) are requested into L2 now, in
+			// one burst, instead of trickling out of HBM one pipeline slot at a time: a write stream with a trickle of
+			// small reads in it loses ~12 % of its bandwidth to DRAM read/write turnarounds (tools/membw.cu: 6.2 -> 5.4
+			// TB/s with 256 B read per 8 KiB written), and the warps of a launch run in near lock step, so the bursts of
+			// all warps coincide.  The next batch's descriptor is fetched again when the batch starts (L1/L2 hits).
+			if (L.prefetch) {
+				if (it == 0 && mine.bytes) {
+					tma_prefetch_l2(mine.blob, mine.bytes);
+				}
+				const uint64_t nx_v64 = my_v64 + (((uint64_t)runs_per_batch * n_warps) << cs);
+				if (nx_v64 < L.total_vecs) {
+					const VecDesc nxt = fetch_desc<T, VT>(L, (uint32_t)nx_v64);
+					if (nxt.bytes) {
+						tma_prefetch_l2(nxt.blob, nxt.bytes);
+					}
+				}
+			}
+		}
+		__syncwarp();
 		uint32_t to_issue = todo;
 		// prologue: fill the pipeline
-		uint32_t slot_i = n_done % n_slots;
-		for (uint32_t s = 0; s < n_slots && to_issue; ++s) {
-			const int k = __ffs(to_issue) - 1;
-			to_issue &= to_issue - 1;
-			const uint8_t* src = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)mine.blob, k);
-			const uint32_t bytes = __shfl_sync(0xffffffffu, mine.bytes, k);
-			if (lane == 0 && bytes) {
-				mbar_expect_tx(bars + slot_i, bytes);
-				tma_load_1d(slots + (size_t)slot_i * L.slot_bytes, src, bytes, bars + slot_i);
+		if (lane == 0) {
+			uint32_t slot_i = n_done % n_slots;
+			for (uint32_t s = 0; s < n_slots && to_issue; ++s) {
+				const int k = __ffs(to_issue) - 1;
+				to_issue &= to_issue - 1;
+				const uint4 q0 = *reinterpret_cast<const uint4*>(descs + (size_t)k * kDescBytes);
+				const uint32_t bytes = *reinterpret_cast<const uint32_t*>(descs + (size_t)k * kDescBytes + 16);
+				if (bytes) {
+					mbar_expect_tx(bars + slot_i, bytes);
+					tma_load_1d(slots + (size_t)slot_i * L.slot_bytes, (const void*)(((unsigned long long)q0.y << 32) | q0.x), bytes,
+					            bars + slot_i);
+				}
+				slot_i = slot_i + 1 == n_slots ? 0 : slot_i + 1;
 			}
-			slot_i = slot_i + 1 == n_slots ? 0 : slot_i + 1;
 		}
+		to_issue = __shfl_sync(0xffffffffu, to_issue, 0);
 		while (todo) {
 			const int k = __ffs(todo) - 1;
 			todo &= todo - 1;
-			const VecDesc d = shfl_desc(mine, k);
+			const VecDesc d = load_desc(descs, k);
 			const uint32_t slot = n_done % n_slots;
 			if (d.bytes) {
 				mbar_wait(bars + slot, (phases >> slot) & 1u);
@@ -340,6 +525,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 				process_dict<T, VT, OB>(d, sp, out_vec, lane, L.conv);
 			} else if constexpr (MODE == 2) {
 				process_rle<VT, OB>(d, sp, stage, out_vec, lane, L.conv);
+			} else if constexpr (T == 64 && !AGG) {
+				process_64_2ph<FAM>(d, sp, stage, out_vec, lane);
 			} else if constexpr (T == 64) {
 				process_64<FAM, AGG>(d, sp, stage, out_vec, lane, part, agg_fast, L.agg_signed, L.agg_float);
 			} else {
@@ -355,11 +542,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			if (to_issue) {
 				const int kn = __ffs(to_issue) - 1;
 				to_issue &= to_issue - 1;
-				const uint8_t* src = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)mine.blob, kn);
-				const uint32_t bytes = __shfl_sync(0xffffffffu, mine.bytes, kn);
-				if (lane == 0 && bytes) {
-					mbar_expect_tx(bars + slot, bytes);
-					tma_load_1d(slots + (size_t)slot * L.slot_bytes, src, bytes, bars + slot);
+				if (lane == 0) {
+					const uint4 q0 = *reinterpret_cast<const uint4*>(descs + (size_t)kn * kDescBytes);
+					const uint32_t bytes = *reinterpret_cast<const uint32_t*>(descs + (size_t)kn * kDescBytes + 16);
+					if (bytes) {
+						mbar_expect_tx(bars + slot, bytes);
+						tma_load_1d(slots + (size_t)slot * L.slot_bytes, (const void*)(((unsigned long long)q0.y << 32) | q0.x), bytes,
+						            bars + slot);
+					}
 				}
 			}
 			++n_done;

@@ -42,12 +42,16 @@ struct FlsLaunch {
 	uint32_t family_mask;      // bit e set: this kernel handles encoding e
 	uint32_t run_shift;        // log2 of the run of consecutive vectors a warp takes (0..5)
 	uint32_t idx_bits;         // DICT launches: only chunks whose codes sit in idx_bits-wide lanes (0: any)
+	uint32_t prefetch;         // 1: request a batch's 32 blobs into L2 at batch start (materialising launches)
 	void* out;
 	// fused aggregate launches (flsgpu_aggregate_column): out is unused, partials are folded into *agg
 	flsgpu_agg_acc* agg;
 	uint32_t agg_signed; // integer columns: 1 = two's complement values
 	uint32_t agg_float;  // 1 = FLOAT/DOUBLE column (fsum + count only)
 };
+
+// Per-warp shared memory holding the 32 vector descriptors of a batch (64 B each), in front of the pipeline slots.
+#define FLS_DESC_BYTES_PER_WARP 2048u
 
 // Encoding families (which kernel template handles which fls_encoding)
 #define FLS_FAMILY_MAIN                                                                                                \

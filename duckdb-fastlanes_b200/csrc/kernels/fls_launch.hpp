@@ -5,7 +5,7 @@
 #include "fls_device.h"
 
 // MODE 0 (T-lane encodings): T = column physical bits, OB = output bytes per value (>= T/8).
-// fam: 0 = light (integer encodings), 1 = ALP, 2 = ALP_RD
+// fam: 0 = light (integer encodings), 1 = ALP, 2 = ALP_RD, 3 = DELTA of 64-bit columns (own instantiation)
 const void* fls_kernel_main(int T, int OB, int fam);
 // MODE 1 (DICT): IT = code lane bits (8/16/32), VT = key bits, OB = output bytes (>= VT/8).
 const void* fls_kernel_dict(int IT, int VT, int OB);

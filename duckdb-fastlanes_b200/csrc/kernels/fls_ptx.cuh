@@ -51,6 +51,11 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
 	             : "memory");
 }
 
+// TMA prefetch of a byte range into L2 (no shared-memory destination, nothing to wait for).
+__device__ __forceinline__ void tma_prefetch_l2(const void* gmem_src, uint32_t bytes) {
+	asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
+
 #if defined(FLS_SINK_SHARED)
 // Aggregate kernels: the "output vector" is the warp's shared-memory tile (generic pointer into shared memory).
 __device__ __forceinline__ void st_cs_u32(void* p, uint32_t a) {

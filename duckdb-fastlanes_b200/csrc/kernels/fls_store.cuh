@@ -117,17 +117,31 @@ template <int T, int OB, bool SWZ>
 __device__ __forceinline__ void copy_out_linear(const uint8_t* smem, uint8_t* out_vec, int tid, uint32_t conv) {
 	constexpr int N_IT = T / 4;        // 1024*T/8 bytes / 16 / 32
 	constexpr int PER = 128 / T;       // elements per granule
+	if constexpr (T == 64 || OB * 8 == T) {
+		// same-width copy: all loads of a batch (<= 8 granules per thread) are issued before its stores, so that the stores
+		// do not wait one by one for a recycled register quad
+		constexpr int B = N_IT < 8 ? N_IT : 8;
 #pragma unroll
-	for (int it = 0; it < N_IT; ++it) {
-		const int g = it * 32 + tid;
-		const uint4 q = *reinterpret_cast<const uint4*>(smem + (size_t)(SWZ ? swz<T>(g) : g) * 16);
-		const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-		const int e0 = g * PER;
-		if constexpr (T == 64) {
-			st_cs_v4(out_vec + (size_t)e0 * 8, w[0], w[1], w[2], w[3]);
-		} else if constexpr (OB * 8 == T) {
-			st_cs_v4(out_vec + (size_t)e0 * OB, w[0], w[1], w[2], w[3]);
-		} else {
+		for (int b0 = 0; b0 < N_IT; b0 += B) {
+			uint4 q[B];
+#pragma unroll
+			for (int j = 0; j < B; ++j) {
+				const int g = (b0 + j) * 32 + tid;
+				q[j] = *reinterpret_cast<const uint4*>(smem + (size_t)(SWZ ? swz<T>(g) : g) * 16);
+			}
+#pragma unroll
+			for (int j = 0; j < B; ++j) {
+				const int g = (b0 + j) * 32 + tid;
+				st_cs_v4(out_vec + (size_t)g * 16, q[j].x, q[j].y, q[j].z, q[j].w);
+			}
+		}
+	} else {
+#pragma unroll
+		for (int it = 0; it < N_IT; ++it) {
+			const int g = it * 32 + tid;
+			const uint4 q = *reinterpret_cast<const uint4*>(smem + (size_t)(SWZ ? swz<T>(g) : g) * 16);
+			const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+			const int e0 = g * PER;
 			constexpr int PW = 32 / T; // elements per 32-bit word
 #pragma unroll
 			for (int k = 0; k < 4; ++k) {

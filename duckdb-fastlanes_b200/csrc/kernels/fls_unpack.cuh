@@ -150,6 +150,60 @@ FLS_HD void unpack_64(const uint32_t* pe, const uint32_t* po, uint32_t (&lo)[32]
 	}
 }
 
+// Rows [J0, J0+NJ) of the thread's half lane only (NJ = 16: the materialising T = 64 kernels decode a vector in two
+// phases so that 16 instead of 32 (lo, hi) pairs are live at a time: half the registers, twice the resident warps).
+// Only the stream words those rows touch are loaded.
+template <int W, int J0, int NJ>
+FLS_HD void unpack_64_part(const uint32_t* pe, const uint32_t* po, uint32_t (&lo)[NJ], uint32_t (&hi)[NJ]) {
+	constexpr int K0 = (J0 * W) >> 5;                      // first stream word touched
+	constexpr int K1 = W == 0 ? 0 : (((J0 + NJ) * W + 31) >> 5); // one past the last
+	uint32_t w[K1 - K0 + 2];
+#pragma unroll
+	for (int k = K0; k < K1; ++k) {
+		w[k - K0] = ((k & 1) ? po : pe)[(k >> 1) * 32 + (k & 1)];
+	}
+	w[K1 - K0] = 0;
+	w[K1 - K0 + 1] = 0;
+#pragma unroll
+	for (int jj = 0; jj < NJ; ++jj) {
+		const int p = (J0 + jj) * W, k = (p >> 5) - K0, sh = p & 31;
+		constexpr int WL = W < 32 ? W : 32;
+		uint32_t l, h;
+		if (W == 0) {
+			l = 0;
+			h = 0;
+		} else {
+			if (sh == 0) {
+				l = w[k];
+			} else if (sh + WL <= 32) {
+				l = w[k] >> sh;
+			} else {
+				l = funnel_r(w[k], w[k + 1], sh);
+			}
+			if (WL < 32) {
+				l &= (1u << (WL & 31)) - 1u;
+			}
+			if (W <= 32) {
+				h = 0;
+			} else {
+				constexpr int WH = W - 32;
+				if (sh == 0) {
+					h = w[k + 1];
+				} else if (sh + WH <= 32) {
+					h = w[k + 1] >> sh;
+				} else {
+					h = funnel_r(w[k + 1], w[k + 2], sh);
+				}
+				if (WH < 32) {
+					h &= (1u << (WH & 31)) - 1u;
+				}
+			}
+		}
+		lo[jj] = l;
+		hi[jj] = h;
+	}
+}
+
 // Base pointers of thread tid's 32-bit word stream inside a T=64 packed vector at s32 (see header comment).
 FLS_HD void stream64_bases(const uint32_t* s32, int tid, int W, const uint32_t*& pe, const uint32_t*& po) {
 	const int l = tid & 15, h = tid >> 4;
@@ -207,6 +261,26 @@ FLS_HD void unpack_64_dispatch(int W, const uint32_t* s32, int tid, uint32_t (&l
 		FLS_CASES8(FLS_CASE_64, 64, 48)
 		FLS_CASES8(FLS_CASE_64, 64, 56)
 		case 64: unpack_64<64>(pe, po, lo, hi); break;
+	default: break;
+	}
+}
+
+#define FLS_CASE_64P(T, Wv) \
+	case Wv: unpack_64_part<Wv, J0, 16>(pe, po, lo, hi); break;
+
+// rows [J0, J0+16) of the half lane; pe/po from stream64_bases
+template <int J0>
+FLS_HD void unpack_64_part_dispatch(int W, const uint32_t* pe, const uint32_t* po, uint32_t (&lo)[16], uint32_t (&hi)[16]) {
+	switch (W) {
+		FLS_CASES8(FLS_CASE_64P, 64, 0)
+		FLS_CASES8(FLS_CASE_64P, 64, 8)
+		FLS_CASES8(FLS_CASE_64P, 64, 16)
+		FLS_CASES8(FLS_CASE_64P, 64, 24)
+		FLS_CASES8(FLS_CASE_64P, 64, 32)
+		FLS_CASES8(FLS_CASE_64P, 64, 40)
+		FLS_CASES8(FLS_CASE_64P, 64, 48)
+		FLS_CASES8(FLS_CASE_64P, 64, 56)
+		case 64: unpack_64_part<64, J0, 16>(pe, po, lo, hi); break;
 	default: break;
 	}
 }

@@ -40,6 +40,10 @@ uint32_t env_u32(const char* name, uint32_t def) {
 	return v ? (uint32_t)std::strtoul(v, nullptr, 10) : def;
 }
 const uint32_t g_run_shift = std::min(5u, env_u32("FLSGPU_RUN_SHIFT", 0));
+const uint32_t g_prefetch = env_u32("FLSGPU_PREFETCH", 1);
+const uint32_t g_force_slots = env_u32("FLSGPU_NSLOTS", 0);     // experiments: pipeline depth override
+const uint32_t g_max_ctas = env_u32("FLSGPU_MAX_CTAS", 0);      // experiments: cap on resident CTAs per SM
+const uint32_t g_budget_kb = env_u32("FLSGPU_WARP_KB", 14);     // shared-memory budget per warp (KiB) the depth is sized for
 
 int cuda_fail(cudaError_t e, const char* where) {
 	char msg[256];
@@ -75,10 +79,10 @@ int ensure_device() {
 
 // ---- per-table device state ---------------------------------------------------------------------------------------
 struct FlsColumnPlan { // what a decode launch over (col, rg range) needs to know about the chunks it covers
-	bool has_main[3] = {false, false, false}; // 0: light (integer encodings), 1: ALP, 2: ALP_RD
+	bool has_main[4] = {false, false, false, false}; // 0: light (integer encodings), 1: ALP, 2: ALP_RD, 3: DELTA (T = 64)
 	bool has_rle = false, has_dict[3] = {false, false, false};
 	bool main_needs_stage = false;
-	uint32_t main_slot[3] = {0, 0, 0}, rle_slot = 0, dict_slot[3] = {0, 0, 0};
+	uint32_t main_slot[4] = {0, 0, 0, 0}, rle_slot = 0, dict_slot[3] = {0, 0, 0};
 };
 
 struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of neighbouring slabs overlap
@@ -313,7 +317,8 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 			p.has_rle = true;
 			p.rle_slot = std::max(p.rle_slot, bytes);
 		} else {
-			const int f = c.encoding == FLS_ENC_ALP ? 1 : c.encoding == FLS_ENC_ALP_RD ? 2 : 0;
+			const int f = c.encoding == FLS_ENC_ALP ? 1 : c.encoding == FLS_ENC_ALP_RD ? 2
+			              : (c.encoding == FLS_ENC_DELTA && c.phys_bits == 64) ? 3 : 0;
 			p.has_main[f] = true;
 			p.main_slot[f] = std::max(p.main_slot[f], bytes);
 			p.main_needs_stage |= c.encoding == FLS_ENC_DELTA;
@@ -334,13 +339,22 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	L.slot_bytes = std::max<uint32_t>(128u, (slot_bytes + 127u) & ~127u);
 	L.stage_bytes = stage_bytes;
 	// shared memory: aim for two resident CTAs per SM (~104 KB each) unless a single slot pair needs more
-	const uint32_t per_warp_budget = 13u * 1024u;
-	const uint32_t fixed = L.stage_bytes + tile_bytes; // per-warp bytes besides the pipeline slots
+	const uint32_t per_warp_budget = g_budget_kb * 1024u;
+	const uint32_t fixed = FLS_DESC_BYTES_PER_WARP + L.stage_bytes + tile_bytes; // per-warp bytes besides the pipeline slots
 	uint32_t n_slots = fixed < per_warp_budget ? (per_warp_budget - fixed) / L.slot_bytes : 0;
-	// never fewer than ~4 KiB of blobs in flight per warp: a bulk copy takes about a microsecond to land, and narrow
-	// vectors (a few hundred bytes) are decoded much faster than that
+	// Two resident CTAs per SM matter more than pipeline depth (measured: 64-bit DELTA, 2 CTAs x 1 slot 0.139 ms vs
+	// 1 CTA x 2 slots 0.154 ms for 100 M values): take the depth the budget allows, down to a single slot; only blobs of
+	// a few hundred bytes, which decode much faster than a bulk copy lands, get at least ~4 KiB in flight per warp.
 	n_slots = std::max(n_slots, std::min(8u, 4096u / L.slot_bytes));
-	n_slots = std::max(2u, std::min(8u, n_slots));
+	n_slots = std::max(1u, std::min(8u, n_slots));
+	// L2 prefetch of the next batch (fls_decode_main.cuh): only while the batch ahead of ALL warps fits L2 comfortably
+	// (~75 000 vectors x blob bytes; measured: helps 128 B blobs by 12 %, hurts 1.3 KiB blobs by 9 %)
+	if (L.slot_bytes > 512u) {
+		L.prefetch = 0;
+	}
+	if (g_force_slots) {
+		n_slots = g_force_slots;
+	}
 	L.n_slots = n_slots;
 	uint32_t wpc = kFlsWarpsPerCta, smem = 0;
 	for (;; wpc >>= 1) { // wide vectors (8 KiB blobs + staging + aggregate tile) may need a smaller CTA to fit 227 KiB
@@ -373,6 +387,9 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 		return fls_set_error(FLSGPU_ERR_CUDA, "decode kernel cannot be resident with the requested shared memory");
 	}
 	const uint64_t want = ((uint64_t)L.total_vecs + wpc - 1) / wpc;
+	if (g_max_ctas) {
+		occ = std::min<int>(occ, (int)g_max_ctas);
+	}
 	const uint32_t grid = (uint32_t)std::min<uint64_t>(want, (uint64_t)occ * g_n_sms);
 	void* args[] = {&L};
 	FLS_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(wpc * 32), args, smem, stream));
@@ -437,19 +454,25 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	L.conv = os.conv;
 	L.out = out_dev;
 	L.run_shift = g_run_shift;
+	// fused aggregates write nothing (no read/write turnarounds to avoid); 8/16-bit outputs are instruction bound, not
+	// bandwidth bound, and the second descriptor fetch costs them ~4 %
+	L.prefetch = (agg || os.ob < 4) ? 0u : g_prefetch;
 	L.agg = agg;
 	L.agg_signed = t->columns[col].is_signed;
 	L.agg_float = t->columns[col].is_float;
 	const uint32_t tile = agg ? 128u * T : 0u; // aggregate launches decode into a per-warp shared-memory tile
 	int rc = FLSGPU_OK;
-	static const uint32_t kFamMask[3] = {FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD)), 1u << FLS_ENC_ALP,
-	                                     1u << FLS_ENC_ALP_RD};
-	for (int f = 0; f < 3 && rc == FLSGPU_OK; ++f) {
+	const uint32_t light = FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD));
+	const uint32_t fam_mask[4] = {T == 64 ? light & ~(1u << FLS_ENC_DELTA) : light, 1u << FLS_ENC_ALP, 1u << FLS_ENC_ALP_RD,
+	                              1u << FLS_ENC_DELTA};
+	for (int f = 0; f < 4 && rc == FLSGPU_OK; ++f) {
 		if (p.has_main[f]) {
-			L.family_mask = kFamMask[f];
+			L.family_mask = fam_mask[f];
 			L.idx_bits = 0;
-			rc = launch_family(agg ? fls_kernel_agg(0, T, T, f) : fls_kernel_main(T, os.ob, f), L, p.main_slot[f],
-			                   (f == 0 && p.main_needs_stage) ? 128u * T : 0u, stream, tile);
+			// DELTA needs the per-warp transposition area (+ 16 lane totals for T = 64)
+			const bool stage = p.main_needs_stage && (f == 3 || (f == 0 && T != 64));
+			rc = launch_family(agg ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, p.main_slot[f],
+			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile);
 		}
 	}
 	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {

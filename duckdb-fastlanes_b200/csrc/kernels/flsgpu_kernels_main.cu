@@ -6,15 +6,16 @@
 
 using namespace flsk;
 
-// fam: 0 = light, 1 = ALP, 2 = ALP_RD
+// fam: 0 = light, 1 = ALP, 2 = ALP_RD, 3 = DELTA (T = 64 only; narrower types keep DELTA in the light kernel)
 const void* fls_kernel_main(int T, int OB, int fam) {
 #define FLS_K(Tv, OBv) \
 	if (fam == 0 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamLight>);
 	FLS_K(8, 1) FLS_K(8, 2) FLS_K(8, 4) FLS_K(8, 8)
 	FLS_K(16, 2) FLS_K(16, 4) FLS_K(16, 8)
 	FLS_K(32, 4) FLS_K(32, 8)
-	FLS_K(64, 8)
 #undef FLS_K
+	if (fam == 0 && T == 64 && OB == 8) return reinterpret_cast<const void*>(&fls_decode_kernel<0, 64, 64, 8, false, kFamLight64>);
+	if (fam == 3 && T == 64 && OB == 8) return reinterpret_cast<const void*>(&fls_decode_kernel<0, 64, 64, 8, false, kFamDelta>);
 #define FLS_K(Tv, OBv) \
 	if (fam == 1 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamAlp>); \
 	if (fam == 2 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamAlpRd>);

@@ -44,6 +44,75 @@ __global__ void __launch_bounds__(256) k_write_tiles(uint4* out, size_t n_tiles,
 	}
 }
 
+// 8 KiB tiles per warp + a small read per tile (rd_bytes from a side buffer, like a vector's packed blob): does a trickle
+// of reads inside a write stream cost DRAM bus turnarounds?
+__global__ void __launch_bounds__(256) k_write_tiles_rd(uint4* out, size_t n_tiles, const uint4* side, uint32_t rd16, uint32_t ahead,
+                                                        uint32_t* sink) {
+	const int lane = threadIdx.x & 31;
+	const size_t n_warps = (size_t)gridDim.x * (blockDim.x >> 5), gw = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	uint32_t acc = 0;
+	for (size_t t = gw; t < n_tiles; t += n_warps) {
+		uint4 r = make_uint4(0, 0, 0, 0);
+		if ((uint32_t)lane < rd16) {
+			const size_t tt = t + ahead * n_warps < n_tiles ? t + ahead * n_warps : t;
+			asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(side + tt * rd16 + lane));
+		}
+		acc ^= r.x ^ r.y ^ r.z ^ r.w;
+		uint4* dst = out + t * 512;
+#pragma unroll
+		for (int it = 0; it < 16; ++it) {
+			const uint32_t v = acc + it;
+			asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + it * 32 + lane), "r"(v), "r"(v), "r"(v), "r"(v) : "memory");
+		}
+	}
+	if (acc == 0x12345678u) {
+		*sink = acc;
+	}
+}
+
+// same, but the reads of 32 tiles are issued together every 32nd tile (per-warp batching), or the whole side buffer is
+// pulled into L2 by a prologue (mode 2) so that the per-tile reads never reach DRAM
+__global__ void __launch_bounds__(256) k_write_tiles_rd_batched(uint4* out, size_t n_tiles, const uint4* side, uint32_t rd16, int mode,
+                                                                uint32_t* sink) {
+	const int lane = threadIdx.x & 31;
+	const size_t n_warps = (size_t)gridDim.x * (blockDim.x >> 5), gw = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	uint32_t acc = 0;
+	if (mode == 2) { // prologue: every warp prefetches its share of the side buffer into L2
+		const size_t total16 = n_tiles * rd16;
+		for (size_t i = (gw * 32 + lane) * 8; i < total16; i += n_warps * 32 * 8) { // 128 B per lane
+			asm volatile("prefetch.global.L2::evict_last [%0];" ::"l"(side + i));
+		}
+	}
+	size_t k = 0;
+	for (size_t t = gw; t < n_tiles; t += n_warps, ++k) {
+		if (mode == 1) {
+			if ((k & 31) == 0) { // reads of the next 32 tiles of this warp, all at once
+				for (uint32_t j = 0; j < 32; ++j) {
+					const size_t tt = t + j * n_warps;
+					if (tt < n_tiles && (uint32_t)lane < rd16) {
+						uint4 r;
+						asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(side + tt * rd16 + lane));
+						acc ^= r.x ^ r.y ^ r.z ^ r.w;
+					}
+				}
+			}
+		} else if ((uint32_t)lane < rd16) {
+			uint4 r;
+			asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(side + t * rd16 + lane));
+			acc ^= r.x ^ r.y ^ r.z ^ r.w;
+		}
+		uint4* dst = out + t * 512;
+#pragma unroll
+		for (int it = 0; it < 16; ++it) {
+			const uint32_t v = acc + it;
+			asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(dst + it * 32 + lane), "r"(v), "r"(v), "r"(v), "r"(v) : "memory");
+		}
+	}
+	if (acc == 0x12345678u) {
+		*sink = acc;
+	}
+}
+
 // TMA bulk store: each warp fills an 8 KiB shared tile once, then streams it out tile after tile (two tiles in flight)
 __global__ void __launch_bounds__(256) k_write_tma(uint8_t* out, size_t n_tiles, uint32_t tile_bytes, int depth) {
 	extern __shared__ __align__(128) uint8_t smem[];
@@ -143,6 +212,29 @@ int main(int argc, char** argv) {
 		std::printf("write st.global.cs    grid %4d: %.4f ms %7.1f GB/s\n", grid, ms, bytes / ms / 1e6);
 		ms = timed([&] { k_write_tiles<<<grid, 256>>>((uint4*)next(), bytes / 8192, 7); });
 		std::printf("write 8K tiles/warp   grid %4d: %.4f ms %7.1f GB/s\n", grid, ms, bytes / ms / 1e6);
+	}
+	for (int cps : {2, 8}) {
+		for (uint32_t rd16 : {0u, 8u, 16u, 32u}) {
+			const int grid = sms * cps;
+			uint8_t* side = c;
+			float ms = timed([&] {
+				uint8_t* d = bufs[rot++ % 2];
+				k_write_tiles_rd<<<grid, 256>>>((uint4*)d, bytes / 8192, (const uint4*)side, rd16, 0, sink);
+			});
+			std::printf("write 8K tiles + %3u B read/tile grid %4d: %.4f ms %7.1f GB/s written\n", rd16 * 16, grid, ms, bytes / ms / 1e6);
+		}
+	}
+	for (int mode : {1, 2}) {
+		for (uint32_t rd16 : {8u, 16u, 32u}) {
+			const int grid = sms * 2;
+			uint8_t* side = c;
+			float ms = timed([&] {
+				uint8_t* d = bufs[rot++ % 2];
+				k_write_tiles_rd_batched<<<grid, 256>>>((uint4*)d, bytes / 8192, (const uint4*)side, rd16, mode, sink);
+			});
+			std::printf("write 8K tiles + %3u B read/tile %s grid %4d: %.4f ms %7.1f GB/s written\n", rd16 * 16,
+			            mode == 1 ? "batched x32 per warp" : "L2 prefetch prologue", grid, ms, bytes / ms / 1e6);
+		}
 	}
 	for (uint32_t tile : {4096u, 8192u}) {
 		for (int cps : {1, 2}) {
