@@ -30,6 +30,8 @@ ColumnType column_type_of(int data_type, int decimal_precision) {
 		t.phys_bits = decimal_precision <= 4 ? 16 : decimal_precision <= 9 ? 32 : 64;
 		t.is_signed = true;
 		break;
+	case FLS_TYPE_FLS_STR:
+	case FLS_TYPE_BYTE_ARRAY: t.phys_bits = 128; break; // decoded element = 16-byte string_t
 	default: t.phys_bits = 0; break;
 	}
 	return t;

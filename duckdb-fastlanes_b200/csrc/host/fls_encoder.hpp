@@ -25,6 +25,11 @@ struct ColumnType {
 bool encode_chunk(const ColumnType& type, const void* values, uint32_t n_tuples, int force_encoding,
                   EncodedChunk& out, const char** err);
 
+// String columns (VARCHAR / BLOB): string i of the chunk = bytes[offsets[i], offsets[i+1]).  force_encoding: one of the
+// string encodings (FLS_ENC_DICT_STR ...) or < 0.
+bool encode_string_chunk(const uint64_t* offsets, const uint8_t* bytes, uint32_t n_tuples, int force_encoding, EncodedChunk& out,
+                         const char** err);
+
 ColumnType column_type_of(int data_type, int decimal_precision);
 
 } // namespace flshost

@@ -1,0 +1,38 @@
+// fls_fsst.hpp — product-side FSST symbol-table construction and compression (host C++).
+//
+// The reference gets FSST from the absent FastLanes library (which vendors cwida/fsst); the code format it decodes is the
+// one of duckdb/third_party/fsst/fsst.h:162-230, which IS in the reference tree: one byte per code, code c < 255 stands
+// for symbol[c] (len[c] = 1..8 bytes), code 255 escapes the next byte as a literal.  Any table + code stream obeying
+// that format is decodable by the reference's fsst_decompress; how the table is chosen is encoder policy.
+// This file is a from-scratch trainer (iterative: encode a sample with the current table, count symbols and adjacent
+// symbol pairs, keep the 255 candidates with the largest gain = frequency x length) and a greedy longest-match encoder.
+#pragma once
+#include <cstdint>
+#include <vector>
+#include "fls_format.h"
+
+namespace flshost {
+
+struct FsstEncoder {
+	fls_fsst_table table {};
+	uint32_t n_symbols = 0;
+	// lookup: open-addressed hash of (length, bytes) -> code, probed from the longest length down
+	std::vector<uint32_t> slots; // code + 1, 0 = empty
+	uint8_t max_len = 0;
+	// single-byte symbols: direct table (code + 1)
+	uint16_t byte_code[256] = {};
+
+	// strings: n strings, string i = bytes[offsets[i] .. offsets[i+1])
+	void train(const uint64_t* offsets, const uint8_t* bytes, uint64_t n);
+	// appends the code stream of one string to out
+	void compress(const uint8_t* s, uint64_t len, std::vector<uint8_t>& out) const;
+
+  private:
+	void rebuild_lookup();
+	int find(const uint8_t* s, uint64_t remaining, uint32_t* len_out) const;
+};
+
+// decoded length of a code stream under `table` (len of each code, 1 per escaped literal); ~0ull if malformed
+uint64_t fsst_decoded_length(const fls_fsst_table& table, const uint8_t* codes, uint64_t n);
+
+} // namespace flshost

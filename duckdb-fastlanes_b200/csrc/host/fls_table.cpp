@@ -35,6 +35,96 @@ static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
 	return packed_bytes(c, m) + (is_patched(c.encoding) ? FLS_EXC_TAIL_BYTES(m.aux_cnt, c.phys_bits / 8u) : 0u);
 }
 
+static bool is_string_enc(unsigned enc) {
+	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_STR_UNCOMPRESSED || enc == FLS_ENC_STR_CONSTANT || enc == FLS_ENC_FSST ||
+	       enc == FLS_ENC_FSST_DICT;
+}
+
+// String chunk (fls_format.h "String columns"): every offset array must be monotone and end at its byte segment's size,
+// packed codes must stay inside the dictionary's lane width, and FSST code streams must decode to exactly the lengths the
+// decoded end offsets promise (the GPU writes each string at its promised heap position without further checks).
+static const char* validate_string_chunk(const flsgpu_table* t, const fls_chunk_desc& ch) {
+	const uint8_t* base = t->bytes + ch.offset;
+	const uint8_t* aux0 = base + ch.seg_off[FLS_SEG_AUX0];
+	const uint32_t* aux1 = reinterpret_cast<const uint32_t*>(base + ch.seg_off[FLS_SEG_AUX1]);
+	const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(base + ch.seg_off[FLS_SEG_META]);
+	const bool dict = ch.encoding == FLS_ENC_DICT_STR || ch.encoding == FLS_ENC_FSST_DICT;
+	const bool fsst = ch.encoding == FLS_ENC_FSST || ch.encoding == FLS_ENC_FSST_DICT;
+	for (uint32_t v = 0; v < ch.n_vec; ++v) {
+		if (meta[v].n_valid == 0 || meta[v].n_valid > FLS_VEC_SZ) {
+			return "vector n_valid out of range";
+		}
+	}
+	if (ch.encoding == FLS_ENC_STR_CONSTANT) {
+		return (ch.seg_size[FLS_SEG_AUX0] == ch.aux_count && ch.const_val == ch.aux_count) ? nullptr : "constant string segment has the wrong size";
+	}
+	const uint64_t n = dict ? ch.aux_count : (uint64_t)ch.n_vec * FLS_VEC_SZ;
+	if (n == 0 || ch.aux_count != n) {
+		return "string count disagrees with the chunk descriptor";
+	}
+	if (ch.seg_size[FLS_SEG_AUX1] != n * 4 * (fsst ? 2 : 1)) {
+		return "string offset segment has the wrong size";
+	}
+	if (dict) {
+		if (ch.idx_bits != 8 && ch.idx_bits != 16 && ch.idx_bits != 32) {
+			return "dictionary idx_bits must be 8, 16 or 32";
+		}
+		for (uint32_t v = 0; v < ch.n_vec; ++v) {
+			const fls_vec_meta& m = meta[v];
+			if (m.width > ch.idx_bits || (uint64_t)m.data_off16 * 16 + 128u * m.width > ch.seg_size[FLS_SEG_DATA] ||
+			    128u * m.width > ch.max_blob_bytes || m.aux_cnt != 0) {
+				return "code vector entry point or width out of range";
+			}
+		}
+	}
+	const uint64_t table_bytes = fsst ? sizeof(fls_fsst_table) : 0;
+	if (ch.seg_size[FLS_SEG_AUX0] < table_bytes) {
+		return "FSST table missing";
+	}
+	const uint64_t n_bytes = ch.seg_size[FLS_SEG_AUX0] - table_bytes;
+	uint32_t prev = 0;
+	for (uint64_t i = 0; i < n; ++i) {
+		if (aux1[i] < prev) {
+			return "string end offsets are not monotone";
+		}
+		prev = aux1[i];
+	}
+	if (prev != n_bytes) {
+		return "string end offsets do not cover the byte segment";
+	}
+	if (!fsst) {
+		return ch.const_val == n_bytes ? nullptr : "decoded byte count disagrees with the byte segment";
+	}
+	const fls_fsst_table* tab = reinterpret_cast<const fls_fsst_table*>(aux0);
+	for (int c = 0; c < 256; ++c) {
+		if (tab->len[c] == 0 || tab->len[c] > 8) {
+			return "FSST symbol length out of range";
+		}
+	}
+	const uint8_t* codes = aux0 + table_bytes;
+	const uint32_t* dec_end = aux1 + n;
+	uint32_t cprev = 0, dprev = 0;
+	for (uint64_t i = 0; i < n; ++i) {
+		uint64_t len = 0;
+		for (uint32_t p = cprev; p < aux1[i]; ++p) {
+			if (codes[p] == FLS_FSST_ESC) {
+				if (++p >= aux1[i]) {
+					return "FSST escape without its literal";
+				}
+				++len;
+			} else {
+				len += tab->len[codes[p]];
+			}
+		}
+		if (dec_end[i] < dprev || dec_end[i] - dprev != len) {
+			return "FSST decoded end offsets disagree with the code stream";
+		}
+		cprev = aux1[i];
+		dprev = dec_end[i];
+	}
+	return ch.const_val == dprev ? nullptr : "decoded byte count disagrees with the decoded end offsets";
+}
+
 int fls_table_parse(flsgpu_table* t) {
 	char msg[256];
 	if (t->size < sizeof(fls_file_header)) {
@@ -100,6 +190,16 @@ int fls_table_parse(flsgpu_table* t) {
 			}
 			if (ch.seg_size[FLS_SEG_META] != (uint64_t)ch.n_vec * sizeof(fls_vec_meta)) {
 				return fail("meta segment has the wrong size");
+			}
+			if (is_string_enc(ch.encoding) != (col.phys_bits == 128)) {
+				return fail("string encoding on a numeric column or vice versa");
+			}
+			if (col.phys_bits == 128) {
+				const char* why = validate_string_chunk(t, ch);
+				if (why) {
+					return fail(why);
+				}
+				continue;
 			}
 			const unsigned T = ch.phys_bits, esz = T / 8;
 			const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_META]);

@@ -23,7 +23,8 @@ struct flsgpu_writer {
 	std::vector<int> force;
 	uint32_t vec_per_rg = FLS_DEFAULT_VEC_PER_RG;
 	uint64_t rg_tuples = 0;
-	std::vector<std::vector<uint8_t>> pending; // per column, < rg_tuples rows
+	std::vector<std::vector<uint8_t>> pending; // per column, < rg_tuples rows (string columns: the bytes)
+	std::vector<std::vector<uint64_t>> pending_off; // string columns: pending_rows + 1 offsets into pending[c]
 	uint64_t pending_rows = 0;
 	std::vector<fls_rowgroup_desc> rgs;
 	std::vector<std::unique_ptr<EncodedChunk>> chunks; // row-group major
@@ -32,7 +33,17 @@ struct flsgpu_writer {
 	std::vector<uint8_t> image;
 };
 
-static int encode_rowgroups(flsgpu_writer* w, const std::vector<const uint8_t*>& col_ptrs, uint64_t n_rows, int n_threads) {
+// Where the rows of one column start: fixed-width values, or (offsets, bytes) of a string column.
+struct ColSrc {
+	const uint8_t* data = nullptr;
+	const uint64_t* offsets = nullptr; // string columns: offsets[i], offsets[i+1] delimit row i inside data
+};
+
+static bool is_string(const ColumnType& t) {
+	return t.phys_bits == 128;
+}
+
+static int encode_rowgroups(flsgpu_writer* w, const std::vector<ColSrc>& col_ptrs, uint64_t n_rows, int n_threads) {
 	// n_rows covers k full row groups, or one partial tail row group
 	const uint64_t n_rg = (n_rows + w->rg_tuples - 1) / w->rg_tuples;
 	const size_t n_cols = w->cols.size();
@@ -60,7 +71,10 @@ static int encode_rowgroups(flsgpu_writer* w, const std::vector<const uint8_t*>&
 			const size_t esz = w->types[c].phys_bits / 8;
 			auto ch = std::make_unique<EncodedChunk>();
 			const char* err = "";
-			if (!encode_chunk(w->types[c], col_ptrs[c] + r * w->rg_tuples * esz, nt, w->force[c], *ch, &err)) {
+			const bool ok = is_string(w->types[c])
+			                    ? encode_string_chunk(col_ptrs[c].offsets + r * w->rg_tuples, col_ptrs[c].data, nt, w->force[c], *ch, &err)
+			                    : encode_chunk(w->types[c], col_ptrs[c].data + r * w->rg_tuples * esz, nt, w->force[c], *ch, &err);
+			if (!ok) {
 				std::lock_guard<std::mutex> g(*mu);
 				failed = true;
 				fail_msg = std::string("column '") + w->cols[c].name + "': " + err;
@@ -118,6 +132,12 @@ int flsgpu_writer_create(uint32_t n_columns, const flsgpu_column_spec* cols, uin
 		w->force.push_back(cols[i].force_encoding);
 	}
 	w->pending.resize(n_columns);
+	w->pending_off.resize(n_columns);
+	for (uint32_t i = 0; i < n_columns; ++i) {
+		if (is_string(w->types[i])) {
+			w->pending_off[i].assign(1, 0);
+		}
+	}
 	*out = w.release();
 	return FLSGPU_OK;
 }
@@ -131,37 +151,72 @@ int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t 
 	}
 	const size_t n_cols = w->cols.size();
 	uint64_t consumed = 0;
+	// rows [first, first + n) of the caller's column c appended to the pending buffer
+	auto keep = [&](size_t c, uint64_t first, uint64_t n) {
+		if (is_string(w->types[c])) {
+			const flsgpu_string_column* sc = static_cast<const flsgpu_string_column*>(columns[c]);
+			const uint64_t b0 = sc->offsets[first], b1 = sc->offsets[first + n];
+			const uint64_t shift = w->pending[c].size() - b0;
+			w->pending[c].insert(w->pending[c].end(), sc->bytes + b0, sc->bytes + b1);
+			for (uint64_t i = 1; i <= n; ++i) {
+				w->pending_off[c].push_back(sc->offsets[first + i] + shift);
+			}
+		} else {
+			const size_t esz = w->types[c].phys_bits / 8;
+			const uint8_t* src = static_cast<const uint8_t*>(columns[c]) + first * esz;
+			w->pending[c].insert(w->pending[c].end(), src, src + n * esz);
+		}
+	};
+	auto pending_src = [&]() {
+		std::vector<ColSrc> ptrs(n_cols);
+		for (size_t c = 0; c < n_cols; ++c) {
+			ptrs[c].data = w->pending[c].data();
+			ptrs[c].offsets = is_string(w->types[c]) ? w->pending_off[c].data() : nullptr;
+		}
+		return ptrs;
+	};
+	auto clear_pending = [&]() {
+		for (size_t c = 0; c < n_cols; ++c) {
+			w->pending[c].clear();
+			if (is_string(w->types[c])) {
+				w->pending_off[c].assign(1, 0);
+			}
+		}
+		w->pending_rows = 0;
+	};
+	for (size_t c = 0; c < n_cols; ++c) {
+		if (!columns[c]) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_append: null column pointer");
+		}
+	}
 	// 1. top up the pending buffer to a full row group
 	if (w->pending_rows) {
 		const uint64_t take = std::min<uint64_t>(n_tuples, w->rg_tuples - w->pending_rows);
 		for (size_t c = 0; c < n_cols; ++c) {
-			const size_t esz = w->types[c].phys_bits / 8;
-			const uint8_t* src = static_cast<const uint8_t*>(columns[c]);
-			w->pending[c].insert(w->pending[c].end(), src, src + take * esz);
+			keep(c, 0, take);
 		}
 		w->pending_rows += take;
 		consumed = take;
 		if (w->pending_rows == w->rg_tuples) {
-			std::vector<const uint8_t*> ptrs(n_cols);
-			for (size_t c = 0; c < n_cols; ++c) {
-				ptrs[c] = w->pending[c].data();
-			}
-			const int rc = encode_rowgroups(w, ptrs, w->rg_tuples, n_threads);
+			const int rc = encode_rowgroups(w, pending_src(), w->rg_tuples, n_threads);
 			if (rc) {
 				return rc;
 			}
-			for (auto& p : w->pending) {
-				p.clear();
-			}
-			w->pending_rows = 0;
+			clear_pending();
 		}
 	}
 	// 2. encode full row groups straight from the caller's arrays
 	const uint64_t full = (n_tuples - consumed) / w->rg_tuples * w->rg_tuples;
 	if (full) {
-		std::vector<const uint8_t*> ptrs(n_cols);
+		std::vector<ColSrc> ptrs(n_cols);
 		for (size_t c = 0; c < n_cols; ++c) {
-			ptrs[c] = static_cast<const uint8_t*>(columns[c]) + consumed * (w->types[c].phys_bits / 8);
+			if (is_string(w->types[c])) {
+				const flsgpu_string_column* sc = static_cast<const flsgpu_string_column*>(columns[c]);
+				ptrs[c].data = sc->bytes;
+				ptrs[c].offsets = sc->offsets + consumed;
+			} else {
+				ptrs[c].data = static_cast<const uint8_t*>(columns[c]) + consumed * (w->types[c].phys_bits / 8);
+			}
 		}
 		const int rc = encode_rowgroups(w, ptrs, full, n_threads);
 		if (rc) {
@@ -173,9 +228,7 @@ int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t 
 	if (consumed < n_tuples) {
 		const uint64_t rest = n_tuples - consumed;
 		for (size_t c = 0; c < n_cols; ++c) {
-			const size_t esz = w->types[c].phys_bits / 8;
-			const uint8_t* src = static_cast<const uint8_t*>(columns[c]) + consumed * esz;
-			w->pending[c].insert(w->pending[c].end(), src, src + rest * esz);
+			keep(c, consumed, rest);
 		}
 		w->pending_rows += rest;
 	}
@@ -190,9 +243,10 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 		return FLSGPU_OK;
 	}
 	if (w->pending_rows) {
-		std::vector<const uint8_t*> ptrs(w->cols.size());
+		std::vector<ColSrc> ptrs(w->cols.size());
 		for (size_t c = 0; c < w->cols.size(); ++c) {
-			ptrs[c] = w->pending[c].data();
+			ptrs[c].data = w->pending[c].data();
+			ptrs[c].offsets = is_string(w->types[c]) ? w->pending_off[c].data() : nullptr;
 		}
 		const int rc = encode_rowgroups(w, ptrs, w->pending_rows, 1);
 		if (rc) {

@@ -19,9 +19,12 @@ lib = C.CDLL(LIB_PATH)
 
 # ---- enums (include/fls_format.h, include/flsgpu.h) -------------------------------------------------------------
 TYPE = dict(INT8=1, INT16=2, INT32=3, INT64=4, UINT8=5, UINT16=6, UINT32=7, UINT64=8, FLOAT=9, DOUBLE=10,
-            BOOLEAN=11, DATE=12, TIMESTAMP=13, DECIMAL=14)
+            BOOLEAN=11, DATE=12, TIMESTAMP=13, DECIMAL=14, VARCHAR=15, BLOB=16)
 ENC = dict(UNCOMPRESSED=0, CONSTANT=1, FFOR=2, DELTA=3, DICT=4, RLE=5, ALP=6, ALP_RD=7, CROSS_RLE=8, FREQUENCY=9,
-           SLPATCH=10)
+           SLPATCH=10, DICT_STR=11, STR_UNCOMPRESSED=12, STR_CONSTANT=13, FSST=14, FSST_DICT=15)
+STRING_TYPES = (15, 16)
+# DuckDB string_t (string_type.hpp:236-247): u32 length + 12 bytes (inlined | 4 prefix bytes + pointer)
+STRING_T = np.dtype([("length", "<u4"), ("body", "u1", 12)])
 ENC_NAME = {v: k for k, v in ENC.items()}
 OUT = dict(NATIVE=0, I8=1, I16=2, I32=3, I64=4, U8=5, U16=6, U32=7, U64=8, F32=9, F64=10)
 OUT_NP = {1: np.int8, 2: np.int16, 3: np.int32, 4: np.int64, 5: np.uint8, 6: np.uint16, 7: np.uint32, 8: np.uint64,
@@ -34,6 +37,36 @@ VEC = 1024
 class ColumnSpec(C.Structure):
     _fields_ = [("name", C.c_char_p), ("data_type", C.c_int32), ("decimal_precision", C.c_int32),
                 ("decimal_scale", C.c_int32), ("force_encoding", C.c_int32)]
+
+
+class StringColumn(C.Structure):
+    _fields_ = [("offsets", C.c_void_p), ("bytes", C.c_void_p)]
+
+
+def pack_strings(values):
+    """list of str/bytes (or an (offsets, bytes) pair) -> (uint64 offsets[n+1], uint8 bytes)."""
+    if isinstance(values, tuple):
+        off, data = values
+        return np.ascontiguousarray(off, dtype=np.uint64), np.ascontiguousarray(data, dtype=np.uint8)
+    enc = [v.encode() if isinstance(v, str) else bytes(v) for v in values]
+    off = np.zeros(len(enc) + 1, dtype=np.uint64)
+    np.cumsum([len(e) for e in enc], out=off[1:])
+    data = np.frombuffer(b"".join(enc), dtype=np.uint8)
+    return off, (data if data.size else np.zeros(1, dtype=np.uint8))
+
+
+def strings_from(string_t, heap, heap_base=0):
+    """Python bytes of every element of a STRING_T array whose pointers are heap_base + offset into heap."""
+    out = []
+    hb = heap.tobytes() if isinstance(heap, np.ndarray) else bytes(heap)
+    for s in string_t:
+        n = int(s["length"])
+        if n <= 12:
+            out.append(s["body"][:n].tobytes())
+        else:
+            off = int(s["body"][4:].view("<u8")[0]) - heap_base
+            out.append(hb[off:off + n])
+    return out
 
 
 class ColumnDesc(C.Structure):
@@ -114,16 +147,30 @@ class Writer:
             specs[i] = ColumnSpec(self._names[i], TYPE[c[1]], prec, scale, -1 if c[2] is None else ENC[c[2]])
             if c[1] == "DECIMAL":
                 self.np_types.append(np.int16 if prec <= 4 else np.int32 if prec <= 9 else np.int64)
+            elif TYPE[c[1]] in STRING_TYPES:
+                self.np_types.append(None)
             else:
                 self.np_types.append(_NP_OF_TYPE[TYPE[c[1]]])
         self._h = C.c_void_p()
         _check(lib.flsgpu_writer_create(len(columns), specs, vec_per_rowgroup, C.byref(self._h)), "writer_create")
 
     def append(self, arrays, n_threads=None):
-        n = len(arrays[0])
-        keep = [np.ascontiguousarray(a, dtype=t) for a, t in zip(arrays, self.np_types)]
-        assert all(len(a) == n for a in keep)
-        ptrs = (C.c_void_p * len(keep))(*[a.ctypes.data for a in keep])
+        keep, addrs, n = [], [], None
+        for a, t in zip(arrays, self.np_types):
+            if t is None:  # string column: flsgpu_string_column {offsets, bytes}
+                off, data = pack_strings(a)
+                sc = StringColumn(off.ctypes.data, data.ctypes.data)
+                keep += [off, data, sc]
+                addrs.append(C.addressof(sc))
+                rows = len(off) - 1
+            else:
+                arr = np.ascontiguousarray(a, dtype=t)
+                keep.append(arr)
+                addrs.append(arr.ctypes.data)
+                rows = len(arr)
+            assert n is None or rows == n, "columns of different lengths"
+            n = rows
+        ptrs = (C.c_void_p * len(addrs))(*addrs)
         _check(lib.flsgpu_writer_append(self._h, ptrs, C.c_uint64(n), n_threads or (os.cpu_count() or 1)), "writer_append")
 
     def finish(self):

@@ -65,16 +65,20 @@ typedef enum fls_encoding {
 	FLS_ENC_CROSS_RLE = 8,    /* dec_cross_rle_opr: row-group wide (value,length) runs */
 	FLS_ENC_FREQUENCY = 9,    /* dec_frequency_opr: frequent value + exceptions */
 	FLS_ENC_SLPATCH = 10,     /* dec_slpatch_opr: FFOR at reduced width + patches */
-	FLS_ENC_DICT_STR = 11,    /* dec_dict_opr<fls_string_t,IDX> */
-	FLS_ENC_COUNT = 12
+	FLS_ENC_DICT_STR = 11,    /* dec_dict_opr<fls_string_t,IDX>: dictionary of strings + packed codes */
+	FLS_ENC_STR_UNCOMPRESSED = 12, /* dec_fls_str_uncompressed_opr: lengths + bytes */
+	FLS_ENC_STR_CONSTANT = 13, /* dec_constant_str_opr */
+	FLS_ENC_FSST = 14,        /* dec_fsst_opr: FSST-compressed strings (8-bit codes, 255 = escape) */
+	FLS_ENC_FSST_DICT = 15,   /* dec_fsst_dict_opr<IDX>: dictionary whose strings are FSST-compressed + packed codes */
+	FLS_ENC_COUNT = 16
 } fls_encoding;
 
 /* Segment slots inside a column chunk. */
 enum {
 	FLS_SEG_META = 0, /* fls_vec_meta[n_vec] */
 	FLS_SEG_DATA = 1, /* per-vector packed blobs, addressed by fls_vec_meta.data_off16 */
-	FLS_SEG_AUX0 = 2, /* DICT keys | RLE run values | CROSS_RLE values | string bytes */
-	FLS_SEG_AUX1 = 3, /* CROSS_RLE lengths (u32) | string end offsets (u32) */
+	FLS_SEG_AUX0 = 2, /* DICT keys | RLE run values | CROSS_RLE values | string bytes ([FSST table] + bytes) */
+	FLS_SEG_AUX1 = 3, /* CROSS_RLE lengths (u32) | string end offsets (u32; FSST: compressed ends, then decoded ends) */
 	FLS_SEG_COUNT = 4
 };
 
@@ -154,6 +158,22 @@ typedef struct fls_vec_meta { /* 32 bytes */
  * The exceptions travel with the vector so that ONE bulk copy stages everything a vector needs (out[pos[k]] = value[k]
  * after the vector has been decoded: alp.hpp:401-404, slpatch / frequency patches).
  */
+/* String columns (data_type FLS_TYPE_FLS_STR / BYTE_ARRAY, phys_bits = 128: the decoded element is DuckDB's 16-byte
+ * string_t).  "n" below is the number of strings the offsets cover: n_vec*1024 for per-row encodings (the padding rows
+ * of a partial last vector are empty strings), aux_count (#keys) for the dictionary encodings.
+ *   STR_UNCOMPRESSED: AUX0 = bytes of all strings back to back; AUX1 = u32 end[n].                 const_val = bytes
+ *   STR_CONSTANT:     AUX0 = the string; aux_count = its length.                                  const_val = length
+ *   DICT_STR:         META/DATA = packed codes as for DICT (idx_bits lanes); AUX0 = dictionary bytes; AUX1 = u32 end[n_keys]
+ *   FSST:             AUX0 = fls_fsst_table | compressed bytes; AUX1 = u32 comp_end[n] | u32 dec_end[n]
+ *   FSST_DICT:        META/DATA = packed codes; AUX0 = fls_fsst_table | compressed dictionary; AUX1 = comp_end[n_keys] | dec_end[n_keys]
+ * const_val = number of DECODED string bytes of the chunk (its share of the string heap); the per-string decoded end
+ * offsets make every string's heap position known without decoding its predecessors (entry points, like PointTo). */
+typedef struct fls_fsst_table { /* fsst_decoder_t of duckdb/third_party/fsst/fsst.h:70-75 without its header bytes */
+	uint64_t symbol[256]; /* symbol[c]: up to 8 bytes, little endian; c = 255 is the escape code and unused */
+	uint8_t len[256];     /* byte length of symbol[c], 1..8 */
+} fls_fsst_table;
+#define FLS_FSST_ESC 255u
+
 #define FLS_PAD16(x) (((x) + 15u) & ~15u)
 #define FLS_EXC_TAIL_BYTES(n, elem_bytes) ((n) ? FLS_PAD16((uint32_t)(n) * (elem_bytes)) + FLS_PAD16((uint32_t)(n) * 2u) : 0u)
 

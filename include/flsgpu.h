@@ -48,10 +48,18 @@ typedef struct flsgpu_column_spec {
 	int32_t force_encoding;    /* fls_encoding, or -1: choose the smallest (encoding selection lives in the absent lib) */
 } flsgpu_column_spec;
 
+/* Rows of a VARCHAR / BLOB column as handed to flsgpu_writer_append (fls_view_writer.cpp:61-94: offsets + bytes):
+ * row i = bytes[offsets[i], offsets[i+1]); offsets has n_tuples + 1 entries. */
+typedef struct flsgpu_string_column {
+	const uint64_t* offsets;
+	const uint8_t* bytes;
+} flsgpu_string_column;
+
 /* WithSchema/WithRowGroupSize (fls_writer.cpp:271-284); vec_per_rowgroup 0 -> 64 (fls_writer.hpp:14). */
 int flsgpu_writer_create(uint32_t n_columns, const flsgpu_column_spec* cols, uint32_t vec_per_rowgroup,
                          flsgpu_writer** out);
-/* Sink (fls_writer.cpp:46-102): columns[i] points at n_tuples values of column i's PHYSICAL type.  Rows are
+/* Sink (fls_writer.cpp:46-102): columns[i] points at n_tuples values of column i's PHYSICAL type
+ * (string columns: columns[i] points at a flsgpu_string_column).  Rows are
  * buffered until a full row group exists; full row groups are encoded on n_threads host threads. */
 int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t n_tuples, int n_threads);
 /* Finalize (fls_writer.cpp:332-347): flush the tail row group and build the footer. */

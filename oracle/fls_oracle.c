@@ -194,3 +194,33 @@ int fls_oracle_decode_vector(const fls_oracle_table* t, uint32_t rg, uint32_t co
 	default: return -2;
 	}
 }
+
+/* Codes of one vector of a dictionary-encoded chunk (numeric DICT, DICT_STR, FSST_DICT): dec_dict_opr<KEY, IDX>::Index()
+ * (reference dictionary_kernel.hpp:14-20,89-99): FFOR-packed in idx_bits lanes, base = smallest code of the vector. */
+int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, uint32_t* codes) {
+	if (rg >= t->header.n_rowgroups || col >= t->header.n_columns) {
+		return -1;
+	}
+	const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + col];
+	if (vec >= ch->n_vec || (ch->encoding != FLS_ENC_DICT && ch->encoding != FLS_ENC_DICT_STR && ch->encoding != FLS_ENC_FSST_DICT)) {
+		return -1;
+	}
+	const uint8_t* base = t->bytes + ch->offset;
+	const fls_vec_meta* m = (const fls_vec_meta*)(base + ch->seg_off[FLS_SEG_META]) + vec;
+	const uint8_t* blob = base + ch->seg_off[FLS_SEG_DATA] + (size_t)m->data_off16 * 16;
+	if (ch->idx_bits == 8) {
+		uint8_t c8[1024];
+		unffor_8((const uint8_t*)blob, m->width, 0, c8);
+		for (unsigned i = 0; i < 1024; ++i) codes[i] = c8[i];
+	} else if (ch->idx_bits == 16) {
+		uint16_t c16[1024];
+		unffor_16((const uint16_t*)blob, m->width, 0, c16);
+		for (unsigned i = 0; i < 1024; ++i) codes[i] = c16[i];
+	} else {
+		unffor_32((const uint32_t*)blob, m->width, 0, codes);
+	}
+	for (unsigned i = 0; i < 1024; ++i) {
+		codes[i] += (uint32_t)m->base;
+	}
+	return 0;
+}

@@ -66,6 +66,19 @@ float fls_oracle_alp_decode_f32(int32_t digit, int e, int f);
 int fls_oracle_aggregate(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* sum_lo,
                          uint64_t* sum_hi, uint64_t* count, int64_t* min_val, int64_t* max_val, double* fsum);
 
+/* ---- string columns (fls_oracle_str.c) ---------------------------------------------------------------------------- */
+int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, uint32_t* codes /* 1024 */);
+uint64_t fls_oracle_fsst_decompress(const fls_fsst_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out);
+/* Bytes of string heap a flat decode of [rg_begin, rg_begin + n_rg) needs (sum of the chunks' 16-byte padded decoded sizes). */
+int fls_oracle_string_heap_bytes(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out);
+/* Flat materialisation: 16-byte string_t per row (same row layout as fls_oracle_decode_column) + heap; pointers of
+ * non-inlined strings are heap_base_addr + offset into heap. */
+int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings,
+                              uint8_t* heap, uint64_t heap_base_addr);
+/* Dictionary form: string_t of every key of chunk (rg, col) + the dictionary bytes (const_val of them). */
+int fls_oracle_decode_string_dict(const fls_oracle_table* t, uint32_t col, uint32_t rg, void* out_keys, uint8_t* heap,
+                                  uint64_t heap_base_addr);
+
 #ifdef __cplusplus
 }
 #endif

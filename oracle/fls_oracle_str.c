@@ -1,0 +1,163 @@
+/*
+ * fls_oracle_str.c — CPU restatement of the string side of the read_fls decode path.  TEST INFRASTRUCTURE ONLY
+ * (see fls_oracle.h: only tests/, smoke() and bench.py's CPU legs may load this).
+ *
+ * Follows the reference materializer's string kernels (src/include/reader/materializer/kernels/):
+ *   dec_fls_str_uncompressed_opr  uncompressed_kernel.hpp:26-38   AddString(data + offset, length[i]), offset += length
+ *   dec_constant_str_opr          constant_kernel.hpp:40-49       one string for the whole vector
+ *   dec_dict_opr<fls_string_t>    dictionary_kernel.hpp:52-102    Prepare: dictionary of string_t from end offsets + bytes;
+ *                                                                 Decode: selection vector = the codes
+ *   dec_fsst_opr                  fsst_kernel.hpp:19-57           per string: fsst_decompress(decoder, len, in, 8*len, buf)
+ *   dec_fsst_dict_opr             fsst_dict_kernel.hpp:20-52,54-80 FSST-decoded dictionary + codes
+ * FSST decoding = duckdb/third_party/fsst/fsst.h:162-230 (in the reference tree): code < 255 -> symbol[code] (len[code]
+ * bytes), 255 -> next byte literal.  The decoded element is DuckDB's string_t
+ * (duckdb/src/include/duckdb/common/types/string_type.hpp:22-60,236-247): length <= 12 -> inlined, zero padded;
+ * otherwise 4 prefix bytes + pointer.  Pointers are heap_base_addr + offset into the heap this function fills, so the
+ * result is position independent and comparable bit for bit with the CUDA path.
+ *
+ * PARITY: the FSST decoder is pinned against the in-tree libfsst (oracle/_ref/libfsstref.so, tests/golden/fsst_golden.npz);
+ * the segment layout is this engine's own container (the real .fls bytes live in the absent library): unpinned.
+ */
+#include <string.h>
+#include "fls_oracle.h"
+
+typedef struct {
+	uint32_t length;
+	uint8_t body[12]; /* inlined[12] | prefix[4] + ptr(8) */
+} ostr_t;
+
+static void make_string(ostr_t* s, const uint8_t* data, uint32_t len, uint64_t addr) {
+	s->length = len;
+	memset(s->body, 0, 12);
+	if (len <= 12) {
+		if (len) {
+			memcpy(s->body, data, len);
+		}
+	} else {
+		memcpy(s->body, data, 4);
+		memcpy(s->body + 4, &addr, 8);
+	}
+}
+
+static uint64_t pad16(uint64_t x) {
+	return (x + 15u) & ~(uint64_t)15u;
+}
+
+/* fsst.h:162-230, the scalar tail loop (:219-230) applied to the whole string */
+uint64_t fls_oracle_fsst_decompress(const fls_fsst_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out) {
+	uint64_t pos_out = 0;
+	for (uint64_t p = 0; p < len_in;) {
+		const unsigned code = in[p++];
+		if (code < FLS_FSST_ESC) {
+			memcpy(out + pos_out, &tab->symbol[code], tab->len[code]);
+			pos_out += tab->len[code];
+		} else {
+			out[pos_out++] = in[p++];
+		}
+	}
+	return pos_out;
+}
+
+int fls_oracle_string_heap_bytes(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out) {
+	uint64_t total = 0;
+	if (col >= t->header.n_columns || t->columns[col].phys_bits != 128) {
+		return -1;
+	}
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		total += pad16(t->chunks[(uint64_t)r * t->header.n_columns + col].const_val);
+	}
+	*out = total;
+	return 0;
+}
+
+/* Decoded bytes of one chunk into its heap region; returns per-string (start, end) lookup through ends[]. */
+static void fill_heap(const fls_oracle_table* t, const fls_chunk_desc* ch, uint8_t* heap) {
+	const uint8_t* aux0 = t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX0];
+	const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
+	if (ch->encoding == FLS_ENC_FSST || ch->encoding == FLS_ENC_FSST_DICT) {
+		const fls_fsst_table* tab = (const fls_fsst_table*)aux0;
+		const uint8_t* codes = aux0 + sizeof(fls_fsst_table);
+		const uint32_t n = ch->aux_count;
+		uint32_t cprev = 0, dprev = 0;
+		for (uint32_t i = 0; i < n; ++i) {
+			fls_oracle_fsst_decompress(tab, codes + cprev, aux1[i] - cprev, heap + dprev);
+			cprev = aux1[i];
+			dprev = aux1[n + i];
+		}
+	} else {
+		memcpy(heap, aux0, ch->const_val);
+	}
+}
+
+int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings,
+                              uint8_t* heap, uint64_t heap_base_addr) {
+	if (col >= t->header.n_columns || t->columns[col].phys_bits != 128) {
+		return -1;
+	}
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	uint64_t heap_off = 0;
+	uint32_t codes[FLS_VEC_SZ];
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		const fls_chunk_desc* ch = &t->chunks[(uint64_t)(rg_begin + r) * t->header.n_columns + col];
+		ostr_t* out = (ostr_t*)out_strings + (uint64_t)r * vpr * FLS_VEC_SZ;
+		uint8_t* hp = heap + heap_off;
+		const uint64_t haddr = heap_base_addr + heap_off;
+		const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
+		const int fsst = ch->encoding == FLS_ENC_FSST || ch->encoding == FLS_ENC_FSST_DICT;
+		const uint32_t* ends = fsst ? aux1 + ch->aux_count : aux1; /* decoded end offsets */
+		fill_heap(t, ch, hp);
+		const uint32_t n_rows = ch->n_vec * FLS_VEC_SZ;
+		switch (ch->encoding) {
+		case FLS_ENC_STR_CONSTANT:
+			for (uint32_t i = 0; i < n_rows; ++i) {
+				make_string(&out[i], hp, ch->aux_count, haddr);
+			}
+			break;
+		case FLS_ENC_STR_UNCOMPRESSED:
+		case FLS_ENC_FSST:
+			for (uint32_t i = 0; i < n_rows; ++i) {
+				const uint32_t start = i ? ends[i - 1] : 0;
+				make_string(&out[i], hp + start, ends[i] - start, haddr + start);
+			}
+			break;
+		case FLS_ENC_DICT_STR:
+		case FLS_ENC_FSST_DICT:
+			for (uint32_t v = 0; v < ch->n_vec; ++v) {
+				if (fls_oracle_decode_codes(t, rg_begin + r, col, v, codes)) {
+					return -2;
+				}
+				for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+					const uint32_t k = codes[i] < ch->aux_count ? codes[i] : ch->aux_count - 1;
+					const uint32_t start = k ? ends[k - 1] : 0;
+					make_string(&out[(uint64_t)v * FLS_VEC_SZ + i], hp + start, ends[k] - start, haddr + start);
+				}
+			}
+			break;
+		default: return -3;
+		}
+		heap_off += pad16(ch->const_val);
+	}
+	return 0;
+}
+
+/* Dictionary form (what the reference hands to DuckDB as a DICTIONARY_VECTOR, dictionary_kernel.hpp:60-78): the string_t
+ * of every key of chunk (rg, col) + the dictionary bytes. */
+int fls_oracle_decode_string_dict(const fls_oracle_table* t, uint32_t col, uint32_t rg, void* out_keys, uint8_t* heap,
+                                  uint64_t heap_base_addr) {
+	if (col >= t->header.n_columns || rg >= t->header.n_rowgroups) {
+		return -1;
+	}
+	const fls_chunk_desc* ch = &t->chunks[(uint64_t)rg * t->header.n_columns + col];
+	if (ch->encoding != FLS_ENC_DICT_STR && ch->encoding != FLS_ENC_FSST_DICT) {
+		return -3;
+	}
+	const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
+	const uint32_t* ends = ch->encoding == FLS_ENC_FSST_DICT ? aux1 + ch->aux_count : aux1;
+	fill_heap(t, ch, heap);
+	ostr_t* out = (ostr_t*)out_keys;
+	for (uint32_t k = 0; k < ch->aux_count; ++k) {
+		const uint32_t start = k ? ends[k - 1] : 0;
+		make_string(&out[k], heap + start, ends[k] - start, heap_base_addr + start);
+	}
+	return 0;
+}

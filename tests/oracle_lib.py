@@ -11,7 +11,7 @@ LIB = os.path.join(ORACLE_DIR, "liboracle.so")
 
 
 def build():
-    srcs = ["fls_oracle.c", "fls_oracle_scan.c", "fls_oracle_tmpl.h", "fls_oracle.h"]
+    srcs = ["fls_oracle.c", "fls_oracle_scan.c", "fls_oracle_str.c", "fls_oracle_tmpl.h", "fls_oracle.h"]
     stale = not os.path.exists(LIB) or any(
         os.path.getmtime(os.path.join(ORACLE_DIR, s)) > os.path.getmtime(LIB) for s in srcs)
     if stale:
@@ -56,6 +56,37 @@ class Oracle:
         if rc:
             raise RuntimeError(f"fls_oracle_scan failed: {rc}")
         return nbytes.value, cks.value
+
+    def decode_codes(self, rg, col, vec):
+        codes = np.zeros(1024, dtype=np.uint32)
+        if lib.fls_oracle_decode_codes(C.byref(self.t), rg, col, vec, C.c_void_p(codes.ctypes.data)):
+            raise RuntimeError("fls_oracle_decode_codes failed")
+        return codes
+
+    def string_heap_bytes(self, col, rg_begin, n_rg):
+        n = C.c_uint64()
+        if lib.fls_oracle_string_heap_bytes(C.byref(self.t), col, rg_begin, n_rg, C.byref(n)):
+            raise RuntimeError("fls_oracle_string_heap_bytes failed")
+        return n.value
+
+    def decode_strings(self, col, rg_begin, n_rg, vec_per_rg, heap_base=0):
+        """(string_t array as a (n, 16) uint8 view source, heap bytes): flat materialisation of a string column."""
+        out = np.zeros((n_rg * vec_per_rg * 1024, 16), dtype=np.uint8)
+        heap = np.zeros(max(16, self.string_heap_bytes(col, rg_begin, n_rg)), dtype=np.uint8)
+        rc = lib.fls_oracle_decode_strings(C.byref(self.t), col, rg_begin, n_rg, C.c_void_p(out.ctypes.data),
+                                           C.c_void_p(heap.ctypes.data), C.c_uint64(heap_base))
+        if rc:
+            raise RuntimeError(f"fls_oracle_decode_strings failed: {rc}")
+        return out, heap
+
+    def decode_string_dict(self, col, rg, n_keys, heap_bytes, heap_base=0):
+        out = np.zeros((n_keys, 16), dtype=np.uint8)
+        heap = np.zeros(max(16, heap_bytes), dtype=np.uint8)
+        rc = lib.fls_oracle_decode_string_dict(C.byref(self.t), col, rg, C.c_void_p(out.ctypes.data),
+                                               C.c_void_p(heap.ctypes.data), C.c_uint64(heap_base))
+        if rc:
+            raise RuntimeError(f"fls_oracle_decode_string_dict failed: {rc}")
+        return out, heap
 
     def aggregate(self, col, rg_begin, n_rg):
         lo, hi, cnt = C.c_uint64(), C.c_uint64(), C.c_uint64()
