@@ -114,3 +114,25 @@ def unpack(packed, T, W):
     out = np.zeros(1024, dtype=np.dtype(f"u{T // 8}"))
     lib.fls_oracle_unpack(C.c_void_p(packed.ctypes.data), T, W, C.c_void_p(out.ctypes.data))
     return out
+
+
+lib.fls_oracle_fsst_decompress.restype = C.c_uint64
+lib.fls_oracle_fsst_decompress.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+
+
+def fsst_decode_stream(symbol, length, codes, comp_end, dec_cap):
+    """Oracle FSST decoder (fls_oracle_str.c) over back-to-back code streams: (decoded bytes, decoded end offsets)."""
+    table = np.zeros(256 * 8 + 256, dtype=np.uint8)  # fls_fsst_table: symbol[256] u64 | len[256] u8
+    table[:2048] = np.ascontiguousarray(symbol, dtype="<u8").view(np.uint8)
+    table[2048:] = length
+    codes = np.ascontiguousarray(codes, dtype=np.uint8)
+    out = np.zeros(dec_cap + 16, dtype=np.uint8)
+    ends = np.zeros(len(comp_end), dtype=np.uint64)
+    pos = prev = 0
+    for i, e in enumerate(comp_end):
+        e = int(e)
+        pos += lib.fls_oracle_fsst_decompress(C.c_void_p(table.ctypes.data), C.c_void_p(codes.ctypes.data + prev), e - prev,
+                                              C.c_void_p(out.ctypes.data + pos))
+        ends[i] = pos
+        prev = e
+    return out[:pos].copy(), ends

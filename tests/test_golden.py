@@ -4,6 +4,9 @@
    vendored alp.hpp / alprd.hpp, compiled by oracle/Makefile into oracle/_ref; generator: oracle/make_golden.py).
 2. The reference's own test tables (test/all_types_single_threaded.test) round-trip through writer + oracle, at the
    reference's 1024 rows and at BASELINE config 1's 1 000 000 rows.
+3. FSST: the oracle's decoder against code streams produced by the reference tree's own FSST compressor
+   (duckdb/third_party/fsst, oracle/_ref/libfsstref.so; generator: oracle/make_golden_fsst.py), and the product encoder's
+   streams against what the reference's fsst_decompress makes of them.
 Byte-level parity with the reference's .fls files stays UNPINNED (third-party FastLanes library absent).
 """
 import ctypes as C
@@ -70,6 +73,44 @@ def test_golden_file_is_not_stale():
     spec.loader.exec_module(mg)
     fresh = mg.generate()
     committed = np.load(GOLDEN)
+    assert sorted(fresh) == sorted(committed.files)
+    for k in fresh:
+        assert fresh[k].tobytes() == committed[k].tobytes(), k
+
+
+FSST_GOLDEN = os.path.join(ROOT, "tests", "golden", "fsst_golden.npz")
+
+
+@pytest.mark.parametrize("corpus", ["comment", "blob", "value"])
+def test_fsst_oracle_decodes_reference_streams(corpus):
+    g = np.load(FSST_GOLDEN)
+    off, data = g[f"ref_{corpus}_offsets"], g[f"ref_{corpus}_bytes"]
+    dec, ends = oracle_lib.fsst_decode_stream(g[f"ref_{corpus}_symbol"], g[f"ref_{corpus}_len"], g[f"ref_{corpus}_codes"],
+                                              g[f"ref_{corpus}_comp_end"], int(off[-1]))
+    assert dec.tobytes() == data.tobytes()
+    assert ends.tolist() == off[1:].tolist()
+
+
+@pytest.mark.parametrize("corpus", ["comment", "blob", "value"])
+def test_fsst_product_streams_decode_like_the_reference(corpus):
+    """The reference decoder's output over the product encoder's table + streams (stored in the golden file) equals what
+    the oracle makes of the same streams."""
+    g = np.load(FSST_GOLDEN)
+    want, want_ends = g[f"prod_{corpus}_ref_decoded"], g[f"prod_{corpus}_ref_ends"]
+    dec, ends = oracle_lib.fsst_decode_stream(g[f"prod_{corpus}_symbol"], g[f"prod_{corpus}_len"], g[f"prod_{corpus}_codes"],
+                                              g[f"prod_{corpus}_comp_end"], int(want_ends[-1]))
+    assert dec.tobytes() == want.tobytes() and ends.tolist() == want_ends.tolist()
+
+
+def test_fsst_golden_file_is_not_stale():
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libfsstref.so")):
+        pytest.skip("oracle/_ref not built here (needs /root/reference)")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_fsst", os.path.join(ROOT, "oracle", "make_golden_fsst.py"))
+    mg = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mg)
+    fresh = mg.generate()
+    committed = np.load(FSST_GOLDEN)
     assert sorted(fresh) == sorted(committed.files)
     for k in fresh:
         assert fresh[k].tobytes() == committed[k].tobytes(), k
