@@ -386,4 +386,19 @@ int flsgpu_table_chunk(const flsgpu_table* t, uint32_t rg, uint32_t col, fls_chu
 	return FLSGPU_OK;
 }
 
+int flsgpu_string_heap_bytes(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out) {
+	if (!t || !out || col >= t->header.n_columns || rg_begin > t->header.n_rowgroups || n_rg > t->header.n_rowgroups - rg_begin) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_string_heap_bytes: column or row-group range out of bounds");
+	}
+	if (t->columns[col].phys_bits != 128) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_string_heap_bytes: not a string column");
+	}
+	uint64_t total = 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		total += (t->chunk(r, col).const_val + 15u) & ~15ull; // every chunk's slice of the heap starts 16-byte aligned
+	}
+	*out = total;
+	return FLSGPU_OK;
+}
+
 } // extern "C"

@@ -50,6 +50,21 @@ struct FlsLaunch {
 	uint32_t agg_float;  // 1 = FLOAT/DOUBLE column (fsum + count only)
 };
 
+// Launch parameters of the string kernels (flsgpu_kernels_str.cu): column `col` of row groups [rg_begin, rg_begin + n_rg).
+struct FlsStrLaunch {
+	const FlsChunkDev* chunks;   // &chunk_dev[rg_begin * n_cols + col]
+	const uint64_t* heap_prefix; // &heap_prefix[rg_begin * n_cols + col]: 16-byte padded decoded bytes of the column's chunks before this one
+	uint64_t heap_prefix0;       // heap_prefix of row group rg_begin (the heap handed in starts there)
+	uint8_t* heap;               // device string heap, 16-byte aligned
+	uint64_t heap_base_addr;     // address the heap will have where the strings are consumed (string_t pointers)
+	void* out;                   // string_t[n_rg * vec_per_rg * 1024] | u32 codes | string_t[n_keys]
+	uint32_t chunk_stride;       // n_cols
+	uint32_t vec_per_rg;
+	uint32_t n_rg;
+	uint32_t groups_per_rg;      // heap kernel: CTAs per chunk (set by the launcher)
+	uint32_t codes_only;         // rows kernel: emit the u32 selection vector instead of string_t
+};
+
 // Per-warp shared memory holding the 32 vector descriptors of a batch (64 B each), in front of the pipeline slots.
 #define FLS_DESC_BYTES_PER_WARP 2048u
 

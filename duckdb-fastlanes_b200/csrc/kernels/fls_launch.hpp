@@ -21,6 +21,11 @@ const void* fls_kernel_agg(int mode, int T, int VT, int fam);
 cudaError_t fls_agg_finalize(flsgpu_agg_acc* acc, uint32_t is_signed, unsigned long long key_min, unsigned long long key_max,
                              cudaStream_t stream);
 cudaError_t fls_agg_reset(flsgpu_agg_acc* acc, cudaStream_t stream);
+// String columns (flsgpu_kernels_str.cu): heap fill (plain copy / parallel FSST decode), string_t rows or u32 codes of
+// whole vectors, string_t of the keys of one dictionary chunk.
+cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream);
+cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream);
+cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t n_keys, cudaStream_t stream);
 #endif
 
 constexpr int kFlsWarpsPerCta = 8;

@@ -97,6 +97,8 @@ struct FlsDeviceState {
 	uint64_t image_bytes = 0;
 	FlsChunkDev* d_chunks = nullptr; // [rg * n_columns + col]
 	uint32_t* d_run_starts = nullptr; // CROSS_RLE: exclusive prefix sums of the run lengths, all chunks back to back
+	uint64_t* d_heap_prefix = nullptr; // string columns: [rg * n_columns + col] = 16-byte padded decoded bytes of the column's earlier chunks
+	std::vector<uint64_t> heap_prefix; // host copy (n_chunks + n_columns entries: the last row holds the column totals)
 	std::vector<uint8_t> chunk_resident; // [rg * n_columns + col]
 	uint64_t resident_bytes = 0;
 	bool host_pinned_tried = false;
@@ -126,6 +128,7 @@ void fls_device_release(flsgpu_table* t) {
 	cudaFree(d->d_image);
 	cudaFree(d->d_chunks);
 	cudaFree(d->d_run_starts);
+	cudaFree(d->d_heap_prefix);
 	if (d->host_registered) {
 		cudaHostUnregister(const_cast<uint8_t*>(t->bytes));
 	}
@@ -161,6 +164,7 @@ int device_state(flsgpu_table* t, FlsDeviceState** out) {
 		cudaFree(d->d_image);
 		cudaFree(d->d_chunks);
 		cudaFree(d->d_run_starts);
+		cudaFree(d->d_heap_prefix);
 		delete d;
 		return rc2;
 	}
@@ -204,6 +208,26 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 		}
 		FLS_CUDA(cudaMalloc(&d->d_run_starts, n_starts * sizeof(uint32_t)));
 		FLS_CUDA(cudaMemcpy(d->d_run_starts, starts.data(), n_starts * sizeof(uint32_t), cudaMemcpyHostToDevice));
+	}
+
+	// string heap layout: a chunk's decoded bytes start at the padded prefix sum of the column's chunks before it
+	bool any_string = false;
+	for (uint32_t c = 0; c < h.n_columns; ++c) {
+		any_string |= t->columns[c].phys_bits == 128;
+	}
+	if (any_string) {
+		d->heap_prefix.assign(n_chunks + h.n_columns, 0);
+		for (uint32_t c = 0; c < h.n_columns; ++c) {
+			uint64_t acc = 0;
+			for (uint32_t r = 0; r <= h.n_rowgroups; ++r) {
+				d->heap_prefix[(uint64_t)r * h.n_columns + c] = acc;
+				if (r < h.n_rowgroups && t->columns[c].phys_bits == 128) {
+					acc += (t->chunk(r, c).const_val + 15u) & ~15ull;
+				}
+			}
+		}
+		FLS_CUDA(cudaMalloc(&d->d_heap_prefix, d->heap_prefix.size() * sizeof(uint64_t)));
+		FLS_CUDA(cudaMemcpy(d->d_heap_prefix, d->heap_prefix.data(), d->heap_prefix.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
 	}
 
 	std::vector<FlsChunkDev> host_chunks(n_chunks);
@@ -441,6 +465,9 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
                        void* out_dev, cudaStream_t stream, flsgpu_agg_acc* agg = nullptr) {
 	const fls_file_header& h = t->header;
 	const int T = t->columns[col].phys_bits;
+	if (T == 128) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "string column: use flsgpu_decode_strings / flsgpu_decode_string_codes");
+	}
 	FlsColumnPlan p;
 	{
 		std::lock_guard<std::mutex> g(d->mu);
@@ -828,6 +855,223 @@ int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, ui
 	}
 	FLS_CUDA(fls_agg_finalize(acc, t->columns[col].is_signed, key_min, key_max, s));
 	return FLSGPU_OK;
+}
+
+// ---- string columns ------------------------------------------------------------------------------------------------
+namespace {
+
+int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const char* who, FlsDeviceState** dout,
+                        FlsStrLaunch* L) {
+	int rc = check_range(t, col, rg_begin, n_rg, who);
+	if (rc) {
+		return rc;
+	}
+	if (t->columns[col].phys_bits != 128) {
+		char msg[160];
+		std::snprintf(msg, sizeof(msg), "%s: column %u is not a string column", who, col);
+		return fls_set_error(FLSGPU_ERR_INVALID, msg);
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	rc = check_resident(t, d, col, rg_begin, n_rg);
+	if (rc) {
+		return rc;
+	}
+	const uint64_t i0 = (uint64_t)rg_begin * t->header.n_columns + col;
+	L->chunks = d->d_chunks + i0;
+	L->heap_prefix = d->d_heap_prefix + i0;
+	L->heap_prefix0 = d->heap_prefix[i0];
+	L->chunk_stride = t->header.n_columns;
+	L->vec_per_rg = t->header.vec_per_rowgroup;
+	L->n_rg = n_rg;
+	L->groups_per_rg = 0;
+	L->codes_only = 0;
+	*dout = d;
+	return FLSGPU_OK;
+}
+
+bool is_dict_string_enc(unsigned enc) {
+	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_FSST_DICT;
+}
+
+} // namespace
+
+int flsgpu_decode_strings(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings_dev,
+                          uint64_t out_capacity_bytes, void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr,
+                          void* cuda_stream) {
+	FlsDeviceState* d = nullptr;
+	FlsStrLaunch L {};
+	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_strings", &d, &L);
+	if (rc) {
+		return rc;
+	}
+	uint64_t heap_need = 0;
+	flsgpu_string_heap_bytes(t, col, rg_begin, n_rg, &heap_need);
+	const uint64_t need = (uint64_t)n_rg * t->header.vec_per_rowgroup * FLS_VEC_SZ * 16u;
+	if (!out_strings_dev || (reinterpret_cast<uintptr_t>(out_strings_dev) & 15u) || out_capacity_bytes < need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_strings: string_t buffer null, misaligned or too small");
+	}
+	if (!heap_dev || (reinterpret_cast<uintptr_t>(heap_dev) & 15u) || heap_capacity_bytes < heap_need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_strings: heap null, misaligned or smaller than flsgpu_string_heap_bytes");
+	}
+	L.heap = static_cast<uint8_t*>(heap_dev);
+	L.heap_base_addr = heap_base_addr;
+	L.out = out_strings_dev;
+	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+	FLS_CUDA(fls_str_launch_heap(L, s));
+	FLS_CUDA(fls_str_launch_rows(L, s));
+	g_launches.fetch_add(2, std::memory_order_relaxed);
+	return FLSGPU_OK;
+}
+
+int flsgpu_decode_string_codes(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint32_t* out_codes_dev,
+                               uint64_t out_capacity_bytes, void* cuda_stream) {
+	FlsDeviceState* d = nullptr;
+	FlsStrLaunch L {};
+	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_string_codes", &d, &L);
+	if (rc) {
+		return rc;
+	}
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		if (!is_dict_string_enc(t->chunk(r, col).encoding)) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_decode_string_codes: chunk is not dictionary encoded (decode it with flsgpu_decode_strings)");
+		}
+	}
+	const uint64_t need = (uint64_t)n_rg * t->header.vec_per_rowgroup * FLS_VEC_SZ * 4u;
+	if (!out_codes_dev || (reinterpret_cast<uintptr_t>(out_codes_dev) & 15u) || out_capacity_bytes < need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_string_codes: output buffer null, misaligned or too small");
+	}
+	L.out = out_codes_dev;
+	L.codes_only = 1;
+	FLS_CUDA(fls_str_launch_rows(L, static_cast<cudaStream_t>(cuda_stream)));
+	g_launches.fetch_add(1, std::memory_order_relaxed);
+	return FLSGPU_OK;
+}
+
+int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg, void* out_keys_dev, uint64_t keys_capacity_bytes,
+                              void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr, void* cuda_stream) {
+	FlsDeviceState* d = nullptr;
+	FlsStrLaunch L {};
+	int rc = string_launch_setup(t, col, rg, 1, "flsgpu_decode_string_dict", &d, &L);
+	if (rc) {
+		return rc;
+	}
+	const fls_chunk_desc& ch = t->chunk(rg, col);
+	if (!is_dict_string_enc(ch.encoding)) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_decode_string_dict: chunk is not dictionary encoded");
+	}
+	if (!out_keys_dev || (reinterpret_cast<uintptr_t>(out_keys_dev) & 15u) || keys_capacity_bytes < (uint64_t)ch.aux_count * 16u) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_string_dict: key buffer null, misaligned or too small");
+	}
+	if (!heap_dev || (reinterpret_cast<uintptr_t>(heap_dev) & 15u) || heap_capacity_bytes < ((ch.const_val + 15u) & ~15ull)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_string_dict: heap null, misaligned or too small");
+	}
+	L.heap = static_cast<uint8_t*>(heap_dev);
+	L.heap_base_addr = heap_base_addr;
+	L.out = out_keys_dev;
+	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+	FLS_CUDA(fls_str_launch_heap(L, s));
+	FLS_CUDA(fls_str_launch_keys(L, ch.aux_count, s));
+	g_launches.fetch_add(2, std::memory_order_relaxed);
+	return FLSGPU_OK;
+}
+
+int flsgpu_scan_strings_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings_host,
+                                uint64_t out_capacity_bytes, void* heap_host, uint64_t heap_capacity_bytes) {
+	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_scan_strings_to_host");
+	if (rc) {
+		return rc;
+	}
+	if (t->columns[col].phys_bits != 128) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_strings_to_host: not a string column");
+	}
+	uint64_t heap_need = 0;
+	flsgpu_string_heap_bytes(t, col, rg_begin, n_rg, &heap_need);
+	const uint64_t rg_bytes = (uint64_t)t->header.vec_per_rowgroup * FLS_VEC_SZ * 16u;
+	if (!out_strings_host || out_capacity_bytes < rg_bytes * n_rg || !heap_host || heap_capacity_bytes < heap_need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_strings_to_host: output buffer null or too small");
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	// slabs of row groups (~64 MiB of string_t + heap), alternating between two streams so that H2D, decode and D2H overlap
+	const uint64_t i0 = (uint64_t)rg_begin * t->header.n_columns + col;
+	const uint32_t n_cols = t->header.n_columns;
+	auto heap_off = [&](uint32_t r) { return d->heap_prefix[i0 + (uint64_t)r * n_cols] - d->heap_prefix[i0]; };
+	const uint64_t avg_rg = rg_bytes + heap_need / n_rg + 1;
+	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (64ull << 20) / avg_rg));
+	uint64_t slab_heap_max = 0;
+	for (uint32_t r = 0; r < n_rg; r += slab_rg) {
+		slab_heap_max = std::max(slab_heap_max, heap_off(std::min(n_rg, r + slab_rg)) - heap_off(r));
+	}
+	const uint64_t slab_bytes = rg_bytes * slab_rg + slab_heap_max + 16;
+	FlsScanScratch* sc = nullptr;
+	{
+		std::lock_guard<std::mutex> g(d->mu);
+		if (!d->scratch_free.empty()) {
+			sc = d->scratch_free.back();
+			d->scratch_free.pop_back();
+		} else {
+			sc = new FlsScanScratch();
+			d->scratch_all.push_back(sc);
+		}
+	}
+	struct Return {
+		FlsDeviceState* d;
+		FlsScanScratch* sc;
+		~Return() {
+			std::lock_guard<std::mutex> g(d->mu);
+			d->scratch_free.push_back(sc);
+		}
+	} ret {d, sc};
+	if (sc->out_bytes < slab_bytes) {
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaFree(sc->out[i]));
+			sc->out[i] = nullptr;
+			FLS_CUDA(cudaMalloc(&sc->out[i], slab_bytes));
+		}
+		sc->out_bytes = slab_bytes;
+	}
+	for (int i = 0; i < 2; ++i) {
+		if (!sc->streams[i]) {
+			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
+		}
+	}
+	int status = FLSGPU_OK;
+	uint32_t slab = 0;
+	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
+		const uint32_t n = std::min(slab_rg, n_rg - r);
+		cudaStream_t s = sc->streams[slab & 1];
+		{
+			std::lock_guard<std::mutex> g(d->mu);
+			status = stage_range(t, d, rg_begin + r, n, &col, 1, s);
+		}
+		if (status != FLSGPU_OK) {
+			break;
+		}
+		uint8_t* dev_rows = static_cast<uint8_t*>(sc->out[slab & 1]);
+		uint8_t* dev_heap = dev_rows + rg_bytes * slab_rg;
+		const uint64_t hoff = heap_off(r), hbytes = heap_off(r + n) - hoff;
+		uint8_t* host_heap = static_cast<uint8_t*>(heap_host) + hoff;
+		status = flsgpu_decode_strings(t, col, rg_begin + r, n, dev_rows, rg_bytes * n, dev_heap, hbytes + 16, reinterpret_cast<uint64_t>(host_heap), s);
+		if (status != FLSGPU_OK) {
+			break;
+		}
+		if (cudaMemcpyAsync(static_cast<uint8_t*>(out_strings_host) + (uint64_t)r * rg_bytes, dev_rows, rg_bytes * n, cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+		    (hbytes && cudaMemcpyAsync(host_heap, dev_heap, hbytes, cudaMemcpyDeviceToHost, s) != cudaSuccess)) {
+			status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
+		}
+	}
+	const cudaError_t e0 = cudaStreamSynchronize(sc->streams[0]), e1 = cudaStreamSynchronize(sc->streams[1]);
+	if (status == FLSGPU_OK && (e0 != cudaSuccess || e1 != cudaSuccess)) {
+		status = cuda_fail(e0 != cudaSuccess ? e0 : e1, "cudaStreamSynchronize");
+	}
+	return status;
 }
 
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {

@@ -1,0 +1,286 @@
+// flsgpu_kernels_str.cu — string column kernels (sm_100a): FSST decode, string heap fill, string_t materialisation,
+// dictionary codes (selection vectors).
+//
+// Replaces, for VARCHAR / BLOB columns, the reference materializer's string kernels
+// (reference src/include/reader/materializer/kernels/): uncompressed_kernel.hpp:26-38, constant_kernel.hpp:40-49,
+// dictionary_kernel.hpp:52-102, fsst_kernel.hpp:19-57, fsst_dict_kernel.hpp:20-80 — which build 1024 string_t per vector
+// with one heap allocation + one scalar fsst_decompress (duckdb/third_party/fsst/fsst.h:162-230) per string.
+//
+// Here a string column of a row-group range is decoded by two launches:
+//   1. fls_str_heap_kernel: every chunk's decoded bytes go to its slice of ONE string heap (the chunk's slice starts at the
+//      16-byte padded prefix sum of the chunks before it).  Plain encodings are a 16-byte-granule copy; FSST chunks are
+//      decoded in parallel: the per-string entry points (compressed end, decoded end) let every lane start at its own
+//      string, a lane decodes a run of consecutive strings = one contiguous sub-stream, assembles the output in a 64-bit
+//      register and writes aligned 8-byte words (only the first/last partial word of a lane's run is written bytewise,
+//      because it is shared with the neighbouring lane).  The 255-symbol table sits in shared memory.
+//   2. fls_str_rows_kernel: one warp per 1024-row vector builds DuckDB string_t (string_type.hpp:22-60,236-247): length,
+//      then 12 inlined bytes (zero padded) or 4 prefix bytes + pointer.  Pointers are heap_base_addr + offset, i.e. already
+//      valid for wherever the caller is going to place the heap (its own host buffer after the D2H copy, or the device heap).
+//      Dictionary encodings unpack their codes (same FFOR blobs as numeric DICT) through a per-warp shared-memory tile.
+// fls_str_codes_kernel emits the u32 selection vector of dictionary-encoded chunks (dictionary_kernel.hpp:80-101: the
+// reference hands DuckDB a DICTIONARY_VECTOR = keys + selection vector instead of flat strings).
+#include <cuda_runtime.h>
+
+#include "fls_launch.hpp"
+#include "fls_unpack.cuh"
+
+using namespace flsk;
+
+namespace {
+
+constexpr int kWarps = 8;
+constexpr uint32_t kTileStrings = 256; // strings per warp tile of the FSST decode (8 per lane)
+constexpr uint32_t kLaneStrings = kTileStrings / 32;
+
+__device__ __forceinline__ bool is_fsst(uint32_t enc) {
+	return enc == FLS_ENC_FSST || enc == FLS_ENC_FSST_DICT;
+}
+
+// One lane decodes the code stream [cbeg, cend) (relative to `in`, which is 4-byte aligned) to out[dbeg ...).
+// `out` is 8-byte aligned.  fsst.h:219-230 per code; output assembled in a register, flushed as aligned 64-bit words.
+__device__ __forceinline__ void fsst_decode_lane(const uint8_t* __restrict__ in, uint32_t cbeg, uint32_t cend, uint8_t* __restrict__ out,
+                                                 uint32_t dbeg, const unsigned long long* s_sym, const uint8_t* s_len) {
+	if (cbeg >= cend) {
+		return;
+	}
+	const uint32_t mis = dbeg & 7u;
+	unsigned long long* ow = reinterpret_cast<unsigned long long*>(out + (dbeg - mis));
+	unsigned long long acc = 0;
+	uint32_t fill = mis, head = mis; // head: low bytes of the first word that belong to the previous lane's strings
+	const uint32_t* inw = reinterpret_cast<const uint32_t*>(in);
+	uint32_t p = cbeg, widx = p >> 2;
+	uint32_t w = __ldg(inw + widx);
+	while (p < cend) {
+		if ((p >> 2) != widx) {
+			widx = p >> 2;
+			w = __ldg(inw + widx);
+		}
+		const uint32_t code = __byte_perm(w, 0, 0x4440u | (p & 3u));
+		++p;
+		unsigned long long sym;
+		uint32_t len;
+		if (code != FLS_FSST_ESC) {
+			sym = s_sym[code];
+			len = s_len[code];
+		} else {
+			if ((p >> 2) != widx) {
+				widx = p >> 2;
+				w = __ldg(inw + widx);
+			}
+			sym = __byte_perm(w, 0, 0x4440u | (p & 3u));
+			len = 1;
+			++p;
+		}
+		acc |= sym << (8u * fill);
+		uint32_t nf = fill + len;
+		if (nf >= 8u) {
+			if (head) {
+				uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
+				for (uint32_t k = head; k < 8u; ++k) {
+					ob[k] = (uint8_t)(acc >> (8u * k));
+				}
+				head = 0;
+			} else {
+				*ow = acc;
+			}
+			++ow;
+			nf -= 8u;
+			acc = nf ? (sym >> (8u * (len - nf))) : 0ull;
+		}
+		fill = nf;
+	}
+	uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
+	for (uint32_t k = head; k < fill; ++k) {
+		ob[k] = (uint8_t)(acc >> (8u * k));
+	}
+}
+
+// grid: n_rg * groups_per_rg CTAs of 8 warps; CTA (rg, g) takes tiles [8g, 8g + 8) of chunk rg (FSST) or the g-th share
+// of its bytes (plain copy).
+__global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrLaunch L) {
+	__shared__ unsigned long long s_sym[256];
+	__shared__ uint8_t s_len[256];
+	const uint32_t rg = blockIdx.x / L.groups_per_rg, g = blockIdx.x - rg * L.groups_per_rg;
+	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
+	const uint32_t enc = ch->encoding;
+	uint8_t* heap = L.heap + (L.heap_prefix[(size_t)rg * L.chunk_stride] - L.heap_prefix0);
+	if (is_fsst(enc)) {
+		const uint32_t n = ch->aux_count;
+		if ((uint64_t)g * kWarps * kTileStrings >= n) {
+			return;
+		}
+		{ // symbol table -> shared memory, symbols masked to their length so that OR-ing them into the output word is exact
+			const fls_fsst_table* tab = reinterpret_cast<const fls_fsst_table*>(ch->aux0);
+			const uint32_t c = threadIdx.x;
+			const uint32_t len = __ldg(&tab->len[c]);
+			const unsigned long long sym = __ldg(reinterpret_cast<const unsigned long long*>(&tab->symbol[c]));
+			s_sym[c] = len >= 8u ? sym : (sym & ((1ull << (8u * len)) - 1ull));
+			s_len[c] = (uint8_t)len;
+		}
+		__syncthreads();
+		const uint32_t* comp_end = reinterpret_cast<const uint32_t*>(ch->aux1);
+		const uint32_t* dec_end = comp_end + n;
+		const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+		const uint32_t first = (g * kWarps + warp) * kTileStrings + lane * kLaneStrings;
+		if (first >= n) {
+			return;
+		}
+		const uint32_t last = min(n, first + kLaneStrings) - 1u;
+		const uint32_t cbeg = first ? __ldg(comp_end + first - 1) : 0u, dbeg = first ? __ldg(dec_end + first - 1) : 0u;
+		const uint32_t cend = __ldg(comp_end + last);
+		fsst_decode_lane(ch->aux0 + sizeof(fls_fsst_table), cbeg, cend, heap, dbeg, s_sym, s_len);
+		return;
+	}
+	// plain bytes: STR_UNCOMPRESSED / DICT_STR / STR_CONSTANT
+	const uint64_t bytes = ch->const_val;
+	const uint64_t n_gran = (bytes + 15u) >> 4; // the heap slice is padded to 16 bytes, the source segment has 128 bytes of slack
+	const uint64_t per = (n_gran + L.groups_per_rg - 1) / L.groups_per_rg;
+	const uint64_t g0 = (uint64_t)g * per, g1 = min(n_gran, g0 + per);
+	const uint4* src = reinterpret_cast<const uint4*>(ch->aux0);
+	uint4* dst = reinterpret_cast<uint4*>(heap);
+	for (uint64_t i = g0 + threadIdx.x; i < g1; i += blockDim.x) {
+		dst[i] = __ldg(src + i);
+	}
+}
+
+// DuckDB string_t of the string at [start, start + len) of the chunk's heap slice (hp = device address of the slice,
+// haddr = the address the slice will have where the caller reads the strings).
+__device__ __forceinline__ uint4 make_string_t(const uint8_t* hp, uint64_t haddr, uint32_t start, uint32_t len) {
+	const uint32_t need = len <= 12u ? len : 4u;
+	const uint32_t a = start & ~3u, off = start & 3u, span = off + need;
+	const uint32_t* wp = reinterpret_cast<const uint32_t*>(hp + a);
+	const uint32_t w0 = span > 0u ? wp[0] : 0u, w1 = span > 4u ? wp[1] : 0u, w2 = span > 8u ? wp[2] : 0u, w3 = span > 12u ? wp[3] : 0u;
+	const uint32_t sh = off * 8u;
+	uint32_t b0 = __funnelshift_r(w0, w1, sh), b1 = __funnelshift_r(w1, w2, sh), b2 = __funnelshift_r(w2, w3, sh);
+	b0 &= need >= 4u ? 0xffffffffu : ((1u << (8u * need)) - 1u);
+	b1 &= need >= 8u ? 0xffffffffu : need > 4u ? ((1u << (8u * (need - 4u))) - 1u) : 0u;
+	b2 &= need >= 12u ? 0xffffffffu : need > 8u ? ((1u << (8u * (need - 8u))) - 1u) : 0u;
+	if (len <= 12u) {
+		return make_uint4(len, b0, b1, b2);
+	}
+	const uint64_t ptr = haddr + start;
+	return make_uint4(len, b0, (uint32_t)ptr, (uint32_t)(ptr >> 32));
+}
+
+template <int IT>
+__device__ __forceinline__ void codes_to_tile(const FlsChunkDev* ch, uint32_t vi, uint32_t lane, uint32_t* tile) {
+	const uint4* mp = reinterpret_cast<const uint4*>(ch->meta + vi);
+	const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
+	const uint32_t base = m0.x, W = (m1.x >> 16) & 0xffu;
+	const uint32_t* blob = reinterpret_cast<const uint32_t*>(ch->data + (size_t)m0.z * 16);
+	uint32_t v[32];
+	unpack_small_dispatch<IT>((int)W, blob, (int)lane, v);
+	const uint32_t n_keys = ch->aux_count;
+#pragma unroll
+	for (int i = 0; i < 32; ++i) {
+		tile[value_pos<IT>((int)lane, i)] = min(v[i] + base, n_keys - 1u); // clamp: never index outside the dictionary
+	}
+}
+
+__device__ __forceinline__ void vector_codes(const FlsChunkDev* ch, uint32_t vi, uint32_t lane, uint32_t* tile) {
+	const uint32_t ib = ch->idx_bits;
+	if (ib == 8) {
+		codes_to_tile<8>(ch, vi, lane, tile);
+	} else if (ib == 16) {
+		codes_to_tile<16>(ch, vi, lane, tile);
+	} else {
+		codes_to_tile<32>(ch, vi, lane, tile);
+	}
+	__syncwarp();
+}
+
+// one warp per vector: 1024 string_t (flat form), or the u32 codes (selection vector) when L.codes_only
+__global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrLaunch L) {
+	__shared__ uint32_t s_codes[kWarps][1024];
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const uint32_t v = blockIdx.x * kWarps + warp;
+	if (v >= L.n_rg * L.vec_per_rg) {
+		return;
+	}
+	const uint32_t rg = v / L.vec_per_rg, vi = v - rg * L.vec_per_rg;
+	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
+	if (vi >= ch->n_vec) {
+		return;
+	}
+	const uint32_t enc = ch->encoding;
+	const bool dict = enc == FLS_ENC_DICT_STR || enc == FLS_ENC_FSST_DICT;
+	if (L.codes_only) {
+		if (dict) {
+			uint32_t* tile = s_codes[warp];
+			vector_codes(ch, vi, lane, tile);
+			uint4* out = reinterpret_cast<uint4*>(static_cast<uint32_t*>(L.out) + (size_t)v * 1024u);
+			const uint4* t4 = reinterpret_cast<const uint4*>(tile);
+#pragma unroll
+			for (int it = 0; it < 8; ++it) {
+				out[it * 32 + lane] = t4[it * 32 + lane];
+			}
+		}
+		return;
+	}
+	const uint64_t hoff = L.heap_prefix[(size_t)rg * L.chunk_stride] - L.heap_prefix0;
+	const uint8_t* hp = L.heap + hoff;
+	const uint64_t haddr = L.heap_base_addr + hoff;
+	uint4* out = static_cast<uint4*>(L.out) + (size_t)v * 1024u;
+	const uint32_t* ends = reinterpret_cast<const uint32_t*>(ch->aux1) + (is_fsst(enc) ? ch->aux_count : 0u); // decoded end offsets
+	if (enc == FLS_ENC_STR_CONSTANT) {
+		const uint4 s = make_string_t(hp, haddr, 0, ch->aux_count);
+#pragma unroll 4
+		for (int it = 0; it < 32; ++it) {
+			out[it * 32 + lane] = s;
+		}
+	} else if (dict) {
+		uint32_t* tile = s_codes[warp];
+		vector_codes(ch, vi, lane, tile);
+#pragma unroll 2
+		for (int it = 0; it < 32; ++it) {
+			const uint32_t k = tile[it * 32 + lane];
+			const uint32_t start = k ? __ldg(ends + k - 1) : 0u, end = __ldg(ends + k);
+			out[it * 32 + lane] = make_string_t(hp, haddr, start, end - start);
+		}
+	} else { // STR_UNCOMPRESSED, FSST: one string per row
+		const uint32_t i0 = vi * 1024u;
+		uint32_t carry = i0 ? __ldg(ends + i0 - 1) : 0u; // end of the string before this warp step
+#pragma unroll 2
+		for (int it = 0; it < 32; ++it) {
+			const uint32_t end = __ldg(ends + i0 + it * 32 + lane);
+			uint32_t start = __shfl_up_sync(0xffffffffu, end, 1);
+			if (lane == 0) {
+				start = carry;
+			}
+			carry = __shfl_sync(0xffffffffu, end, 31);
+			out[it * 32 + lane] = make_string_t(hp, haddr, start, end - start);
+		}
+	}
+}
+
+// dictionary form: string_t of every key of ONE dictionary chunk (dictionary_kernel.hpp:60-78, fsst_dict_kernel.hpp:54-80)
+__global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L) {
+	const FlsChunkDev* ch = L.chunks;
+	const uint32_t n = ch->aux_count;
+	const uint32_t* ends = reinterpret_cast<const uint32_t*>(ch->aux1) + (is_fsst(ch->encoding) ? n : 0u);
+	uint4* out = static_cast<uint4*>(L.out);
+	for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+		const uint32_t start = k ? __ldg(ends + k - 1) : 0u, end = __ldg(ends + k);
+		out[k] = make_string_t(L.heap, L.heap_base_addr, start, end - start);
+	}
+}
+
+} // namespace
+
+cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream) {
+	// 8 tiles of 256 strings per CTA; a chunk has at most vec_per_rg * 1024 strings
+	L.groups_per_rg = (L.vec_per_rg * 1024u + kWarps * kTileStrings - 1u) / (kWarps * kTileStrings);
+	fls_str_heap_kernel<<<L.n_rg * L.groups_per_rg, kWarps * 32, 0, stream>>>(L);
+	return cudaGetLastError();
+}
+
+cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream) {
+	const uint32_t n_vec = L.n_rg * L.vec_per_rg;
+	fls_str_rows_kernel<<<(n_vec + kWarps - 1) / kWarps, kWarps * 32, 0, stream>>>(L);
+	return cudaGetLastError();
+}
+
+cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t n_keys, cudaStream_t stream) {
+	fls_str_keys_kernel<<<(n_keys + 255u) / 256u, 256, 0, stream>>>(L);
+	return cudaGetLastError();
+}

@@ -115,6 +115,8 @@ ABI_SYMBOLS = [
     "flsgpu_table_stage", "flsgpu_table_evict", "flsgpu_table_unstage", "flsgpu_table_resident_bytes", "flsgpu_decode_column",
     "flsgpu_rowgroup_decode", "flsgpu_aggregate_column", "flsgpu_agg_reset", "flsgpu_scan_column_to_host", "flsgpu_scan_columns_to_host",
     "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
+    "flsgpu_string_heap_bytes", "flsgpu_decode_strings", "flsgpu_decode_string_codes", "flsgpu_decode_string_dict",
+    "flsgpu_scan_strings_to_host",
 ]
 
 
@@ -287,6 +289,32 @@ class Table:
         pa = (C.c_void_p * n)(*[int(p) for p in out_host_ptrs])
         ba = (C.c_uint64 * n)(*out_bytes)
         _check(lib.flsgpu_scan_columns_to_host(self._h, ca, n, rg_begin, n_rg, ta, pa, ba), "scan_columns_to_host")
+
+    # ---- string columns (flsgpu.h "string columns") ----
+    def string_heap_bytes(self, col, rg_begin=0, n_rg=None):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        n = C.c_uint64()
+        _check(lib.flsgpu_string_heap_bytes(self._h, col, rg_begin, n_rg, C.byref(n)), "string_heap_bytes")
+        return n.value
+
+    def decode_strings(self, col, out_ptr, out_bytes, heap_ptr, heap_bytes, heap_base_addr, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_decode_strings(self._h, col, rg_begin, n_rg, _vp(out_ptr), C.c_uint64(out_bytes), _vp(heap_ptr),
+                                         C.c_uint64(heap_bytes), C.c_uint64(heap_base_addr), _vp(stream)), "decode_strings")
+
+    def decode_string_codes(self, col, out_ptr, out_bytes, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_decode_string_codes(self._h, col, rg_begin, n_rg, _vp(out_ptr), C.c_uint64(out_bytes), _vp(stream)),
+               "decode_string_codes")
+
+    def decode_string_dict(self, col, rg, keys_ptr, keys_bytes, heap_ptr, heap_bytes, heap_base_addr, stream=0):
+        _check(lib.flsgpu_decode_string_dict(self._h, col, rg, _vp(keys_ptr), C.c_uint64(keys_bytes), _vp(heap_ptr),
+                                             C.c_uint64(heap_bytes), C.c_uint64(heap_base_addr), _vp(stream)), "decode_string_dict")
+
+    def scan_strings_to_host(self, col, out_host_ptr, out_bytes, heap_host_ptr, heap_bytes, rg_begin=0, n_rg=None):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_scan_strings_to_host(self._h, col, rg_begin, n_rg, _vp(out_host_ptr), C.c_uint64(out_bytes),
+                                               _vp(heap_host_ptr), C.c_uint64(heap_bytes)), "scan_strings_to_host")
 
     def valid_mask_slices(self, rg_begin=0, n_rg=None):
         """(start, stop) element ranges of real tuples in the decode_column output layout."""

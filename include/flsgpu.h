@@ -120,6 +120,32 @@ int flsgpu_decode_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint3
 int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids, uint32_t n_cols,
                            void* const* out_ptrs, const int32_t* out_types, void* cuda_stream);
 
+/* ---- string columns (VARCHAR / BLOB): the materializer's string kernels ------------------------------------------ */
+/* The decoded element is DuckDB's 16-byte string_t (duckdb/common/types/string_type.hpp:22-60,236-247): u32 length, then
+ * 12 inlined bytes (zero padded) when length <= 12, else 4 prefix bytes + a pointer.  The bytes of non-inlined strings go
+ * to ONE string heap per call (the reference allocates per string: uncompressed_kernel.hpp:26-38, fsst_kernel.hpp:42-56);
+ * pointers are heap_base_addr + offset, so the caller decides where the heap is going to live (its own host buffer after
+ * a D2H copy, DuckDB's VectorStringBuffer, or the device heap itself: heap_base_addr = (uint64_t)heap_dev).
+ * Row layout as for flsgpu_decode_column (whole vectors; padding rows are empty strings or repeat the last code). */
+/* Bytes of heap a flat decode of [rg_begin, rg_begin + n_rg) needs: every chunk's decoded bytes, padded to 16. Host only. */
+int flsgpu_string_heap_bytes(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out);
+/* Flat materialisation: dec_fls_str_uncompressed_opr / dec_constant_str_opr / dec_fsst_opr / dec_fsst_dict_opr /
+ * dec_dict_opr<fls_string_t> -> string_t per row.  Two launches (heap fill incl. parallel FSST decode, then rows). */
+int flsgpu_decode_strings(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings_dev,
+                          uint64_t out_capacity_bytes, void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr,
+                          void* cuda_stream);
+/* Dictionary form, as the reference hands dictionary-encoded chunks to DuckDB (DICTIONARY_VECTOR: dictionary_kernel.hpp:
+ * 60-101, fsst_dict_kernel.hpp:54-80): the u32 selection vector of every row ... */
+int flsgpu_decode_string_codes(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint32_t* out_codes_dev,
+                               uint64_t out_capacity_bytes, void* cuda_stream);
+/* ... and the string_t of the keys of chunk (rg, col) (fls_chunk_desc.aux_count keys, const_val heap bytes).
+ * FLSGPU_ERR_UNSUPPORTED for chunks that are not DICT_STR / FSST_DICT (the reader then takes the flat form). */
+int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg, void* out_keys_dev, uint64_t keys_capacity_bytes,
+                              void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr, void* cuda_stream);
+/* Host to host: stage + decode + D2H of string_t rows and heap, pipelined in slabs; pointers refer to heap_host. */
+int flsgpu_scan_strings_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings_host,
+                                uint64_t out_capacity_bytes, void* heap_host, uint64_t heap_capacity_bytes);
+
 /* ---- fused decode + aggregate (SUM/COUNT/MIN/MAX over a scan) ---------------------------- */
 typedef struct flsgpu_agg_result { /* written to device memory, 64 bytes */
 	uint64_t sum_lo;  /* 128-bit two's complement sum (HUGEINT / DECIMAL(38) semantics, sum.cpp:161-210) */

@@ -70,6 +70,14 @@ def test_no_cpu_fallback_without_a_device():
         t.stage()
     assert e.value.status == -3  # FLSGPU_ERR_CUDA: the product never decodes on the CPU
     t.close()
+    # string columns: heap sizing is host metadata, every decode entry point needs the device
+    t = flsgpu.Table(flsgpu.write_table([("s", "VARCHAR", None)], [[b"Value %d" % (i % 10) for i in range(3000)]]))
+    assert t.string_heap_bytes(0) == sum((t.chunk(r, 0).const_val + 15) // 16 * 16 for r in range(t.n_rowgroups))
+    rows, heap = np.zeros((t.out_elems(t.n_rowgroups), 16), dtype=np.uint8), np.zeros(4096, dtype=np.uint8)
+    with pytest.raises(flsgpu.FlsError) as e:
+        t.scan_strings_to_host(0, rows.ctypes.data, rows.nbytes, heap.ctypes.data, heap.nbytes)
+    assert e.value.status == -3
+    t.close()
 
 
 def test_writer_rejects_bad_input():
