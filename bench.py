@@ -49,10 +49,27 @@ COLUMNS = [
     ("dec", "DECIMAL", None, lambda i: (i % 10_000_000) * 100, 10, 2),
     ("date", "DATE", None, lambda i: (8116 + (i % 10000)).astype(np.int32)),
     ("ts", "TIMESTAMP", None, lambda i: 1_735_689_600_000_000 + i * 1_000_000),
-    # VARCHAR 'Value ' || (i % 1000): a 1000-key dictionary; the scan decodes the codes (the reference emits a
-    # DICTIONARY_VECTOR = selection vector over a per-row-group dictionary, dictionary_kernel.hpp:89-100)
-    ("varchar_codes", "UINT16", "DICT", lambda i: (i % 1000).astype(np.uint16)),
+    # VARCHAR 'Value ' || (i % 1000): a true string column, 1000-key dictionary per row group (DICT_STR).  The scan emits
+    # what the reference hands DuckDB for such a chunk: a DICTIONARY_VECTOR = the keys' string_t + dictionary bytes once
+    # per row group and a u32 selection vector per row (dictionary_kernel.hpp:60-101)
+    ("varchar", "VARCHAR", None, lambda i: value_strings(i % 1000)),
 ]
+
+_VALUE_KEYS = [b"Value %d" % k for k in range(1000)]
+_VALUE_LEN = np.array([len(k) for k in _VALUE_KEYS], dtype=np.int64)
+_VALUE_MAT = np.zeros((1000, 9), dtype=np.uint8)
+for _k, _v in enumerate(_VALUE_KEYS):
+    _VALUE_MAT[_k, :len(_v)] = np.frombuffer(_v, dtype=np.uint8)
+
+
+def value_strings(k):
+    """(offsets, bytes) of 'Value <k>' for every element of k (vectorised: no Python string objects)."""
+    lens = _VALUE_LEN[k]
+    off = np.zeros(len(k) + 1, dtype=np.uint64)
+    np.cumsum(lens, out=off[1:])
+    mat = _VALUE_MAT[k]
+    data = mat[np.arange(9)[None, :] < lens[:, None]]
+    return off, np.ascontiguousarray(data)
 
 
 def build_table_image(n_rows, threads, batch_rows=64 * 65536):
@@ -88,6 +105,15 @@ def algorithmic_bytes(t, img, col):
     sz = cd.phys_bits // 8
     read = 0
     written = 0
+    if cd.phys_bits == 128:
+        # dictionary form: packed codes (128*W + 1 + 4 per vector) + dictionary bytes and end offsets read; u32 selection
+        # entries + the keys' string_t + dictionary bytes written
+        for r in range(t.n_rowgroups):
+            ch = t.chunk(r, col)
+            m = np.frombuffer(img, dtype=META_DT, count=ch.n_vec, offset=ch.offset + ch.seg_off[0])
+            read += int((128 * m["width"].astype(np.int64)).sum()) + ch.n_vec * 5 + ch.const_val + 4 * ch.aux_count
+            written += ch.n_vec * 4096 + 16 * ch.aux_count + ch.const_val
+        return read, written
     for r in range(t.n_rowgroups):
         ch = t.chunk(r, col)
         off = ch.offset + ch.seg_off[0]
@@ -248,10 +274,12 @@ def kernel_name(t, col):
         ch = t.chunk(r, col)
         e = flsgpu.ENC_NAME[ch.encoding]
         encs.add(e)
-        fams.add("dict%d" % ch.idx_bits if e == "DICT" else "rle" if e == "RLE" else "alp" if e == "ALP" else "alprd" if e == "ALP_RD"
+        fams.add("str_dict" if e in ("DICT_STR", "FSST_DICT") else "dict%d" % ch.idx_bits if e == "DICT" else "rle" if e == "RLE" else "alp" if e == "ALP" else "alprd" if e == "ALP_RD"
                  else "delta" if e == "DELTA" and ch.phys_bits == 64 else "light")
     T = t.column(col).phys_bits
     fams = sorted(fams)  # "delta": 64-bit DELTA chunks have their own instantiation
+    if fams == ["str_dict"]:
+        return "fls_str_kernels<dictionary form>", sorted(encs), 3  # heap fill + keys + codes
     if len(fams) == 1:
         return f"fls_decode_kernel<{fams[0]},T={T}>", sorted(encs), 1
     return f"mixed({'+'.join(fams)}),T={T}", sorted(encs), len(fams)
@@ -277,17 +305,29 @@ def run_gpu(args, rank, world, local_rank):
     t.stage(stream=stream)
     torch.cuda.synchronize()
 
-    widths = [t.column(c).phys_bits // 8 for c in range(n_cols)]
+    # string columns are scanned in dictionary form: 4-byte selection entries per row (+ keys and dictionary bytes per row group)
+    is_str = [t.column(c).phys_bits == 128 for c in range(n_cols)]
+    widths = [4 if is_str[c] else t.column(c).phys_bits // 8 for c in range(n_cols)]
     out_elems = t.out_elems(t.n_rowgroups)
     outs = [torch.empty(out_elems * wd, dtype=torch.uint8, device="cuda") for wd in widths]
     decoded_bytes = sum(t.n_tuples * wd for wd in widths)  # real tuples only (padding of the last vector excluded)
     compressed_bytes = t.resident_bytes()
+    str_keys, str_heap = {}, {}
+    for c in range(n_cols):
+        if is_str[c]:
+            str_keys[c] = torch.empty(max(16, t.string_dict_keys(c) * 16), dtype=torch.uint8, device="cuda")
+            str_heap[c] = torch.empty(max(16, t.string_heap_bytes(c)), dtype=torch.uint8, device="cuda")
 
     def scan_step(events=None):
         for c in range(n_cols):
             if events is not None:
                 events[c][0].record()
-            t.decode_column(c, outs[c].data_ptr(), outs[c].numel(), stream=stream)
+            if is_str[c]:
+                t.decode_string_dict(c, str_keys[c].data_ptr(), str_keys[c].numel(), str_heap[c].data_ptr(), str_heap[c].numel(),
+                                     str_heap[c].data_ptr(), stream=stream)
+                t.decode_string_codes(c, outs[c].data_ptr(), outs[c].numel(), stream=stream)
+            else:
+                t.decode_column(c, outs[c].data_ptr(), outs[c].numel(), stream=stream)
             if events is not None:
                 events[c][1].record()
 
@@ -318,12 +358,23 @@ def run_gpu(args, rank, world, local_rank):
 
     # ---- end to end: pinned host container -> H2D -> decode -> D2H into pinned host buffers, every step
     host_outs = [flsgpu.host_alloc(out_elems * wd) for wd in widths]
+    scan_cols, d2h_bytes = [], 0
+    for c in range(n_cols):
+        sc = flsgpu.ScanColumn(col=c, out_type=0, out_host=host_outs[c], out_capacity_bytes=out_elems * widths[c])
+        d2h_bytes += out_elems * widths[c]
+        if is_str[c]:  # dictionary form: selection vector + keys + dictionary bytes come back to the host
+            sc.string_form = flsgpu.STRING_DICTIONARY
+            sc.keys_capacity_bytes, sc.heap_capacity_bytes = str_keys[c].numel(), str_heap[c].numel()
+            sc.keys_host, sc.heap_host = flsgpu.host_alloc(sc.keys_capacity_bytes), flsgpu.host_alloc(sc.heap_capacity_bytes)
+            host_outs += [sc.keys_host, sc.heap_host]
+            d2h_bytes += t.string_dict_keys(c) * 16 + t.string_heap_bytes(c)
+        scan_cols.append(sc)
     e2e_times = []
     for s in range(1 + args.steps):
         t.evict()
         barrier()
         t0 = time.perf_counter()
-        t.scan_columns_to_host(list(range(n_cols)), host_outs, [out_elems * wd for wd in widths])
+        t.scan_projection_to_host(scan_cols)
         dt = time.perf_counter() - t0
         if s > 0:
             e2e_times.append(dt)
@@ -345,6 +396,13 @@ def run_gpu(args, rank, world, local_rank):
     # spot check of the e2e result against the generator (first and last rows of two columns)
     big = np.ctypeslib.as_array((__import__("ctypes").c_int64 * 4).from_address(host_outs[3]))
     assert list(big) == [10, 20, 30, 40], "e2e scan returned wrong data"
+    for c in range(n_cols):
+        if is_str[c]:  # first rows of the VARCHAR column through selection vector -> key string_t -> dictionary bytes
+            ct = __import__("ctypes")
+            sel = np.ctypeslib.as_array((ct.c_uint32 * 4).from_address(host_outs[c]))
+            keys = np.ctypeslib.as_array((ct.c_uint8 * (16 * 8)).from_address(scan_cols[c].keys_host)).view(flsgpu.STRING_T)
+            got = [keys[k]["body"][:int(keys[k]["length"])].tobytes() for k in sel]
+            assert got == [b"Value 1", b"Value 2", b"Value 3", b"Value 4"], got
 
     # ---- reduce over ranks: time = max, bytes = sum; reduced scan result (COUNT, SUM(int)) via NCCL
     tm = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device="cuda")
@@ -435,7 +493,7 @@ def run_gpu(args, rank, world, local_rank):
             "l2": "inputs + outputs per step exceed L2 (126 MB); no explicit flush", "table_build_s": round(build_s, 1)}),
         "values_per_s": round(all_rows * n_cols * args.steps / (total_ms / 1e3), 1),
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(compressed_bytes),
-                "d2h_bytes_per_step": int(sum(out_elems * wd for wd in widths)), "ms_per_step": round(e2e_s / args.steps * 1e3, 2), "pcie_measured": pcie},
+                "d2h_bytes_per_step": int(d2h_bytes), "ms_per_step": round(e2e_s / args.steps * 1e3, 2), "pcie_measured": pcie},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "per_column": per_column, "reduced_scan": {"query": "SELECT SUM(big), COUNT(*) over all shards (fused decode+aggregate, NCCL all-reduce of limbs)",
                                                      "count": red_count, "sum": str(red_sum), "fused_agg_ms_per_gpu": round(agg_ms, 4),

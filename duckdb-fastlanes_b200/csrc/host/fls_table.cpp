@@ -401,4 +401,20 @@ int flsgpu_string_heap_bytes(const flsgpu_table* t, uint32_t col, uint32_t rg_be
 	return FLSGPU_OK;
 }
 
+int flsgpu_string_dict_keys(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out) {
+	if (!t || !out || col >= t->header.n_columns || rg_begin > t->header.n_rowgroups || n_rg > t->header.n_rowgroups - rg_begin) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_string_dict_keys: column or row-group range out of bounds");
+	}
+	uint64_t total = 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		const fls_chunk_desc& ch = t->chunk(r, col);
+		if (ch.encoding != FLS_ENC_DICT_STR && ch.encoding != FLS_ENC_FSST_DICT) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_string_dict_keys: chunk is not dictionary encoded");
+		}
+		total += ch.aux_count;
+	}
+	*out = total;
+	return FLSGPU_OK;
+}
+
 } // extern "C"

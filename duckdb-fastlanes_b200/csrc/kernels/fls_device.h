@@ -55,6 +55,8 @@ struct FlsStrLaunch {
 	const FlsChunkDev* chunks;   // &chunk_dev[rg_begin * n_cols + col]
 	const uint64_t* heap_prefix; // &heap_prefix[rg_begin * n_cols + col]: 16-byte padded decoded bytes of the column's chunks before this one
 	uint64_t heap_prefix0;       // heap_prefix of row group rg_begin (the heap handed in starts there)
+	const uint64_t* key_prefix;  // &key_prefix[rg_begin * n_cols + col]: dictionary keys of the column's chunks before this one
+	uint64_t key_prefix0;
 	uint8_t* heap;               // device string heap, 16-byte aligned
 	uint64_t heap_base_addr;     // address the heap will have where the strings are consumed (string_t pointers)
 	void* out;                   // string_t[n_rg * vec_per_rg * 1024] | u32 codes | string_t[n_keys]
@@ -63,6 +65,7 @@ struct FlsStrLaunch {
 	uint32_t n_rg;
 	uint32_t groups_per_rg;      // heap kernel: CTAs per chunk (set by the launcher)
 	uint32_t codes_only;         // rows kernel: emit the u32 selection vector instead of string_t
+	uint32_t dict_only;          // heap kernel: fill only the slices of dictionary-encoded chunks
 };
 
 // Per-warp shared memory holding the 32 vector descriptors of a batch (64 B each), in front of the pipeline slots.

@@ -25,7 +25,7 @@ cudaError_t fls_agg_reset(flsgpu_agg_acc* acc, cudaStream_t stream);
 // whole vectors, string_t of the keys of one dictionary chunk.
 cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream);
 cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream);
-cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t n_keys, cudaStream_t stream);
+cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t max_keys_per_chunk, cudaStream_t stream);
 #endif
 
 constexpr int kFlsWarpsPerCta = 8;

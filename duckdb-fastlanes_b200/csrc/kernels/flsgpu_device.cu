@@ -99,6 +99,8 @@ struct FlsDeviceState {
 	uint32_t* d_run_starts = nullptr; // CROSS_RLE: exclusive prefix sums of the run lengths, all chunks back to back
 	uint64_t* d_heap_prefix = nullptr; // string columns: [rg * n_columns + col] = 16-byte padded decoded bytes of the column's earlier chunks
 	std::vector<uint64_t> heap_prefix; // host copy (n_chunks + n_columns entries: the last row holds the column totals)
+	uint64_t* d_key_prefix = nullptr;  // string columns: dictionary keys (DICT_STR / FSST_DICT aux_count) of the column's earlier chunks
+	std::vector<uint64_t> key_prefix;
 	std::vector<uint8_t> chunk_resident; // [rg * n_columns + col]
 	uint64_t resident_bytes = 0;
 	bool host_pinned_tried = false;
@@ -129,6 +131,7 @@ void fls_device_release(flsgpu_table* t) {
 	cudaFree(d->d_chunks);
 	cudaFree(d->d_run_starts);
 	cudaFree(d->d_heap_prefix);
+	cudaFree(d->d_key_prefix);
 	if (d->host_registered) {
 		cudaHostUnregister(const_cast<uint8_t*>(t->bytes));
 	}
@@ -165,6 +168,7 @@ int device_state(flsgpu_table* t, FlsDeviceState** out) {
 		cudaFree(d->d_chunks);
 		cudaFree(d->d_run_starts);
 		cudaFree(d->d_heap_prefix);
+		cudaFree(d->d_key_prefix);
 		delete d;
 		return rc2;
 	}
@@ -217,17 +221,23 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 	}
 	if (any_string) {
 		d->heap_prefix.assign(n_chunks + h.n_columns, 0);
+		d->key_prefix.assign(n_chunks + h.n_columns, 0);
 		for (uint32_t c = 0; c < h.n_columns; ++c) {
-			uint64_t acc = 0;
+			uint64_t acc = 0, keys = 0;
 			for (uint32_t r = 0; r <= h.n_rowgroups; ++r) {
 				d->heap_prefix[(uint64_t)r * h.n_columns + c] = acc;
+				d->key_prefix[(uint64_t)r * h.n_columns + c] = keys;
 				if (r < h.n_rowgroups && t->columns[c].phys_bits == 128) {
-					acc += (t->chunk(r, c).const_val + 15u) & ~15ull;
+					const fls_chunk_desc& ch = t->chunk(r, c);
+					acc += (ch.const_val + 15u) & ~15ull;
+					keys += (ch.encoding == FLS_ENC_DICT_STR || ch.encoding == FLS_ENC_FSST_DICT) ? ch.aux_count : 0u;
 				}
 			}
 		}
 		FLS_CUDA(cudaMalloc(&d->d_heap_prefix, d->heap_prefix.size() * sizeof(uint64_t)));
 		FLS_CUDA(cudaMemcpy(d->d_heap_prefix, d->heap_prefix.data(), d->heap_prefix.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
+		FLS_CUDA(cudaMalloc(&d->d_key_prefix, d->key_prefix.size() * sizeof(uint64_t)));
+		FLS_CUDA(cudaMemcpy(d->d_key_prefix, d->key_prefix.data(), d->key_prefix.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
 	}
 
 	std::vector<FlsChunkDev> host_chunks(n_chunks);
@@ -684,27 +694,52 @@ int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids
 	return FLSGPU_OK;
 }
 
-int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg,
-                                const int32_t* out_types, void* const* out_hosts, const uint64_t* out_capacity_bytes) {
-	if (!t || !col_ids || !out_hosts || !out_capacity_bytes || n_cols == 0) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_columns_to_host: null argument");
+// Pipelined host-to-host scan of a projection (numeric columns, flat strings, dictionary-form strings).
+int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg) {
+	if (!t || !cols || n_cols == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_projection_to_host: null argument");
 	}
-	std::vector<OutSpec> os(n_cols);
-	std::vector<uint64_t> rg_bytes(n_cols);
+	const fls_file_header& h = t->header;
+	struct ColPlan {
+		OutSpec os;
+		bool is_string = false, dict = false;
+		uint64_t rg_bytes = 0;            // row bytes per row group (values, string_t or selection entries)
+		uint64_t dev_rows = 0, dev_heap = 0, dev_keys = 0; // offsets inside a slab's device scratch
+	};
+	std::vector<ColPlan> cp(n_cols);
 	uint64_t rg_bytes_all = 0;
 	for (uint32_t i = 0; i < n_cols; ++i) {
-		int rc = check_range(t, col_ids[i], rg_begin, n_rg, "flsgpu_scan_columns_to_host");
+		const flsgpu_scan_column& c = cols[i];
+		int rc = check_range(t, c.col, rg_begin, n_rg, "flsgpu_scan_projection_to_host");
 		if (rc) {
 			return rc;
 		}
-		rc = resolve_out(t->columns[col_ids[i]], out_types ? out_types[i] : FLSGPU_OUT_NATIVE, &os[i]);
-		if (rc) {
-			return rc;
+		ColPlan& p = cp[i];
+		p.is_string = t->columns[c.col].phys_bits == 128;
+		if (p.is_string) {
+			p.dict = c.string_form == FLSGPU_STRING_DICTIONARY;
+			p.rg_bytes = (uint64_t)h.vec_per_rowgroup * FLS_VEC_SZ * (p.dict ? 4u : 16u);
+			uint64_t heap_need = 0, keys_need = 0;
+			flsgpu_string_heap_bytes(t, c.col, rg_begin, n_rg, &heap_need);
+			if (p.dict) {
+				rc = flsgpu_string_dict_keys(t, c.col, rg_begin, n_rg, &keys_need);
+				if (rc) {
+					return rc;
+				}
+			}
+			if (!c.heap_host || c.heap_capacity_bytes < heap_need || (p.dict && (!c.keys_host || c.keys_capacity_bytes < keys_need * 16u))) {
+				return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_projection_to_host: string heap / key buffer null or too small");
+			}
+		} else {
+			rc = resolve_out(t->columns[c.col], c.out_type, &p.os);
+			if (rc) {
+				return rc;
+			}
+			p.rg_bytes = (uint64_t)h.vec_per_rowgroup * FLS_VEC_SZ * p.os.ob;
 		}
-		rg_bytes[i] = (uint64_t)t->header.vec_per_rowgroup * FLS_VEC_SZ * os[i].ob;
-		rg_bytes_all += rg_bytes[i];
-		if (!out_hosts[i] || out_capacity_bytes[i] < rg_bytes[i] * n_rg) {
-			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_columns_to_host: output buffer null or too small");
+		rg_bytes_all += p.rg_bytes;
+		if (!c.out_host || c.out_capacity_bytes < p.rg_bytes * n_rg) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_projection_to_host: output buffer null or too small");
 		}
 	}
 	FlsDeviceState* d = nullptr;
@@ -712,10 +747,41 @@ int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32
 	if (rc) {
 		return rc;
 	}
+	auto heap_off = [&](uint32_t col, uint32_t r) { // bytes of heap before row group rg_begin + r, relative to the range
+		const uint64_t i0 = (uint64_t)rg_begin * h.n_columns + col;
+		return d->heap_prefix[i0 + (uint64_t)r * h.n_columns] - d->heap_prefix[i0];
+	};
+	auto key_off = [&](uint32_t col, uint32_t r) {
+		const uint64_t i0 = (uint64_t)rg_begin * h.n_columns + col;
+		return d->key_prefix[i0 + (uint64_t)r * h.n_columns] - d->key_prefix[i0];
+	};
 	// slabs of ~64 MiB decoded (all projected columns together): deep enough to hide launch latency, small enough
 	// that H2D, decode and D2H of neighbouring slabs overlap on the two streams
-	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (64ull << 20) / rg_bytes_all));
-	const uint64_t slab_bytes = rg_bytes_all * slab_rg;
+	uint64_t rg_avg = rg_bytes_all;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		if (cp[i].is_string) {
+			rg_avg += heap_off(cols[i].col, n_rg) / n_rg;
+		}
+	}
+	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (64ull << 20) / std::max<uint64_t>(1, rg_avg)));
+	uint64_t slab_bytes = 0;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		ColPlan& p = cp[i];
+		p.dev_rows = slab_bytes;
+		slab_bytes += p.rg_bytes * slab_rg;
+		if (p.is_string) {
+			uint64_t heap_max = 0, keys_max = 0;
+			for (uint32_t r = 0; r < n_rg; r += slab_rg) {
+				const uint32_t e = std::min(n_rg, r + slab_rg);
+				heap_max = std::max(heap_max, heap_off(cols[i].col, e) - heap_off(cols[i].col, r));
+				keys_max = std::max(keys_max, key_off(cols[i].col, e) - key_off(cols[i].col, r));
+			}
+			p.dev_heap = slab_bytes;
+			slab_bytes += heap_max + 16;
+			p.dev_keys = slab_bytes;
+			slab_bytes += p.dict ? keys_max * 16u + 16u : 0u;
+		}
+	}
 	FlsScanScratch* sc = nullptr;
 	{
 		std::lock_guard<std::mutex> g(d->mu);
@@ -748,24 +814,53 @@ int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32
 			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
 		}
 	}
+	std::vector<uint32_t> col_ids(n_cols);
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		col_ids[i] = cols[i].col;
+	}
 	uint32_t slab = 0;
 	int status = FLSGPU_OK;
+	auto d2h = [&](void* dst, const void* src, uint64_t bytes, cudaStream_t s) {
+		if (status == FLSGPU_OK && bytes && cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s) != cudaSuccess) {
+			status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
+		}
+	};
 	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
 		const uint32_t n = std::min(slab_rg, n_rg - r);
 		cudaStream_t s = sc->streams[slab & 1];
 		{
 			std::lock_guard<std::mutex> g(d->mu);
-			status = stage_range(t, d, rg_begin + r, n, col_ids, n_cols, s);
+			status = stage_range(t, d, rg_begin + r, n, col_ids.data(), n_cols, s);
 		}
-		uint8_t* dev = static_cast<uint8_t*>(sc->out[slab & 1]);
+		uint8_t* base = static_cast<uint8_t*>(sc->out[slab & 1]);
 		for (uint32_t i = 0; i < n_cols && status == FLSGPU_OK; ++i) {
-			status = decode_column_impl(t, d, col_ids[i], rg_begin + r, n, os[i], dev, s);
-			if (status == FLSGPU_OK &&
-			    cudaMemcpyAsync(static_cast<uint8_t*>(out_hosts[i]) + (uint64_t)r * rg_bytes[i], dev, rg_bytes[i] * n,
-			                    cudaMemcpyDeviceToHost, s) != cudaSuccess) {
-				status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
+			const flsgpu_scan_column& c = cols[i];
+			const ColPlan& p = cp[i];
+			uint8_t* dev = base + p.dev_rows;
+			uint8_t* host_rows = static_cast<uint8_t*>(c.out_host) + (uint64_t)r * p.rg_bytes;
+			if (!p.is_string) {
+				status = decode_column_impl(t, d, c.col, rg_begin + r, n, p.os, dev, s);
+				d2h(host_rows, dev, p.rg_bytes * n, s);
+				continue;
 			}
-			dev += rg_bytes[i] * slab_rg;
+			const uint64_t hoff = heap_off(c.col, r), hbytes = heap_off(c.col, r + n) - hoff;
+			uint8_t* host_heap = static_cast<uint8_t*>(c.heap_host) + hoff;
+			uint8_t* dev_heap = base + p.dev_heap;
+			if (p.dict) {
+				const uint64_t koff = key_off(c.col, r), kbytes = (key_off(c.col, r + n) - koff) * 16u;
+				uint8_t* dev_keys = base + p.dev_keys;
+				status = flsgpu_decode_string_dict(t, c.col, rg_begin + r, n, dev_keys, kbytes + 16, dev_heap, hbytes + 16,
+				                                   reinterpret_cast<uint64_t>(host_heap), s);
+				if (status == FLSGPU_OK) {
+					status = flsgpu_decode_string_codes(t, c.col, rg_begin + r, n, reinterpret_cast<uint32_t*>(dev), p.rg_bytes * n, s);
+				}
+				d2h(static_cast<uint8_t*>(c.keys_host) + koff * 16u, dev_keys, kbytes, s);
+			} else {
+				status = flsgpu_decode_strings(t, c.col, rg_begin + r, n, dev, p.rg_bytes * n, dev_heap, hbytes + 16,
+				                               reinterpret_cast<uint64_t>(host_heap), s);
+			}
+			d2h(host_rows, dev, p.rg_bytes * n, s);
+			d2h(host_heap, dev_heap, hbytes, s);
 		}
 	}
 	// always drain both streams before the scratch goes back to the pool
@@ -774,6 +869,25 @@ int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32
 		status = cuda_fail(e0 != cudaSuccess ? e0 : e1, "cudaStreamSynchronize");
 	}
 	return status;
+}
+
+int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg,
+                                const int32_t* out_types, void* const* out_hosts, const uint64_t* out_capacity_bytes) {
+	if (!t || !col_ids || !out_hosts || !out_capacity_bytes || n_cols == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_columns_to_host: null argument");
+	}
+	std::vector<flsgpu_scan_column> cols(n_cols);
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		if (col_ids[i] < t->header.n_columns && t->columns[col_ids[i]].phys_bits == 128) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_scan_columns_to_host: string column (use flsgpu_scan_projection_to_host)");
+		}
+		cols[i] = flsgpu_scan_column {};
+		cols[i].col = col_ids[i];
+		cols[i].out_type = out_types ? out_types[i] : FLSGPU_OUT_NATIVE;
+		cols[i].out_host = out_hosts[i];
+		cols[i].out_capacity_bytes = out_capacity_bytes[i];
+	}
+	return flsgpu_scan_projection_to_host(t, cols.data(), n_cols, rg_begin, n_rg);
 }
 
 int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type, void* out_host,
@@ -884,6 +998,9 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	L->chunks = d->d_chunks + i0;
 	L->heap_prefix = d->d_heap_prefix + i0;
 	L->heap_prefix0 = d->heap_prefix[i0];
+	L->key_prefix = d->d_key_prefix + i0;
+	L->key_prefix0 = d->key_prefix[i0];
+	L->dict_only = 0;
 	L->chunk_stride = t->header.n_columns;
 	L->vec_per_rg = t->header.vec_per_rowgroup;
 	L->n_rg = n_rg;
@@ -951,127 +1068,56 @@ int flsgpu_decode_string_codes(flsgpu_table* t, uint32_t col, uint32_t rg_begin,
 	return FLSGPU_OK;
 }
 
-int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg, void* out_keys_dev, uint64_t keys_capacity_bytes,
-                              void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr, void* cuda_stream) {
+int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_keys_dev,
+                              uint64_t keys_capacity_bytes, void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr,
+                              void* cuda_stream) {
 	FlsDeviceState* d = nullptr;
 	FlsStrLaunch L {};
-	int rc = string_launch_setup(t, col, rg, 1, "flsgpu_decode_string_dict", &d, &L);
+	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_string_dict", &d, &L);
 	if (rc) {
 		return rc;
 	}
-	const fls_chunk_desc& ch = t->chunk(rg, col);
-	if (!is_dict_string_enc(ch.encoding)) {
-		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_decode_string_dict: chunk is not dictionary encoded");
+	uint64_t n_keys = 0, heap_need = 0;
+	uint32_t max_keys = 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		const fls_chunk_desc& ch = t->chunk(r, col);
+		if (!is_dict_string_enc(ch.encoding)) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_decode_string_dict: chunk is not dictionary encoded (decode it with flsgpu_decode_strings)");
+		}
+		n_keys += ch.aux_count;
+		max_keys = std::max(max_keys, ch.aux_count);
+		heap_need += (ch.const_val + 15u) & ~15ull;
 	}
-	if (!out_keys_dev || (reinterpret_cast<uintptr_t>(out_keys_dev) & 15u) || keys_capacity_bytes < (uint64_t)ch.aux_count * 16u) {
+	if (!out_keys_dev || (reinterpret_cast<uintptr_t>(out_keys_dev) & 15u) || keys_capacity_bytes < n_keys * 16u) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_string_dict: key buffer null, misaligned or too small");
 	}
-	if (!heap_dev || (reinterpret_cast<uintptr_t>(heap_dev) & 15u) || heap_capacity_bytes < ((ch.const_val + 15u) & ~15ull)) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_string_dict: heap null, misaligned or too small");
+	if (!heap_dev || (reinterpret_cast<uintptr_t>(heap_dev) & 15u) || heap_capacity_bytes < heap_need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_decode_string_dict: heap null, misaligned or smaller than flsgpu_string_heap_bytes");
 	}
 	L.heap = static_cast<uint8_t*>(heap_dev);
 	L.heap_base_addr = heap_base_addr;
 	L.out = out_keys_dev;
+	L.dict_only = 1;
 	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
 	FLS_CUDA(fls_str_launch_heap(L, s));
-	FLS_CUDA(fls_str_launch_keys(L, ch.aux_count, s));
+	FLS_CUDA(fls_str_launch_keys(L, max_keys, s));
 	g_launches.fetch_add(2, std::memory_order_relaxed);
 	return FLSGPU_OK;
 }
 
 int flsgpu_scan_strings_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings_host,
                                 uint64_t out_capacity_bytes, void* heap_host, uint64_t heap_capacity_bytes) {
-	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_scan_strings_to_host");
-	if (rc) {
-		return rc;
-	}
-	if (t->columns[col].phys_bits != 128) {
+	if (!t || col >= t->header.n_columns || t->columns[col].phys_bits != 128) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_strings_to_host: not a string column");
 	}
-	uint64_t heap_need = 0;
-	flsgpu_string_heap_bytes(t, col, rg_begin, n_rg, &heap_need);
-	const uint64_t rg_bytes = (uint64_t)t->header.vec_per_rowgroup * FLS_VEC_SZ * 16u;
-	if (!out_strings_host || out_capacity_bytes < rg_bytes * n_rg || !heap_host || heap_capacity_bytes < heap_need) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_strings_to_host: output buffer null or too small");
-	}
-	FlsDeviceState* d = nullptr;
-	rc = device_state(t, &d);
-	if (rc) {
-		return rc;
-	}
-	// slabs of row groups (~64 MiB of string_t + heap), alternating between two streams so that H2D, decode and D2H overlap
-	const uint64_t i0 = (uint64_t)rg_begin * t->header.n_columns + col;
-	const uint32_t n_cols = t->header.n_columns;
-	auto heap_off = [&](uint32_t r) { return d->heap_prefix[i0 + (uint64_t)r * n_cols] - d->heap_prefix[i0]; };
-	const uint64_t avg_rg = rg_bytes + heap_need / n_rg + 1;
-	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, (64ull << 20) / avg_rg));
-	uint64_t slab_heap_max = 0;
-	for (uint32_t r = 0; r < n_rg; r += slab_rg) {
-		slab_heap_max = std::max(slab_heap_max, heap_off(std::min(n_rg, r + slab_rg)) - heap_off(r));
-	}
-	const uint64_t slab_bytes = rg_bytes * slab_rg + slab_heap_max + 16;
-	FlsScanScratch* sc = nullptr;
-	{
-		std::lock_guard<std::mutex> g(d->mu);
-		if (!d->scratch_free.empty()) {
-			sc = d->scratch_free.back();
-			d->scratch_free.pop_back();
-		} else {
-			sc = new FlsScanScratch();
-			d->scratch_all.push_back(sc);
-		}
-	}
-	struct Return {
-		FlsDeviceState* d;
-		FlsScanScratch* sc;
-		~Return() {
-			std::lock_guard<std::mutex> g(d->mu);
-			d->scratch_free.push_back(sc);
-		}
-	} ret {d, sc};
-	if (sc->out_bytes < slab_bytes) {
-		for (int i = 0; i < 2; ++i) {
-			FLS_CUDA(cudaFree(sc->out[i]));
-			sc->out[i] = nullptr;
-			FLS_CUDA(cudaMalloc(&sc->out[i], slab_bytes));
-		}
-		sc->out_bytes = slab_bytes;
-	}
-	for (int i = 0; i < 2; ++i) {
-		if (!sc->streams[i]) {
-			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
-		}
-	}
-	int status = FLSGPU_OK;
-	uint32_t slab = 0;
-	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
-		const uint32_t n = std::min(slab_rg, n_rg - r);
-		cudaStream_t s = sc->streams[slab & 1];
-		{
-			std::lock_guard<std::mutex> g(d->mu);
-			status = stage_range(t, d, rg_begin + r, n, &col, 1, s);
-		}
-		if (status != FLSGPU_OK) {
-			break;
-		}
-		uint8_t* dev_rows = static_cast<uint8_t*>(sc->out[slab & 1]);
-		uint8_t* dev_heap = dev_rows + rg_bytes * slab_rg;
-		const uint64_t hoff = heap_off(r), hbytes = heap_off(r + n) - hoff;
-		uint8_t* host_heap = static_cast<uint8_t*>(heap_host) + hoff;
-		status = flsgpu_decode_strings(t, col, rg_begin + r, n, dev_rows, rg_bytes * n, dev_heap, hbytes + 16, reinterpret_cast<uint64_t>(host_heap), s);
-		if (status != FLSGPU_OK) {
-			break;
-		}
-		if (cudaMemcpyAsync(static_cast<uint8_t*>(out_strings_host) + (uint64_t)r * rg_bytes, dev_rows, rg_bytes * n, cudaMemcpyDeviceToHost, s) != cudaSuccess ||
-		    (hbytes && cudaMemcpyAsync(host_heap, dev_heap, hbytes, cudaMemcpyDeviceToHost, s) != cudaSuccess)) {
-			status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
-		}
-	}
-	const cudaError_t e0 = cudaStreamSynchronize(sc->streams[0]), e1 = cudaStreamSynchronize(sc->streams[1]);
-	if (status == FLSGPU_OK && (e0 != cudaSuccess || e1 != cudaSuccess)) {
-		status = cuda_fail(e0 != cudaSuccess ? e0 : e1, "cudaStreamSynchronize");
-	}
-	return status;
+	flsgpu_scan_column c {};
+	c.col = col;
+	c.string_form = FLSGPU_STRING_FLAT;
+	c.out_host = out_strings_host;
+	c.out_capacity_bytes = out_capacity_bytes;
+	c.heap_host = heap_host;
+	c.heap_capacity_bytes = heap_capacity_bytes;
+	return flsgpu_scan_projection_to_host(t, &c, 1, rg_begin, n_rg);
 }
 
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {

@@ -104,6 +104,9 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
 	const uint32_t enc = ch->encoding;
 	uint8_t* heap = L.heap + (L.heap_prefix[(size_t)rg * L.chunk_stride] - L.heap_prefix0);
+	if (L.dict_only && enc != FLS_ENC_DICT_STR && enc != FLS_ENC_FSST_DICT) {
+		return;
+	}
 	if (is_fsst(enc)) {
 		const uint32_t n = ch->aux_count;
 		if ((uint64_t)g * kWarps * kTileStrings >= n) {
@@ -253,15 +256,22 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrL
 	}
 }
 
-// dictionary form: string_t of every key of ONE dictionary chunk (dictionary_kernel.hpp:60-78, fsst_dict_kernel.hpp:54-80)
+// dictionary form: string_t of every key of the dictionary chunks of the range (dictionary_kernel.hpp:60-78,
+// fsst_dict_kernel.hpp:54-80); chunk rg's keys start at key_prefix[rg] - key_prefix0.  grid: n_rg * groups_per_rg CTAs.
 __global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L) {
-	const FlsChunkDev* ch = L.chunks;
+	const uint32_t rg = blockIdx.x / L.groups_per_rg, g = blockIdx.x - rg * L.groups_per_rg;
+	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
+	const uint32_t enc = ch->encoding;
+	if (enc != FLS_ENC_DICT_STR && enc != FLS_ENC_FSST_DICT) {
+		return;
+	}
 	const uint32_t n = ch->aux_count;
-	const uint32_t* ends = reinterpret_cast<const uint32_t*>(ch->aux1) + (is_fsst(ch->encoding) ? n : 0u);
-	uint4* out = static_cast<uint4*>(L.out);
-	for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+	const uint32_t* ends = reinterpret_cast<const uint32_t*>(ch->aux1) + (is_fsst(enc) ? n : 0u);
+	const uint64_t hoff = L.heap_prefix[(size_t)rg * L.chunk_stride] - L.heap_prefix0;
+	uint4* out = static_cast<uint4*>(L.out) + (L.key_prefix[(size_t)rg * L.chunk_stride] - L.key_prefix0);
+	for (uint32_t k = g * blockDim.x + threadIdx.x; k < n; k += L.groups_per_rg * blockDim.x) {
 		const uint32_t start = k ? __ldg(ends + k - 1) : 0u, end = __ldg(ends + k);
-		out[k] = make_string_t(L.heap, L.heap_base_addr, start, end - start);
+		out[k] = make_string_t(L.heap + hoff, L.heap_base_addr + hoff, start, end - start);
 	}
 }
 
@@ -280,7 +290,9 @@ cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream) {
 	return cudaGetLastError();
 }
 
-cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t n_keys, cudaStream_t stream) {
-	fls_str_keys_kernel<<<(n_keys + 255u) / 256u, 256, 0, stream>>>(L);
+cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t max_keys_per_chunk, cudaStream_t stream) {
+	L.groups_per_rg = (uint32_t)((max_keys_per_chunk + 255u) / 256u);
+	L.groups_per_rg = L.groups_per_rg < 1u ? 1u : L.groups_per_rg > 64u ? 64u : L.groups_per_rg;
+	fls_str_keys_kernel<<<L.n_rg * L.groups_per_rg, 256, 0, stream>>>(L);
 	return cudaGetLastError();
 }

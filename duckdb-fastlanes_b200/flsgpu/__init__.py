@@ -39,6 +39,15 @@ class ColumnSpec(C.Structure):
                 ("decimal_scale", C.c_int32), ("force_encoding", C.c_int32)]
 
 
+class ScanColumn(C.Structure):  # flsgpu_scan_column
+    _fields_ = [("col", C.c_uint32), ("out_type", C.c_int32), ("string_form", C.c_int32), ("reserved", C.c_uint32),
+                ("out_host", C.c_void_p), ("out_capacity_bytes", C.c_uint64), ("heap_host", C.c_void_p),
+                ("heap_capacity_bytes", C.c_uint64), ("keys_host", C.c_void_p), ("keys_capacity_bytes", C.c_uint64)]
+
+
+STRING_FLAT, STRING_DICTIONARY = 0, 1
+
+
 class StringColumn(C.Structure):
     _fields_ = [("offsets", C.c_void_p), ("bytes", C.c_void_p)]
 
@@ -116,7 +125,7 @@ ABI_SYMBOLS = [
     "flsgpu_rowgroup_decode", "flsgpu_aggregate_column", "flsgpu_agg_reset", "flsgpu_scan_column_to_host", "flsgpu_scan_columns_to_host",
     "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
     "flsgpu_string_heap_bytes", "flsgpu_decode_strings", "flsgpu_decode_string_codes", "flsgpu_decode_string_dict",
-    "flsgpu_scan_strings_to_host",
+    "flsgpu_string_dict_keys", "flsgpu_scan_strings_to_host", "flsgpu_scan_projection_to_host",
 ]
 
 
@@ -307,14 +316,27 @@ class Table:
         _check(lib.flsgpu_decode_string_codes(self._h, col, rg_begin, n_rg, _vp(out_ptr), C.c_uint64(out_bytes), _vp(stream)),
                "decode_string_codes")
 
-    def decode_string_dict(self, col, rg, keys_ptr, keys_bytes, heap_ptr, heap_bytes, heap_base_addr, stream=0):
-        _check(lib.flsgpu_decode_string_dict(self._h, col, rg, _vp(keys_ptr), C.c_uint64(keys_bytes), _vp(heap_ptr),
+    def string_dict_keys(self, col, rg_begin=0, n_rg=None):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        n = C.c_uint64()
+        _check(lib.flsgpu_string_dict_keys(self._h, col, rg_begin, n_rg, C.byref(n)), "string_dict_keys")
+        return n.value
+
+    def decode_string_dict(self, col, keys_ptr, keys_bytes, heap_ptr, heap_bytes, heap_base_addr, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_decode_string_dict(self._h, col, rg_begin, n_rg, _vp(keys_ptr), C.c_uint64(keys_bytes), _vp(heap_ptr),
                                              C.c_uint64(heap_bytes), C.c_uint64(heap_base_addr), _vp(stream)), "decode_string_dict")
 
     def scan_strings_to_host(self, col, out_host_ptr, out_bytes, heap_host_ptr, heap_bytes, rg_begin=0, n_rg=None):
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_scan_strings_to_host(self._h, col, rg_begin, n_rg, _vp(out_host_ptr), C.c_uint64(out_bytes),
                                                _vp(heap_host_ptr), C.c_uint64(heap_bytes)), "scan_strings_to_host")
+
+    def scan_projection_to_host(self, scan_columns, rg_begin=0, n_rg=None):
+        """scan_columns: list of ScanColumn."""
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        arr = (ScanColumn * len(scan_columns))(*scan_columns)
+        _check(lib.flsgpu_scan_projection_to_host(self._h, arr, len(scan_columns), rg_begin, n_rg), "scan_projection_to_host")
 
     def valid_mask_slices(self, rg_begin=0, n_rg=None):
         """(start, stop) element ranges of real tuples in the decode_column output layout."""

@@ -138,10 +138,14 @@ int flsgpu_decode_strings(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint
  * 60-101, fsst_dict_kernel.hpp:54-80): the u32 selection vector of every row ... */
 int flsgpu_decode_string_codes(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint32_t* out_codes_dev,
                                uint64_t out_capacity_bytes, void* cuda_stream);
-/* ... and the string_t of the keys of chunk (rg, col) (fls_chunk_desc.aux_count keys, const_val heap bytes).
- * FLSGPU_ERR_UNSUPPORTED for chunks that are not DICT_STR / FSST_DICT (the reader then takes the flat form). */
-int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg, void* out_keys_dev, uint64_t keys_capacity_bytes,
-                              void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr, void* cuda_stream);
+/* ... and the string_t of the keys of every chunk of the range: chunk r's keys follow those of the range's earlier
+ * chunks (fls_chunk_desc.aux_count keys each; flsgpu_string_dict_keys gives the total), its dictionary bytes sit in its
+ * slice of the heap (same layout as the flat form).  FLSGPU_ERR_UNSUPPORTED when a chunk of the range is not
+ * DICT_STR / FSST_DICT (the reader then takes the flat form for that row group). */
+int flsgpu_string_dict_keys(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out);
+int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_keys_dev,
+                              uint64_t keys_capacity_bytes, void* heap_dev, uint64_t heap_capacity_bytes, uint64_t heap_base_addr,
+                              void* cuda_stream);
 /* Host to host: stage + decode + D2H of string_t rows and heap, pipelined in slabs; pointers refer to heap_host. */
 int flsgpu_scan_strings_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, void* out_strings_host,
                                 uint64_t out_capacity_bytes, void* heap_host, uint64_t heap_capacity_bytes);
@@ -171,6 +175,25 @@ int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin,
  * staged with merged copies, decoded and copied back together. out_hosts[i] receives column col_ids[i]. */
 int flsgpu_scan_columns_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg,
                                 const int32_t* out_types, void* const* out_hosts, const uint64_t* out_capacity_bytes);
+
+/* General projection (numeric columns and string columns in either form) through the same slab pipeline. */
+typedef enum flsgpu_string_form {
+	FLSGPU_STRING_FLAT = 0,      /* out_host: string_t per row; heap_host: string bytes */
+	FLSGPU_STRING_DICTIONARY = 1 /* out_host: u32 selection entry per row; keys_host: string_t per key; heap_host: dictionary bytes */
+} flsgpu_string_form;
+typedef struct flsgpu_scan_column {
+	uint32_t col;
+	int32_t out_type;           /* numeric columns: flsgpu_out_type */
+	int32_t string_form;        /* string columns: flsgpu_string_form */
+	uint32_t reserved;
+	void* out_host;             /* rows of the column, layout of flsgpu_decode_column */
+	uint64_t out_capacity_bytes;
+	void* heap_host;            /* string columns: >= flsgpu_string_heap_bytes; string_t pointers point into it */
+	uint64_t heap_capacity_bytes;
+	void* keys_host;            /* dictionary form: >= 16 * flsgpu_string_dict_keys */
+	uint64_t keys_capacity_bytes;
+} flsgpu_scan_column;
+int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg);
 
 int flsgpu_sync(void* cuda_stream);
 /* Pinned host allocations for staging / results (cudaHostAlloc). */

@@ -79,6 +79,11 @@ int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t 
 int fls_oracle_decode_string_dict(const fls_oracle_table* t, uint32_t col, uint32_t rg, void* out_keys, uint8_t* heap,
                                   uint64_t heap_base_addr);
 
+/* One vector of a per-row string chunk (STR_CONSTANT / STR_UNCOMPRESSED / FSST) as the reference materializer decodes it
+ * (string by string); -3 for dictionary encodings (those go through decode_string_dict + decode_codes). */
+int fls_oracle_decode_string_vector(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, void* out_strings,
+                                    uint8_t* heap, uint64_t heap_base_addr, uint64_t* heap_used);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,6 +5,7 @@
 #include "fls_oracle.h"
 
 #include <pthread.h>
+#include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -117,7 +118,13 @@ static void* worker(void* arg) {
 	const uint32_t vpr = t->header.vec_per_rowgroup;
 	uint64_t scratch[1024];
 	/* one 2048-row DuckDB chunk buffer per projected column (vector_size.hpp:16) */
-	uint64_t* chunkbuf = j->mode ? (uint64_t*)malloc((size_t)j->n_cols * 2048 * 8) : NULL;
+	/* (string columns: 16-byte string_t or 4-byte selection entries; the slot is sized for string_t) */
+	uint64_t* chunkbuf = j->mode ? (uint64_t*)malloc((size_t)j->n_cols * 2048 * 16) : NULL;
+	/* string columns: per-column dictionary (keys + bytes, rebuilt per row group like dictionary_kernel.hpp:60-78 Prepare)
+	 * and the per-chunk string heap of flat vectors (the reference allocates per string) */
+	uint8_t** str_keys = j->mode ? (uint8_t**)calloc(j->n_cols, sizeof(uint8_t*)) : NULL;
+	uint8_t** str_heap = j->mode ? (uint8_t**)calloc(j->n_cols, sizeof(uint8_t*)) : NULL;
+	uint64_t* str_cap = j->mode ? (uint64_t*)calloc((size_t)j->n_cols * 2, sizeof(uint64_t)) : NULL;
 	for (;;) {
 		/* TryAssignNextRowGroup: row groups are handed out one at a time (fls_reader.cpp:337-355) */
 		const uint32_t r = __atomic_fetch_add(j->next, 1, __ATOMIC_RELAXED);
@@ -144,13 +151,64 @@ static void* worker(void* arg) {
 		} else {
 			/* Scan: GetScanBatch takes <= 2 vectors per call (fls_reader.cpp:422-434), DecodePhysicalColumns visits
 			 * every projected column per vector (:436-472) with Pass::First / Pass::Second destinations */
+			/* InitializeColumnDecoders -> Prepare (fls_reader.cpp:382-420): string dictionaries are built once per row group */
+			for (uint32_t ci = 0; ci < j->n_cols; ++ci) {
+				const fls_column_desc* c = &t->columns[j->cols[ci]];
+				if (c->phys_bits != 128) {
+					continue;
+				}
+				const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + j->cols[ci]];
+				const int is_dict = ch->encoding == FLS_ENC_DICT_STR || ch->encoding == FLS_ENC_FSST_DICT;
+				const uint64_t need_keys = is_dict ? (uint64_t)ch->aux_count * 16 + 16 : 0;
+				const uint64_t need_heap = (is_dict ? ch->const_val : ch->encoding == FLS_ENC_STR_CONSTANT ? (uint64_t)ch->aux_count : ch->const_val) + 64;
+				if (str_cap[2 * ci] < need_keys) {
+					free(str_keys[ci]);
+					str_keys[ci] = (uint8_t*)malloc(need_keys);
+					str_cap[2 * ci] = need_keys;
+				}
+				if (str_cap[2 * ci + 1] < need_heap) {
+					free(str_heap[ci]);
+					str_heap[ci] = (uint8_t*)malloc(need_heap);
+					str_cap[2 * ci + 1] = need_heap;
+				}
+				if (is_dict) {
+					const int rc = fls_oracle_decode_string_dict(t, j->cols[ci], rg, str_keys[ci], str_heap[ci], (uint64_t)(uintptr_t)str_heap[ci]);
+					if (rc) {
+						j->rc = rc;
+						goto done;
+					}
+					j->checksum = fold((const uint64_t*)str_keys[ci], (size_t)ch->aux_count * 2, j->checksum);
+				}
+			}
 			for (uint32_t v0 = 0; v0 < n_vec; v0 += 2) {
 				const uint32_t nv = n_vec - v0 < 2 ? n_vec - v0 : 2;
 				for (uint32_t b = 0; b < nv; ++b) {
 					for (uint32_t ci = 0; ci < j->n_cols; ++ci) {
 						const fls_column_desc* c = &t->columns[j->cols[ci]];
+						if (c->phys_bits == 128) { /* string column: selection vector over the dictionary, or flat string_t */
+							const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + j->cols[ci]];
+							int rc;
+							if (ch->encoding == FLS_ENC_DICT_STR || ch->encoding == FLS_ENC_FSST_DICT) {
+								uint32_t* sel = (uint32_t*)(chunkbuf + (size_t)ci * 4096) + (size_t)b * 1024;
+								rc = fls_oracle_decode_codes(t, rg, j->cols[ci], v0 + b, sel);
+								j->checksum = fold((const uint64_t*)sel, 512, j->checksum);
+								j->bytes += 4096;
+							} else {
+								uint8_t* dst = (uint8_t*)(chunkbuf + (size_t)ci * 4096) + (size_t)b * 1024 * 16;
+								uint64_t used = 0;
+								rc = fls_oracle_decode_string_vector(t, rg, j->cols[ci], v0 + b, dst, str_heap[ci],
+								                                     (uint64_t)(uintptr_t)str_heap[ci], &used);
+								j->checksum = fold((const uint64_t*)str_heap[ci], used / 8, j->checksum);
+								j->bytes += 16384 + used;
+							}
+							if (rc) {
+								j->rc = rc;
+								goto done;
+							}
+							continue;
+						}
 						const size_t esz = (size_t)c->phys_bits / 8;
-						uint8_t* dst = (uint8_t*)(chunkbuf + (size_t)ci * 2048) + (size_t)b * 1024 * esz;
+						uint8_t* dst = (uint8_t*)(chunkbuf + (size_t)ci * 4096) + (size_t)b * 1024 * esz;
 						int tr = 0;
 						int rc = fls_oracle_decode_vector(t, rg, j->cols[ci], v0 + b, scratch, &tr);
 						if (!rc) {
@@ -158,21 +216,31 @@ static void* worker(void* arg) {
 						}
 						if (rc) {
 							j->rc = rc;
-							free(chunkbuf);
-							return NULL;
+							goto done;
 						}
 					}
 				}
 				for (uint32_t ci = 0; ci < j->n_cols; ++ci) {
+					if (t->columns[j->cols[ci]].phys_bits == 128) {
+						continue; /* counted above */
+					}
 					const size_t esz = (size_t)t->columns[j->cols[ci]].phys_bits / 8;
 					const size_t nbytes = (size_t)nv * 1024 * esz;
-					j->checksum = fold(chunkbuf + (size_t)ci * 2048, nbytes / 8, j->checksum);
+					j->checksum = fold(chunkbuf + (size_t)ci * 4096, nbytes / 8, j->checksum);
 					j->bytes += nbytes;
 				}
 			}
 		}
 	}
+done:
 	free(chunkbuf);
+	for (uint32_t ci = 0; str_keys && ci < j->n_cols; ++ci) {
+		free(str_keys[ci]);
+		free(str_heap[ci]);
+	}
+	free(str_keys);
+	free(str_heap);
+	free(str_cap);
 	return NULL;
 }
 

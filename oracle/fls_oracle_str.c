@@ -161,3 +161,56 @@ int fls_oracle_decode_string_dict(const fls_oracle_table* t, uint32_t col, uint3
 	}
 	return 0;
 }
+
+/* One vector of a per-row (non-dictionary) string chunk, the way the reference materializer does it: for every row of the
+ * vector, decode / copy the string into the vector's heap and build its string_t (uncompressed_kernel.hpp:26-38,
+ * constant_kernel.hpp:40-49, fsst_kernel.hpp:42-56: one fsst_decompress call per string).  heap must hold the vector's
+ * decoded bytes (at most the chunk's const_val, or 1024 x the constant's length); *heap_used returns them. */
+int fls_oracle_decode_string_vector(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, void* out_strings,
+                                    uint8_t* heap, uint64_t heap_base_addr, uint64_t* heap_used) {
+	if (col >= t->header.n_columns || rg >= t->header.n_rowgroups) {
+		return -1;
+	}
+	const fls_chunk_desc* ch = &t->chunks[(uint64_t)rg * t->header.n_columns + col];
+	if (vec >= ch->n_vec) {
+		return -1;
+	}
+	const uint8_t* aux0 = t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX0];
+	const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
+	ostr_t* out = (ostr_t*)out_strings;
+	uint64_t pos = 0;
+	const uint32_t i0 = vec * FLS_VEC_SZ;
+	switch (ch->encoding) {
+	case FLS_ENC_STR_CONSTANT:
+		memcpy(heap, aux0, ch->aux_count);
+		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+			make_string(&out[i], heap, ch->aux_count, heap_base_addr);
+		}
+		pos = ch->aux_count;
+		break;
+	case FLS_ENC_STR_UNCOMPRESSED:
+		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+			const uint32_t start = (i0 + i) ? aux1[i0 + i - 1] : 0, len = aux1[i0 + i] - start;
+			memcpy(heap + pos, aux0 + start, len);
+			make_string(&out[i], heap + pos, len, heap_base_addr + pos);
+			pos += len;
+		}
+		break;
+	case FLS_ENC_FSST: {
+		const fls_fsst_table* tab = (const fls_fsst_table*)aux0;
+		const uint8_t* codes = aux0 + sizeof(fls_fsst_table);
+		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+			const uint32_t cstart = (i0 + i) ? aux1[i0 + i - 1] : 0;
+			const uint64_t len = fls_oracle_fsst_decompress(tab, codes + cstart, aux1[i0 + i] - cstart, heap + pos);
+			make_string(&out[i], heap + pos, (uint32_t)len, heap_base_addr + pos);
+			pos += len;
+		}
+		break;
+	}
+	default: return -3;
+	}
+	if (heap_used) {
+		*heap_used = pos;
+	}
+	return 0;
+}

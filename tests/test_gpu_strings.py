@@ -88,26 +88,38 @@ def test_dictionary_form_matches_oracle():
         t.decode_string_codes(col, codes.data_ptr(), codes.numel() * 4)
         flsgpu.sync()
         codes = codes.cpu().numpy().view(np.uint32)
-        row0 = 0
+        # all dictionaries of the column in one call: keys back to back, dictionary bytes in the chunks' heap slices
+        n_keys, hb = t.string_dict_keys(col), t.string_heap_bytes(col)
+        keys = torch.zeros((n_keys * 16,), dtype=torch.uint8, device="cuda")
+        heap = torch.zeros((max(16, hb),), dtype=torch.uint8, device="cuda")
+        t.decode_string_dict(col, keys.data_ptr(), keys.numel(), heap.data_ptr(), heap.numel(), HEAP_BASE)
+        flsgpu.sync()
+        all_keys = keys.cpu().numpy().reshape(-1, 16)
+        all_heap = heap.cpu().numpy()
+        row0 = k0 = h0 = 0
         for rg in range(t.n_rowgroups):
             ch = t.chunk(rg, col)
-            exp_keys, exp_heap = o.decode_string_dict(col, rg, ch.aux_count, ch.const_val, HEAP_BASE)
-            keys = torch.zeros((ch.aux_count * 16,), dtype=torch.uint8, device="cuda")
-            heap = torch.zeros((max(16, (ch.const_val + 15) // 16 * 16),), dtype=torch.uint8, device="cuda")
-            t.decode_string_dict(col, rg, keys.data_ptr(), keys.numel(), heap.data_ptr(), heap.numel(), HEAP_BASE)
-            flsgpu.sync()
-            got_keys = keys.cpu().numpy().reshape(-1, 16)
-            got_heap = heap.cpu().numpy()
+            exp_keys, exp_heap = o.decode_string_dict(col, rg, ch.aux_count, ch.const_val, HEAP_BASE + h0)
+            got_keys = all_keys[k0:k0 + ch.aux_count]
+            got_heap = all_heap[h0:h0 + ch.const_val]
             assert got_keys.tobytes() == exp_keys.tobytes()
-            assert got_heap[:ch.const_val].tobytes() == exp_heap[:ch.const_val].tobytes()
+            assert got_heap.tobytes() == exp_heap[:ch.const_val].tobytes()
+            # single row group form: same keys, heap starting at this chunk
+            k1 = torch.zeros((ch.aux_count * 16,), dtype=torch.uint8, device="cuda")
+            h1 = torch.zeros((max(16, (ch.const_val + 15) // 16 * 16),), dtype=torch.uint8, device="cuda")
+            t.decode_string_dict(col, k1.data_ptr(), k1.numel(), h1.data_ptr(), h1.numel(), HEAP_BASE + h0, rg, 1)
+            flsgpu.sync()
+            assert k1.cpu().numpy().tobytes() == exp_keys.tobytes()
             for v in range(ch.n_vec):
                 a = (rg * t.vec_per_rowgroup + v) * 1024
                 assert codes[a:a + 1024].tolist() == o.decode_codes(rg, col, v).tolist()
             n = t.rowgroup(rg).n_tuples
-            kk = flsgpu.strings_from(got_keys.copy().view(flsgpu.STRING_T).reshape(-1), got_heap, HEAP_BASE)
+            kk = flsgpu.strings_from(got_keys.copy().view(flsgpu.STRING_T).reshape(-1), got_heap, HEAP_BASE + h0)
             a = rg * t.vec_per_rowgroup * 1024
             assert [kk[c] for c in codes[a:a + n]] == src[row0:row0 + n]
             row0 += n
+            k0 += ch.aux_count
+            h0 += (ch.const_val + 15) // 16 * 16
     # chunks that are not dictionary encoded have no dictionary form
     buf = torch.zeros((t.out_elems(t.n_rowgroups),), dtype=torch.int32, device="cuda")
     with pytest.raises(flsgpu.FlsError):
@@ -169,3 +181,50 @@ def test_long_strings_and_wide_dictionaries():
             got += flsgpu.strings_from(st[a:b], got_heap, HEAP_BASE)
         assert got == vals
         t.close()
+
+
+def test_projection_scan_mixes_numeric_flat_and_dictionary_strings():
+    """flsgpu_scan_projection_to_host: one pipelined scan returns an integer column, a flat FSST string column and a
+    dictionary-form string column; everything equals the oracle / the input."""
+    import ctypes as C
+    n = 3 * 65536 + 999
+    ids = np.arange(n, dtype=np.int64) * 3
+    comments = str_cases.comment_like(n, seed=9)
+    modes = [[b"AIR", b"RAIL", b"TRUCK", b"REG AIR", b"SHIP", b"FOB", b"MAIL"][i % 7] for i in range(n)]
+    img = flsgpu.write_table([("id", "INT64", None), ("c", "VARCHAR", "FSST"), ("m", "VARCHAR", "DICT_STR")], [ids, comments, modes])
+    t = flsgpu.Table(img)
+    rows = t.out_elems(t.n_rowgroups)
+    out_id = np.zeros(rows, dtype=np.int64)
+    out_c = np.zeros((rows, 16), dtype=np.uint8)
+    heap_c = np.zeros(max(16, t.string_heap_bytes(1)), dtype=np.uint8)
+    out_m = np.zeros(rows, dtype=np.uint32)
+    keys_m = np.zeros((t.string_dict_keys(2), 16), dtype=np.uint8)
+    heap_m = np.zeros(max(16, t.string_heap_bytes(2)), dtype=np.uint8)
+    cols = [
+        flsgpu.ScanColumn(col=0, out_host=out_id.ctypes.data, out_capacity_bytes=out_id.nbytes),
+        flsgpu.ScanColumn(col=1, string_form=flsgpu.STRING_FLAT, out_host=out_c.ctypes.data, out_capacity_bytes=out_c.nbytes,
+                          heap_host=heap_c.ctypes.data, heap_capacity_bytes=heap_c.nbytes),
+        flsgpu.ScanColumn(col=2, string_form=flsgpu.STRING_DICTIONARY, out_host=out_m.ctypes.data, out_capacity_bytes=out_m.nbytes,
+                          heap_host=heap_m.ctypes.data, heap_capacity_bytes=heap_m.nbytes, keys_host=keys_m.ctypes.data,
+                          keys_capacity_bytes=keys_m.nbytes),
+    ]
+    t.scan_projection_to_host(cols)
+    sl = t.valid_mask_slices()
+    assert np.concatenate([out_id[a:b] for a, b in sl]).tobytes() == ids.tobytes()
+    st = out_c.view(flsgpu.STRING_T).reshape(-1)
+    got = []
+    for a, b in sl:
+        got += flsgpu.strings_from(st[a:b], heap_c, heap_c.ctypes.data)
+    assert got == comments
+    km = keys_m.view(flsgpu.STRING_T).reshape(-1)
+    k0, got = 0, []
+    for rg, (a, b) in enumerate(sl):
+        nk = t.chunk(rg, 2).aux_count
+        kk = flsgpu.strings_from(km[k0:k0 + nk], heap_m, heap_m.ctypes.data)
+        got += [kk[c] for c in out_m[a:b]]
+        k0 += nk
+    assert got == modes
+    # numeric-only entry point refuses string columns
+    with pytest.raises(flsgpu.FlsError):
+        t.scan_columns_to_host([1], [out_c.ctypes.data], [out_c.nbytes])
+    t.close()
