@@ -128,7 +128,8 @@ __device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
 		const uint32_t r = v / L.vec_per_rg, vi = v - r * L.vec_per_rg;
 		const FlsChunkDev* ch = L.chunks + (size_t)r * L.chunk_stride;
 		const uint32_t enc = ch->encoding;
-		if (vi < ch->n_vec && ((L.family_mask >> enc) & 1u) && (L.idx_bits == 0 || ch->idx_bits == L.idx_bits)) {
+		if (vi < ch->n_vec && ((L.family_mask >> enc) & 1u) && (L.idx_bits == 0 || ch->idx_bits == L.idx_bits) &&
+		    (L.rg_keep == nullptr || L.rg_keep[r])) {
 			const uint4* mp = reinterpret_cast<const uint4*>(ch->meta + vi);
 			const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
 			// fls_vec_meta: base(8) data_off16(4) aux_off(4) | aux_cnt(2) width(1) width2(1) e(1) f(1) n_valid(2) reserved(8)
@@ -296,6 +297,105 @@ struct AggPartial {
 			hi -= (is_signed && (long long)u < 0) ? 1 : 0;
 		}
 		cnt += n_valid > (uint32_t)lane ? (n_valid - lane + 31u) / 32u : 0u;
+	}
+
+	// Filter pushdown: value i of the natural-order tile as the 64-bit comparison domain of its column.
+	template <int VT>
+	static __device__ __forceinline__ unsigned long long tile_value(const uint8_t* tile, uint32_t i, uint32_t is_signed) {
+		if constexpr (VT == 8) {
+			const unsigned long long u = tile[i];
+			return is_signed ? (unsigned long long)(long long)(int8_t)u : u;
+		} else if constexpr (VT == 16) {
+			const unsigned long long u = reinterpret_cast<const uint16_t*>(tile)[i];
+			return is_signed ? (unsigned long long)(long long)(int16_t)u : u;
+		} else if constexpr (VT == 32) {
+			const uint32_t w = reinterpret_cast<const uint32_t*>(tile)[i];
+			return is_signed ? (unsigned long long)(long long)(int32_t)w : w;
+		} else {
+			return reinterpret_cast<const unsigned long long*>(tile)[i];
+		}
+	}
+
+	// DuckDB comparison semantics (ConstantFilter, duckdb/planner/filter/constant_filter.hpp): integers in their own
+	// signedness; floating point with NaN equal to itself and greater than everything else.
+	template <int VT>
+	static __device__ __forceinline__ bool compare(unsigned long long v, unsigned long long c, uint32_t op, uint32_t is_signed, uint32_t is_float) {
+		int lt, eq; // v < c, v == c
+		if (is_float) {
+			double a, b;
+			if constexpr (VT == 32) {
+				a = (double)__uint_as_float((uint32_t)v);
+				b = (double)__uint_as_float((uint32_t)c);
+			} else {
+				a = __longlong_as_double((long long)v);
+				b = __longlong_as_double((long long)c);
+			}
+			const bool an = a != a, bn = b != b;
+			eq = (an && bn) || (!an && !bn && a == b);
+			lt = an ? 0 : (bn ? 1 : (a < b));
+		} else if (is_signed) {
+			lt = (long long)v < (long long)c;
+			eq = v == c;
+		} else {
+			lt = v < c;
+			eq = v == c;
+		}
+		switch (op) {
+		case 0: return eq;
+		case 1: return !eq;
+		case 2: return lt;
+		case 3: return lt || eq;
+		case 4: return !lt && !eq;
+		default: return !lt;
+		}
+	}
+
+	// mask words of one vector: bit `lane` of word `it` = row it*32 + lane passes (rows >= n_valid never pass)
+	template <int VT>
+	static __device__ __forceinline__ void build_mask(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float,
+	                                                  uint32_t op, unsigned long long c, bool and_into, uint32_t* mask_vec) {
+		uint32_t mine = 0;
+#pragma unroll 4
+		for (uint32_t it = 0; it < 32u; ++it) {
+			const uint32_t i = it * 32u + lane;
+			const bool pass = i < n_valid && compare<VT>(tile_value<VT>(tile, i, is_signed && !is_float), c, op, is_signed, is_float);
+			const uint32_t word = __ballot_sync(0xffffffffu, pass);
+			if ((uint32_t)lane == it) {
+				mine = word;
+			}
+		}
+		mask_vec[lane] = and_into ? (mask_vec[lane] & mine) : mine;
+	}
+
+	// SUM / COUNT over the rows of the tile whose mask bit is set
+	template <int VT>
+	__device__ __forceinline__ void fold_masked(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float,
+	                                            const uint32_t* mask_vec) {
+		const uint32_t my_word = __ldg(mask_vec + lane);
+		if (__ballot_sync(0xffffffffu, my_word != 0u) == 0u) {
+			return;
+		}
+#pragma unroll 4
+		for (uint32_t it = 0; it < 32u; ++it) {
+			const uint32_t word = __shfl_sync(0xffffffffu, my_word, it);
+			const uint32_t i = it * 32u + lane;
+			if (!((word >> lane) & 1u) || i >= n_valid) {
+				continue;
+			}
+			++cnt;
+			if (is_float) {
+				if constexpr (VT == 32) {
+					fs += (double)__uint_as_float(reinterpret_cast<const uint32_t*>(tile)[i]);
+				} else if constexpr (VT == 64) {
+					fs += __longlong_as_double((long long)reinterpret_cast<const unsigned long long*>(tile)[i]);
+				}
+				continue;
+			}
+			const unsigned long long u = tile_value<VT>(tile, i, is_signed);
+			lo += u;
+			hi += (lo < u) ? 1 : 0;
+			hi -= (is_signed && (long long)u < 0) ? 1 : 0;
+		}
 	}
 
 	// ---- register fast path: the 32 values a thread holds right after decoding (vector complete, no exceptions) -------

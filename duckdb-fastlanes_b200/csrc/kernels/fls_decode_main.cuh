@@ -519,7 +519,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
 			// aggregate fast path: complete vector, no exceptions, an encoding whose values end up in registers
 			const uint32_t enc_k = d.misc >> 24;
-			const bool agg_fast = AGG && MODE == 0 && (d.vec_in_chunk >> 16) == 1024u && (d.misc & 0xffffu) == 0u &&
+			const bool agg_fast = AGG && MODE == 0 && L.mask_mode == 0u && (d.vec_in_chunk >> 16) == 1024u && (d.misc & 0xffffu) == 0u &&
 			                      enc_k != FLS_ENC_UNCOMPRESSED && enc_k != FLS_ENC_CONSTANT && enc_k != FLS_ENC_CROSS_RLE;
 			if constexpr (MODE == 1) {
 				process_dict<T, VT, OB>(d, sp, out_vec, lane, L.conv);
@@ -534,7 +534,16 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			}
 			__syncwarp(); // all lanes are done reading the slot (and the staging area)
 			if constexpr (AGG) {
-				if (!agg_fast) {
+				if (L.mask_mode != 0u) { // filter pushdown: the tile holds the vector in natural order
+					uint32_t* mask_vec = L.mask + (size_t)vk * 32u;
+					if (L.mask_mode == 3u) {
+						part.template fold_masked<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float, mask_vec);
+					} else {
+						AggPartial::template build_mask<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float, L.cmp_op, L.cmp_const,
+						                                    L.mask_mode == 2u, mask_vec);
+					}
+					__syncwarp();
+				} else if (!agg_fast) {
 					part.template fold<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float);
 					__syncwarp();
 				}
@@ -556,7 +565,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 		}
 	}
 	if constexpr (AGG) {
-		part.flush(L.agg, lane, L.agg_float);
+		if (L.mask_mode == 0u || L.mask_mode == 3u) {
+			part.flush(L.agg, lane, L.agg_float);
+		}
 	}
 }
 

@@ -48,6 +48,12 @@ struct FlsLaunch {
 	flsgpu_agg_acc* agg;
 	uint32_t agg_signed; // integer columns: 1 = two's complement values
 	uint32_t agg_float;  // 1 = FLOAT/DOUBLE column (fsum + count only)
+	// filter pushdown (aggregate-family launches only; FilterExecutor::Apply, reference filter_executor.cpp:19-60)
+	uint32_t mask_mode;  // 0: none; 1: mask = cmp; 2: mask &= cmp; 3: aggregate only rows whose mask bit is set
+	uint32_t cmp_op;     // flsgpu_cmp
+	uint64_t cmp_const;  // physical bits of the constant (integers sign/zero-extended to 64, float/double raw bits)
+	uint32_t* mask;      // [total_vecs * 32] words: bit i of word w of vector v = row v*1024 + w*32 + i
+	const uint8_t* rg_keep; // per row group of the range: 0 = pruned by its zone map (skipped), or nullptr
 };
 
 // Launch parameters of the string kernels (flsgpu_kernels_str.cu): column `col` of row groups [rg_begin, rg_begin + n_rg).

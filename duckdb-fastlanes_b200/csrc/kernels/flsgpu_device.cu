@@ -471,8 +471,15 @@ int resolve_out(const fls_column_desc& col, int32_t out_type, OutSpec* o) {
 	return FLSGPU_OK;
 }
 
+struct MaskSpec { // filter pushdown on aggregate-family launches (FlsLaunch.mask_mode)
+	uint32_t mode = 0, op = 0;
+	uint64_t constant = 0;
+	uint32_t* mask = nullptr;
+	const uint8_t* rg_keep = nullptr;
+};
+
 int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const OutSpec& os,
-                       void* out_dev, cudaStream_t stream, flsgpu_agg_acc* agg = nullptr) {
+                       void* out_dev, cudaStream_t stream, flsgpu_agg_acc* agg = nullptr, const MaskSpec* ms = nullptr) {
 	const fls_file_header& h = t->header;
 	const int T = t->columns[col].phys_bits;
 	if (T == 128) {
@@ -493,11 +500,19 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	L.run_shift = g_run_shift;
 	// fused aggregates write nothing (no read/write turnarounds to avoid); 8/16-bit outputs are instruction bound, not
 	// bandwidth bound, and the second descriptor fetch costs them ~4 %
-	L.prefetch = (agg || os.ob < 4) ? 0u : g_prefetch;
+	L.prefetch = (agg || ms || os.ob < 4) ? 0u : g_prefetch;
 	L.agg = agg;
 	L.agg_signed = t->columns[col].is_signed;
 	L.agg_float = t->columns[col].is_float;
-	const uint32_t tile = agg ? 128u * T : 0u; // aggregate launches decode into a per-warp shared-memory tile
+	if (ms) {
+		L.mask_mode = ms->mode;
+		L.cmp_op = ms->op;
+		L.cmp_const = ms->constant;
+		L.mask = ms->mask;
+		L.rg_keep = ms->rg_keep;
+	}
+	const bool agg_family = agg || ms;
+	const uint32_t tile = agg_family ? 128u * T : 0u; // aggregate launches decode into a per-warp shared-memory tile
 	int rc = FLSGPU_OK;
 	const uint32_t light = FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD));
 	const uint32_t fam_mask[4] = {T == 64 ? light & ~(1u << FLS_ENC_DELTA) : light, 1u << FLS_ENC_ALP, 1u << FLS_ENC_ALP_RD,
@@ -508,7 +523,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 			L.idx_bits = 0;
 			// DELTA needs the per-warp transposition area (+ 16 lane totals for T = 64)
 			const bool stage = p.main_needs_stage && (f == 3 || (f == 0 && T != 64));
-			rc = launch_family(agg ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, p.main_slot[f],
+			rc = launch_family(agg_family ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, p.main_slot[f],
 			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile);
 		}
 	}
@@ -517,13 +532,13 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 			const int it = 8 << k;
 			L.family_mask = FLS_FAMILY_DICT;
 			L.idx_bits = (uint32_t)it;
-			rc = launch_family(agg ? fls_kernel_agg(1, it, T, 0) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile);
+			rc = launch_family(agg_family ? fls_kernel_agg(1, it, T, 0) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile);
 		}
 	}
 	if (p.has_rle && rc == FLSGPU_OK) {
 		L.family_mask = FLS_FAMILY_RLE;
 		L.idx_bits = 0;
-		rc = launch_family(agg ? fls_kernel_agg(2, 16, T, 0) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
+		rc = launch_family(agg_family ? fls_kernel_agg(2, 16, T, 0) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
 	}
 	return rc;
 }
@@ -1118,6 +1133,161 @@ int flsgpu_scan_strings_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin
 	c.heap_host = heap_host;
 	c.heap_capacity_bytes = heap_capacity_bytes;
 	return flsgpu_scan_projection_to_host(t, &c, 1, rg_begin, n_rg);
+}
+
+// ---- filter pushdown ---------------------------------------------------------------------------------------------------
+namespace {
+
+// order of two physical values of a column (integers in their signedness; floats with DuckDB's NaN rules)
+int cmp_physical(const fls_column_desc& c, uint64_t a, uint64_t b) {
+	if (c.is_float) {
+		double x, y;
+		if (c.phys_bits == 32) {
+			float fx, fy;
+			const uint32_t ua = (uint32_t)a, ub = (uint32_t)b;
+			std::memcpy(&fx, &ua, 4);
+			std::memcpy(&fy, &ub, 4);
+			x = fx;
+			y = fy;
+		} else {
+			std::memcpy(&x, &a, 8);
+			std::memcpy(&y, &b, 8);
+		}
+		const bool xn = x != x, yn = y != y;
+		if (xn || yn) {
+			return xn && yn ? 0 : xn ? 1 : -1;
+		}
+		return x < y ? -1 : x > y ? 1 : 0;
+	}
+	if (c.is_signed) {
+		return (int64_t)a < (int64_t)b ? -1 : (int64_t)a > (int64_t)b ? 1 : 0;
+	}
+	return a < b ? -1 : a > b ? 1 : 0;
+}
+
+int check_filters(const flsgpu_table* t, const flsgpu_filter* f, uint32_t n, const char* who) {
+	if (!t || (!f && n)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "filter list is null");
+	}
+	for (uint32_t i = 0; i < n; ++i) {
+		if (f[i].col >= t->header.n_columns || f[i].op < FLSGPU_CMP_EQ || f[i].op > FLSGPU_CMP_GE) {
+			char msg[160];
+			std::snprintf(msg, sizeof(msg), "%s: filter %u has a bad column or comparison", who, i);
+			return fls_set_error(FLSGPU_ERR_INVALID, msg);
+		}
+		if (t->columns[f[i].col].phys_bits == 128) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "filters on string columns are evaluated by the host after decode");
+		}
+	}
+	return FLSGPU_OK;
+}
+
+} // namespace
+
+int flsgpu_rowgroup_prune(const flsgpu_table* t, const flsgpu_filter* filters, uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg,
+                          uint8_t* keep_out) {
+	int rc = check_range(t, 0, rg_begin, n_rg, "flsgpu_rowgroup_prune");
+	if (!rc) {
+		rc = check_filters(t, filters, n_filters, "flsgpu_rowgroup_prune");
+	}
+	if (rc) {
+		return rc;
+	}
+	if (!keep_out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_rowgroup_prune: null output");
+	}
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		bool keep = true;
+		for (uint32_t i = 0; i < n_filters && keep; ++i) {
+			const fls_chunk_desc& ch = t->chunk(rg_begin + r, filters[i].col);
+			const fls_column_desc& col = t->columns[filters[i].col];
+			if (!ch.has_stats || col.is_float) {
+				continue; // no zone map: the row group may satisfy the filter (row_group_filter.cpp:157-160)
+			}
+			const int cmin = cmp_physical(col, ch.min_val, filters[i].constant), cmax = cmp_physical(col, ch.max_val, filters[i].constant);
+			switch (filters[i].op) { // row_group_filter.cpp:177-196 (+ the EQ case, which cannot change the result)
+			case FLSGPU_CMP_GT: keep = cmax > 0; break;
+			case FLSGPU_CMP_GE: keep = cmax >= 0; break;
+			case FLSGPU_CMP_LT: keep = cmin < 0; break;
+			case FLSGPU_CMP_LE: keep = cmin <= 0; break;
+			case FLSGPU_CMP_EQ: keep = cmin <= 0 && cmax >= 0; break;
+			default: break;
+			}
+		}
+		keep_out[r] = keep ? 1 : 0;
+	}
+	return FLSGPU_OK;
+}
+
+int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg,
+                       const uint8_t* rg_keep_dev, uint32_t* mask_dev, uint64_t mask_capacity_bytes, void* cuda_stream) {
+	int rc = check_range(t, 0, rg_begin, n_rg, "flsgpu_filter_mask");
+	if (!rc) {
+		rc = check_filters(t, filters, n_filters, "flsgpu_filter_mask");
+	}
+	if (rc) {
+		return rc;
+	}
+	const uint64_t need = (uint64_t)n_rg * t->header.vec_per_rowgroup * 128u;
+	if (!mask_dev || (reinterpret_cast<uintptr_t>(mask_dev) & 15u) || mask_capacity_bytes < need || n_filters == 0) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_filter_mask: mask buffer null, misaligned or too small, or no filters");
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+	// vectors nobody writes (pruned row groups, the missing vectors of a short last row group) select nothing
+	FLS_CUDA(cudaMemsetAsync(mask_dev, 0, need, s));
+	for (uint32_t i = 0; i < n_filters; ++i) {
+		rc = check_resident(t, d, filters[i].col, rg_begin, n_rg);
+		if (rc) {
+			return rc;
+		}
+		MaskSpec ms;
+		ms.mode = i == 0 ? 1u : 2u;
+		ms.op = (uint32_t)filters[i].op;
+		ms.constant = filters[i].constant;
+		ms.mask = mask_dev;
+		ms.rg_keep = rg_keep_dev;
+		OutSpec os;
+		os.ob = t->columns[filters[i].col].phys_bits / 8;
+		rc = decode_column_impl(t, d, filters[i].col, rg_begin, n_rg, os, nullptr, s, nullptr, &ms);
+		if (rc) {
+			return rc;
+		}
+	}
+	return FLSGPU_OK;
+}
+
+int flsgpu_aggregate_column_masked(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const uint32_t* mask_dev,
+                                   const uint8_t* rg_keep_dev, flsgpu_agg_result* result_dev, void* cuda_stream) {
+	int rc = check_range(t, col, rg_begin, n_rg, "flsgpu_aggregate_column_masked");
+	if (rc) {
+		return rc;
+	}
+	if (!result_dev || (reinterpret_cast<uintptr_t>(result_dev) & 7u) || !mask_dev) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_aggregate_column_masked: result or mask pointer null or misaligned");
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	rc = check_resident(t, d, col, rg_begin, n_rg);
+	if (rc) {
+		return rc;
+	}
+	MaskSpec ms;
+	ms.mode = 3;
+	ms.mask = const_cast<uint32_t*>(mask_dev);
+	ms.rg_keep = rg_keep_dev;
+	OutSpec os;
+	os.ob = t->columns[col].phys_bits / 8;
+	flsgpu_agg_acc* acc = reinterpret_cast<flsgpu_agg_acc*>(result_dev);
+	// SUM / COUNT only: MIN / MAX of a filtered scan cannot come from the zone maps
+	return decode_column_impl(t, d, col, rg_begin, n_rg, os, nullptr, static_cast<cudaStream_t>(cuda_stream), acc, &ms);
 }
 
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {

@@ -46,6 +46,16 @@ class ScanColumn(C.Structure):  # flsgpu_scan_column
 
 
 STRING_FLAT, STRING_DICTIONARY = 0, 1
+CMP = dict(EQ=0, NE=1, LT=2, LE=3, GT=4, GE=5)
+
+
+class Filter(C.Structure):  # flsgpu_filter
+    _fields_ = [("col", C.c_uint32), ("op", C.c_int32), ("constant", C.c_uint64)]
+
+
+def make_filters(filters):
+    """[(col, 'GE', physical constant bits)] -> ctypes array."""
+    return (Filter * len(filters))(*[Filter(c, CMP[op] if isinstance(op, str) else op, k & 0xFFFFFFFFFFFFFFFF) for c, op, k in filters])
 
 
 class StringColumn(C.Structure):
@@ -126,6 +136,7 @@ ABI_SYMBOLS = [
     "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
     "flsgpu_string_heap_bytes", "flsgpu_decode_strings", "flsgpu_decode_string_codes", "flsgpu_decode_string_dict",
     "flsgpu_string_dict_keys", "flsgpu_scan_strings_to_host", "flsgpu_scan_projection_to_host",
+    "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked",
 ]
 
 
@@ -331,6 +342,23 @@ class Table:
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_scan_strings_to_host(self._h, col, rg_begin, n_rg, _vp(out_host_ptr), C.c_uint64(out_bytes),
                                                _vp(heap_host_ptr), C.c_uint64(heap_bytes)), "scan_strings_to_host")
+
+    # ---- filter pushdown ----
+    def rowgroup_prune(self, filters, rg_begin=0, n_rg=None):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        keep = np.zeros(n_rg, dtype=np.uint8)
+        _check(lib.flsgpu_rowgroup_prune(self._h, make_filters(filters), len(filters), rg_begin, n_rg, _vp(keep.ctypes.data)), "rowgroup_prune")
+        return keep
+
+    def filter_mask(self, filters, mask_ptr, mask_bytes, keep_ptr=0, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_filter_mask(self._h, make_filters(filters), len(filters), rg_begin, n_rg, _vp(keep_ptr), _vp(mask_ptr),
+                                      C.c_uint64(mask_bytes), _vp(stream)), "filter_mask")
+
+    def aggregate_column_masked(self, col, mask_ptr, result_ptr, keep_ptr=0, rg_begin=0, n_rg=None, stream=0):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_aggregate_column_masked(self._h, col, rg_begin, n_rg, _vp(mask_ptr), _vp(keep_ptr), _vp(result_ptr), _vp(stream)),
+               "aggregate_column_masked")
 
     def scan_projection_to_host(self, scan_columns, rg_begin=0, n_rg=None):
         """scan_columns: list of ScanColumn."""

@@ -165,6 +165,34 @@ int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, ui
                             flsgpu_agg_result* result_dev, void* cuda_stream);
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream);
 
+/* ---- filter pushdown: RowGroupFilter (row_group_filter.cpp:96-199) + FilterExecutor (filter_executor.cpp:19-60) ------ */
+/* Constant comparisons on numeric columns (DuckDB ConstantFilter), combined with AND like a TableFilterSet.  `constant` is
+ * the physical value of the column's type: integers sign- / zero-extended to 64 bits (DATE days, TIMESTAMP micros,
+ * DECIMAL unscaled), FLOAT bits in the low word, DOUBLE bits.  Floating point follows DuckDB: NaN equals NaN and is
+ * greater than every other value. */
+typedef enum flsgpu_cmp {
+	FLSGPU_CMP_EQ = 0, FLSGPU_CMP_NE = 1, FLSGPU_CMP_LT = 2, FLSGPU_CMP_LE = 3, FLSGPU_CMP_GT = 4, FLSGPU_CMP_GE = 5
+} flsgpu_cmp;
+typedef struct flsgpu_filter {
+	uint32_t col;
+	int32_t op; /* flsgpu_cmp */
+	uint64_t constant;
+} flsgpu_filter;
+/* RowGroupMaySatisfyFilters: keep_out[r] = 0 when the zone maps (fls_chunk_desc.min_val / max_val) of row group
+ * rg_begin + r prove that no row passes.  Host only. */
+int flsgpu_rowgroup_prune(const flsgpu_table* t, const flsgpu_filter* filters, uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg,
+                          uint8_t* keep_out);
+/* FilterExecutor::Apply on the device: decode each filter column (fused, nothing is written but the mask) and set bit i
+ * of word w of vector v (mask_dev[v * 32 + w], vectors laid out as in flsgpu_decode_column) when row v*1024 + w*32 + i
+ * passes every filter.  Padding rows never pass.  rg_keep_dev (device copy of flsgpu_rowgroup_prune's output, or NULL):
+ * pruned row groups are not decoded and select nothing. */
+int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg,
+                       const uint8_t* rg_keep_dev, uint32_t* mask_dev, uint64_t mask_capacity_bytes, void* cuda_stream);
+/* SUM / COUNT of the rows whose mask bit is set (SELECT SUM(col), COUNT(*) ... WHERE <filters>): accumulates into
+ * *result_dev like flsgpu_aggregate_column; min_val / max_val are not produced. */
+int flsgpu_aggregate_column_masked(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const uint32_t* mask_dev,
+                                   const uint8_t* rg_keep_dev, flsgpu_agg_result* result_dev, void* cuda_stream);
+
 /* ---- end to end from host buffers: what FastLanesReader::Scan hands to DuckDB -------------------------- */
 /* Stage (H2D) + decode + copy back (D2H) into pinned/pageable host memory `out_host`, pipelined in slabs of
  * row groups over two streams.  Synchronous: returns when out_host is complete. */

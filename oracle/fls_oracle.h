@@ -66,6 +66,18 @@ float fls_oracle_alp_decode_f32(int32_t digit, int e, int f);
 int fls_oracle_aggregate(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* sum_lo,
                          uint64_t* sum_hi, uint64_t* count, int64_t* min_val, int64_t* max_val, double* fsum);
 
+/* ---- filter pushdown (fls_oracle_scan.c): constant comparisons, op numbering of flsgpu_cmp (EQ NE LT LE GT GE) ---------- */
+typedef struct fls_oracle_filter {
+	uint32_t col;
+	int32_t op;
+	uint64_t constant; /* physical bits, integers extended to 64 */
+} fls_oracle_filter;
+int fls_oracle_filter_mask(const fls_oracle_table* t, const fls_oracle_filter* filters, uint32_t n_filters, uint32_t rg_begin,
+                           uint32_t n_rg, uint32_t* mask /* n_rg * vec_per_rowgroup * 32 words */);
+int fls_oracle_rowgroup_may_satisfy(const fls_oracle_table* t, const fls_oracle_filter* filters, uint32_t n_filters, uint32_t rg);
+int fls_oracle_aggregate_masked(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const uint32_t* mask,
+                                uint64_t* sum_lo, uint64_t* sum_hi, uint64_t* count, double* fsum);
+
 /* ---- string columns (fls_oracle_str.c) ---------------------------------------------------------------------------- */
 int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, uint32_t* codes /* 1024 */);
 uint64_t fls_oracle_fsst_decompress(const fls_fsst_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out);

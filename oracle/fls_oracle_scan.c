@@ -384,3 +384,157 @@ int fls_oracle_aggregate(const fls_oracle_table* t, uint32_t col, uint32_t rg_be
 	*fsum = fs;
 	return 0;
 }
+
+/* ---- filter pushdown ------------------------------------------------------------------------------------------------
+ * FilterExecutor::Apply (reference src/reader/filter_executor.cpp:19-60) hands every filter column of a decoded chunk to
+ * DuckDB's ColumnSegment::FilterSelection; for a ConstantFilter that is a comparison of each value with the constant in
+ * the column's type (duckdb/src/storage/table/column_segment.cpp, templated_filter_operation), floating point with
+ * DuckDB's total order (NaN == NaN, NaN greater than everything: duckdb/common/operator/comparison_operators.hpp).
+ * The selection is returned as a bit mask in decode_column's row layout: bit i of word w of vector v. */
+static int cmp_values(const fls_column_desc* c, uint64_t a, uint64_t b) {
+	if (c->is_float) {
+		double x, y;
+		if (c->phys_bits == 32) {
+			float fx, fy;
+			const uint32_t ua = (uint32_t)a, ub = (uint32_t)b;
+			memcpy(&fx, &ua, 4);
+			memcpy(&fy, &ub, 4);
+			x = fx;
+			y = fy;
+		} else {
+			memcpy(&x, &a, 8);
+			memcpy(&y, &b, 8);
+		}
+		const int xn = x != x, yn = y != y;
+		if (xn || yn) {
+			return xn && yn ? 0 : xn ? 1 : -1;
+		}
+		return x < y ? -1 : x > y ? 1 : 0;
+	}
+	if (c->is_signed) {
+		return (int64_t)a < (int64_t)b ? -1 : (int64_t)a > (int64_t)b ? 1 : 0;
+	}
+	return a < b ? -1 : a > b ? 1 : 0;
+}
+
+static int passes(int op, int cmp) {
+	switch (op) {
+	case 0: return cmp == 0;
+	case 1: return cmp != 0;
+	case 2: return cmp < 0;
+	case 3: return cmp <= 0;
+	case 4: return cmp > 0;
+	default: return cmp >= 0;
+	}
+}
+
+int fls_oracle_filter_mask(const fls_oracle_table* t, const fls_oracle_filter* filters, uint32_t n_filters, uint32_t rg_begin,
+                           uint32_t n_rg, uint32_t* mask) {
+	if (rg_begin + n_rg > t->header.n_rowgroups) {
+		return -1;
+	}
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	memset(mask, 0, (size_t)n_rg * vpr * 128);
+	uint64_t scratch[1024], nat[1024];
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		const uint32_t rg = rg_begin + r;
+		uint32_t left = t->rowgroups[rg].n_tuples;
+		for (uint32_t v = 0; v < t->rowgroups[rg].n_vec; ++v) {
+			const uint32_t valid = left < 1024 ? left : 1024;
+			left -= valid;
+			uint32_t* mv = mask + ((size_t)r * vpr + v) * 32;
+			for (uint32_t i = 0; i < valid; ++i) {
+				mv[i >> 5] |= 1u << (i & 31);
+			}
+			for (uint32_t f = 0; f < n_filters; ++f) {
+				if (filters[f].col >= t->header.n_columns || t->columns[filters[f].col].phys_bits == 128) {
+					return -1;
+				}
+				const fls_column_desc* c = &t->columns[filters[f].col];
+				int tr = 0;
+				int rc = fls_oracle_decode_vector(t, rg, filters[f].col, v, scratch, &tr);
+				if (!rc) {
+					rc = fls_oracle_materialize(t, filters[f].col, scratch, tr, OUT_NATIVE, nat);
+				}
+				if (rc) {
+					return rc;
+				}
+				for (uint32_t i = 0; i < valid; ++i) {
+					const uint64_t val = c->is_float ? (c->phys_bits == 32 ? ((const uint32_t*)nat)[i] : nat[i])
+					                                 : load_src(nat, c->phys_bits, i, c->is_signed);
+					if (!passes(filters[f].op, cmp_values(c, val, filters[f].constant))) {
+						mv[i >> 5] &= ~(1u << (i & 31));
+					}
+				}
+			}
+		}
+	}
+	return 0;
+}
+
+/* RowGroupFilter::RowGroupMaySatisfyFilters (reference src/reader/row_group_filter.cpp:96-199): only <, <=, >, >= against
+ * the row group's min / max statistic prune. */
+int fls_oracle_rowgroup_may_satisfy(const fls_oracle_table* t, const fls_oracle_filter* filters, uint32_t n_filters, uint32_t rg) {
+	for (uint32_t f = 0; f < n_filters; ++f) {
+		const fls_column_desc* c = &t->columns[filters[f].col];
+		const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + filters[f].col];
+		if (!ch->has_stats || c->is_float) {
+			continue;
+		}
+		const int cmin = cmp_values(c, ch->min_val, filters[f].constant), cmax = cmp_values(c, ch->max_val, filters[f].constant);
+		switch (filters[f].op) {
+		case 4: if (cmax <= 0) return 0; break; /* > : skip when max <= constant */
+		case 5: if (cmax < 0) return 0; break;
+		case 2: if (cmin >= 0) return 0; break;
+		case 3: if (cmin > 0) return 0; break;
+		default: break;
+		}
+	}
+	return 1;
+}
+
+/* SUM (128-bit) / COUNT of the rows of `col` whose mask bit is set. */
+int fls_oracle_aggregate_masked(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const uint32_t* mask,
+                                uint64_t* sum_lo, uint64_t* sum_hi, uint64_t* count, double* fsum) {
+	if (col >= t->header.n_columns || rg_begin + n_rg > t->header.n_rowgroups) {
+		return -1;
+	}
+	const fls_column_desc* c = &t->columns[col];
+	const unsigned T = c->phys_bits;
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	unsigned __int128 acc = 0;
+	uint64_t n = 0;
+	double fs = 0.0;
+	uint64_t scratch[1024], nat[1024];
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		const uint32_t rg = rg_begin + r;
+		for (uint32_t v = 0; v < t->rowgroups[rg].n_vec; ++v) {
+			const uint32_t* mv = mask + ((size_t)r * vpr + v) * 32;
+			int tr = 0;
+			int rc = fls_oracle_decode_vector(t, rg, col, v, scratch, &tr);
+			if (!rc) {
+				rc = fls_oracle_materialize(t, col, scratch, tr, OUT_NATIVE, nat);
+			}
+			if (rc) {
+				return rc;
+			}
+			for (uint32_t i = 0; i < 1024; ++i) {
+				if (!((mv[i >> 5] >> (i & 31)) & 1u)) {
+					continue;
+				}
+				++n;
+				if (c->is_float) {
+					fs += T == 32 ? (double)((const float*)nat)[i] : ((const double*)nat)[i];
+					continue;
+				}
+				const uint64_t u = load_src(nat, T, i, c->is_signed);
+				acc += c->is_signed ? (unsigned __int128)(__int128)(int64_t)u : (unsigned __int128)u;
+			}
+		}
+	}
+	*sum_lo = (uint64_t)acc;
+	*sum_hi = (uint64_t)(acc >> 64);
+	*count = n;
+	*fsum = fs;
+	return 0;
+}

@@ -33,6 +33,10 @@ lib.fls_oracle_alp_decode_f32.restype = C.c_float
 lib.fls_oracle_alp_decode_f32.argtypes = [C.c_int32, C.c_int, C.c_int]
 
 
+class OracleFilter(C.Structure):
+    _fields_ = [("col", C.c_uint32), ("op", C.c_int32), ("constant", C.c_uint64)]
+
+
 class Oracle:
     def __init__(self, image):
         self.image = np.ascontiguousarray(image, dtype=np.uint8)
@@ -87,6 +91,29 @@ class Oracle:
         if rc:
             raise RuntimeError(f"fls_oracle_decode_string_dict failed: {rc}")
         return out, heap
+
+    def filter_mask(self, filters, rg_begin, n_rg, vec_per_rg):
+        """filters: [(col, op, constant_bits)] -> uint32 mask [n_rg * vec_per_rg * 32]."""
+        arr = (OracleFilter * len(filters))(*[OracleFilter(c, op, k & 0xFFFFFFFFFFFFFFFF) for c, op, k in filters])
+        mask = np.zeros(n_rg * vec_per_rg * 32, dtype=np.uint32)
+        rc = lib.fls_oracle_filter_mask(C.byref(self.t), arr, len(filters), rg_begin, n_rg, C.c_void_p(mask.ctypes.data))
+        if rc:
+            raise RuntimeError(f"fls_oracle_filter_mask failed: {rc}")
+        return mask
+
+    def rowgroup_may_satisfy(self, filters, rg):
+        arr = (OracleFilter * len(filters))(*[OracleFilter(c, op, k & 0xFFFFFFFFFFFFFFFF) for c, op, k in filters])
+        return bool(lib.fls_oracle_rowgroup_may_satisfy(C.byref(self.t), arr, len(filters), rg))
+
+    def aggregate_masked(self, col, rg_begin, n_rg, mask):
+        lo, hi, cnt, fs = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_double()
+        mask = np.ascontiguousarray(mask, dtype=np.uint32)
+        rc = lib.fls_oracle_aggregate_masked(C.byref(self.t), col, rg_begin, n_rg, C.c_void_p(mask.ctypes.data), C.byref(lo),
+                                             C.byref(hi), C.byref(cnt), C.byref(fs))
+        if rc:
+            raise RuntimeError(f"fls_oracle_aggregate_masked failed: {rc}")
+        s = (hi.value << 64) | lo.value
+        return (s - (1 << 128) if s >= (1 << 127) else s), cnt.value, fs.value
 
     def aggregate(self, col, rg_begin, n_rg):
         lo, hi, cnt = C.c_uint64(), C.c_uint64(), C.c_uint64()
