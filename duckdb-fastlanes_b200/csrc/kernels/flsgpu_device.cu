@@ -431,6 +431,24 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	return FLSGPU_OK;
 }
 
+int check_filters(const flsgpu_table* t, const flsgpu_filter* f, uint32_t n, const char* who) {
+	if (!t || (!f && n)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "filter list is null");
+	}
+	for (uint32_t i = 0; i < n; ++i) {
+		if (f[i].col >= t->header.n_columns || f[i].op < FLSGPU_CMP_EQ || f[i].op > FLSGPU_CMP_GE) {
+			char msg[160];
+			std::snprintf(msg, sizeof(msg), "%s: filter %u has a bad column or comparison", who, i);
+			return fls_set_error(FLSGPU_ERR_INVALID, msg);
+		}
+		if (t->columns[f[i].col].phys_bits == 128) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "filters on string columns are evaluated by the host after decode");
+		}
+	}
+	return FLSGPU_OK;
+}
+
+
 struct OutSpec {
 	int ob = 0;        // bytes per output value
 	uint32_t conv = 0; // 0 zero-extend / same width, 1 sign-extend, 2 f32 -> f64
@@ -709,10 +727,25 @@ int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids
 	return FLSGPU_OK;
 }
 
-// Pipelined host-to-host scan of a projection (numeric columns, flat strings, dictionary-form strings).
+// Pipelined host-to-host scan of a projection (numeric columns, flat strings, dictionary-form strings), optionally with
+// the selection mask of a filter set evaluated on the device slab by slab.
 int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg) {
+	return flsgpu_scan_filtered_to_host(t, cols, n_cols, nullptr, 0, rg_begin, n_rg, nullptr, 0);
+}
+
+int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, const flsgpu_filter* filters,
+                                 uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg, uint32_t* mask_host, uint64_t mask_capacity_bytes) {
 	if (!t || !cols || n_cols == 0) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_projection_to_host: null argument");
+	}
+	if (n_filters) {
+		const int frc = check_filters(t, filters, n_filters, "flsgpu_scan_filtered_to_host");
+		if (frc) {
+			return frc;
+		}
+		if (!mask_host || mask_capacity_bytes < (uint64_t)n_rg * t->header.vec_per_rowgroup * 128u) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_filtered_to_host: mask buffer null or too small");
+		}
 	}
 	const fls_file_header& h = t->header;
 	struct ColPlan {
@@ -797,6 +830,8 @@ int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* co
 			slab_bytes += p.dict ? keys_max * 16u + 16u : 0u;
 		}
 	}
+	const uint64_t dev_mask = slab_bytes, rg_mask_bytes = (uint64_t)h.vec_per_rowgroup * 128u;
+	slab_bytes += n_filters ? rg_mask_bytes * slab_rg : 0u;
 	FlsScanScratch* sc = nullptr;
 	{
 		std::lock_guard<std::mutex> g(d->mu);
@@ -833,6 +868,11 @@ int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* co
 	for (uint32_t i = 0; i < n_cols; ++i) {
 		col_ids[i] = cols[i].col;
 	}
+	for (uint32_t i = 0; i < n_filters; ++i) { // filter columns are staged too, whether projected or not
+		if (std::find(col_ids.begin(), col_ids.end(), filters[i].col) == col_ids.end()) {
+			col_ids.push_back(filters[i].col);
+		}
+	}
 	uint32_t slab = 0;
 	int status = FLSGPU_OK;
 	auto d2h = [&](void* dst, const void* src, uint64_t bytes, cudaStream_t s) {
@@ -845,9 +885,14 @@ int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* co
 		cudaStream_t s = sc->streams[slab & 1];
 		{
 			std::lock_guard<std::mutex> g(d->mu);
-			status = stage_range(t, d, rg_begin + r, n, col_ids.data(), n_cols, s);
+			status = stage_range(t, d, rg_begin + r, n, col_ids.data(), (uint32_t)col_ids.size(), s);
 		}
 		uint8_t* base = static_cast<uint8_t*>(sc->out[slab & 1]);
+		if (n_filters && status == FLSGPU_OK) { // FilterExecutor::Apply for the slab: selection mask -> host
+			status = flsgpu_filter_mask(t, filters, n_filters, rg_begin + r, n, nullptr, reinterpret_cast<uint32_t*>(base + dev_mask),
+			                            rg_mask_bytes * n, s);
+			d2h(reinterpret_cast<uint8_t*>(mask_host) + (uint64_t)r * rg_mask_bytes, base + dev_mask, rg_mask_bytes * n, s);
+		}
 		for (uint32_t i = 0; i < n_cols && status == FLSGPU_OK; ++i) {
 			const flsgpu_scan_column& c = cols[i];
 			const ColPlan& p = cp[i];
@@ -1163,23 +1208,6 @@ int cmp_physical(const fls_column_desc& c, uint64_t a, uint64_t b) {
 		return (int64_t)a < (int64_t)b ? -1 : (int64_t)a > (int64_t)b ? 1 : 0;
 	}
 	return a < b ? -1 : a > b ? 1 : 0;
-}
-
-int check_filters(const flsgpu_table* t, const flsgpu_filter* f, uint32_t n, const char* who) {
-	if (!t || (!f && n)) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "filter list is null");
-	}
-	for (uint32_t i = 0; i < n; ++i) {
-		if (f[i].col >= t->header.n_columns || f[i].op < FLSGPU_CMP_EQ || f[i].op > FLSGPU_CMP_GE) {
-			char msg[160];
-			std::snprintf(msg, sizeof(msg), "%s: filter %u has a bad column or comparison", who, i);
-			return fls_set_error(FLSGPU_ERR_INVALID, msg);
-		}
-		if (t->columns[f[i].col].phys_bits == 128) {
-			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "filters on string columns are evaluated by the host after decode");
-		}
-	}
-	return FLSGPU_OK;
 }
 
 } // namespace

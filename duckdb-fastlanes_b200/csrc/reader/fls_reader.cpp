@@ -58,6 +58,8 @@ LogicalType TranslateType(const fls_column_desc& col, int32_t* out_type) {
 		t.scale = col.decimal_scale;
 		t.physical_bytes = col.phys_bits / 8;
 		break;
+	case FLS_TYPE_FLS_STR: t.id = LogicalTypeId::VARCHAR; t.physical_bytes = 16; break; // :38-39 (string_t)
+	case FLS_TYPE_BYTE_ARRAY: t.id = LogicalTypeId::BLOB; t.physical_bytes = 16; break;
 	default: throw ReaderError(FLSGPU_ERR_UNSUPPORTED, "TranslateType: unsupported FastLanes data type"); // :44-46
 	}
 	if (out_type) {
@@ -168,11 +170,24 @@ FastLanesReaderProjectionPlan FastLanesReader::BuildReaderProjectionPlan() const
 
 // FastLanesReader::TryAssignNextRowGroup (fls_reader.cpp:337-355), handing out a batch of row groups.
 bool FastLanesReader::TryAssignNextRowGroup(FastLanesReadGlobalState& global_state, FastLanesReadLocalState& local_state) {
+	// RowGroupFilter: row groups whose zone maps rule the filters out are never handed out (row_group_filter.cpp:80-94)
+	if (!filters.empty() && !rowgroup_filter_built) {
+		BuildRowGroupFilter();
+	}
+	const bool pruning = !filters.empty();
+	while (pruning && global_state.next_rowgroup < info.n_rowgroups && !rowgroups_to_scan[global_state.next_rowgroup]) {
+		global_state.next_rowgroup++;
+	}
 	if (global_state.next_rowgroup >= info.n_rowgroups) {
 		return false;
 	}
 	local_state.batch_begin = global_state.next_rowgroup;
 	local_state.batch_end = std::min<idx_t>(info.n_rowgroups, local_state.batch_begin + reader_options.rowgroups_per_batch);
+	for (idx_t r = local_state.batch_begin; pruning && r < local_state.batch_end; ++r) { // a batch is a run of kept row groups
+		if (!rowgroups_to_scan[r]) {
+			local_state.batch_end = r;
+		}
+	}
 	local_state.cur_rowgroup = local_state.batch_begin;
 	local_state.projection = BuildReaderProjectionPlan();
 	local_state.row_group_base = row_group_offsets[local_state.cur_rowgroup];
@@ -188,7 +203,13 @@ bool FastLanesReader::TryInitializeScan(FastLanesReadGlobalState& gstate, FastLa
 		return false;
 	}
 	gstate.next_rowgroup = lstate.batch_end; // mark the row groups as consumed (:511)
-	lstate.staging.resize(lstate.projection.reader_column_ids.size());
+	const size_t n_reader_cols = lstate.projection.reader_column_ids.size();
+	lstate.staging.resize(n_reader_cols);
+	lstate.heaps.resize(n_reader_cols);
+	lstate.keys.resize(n_reader_cols);
+	lstate.dict_form.assign(n_reader_cols, 0);
+	lstate.key_offsets.assign(n_reader_cols, {});
+	lstate.has_mask = false;
 	lstate.row_numbers.clear();
 	lstate.cur_vector = ~0ull; // batch not decoded yet
 	return true;
@@ -198,23 +219,111 @@ bool FastLanesReader::TryInitializeScan(FastLanesReadGlobalState& gstate, FastLa
 // one pipelined H2D -> decode -> D2H call for all projected columns of all row groups of the batch.
 void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState& ls) {
 	const auto& ids = ls.projection.reader_column_ids;
-	const uint32_t n_rg = (uint32_t)(ls.batch_end - ls.batch_begin);
+	const uint32_t n_rg = (uint32_t)(ls.batch_end - ls.batch_begin), rg0 = (uint32_t)ls.batch_begin;
+	const std::vector<flsgpu_filter> phys_filters = PhysicalFilters();
 	if (!ids.empty()) {
-		std::vector<int32_t> out_types(ids.size());
-		std::vector<void*> ptrs(ids.size());
-		std::vector<uint64_t> caps(ids.size());
+		std::vector<flsgpu_scan_column> sc(ids.size());
 		for (size_t i = 0; i < ids.size(); ++i) {
-			out_types[i] = column_out_types[ids[i]];
-			const uint64_t need = (uint64_t)n_rg * info.vec_per_rowgroup * FLS_VEC_SZ * columns[ids[i]].type.physical_bytes;
-			ls.staging[i].Reserve(need);
-			ptrs[i] = ls.staging[i].ptr;
-			caps[i] = ls.staging[i].bytes;
+			const LogicalType& type = columns[ids[i]].type;
+			flsgpu_scan_column& c = sc[i];
+			c = flsgpu_scan_column {};
+			c.col = ids[i];
+			c.out_type = column_out_types[ids[i]];
+			const uint64_t rows = (uint64_t)n_rg * info.vec_per_rowgroup * FLS_VEC_SZ;
+			if (type.id == LogicalTypeId::VARCHAR || type.id == LogicalTypeId::BLOB) {
+				// dec_dict_opr<fls_string_t> / dec_fsst_dict_opr hand DuckDB a DICTIONARY_VECTOR (dictionary_kernel.hpp:80-101);
+				// taken here when every chunk of the batch is dictionary encoded, else the batch is materialised flat
+				uint64_t n_keys = 0, heap_bytes = 0;
+				const bool dict = flsgpu_string_dict_keys(table, ids[i], rg0, n_rg, &n_keys) == FLSGPU_OK;
+				Check(flsgpu_string_heap_bytes(table, ids[i], rg0, n_rg, &heap_bytes), "flsgpu_string_heap_bytes");
+				ls.dict_form[i] = dict ? 1 : 0;
+				c.string_form = dict ? FLSGPU_STRING_DICTIONARY : FLSGPU_STRING_FLAT;
+				ls.staging[i].Reserve(rows * (dict ? 4u : 16u));
+				ls.heaps[i].Reserve(heap_bytes + 16);
+				c.heap_host = ls.heaps[i].ptr;
+				c.heap_capacity_bytes = ls.heaps[i].bytes;
+				if (dict) {
+					ls.keys[i].Reserve(n_keys * 16 + 16);
+					c.keys_host = ls.keys[i].ptr;
+					c.keys_capacity_bytes = ls.keys[i].bytes;
+					ls.key_offsets[i].assign(n_rg + 1, 0);
+					for (uint32_t r = 0; r < n_rg; ++r) {
+						fls_chunk_desc ch;
+						Check(flsgpu_table_chunk(table, rg0 + r, ids[i], &ch), "flsgpu_table_chunk");
+						ls.key_offsets[i][r + 1] = ls.key_offsets[i][r] + ch.aux_count;
+					}
+				}
+			} else {
+				ls.staging[i].Reserve(rows * type.physical_bytes);
+			}
+			c.out_host = ls.staging[i].ptr;
+			c.out_capacity_bytes = ls.staging[i].bytes;
 		}
-		Check(flsgpu_scan_columns_to_host(table, ids.data(), (uint32_t)ids.size(), (uint32_t)ls.batch_begin, n_rg, out_types.data(),
-		                                  ptrs.data(), caps.data()),
-		      "flsgpu_scan_columns_to_host");
+		if (!phys_filters.empty()) {
+			ls.mask.Reserve((uint64_t)n_rg * info.vec_per_rowgroup * 128u);
+			ls.has_mask = true;
+		}
+		Check(flsgpu_scan_filtered_to_host(table, sc.data(), (uint32_t)sc.size(), phys_filters.data(), (uint32_t)phys_filters.size(), rg0, n_rg,
+		                                   static_cast<uint32_t*>(ls.mask.ptr), ls.mask.bytes),
+		      "flsgpu_scan_filtered_to_host");
 	}
 	ls.cur_vector = 0;
+}
+
+// TableFilterSet -> device filters: the filter's column_index addresses column_ids (multi_file_function.hpp:356-379)
+std::vector<flsgpu_filter> FastLanesReader::PhysicalFilters() const {
+	std::vector<flsgpu_filter> out;
+	for (const TableFilter& f : filters) {
+		if (f.column_index >= column_ids.size() || IsFileRowNumberColumn(column_ids[f.column_index]) ||
+		    column_ids[f.column_index] >= info.n_columns) {
+			throw ReaderError(FLSGPU_ERR_INVALID, "Filter refers to a column that is not a projected physical column");
+		}
+		flsgpu_filter p;
+		p.col = (uint32_t)column_ids[f.column_index];
+		p.op = f.op;
+		p.constant = f.constant;
+		out.push_back(p);
+	}
+	return out;
+}
+
+// RowGroupFilter::BuildRowGroupsToScan / RowGroupMaySatisfyFilters (row_group_filter.cpp:80-199)
+void FastLanesReader::BuildRowGroupFilter() {
+	rowgroups_to_scan.assign(info.n_rowgroups, 1);
+	const std::vector<flsgpu_filter> pf = PhysicalFilters();
+	if (!pf.empty() && info.n_rowgroups) {
+		Check(flsgpu_rowgroup_prune(table, pf.data(), (uint32_t)pf.size(), 0, info.n_rowgroups, rowgroups_to_scan.data()), "flsgpu_rowgroup_prune");
+	}
+	rowgroup_filter_built = true;
+}
+
+// FilterExecutor::Apply (filter_executor.cpp:19-60): the device already evaluated the filters for the whole batch; turn the
+// mask bits of this chunk's rows into the selection vector the chunk is sliced with.
+void FastLanesReader::ApplyFilters(FastLanesReadLocalState& ls, DataChunk& chunk, idx_t start_vector, idx_t count) const {
+	chunk.sel.clear();
+	if (!ls.has_mask) {
+		return;
+	}
+	const idx_t rg_in_batch = ls.cur_rowgroup - ls.batch_begin;
+	const uint32_t* words = static_cast<const uint32_t*>(ls.mask.ptr) + (rg_in_batch * info.vec_per_rowgroup + start_vector) * 32;
+	for (idx_t w = 0; w < (count + 31) / 32; ++w) {
+		uint32_t bits = words[w];
+		while (bits) {
+			const uint32_t i = (uint32_t)w * 32 + (uint32_t)__builtin_ctz(bits);
+			bits &= bits - 1;
+			if (i < count) {
+				chunk.sel.push_back(i);
+			}
+		}
+	}
+	if (chunk.sel.size() == count) {
+		chunk.sel.clear(); // nothing filtered: no slice (filter_executor.cpp:57)
+	} else {
+		chunk.SetCardinality(chunk.sel.size());
+		if (chunk.sel.empty()) {
+			chunk.sel.push_back(0); // keep "sliced" distinguishable from "identity"; count is 0
+		}
+	}
 }
 
 // FastLanesReader::GetScanBatch (fls_reader.cpp:422-434): at most two FastLanes vectors = one DuckDB chunk, never
@@ -242,8 +351,17 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState& ls, DataChu
 			continue;
 		}
 		const ColumnDefinition& def = columns[ls.projection.reader_column_ids[ri]];
-		chunk.data[i].type = def.type;
-		chunk.data[i].data = static_cast<const uint8_t*>(ls.staging[ri].ptr) + first_elem * def.type.physical_bytes;
+		Vector& v = chunk.data[i];
+		v = Vector();
+		v.type = def.type;
+		if (ls.dict_form[ri]) { // Vector::Dictionary(dictionary of this row group, selection vector of the chunk's rows)
+			v.vector_type = VectorType::DICTIONARY_VECTOR;
+			v.sel = static_cast<const uint32_t*>(ls.staging[ri].ptr) + first_elem;
+			v.data = static_cast<const uint8_t*>(ls.keys[ri].ptr) + ls.key_offsets[ri][rg_in_batch] * 16;
+			v.dict_size = ls.key_offsets[ri][rg_in_batch + 1] - ls.key_offsets[ri][rg_in_batch];
+		} else {
+			v.data = static_cast<const uint8_t*>(ls.staging[ri].ptr) + first_elem * def.type.physical_bytes;
+		}
 	}
 }
 
@@ -257,6 +375,7 @@ void FastLanesReader::PopulateVirtualColumns(FastLanesReadLocalState& ls, DataCh
 		for (idx_t row = 0; row < count; ++row) {
 			ls.row_numbers[row] = (int64_t)(row_start + row);
 		}
+		chunk.data[i] = Vector();
 		chunk.data[i].type.id = LogicalTypeId::BIGINT;
 		chunk.data[i].type.physical_bytes = 8;
 		chunk.data[i].data = ls.row_numbers.data();
@@ -268,6 +387,7 @@ void FastLanesReader::PopulateVirtualColumns(FastLanesReadLocalState& ls, DataCh
 void FastLanesReader::Scan(FastLanesReadGlobalState&, FastLanesReadLocalState& ls, DataChunk& chunk) {
 	chunk.data.resize(column_ids.size());
 	chunk.SetCardinality(0);
+	chunk.sel.clear();
 	if (ls.batch_begin >= ls.batch_end) {
 		return;
 	}
@@ -292,8 +412,12 @@ void FastLanesReader::Scan(FastLanesReadGlobalState&, FastLanesReadLocalState& l
 		const idx_t row_start = ls.row_group_base + batch.start_tuple;
 		PopulateVirtualColumns(ls, chunk, row_start, batch.count);
 		chunk.SetCardinality(batch.count);
+		ApplyFilters(ls, chunk, ls.cur_vector, batch.count);
 		ls.cur_vector += batch.input_vector_count;
 		vectors_read += batch.input_vector_count;
+		if (chunk.count == 0) {
+			continue; // every row of the chunk was filtered out: serve the next one
+		}
 		return;
 	}
 }

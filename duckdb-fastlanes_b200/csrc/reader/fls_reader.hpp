@@ -26,7 +26,27 @@ constexpr idx_t STANDARD_VECTOR_SIZE = 2048; // duckdb/src/include/duckdb/common
 constexpr idx_t COLUMN_IDENTIFIER_FILE_ROW_NUMBER = ~0ull - 1; // virtual column (fls_multi_file_info.cpp:166-171)
 
 // DuckDB LogicalTypeId subset the reader binds (src/reader/translation_utils.cpp:5-48)
-enum class LogicalTypeId : uint8_t { INVALID, BOOLEAN, TINYINT, SMALLINT, INTEGER, BIGINT, UBIGINT, FLOAT, DOUBLE, DATE, TIMESTAMP, DECIMAL };
+enum class LogicalTypeId : uint8_t { INVALID, BOOLEAN, TINYINT, SMALLINT, INTEGER, BIGINT, UBIGINT, FLOAT, DOUBLE, DATE, TIMESTAMP, DECIMAL, VARCHAR, BLOB };
+
+// duckdb::string_t (duckdb/src/include/duckdb/common/types/string_type.hpp:22-60,236-247): what the device writes for
+// VARCHAR / BLOB values; non-inlined strings point into the reader's pinned string heap.
+struct string_t {
+	static constexpr uint32_t INLINE_LENGTH = 12;
+	uint32_t length;
+	char body[12]; // inlined[12] | prefix[4] + pointer
+	uint32_t GetSize() const {
+		return length;
+	}
+	const char* GetData() const {
+		if (length <= INLINE_LENGTH) {
+			return body;
+		}
+		const char* p;
+		__builtin_memcpy(&p, body + 4, sizeof(p));
+		return p;
+	}
+};
+static_assert(sizeof(string_t) == 16, "string_t must be 16 bytes");
 
 struct LogicalType {
 	LogicalTypeId id = LogicalTypeId::INVALID;
@@ -48,17 +68,41 @@ struct FastLanesFileReaderOptions {
 	idx_t rowgroups_per_batch = 32;
 };
 
-// Stand-in for duckdb::Vector / DataChunk: flat vectors only, data owned by the reader's staging buffers.
+// Stand-in for duckdb::Vector / DataChunk; data is owned by the reader's staging buffers (FlatVector::SetData /
+// Vector::Dictionary style hand-off, dictionary_kernel.hpp:80-101).
+enum class VectorType : uint8_t { FLAT_VECTOR, DICTIONARY_VECTOR };
 struct Vector {
 	LogicalType type;
-	const void* data = nullptr; // `count` values of type.physical_bytes
+	VectorType vector_type = VectorType::FLAT_VECTOR;
+	const void* data = nullptr;    // FLAT: the chunk's values; DICTIONARY: the dictionary's values (dict_size of them)
+	const uint32_t* sel = nullptr; // DICTIONARY: selection vector, one entry per row of the (unsliced) chunk
+	idx_t dict_size = 0;
+	// value of (unsliced) row i as a pointer to its physical representation
+	const void* Row(idx_t i) const {
+		const idx_t k = vector_type == VectorType::DICTIONARY_VECTOR ? sel[i] : i;
+		return static_cast<const uint8_t*>(data) + k * type.physical_bytes;
+	}
 };
 struct DataChunk {
 	std::vector<Vector> data;
 	idx_t count = 0;
+	// DataChunk::Slice(sel, count) after FilterExecutor::Apply (filter_executor.cpp:57-59): row i of the chunk is row
+	// sel[i] of the vectors; empty = identity
+	std::vector<uint32_t> sel;
 	void SetCardinality(idx_t n) {
 		count = n;
 	}
+	idx_t RowIndex(idx_t i) const {
+		return sel.empty() ? i : sel[i];
+	}
+};
+
+// ConstantFilter entry of a TableFilterSet (BaseFileReader::filters, base_file_reader.hpp:36-54): keyed by the position
+// of the column in column_ids; the constant is the physical value of the column's type (flsgpu_filter).
+struct TableFilter {
+	idx_t column_index = 0; // index into column_ids
+	flsgpu_cmp op = FLSGPU_CMP_EQ;
+	uint64_t constant = 0;
 };
 
 // FastLanesReaderProjectionPlan (fls_multi_file_info.hpp:48-55)
@@ -89,6 +133,12 @@ struct FastLanesReadLocalState { // fls_multi_file_info.hpp:57-77
 	// batch decoded by the last TryInitializeScan
 	idx_t batch_begin = 0, batch_end = 0; // row groups [begin, end)
 	std::vector<PinnedBuffer> staging;    // one per reader column: batch_rowgroups * vec_per_rowgroup * 1024 values
+	// string columns: string heap, dictionary keys (dictionary form) and the first key of every row group of the batch
+	std::vector<PinnedBuffer> heaps, keys;
+	std::vector<uint8_t> dict_form;
+	std::vector<std::vector<idx_t>> key_offsets;
+	PinnedBuffer mask;                    // selection mask of the pushed-down filters for the batch
+	bool has_mask = false;
 	std::vector<int64_t> row_numbers;     // file_row_number chunk buffer
 };
 
@@ -114,10 +164,17 @@ public:
 	}
 	// filled by the caller before the scan, like BaseFileReader::column_ids (base_file_reader.hpp:36-54)
 	std::vector<idx_t> column_ids;
+	std::vector<TableFilter> filters; // pushed-down constant comparisons (read_fls.cpp:39-42: filter_pushdown = true)
 	const std::vector<ColumnDefinition>& GetColumns() const {
 		return columns;
 	}
 
+	// a new scan over the same reader (new column_ids / filters): forget the row-group filter and the progress counter
+	void ResetScan() {
+		rowgroup_filter_built = false;
+		rowgroups_to_scan.clear();
+		vectors_read = 0;
+	}
 	bool TryInitializeScan(FastLanesReadGlobalState& gstate, FastLanesReadLocalState& lstate);
 	void Scan(FastLanesReadGlobalState& gstate, FastLanesReadLocalState& lstate, DataChunk& chunk);
 	double GetProgressInFile() const;
@@ -131,6 +188,13 @@ public:
 	idx_t GetNVectors(idx_t row_group_idx) const;
 	size_t GetTotalTuples() const {
 		return total_tuples;
+	}
+	idx_t GetNPrunedRowGroups() const {
+		idx_t n = 0;
+		for (uint8_t k : rowgroups_to_scan) {
+			n += k ? 0 : 1;
+		}
+		return n;
 	}
 	size_t GetTotalVectors() const {
 		return total_vectors;
@@ -157,6 +221,9 @@ private:
 	ScanBatch GetScanBatch(const FastLanesReadLocalState& local_state) const;
 	void DecodePhysicalColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t input_vector_count);
 	void PopulateVirtualColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t row_start, idx_t count);
+	void ApplyFilters(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t count) const;
+	std::vector<flsgpu_filter> PhysicalFilters() const;
+	void BuildRowGroupFilter();
 	FastLanesReaderProjectionPlan BuildReaderProjectionPlan() const;
 	bool IsFileRowNumberColumn(idx_t column_id) const;
 
@@ -166,6 +233,8 @@ private:
 	std::vector<int32_t> column_out_types;   // flsgpu_out_type per physical column
 	std::vector<idx_t> row_group_offsets;    // first tuple of each row group
 	std::vector<fls_rowgroup_desc> row_groups;
+	std::vector<uint8_t> rowgroups_to_scan;  // RowGroupFilter (row_group_filter.cpp:80-94): 0 = pruned by its zone maps
+	bool rowgroup_filter_built = false;
 	size_t total_vectors = 0; // the reference leaves these uninitialised; zeroed here
 	size_t total_tuples = 0;
 	std::atomic<idx_t> vectors_read {0};

@@ -98,77 +98,132 @@ int flsreader_statistics(const flsreader_handle* h, const char* name, int* has_s
 	})
 }
 
+namespace {
+
+// SELECT column_ids FROM read_fls(path) [WHERE filters]: drives TryInitializeScan / Scan on n_threads workers.
+// Without filters rows land at their file row number; with filters the passing rows are appended in arrival order and
+// their file row numbers go to row_ids_out.
+void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
+               int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats) {
+	FastLanesReader& reader = *h->reader;
+	// the driver appends file_row_number to the projection to know where each chunk belongs
+	reader.column_ids.assign(column_ids, column_ids + n_cols);
+	reader.column_ids.push_back(COLUMN_IDENTIFIER_FILE_ROW_NUMBER);
+	reader.filters.clear();
+	reader.ResetScan();
+	for (uint32_t i = 0; i < n_filters; ++i) {
+		TableFilter f;
+		f.column_index = filters[i].column_index;
+		f.op = (flsgpu_cmp)filters[i].op;
+		f.constant = filters[i].constant;
+		reader.filters.push_back(f);
+	}
+	const auto& cols = reader.GetColumns();
+	std::vector<uint32_t> widths(n_cols);
+	std::vector<uint8_t> is_str(n_cols);
+	for (uint32_t c = 0; c < n_cols; ++c) {
+		if (column_ids[c] >= cols.size()) {
+			throw ReaderError(FLSGPU_ERR_INVALID, "Projected column id out of range");
+		}
+		widths[c] = cols[column_ids[c]].type.physical_bytes;
+		is_str[c] = cols[column_ids[c]].type.id == LogicalTypeId::VARCHAR || cols[column_ids[c]].type.id == LogicalTypeId::BLOB;
+	}
+	FastLanesReadGlobalState gstate;
+	std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0}, dict_vectors {0}, cursor {0};
+	std::mutex err_mu;
+	std::string err;
+	int err_status = 0;
+	const int nt = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)std::max(1, n_threads), reader.MaxThreads()));
+	auto worker = [&]() {
+		try {
+			FastLanesReadLocalState lstate;
+			DataChunk chunk;
+			for (;;) {
+				{
+					std::lock_guard<std::mutex> g(gstate.lock);
+					if (!reader.TryInitializeScan(gstate, lstate)) {
+						return;
+					}
+				}
+				for (;;) {
+					reader.Scan(gstate, lstate, chunk);
+					if (chunk.count == 0) {
+						break;
+					}
+					const int64_t* frn = static_cast<const int64_t*>(chunk.data[n_cols].data);
+					const uint64_t base = row_ids_out ? cursor.fetch_add(chunk.count) : (uint64_t)frn[0];
+					for (uint32_t c = 0; c < n_cols; ++c) {
+						const Vector& v = chunk.data[c];
+						dict_vectors += v.vector_type == VectorType::DICTIONARY_VECTOR ? 1 : 0;
+						if (is_str[c]) {
+							const flsreader_string_sink* sink = static_cast<const flsreader_string_sink*>(out_cols[c]);
+							for (idx_t i = 0; i < chunk.count; ++i) {
+								const string_t* sv = static_cast<const string_t*>(v.Row(chunk.RowIndex(i)));
+								if (sv->GetSize() > sink->stride) {
+									throw ReaderError(FLSGPU_ERR_INVALID, "string longer than the sink's stride");
+								}
+								std::memcpy(sink->bytes + (base + i) * sink->stride, sv->GetData(), sv->GetSize());
+								sink->lengths[base + i] = sv->GetSize();
+							}
+						} else if (chunk.sel.empty() && v.vector_type == VectorType::FLAT_VECTOR) {
+							std::memcpy(static_cast<uint8_t*>(out_cols[c]) + base * widths[c], v.data, chunk.count * widths[c]);
+						} else {
+							for (idx_t i = 0; i < chunk.count; ++i) {
+								std::memcpy(static_cast<uint8_t*>(out_cols[c]) + (base + i) * widths[c], v.Row(chunk.RowIndex(i)), widths[c]);
+							}
+						}
+					}
+					for (idx_t i = 0; row_ids_out && i < chunk.count; ++i) {
+						row_ids_out[base + i] = frn[chunk.RowIndex(i)];
+					}
+					rows += chunk.count;
+					chunks += 1;
+					uint64_t m = maxrows.load();
+					while (chunk.count > m && !maxrows.compare_exchange_weak(m, chunk.count)) {
+					}
+				}
+			}
+		} catch (const ReaderError& e) {
+			std::lock_guard<std::mutex> g(err_mu);
+			err = e.what();
+			err_status = e.status;
+		} catch (const std::exception& e) {
+			std::lock_guard<std::mutex> g(err_mu);
+			err = e.what();
+			err_status = FLSGPU_ERR_INVALID;
+		}
+	};
+	std::vector<std::thread> th;
+	for (int i = 0; i < nt; ++i) {
+		th.emplace_back(worker);
+	}
+	for (auto& t : th) {
+		t.join();
+	}
+	if (err_status) {
+		throw ReaderError(err_status, err);
+	}
+	stats->rows = rows;
+	stats->chunks = chunks;
+	stats->max_chunk_rows = maxrows;
+	stats->dictionary_vectors = dict_vectors;
+	stats->pruned_rowgroups = reader.GetNPrunedRowGroups();
+}
+
+} // namespace
+
 int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, int n_threads, void* const* out_cols,
                        uint64_t* rows_out, uint64_t* chunks_out, uint64_t* max_chunk_rows) {
 	FLSR_TRY({
-		FastLanesReader& reader = *h->reader;
-		// the driver appends file_row_number to the projection to know where each chunk belongs
-		reader.column_ids.assign(column_ids, column_ids + n_cols);
-		reader.column_ids.push_back(COLUMN_IDENTIFIER_FILE_ROW_NUMBER);
-		const auto& cols = reader.GetColumns();
-		std::vector<uint32_t> widths(n_cols);
-		for (uint32_t c = 0; c < n_cols; ++c) {
-			if (column_ids[c] >= cols.size()) {
-				throw ReaderError(FLSGPU_ERR_INVALID, "Projected column id out of range");
-			}
-			widths[c] = cols[column_ids[c]].type.physical_bytes;
-		}
-		FastLanesReadGlobalState gstate;
-		std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0};
-		std::mutex err_mu;
-		std::string err;
-		int err_status = 0;
-		const int nt = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)std::max(1, n_threads), reader.MaxThreads()));
-		auto worker = [&]() {
-			try {
-				FastLanesReadLocalState lstate;
-				DataChunk chunk;
-				for (;;) {
-					{
-						std::lock_guard<std::mutex> g(gstate.lock);
-						if (!reader.TryInitializeScan(gstate, lstate)) {
-							return;
-						}
-					}
-					for (;;) {
-						reader.Scan(gstate, lstate, chunk);
-						if (chunk.count == 0) {
-							break;
-						}
-						const int64_t row0 = static_cast<const int64_t*>(chunk.data[n_cols].data)[0];
-						for (uint32_t c = 0; c < n_cols; ++c) {
-							std::memcpy(static_cast<uint8_t*>(out_cols[c]) + (uint64_t)row0 * widths[c], chunk.data[c].data,
-							            chunk.count * widths[c]);
-						}
-						rows += chunk.count;
-						chunks += 1;
-						uint64_t m = maxrows.load();
-						while (chunk.count > m && !maxrows.compare_exchange_weak(m, chunk.count)) {
-						}
-					}
-				}
-			} catch (const ReaderError& e) {
-				std::lock_guard<std::mutex> g(err_mu);
-				err = e.what();
-				err_status = e.status;
-			} catch (const std::exception& e) {
-				std::lock_guard<std::mutex> g(err_mu);
-				err = e.what();
-				err_status = FLSGPU_ERR_INVALID;
-			}
-		};
-		std::vector<std::thread> th;
-		for (int i = 0; i < nt; ++i) {
-			th.emplace_back(worker);
-		}
-		for (auto& t : th) {
-			t.join();
-		}
-		if (err_status) {
-			throw ReaderError(err_status, err);
-		}
-		*rows_out = rows;
-		*chunks_out = chunks;
-		*max_chunk_rows = maxrows;
+		flsreader_scan_stats st {};
+		scan_impl(h, column_ids, n_cols, nullptr, 0, n_threads, out_cols, nullptr, &st);
+		*rows_out = st.rows;
+		*chunks_out = st.chunks;
+		*max_chunk_rows = st.max_chunk_rows;
 	})
+}
+
+int flsreader_scan(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
+                   int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats) {
+	FLSR_TRY({ scan_impl(h, column_ids, n_cols, filters, n_filters, n_threads, out_cols, n_filters ? row_ids_out : nullptr, stats); })
 }

@@ -27,6 +27,27 @@ int flsreader_statistics(const flsreader_handle* h, const char* name, int* has_s
  * column id == n_columns (with file_row_number enabled) selects the virtual column. */
 int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, int n_threads, void* const* out_cols,
                        uint64_t* rows_out, uint64_t* chunks_out, uint64_t* max_chunk_rows);
+/* General form: string columns (VARCHAR / BLOB) are written through a fixed-stride sink (out_cols[c] points at a
+ * flsreader_string_sink), optional pushed-down filters (column_index addresses column_ids, constants are physical values
+ * as in flsgpu_filter).  With filters the passing rows are appended in arrival order and row_ids_out receives their file
+ * row numbers; without, rows land at their file row number and row_ids_out is ignored. */
+typedef struct flsreader_string_sink {
+	uint8_t* bytes;    /* row r occupies bytes[r*stride, r*stride + lengths[r]) */
+	uint32_t* lengths;
+	uint32_t stride;
+} flsreader_string_sink;
+typedef struct flsreader_filter {
+	uint64_t column_index;
+	int32_t op; /* flsgpu_cmp */
+	uint64_t constant;
+} flsreader_filter;
+typedef struct flsreader_scan_stats {
+	uint64_t rows, chunks, max_chunk_rows;
+	uint64_t dictionary_vectors; /* vectors handed over as DICTIONARY_VECTOR (dictionary_kernel.hpp:80-101) */
+	uint64_t pruned_rowgroups;   /* row groups the zone maps ruled out (row_group_filter.cpp:80-94) */
+} flsreader_scan_stats;
+int flsreader_scan(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
+                   int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats);
 #ifdef __cplusplus
 }
 #endif

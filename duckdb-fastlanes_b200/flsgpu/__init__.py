@@ -136,7 +136,7 @@ ABI_SYMBOLS = [
     "flsgpu_sync", "flsgpu_host_alloc", "flsgpu_host_free", "flsgpu_launch_count",
     "flsgpu_string_heap_bytes", "flsgpu_decode_strings", "flsgpu_decode_string_codes", "flsgpu_decode_string_dict",
     "flsgpu_string_dict_keys", "flsgpu_scan_strings_to_host", "flsgpu_scan_projection_to_host",
-    "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked",
+    "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked", "flsgpu_scan_filtered_to_host",
 ]
 
 
@@ -359,6 +359,12 @@ class Table:
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_aggregate_column_masked(self._h, col, rg_begin, n_rg, _vp(mask_ptr), _vp(keep_ptr), _vp(result_ptr), _vp(stream)),
                "aggregate_column_masked")
+
+    def scan_filtered_to_host(self, scan_columns, filters, mask_host_ptr, mask_bytes, rg_begin=0, n_rg=None):
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        arr = (ScanColumn * len(scan_columns))(*scan_columns)
+        _check(lib.flsgpu_scan_filtered_to_host(self._h, arr, len(scan_columns), make_filters(filters), len(filters), rg_begin, n_rg,
+                                                _vp(mask_host_ptr), C.c_uint64(mask_bytes)), "scan_filtered_to_host")
 
     def scan_projection_to_host(self, scan_columns, rg_begin=0, n_rg=None):
         """scan_columns: list of ScanColumn."""

@@ -222,6 +222,11 @@ typedef struct flsgpu_scan_column {
 	uint64_t keys_capacity_bytes;
 } flsgpu_scan_column;
 int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg);
+/* The same scan with pushed-down filters (FastLanesReader::Scan -> FilterExecutor::Apply, fls_reader.cpp:516-547): every
+ * projected column is returned in full, plus the selection mask of the filter set (flsgpu_filter_mask layout) so that the
+ * reader slices each 2048-row chunk with a selection vector.  Filter columns need not be projected. */
+int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, const flsgpu_filter* filters,
+                                 uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg, uint32_t* mask_host, uint64_t mask_capacity_bytes);
 
 int flsgpu_sync(void* cuda_stream);
 /* Pinned host allocations for staging / results (cudaHostAlloc). */

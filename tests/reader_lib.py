@@ -15,7 +15,20 @@ lib.flsreader_total_tuples.restype = C.c_uint64
 lib.flsreader_progress.restype = C.c_double
 
 TYPE_NAMES = ["INVALID", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UBIGINT", "FLOAT", "DOUBLE", "DATE",
-              "TIMESTAMP", "DECIMAL"]
+              "TIMESTAMP", "DECIMAL", "VARCHAR", "BLOB"]
+
+
+class StringSink(C.Structure):
+    _fields_ = [("bytes", C.c_void_p), ("lengths", C.c_void_p), ("stride", C.c_uint32)]
+
+
+class ReaderFilter(C.Structure):
+    _fields_ = [("column_index", C.c_uint64), ("op", C.c_int32), ("constant", C.c_uint64)]
+
+
+class ScanStats(C.Structure):
+    _fields_ = [("rows", C.c_uint64), ("chunks", C.c_uint64), ("max_chunk_rows", C.c_uint64), ("dictionary_vectors", C.c_uint64),
+                ("pruned_rowgroups", C.c_uint64)]
 NP_OF = {"BOOLEAN": np.uint8, "TINYINT": np.int8, "SMALLINT": np.int16, "INTEGER": np.int32, "BIGINT": np.int64,
          "UBIGINT": np.uint64, "FLOAT": np.float32, "DOUBLE": np.float64, "DATE": np.int32, "TIMESTAMP": np.int64}
 
@@ -91,6 +104,46 @@ class Reader:
         if rc:
             raise ReaderError(rc)
         return outs, dict(rows=rows.value, chunks=chunks.value, max_chunk_rows=mx.value)
+
+    def scan(self, column_ids=None, filters=(), n_threads=1, stride=64):
+        """SELECT cols FROM read_fls(path) WHERE filters.  filters: [(index into column_ids, op, physical constant)].
+        Returns (columns, row ids or None, stats): string columns come back as lists of bytes; with filters the rows are
+        sorted by file row number."""
+        ids = list(range(len(self.columns))) if column_ids is None else list(column_ids)
+        n = self.total_tuples
+        outs, keep, ptrs = [], [], []
+        for i in ids:
+            if self.columns[i]["type"] in ("VARCHAR", "BLOB"):
+                data = np.zeros((n, stride), dtype=np.uint8)
+                lens = np.zeros(n, dtype=np.uint32)
+                sink = StringSink(data.ctypes.data, lens.ctypes.data, stride)
+                keep.append(sink)
+                outs.append((data, lens))
+                ptrs.append(C.addressof(sink))
+            else:
+                a = np.zeros(n, dtype=self.np_dtype(i))
+                outs.append(a)
+                ptrs.append(a.ctypes.data)
+        ia = (C.c_uint64 * len(ids))(*ids)
+        pa = (C.c_void_p * len(ids))(*ptrs)
+        fa = (ReaderFilter * max(1, len(filters)))(*[ReaderFilter(ci, op, k & 0xFFFFFFFFFFFFFFFF) for ci, op, k in filters])
+        row_ids = np.zeros(n, dtype=np.int64)
+        st = ScanStats()
+        rc = lib.flsreader_scan(self._h, ia, len(ids), fa, len(filters), n_threads, pa, C.c_void_p(row_ids.ctypes.data), C.byref(st))
+        if rc:
+            raise ReaderError(rc)
+        m = st.rows
+        order = np.argsort(row_ids[:m], kind="stable") if filters else np.arange(m)
+        cols = []
+        for o in outs:
+            if isinstance(o, tuple):
+                data, lens = o
+                cols.append([data[j, :lens[j]].tobytes() for j in order])
+            else:
+                cols.append(o[:m][order] if filters else o)
+        stats = dict(rows=st.rows, chunks=st.chunks, max_chunk_rows=st.max_chunk_rows, dictionary_vectors=st.dictionary_vectors,
+                     pruned_rowgroups=st.pruned_rowgroups)
+        return cols, (row_ids[:m][order] if filters else None), stats
 
     def close(self):
         if self._h:

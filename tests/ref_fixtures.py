@@ -20,3 +20,15 @@ def reference_test_tables(n=1024):
         "date_table": ("TIMESTAMP", (8116 + i) * 86_400_000_000),                      # :120-125 (DATE + INTERVAL -> TIMESTAMP)
         "timestamp_table": ("TIMESTAMP", 1_735_689_600_000_000 + i * 1_000_000),       # :127-132
     }
+
+
+def reference_string_tables(n=1024):
+    """The string-typed tables of the same test: VARCHAR (:113-118), BLOB (:155-160), and HUGEINT / UHUGEINT (:78-90), which
+    the reference writes as decimal strings (src/writer/fls_view_writer.cpp:20-46, Int128ViewWriterFactory)."""
+    import hashlib
+    return {
+        "varchar_table": ("VARCHAR", [b"Value %d" % i for i in range(1, n + 1)]),
+        "blob_table": ("BLOB", [hashlib.md5(str(i).encode()).hexdigest().encode() for i in range(1, n + 1)]),
+        "hugeint_table": ("VARCHAR", [str(i * -469231731687303715884105728).encode() for i in range(1, n + 1)]),
+        "uhugeint_table": ("VARCHAR", [str(i * 469231731687303715884105728).encode() for i in range(1, n + 1)]),
+    }

@@ -17,7 +17,7 @@ import pytest
 
 import flsgpu
 import oracle_lib
-from ref_fixtures import reference_test_tables
+from ref_fixtures import reference_string_tables, reference_test_tables
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLDEN = os.path.join(ROOT, "tests", "golden", "alp_golden.npz")
@@ -132,4 +132,22 @@ def test_reference_test_tables_roundtrip(n):
             out = o.decode_column(c, 0, t.n_rowgroups, 0, dt, t.vec_per_rowgroup, n_threads=4)
             got = np.concatenate([out[a:b] for a, b in t.valid_mask_slices()])
             assert got.tobytes() == np.ascontiguousarray(src).tobytes(), (name, c)
+        t.close()
+
+
+@pytest.mark.parametrize("n", [1024, 100_000])
+def test_reference_string_tables_roundtrip(n):
+    """VARCHAR, BLOB, HUGEINT and UHUGEINT (written as decimal strings) tables of the reference test (:78-90,113-118,155-160,
+    :300-326,350-352): writer + oracle give back every value."""
+    ids = np.arange(1, n + 1, dtype=np.int64)
+    for name, (tname, vals) in reference_string_tables(n).items():
+        img = flsgpu.write_table([("id", "INT64", None), ("col", tname, None)], [ids, vals])
+        t = flsgpu.Table(img)
+        o = oracle_lib.Oracle(img)
+        st, heap = o.decode_strings(1, 0, t.n_rowgroups, t.vec_per_rowgroup)
+        st = st.view(flsgpu.STRING_T).reshape(-1)
+        got = []
+        for a, b in t.valid_mask_slices():
+            got += flsgpu.strings_from(st[a:b], heap)
+        assert got == vals, name
         t.close()

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 import flsgpu
-from ref_fixtures import reference_test_tables
+from ref_fixtures import reference_string_tables, reference_test_tables
 
 
 def write(tmp_path, name, cols, arrs, vec_per_rg=64):
@@ -103,4 +103,79 @@ def test_projection_virtual_column_and_chunking(tmp_path):
     assert st["chunks"] == 5 * 4 + 1 and st["rows"] == n
     with pytest.raises(reader_lib.ReaderError):
         r.scan_all([9])
+    r.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("threads", [1, 4])
+@pytest.mark.parametrize("n", [1024, 50_000])
+def test_reference_string_tables_through_reader(tmp_path, n, threads):
+    """varchar_table / blob_table / hugeint_table / uhugeint_table of the reference test: SELECT * FROM read_fls(...)."""
+    import reader_lib
+    ids = np.arange(1, n + 1, dtype=np.int64)
+    for name, (tname, vals) in reference_string_tables(n).items():
+        p = write(tmp_path, f"{name}_{n}_{threads}.fls", [("id", "INT64", None), ("col", tname, None)], [ids, vals], 8)
+        r = reader_lib.Reader(p, rowgroups_per_batch=3)
+        assert r.columns[1]["type"] == ("BLOB" if tname == "BLOB" else "VARCHAR")
+        (got_id, got_col), _, st = r.scan(n_threads=threads)
+        assert st["rows"] == n and np.array_equal(got_id, ids), name
+        assert got_col == vals, name
+        r.close()
+
+
+@pytest.mark.gpu
+def test_dictionary_vectors_and_mixed_encodings(tmp_path):
+    """Dictionary-encoded string chunks reach the consumer as DICTIONARY_VECTORs (dictionary_kernel.hpp:80-101); a batch
+    that mixes dictionary and FSST chunks is materialised flat; both give the same strings."""
+    import reader_lib
+    n = 6 * 8192
+    low = [[b"AIR", b"RAIL", b"TRUCK", b"REG AIR", b"SHIP", b"FOB", b"MAIL"][i % 7] for i in range(n)]
+    rng = np.random.default_rng(8)
+    mixed = [b"k%d" % (i % 13) if (i // 8192) % 2 == 0 else b"unique-%d-%d" % (i, int(rng.integers(0, 1 << 30))) for i in range(n)]
+    p = write(tmp_path, "d.fls", [("low", "VARCHAR", None), ("mixed", "VARCHAR", None)], [low, mixed], 8)
+    t = flsgpu.Table(path=p)
+    encs = {flsgpu.ENC_NAME[t.chunk(r, 1).encoding] for r in range(t.n_rowgroups)}
+    assert "DICT_STR" in encs and len(encs) > 1
+    t.close()
+    r = reader_lib.Reader(p, rowgroups_per_batch=2)
+    (got_low,), _, st = r.scan([0], n_threads=2)
+    assert got_low == low and st["dictionary_vectors"] == st["chunks"] > 0
+    (got_mixed,), _, st = r.scan([1], n_threads=2)
+    assert got_mixed == mixed and st["dictionary_vectors"] == 0
+    r2 = reader_lib.Reader(p, rowgroups_per_batch=1)  # one row group per batch: the dictionary row groups keep their form
+    (got_mixed,), _, st = r2.scan([1], n_threads=3)
+    assert got_mixed == mixed and 0 < st["dictionary_vectors"] < st["chunks"]
+    r.close()
+    r2.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("threads", [1, 4])
+def test_filter_pushdown_through_reader(tmp_path, threads):
+    """WHERE clauses pushed into the scan (read_fls.cpp:39-42): zone maps prune row groups, the device evaluates the
+    comparisons, chunks come back sliced by a selection vector; result == numpy."""
+    import reader_lib
+    from filter_cases import bits, filter_sets, numpy_mask, table
+    n = 20 * 8192 + 333
+    cols = table(n, seed=21)
+    names = [c[0] for c in cols]
+    comments = [b"row %d" % i for i in range(n)]
+    p = write(tmp_path, "f.fls", [(c[0], c[1], c[2]) + tuple(c[4:6]) for c in cols] + [("note", "VARCHAR", None)],
+              [c[3] for c in cols] + [comments], 8)
+    r = reader_lib.Reader(p, rowgroups_per_batch=4)
+    proj = list(range(len(cols) + 1))
+    for fname in ("q6", "dbl_nan_gt", "small_neg", "runs_band", "none_pass", "all_pass", "dic_eq"):
+        fs = filter_sets()[fname]
+        filt = [(names.index(c), flsgpu.CMP[op], bits(k, k.dtype)) for c, op, k in fs]
+        got, row_ids, st = r.scan(proj, filt, n_threads=threads)
+        want = numpy_mask(cols, fs)
+        assert st["rows"] == int(want.sum()), fname
+        assert np.array_equal(row_ids, np.nonzero(want)[0]), fname
+        for ci in (names.index("price"), names.index("shipdate"), names.index("dbl")):
+            assert got[ci].tobytes() == cols[ci][3][want].tobytes(), (fname, names[ci])
+        assert got[-1] == [comments[i] for i in np.nonzero(want)[0]], fname
+        if fname == "q6":
+            assert st["pruned_rowgroups"] > 0
+        if fname == "none_pass":
+            assert st["pruned_rowgroups"] == 21 and st["chunks"] == 0
     r.close()
