@@ -72,6 +72,10 @@ struct FlsStrLaunch {
 	uint32_t groups_per_rg;      // heap kernel: CTAs per chunk (set by the launcher)
 	uint32_t codes_only;         // rows kernel: emit the u32 selection vector instead of string_t
 	uint32_t dict_only;          // heap kernel: fill only the slices of dictionary-encoded chunks
+	uint32_t lane_strings;       // FSST decode: strings per lane (a warp tile = 32 * lane_strings strings)
+	uint32_t cbuf_bytes;         // per-warp shared-memory staging of a tile's codes / decoded bytes (multiples of 16;
+	uint32_t dbuf_bytes;         //  tiles that do not fit are decoded straight to global memory)
+	uint32_t fuse_rows;          // FSST chunks: the heap kernel also builds the string_t rows (the rows kernel skips them)
 };
 
 // Per-warp shared memory holding the 32 vector descriptors of a batch (64 B each), in front of the pipeline slots.

@@ -1061,6 +1061,41 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	L->key_prefix = d->d_key_prefix + i0;
 	L->key_prefix0 = d->key_prefix[i0];
 	L->dict_only = 0;
+	L->fuse_rows = 0;
+	// FSST tiling: size a warp tile (32 * lane_strings strings) so that its codes + decoded bytes take <= 8 KiB of shared
+	// memory at twice the column's average string length: the decode is latency bound (dependent shared-memory lookups per
+	// code), so resident warps matter more than long per-lane runs (measured, 20 M l_comment-like strings: 26 KiB/warp
+	// 1.17 ms, 14 KiB 0.79 ms, 7-10 KiB 0.63 ms, <= 5 KiB (one string per lane) 0.70 ms)
+	uint64_t n_str = 0, dec_bytes = 0, comp_bytes = 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		const fls_chunk_desc& ch = t->chunk(r, col);
+		if (ch.encoding == FLS_ENC_FSST || ch.encoding == FLS_ENC_FSST_DICT) {
+			n_str += ch.aux_count;
+			dec_bytes += ch.const_val;
+			comp_bytes += ch.seg_size[FLS_SEG_AUX0] - sizeof(fls_fsst_table);
+		}
+	}
+	L->lane_strings = 8;
+	L->cbuf_bytes = L->dbuf_bytes = 0;
+	if (n_str) {
+		const double avg_dec = (double)dec_bytes / (double)n_str, avg_comp = (double)comp_bytes / (double)n_str;
+		const uint32_t budget = env_u32("FLSGPU_STR_WARP_KB", 8) * 1024u, cap = 26u * 1024u;
+		uint32_t ls = std::min(16u, env_u32("FLSGPU_STR_LANE_STRINGS", 16));
+		for (;; ls >>= 1) {
+			const uint32_t db = ((uint32_t)(2.0 * 32.0 * ls * avg_dec) + 64u + 255u) & ~255u;
+			const uint32_t cb = ((uint32_t)(2.0 * 32.0 * ls * avg_comp) + 64u + 255u) & ~255u;
+			if (db + cb <= budget || ls == 1) {
+				L->lane_strings = ls;
+				L->dbuf_bytes = db;
+				L->cbuf_bytes = cb;
+				if (db + cb > cap) { // very long strings: whatever fits goes through the buffers, the rest decodes to global
+					L->dbuf_bytes = (cap * 3u / 4u) & ~255u;
+					L->cbuf_bytes = cap - L->dbuf_bytes;
+				}
+				break;
+			}
+		}
+	}
 	L->chunk_stride = t->header.n_columns;
 	L->vec_per_rg = t->header.vec_per_rowgroup;
 	L->n_rg = n_rg;
@@ -1097,6 +1132,7 @@ int flsgpu_decode_strings(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint
 	L.heap = static_cast<uint8_t*>(heap_dev);
 	L.heap_base_addr = heap_base_addr;
 	L.out = out_strings_dev;
+	L.fuse_rows = env_u32("FLSGPU_STR_FUSE_ROWS", 1);
 	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
 	FLS_CUDA(fls_str_launch_heap(L, s));
 	FLS_CUDA(fls_str_launch_rows(L, s));
