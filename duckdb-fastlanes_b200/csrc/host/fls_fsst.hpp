@@ -32,6 +32,25 @@ struct FsstEncoder {
 	int find(const uint8_t* s, uint64_t remaining, uint32_t* len_out) const;
 };
 
+// FSST12 (fls_format.h fls_fsst12_table): 12-bit codes, codes < 256 are the bytes themselves, up to 3840 trained symbols of
+// 2..8 bytes.  Same trainer idea (count symbols and adjacent pairs on a sample, keep the best), greedy longest match.
+struct Fsst12Encoder {
+	fls_fsst12_table table {};
+	uint32_t n_symbols = 0; // trained symbols: codes 256 .. 256 + n_symbols - 1
+	std::vector<uint32_t> slots;
+	uint8_t max_len = 0;
+
+	void train(const uint64_t* offsets, const uint8_t* bytes, uint64_t n);
+	// appends the packed 12-bit code stream of one string to out
+	void compress(const uint8_t* s, uint64_t len, std::vector<uint8_t>& out) const;
+
+  private:
+	void rebuild_lookup();
+	int find(const uint8_t* s, uint64_t remaining, uint32_t* len_out) const; // code >= 256 or -1
+};
+// decoded length of a packed 12-bit code stream; ~0ull if malformed (1 trailing byte)
+uint64_t fsst12_decoded_length(const fls_fsst12_table& table, const uint8_t* codes, uint64_t n);
+
 // decoded length of a code stream under `table` (len of each code, 1 per escaped literal); ~0ull if malformed
 uint64_t fsst_decoded_length(const fls_fsst_table& table, const uint8_t* codes, uint64_t n);
 

@@ -7,6 +7,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <memory>
 #include <string_view>
 #include <unordered_map>
 
@@ -79,11 +80,13 @@ void encode_str_uncompressed(const StrChunk& c, EncodedChunk& out) {
 }
 
 // AUX0 = table | code streams, AUX1 = comp_end[n] | dec_end[n] for the n strings given by (offsets, bytes)
-void fsst_segments(const uint64_t* offsets, const uint8_t* bytes, uint32_t n, uint32_t n_padded, ChunkBuilder& b, uint64_t* decoded_total) {
-	FsstEncoder enc;
+template <class Encoder, class Table>
+void fsst_segments_t(const uint64_t* offsets, const uint8_t* bytes, uint32_t n, uint32_t n_padded, ChunkBuilder& b, uint64_t* decoded_total) {
+	auto enc_holder = std::make_unique<Encoder>(); // the FSST12 encoder carries a 36 KiB table: keep it off the stack
+	Encoder& enc = *enc_holder;
 	enc.train(offsets, bytes, n);
-	b.aux0.resize(sizeof(fls_fsst_table));
-	std::memcpy(b.aux0.data(), &enc.table, sizeof(fls_fsst_table));
+	b.aux0.resize(sizeof(Table));
+	std::memcpy(b.aux0.data(), &enc.table, sizeof(Table));
 	std::vector<uint8_t> codes;
 	codes.reserve((size_t)(offsets[n] - offsets[0]) / 2 + 16);
 	std::vector<uint32_t> comp_end(n_padded), dec_end(n_padded);
@@ -102,12 +105,21 @@ void fsst_segments(const uint64_t* offsets, const uint8_t* bytes, uint32_t n, ui
 	*decoded_total = offsets[n] - offsets[0];
 }
 
-void encode_str_fsst(const StrChunk& c, EncodedChunk& out) {
+void fsst_segments(bool twelve, const uint64_t* offsets, const uint8_t* bytes, uint32_t n, uint32_t n_padded, ChunkBuilder& b,
+                   uint64_t* decoded_total) {
+	if (twelve) {
+		fsst_segments_t<Fsst12Encoder, fls_fsst12_table>(offsets, bytes, n, n_padded, b, decoded_total);
+	} else {
+		fsst_segments_t<FsstEncoder, fls_fsst_table>(offsets, bytes, n, n_padded, b, decoded_total);
+	}
+}
+
+void encode_str_fsst(const StrChunk& c, bool twelve, EncodedChunk& out) {
 	ChunkBuilder b;
 	plain_meta(c, b);
 	uint64_t total = 0;
-	fsst_segments(c.offsets, c.bytes, c.n_tuples, c.n_vec * kVec, b, &total);
-	fls_chunk_desc d = c.base_desc(FLS_ENC_FSST);
+	fsst_segments(twelve, c.offsets, c.bytes, c.n_tuples, c.n_vec * kVec, b, &total);
+	fls_chunk_desc d = c.base_desc(twelve ? FLS_ENC_FSST12 : FLS_ENC_FSST);
 	d.aux_count = c.n_vec * kVec;
 	d.const_val = total;
 	b.finish(out, d);
@@ -172,7 +184,8 @@ bool build_dict(const StrChunk& c, size_t max_keys, StrDict& d) {
 	return true;
 }
 
-void encode_str_dict(const StrChunk& c, const StrDict& dict, bool fsst, EncodedChunk& out) {
+void encode_str_dict(const StrChunk& c, const StrDict& dict, int enc_kind, EncodedChunk& out) {
+	const bool fsst = enc_kind != FLS_ENC_DICT_STR;
 	const uint32_t n_keys = (uint32_t)dict.key_off.size() - 1;
 	const unsigned idx_bits = n_keys <= 256 ? 8 : n_keys <= 65536 ? 16 : 32;
 	ChunkBuilder b;
@@ -187,12 +200,12 @@ void encode_str_dict(const StrChunk& c, const StrDict& dict, bool fsst, EncodedC
 		pack_codes(codes, idx_bits, b, m);
 		b.meta.push_back(m);
 	}
-	fls_chunk_desc d = c.base_desc(fsst ? FLS_ENC_FSST_DICT : FLS_ENC_DICT_STR);
+	fls_chunk_desc d = c.base_desc(enc_kind);
 	d.idx_bits = (uint8_t)idx_bits;
 	d.aux_count = n_keys;
 	if (fsst) {
 		uint64_t total = 0;
-		fsst_segments(dict.key_off.data(), dict.key_bytes.data(), n_keys, n_keys, b, &total);
+		fsst_segments(enc_kind == FLS_ENC_FSST12_DICT, dict.key_off.data(), dict.key_bytes.data(), n_keys, n_keys, b, &total);
 		d.const_val = total;
 	} else {
 		b.aux0 = dict.key_bytes;
@@ -255,14 +268,16 @@ bool encode_string_chunk(const uint64_t* offsets, const uint8_t* bytes, uint32_t
 		encode_str_constant(c, out);
 		return true;
 	case FLS_ENC_STR_UNCOMPRESSED: encode_str_uncompressed(c, out); return true;
-	case FLS_ENC_FSST: encode_str_fsst(c, out); return true;
+	case FLS_ENC_FSST: encode_str_fsst(c, false, out); return true;
+	case FLS_ENC_FSST12: encode_str_fsst(c, true, out); return true;
 	case FLS_ENC_DICT_STR:
 	case FLS_ENC_FSST_DICT:
+	case FLS_ENC_FSST12_DICT:
 		if (!have_dict && !build_dict(c, ~(size_t)0 >> 1, dict)) {
 			*err = "dictionary too large";
 			return false;
 		}
-		encode_str_dict(c, dict, enc == FLS_ENC_FSST_DICT, out);
+		encode_str_dict(c, dict, enc, out);
 		return true;
 	default: *err = "encoding not applicable to a string column"; return false;
 	}

@@ -1077,6 +1077,16 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	}
 	L->lane_strings = 8;
 	L->cbuf_bytes = L->dbuf_bytes = 0;
+	uint32_t max_fsst_strings = 0;
+	uint64_t max_plain_bytes = 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		const fls_chunk_desc& ch = t->chunk(r, col);
+		if (ch.encoding == FLS_ENC_FSST || ch.encoding == FLS_ENC_FSST_DICT) {
+			max_fsst_strings = std::max(max_fsst_strings, ch.aux_count);
+		} else {
+			max_plain_bytes = std::max<uint64_t>(max_plain_bytes, ch.const_val);
+		}
+	}
 	if (n_str) {
 		const double avg_dec = (double)dec_bytes / (double)n_str, avg_comp = (double)comp_bytes / (double)n_str;
 		const uint32_t budget = env_u32("FLSGPU_STR_WARP_KB", 8) * 1024u, cap = 26u * 1024u;
@@ -1096,10 +1106,14 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 			}
 		}
 	}
+	// CTAs per chunk of the heap kernel: enough 8-warp CTAs for the largest FSST chunk's tiles, and one CTA per 32 KiB of
+	// plain bytes (a 9 KiB dictionary is one CTA's work, not 32 CTAs copying 280 bytes each)
+	const uint32_t per_cta = 8u * 32u * L->lane_strings;
+	L->groups_per_rg = std::max<uint32_t>(1u, std::max<uint32_t>((max_fsst_strings + per_cta - 1u) / per_cta,
+	                                                            (uint32_t)((max_plain_bytes + 32767u) >> 15)));
 	L->chunk_stride = t->header.n_columns;
 	L->vec_per_rg = t->header.vec_per_rowgroup;
 	L->n_rg = n_rg;
-	L->groups_per_rg = 0;
 	L->codes_only = 0;
 	*dout = d;
 	return FLSGPU_OK;

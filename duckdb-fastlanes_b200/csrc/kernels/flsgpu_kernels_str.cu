@@ -386,12 +386,15 @@ __global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L)
 } // namespace
 
 cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream) {
-	// 8 warp tiles of 32 * lane_strings strings per CTA; a chunk has at most vec_per_rg * 1024 strings
+	// 8 warp tiles of 32 * lane_strings strings per CTA; groups_per_rg (CTAs per chunk) comes from the launcher, which knows
+	// the largest chunk of the range
 	if (L.lane_strings == 0) {
 		L.lane_strings = 8;
 	}
-	const uint32_t per_cta = kWarps * 32u * L.lane_strings;
-	L.groups_per_rg = (L.vec_per_rg * 1024u + per_cta - 1u) / per_cta;
+	if (L.groups_per_rg == 0) {
+		const uint32_t per_cta = kWarps * 32u * L.lane_strings;
+		L.groups_per_rg = (L.vec_per_rg * 1024u + per_cta - 1u) / per_cta;
+	}
 	const uint32_t smem = kWarps * (L.cbuf_bytes + L.dbuf_bytes);
 	static bool attr_set = false; // benign race: the attribute is idempotent
 	if (!attr_set) {

@@ -70,8 +70,16 @@ typedef enum fls_encoding {
 	FLS_ENC_STR_CONSTANT = 13, /* dec_constant_str_opr */
 	FLS_ENC_FSST = 14,        /* dec_fsst_opr: FSST-compressed strings (8-bit codes, 255 = escape) */
 	FLS_ENC_FSST_DICT = 15,   /* dec_fsst_dict_opr<IDX>: dictionary whose strings are FSST-compressed + packed codes */
-	FLS_ENC_COUNT = 16
+	FLS_ENC_FSST12 = 16,      /* dec_fsst12_opr: FSST with 12-bit codes (4096 symbols, codes < 256 = the byte itself, no escapes) */
+	FLS_ENC_FSST12_DICT = 17, /* dec_fsst12_dict_opr<IDX> */
+	FLS_ENC_COUNT = 18
 } fls_encoding;
+
+#define FLS_ENC_IS_FSST8(e) ((e) == FLS_ENC_FSST || (e) == FLS_ENC_FSST_DICT)
+#define FLS_ENC_IS_FSST12(e) ((e) == FLS_ENC_FSST12 || (e) == FLS_ENC_FSST12_DICT)
+#define FLS_ENC_IS_FSST_ANY(e) (FLS_ENC_IS_FSST8(e) || FLS_ENC_IS_FSST12(e))
+#define FLS_ENC_IS_FSST_ROWS(e) ((e) == FLS_ENC_FSST || (e) == FLS_ENC_FSST12) /* one compressed string per row */
+#define FLS_ENC_IS_STR_DICT(e) ((e) == FLS_ENC_DICT_STR || (e) == FLS_ENC_FSST_DICT || (e) == FLS_ENC_FSST12_DICT)
 
 /* Segment slots inside a column chunk. */
 enum {
@@ -166,6 +174,7 @@ typedef struct fls_vec_meta { /* 32 bytes */
  *   DICT_STR:         META/DATA = packed codes as for DICT (idx_bits lanes); AUX0 = dictionary bytes; AUX1 = u32 end[n_keys]
  *   FSST:             AUX0 = fls_fsst_table | compressed bytes; AUX1 = u32 comp_end[n] | u32 dec_end[n]
  *   FSST_DICT:        META/DATA = packed codes; AUX0 = fls_fsst_table | compressed dictionary; AUX1 = comp_end[n_keys] | dec_end[n_keys]
+ *   FSST12 / FSST12_DICT: the same with fls_fsst12_table and 12-bit code streams
  * const_val = number of DECODED string bytes of the chunk (its share of the string heap); the per-string decoded end
  * offsets make every string's heap position known without decoding its predecessors (entry points, like PointTo). */
 typedef struct fls_fsst_table { /* fsst_decoder_t of duckdb/third_party/fsst/fsst.h:70-75 without its header bytes */
@@ -173,6 +182,15 @@ typedef struct fls_fsst_table { /* fsst_decoder_t of duckdb/third_party/fsst/fss
 	uint8_t len[256];     /* byte length of symbol[c], 1..8 */
 } fls_fsst_table;
 #define FLS_FSST_ESC 255u
+/* FSST12 (reference fsst12_kernel.hpp:14-57, fsst12_dict_kernel.hpp; decoder of cwida/fsst's fsst12.h, which lives in the
+ * absent FastLanes library): 12-bit codes, two per 3 bytes, little endian: code0 = b0 | (b1 & 15) << 8, code1 = b1 >> 4 |
+ * b2 << 4; a string with an odd number of codes ends with one code in 2 bytes.  Codes < 256 stand for the byte itself,
+ * codes >= 256 for symbol[code] (2..8 bytes, zero padded).  Segment layout as FSST / FSST_DICT with this table in front. */
+typedef struct fls_fsst12_table {
+	uint64_t symbol[4096];
+	uint8_t len[4096];
+} fls_fsst12_table;
+#define FLS_FSST_TABLE_BYTES(e) (FLS_ENC_IS_FSST12(e) ? sizeof(fls_fsst12_table) : sizeof(fls_fsst_table))
 
 #define FLS_PAD16(x) (((x) + 15u) & ~15u)
 #define FLS_EXC_TAIL_BYTES(n, elem_bytes) ((n) ? FLS_PAD16((uint32_t)(n) * (elem_bytes)) + FLS_PAD16((uint32_t)(n) * 2u) : 0u)
