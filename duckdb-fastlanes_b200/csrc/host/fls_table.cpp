@@ -2,6 +2,7 @@
 #include "flsgpu.h"
 #include "fls_error.hpp"
 #include "fls_table.hpp"
+#include "fls_fsst.hpp"
 
 #include <cstdio>
 #include <cstring>
@@ -36,8 +37,7 @@ static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
 }
 
 static bool is_string_enc(unsigned enc) {
-	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_STR_UNCOMPRESSED || enc == FLS_ENC_STR_CONSTANT || enc == FLS_ENC_FSST ||
-	       enc == FLS_ENC_FSST_DICT;
+	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_STR_UNCOMPRESSED || enc == FLS_ENC_STR_CONSTANT || FLS_ENC_IS_FSST_ANY(enc);
 }
 
 // String chunk (fls_format.h "String columns"): every offset array must be monotone and end at its byte segment's size,
@@ -48,8 +48,8 @@ static const char* validate_string_chunk(const flsgpu_table* t, const fls_chunk_
 	const uint8_t* aux0 = base + ch.seg_off[FLS_SEG_AUX0];
 	const uint32_t* aux1 = reinterpret_cast<const uint32_t*>(base + ch.seg_off[FLS_SEG_AUX1]);
 	const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(base + ch.seg_off[FLS_SEG_META]);
-	const bool dict = ch.encoding == FLS_ENC_DICT_STR || ch.encoding == FLS_ENC_FSST_DICT;
-	const bool fsst = ch.encoding == FLS_ENC_FSST || ch.encoding == FLS_ENC_FSST_DICT;
+	const bool dict = FLS_ENC_IS_STR_DICT(ch.encoding);
+	const bool fsst = FLS_ENC_IS_FSST_ANY(ch.encoding), fsst12 = FLS_ENC_IS_FSST12(ch.encoding);
 	for (uint32_t v = 0; v < ch.n_vec; ++v) {
 		if (meta[v].n_valid == 0 || meta[v].n_valid > FLS_VEC_SZ) {
 			return "vector n_valid out of range";
@@ -77,7 +77,7 @@ static const char* validate_string_chunk(const flsgpu_table* t, const fls_chunk_
 			}
 		}
 	}
-	const uint64_t table_bytes = fsst ? sizeof(fls_fsst_table) : 0;
+	const uint64_t table_bytes = fsst ? FLS_FSST_TABLE_BYTES(ch.encoding) : 0;
 	if (ch.seg_size[FLS_SEG_AUX0] < table_bytes) {
 		return "FSST table missing";
 	}
@@ -94,6 +94,32 @@ static const char* validate_string_chunk(const flsgpu_table* t, const fls_chunk_
 	}
 	if (!fsst) {
 		return ch.const_val == n_bytes ? nullptr : "decoded byte count disagrees with the byte segment";
+	}
+	if (fsst12) {
+		// 12-bit codes: every symbol zero padded beyond its length (the device ORs symbols into the output word unmasked),
+		// codes < 256 are the bytes themselves, streams decode to the promised lengths
+		const fls_fsst12_table* t12 = reinterpret_cast<const fls_fsst12_table*>(aux0);
+		for (int c = 0; c < 4096; ++c) {
+			const unsigned len = t12->len[c];
+			if (len == 0 || len > 8 || (len < 8 && (t12->symbol[c] >> (8 * len)) != 0)) {
+				return "FSST12 symbol length out of range or symbol not zero padded";
+			}
+			if (c < 256 && (len != 1 || t12->symbol[c] != (uint64_t)c)) {
+				return "FSST12 codes below 256 must stand for their own byte";
+			}
+		}
+		const uint8_t* codes12 = aux0 + table_bytes;
+		const uint32_t* dec_end12 = aux1 + n;
+		uint32_t cprev12 = 0, dprev12 = 0;
+		for (uint64_t i = 0; i < n; ++i) {
+			const uint64_t len = flshost::fsst12_decoded_length(*t12, codes12 + cprev12, aux1[i] - cprev12);
+			if (len == ~0ull || dec_end12[i] < dprev12 || dec_end12[i] - dprev12 != len) {
+				return "FSST12 decoded end offsets disagree with the code stream";
+			}
+			cprev12 = aux1[i];
+			dprev12 = dec_end12[i];
+		}
+		return ch.const_val == dprev12 ? nullptr : "decoded byte count disagrees with the decoded end offsets";
 	}
 	const fls_fsst_table* tab = reinterpret_cast<const fls_fsst_table*>(aux0);
 	for (int c = 0; c < 256; ++c) {
@@ -408,7 +434,7 @@ int flsgpu_string_dict_keys(const flsgpu_table* t, uint32_t col, uint32_t rg_beg
 	uint64_t total = 0;
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
 		const fls_chunk_desc& ch = t->chunk(r, col);
-		if (ch.encoding != FLS_ENC_DICT_STR && ch.encoding != FLS_ENC_FSST_DICT) {
+		if (!FLS_ENC_IS_STR_DICT(ch.encoding)) {
 			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_string_dict_keys: chunk is not dictionary encoded");
 		}
 		total += ch.aux_count;

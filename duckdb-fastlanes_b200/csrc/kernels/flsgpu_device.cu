@@ -230,7 +230,7 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 				if (r < h.n_rowgroups && t->columns[c].phys_bits == 128) {
 					const fls_chunk_desc& ch = t->chunk(r, c);
 					acc += (ch.const_val + 15u) & ~15ull;
-					keys += (ch.encoding == FLS_ENC_DICT_STR || ch.encoding == FLS_ENC_FSST_DICT) ? ch.aux_count : 0u;
+					keys += FLS_ENC_IS_STR_DICT(ch.encoding) ? ch.aux_count : 0u;
 				}
 			}
 		}
@@ -1069,10 +1069,10 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	uint64_t n_str = 0, dec_bytes = 0, comp_bytes = 0;
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
 		const fls_chunk_desc& ch = t->chunk(r, col);
-		if (ch.encoding == FLS_ENC_FSST || ch.encoding == FLS_ENC_FSST_DICT) {
+		if (FLS_ENC_IS_FSST_ANY(ch.encoding)) {
 			n_str += ch.aux_count;
 			dec_bytes += ch.const_val;
-			comp_bytes += ch.seg_size[FLS_SEG_AUX0] - sizeof(fls_fsst_table);
+			comp_bytes += ch.seg_size[FLS_SEG_AUX0] - FLS_FSST_TABLE_BYTES(ch.encoding);
 		}
 	}
 	L->lane_strings = 8;
@@ -1081,7 +1081,7 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	uint64_t max_plain_bytes = 0;
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
 		const fls_chunk_desc& ch = t->chunk(r, col);
-		if (ch.encoding == FLS_ENC_FSST || ch.encoding == FLS_ENC_FSST_DICT) {
+		if (FLS_ENC_IS_FSST_ANY(ch.encoding)) {
 			max_fsst_strings = std::max(max_fsst_strings, ch.aux_count);
 		} else {
 			max_plain_bytes = std::max<uint64_t>(max_plain_bytes, ch.const_val);
@@ -1120,7 +1120,7 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 }
 
 bool is_dict_string_enc(unsigned enc) {
-	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_FSST_DICT;
+	return FLS_ENC_IS_STR_DICT(enc);
 }
 
 } // namespace

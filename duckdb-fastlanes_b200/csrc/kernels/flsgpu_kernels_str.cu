@@ -31,8 +31,75 @@ namespace {
 
 constexpr int kWarps = 8;
 
-__device__ __forceinline__ bool is_fsst(uint32_t enc) {
-	return enc == FLS_ENC_FSST || enc == FLS_ENC_FSST_DICT;
+__device__ __forceinline__ bool is_fsst(uint32_t enc) { // FSST or FSST12, per row or dictionary
+	return FLS_ENC_IS_FSST_ANY(enc);
+}
+
+// Output side of a lane's decode: symbols are ORed into a 64-bit register at the current byte offset and flushed as aligned
+// 8-byte words; the first / last partial word of the lane's run is written bytewise (the neighbouring lanes own the rest).
+struct LaneOut {
+	unsigned long long* ow;
+	unsigned long long acc;
+	uint32_t fill, head; // head: low bytes of the first word that belong to the previous lane's strings
+	__device__ __forceinline__ LaneOut(uint8_t* out, uint32_t dbeg) {
+		const uint32_t mis = dbeg & 7u;
+		ow = reinterpret_cast<unsigned long long*>(out + (dbeg - mis));
+		acc = 0;
+		fill = head = mis;
+	}
+	__device__ __forceinline__ void append(unsigned long long sym, uint32_t len) { // sym zero padded beyond len (1..8)
+		acc |= sym << (8u * fill);
+		uint32_t nf = fill + len;
+		if (nf >= 8u) {
+			if (head) {
+				uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
+				for (uint32_t k = head; k < 8u; ++k) {
+					ob[k] = (uint8_t)(acc >> (8u * k));
+				}
+				head = 0;
+			} else {
+				*ow = acc;
+			}
+			++ow;
+			nf -= 8u;
+			acc = nf ? (sym >> (8u * (len - nf))) : 0ull;
+		}
+		fill = nf;
+	}
+	__device__ __forceinline__ void finish() {
+		uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
+		for (uint32_t k = head; k < fill; ++k) {
+			ob[k] = (uint8_t)(acc >> (8u * k));
+		}
+	}
+};
+
+// FSST12 (fls_format.h fls_fsst12_table; reference fsst12_kernel.hpp:53): one lane decodes its strings [first, last] one
+// after the other - a string's stream starts on a byte boundary, packs two 12-bit codes per 3 bytes and ends with a
+// 2-byte single code when its code count is odd.  The 36 KiB table stays in global memory (read-only path, L1 resident).
+template <bool GLOBAL_IN>
+__device__ __forceinline__ void fsst12_decode_lane(const uint8_t* __restrict__ in, const uint32_t* comp_end, uint32_t first, uint32_t last,
+                                                   uint32_t cbeg, uint8_t* __restrict__ out, uint32_t dbeg, const fls_fsst12_table* tab) {
+	LaneOut o(out, dbeg);
+	uint32_t p = cbeg;
+	for (uint32_t s = first; s <= last; ++s) {
+		const uint32_t ce = __ldg(comp_end + s);
+		while (p + 2u <= ce) {
+			const uint32_t b0 = GLOBAL_IN ? __ldg(in + p) : in[p], b1 = GLOBAL_IN ? __ldg(in + p + 1) : in[p + 1];
+			const uint32_t c0 = b0 | ((b1 & 15u) << 8);
+			o.append(__ldg(reinterpret_cast<const unsigned long long*>(&tab->symbol[c0])), __ldg(&tab->len[c0]));
+			if (p + 3u <= ce) {
+				const uint32_t b2 = GLOBAL_IN ? __ldg(in + p + 2) : in[p + 2];
+				const uint32_t c1 = (b1 >> 4) | (b2 << 4);
+				o.append(__ldg(reinterpret_cast<const unsigned long long*>(&tab->symbol[c1])), __ldg(&tab->len[c1]));
+				p += 3u;
+			} else {
+				p += 2u;
+			}
+		}
+		p = ce;
+	}
+	o.finish();
 }
 
 // One lane decodes the code stream [cbeg, cend) (relative to `in`, which is 4-byte aligned) to out[dbeg ...).
@@ -167,10 +234,11 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 	const uint32_t enc = ch->encoding;
 	const uint64_t hoff = L.heap_prefix[(size_t)rg * L.chunk_stride] - L.heap_prefix0;
 	uint8_t* heap = L.heap + hoff;
-	if (L.dict_only && enc != FLS_ENC_DICT_STR && enc != FLS_ENC_FSST_DICT) {
+	if (L.dict_only && !FLS_ENC_IS_STR_DICT(enc)) {
 		return;
 	}
 	if (is_fsst(enc)) {
+		const bool twelve = FLS_ENC_IS_FSST12(enc);
 		const uint32_t n = ch->aux_count;
 		const uint32_t tile_strings = 32u * L.lane_strings;
 		if ((uint64_t)g * kWarps * tile_strings >= n) {
@@ -178,12 +246,15 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 		}
 		const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 		{ // symbol table -> shared memory, symbols masked to their length so that OR-ing them into the output word is exact
-			const fls_fsst_table* tab = reinterpret_cast<const fls_fsst_table*>(ch->aux0);
-			const uint32_t c = threadIdx.x;
-			const uint32_t len = __ldg(&tab->len[c]);
-			const unsigned long long sym = __ldg(reinterpret_cast<const unsigned long long*>(&tab->symbol[c]));
-			s_sym[c] = len >= 8u ? sym : (sym & ((1ull << (8u * len)) - 1ull));
-			s_len[c] = (uint8_t)len;
+			// (FSST12: the 4096-entry table is read from global memory, validated zero padded when the table was opened)
+			if (!twelve) {
+				const fls_fsst_table* tab = reinterpret_cast<const fls_fsst_table*>(ch->aux0);
+				const uint32_t c = threadIdx.x;
+				const uint32_t len = __ldg(&tab->len[c]);
+				const unsigned long long sym = __ldg(reinterpret_cast<const unsigned long long*>(&tab->symbol[c]));
+				s_sym[c] = len >= 8u ? sym : (sym & ((1ull << (8u * len)) - 1ull));
+				s_len[c] = (uint8_t)len;
+			}
 			if (lane == 0) {
 				mbar_init(&s_bar[warp], 1);
 				fence_mbar_init();
@@ -192,7 +263,8 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 		__syncthreads();
 		const uint32_t* comp_end = reinterpret_cast<const uint32_t*>(ch->aux1);
 		const uint32_t* dec_end = comp_end + n;
-		const uint8_t* codes = ch->aux0 + sizeof(fls_fsst_table);
+		const uint8_t* codes = ch->aux0 + (twelve ? sizeof(fls_fsst12_table) : sizeof(fls_fsst_table));
+		const fls_fsst12_table* tab12 = reinterpret_cast<const fls_fsst12_table*>(ch->aux0);
 		const uint32_t s0 = (g * kWarps + warp) * tile_strings;
 		if (s0 >= n) {
 			return;
@@ -203,14 +275,14 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 		const uint32_t c1 = __ldg(comp_end + s1 - 1), d1 = __ldg(dec_end + s1 - 1);
 		// this lane's strings
 		const uint32_t first = s0 + lane * L.lane_strings;
-		uint32_t cbeg = 0, cend = 0, dbeg = 0;
+		uint32_t cbeg = 0, cend = 0, dbeg = 0, last = first;
 		if (first < s1) {
-			const uint32_t last = min(s1, first + L.lane_strings) - 1u;
+			last = min(s1, first + L.lane_strings) - 1u;
 			cbeg = first ? __ldg(comp_end + first - 1) : 0u;
 			dbeg = first ? __ldg(dec_end + first - 1) : 0u;
 			cend = __ldg(comp_end + last);
 		}
-		const bool is_rows = L.fuse_rows && enc == FLS_ENC_FSST;
+		const bool is_rows = L.fuse_rows && FLS_ENC_IS_FSST_ROWS(enc);
 		uint4* out_chunk = static_cast<uint4*>(L.out) + (size_t)rg * L.vec_per_rg * 1024u;
 		const uint64_t haddr = L.heap_base_addr + hoff;
 		const uint32_t ca = c0 & ~15u, cbytes = (c1 - ca + 15u) & ~15u;
@@ -225,7 +297,13 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 				}
 				mbar_wait(&s_bar[warp], 0);
 			}
-			fsst_decode_lane<false>(cbuf - ca, cbeg, cend, dbuf - da, dbeg, s_sym, s_len);
+			if (twelve) {
+				if (first < s1) {
+					fsst12_decode_lane<false>(cbuf - ca, comp_end, first, last, cbeg, dbuf - da, dbeg, tab12);
+				}
+			} else {
+				fsst_decode_lane<false>(cbuf - ca, cbeg, cend, dbuf - da, dbeg, s_sym, s_len);
+			}
 			__syncwarp();
 			// heap bytes [d0, d1): head bytes up to the first granule boundary, whole granules, tail bytes
 			const uint32_t g_lo = (d0 + 15u) & ~15u, g_hi = d1 & ~15u;
@@ -250,7 +328,13 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 			return;
 		}
 		// oversize tile (very long strings): decode straight to the heap
-		fsst_decode_lane<true>(codes, cbeg, cend, heap, dbeg, s_sym, s_len);
+		if (twelve) {
+			if (first < s1) {
+				fsst12_decode_lane<true>(codes, comp_end, first, last, cbeg, heap, dbeg, tab12);
+			}
+		} else {
+			fsst_decode_lane<true>(codes, cbeg, cend, heap, dbeg, s_sym, s_len);
+		}
 		if (is_rows) {
 			__threadfence_block();
 			__syncwarp();
@@ -311,8 +395,8 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrL
 		return;
 	}
 	const uint32_t enc = ch->encoding;
-	const bool dict = enc == FLS_ENC_DICT_STR || enc == FLS_ENC_FSST_DICT;
-	if (L.fuse_rows && enc == FLS_ENC_FSST) {
+	const bool dict = FLS_ENC_IS_STR_DICT(enc);
+	if (L.fuse_rows && FLS_ENC_IS_FSST_ROWS(enc)) {
 		return; // the heap kernel has built these rows from its staging buffer
 	}
 	if (L.codes_only) {
@@ -370,7 +454,7 @@ __global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L)
 	const uint32_t rg = blockIdx.x / L.groups_per_rg, g = blockIdx.x - rg * L.groups_per_rg;
 	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
 	const uint32_t enc = ch->encoding;
-	if (enc != FLS_ENC_DICT_STR && enc != FLS_ENC_FSST_DICT) {
+	if (!FLS_ENC_IS_STR_DICT(enc)) {
 		return;
 	}
 	const uint32_t n = ch->aux_count;

@@ -202,7 +202,7 @@ int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col
 		return -1;
 	}
 	const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + col];
-	if (vec >= ch->n_vec || (ch->encoding != FLS_ENC_DICT && ch->encoding != FLS_ENC_DICT_STR && ch->encoding != FLS_ENC_FSST_DICT)) {
+	if (vec >= ch->n_vec || (ch->encoding != FLS_ENC_DICT && !FLS_ENC_IS_STR_DICT(ch->encoding))) {
 		return -1;
 	}
 	const uint8_t* base = t->bytes + ch->offset;

@@ -81,6 +81,7 @@ int fls_oracle_aggregate_masked(const fls_oracle_table* t, uint32_t col, uint32_
 /* ---- string columns (fls_oracle_str.c) ---------------------------------------------------------------------------- */
 int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, uint32_t* codes /* 1024 */);
 uint64_t fls_oracle_fsst_decompress(const fls_fsst_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out);
+uint64_t fls_oracle_fsst12_decompress(const fls_fsst12_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out);
 /* Bytes of string heap a flat decode of [rg_begin, rg_begin + n_rg) needs (sum of the chunks' 16-byte padded decoded sizes). */
 int fls_oracle_string_heap_bytes(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out);
 /* Flat materialisation: 16-byte string_t per row (same row layout as fls_oracle_decode_column) + heap; pointers of

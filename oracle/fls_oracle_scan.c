@@ -158,7 +158,7 @@ static void* worker(void* arg) {
 					continue;
 				}
 				const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + j->cols[ci]];
-				const int is_dict = ch->encoding == FLS_ENC_DICT_STR || ch->encoding == FLS_ENC_FSST_DICT;
+				const int is_dict = FLS_ENC_IS_STR_DICT(ch->encoding);
 				const uint64_t need_keys = is_dict ? (uint64_t)ch->aux_count * 16 + 16 : 0;
 				const uint64_t need_heap = (is_dict ? ch->const_val : ch->encoding == FLS_ENC_STR_CONSTANT ? (uint64_t)ch->aux_count : ch->const_val) + 64;
 				if (str_cap[2 * ci] < need_keys) {
@@ -188,7 +188,7 @@ static void* worker(void* arg) {
 						if (c->phys_bits == 128) { /* string column: selection vector over the dictionary, or flat string_t */
 							const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + j->cols[ci]];
 							int rc;
-							if (ch->encoding == FLS_ENC_DICT_STR || ch->encoding == FLS_ENC_FSST_DICT) {
+							if (FLS_ENC_IS_STR_DICT(ch->encoding)) {
 								uint32_t* sel = (uint32_t*)(chunkbuf + (size_t)ci * 4096) + (size_t)b * 1024;
 								rc = fls_oracle_decode_codes(t, rg, j->cols[ci], v0 + b, sel);
 								j->checksum = fold((const uint64_t*)sel, 512, j->checksum);

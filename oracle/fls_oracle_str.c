@@ -58,6 +58,32 @@ uint64_t fls_oracle_fsst_decompress(const fls_fsst_table* tab, const uint8_t* in
 	return pos_out;
 }
 
+/* fsst12_decompress of the absent library (called at reference fsst12_kernel.hpp:53, fsst12_dict_kernel.hpp:39), restated
+ * from cwida/fsst's fsst12.h as published: 12-bit codes, two per 3 bytes (little endian), a trailing single code in 2 bytes;
+ * every code indexes symbol[] / len[] (codes < 256 are the bytes themselves).  UNPINNED: no copy of fsst12.h in the tree. */
+uint64_t fls_oracle_fsst12_decompress(const fls_fsst12_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out) {
+	uint64_t pos_out = 0, p = 0;
+	for (; p + 3 <= len_in; p += 3) {
+		const unsigned c0 = in[p] | ((in[p + 1] & 15u) << 8), c1 = (in[p + 1] >> 4) | ((unsigned)in[p + 2] << 4);
+		memcpy(out + pos_out, &tab->symbol[c0], tab->len[c0]);
+		pos_out += tab->len[c0];
+		memcpy(out + pos_out, &tab->symbol[c1], tab->len[c1]);
+		pos_out += tab->len[c1];
+	}
+	if (len_in - p == 2) {
+		const unsigned c0 = in[p] | ((in[p + 1] & 15u) << 8);
+		memcpy(out + pos_out, &tab->symbol[c0], tab->len[c0]);
+		pos_out += tab->len[c0];
+	}
+	return pos_out;
+}
+
+/* one compressed string of a FSST / FSST12 chunk */
+static uint64_t fsst_any_decompress(unsigned enc, const uint8_t* aux0, const uint8_t* in, uint64_t len_in, uint8_t* out) {
+	return FLS_ENC_IS_FSST12(enc) ? fls_oracle_fsst12_decompress((const fls_fsst12_table*)aux0, in, len_in, out)
+	                              : fls_oracle_fsst_decompress((const fls_fsst_table*)aux0, in, len_in, out);
+}
+
 int fls_oracle_string_heap_bytes(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out) {
 	uint64_t total = 0;
 	if (col >= t->header.n_columns || t->columns[col].phys_bits != 128) {
@@ -74,13 +100,12 @@ int fls_oracle_string_heap_bytes(const fls_oracle_table* t, uint32_t col, uint32
 static void fill_heap(const fls_oracle_table* t, const fls_chunk_desc* ch, uint8_t* heap) {
 	const uint8_t* aux0 = t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX0];
 	const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
-	if (ch->encoding == FLS_ENC_FSST || ch->encoding == FLS_ENC_FSST_DICT) {
-		const fls_fsst_table* tab = (const fls_fsst_table*)aux0;
-		const uint8_t* codes = aux0 + sizeof(fls_fsst_table);
+	if (FLS_ENC_IS_FSST_ANY(ch->encoding)) {
+		const uint8_t* codes = aux0 + FLS_FSST_TABLE_BYTES(ch->encoding);
 		const uint32_t n = ch->aux_count;
 		uint32_t cprev = 0, dprev = 0;
 		for (uint32_t i = 0; i < n; ++i) {
-			fls_oracle_fsst_decompress(tab, codes + cprev, aux1[i] - cprev, heap + dprev);
+			fsst_any_decompress(ch->encoding, aux0, codes + cprev, aux1[i] - cprev, heap + dprev);
 			cprev = aux1[i];
 			dprev = aux1[n + i];
 		}
@@ -103,7 +128,7 @@ int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t 
 		uint8_t* hp = heap + heap_off;
 		const uint64_t haddr = heap_base_addr + heap_off;
 		const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
-		const int fsst = ch->encoding == FLS_ENC_FSST || ch->encoding == FLS_ENC_FSST_DICT;
+		const int fsst = FLS_ENC_IS_FSST_ANY(ch->encoding);
 		const uint32_t* ends = fsst ? aux1 + ch->aux_count : aux1; /* decoded end offsets */
 		fill_heap(t, ch, hp);
 		const uint32_t n_rows = ch->n_vec * FLS_VEC_SZ;
@@ -115,6 +140,7 @@ int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t 
 			break;
 		case FLS_ENC_STR_UNCOMPRESSED:
 		case FLS_ENC_FSST:
+		case FLS_ENC_FSST12:
 			for (uint32_t i = 0; i < n_rows; ++i) {
 				const uint32_t start = i ? ends[i - 1] : 0;
 				make_string(&out[i], hp + start, ends[i] - start, haddr + start);
@@ -122,6 +148,7 @@ int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t 
 			break;
 		case FLS_ENC_DICT_STR:
 		case FLS_ENC_FSST_DICT:
+		case FLS_ENC_FSST12_DICT:
 			for (uint32_t v = 0; v < ch->n_vec; ++v) {
 				if (fls_oracle_decode_codes(t, rg_begin + r, col, v, codes)) {
 					return -2;
@@ -148,11 +175,11 @@ int fls_oracle_decode_string_dict(const fls_oracle_table* t, uint32_t col, uint3
 		return -1;
 	}
 	const fls_chunk_desc* ch = &t->chunks[(uint64_t)rg * t->header.n_columns + col];
-	if (ch->encoding != FLS_ENC_DICT_STR && ch->encoding != FLS_ENC_FSST_DICT) {
+	if (!FLS_ENC_IS_STR_DICT(ch->encoding)) {
 		return -3;
 	}
 	const uint32_t* aux1 = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
-	const uint32_t* ends = ch->encoding == FLS_ENC_FSST_DICT ? aux1 + ch->aux_count : aux1;
+	const uint32_t* ends = FLS_ENC_IS_FSST_ANY(ch->encoding) ? aux1 + ch->aux_count : aux1;
 	fill_heap(t, ch, heap);
 	ostr_t* out = (ostr_t*)out_keys;
 	for (uint32_t k = 0; k < ch->aux_count; ++k) {
@@ -196,12 +223,12 @@ int fls_oracle_decode_string_vector(const fls_oracle_table* t, uint32_t rg, uint
 			pos += len;
 		}
 		break;
-	case FLS_ENC_FSST: {
-		const fls_fsst_table* tab = (const fls_fsst_table*)aux0;
-		const uint8_t* codes = aux0 + sizeof(fls_fsst_table);
+	case FLS_ENC_FSST:
+	case FLS_ENC_FSST12: {
+		const uint8_t* codes = aux0 + FLS_FSST_TABLE_BYTES(ch->encoding);
 		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
 			const uint32_t cstart = (i0 + i) ? aux1[i0 + i - 1] : 0;
-			const uint64_t len = fls_oracle_fsst_decompress(tab, codes + cstart, aux1[i0 + i] - cstart, heap + pos);
+			const uint64_t len = fsst_any_decompress(ch->encoding, aux0, codes + cstart, aux1[i0 + i] - cstart, heap + pos);
 			make_string(&out[i], heap + pos, (uint32_t)len, heap_base_addr + pos);
 			pos += len;
 		}

@@ -29,6 +29,9 @@ def cases(n):
         "instruct": ("VARCHAR", "FSST_DICT", [[b"DELIVER IN PERSON", b"COLLECT COD", b"NONE", b"TAKE BACK RETURN"][(i * 7) % 4] for i in range(n)]),
         "blob": ("BLOB", "FSST", binary),                                                         # escapes, 0xFF literals
         "blob_plain": ("BLOB", "STR_UNCOMPRESSED", binary),
+        "comment12": ("VARCHAR", "FSST12", comment_like(n, seed=13)),                              # 12-bit codes, odd / even code counts
+        "blob12": ("BLOB", "FSST12", binary),                                                     # mostly literal codes (< 256)
+        "instruct12": ("VARCHAR", "FSST12_DICT", [[b"DELIVER IN PERSON", b"COLLECT COD", b"NONE", b"TAKE BACK RETURN"][(i * 5) % 4] for i in range(n)]),
         "len_edges": ("VARCHAR", "FSST", [b"x" * (i % 30) for i in range(n)]),                   # lengths around the 12-byte inline limit
         "long": ("VARCHAR", "STR_UNCOMPRESSED", [b"%05d:" % i + b"abcdefghij" * (1 + i % 50) for i in range(n)]),
     }

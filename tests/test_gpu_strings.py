@@ -78,12 +78,13 @@ def test_subrange_heap_starts_at_the_range():
 def test_dictionary_form_matches_oracle():
     import torch
     cs = str_cases.cases(3000)
-    img = flsgpu.write_table([("s", "VARCHAR", "DICT_STR"), ("f", "VARCHAR", "FSST_DICT"), ("c", "VARCHAR", "FSST")],
-                             [cs["value_i"][2], cs["instruct"][2], cs["comment"][2]], vec_per_rowgroup=2)
+    img = flsgpu.write_table([("s", "VARCHAR", "DICT_STR"), ("f", "VARCHAR", "FSST_DICT"), ("c", "VARCHAR", "FSST"),
+                              ("g", "VARCHAR", "FSST12_DICT")],
+                             [cs["value_i"][2], cs["instruct"][2], cs["comment"][2], cs["instruct12"][2]], vec_per_rowgroup=2)
     t = flsgpu.Table(img)
     t.stage()
     o = oracle_lib.Oracle(img)
-    for col, src in ((0, cs["value_i"][2]), (1, cs["instruct"][2])):
+    for col, src in ((0, cs["value_i"][2]), (1, cs["instruct"][2]), (3, cs["instruct12"][2])):
         codes = torch.zeros((t.out_elems(t.n_rowgroups),), dtype=torch.int32, device="cuda")
         t.decode_string_codes(col, codes.data_ptr(), codes.numel() * 4)
         flsgpu.sync()

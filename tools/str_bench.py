@@ -66,6 +66,7 @@ def main():
     values = dict_column(n, [b"Value %d" % k for k in range(1000)])
     cases = {
         "fsst": ("VARCHAR", "FSST", comment, "flat"),
+        "fsst12": ("VARCHAR", "FSST12", comment, "flat"),
         "plain": ("VARCHAR", "STR_UNCOMPRESSED", comment, "flat"),
         "dict_flat": ("VARCHAR", "DICT_STR", values, "flat"),
         "dict_form": ("VARCHAR", "DICT_STR", values, "dict"),
