@@ -317,10 +317,11 @@ struct AggPartial {
 	}
 
 	// DuckDB comparison semantics (ConstantFilter, duckdb/planner/filter/constant_filter.hpp): integers in their own
-	// signedness; floating point with NaN equal to itself and greater than everything else.
+	// signedness; floating point with NaN equal to itself and greater than everything else.  Returns 0 / 1 / 2 for
+	// v < c / v == c / v > c; a comparison operator is then a 3-bit truth table indexed by that (cmp_truth).
 	template <int VT>
-	static __device__ __forceinline__ bool compare(unsigned long long v, unsigned long long c, uint32_t op, uint32_t is_signed, uint32_t is_float) {
-		int lt, eq; // v < c, v == c
+	static __device__ __forceinline__ uint32_t order3(unsigned long long v, unsigned long long c, uint32_t is_signed, uint32_t is_float) {
+		bool lt, eq;
 		if (is_float) {
 			double a, b;
 			if constexpr (VT == 32) {
@@ -332,7 +333,7 @@ struct AggPartial {
 			}
 			const bool an = a != a, bn = b != b;
 			eq = (an && bn) || (!an && !bn && a == b);
-			lt = an ? 0 : (bn ? 1 : (a < b));
+			lt = an ? false : (bn ? true : (a < b));
 		} else if (is_signed) {
 			lt = (long long)v < (long long)c;
 			eq = v == c;
@@ -340,25 +341,36 @@ struct AggPartial {
 			lt = v < c;
 			eq = v == c;
 		}
+		return lt ? 0u : eq ? 1u : 2u;
+	}
+	static __device__ __forceinline__ uint32_t cmp_truth(uint32_t op) { // bit 0: passes when <, bit 1: when ==, bit 2: when >
 		switch (op) {
-		case 0: return eq;
-		case 1: return !eq;
-		case 2: return lt;
-		case 3: return lt || eq;
-		case 4: return !lt && !eq;
-		default: return !lt;
+		case 0: return 2u;      // EQ
+		case 1: return 5u;      // NE
+		case 2: return 1u;      // LT
+		case 3: return 3u;      // LE
+		case 4: return 4u;      // GT
+		case 5: return 6u;      // GE
+		default: return 7u;     // no second comparison
 		}
 	}
 
 	// mask words of one vector: bit `lane` of word `it` = row it*32 + lane passes (rows >= n_valid never pass)
 	template <int VT>
 	static __device__ __forceinline__ void build_mask(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float,
-	                                                  uint32_t op, unsigned long long c, bool and_into, uint32_t* mask_vec) {
+	                                                  uint32_t op, unsigned long long c, uint32_t op2, unsigned long long c2, bool and_into,
+	                                                  uint32_t* mask_vec) {
 		uint32_t mine = 0;
-#pragma unroll 4
+		const uint32_t t1 = cmp_truth(op), t2 = cmp_truth(op2);
+		const uint32_t sgn = is_signed && !is_float;
+#pragma unroll 8
 		for (uint32_t it = 0; it < 32u; ++it) {
 			const uint32_t i = it * 32u + lane;
-			const bool pass = i < n_valid && compare<VT>(tile_value<VT>(tile, i, is_signed && !is_float), c, op, is_signed, is_float);
+			const unsigned long long v = tile_value<VT>(tile, i, sgn);
+			bool pass = i < n_valid && ((t1 >> order3<VT>(v, c, is_signed, is_float)) & 1u);
+			if (t2 != 7u) {
+				pass = pass && ((t2 >> order3<VT>(v, c2, is_signed, is_float)) & 1u);
+			}
 			const uint32_t word = __ballot_sync(0xffffffffu, pass);
 			if ((uint32_t)lane == it) {
 				mine = word;

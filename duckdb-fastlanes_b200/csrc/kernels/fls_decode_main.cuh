@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 						part.template fold_masked<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float, mask_vec);
 					} else {
 						AggPartial::template build_mask<VT>(tile, lane, d.vec_in_chunk >> 16, L.agg_signed, L.agg_float, L.cmp_op, L.cmp_const,
-						                                    L.mask_mode == 2u, mask_vec);
+						                                    L.cmp_op2, L.cmp_const2, L.mask_mode == 2u, mask_vec);
 					}
 					__syncwarp();
 				} else if (!agg_fast) {

@@ -52,6 +52,8 @@ struct FlsLaunch {
 	uint32_t mask_mode;  // 0: none; 1: mask = cmp; 2: mask &= cmp; 3: aggregate only rows whose mask bit is set
 	uint32_t cmp_op;     // flsgpu_cmp
 	uint64_t cmp_const;  // physical bits of the constant (integers sign/zero-extended to 64, float/double raw bits)
+	uint32_t cmp_op2;    // second comparison on the same column, ANDed in the same pass (0xff: none): ranges cost one decode
+	uint64_t cmp_const2;
 	uint32_t* mask;      // [total_vecs * 32] words: bit i of word w of vector v = row v*1024 + w*32 + i
 	const uint8_t* rg_keep; // per row group of the range: 0 = pruned by its zone map (skipped), or nullptr
 };

@@ -492,6 +492,8 @@ int resolve_out(const fls_column_desc& col, int32_t out_type, OutSpec* o) {
 struct MaskSpec { // filter pushdown on aggregate-family launches (FlsLaunch.mask_mode)
 	uint32_t mode = 0, op = 0;
 	uint64_t constant = 0;
+	uint32_t op2 = 0xff; // second comparison on the same column, evaluated in the same pass
+	uint64_t constant2 = 0;
 	uint32_t* mask = nullptr;
 	const uint8_t* rg_keep = nullptr;
 };
@@ -526,6 +528,8 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 		L.mask_mode = ms->mode;
 		L.cmp_op = ms->op;
 		L.cmp_const = ms->constant;
+		L.cmp_op2 = ms->op2;
+		L.cmp_const2 = ms->constant2;
 		L.mask = ms->mask;
 		L.rg_keep = ms->rg_keep;
 	}
@@ -1318,17 +1322,34 @@ int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n
 	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
 	// vectors nobody writes (pruned row groups, the missing vectors of a short last row group) select nothing
 	FLS_CUDA(cudaMemsetAsync(mask_dev, 0, need, s));
+	// one decode pass per (column, pair of comparisons): the filters are ANDed, so their order is free; a range
+	// (l_shipdate >= a AND l_shipdate < b) costs one pass instead of two
+	std::vector<uint8_t> done(n_filters, 0);
+	bool first = true;
 	for (uint32_t i = 0; i < n_filters; ++i) {
+		if (done[i]) {
+			continue;
+		}
 		rc = check_resident(t, d, filters[i].col, rg_begin, n_rg);
 		if (rc) {
 			return rc;
 		}
 		MaskSpec ms;
-		ms.mode = i == 0 ? 1u : 2u;
+		ms.mode = first ? 1u : 2u;
+		first = false;
 		ms.op = (uint32_t)filters[i].op;
 		ms.constant = filters[i].constant;
 		ms.mask = mask_dev;
 		ms.rg_keep = rg_keep_dev;
+		done[i] = 1;
+		for (uint32_t j = i + 1; j < n_filters; ++j) {
+			if (!done[j] && filters[j].col == filters[i].col) {
+				ms.op2 = (uint32_t)filters[j].op;
+				ms.constant2 = filters[j].constant;
+				done[j] = 1;
+				break;
+			}
+		}
 		OutSpec os;
 		os.ob = t->columns[filters[i].col].phys_bits / 8;
 		rc = decode_column_impl(t, d, filters[i].col, rg_begin, n_rg, os, nullptr, s, nullptr, &ms);

@@ -77,6 +77,7 @@ struct Vector {
 	const void* data = nullptr;    // FLAT: the chunk's values; DICTIONARY: the dictionary's values (dict_size of them)
 	const uint32_t* sel = nullptr; // DICTIONARY: selection vector, one entry per row of the (unsliced) chunk
 	idx_t dict_size = 0;
+	bool all_null = false;         // CONSTANT NULL vector: a union_by_name column this file does not have
 	// value of (unsliced) row i as a pointer to its physical representation
 	const void* Row(idx_t i) const {
 		const idx_t k = vector_type == VectorType::DICTIONARY_VECTOR ? sel[i] : i;

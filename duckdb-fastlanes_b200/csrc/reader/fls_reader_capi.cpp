@@ -5,6 +5,7 @@
 #include <cstring>
 #include <thread>
 
+#include "fls_multi_file.hpp"
 #include "fls_reader.hpp"
 
 using namespace flsreader;
@@ -226,4 +227,170 @@ int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t
 int flsreader_scan(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
                    int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats) {
 	FLSR_TRY({ scan_impl(h, column_ids, n_cols, filters, n_filters, n_threads, out_cols, n_filters ? row_ids_out : nullptr, stats); })
+}
+
+// ---- multi-file ---------------------------------------------------------------------------------------------------------
+struct flsmulti_handle {
+	FastLanesMultiFileInfo info;
+};
+
+int flsmulti_open(const char* const* patterns, uint32_t n_patterns, const char* const* option_keys, const char* const* option_values,
+                  uint32_t n_options, flsmulti_handle** out) {
+	FLSR_TRY({
+		auto h = std::make_unique<flsmulti_handle>();
+		for (uint32_t i = 0; i < n_options; ++i) {
+			std::string v;
+			if (option_values[i]) {
+				v = option_values[i];
+			}
+			if (!h->info.ParseOption(option_keys[i], option_values[i] ? &v : nullptr)) {
+				throw BinderException(std::string("Invalid named parameter \"") + option_keys[i] + "\" for function read_fls");
+			}
+		}
+		std::vector<std::string> pats(patterns, patterns + n_patterns);
+		h->info.Bind(FastLanesMultiFileInfo::ExpandFiles(pats));
+		*out = h.release();
+	})
+}
+void flsmulti_close(flsmulti_handle* h) {
+	delete h;
+}
+int flsmulti_n_files(const flsmulti_handle* h) {
+	return (int)h->info.FileCount();
+}
+int flsmulti_file(const flsmulti_handle* h, int i, char* name256, uint64_t* n_tuples) {
+	if (i < 0 || (idx_t)i >= h->info.FileCount()) {
+		g_err = "file index out of range";
+		return FLSGPU_ERR_INVALID;
+	}
+	std::snprintf(name256, 256, "%s", h->info.FileName(i).c_str());
+	*n_tuples = const_cast<flsmulti_handle*>(h)->info.Reader(i).GetTotalTuples();
+	return 0;
+}
+int flsmulti_n_columns(const flsmulti_handle* h) {
+	return (int)h->info.Columns().size();
+}
+int flsmulti_column(const flsmulti_handle* h, int i, char* name64, int* type_id, int* physical_bytes, int* width, int* scale) {
+	const auto& cols = h->info.Columns();
+	if (i < 0 || (size_t)i >= cols.size()) {
+		g_err = "column index out of range";
+		return FLSGPU_ERR_INVALID;
+	}
+	std::snprintf(name64, 64, "%s", cols[i].name.c_str());
+	*type_id = (int)cols[i].type.id;
+	*physical_bytes = cols[i].type.physical_bytes;
+	*width = cols[i].type.width;
+	*scale = cols[i].type.scale;
+	return 0;
+}
+uint64_t flsmulti_cardinality(const flsmulti_handle* h) {
+	return h->info.GetCardinality();
+}
+uint64_t flsmulti_max_threads(const flsmulti_handle* h) {
+	return h->info.MaxThreads();
+}
+
+int flsmulti_scan(flsmulti_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
+                  int n_threads, void* const* out_cols, uint8_t* const* valid_out, uint32_t* file_ids_out, int64_t* row_ids_out,
+                  flsreader_scan_stats* stats) {
+	FLSR_TRY({
+		FastLanesMultiFileInfo& info = h->info;
+		// a fresh handle per scan keeps this simple: the projection is bound once
+		info.column_ids.assign(column_ids, column_ids + n_cols);
+		info.column_ids.push_back(COLUMN_IDENTIFIER_FILE_ROW_NUMBER);
+		info.filters.clear();
+		for (uint32_t i = 0; i < n_filters; ++i) {
+			TableFilter f;
+			f.column_index = filters[i].column_index;
+			f.op = (flsgpu_cmp)filters[i].op;
+			f.constant = filters[i].constant;
+			info.filters.push_back(f);
+		}
+		const auto& cols = info.Columns();
+		std::vector<uint32_t> widths(n_cols);
+		std::vector<uint8_t> is_str(n_cols);
+		for (uint32_t c = 0; c < n_cols; ++c) {
+			if (column_ids[c] >= cols.size()) {
+				throw ReaderError(FLSGPU_ERR_INVALID, "Projected column id out of range");
+			}
+			widths[c] = cols[column_ids[c]].type.physical_bytes;
+			is_str[c] = cols[column_ids[c]].type.id == LogicalTypeId::VARCHAR || cols[column_ids[c]].type.id == LogicalTypeId::BLOB;
+		}
+		MultiFileGlobalState gstate;
+		std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0}, dict_vectors {0}, cursor {0};
+		std::mutex err_mu;
+		std::string err;
+		int err_status = 0;
+		const uint64_t mt = info.MaxThreads();
+		const int nt = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)std::max(1, n_threads), mt));
+		auto worker = [&]() {
+			try {
+				MultiFileLocalState lstate;
+				DataChunk chunk;
+				while (info.Scan(gstate, lstate, chunk)) {
+					const int64_t* frn = static_cast<const int64_t*>(chunk.data[n_cols].data);
+					const uint64_t base = cursor.fetch_add(chunk.count);
+					for (uint32_t c = 0; c < n_cols; ++c) {
+						const Vector& v = chunk.data[c];
+						dict_vectors += v.vector_type == VectorType::DICTIONARY_VECTOR ? 1 : 0;
+						for (idx_t i = 0; i < chunk.count; ++i) {
+							if (valid_out && valid_out[c]) {
+								valid_out[c][base + i] = v.all_null ? 0 : 1;
+							}
+							if (v.all_null) {
+								continue;
+							}
+							const void* src = v.Row(chunk.RowIndex(i));
+							if (is_str[c]) {
+								const flsreader_string_sink* sink = static_cast<const flsreader_string_sink*>(out_cols[c]);
+								const string_t* sv = static_cast<const string_t*>(src);
+								if (sv->GetSize() > sink->stride) {
+									throw ReaderError(FLSGPU_ERR_INVALID, "string longer than the sink's stride");
+								}
+								std::memcpy(sink->bytes + (base + i) * sink->stride, sv->GetData(), sv->GetSize());
+								sink->lengths[base + i] = sv->GetSize();
+							} else {
+								std::memcpy(static_cast<uint8_t*>(out_cols[c]) + (base + i) * widths[c], src, widths[c]);
+							}
+						}
+					}
+					for (idx_t i = 0; i < chunk.count; ++i) {
+						row_ids_out[base + i] = frn[chunk.RowIndex(i)];
+						file_ids_out[base + i] = (uint32_t)lstate.file_index;
+					}
+					rows += chunk.count;
+					chunks += 1;
+					uint64_t m = maxrows.load();
+					while (chunk.count > m && !maxrows.compare_exchange_weak(m, chunk.count)) {
+					}
+				}
+			} catch (const ReaderError& e) {
+				std::lock_guard<std::mutex> g(err_mu);
+				err = e.what();
+				err_status = e.status;
+			} catch (const std::exception& e) {
+				std::lock_guard<std::mutex> g(err_mu);
+				err = e.what();
+				err_status = FLSGPU_ERR_INVALID;
+			}
+		};
+		std::vector<std::thread> th;
+		for (int i = 0; i < nt; ++i) {
+			th.emplace_back(worker);
+		}
+		for (auto& t : th) {
+			t.join();
+		}
+		if (err_status) {
+			throw ReaderError(err_status, err);
+		}
+		stats->rows = rows;
+		stats->chunks = chunks;
+		stats->max_chunk_rows = maxrows;
+		stats->dictionary_vectors = dict_vectors;
+		stats->pruned_rowgroups = 0;
+		for (idx_t f = 0; f < info.FileCount(); ++f) {
+			stats->pruned_rowgroups += info.Reader(f).GetNPrunedRowGroups();
+		}
+	})
 }

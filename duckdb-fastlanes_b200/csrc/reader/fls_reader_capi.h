@@ -48,6 +48,24 @@ typedef struct flsreader_scan_stats {
 } flsreader_scan_stats;
 int flsreader_scan(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
                    int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats);
+/* ---- read_fls over several files: FastLanesMultiFileInfo + MultiFileReader semantics (csrc/reader/fls_multi_file.hpp) ---- */
+typedef struct flsmulti_handle flsmulti_handle;
+/* patterns: paths or globs (read_fls(VARCHAR | LIST(VARCHAR))); option_keys / option_values: named parameters as text
+ * (explicit_cardinality, file_row_number, union_by_name, filename); a NULL value pointer is SQL NULL. */
+int flsmulti_open(const char* const* patterns, uint32_t n_patterns, const char* const* option_keys, const char* const* option_values,
+                  uint32_t n_options, flsmulti_handle** out);
+void flsmulti_close(flsmulti_handle* h);
+int flsmulti_n_files(const flsmulti_handle* h);
+int flsmulti_file(const flsmulti_handle* h, int i, char* name256, uint64_t* n_tuples);
+int flsmulti_n_columns(const flsmulti_handle* h);
+int flsmulti_column(const flsmulti_handle* h, int i, char* name64, int* type_id, int* physical_bytes, int* width, int* scale);
+uint64_t flsmulti_cardinality(const flsmulti_handle* h);
+uint64_t flsmulti_max_threads(const flsmulti_handle* h); /* ~0: no limit */
+/* Rows are appended in arrival order; file_ids_out / row_ids_out identify them (file index, file_row_number).
+ * valid_out[c] (one byte per row, may be NULL) is 0 where a union_by_name column is missing from the row's file. */
+int flsmulti_scan(flsmulti_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
+                  int n_threads, void* const* out_cols, uint8_t* const* valid_out, uint32_t* file_ids_out, int64_t* row_ids_out,
+                  flsreader_scan_stats* stats);
 #ifdef __cplusplus
 }
 #endif

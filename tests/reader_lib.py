@@ -152,3 +152,97 @@ class Reader:
 
     def __del__(self):
         self.close()
+
+
+lib.flsmulti_close.restype = None
+lib.flsmulti_cardinality.restype = C.c_uint64
+lib.flsmulti_max_threads.restype = C.c_uint64
+
+
+class MultiReader:
+    """read_fls(patterns, **named parameters): FastLanesMultiFileInfo + MultiFileReader semantics of the C++ reader mirror.
+    A handle binds one scan (open a new one for another projection)."""
+
+    def __init__(self, patterns, **options):
+        pats = [patterns] if isinstance(patterns, (str, bytes)) else list(patterns)
+        pa = (C.c_char_p * len(pats))(*[os.fsencode(p) for p in pats])
+        keys = list(options)
+        ka = (C.c_char_p * max(1, len(keys)))(*[k.encode() for k in keys])
+        va = (C.c_char_p * max(1, len(keys)))(*[None if options[k] is None else str(options[k]).lower().encode() if isinstance(options[k], bool)
+                                               else str(options[k]).encode() for k in keys])
+        self._h = C.c_void_p()
+        rc = lib.flsmulti_open(pa, len(pats), ka, va, len(keys), C.byref(self._h))
+        if rc:
+            raise ReaderError(rc)
+        self.files = []
+        for i in range(lib.flsmulti_n_files(self._h)):
+            name = C.create_string_buffer(256)
+            n = C.c_uint64()
+            lib.flsmulti_file(self._h, i, name, C.byref(n))
+            self.files.append((name.value.decode(), n.value))
+        self.columns = []
+        for i in range(lib.flsmulti_n_columns(self._h)):
+            name = C.create_string_buffer(64)
+            tid, pb, w, s = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+            lib.flsmulti_column(self._h, i, name, C.byref(tid), C.byref(pb), C.byref(w), C.byref(s))
+            self.columns.append(dict(name=name.value.decode(), type=TYPE_NAMES[tid.value], bytes=pb.value, width=w.value, scale=s.value))
+
+    @property
+    def cardinality(self):
+        return lib.flsmulti_cardinality(self._h)
+
+    @property
+    def max_threads(self):
+        v = lib.flsmulti_max_threads(self._h)
+        return None if v == 0xFFFFFFFFFFFFFFFF else v
+
+    def scan(self, column_ids=None, filters=(), n_threads=1, stride=256):
+        """-> (columns ordered by (file, file_row_number); None where a union column is missing), file ids, row ids, stats"""
+        ids = list(range(len(self.columns))) if column_ids is None else list(column_ids)
+        n = sum(t for _, t in self.files)
+        outs, keep, ptrs, valids = [], [], [], []
+        for i in ids:
+            c = self.columns[i]
+            if c["type"] in ("VARCHAR", "BLOB"):
+                data, lens = np.zeros((n, stride), dtype=np.uint8), np.zeros(n, dtype=np.uint32)
+                sink = StringSink(data.ctypes.data, lens.ctypes.data, stride)
+                keep.append(sink)
+                outs.append((data, lens))
+                ptrs.append(C.addressof(sink))
+            else:
+                dt = {2: np.int16, 4: np.int32, 8: np.int64}[c["bytes"]] if c["type"] == "DECIMAL" else NP_OF[c["type"]]
+                a = np.zeros(n, dtype=dt)
+                outs.append(a)
+                ptrs.append(a.ctypes.data)
+            valids.append(np.ones(n, dtype=np.uint8))
+        ia = (C.c_uint64 * len(ids))(*ids)
+        pa = (C.c_void_p * len(ids))(*ptrs)
+        va = (C.c_void_p * len(ids))(*[v.ctypes.data for v in valids])
+        fa = (ReaderFilter * max(1, len(filters)))(*[ReaderFilter(ci, op, k & 0xFFFFFFFFFFFFFFFF) for ci, op, k in filters])
+        file_ids, row_ids = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.int64)
+        st = ScanStats()
+        rc = lib.flsmulti_scan(self._h, ia, len(ids), fa, len(filters), n_threads, pa, va, C.c_void_p(file_ids.ctypes.data),
+                               C.c_void_p(row_ids.ctypes.data), C.byref(st))
+        if rc:
+            raise ReaderError(rc)
+        m = st.rows
+        order = np.lexsort((row_ids[:m], file_ids[:m]))
+        cols = []
+        for o, v in zip(outs, valids):
+            vv = v[:m][order].astype(bool)
+            if isinstance(o, tuple):
+                data, lens = o
+                cols.append([data[j, :lens[j]].tobytes() if ok else None for j, ok in zip(order, vv)])
+            else:
+                cols.append(np.ma.masked_array(o[:m][order], mask=~vv))
+        stats = dict(rows=st.rows, chunks=st.chunks, max_chunk_rows=st.max_chunk_rows, dictionary_vectors=st.dictionary_vectors,
+                     pruned_rowgroups=st.pruned_rowgroups)
+        return cols, file_ids[:m][order], row_ids[:m][order], stats
+
+    def close(self):
+        if self._h:
+            lib.flsmulti_close(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        self.close()
