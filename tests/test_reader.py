@@ -179,3 +179,23 @@ def test_filter_pushdown_through_reader(tmp_path, threads):
         if fname == "none_pass":
             assert st["pruned_rowgroups"] == 21 and st["chunks"] == 0
     r.close()
+
+
+def test_empty_table_scans_to_zero_rows_without_touching_the_device(tmp_path):
+    """0-row COPY ... (FORMAT fls): the file has a schema and no row groups; read_fls returns nothing (and, having nothing to
+    decode, needs no device)."""
+    import reader_lib
+    p = write(tmp_path, "empty.fls", [("a", "INT32", None), ("s", "VARCHAR", None)], [np.zeros(0, dtype=np.int32), []], 2)
+    r = reader_lib.Reader(p, file_row_number=True)
+    assert [c["type"] for c in r.columns] == ["INTEGER", "VARCHAR", "BIGINT"] and r.total_tuples == 0 and r.cardinality == 0
+    assert r.partition_stats() == [] and r.max_threads == 1
+    cols, _, st = r.scan(n_threads=2)
+    assert st["rows"] == 0 and st["chunks"] == 0 and len(cols[0]) == 0 and cols[1] == []
+    cols, ids, st = r.scan([0], [(0, flsgpu.CMP["GT"], 5)])
+    assert st["rows"] == 0 and len(ids) == 0
+    r.close()
+    m = reader_lib.MultiReader([p, p], filename=True)
+    assert m.cardinality == 84  # fls_multi_file_info.cpp:162-163: max(initial, 42) * file_count
+    cols, _, _, st = m.scan()
+    assert st["rows"] == 0
+    m.close()
