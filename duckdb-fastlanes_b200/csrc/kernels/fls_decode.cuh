@@ -317,32 +317,8 @@ struct AggPartial {
 	}
 
 	// DuckDB comparison semantics (ConstantFilter, duckdb/planner/filter/constant_filter.hpp): integers in their own
-	// signedness; floating point with NaN equal to itself and greater than everything else.  Returns 0 / 1 / 2 for
-	// v < c / v == c / v > c; a comparison operator is then a 3-bit truth table indexed by that (cmp_truth).
-	template <int VT>
-	static __device__ __forceinline__ uint32_t order3(unsigned long long v, unsigned long long c, uint32_t is_signed, uint32_t is_float) {
-		bool lt, eq;
-		if (is_float) {
-			double a, b;
-			if constexpr (VT == 32) {
-				a = (double)__uint_as_float((uint32_t)v);
-				b = (double)__uint_as_float((uint32_t)c);
-			} else {
-				a = __longlong_as_double((long long)v);
-				b = __longlong_as_double((long long)c);
-			}
-			const bool an = a != a, bn = b != b;
-			eq = (an && bn) || (!an && !bn && a == b);
-			lt = an ? false : (bn ? true : (a < b));
-		} else if (is_signed) {
-			lt = (long long)v < (long long)c;
-			eq = v == c;
-		} else {
-			lt = v < c;
-			eq = v == c;
-		}
-		return lt ? 0u : eq ? 1u : 2u;
-	}
+	// signedness; floating point with NaN equal to itself and greater than everything else.  A row's order against the
+	// constant is 0 / 1 / 2 for < / == / >; a comparison operator is a 3-bit truth table indexed by that.
 	static __device__ __forceinline__ uint32_t cmp_truth(uint32_t op) { // bit 0: passes when <, bit 1: when ==, bit 2: when >
 		switch (op) {
 		case 0: return 2u;      // EQ
@@ -355,26 +331,82 @@ struct AggPartial {
 		}
 	}
 
-	// mask words of one vector: bit `lane` of word `it` = row it*32 + lane passes (rows >= n_valid never pass)
-	template <int VT>
-	static __device__ __forceinline__ void build_mask(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float,
-	                                                  uint32_t op, unsigned long long c, uint32_t op2, unsigned long long c2, bool and_into,
-	                                                  uint32_t* mask_vec) {
+	// mask words of one vector: bit `lane` of word `it` = row it*32 + lane passes (rows >= n_valid never pass).
+	// KIND 0: unsigned integers, 1: signed integers, 2: floating point - hoisted out of the row loop (the per-row version
+	// with run-time type switches cost ~2300 instructions per vector, this one ~600).
+	template <int VT, int KIND>
+	static __device__ __forceinline__ uint32_t mask_rows(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t t1, unsigned long long c,
+	                                                     uint32_t t2, unsigned long long c2) {
 		uint32_t mine = 0;
-		const uint32_t t1 = cmp_truth(op), t2 = cmp_truth(op2);
-		const uint32_t sgn = is_signed && !is_float;
+		// constants in the comparison domain of the loop
+		double fc = 0.0, fc2 = 0.0;
+		if constexpr (KIND == 2) {
+			fc = VT == 32 ? (double)__uint_as_float((uint32_t)c) : __longlong_as_double((long long)c);
+			fc2 = VT == 32 ? (double)__uint_as_float((uint32_t)c2) : __longlong_as_double((long long)c2);
+		}
+		const bool cn = fc != fc, cn2 = fc2 != fc2;
 #pragma unroll 8
 		for (uint32_t it = 0; it < 32u; ++it) {
 			const uint32_t i = it * 32u + lane;
-			const unsigned long long v = tile_value<VT>(tile, i, sgn);
-			bool pass = i < n_valid && ((t1 >> order3<VT>(v, c, is_signed, is_float)) & 1u);
-			if (t2 != 7u) {
-				pass = pass && ((t2 >> order3<VT>(v, c2, is_signed, is_float)) & 1u);
+			uint32_t o1, o2; // 0: v < c, 1: v == c, 2: v > c
+			if constexpr (KIND == 2) {
+				double a;
+				if constexpr (VT == 32) {
+					a = (double)__uint_as_float(reinterpret_cast<const uint32_t*>(tile)[i]);
+				} else {
+					a = __longlong_as_double((long long)reinterpret_cast<const unsigned long long*>(tile)[i]);
+				}
+				const bool an = a != a; // DuckDB: NaN == NaN, NaN greater than everything else
+				o1 = an ? (cn ? 1u : 2u) : (cn ? 0u : (a < fc ? 0u : (a == fc ? 1u : 2u)));
+				o2 = an ? (cn2 ? 1u : 2u) : (cn2 ? 0u : (a < fc2 ? 0u : (a == fc2 ? 1u : 2u)));
+			} else if constexpr (KIND == 1) {
+				long long v;
+				if constexpr (VT == 8) {
+					v = (int8_t)tile[i];
+				} else if constexpr (VT == 16) {
+					v = reinterpret_cast<const int16_t*>(tile)[i];
+				} else if constexpr (VT == 32) {
+					v = reinterpret_cast<const int32_t*>(tile)[i];
+				} else {
+					v = reinterpret_cast<const long long*>(tile)[i];
+				}
+				o1 = v < (long long)c ? 0u : (v == (long long)c ? 1u : 2u);
+				o2 = v < (long long)c2 ? 0u : (v == (long long)c2 ? 1u : 2u);
+			} else {
+				unsigned long long v;
+				if constexpr (VT == 8) {
+					v = tile[i];
+				} else if constexpr (VT == 16) {
+					v = reinterpret_cast<const uint16_t*>(tile)[i];
+				} else if constexpr (VT == 32) {
+					v = reinterpret_cast<const uint32_t*>(tile)[i];
+				} else {
+					v = reinterpret_cast<const unsigned long long*>(tile)[i];
+				}
+				o1 = v < c ? 0u : (v == c ? 1u : 2u);
+				o2 = v < c2 ? 0u : (v == c2 ? 1u : 2u);
 			}
+			const bool pass = i < n_valid && ((t1 >> o1) & (t2 >> o2) & 1u);
 			const uint32_t word = __ballot_sync(0xffffffffu, pass);
 			if ((uint32_t)lane == it) {
 				mine = word;
 			}
+		}
+		return mine;
+	}
+
+	template <int VT>
+	static __device__ __forceinline__ void build_mask(const uint8_t* tile, int lane, uint32_t n_valid, uint32_t is_signed, uint32_t is_float,
+	                                                  uint32_t op, unsigned long long c, uint32_t op2, unsigned long long c2, bool and_into,
+	                                                  uint32_t* mask_vec) {
+		const uint32_t t1 = cmp_truth(op), t2 = cmp_truth(op2); // t2 = 7 (always true) without a second comparison
+		uint32_t mine;
+		if (VT >= 32 && is_float) {
+			mine = mask_rows<VT, (VT >= 32 ? 2 : 0)>(tile, lane, n_valid, t1, c, t2, c2);
+		} else if (is_signed) {
+			mine = mask_rows<VT, 1>(tile, lane, n_valid, t1, c, t2, c2);
+		} else {
+			mine = mask_rows<VT, 0>(tile, lane, n_valid, t1, c, t2, c2);
 		}
 		mask_vec[lane] = and_into ? (mask_vec[lane] & mine) : mine;
 	}
@@ -387,26 +419,54 @@ struct AggPartial {
 		if (__ballot_sync(0xffffffffu, my_word != 0u) == 0u) {
 			return;
 		}
-#pragma unroll 4
+		(void)n_valid; // padding rows never have their bit set
+		if (VT >= 32 && is_float) {
+			double f = 0.0;
+			uint32_t n = 0;
+#pragma unroll 8
+			for (uint32_t it = 0; it < 32u; ++it) {
+				const uint32_t word = __shfl_sync(0xffffffffu, my_word, it);
+				const uint32_t i = it * 32u + lane;
+				if ((word >> lane) & 1u) {
+					++n;
+					if constexpr (VT == 32) {
+						f += (double)__uint_as_float(reinterpret_cast<const uint32_t*>(tile)[i]);
+					} else if constexpr (VT == 64) {
+						f += __longlong_as_double((long long)reinterpret_cast<const unsigned long long*>(tile)[i]);
+					}
+				}
+			}
+			fs += f;
+			cnt += n;
+			return;
+		}
+		// integers: values of <= 32 bits cannot overflow a 64-bit partial over 32 rows; 64-bit values carry into `hi`
+		unsigned long long s = 0;
+		long long h = 0;
+		uint32_t n = 0;
+#pragma unroll 8
 		for (uint32_t it = 0; it < 32u; ++it) {
 			const uint32_t word = __shfl_sync(0xffffffffu, my_word, it);
 			const uint32_t i = it * 32u + lane;
-			if (!((word >> lane) & 1u) || i >= n_valid) {
-				continue;
+			const bool on = (word >> lane) & 1u;
+			n += on ? 1u : 0u;
+			if constexpr (VT == 64) {
+				const unsigned long long u = on ? reinterpret_cast<const unsigned long long*>(tile)[i] : 0ull;
+				s += u;
+				h += (s < u) ? 1 : 0;
+				h -= (is_signed && (long long)u < 0) ? 1 : 0;
+			} else {
+				const unsigned long long u = on ? tile_value<VT>(tile, i, is_signed) : 0ull; // sign-extended when signed
+				s += u;
 			}
-			++cnt;
-			if (is_float) {
-				if constexpr (VT == 32) {
-					fs += (double)__uint_as_float(reinterpret_cast<const uint32_t*>(tile)[i]);
-				} else if constexpr (VT == 64) {
-					fs += __longlong_as_double((long long)reinterpret_cast<const unsigned long long*>(tile)[i]);
-				}
-				continue;
-			}
-			const unsigned long long u = tile_value<VT>(tile, i, is_signed);
-			lo += u;
-			hi += (lo < u) ? 1 : 0;
-			hi -= (is_signed && (long long)u < 0) ? 1 : 0;
+		}
+		cnt += n;
+		if constexpr (VT == 64) {
+			const unsigned long long before = lo;
+			lo += s;
+			hi += h + ((lo < before) ? 1 : 0);
+		} else {
+			add_u128(s, (is_signed && (long long)s < 0) ? -1ll : 0ll);
 		}
 	}
 
