@@ -33,6 +33,48 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		default: break;
 		}
 	}
+	if constexpr (T == 8 && OB == 1 && !AGG && (FAM & kFamLight) != 0) {
+		// 8-bit columns written as 8 bits: SWAR.  A thread's four lanes of a row stay packed in one register from the unpack
+		// to the store (the per-value form below is instruction bound at ~0.35 of the HBM roofline).
+		if (enc == FLS_ENC_FFOR) {
+			uint32_t x[8];
+			unpack8_swar_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot), lane, x);
+			const uint32_t base4 = ((uint32_t)d.base & 0xffu) * 0x01010101u;
+#pragma unroll
+			for (int row = 0; row < 8; ++row) { // value_pos<8>(lane, 4 * row + b) = row * 128 + 4 * lane + b
+				st_cs_u32(out_vec + row * 128 + 4 * lane, add8x4(x[row], base4));
+			}
+			return;
+		}
+		if (enc == FLS_ENC_DELTA) {
+			const uint32_t* s32 = reinterpret_cast<const uint32_t*>(slot);
+			uint32_t x[8];
+			unpack8_swar_dispatch((int)W, s32 + 32, lane, x);
+			const uint32_t base4 = ((uint32_t)d.base & 0xffu) * 0x01010101u;
+			uint32_t acc = s32[lane]; // the four lane bases
+#pragma unroll
+			for (int row = 0; row < 8; ++row) {
+				acc = add8x4(add8x4(acc, x[row]), base4);
+				x[row] = acc; // byte b = value (chain of lane 4*lane + b, position l0_b + row)
+			}
+			// 4x4 byte transposes: chain b wants its rows 0..3 / 4..7 side by side
+			const uint32_t t0 = __byte_perm(x[0], x[1], 0x5140), t1 = __byte_perm(x[0], x[1], 0x7362);
+			const uint32_t t2 = __byte_perm(x[2], x[3], 0x5140), t3 = __byte_perm(x[2], x[3], 0x7362);
+			const uint32_t u0 = __byte_perm(x[4], x[5], 0x5140), u1 = __byte_perm(x[4], x[5], 0x7362);
+			const uint32_t u2 = __byte_perm(x[6], x[7], 0x5140), u3 = __byte_perm(x[6], x[7], 0x7362);
+			const uint32_t lo4[4] = {__byte_perm(t0, t2, 0x5410), __byte_perm(t0, t2, 0x7632), __byte_perm(t1, t3, 0x5410),
+			                         __byte_perm(t1, t3, 0x7632)};
+			const uint32_t hi4[4] = {__byte_perm(u0, u2, 0x5410), __byte_perm(u0, u2, 0x7632), __byte_perm(u1, u3, 0x5410),
+			                         __byte_perm(u1, u3, 0x7632)};
+			// a chain's 8 values are 8 contiguous output bytes; for a fixed b the 32 lanes of the warp cover four whole
+			// 64-byte blocks (8 full sectors per store instruction), so the vector leaves straight from registers
+#pragma unroll
+			for (int b = 0; b < 4; ++b) {
+				st_cs_v2(out_vec + chain_l0(4 * lane + b), lo4[b], hi4[b]); // byte offset == element offset
+			}
+			return;
+		}
+	}
 	uint32_t v[32];
 	const uint32_t base = (uint32_t)d.base;
 	if ((FAM & kFamLight) != 0 && enc == FLS_ENC_DELTA) {
@@ -418,7 +460,8 @@ __device__ __forceinline__ void process_64_2ph(const VecDesc& d, const uint8_t* 
 // keeps all 32 (lo, hi) pairs of a thread in registers (one CTA of 8 warps, no spills).
 template <int MODE, int T, bool AGG, uint32_t FAM>
 constexpr int min_ctas_per_sm() {
-	return (MODE == 0 && T == 64 && AGG) ? 1 : FLS_MIN_CTAS;
+	// 8/16-bit materialising kernels: short vectors, the per-vector latencies (descriptor, TMA wait) want more resident warps
+	return (MODE == 0 && T == 64 && AGG) ? 1 : (MODE == 0 && T <= 16 && !AGG) ? 3 : FLS_MIN_CTAS;
 }
 
 // AGG: the vector is decoded into the warp's shared-memory tile (FLS_SINK_SHARED translation unit) and folded into

@@ -214,6 +214,49 @@ FLS_HD void stream64_bases(const uint32_t* s32, int tid, int W, const uint32_t*&
 }
 
 // ---- runtime-W dispatch -----------------------------------------------------------------------------------------------
+// ---- T = 8, SWAR form: x[row] keeps the four 8-bit lanes 4tid..4tid+3 of a row side by side in one register -------------
+// (what unpack_small<8, W> computes before it splits the word into four registers; the 8-bit kernels add the base / the
+// running sum with byte-wise SWAR arithmetic and store the word as it is: 4 values per instruction instead of 1)
+template <int W>
+FLS_HD void unpack8_swar(const uint32_t* s32, int tid, uint32_t (&x)[8]) {
+	uint32_t w[W + 1];
+#pragma unroll
+	for (int k = 0; k < W; ++k) {
+		w[k] = s32[k * 32 + tid];
+	}
+	w[W] = 0;
+#pragma unroll
+	for (int row = 0; row < 8; ++row) {
+		const int bit = row * W, k = bit / 8, sh = bit % 8;
+		if (W == 0) {
+			x[row] = 0;
+		} else if (sh + W <= 8) {
+			x[row] = (w[k] >> sh) & field_mask<8>(W);
+		} else {
+			x[row] = ((w[k] >> sh) & field_mask<8>(8 - sh)) | ((w[k + 1] & field_mask<8>(sh + W - 8)) << (8 - sh));
+		}
+	}
+}
+
+FLS_HD void unpack8_swar_dispatch(int W, const uint32_t* s32, int tid, uint32_t (&x)[8]) {
+	switch (W) {
+	case 0: unpack8_swar<0>(s32, tid, x); break;
+	case 1: unpack8_swar<1>(s32, tid, x); break;
+	case 2: unpack8_swar<2>(s32, tid, x); break;
+	case 3: unpack8_swar<3>(s32, tid, x); break;
+	case 4: unpack8_swar<4>(s32, tid, x); break;
+	case 5: unpack8_swar<5>(s32, tid, x); break;
+	case 6: unpack8_swar<6>(s32, tid, x); break;
+	case 7: unpack8_swar<7>(s32, tid, x); break;
+	default: unpack8_swar<8>(s32, tid, x); break;
+	}
+}
+
+// byte-wise a + b (mod 256 per byte, no carries between bytes)
+FLS_HD uint32_t add8x4(uint32_t a, uint32_t b) {
+	return ((a & 0x7f7f7f7fu) + (b & 0x7f7f7f7fu)) ^ ((a ^ b) & 0x80808080u);
+}
+
 #define FLS_CASE_S(T, Wv) \
 	case Wv: unpack_small<T, Wv>(s32, tid, v); break;
 #define FLS_CASES8(M, T, b) M(T, b + 0) M(T, b + 1) M(T, b + 2) M(T, b + 3) M(T, b + 4) M(T, b + 5) M(T, b + 6) M(T, b + 7)

@@ -85,6 +85,7 @@ def main():
     ap.add_argument("--out", default=None)
     ap.add_argument("--kinds", default="FFOR,DELTA,DICT,RLE")
     ap.add_argument("--types", default="INT64,INT32,INT16,INT8")
+    ap.add_argument("--widths", default=None, help="comma list overriding the per-kind width list")
     args = ap.parse_args()
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     flsgpu.init((0,))
@@ -102,6 +103,8 @@ def main():
                 ws = {"ALP0": [4, 10, 20], "ALPX": [10, 24], "ALPRD": [0]}[kind]
             if kind.startswith("ALP") != (tname in ("DOUBLE", "FLOAT")):
                 continue
+            if args.widths:
+                ws = [int(v) for v in args.widths.split(",")]
             for w in ws:
                 if kind == "DICT" and w >= bits:
                     continue
