@@ -16,6 +16,10 @@ constexpr uint32_t kFamAlpRd = 1u << FLS_ENC_ALP_RD;
 // switch(W) dispatches (two phases each) into one and needs > 200 registers; apart they fit 128 with no spills.
 constexpr uint32_t kFamDelta = 1u << FLS_ENC_DELTA;
 constexpr uint32_t kFamLight64 = kFamLight & ~kFamDelta;
+// T = 8 written as 8 bits: FFOR and DELTA chunks get a SWAR instantiation of their own (four lanes per register from the
+// unpack to the store).  It needs 48 registers and no staging area, so five CTAs are resident per SM; 1-byte values
+// leave little work per vector to hide the descriptor / bulk-copy latencies behind, hence the extra warps.
+constexpr uint32_t kFamSwar8 = (1u << FLS_ENC_FFOR) | (1u << FLS_ENC_DELTA);
 
 // AGG + part != nullptr: register fast path of the fused aggregates — the vector is complete (n_valid == 1024) and has
 // no exceptions, so its values are folded into the partials straight from registers instead of being written anywhere.
@@ -25,7 +29,7 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 	const bool fast = AGG && agg_fast;
 	const uint32_t enc = d.misc >> 24, W = (d.misc >> 16) & 0xffu;
 	constexpr uint32_t TMASK = T == 32 ? 0xffffffffu : ((1u << (T & 31)) - 1u);
-	if constexpr ((FAM & kFamLight) != 0) {
+	if constexpr ((FAM & (1u << FLS_ENC_UNCOMPRESSED)) != 0) {
 		switch (enc) {
 		case FLS_ENC_UNCOMPRESSED: copy_out_linear<T, OB, false>(slot, out_vec, lane, conv); return;
 		case FLS_ENC_CONSTANT: fill_constant<T, OB>(out_vec, lane, (uint32_t)d.base, 0, conv); return;
@@ -33,16 +37,25 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 		default: break;
 		}
 	}
-	if constexpr (T == 8 && OB == 1 && !AGG && (FAM & kFamLight) != 0) {
-		// 8-bit columns written as 8 bits: SWAR.  A thread's four lanes of a row stay packed in one register from the unpack
-		// to the store (the per-value form below is instruction bound at ~0.35 of the HBM roofline).
+	if constexpr (FAM == kFamSwar8) {
+		static_assert(T == 8 && OB == 1 && !AGG, "SWAR family: 8-bit lanes written as 8 bits");
+		// A thread's four lanes of a row stay packed in one register from the unpack to the store (the per-value form
+		// below is instruction bound at ~0.35 of the HBM roofline).
 		if (enc == FLS_ENC_FFOR) {
 			uint32_t x[8];
 			unpack8_swar_dispatch((int)W, reinterpret_cast<const uint32_t*>(slot), lane, x);
 			const uint32_t base4 = ((uint32_t)d.base & 0xffu) * 0x01010101u;
+			if (W < 8) { // every byte of x is < 128: the low 7 bits cannot carry out of their byte, bit 7 is an XOR
+				const uint32_t bl = base4 & 0x7f7f7f7fu, bh = base4 & 0x80808080u;
 #pragma unroll
-			for (int row = 0; row < 8; ++row) { // value_pos<8>(lane, 4 * row + b) = row * 128 + 4 * lane + b
-				st_cs_u32(out_vec + row * 128 + 4 * lane, add8x4(x[row], base4));
+				for (int row = 0; row < 8; ++row) { // value_pos<8>(lane, 4 * row + b) = row * 128 + 4 * lane + b
+					st_cs_u32(out_vec + row * 128 + 4 * lane, (x[row] + bl) ^ bh);
+				}
+			} else {
+#pragma unroll
+				for (int row = 0; row < 8; ++row) {
+					st_cs_u32(out_vec + row * 128 + 4 * lane, add8x4(x[row], base4));
+				}
 			}
 			return;
 		}
@@ -50,12 +63,16 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 			const uint32_t* s32 = reinterpret_cast<const uint32_t*>(slot);
 			uint32_t x[8];
 			unpack8_swar_dispatch((int)W, s32 + 32, lane, x);
-			const uint32_t base4 = ((uint32_t)d.base & 0xffu) * 0x01010101u;
-			uint32_t acc = s32[lane]; // the four lane bases
+			// running sums of the even and the odd lanes in 16-bit fields (8 x (255 + 255) + 255 never reaches the neighbour),
+			// the low byte of a field is the value mod 256
+			const uint32_t base2 = ((uint32_t)d.base & 0xffu) * 0x00010001u;
+			const uint32_t acc = s32[lane]; // the four lane bases
+			uint32_t ae = acc & 0x00ff00ffu, ao = __byte_perm(acc, 0u, 0x4341);
 #pragma unroll
 			for (int row = 0; row < 8; ++row) {
-				acc = add8x4(add8x4(acc, x[row]), base4);
-				x[row] = acc; // byte b = value (chain of lane 4*lane + b, position l0_b + row)
+				ae += (x[row] & 0x00ff00ffu) + base2;
+				ao += __byte_perm(x[row], 0u, 0x4341) + base2;
+				x[row] = __byte_perm(ae, ao, 0x6240); // byte b = value (chain of lane 4*lane + b, position l0_b + row)
 			}
 			// 4x4 byte transposes: chain b wants its rows 0..3 / 4..7 side by side
 			const uint32_t t0 = __byte_perm(x[0], x[1], 0x5140), t1 = __byte_perm(x[0], x[1], 0x7362);
@@ -72,8 +89,8 @@ __device__ __forceinline__ void process_small(const VecDesc& d, const uint8_t* s
 			for (int b = 0; b < 4; ++b) {
 				st_cs_v2(out_vec + chain_l0(4 * lane + b), lo4[b], hi4[b]); // byte offset == element offset
 			}
-			return;
 		}
+		return;
 	}
 	uint32_t v[32];
 	const uint32_t base = (uint32_t)d.base;
@@ -461,7 +478,7 @@ __device__ __forceinline__ void process_64_2ph(const VecDesc& d, const uint8_t* 
 template <int MODE, int T, bool AGG, uint32_t FAM>
 constexpr int min_ctas_per_sm() {
 	// 8/16-bit materialising kernels: short vectors, the per-vector latencies (descriptor, TMA wait) want more resident warps
-	return (MODE == 0 && T == 64 && AGG) ? 1 : (MODE == 0 && T <= 16 && !AGG) ? 3 : FLS_MIN_CTAS;
+	return (MODE == 0 && T == 64 && AGG) ? 1 : FAM == kFamSwar8 ? 5 : (MODE == 0 && T <= 16 && !AGG) ? 3 : FLS_MIN_CTAS;
 }
 
 // AGG: the vector is decoded into the warp's shared-memory tile (FLS_SINK_SHARED translation unit) and folded into
@@ -494,7 +511,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 	const uint32_t n_warps = gridDim.x * wpc;
 	const uint32_t gw = blockIdx.x * wpc + warp;
 	uint32_t phases = 0; // bit s: parity to wait for on slot s
-	uint32_t n_done = 0; // vectors processed by this warp (slot = n_done % n_slots)
+	uint32_t slot = 0;   // pipeline slot of the next vector this warp consumes (vectors processed % n_slots, kept incrementally)
 	uint8_t* const out = static_cast<uint8_t*>(L.out);
 
 	// Vector -> warp assignment: a warp takes runs of C = 2^run_shift consecutive vectors (same row group, same
@@ -533,7 +550,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 		uint32_t to_issue = todo;
 		// prologue: fill the pipeline
 		if (lane == 0) {
-			uint32_t slot_i = n_done % n_slots;
+			uint32_t slot_i = slot;
 			for (uint32_t s = 0; s < n_slots && to_issue; ++s) {
 				const int k = __ffs(to_issue) - 1;
 				to_issue &= to_issue - 1;
@@ -548,17 +565,21 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			}
 		}
 		to_issue = __shfl_sync(0xffffffffu, to_issue, 0);
+		const uint64_t vbase = (run0 * n_warps + gw) << cs;
+		uint8_t* const out_batch = out + (size_t)vbase * (1024u * OB);
 		while (todo) {
 			const int k = __ffs(todo) - 1;
 			todo &= todo - 1;
 			const VecDesc d = load_desc(descs, k);
-			const uint32_t slot = n_done % n_slots;
 			if (d.bytes) {
 				mbar_wait(bars + slot, (phases >> slot) & 1u);
 				phases ^= 1u << slot;
 			}
-			const uint64_t vk = (((run0 + ((uint32_t)k >> cs)) * n_warps + gw) << cs) + ((uint32_t)k & cmask);
-			uint8_t* out_vec = AGG ? tile : out + (size_t)vk * 1024u * OB;
+			// vector index = batch base + a 32-bit offset (<= 32 runs further on)
+			const uint32_t voff = ((((uint32_t)k >> cs) * n_warps) << cs) + ((uint32_t)k & cmask);
+			const uint64_t vk = vbase + voff;
+			uint8_t* out_vec = AGG ? tile : out_batch + (size_t)voff * (1024u * OB);
+			(void)vk;
 			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
 			// aggregate fast path: complete vector, no exceptions, an encoding whose values end up in registers
 			const uint32_t enc_k = d.misc >> 24;
@@ -604,7 +625,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 					}
 				}
 			}
-			++n_done;
+			slot = slot + 1 == n_slots ? 0 : slot + 1;
 		}
 	}
 	if constexpr (AGG) {

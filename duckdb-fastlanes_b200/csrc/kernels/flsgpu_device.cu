@@ -44,6 +44,7 @@ const uint32_t g_prefetch = env_u32("FLSGPU_PREFETCH", 1);
 const uint32_t g_force_slots = env_u32("FLSGPU_NSLOTS", 0);     // experiments: pipeline depth override
 const uint32_t g_max_ctas = env_u32("FLSGPU_MAX_CTAS", 0);      // experiments: cap on resident CTAs per SM
 const uint32_t g_budget_kb = env_u32("FLSGPU_WARP_KB", 14);     // shared-memory budget per warp (KiB) the depth is sized for
+const uint32_t g_swar8_kb = env_u32("FLSGPU_SWAR8_KB", 8);      // same for the 8-bit SWAR kernel (48 registers: up to five resident CTAs per SM)
 
 int cuda_fail(cudaError_t e, const char* where) {
 	char msg[256];
@@ -79,10 +80,12 @@ int ensure_device() {
 
 // ---- per-table device state ---------------------------------------------------------------------------------------
 struct FlsColumnPlan { // what a decode launch over (col, rg range) needs to know about the chunks it covers
-	bool has_main[4] = {false, false, false, false}; // 0: light (integer encodings), 1: ALP, 2: ALP_RD, 3: DELTA (T = 64)
+	// 0: light (integer encodings), 1: ALP, 2: ALP_RD, 3: DELTA (T = 64), 4: FFOR + DELTA of 8-bit columns (SWAR kernel
+	// when the output is 8 bits wide too, else folded back into 0 at launch time)
+	bool has_main[5] = {false, false, false, false, false};
 	bool has_rle = false, has_dict[3] = {false, false, false};
 	bool main_needs_stage = false;
-	uint32_t main_slot[4] = {0, 0, 0, 0}, rle_slot = 0, dict_slot[3] = {0, 0, 0};
+	uint32_t main_slot[5] = {0, 0, 0, 0, 0}, rle_slot = 0, dict_slot[3] = {0, 0, 0};
 };
 
 struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of neighbouring slabs overlap
@@ -352,7 +355,8 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 			p.rle_slot = std::max(p.rle_slot, bytes);
 		} else {
 			const int f = c.encoding == FLS_ENC_ALP ? 1 : c.encoding == FLS_ENC_ALP_RD ? 2
-			              : (c.encoding == FLS_ENC_DELTA && c.phys_bits == 64) ? 3 : 0;
+			              : (c.encoding == FLS_ENC_DELTA && c.phys_bits == 64) ? 3
+			              : (c.phys_bits == 8 && (c.encoding == FLS_ENC_FFOR || c.encoding == FLS_ENC_DELTA)) ? 4 : 0;
 			p.has_main[f] = true;
 			p.main_slot[f] = std::max(p.main_slot[f], bytes);
 			p.main_needs_stage |= c.encoding == FLS_ENC_DELTA;
@@ -366,14 +370,14 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 
 // Pick pipeline depth / grid for `fn` and launch it.
 int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t stage_bytes, cudaStream_t stream,
-                  uint32_t tile_bytes = 0) {
+                  uint32_t tile_bytes = 0, uint32_t budget_kb = 0) {
 	if (!fn) {
 		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "no kernel instantiation for this (lane width, value width, output width)");
 	}
 	L.slot_bytes = std::max<uint32_t>(128u, (slot_bytes + 127u) & ~127u);
 	L.stage_bytes = stage_bytes;
 	// shared memory: aim for two resident CTAs per SM (~104 KB each) unless a single slot pair needs more
-	const uint32_t per_warp_budget = g_budget_kb * 1024u;
+	const uint32_t per_warp_budget = (budget_kb ? budget_kb : g_budget_kb) * 1024u; // budget_kb: kernels that want > 2 CTAs/SM
 	const uint32_t fixed = FLS_DESC_BYTES_PER_WARP + L.stage_bytes + tile_bytes; // per-warp bytes besides the pipeline slots
 	uint32_t n_slots = fixed < per_warp_budget ? (per_warp_budget - fixed) / L.slot_bytes : 0;
 	// Two resident CTAs per SM matter more than pipeline depth (measured: 64-bit DELTA, 2 CTAs x 1 slot 0.139 ms vs
@@ -537,16 +541,20 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	const uint32_t tile = agg_family ? 128u * T : 0u; // aggregate launches decode into a per-warp shared-memory tile
 	int rc = FLSGPU_OK;
 	const uint32_t light = FLS_FAMILY_MAIN & ~((1u << FLS_ENC_ALP) | (1u << FLS_ENC_ALP_RD));
-	const uint32_t fam_mask[4] = {T == 64 ? light & ~(1u << FLS_ENC_DELTA) : light, 1u << FLS_ENC_ALP, 1u << FLS_ENC_ALP_RD,
-	                              1u << FLS_ENC_DELTA};
-	for (int f = 0; f < 4 && rc == FLSGPU_OK; ++f) {
-		if (p.has_main[f]) {
+	const uint32_t swar8 = (1u << FLS_ENC_FFOR) | (1u << FLS_ENC_DELTA);
+	const bool use_swar8 = p.has_main[4] && !agg_family && T == 8 && os.ob == 1; // else family 4's chunks decode in the light kernel
+	const uint32_t fam_mask[5] = {T == 64 ? light & ~(1u << FLS_ENC_DELTA) : use_swar8 ? light & ~swar8 : light, 1u << FLS_ENC_ALP,
+	                              1u << FLS_ENC_ALP_RD, 1u << FLS_ENC_DELTA, swar8};
+	for (int f = 0; f < 5 && rc == FLSGPU_OK; ++f) {
+		const bool fold4 = f == 0 && p.has_main[4] && !use_swar8;
+		if ((f == 4 ? use_swar8 : p.has_main[f]) || fold4) {
 			L.family_mask = fam_mask[f];
 			L.idx_bits = 0;
-			// DELTA needs the per-warp transposition area (+ 16 lane totals for T = 64)
+			// DELTA needs the per-warp transposition area (+ 16 lane totals for T = 64); the SWAR kernel stores from registers
 			const bool stage = p.main_needs_stage && (f == 3 || (f == 0 && T != 64));
-			rc = launch_family(agg_family ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, p.main_slot[f],
-			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile);
+			const uint32_t slot = fold4 ? std::max(p.main_slot[0], p.main_slot[4]) : p.main_slot[f];
+			rc = launch_family(agg_family ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, slot,
+			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile, f == 4 ? g_swar8_kb : 0u);
 		}
 	}
 	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {

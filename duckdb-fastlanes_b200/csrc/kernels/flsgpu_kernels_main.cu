@@ -6,8 +6,12 @@
 
 using namespace flsk;
 
-// fam: 0 = light, 1 = ALP, 2 = ALP_RD, 3 = DELTA (T = 64 only; narrower types keep DELTA in the light kernel)
+// fam: 0 = light, 1 = ALP, 2 = ALP_RD, 3 = DELTA (T = 64 only; narrower types keep DELTA in the light kernel),
+// 4 = FFOR + DELTA of 8-bit columns written as 8 bits (SWAR)
 const void* fls_kernel_main(int T, int OB, int fam) {
+	if (fam == 4) {
+		return T == 8 && OB == 1 ? reinterpret_cast<const void*>(&fls_decode_kernel<0, 8, 8, 1, false, kFamSwar8>) : nullptr;
+	}
 #define FLS_K(Tv, OBv) \
 	if (fam == 0 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamLight>);
 	FLS_K(8, 1) FLS_K(8, 2) FLS_K(8, 4) FLS_K(8, 8)
