@@ -265,8 +265,8 @@ def run_reference(args, rank, world):
 
 def kernel_name(t, col):
     """Which kernel instantiation(s) decode this column: the launcher (flsgpu_device.cu decode_column_impl) issues one
-    launch per family present among the column's chunks: light (integer encodings), ALP, ALP_RD, DICT per code width,
-    RLE.  A column whose chunks all fall in one family is one launch of one instantiation (the roofline groups those);
+    launch per family present among the column's chunks: light (integer encodings), 64-bit DELTA, 8-bit FFOR/DELTA (SWAR),
+    ALP, ALP_RD (one launch for both when T = 32), DICT per code width, RLE.  A column whose chunks all fall in one family is one launch of one instantiation (the roofline groups those);
     a column with several families is reported as "mixed(...)"."""
     import flsgpu
     fams, encs = set(), set()
@@ -275,14 +275,15 @@ def kernel_name(t, col):
         e = flsgpu.ENC_NAME[ch.encoding]
         encs.add(e)
         fams.add("str_dict" if e in ("DICT_STR", "FSST_DICT") else "dict%d" % ch.idx_bits if e == "DICT" else "rle" if e == "RLE" else "alp" if e == "ALP" else "alprd" if e == "ALP_RD"
-                 else "delta" if e == "DELTA" and ch.phys_bits == 64 else "light")
+                 else "delta" if e == "DELTA" and ch.phys_bits == 64 else "swar8" if e in ("FFOR", "DELTA") and ch.phys_bits == 8 else "light")
     T = t.column(col).phys_bits
     fams = sorted(fams)  # "delta": 64-bit DELTA chunks have their own instantiation
     if fams == ["str_dict"]:
         return "fls_str_kernels<dictionary form>", sorted(encs), 3  # heap fill + keys + codes
     if len(fams) == 1:
         return f"fls_decode_kernel<{fams[0]},T={T}>", sorted(encs), 1
-    return f"mixed({'+'.join(fams)}),T={T}", sorted(encs), len(fams)
+    fused = T == 32 and "alp" in fams and "alprd" in fams  # FLOAT: ALP and ALP_RD chunks share one launch
+    return f"mixed({'+'.join(fams)}),T={T}", sorted(encs), len(fams) - (1 if fused else 0)
 
 
 def run_gpu(args, rank, world, local_rank):

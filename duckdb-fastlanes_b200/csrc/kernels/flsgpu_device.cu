@@ -550,7 +550,18 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	const bool use_swar8 = p.has_main[4] && !agg_family && T == 8 && os.ob == 1; // else family 4's chunks decode in the light kernel
 	const uint32_t fam_mask[5] = {T == 64 ? light & ~(1u << FLS_ENC_DELTA) : use_swar8 ? light & ~swar8 : light, 1u << FLS_ENC_ALP,
 	                              1u << FLS_ENC_ALP_RD, 1u << FLS_ENC_DELTA, swar8};
+	// FLOAT columns that mix ALP and ALP_RD chunks: one launch of the instantiation that carries both (same 128-register
+	// budget as the ALP_RD kernel alone) instead of two launches with their ramp and tail
+	const bool fuse_alp = T == 32 && !agg_family && p.has_main[1] && p.has_main[2];
+	if (fuse_alp) {
+		L.family_mask = fam_mask[1] | fam_mask[2];
+		L.idx_bits = 0;
+		rc = launch_family(fls_kernel_main(T, os.ob, 5), L, std::max(p.main_slot[1], p.main_slot[2]), 0u, stream, tile);
+	}
 	for (int f = 0; f < 5 && rc == FLSGPU_OK; ++f) {
+		if (fuse_alp && (f == 1 || f == 2)) {
+			continue;
+		}
 		const bool fold4 = f == 0 && p.has_main[4] && !use_swar8;
 		if ((f == 4 ? use_swar8 : p.has_main[f]) || fold4) {
 			L.family_mask = fam_mask[f];

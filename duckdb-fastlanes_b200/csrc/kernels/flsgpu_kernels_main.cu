@@ -25,5 +25,10 @@ const void* fls_kernel_main(int T, int OB, int fam) {
 	if (fam == 2 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamAlpRd>);
 	FLS_K(32, 4) FLS_K(32, 8) FLS_K(64, 8)
 #undef FLS_K
+	// fam 5: ALP and ALP_RD chunks of one column in one launch (columns that mix the two)
+#define FLS_K(Tv, OBv) \
+	if (fam == 5 && T == Tv && OB == OBv) return reinterpret_cast<const void*>(&fls_decode_kernel<0, Tv, Tv, OBv, false, kFamAlp | kFamAlpRd>);
+	FLS_K(32, 4) FLS_K(32, 8) // (T = 64 fused would spill ~600 bytes: the two 64-bit float paths stay separate launches)
+#undef FLS_K
 	return nullptr;
 }
