@@ -294,6 +294,8 @@ def run_gpu(args, rank, world, local_rank):
     if world > 1:
         import torch.distributed as dist_mod
         dist = dist_mod
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # NCCL would print its version line on stdout, next to the JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     flsgpu.init((local_rank,))
     threads = max(1, (os.cpu_count() or 1) // max(1, world))
