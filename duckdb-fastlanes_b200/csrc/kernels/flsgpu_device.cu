@@ -1122,18 +1122,18 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	}
 	if (n_str) {
 		const double avg_dec = (double)dec_bytes / (double)n_str, avg_comp = (double)comp_bytes / (double)n_str;
-		const uint32_t budget = env_u32("FLSGPU_STR_WARP_KB", 8) * 1024u, cap = 26u * 1024u;
+		const uint32_t budget = env_u32("FLSGPU_STR_WARP_KB", 10) * 1024u, cap = 26u * 1024u;
 		uint32_t ls = std::min(16u, env_u32("FLSGPU_STR_LANE_STRINGS", 16));
 		for (;; ls >>= 1) {
 			const uint32_t db = ((uint32_t)(2.0 * 32.0 * ls * avg_dec) + 64u + 255u) & ~255u;
 			const uint32_t cb = ((uint32_t)(2.0 * 32.0 * ls * avg_comp) + 64u + 255u) & ~255u;
-			if (db + cb <= budget || ls == 1) {
+			if (db + 2u * cb <= budget || ls == 1) { // two staging buffers for codes (the next tile's are prefetched) + one decode buffer
 				L->lane_strings = ls;
 				L->dbuf_bytes = db;
 				L->cbuf_bytes = cb;
-				if (db + cb > cap) { // very long strings: whatever fits goes through the buffers, the rest decodes to global
-					L->dbuf_bytes = (cap * 3u / 4u) & ~255u;
-					L->cbuf_bytes = cap - L->dbuf_bytes;
+				if (db + 2u * cb > cap) { // very long strings: whatever fits goes through the buffers, the rest decodes to global
+					L->dbuf_bytes = (cap / 2u) & ~255u;
+					L->cbuf_bytes = (cap / 4u) & ~255u;
 				}
 				break;
 			}
@@ -1141,7 +1141,8 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	}
 	// CTAs per chunk of the heap kernel: enough 8-warp CTAs for the largest FSST chunk's tiles, and one CTA per 32 KiB of
 	// plain bytes (a 9 KiB dictionary is one CTA's work, not 32 CTAs copying 280 bytes each)
-	const uint32_t per_cta = 8u * 32u * L->lane_strings;
+	// (a warp of the heap kernel walks FLSGPU_STR_TILES tiles of the largest chunk as a software pipeline)
+	const uint32_t per_cta = 8u * 32u * L->lane_strings * std::max(1u, env_u32("FLSGPU_STR_TILES", 8));
 	L->groups_per_rg = std::max<uint32_t>(1u, std::max<uint32_t>((max_fsst_strings + per_cta - 1u) / per_cta,
 	                                                            (uint32_t)((max_plain_bytes + 32767u) >> 15)));
 	L->chunk_stride = t->header.n_columns;

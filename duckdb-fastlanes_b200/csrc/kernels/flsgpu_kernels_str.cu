@@ -102,46 +102,57 @@ __device__ __forceinline__ void fsst12_decode_lane(const uint8_t* __restrict__ i
 	o.finish();
 }
 
-// One lane decodes the code stream [cbeg, cend) (relative to `in`, which is 4-byte aligned) to out[dbeg ...).
-// `out` is 8-byte aligned.  fsst.h:219-230 per code; output assembled in a register, flushed as aligned 64-bit words.
+// One lane decodes the code stream [cbeg, cend) (relative to `in`) to out[dbeg ...).  `out` is 8-byte aligned.
+// fsst.h:219-230 per code; output assembled in a 64-bit register, flushed as aligned 64-bit words.
 // GLOBAL_IN: the codes are read straight from global memory (read-only path); otherwise from the warp's staging buffer.
+// tab: shared-memory address of the 256 x 16-byte decoder table {symbol (zero padded), length in BITS}: one 128-bit load
+// per code.  The loop is issue bound, so it is written for instruction count: the next code byte is loaded while the
+// current one is looked up, the fill level is kept in bits, the carry-over after a flush is two shifts (no selects), and
+// the table is addressed from a register (no per-iteration recomputation of shared-memory bases).
+template <bool GLOBAL_IN>
+__device__ __forceinline__ uint32_t fsst_code_at(const uint8_t* p) {
+	if constexpr (GLOBAL_IN) {
+		return __ldg(p);
+	} else {
+		uint32_t v;
+		asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+		return v;
+	}
+}
+
 template <bool GLOBAL_IN>
 __device__ __forceinline__ void fsst_decode_lane(const uint8_t* __restrict__ in, uint32_t cbeg, uint32_t cend, uint8_t* __restrict__ out,
-                                                 uint32_t dbeg, const unsigned long long* s_sym, const uint8_t* s_len) {
+                                                 uint32_t dbeg, uint32_t tab) {
 	if (cbeg >= cend) {
 		return;
 	}
 	const uint32_t mis = dbeg & 7u;
 	unsigned long long* ow = reinterpret_cast<unsigned long long*>(out + (dbeg - mis));
 	unsigned long long acc = 0;
-	uint32_t fill = mis, head = mis; // head: low bytes of the first word that belong to the previous lane's strings
-	const uint32_t* inw = reinterpret_cast<const uint32_t*>(in);
-	uint32_t p = cbeg, widx = p >> 2;
-	uint32_t w = GLOBAL_IN ? __ldg(inw + widx) : inw[widx];
-	while (p < cend) {
-		if ((p >> 2) != widx) {
-			widx = p >> 2;
-			w = GLOBAL_IN ? __ldg(inw + widx) : inw[widx];
-		}
-		const uint32_t code = __byte_perm(w, 0, 0x4440u | (p & 3u));
+	uint32_t fill8 = 8u * mis, head = mis; // head: low bytes of the first word that belong to the previous lane's strings
+	const uint8_t* p = in + cbeg;
+	const uint8_t* const pe = in + cend;
+	asm volatile("mov.u32 %0, %0;" : "+r"(tab)); // keep the table address in a register (else it is recomputed per code)
+	uint32_t code = fsst_code_at<GLOBAL_IN>(p);
+	for (;;) {
 		++p;
+		// speculative: at the end of the stream this reads the byte after it (inside the staging buffer / the segment's slack)
+		uint32_t nxt = fsst_code_at<GLOBAL_IN>(p);
 		unsigned long long sym;
-		uint32_t len;
-		if (code != FLS_FSST_ESC) {
-			sym = s_sym[code];
-			len = s_len[code];
-		} else {
-			if ((p >> 2) != widx) {
-				widx = p >> 2;
-				w = GLOBAL_IN ? __ldg(inw + widx) : inw[widx];
-			}
-			sym = __byte_perm(w, 0, 0x4440u | (p & 3u));
-			len = 1;
+		uint32_t len8;
+		if (__builtin_expect(code != FLS_FSST_ESC, 1)) {
+			uint32_t lo, hi, pad;
+			asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(hi), "=r"(len8), "=r"(pad) : "r"(tab + code * 16u));
+			sym = ((unsigned long long)hi << 32) | lo;
+		} else { // the next byte is a literal
+			sym = nxt;
+			len8 = 8u;
 			++p;
+			nxt = fsst_code_at<GLOBAL_IN>(p);
 		}
-		acc |= sym << (8u * fill);
-		uint32_t nf = fill + len;
-		if (nf >= 8u) {
+		acc |= sym << fill8;
+		uint32_t nf8 = fill8 + len8;
+		if (nf8 >= 64u) {
 			if (head) {
 				uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
 				for (uint32_t k = head; k < 8u; ++k) {
@@ -152,13 +163,19 @@ __device__ __forceinline__ void fsst_decode_lane(const uint8_t* __restrict__ in,
 				*ow = acc;
 			}
 			++ow;
-			nf -= 8u;
-			acc = nf ? (sym >> (8u * (len - nf))) : 0ull;
+			nf8 -= 64u;
+			// what did not fit: sym >> (bits that went into the flushed word) - 8..64 of them, 64 when an 8-byte symbol
+			// filled an empty word, hence the shift in two steps
+			acc = (sym >> (len8 - nf8 - 1u)) >> 1;
 		}
-		fill = nf;
+		fill8 = nf8;
+		if (p >= pe) {
+			break;
+		}
+		code = nxt;
 	}
 	uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
-	for (uint32_t k = head; k < fill; ++k) {
+	for (uint32_t k = head; k < (fill8 >> 3); ++k) {
 		ob[k] = (uint8_t)(acc >> (8u * k));
 	}
 }
@@ -225,9 +242,8 @@ __device__ __forceinline__ void tile_rows(const uint8_t* hp, uint64_t haddr, con
 // Decoding lane-to-global directly (the fallback for tiles that do not fit the buffers) costs 2.8x the DRAM reads and 1.6x
 // the writes: 32 lanes x 8-byte stores hit 32 different sectors, partial sector writes make L2 fetch the rest.
 __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrLaunch L) {
-	__shared__ unsigned long long s_sym[256];
-	__shared__ uint8_t s_len[256];
-	__shared__ __align__(8) uint64_t s_bar[kWarps];
+	__shared__ uint4 s_tab[256]; // FSST decoder table: {symbol lo, symbol hi, length in bits, 0}
+	__shared__ __align__(8) uint64_t s_bar[2 * kWarps]; // one per (warp, staging buffer)
 	extern __shared__ __align__(128) uint8_t s_dyn[];
 	const uint32_t rg = blockIdx.x / L.groups_per_rg, g = blockIdx.x - rg * L.groups_per_rg;
 	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
@@ -252,93 +268,146 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrL
 				const uint32_t c = threadIdx.x;
 				const uint32_t len = __ldg(&tab->len[c]);
 				const unsigned long long sym = __ldg(reinterpret_cast<const unsigned long long*>(&tab->symbol[c]));
-				s_sym[c] = len >= 8u ? sym : (sym & ((1ull << (8u * len)) - 1ull));
-				s_len[c] = (uint8_t)len;
+				const unsigned long long m = len >= 8u ? sym : (sym & ((1ull << (8u * len)) - 1ull));
+				s_tab[c] = make_uint4((uint32_t)m, (uint32_t)(m >> 32), 8u * len, 0u);
 			}
 			if (lane == 0) {
-				mbar_init(&s_bar[warp], 1);
+				mbar_init(&s_bar[2u * warp], 1);
+				mbar_init(&s_bar[2u * warp + 1u], 1);
 				fence_mbar_init();
 			}
 		}
 		__syncthreads();
+		const uint32_t tab_addr = (uint32_t)__cvta_generic_to_shared(s_tab);
 		const uint32_t* comp_end = reinterpret_cast<const uint32_t*>(ch->aux1);
 		const uint32_t* dec_end = comp_end + n;
 		const uint8_t* codes = ch->aux0 + (twelve ? sizeof(fls_fsst12_table) : sizeof(fls_fsst_table));
 		const fls_fsst12_table* tab12 = reinterpret_cast<const fls_fsst12_table*>(ch->aux0);
-		const uint32_t s0 = (g * kWarps + warp) * tile_strings;
-		if (s0 >= n) {
+		// A warp walks tiles tile, tile + stride, ... of the chunk as a three-stage software pipeline: the entry points of tile
+		// k+2 are requested from global memory, the codes of tile k+1 (whose entry points arrived during the previous
+		// iteration) are bulk-copied into the other staging buffer, tile k is decoded.  A warp that handled a single tile
+		// spent a third of its life waiting for those two round trips.
+		const uint32_t n_tiles = (n + tile_strings - 1u) / tile_strings, stride = L.groups_per_rg * kWarps;
+		uint32_t tile = g * kWarps + warp;
+		if (tile >= n_tiles) {
 			return;
-		}
-		const uint32_t s1 = min(n, s0 + tile_strings);
-		// tile extents (same address in every lane: one broadcast load each)
-		const uint32_t c0 = s0 ? __ldg(comp_end + s0 - 1) : 0u, d0 = s0 ? __ldg(dec_end + s0 - 1) : 0u;
-		const uint32_t c1 = __ldg(comp_end + s1 - 1), d1 = __ldg(dec_end + s1 - 1);
-		// this lane's strings
-		const uint32_t first = s0 + lane * L.lane_strings;
-		uint32_t cbeg = 0, cend = 0, dbeg = 0, last = first;
-		if (first < s1) {
-			last = min(s1, first + L.lane_strings) - 1u;
-			cbeg = first ? __ldg(comp_end + first - 1) : 0u;
-			dbeg = first ? __ldg(dec_end + first - 1) : 0u;
-			cend = __ldg(comp_end + last);
 		}
 		const bool is_rows = L.fuse_rows && FLS_ENC_IS_FSST_ROWS(enc);
 		uint4* out_chunk = static_cast<uint4*>(L.out) + (size_t)rg * L.vec_per_rg * 1024u;
 		const uint64_t haddr = L.heap_base_addr + hoff;
-		const uint32_t ca = c0 & ~15u, cbytes = (c1 - ca + 15u) & ~15u;
-		const uint32_t da = d0 & ~15u, dspan = d1 - da;
-		if (cbytes <= L.cbuf_bytes && dspan + 16u <= L.dbuf_bytes) {
-			uint8_t* cbuf = s_dyn + (size_t)warp * (L.cbuf_bytes + L.dbuf_bytes);
-			uint8_t* dbuf = cbuf + L.cbuf_bytes;
-			if (cbytes) {
-				if (lane == 0) {
-					mbar_expect_tx(&s_bar[warp], cbytes);
-					tma_load_1d(cbuf, codes + ca, cbytes, &s_bar[warp]);
-				}
-				mbar_wait(&s_bar[warp], 0);
+		uint8_t* cbuf0 = s_dyn + (size_t)warp * (2u * L.cbuf_bytes + L.dbuf_bytes);
+		uint8_t* dbuf = cbuf0 + 2u * L.cbuf_bytes;
+		struct Tile { // what is LOADED for a tile; everything derived is computed where it is used (so the loads stay in flight)
+			uint32_t s0, s1, first, last;   // strings [s0, s1) of the chunk; this lane's strings [first, last]
+			uint32_t c0, c1, d0, d1;        // code bytes [c0, c1), decoded bytes [d0, d1) of the tile
+			uint32_t cbeg, cend, dbeg;      // where this lane's codes / decoded bytes start, where its codes end
+		};
+		auto load_tile = [&](uint32_t ti) {
+			Tile t;
+			t.s0 = ti * tile_strings;
+			t.s1 = min(n, t.s0 + tile_strings);
+			// tile extents (same address in every lane: one broadcast load each)
+			t.c0 = t.s0 ? __ldg(comp_end + t.s0 - 1) : 0u;
+			t.d0 = t.s0 ? __ldg(dec_end + t.s0 - 1) : 0u;
+			t.c1 = __ldg(comp_end + t.s1 - 1);
+			t.d1 = __ldg(dec_end + t.s1 - 1);
+			t.first = t.s0 + lane * L.lane_strings;
+			t.last = t.first;
+			t.cbeg = t.cend = t.dbeg = 0;
+			if (t.first < t.s1) {
+				t.last = min(t.s1, t.first + L.lane_strings) - 1u;
+				t.cbeg = t.first ? __ldg(comp_end + t.first - 1) : 0u;
+				t.dbeg = t.first ? __ldg(dec_end + t.first - 1) : 0u;
+				t.cend = __ldg(comp_end + t.last);
 			}
-			if (twelve) {
-				if (first < s1) {
-					fsst12_decode_lane<false>(cbuf - ca, comp_end, first, last, cbeg, dbuf - da, dbeg, tab12);
+			return t;
+		};
+		auto is_staged = [&](const Tile& t) {
+			const uint32_t ca = t.c0 & ~15u;
+			return ((t.c1 - ca + 15u) & ~15u) <= L.cbuf_bytes && (t.d1 - (t.d0 & ~15u)) + 16u <= L.dbuf_bytes;
+		};
+		auto stage_codes = [&](const Tile& t, uint32_t b) {
+			const uint32_t ca = t.c0 & ~15u, cbytes = (t.c1 - ca + 15u) & ~15u;
+			if (is_staged(t) && cbytes && lane == 0) {
+				fence_proxy_async(); // the buffer's previous tile was read through the generic proxy
+				mbar_expect_tx(&s_bar[2u * warp + b], cbytes);
+				tma_load_1d(cbuf0 + b * L.cbuf_bytes, codes + ca, cbytes, &s_bar[2u * warp + b]);
+			}
+		};
+		Tile cur = load_tile(tile);
+		stage_codes(cur, 0u);
+		Tile nxt = cur;
+		if (tile + stride < n_tiles) {
+			nxt = load_tile(tile + stride);
+		}
+		uint32_t phase = 0; // bit b: parity to wait for on staging buffer b
+		for (uint32_t k = 0;; ++k) {
+			const uint32_t b = k & 1u;
+			const bool has_next = tile + stride < n_tiles;
+			Tile nn = nxt;
+			if (tile + 2u * stride < n_tiles) {
+				nn = load_tile(tile + 2u * stride);
+			}
+			if (has_next) {
+				stage_codes(nxt, b ^ 1u);
+			}
+			const uint32_t s0 = cur.s0, s1 = cur.s1, d0 = cur.d0, d1 = cur.d1, da = cur.d0 & ~15u, ca = cur.c0 & ~15u;
+			if (is_staged(cur)) {
+				const uint8_t* cbuf = cbuf0 + b * L.cbuf_bytes;
+				if (((cur.c1 - ca + 15u) & ~15u) != 0u) {
+					mbar_wait(&s_bar[2u * warp + b], (phase >> b) & 1u);
+					phase ^= 1u << b;
 				}
+				if (twelve) {
+					if (cur.first < s1) {
+						fsst12_decode_lane<false>(cbuf - ca, comp_end, cur.first, cur.last, cur.cbeg, dbuf - da, cur.dbeg, tab12);
+					}
+				} else {
+					fsst_decode_lane<false>(cbuf - ca, cur.cbeg, cur.cend, dbuf - da, cur.dbeg, tab_addr);
+				}
+				__syncwarp();
+				// heap bytes [d0, d1): head bytes up to the first granule boundary, whole granules, tail bytes
+				const uint32_t g_lo = (d0 + 15u) & ~15u, g_hi = d1 & ~15u;
+				if (g_lo <= g_hi) {
+					for (uint32_t q = d0 + lane; q < g_lo; q += 32u) {
+						heap[q] = dbuf[q - da];
+					}
+					for (uint32_t q = g_lo + lane * 16u; q < g_hi; q += 512u) {
+						*reinterpret_cast<uint4*>(heap + q) = *reinterpret_cast<const uint4*>(dbuf + (q - da));
+					}
+					for (uint32_t q = g_hi + lane; q < d1; q += 32u) {
+						heap[q] = dbuf[q - da];
+					}
+				} else { // the whole tile lies inside one granule
+					for (uint32_t q = d0 + lane; q < d1; q += 32u) {
+						heap[q] = dbuf[q - da];
+					}
+				}
+				if (is_rows) {
+					tile_rows<false>(dbuf - da, haddr, dec_end, s0, s1, d0, lane, out_chunk);
+				}
+				__syncwarp(); // the decode buffer and staging buffer b are free again
 			} else {
-				fsst_decode_lane<false>(cbuf - ca, cbeg, cend, dbuf - da, dbeg, s_sym, s_len);
-			}
-			__syncwarp();
-			// heap bytes [d0, d1): head bytes up to the first granule boundary, whole granules, tail bytes
-			const uint32_t g_lo = (d0 + 15u) & ~15u, g_hi = d1 & ~15u;
-			if (g_lo <= g_hi) {
-				for (uint32_t b = d0 + lane; b < g_lo; b += 32u) {
-					heap[b] = dbuf[b - da];
+				// oversize tile (very long strings): decode straight to the heap
+				if (twelve) {
+					if (cur.first < s1) {
+						fsst12_decode_lane<true>(codes, comp_end, cur.first, cur.last, cur.cbeg, heap, cur.dbeg, tab12);
+					}
+				} else {
+					fsst_decode_lane<true>(codes, cur.cbeg, cur.cend, heap, cur.dbeg, tab_addr);
 				}
-				for (uint32_t q = g_lo + lane * 16u; q < g_hi; q += 512u) {
-					*reinterpret_cast<uint4*>(heap + q) = *reinterpret_cast<const uint4*>(dbuf + (q - da));
-				}
-				for (uint32_t b = g_hi + lane; b < d1; b += 32u) {
-					heap[b] = dbuf[b - da];
-				}
-			} else { // the whole tile lies inside one granule
-				for (uint32_t b = d0 + lane; b < d1; b += 32u) {
-					heap[b] = dbuf[b - da];
+				if (is_rows) {
+					__threadfence_block();
+					__syncwarp();
+					tile_rows<true>(heap, haddr, dec_end, s0, s1, d0, lane, out_chunk);
 				}
 			}
-			if (is_rows) {
-				tile_rows<false>(dbuf - da, haddr, dec_end, s0, s1, d0, lane, out_chunk);
+			if (!has_next) {
+				break;
 			}
-			return;
-		}
-		// oversize tile (very long strings): decode straight to the heap
-		if (twelve) {
-			if (first < s1) {
-				fsst12_decode_lane<true>(codes, comp_end, first, last, cbeg, heap, dbeg, tab12);
-			}
-		} else {
-			fsst_decode_lane<true>(codes, cbeg, cend, heap, dbeg, s_sym, s_len);
-		}
-		if (is_rows) {
-			__threadfence_block();
-			__syncwarp();
-			tile_rows<true>(heap, haddr, dec_end, s0, s1, d0, lane, out_chunk);
+			cur = nxt;
+			nxt = nn;
+			tile += stride;
 		}
 		return;
 	}
@@ -479,7 +548,7 @@ cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream) {
 		const uint32_t per_cta = kWarps * 32u * L.lane_strings;
 		L.groups_per_rg = (L.vec_per_rg * 1024u + per_cta - 1u) / per_cta;
 	}
-	const uint32_t smem = kWarps * (L.cbuf_bytes + L.dbuf_bytes);
+	const uint32_t smem = kWarps * (2u * L.cbuf_bytes + L.dbuf_bytes); // two staging buffers for codes + one decode buffer per warp
 	static bool attr_set = false; // benign race: the attribute is idempotent
 	if (!attr_set) {
 		const cudaError_t e = cudaFuncSetAttribute(fls_str_heap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
