@@ -109,70 +109,96 @@ __device__ __forceinline__ void fsst12_decode_lane(const uint8_t* __restrict__ i
 // per code.  The loop is issue bound, so it is written for instruction count: the next code byte is loaded while the
 // current one is looked up, the fill level is kept in bits, the carry-over after a flush is two shifts (no selects), and
 // the table is addressed from a register (no per-iteration recomputation of shared-memory bases).
+// position in a code stream: a pointer (global memory) or a 32-bit shared-memory address (staging buffer)
 template <bool GLOBAL_IN>
-__device__ __forceinline__ uint32_t fsst_code_at(const uint8_t* p) {
-	if constexpr (GLOBAL_IN) {
-		return __ldg(p);
-	} else {
+struct FsstPos;
+template <>
+struct FsstPos<true> {
+	const uint8_t* p;
+	__device__ __forceinline__ FsstPos(const uint8_t* q) : p(q) {}
+	__device__ __forceinline__ uint32_t at(uint32_t k) const { return __ldg(p + k); }
+};
+template <>
+struct FsstPos<false> {
+	uint32_t p;
+	__device__ __forceinline__ FsstPos(const uint8_t* q) : p((uint32_t)__cvta_generic_to_shared(q)) {}
+	__device__ __forceinline__ uint32_t at(uint32_t k) const {
 		uint32_t v;
-		asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+		asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(p + k));
 		return v;
 	}
-}
+};
 
 template <bool GLOBAL_IN>
 __device__ __forceinline__ void fsst_decode_lane(const uint8_t* __restrict__ in, uint32_t cbeg, uint32_t cend, uint8_t* __restrict__ out,
                                                  uint32_t dbeg, uint32_t tab) {
-	if (cbeg >= cend) {
-		return;
-	}
 	const uint32_t mis = dbeg & 7u;
 	unsigned long long* ow = reinterpret_cast<unsigned long long*>(out + (dbeg - mis));
 	unsigned long long acc = 0;
 	uint32_t fill8 = 8u * mis, head = mis; // head: low bytes of the first word that belong to the previous lane's strings
-	const uint8_t* p = in + cbeg;
-	const uint8_t* const pe = in + cend;
-	asm volatile("mov.u32 %0, %0;" : "+r"(tab)); // keep the table address in a register (else it is recomputed per code)
-	uint32_t code = fsst_code_at<GLOBAL_IN>(p);
-	for (;;) {
-		++p;
-		// speculative: at the end of the stream this reads the byte after it (inside the staging buffer / the segment's slack)
-		uint32_t nxt = fsst_code_at<GLOBAL_IN>(p);
-		unsigned long long sym;
-		uint32_t len8;
-		if (__builtin_expect(code != FLS_FSST_ESC, 1)) {
-			uint32_t lo, hi, pad;
-			asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(hi), "=r"(len8), "=r"(pad) : "r"(tab + code * 16u));
-			sym = ((unsigned long long)hi << 32) | lo;
-		} else { // the next byte is a literal
-			sym = nxt;
-			len8 = 8u;
-			++p;
-			nxt = fsst_code_at<GLOBAL_IN>(p);
-		}
-		acc |= sym << fill8;
-		uint32_t nf8 = fill8 + len8;
-		if (nf8 >= 64u) {
-			if (head) {
+	if (cbeg < cend) {
+		FsstPos<GLOBAL_IN> pos(in + cbeg);
+		auto& p = pos.p;
+		const auto pe = p + (cend - cbeg);
+		asm volatile("mov.u32 %0, %0;" : "+r"(tab)); // keep the table address in a register (else it is recomputed per code)
+		// a full word leaves.  Staged tiles: always as one 8-byte store - the low bytes of a lane's first word belong to the
+		// previous lane, which writes them AFTER the warp has synchronised (below), over the zeros stored here.  Straight to
+		// the heap (GLOBAL_IN) the first word may be shared with another warp's tile, so its bytes are stored one by one.
+		auto flush = [&](unsigned long long sym, uint32_t len8, uint32_t nf8) {
+			if (GLOBAL_IN && head) {
 				uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
 				for (uint32_t k = head; k < 8u; ++k) {
 					ob[k] = (uint8_t)(acc >> (8u * k));
 				}
-				head = 0;
 			} else {
 				*ow = acc;
 			}
+			head = 0;
 			++ow;
 			nf8 -= 64u;
 			// what did not fit: sym >> (bits that went into the flushed word) - 8..64 of them, 64 when an 8-byte symbol
 			// filled an empty word, hence the shift in two steps
 			acc = (sym >> (len8 - nf8 - 1u)) >> 1;
+			return nf8;
+		};
+		uint32_t code = pos.at(0);
+		for (;;) {
+			// hot loop: table codes only, its two exits (escape, end of stream) are real branches
+			while (code != FLS_FSST_ESC) {
+				++p;
+				// speculative: at the end of the stream this reads the byte after it (inside the staging buffer / the segment's slack)
+				const uint32_t nxt = pos.at(0);
+				uint32_t lo, hi, len8, pad;
+				asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(hi), "=r"(len8), "=r"(pad) : "r"(tab + code * 16u));
+				const unsigned long long sym = ((unsigned long long)hi << 32) | lo;
+				acc |= sym << fill8;
+				fill8 += len8;
+				if (fill8 >= 64u) {
+					fill8 = flush(sym, len8, fill8);
+				}
+				if (p >= pe) {
+					goto done;
+				}
+				code = nxt;
+			}
+			{ // escape: the next byte is a literal
+				const unsigned long long lit = pos.at(1);
+				p += 2;
+				acc |= lit << fill8;
+				fill8 += 8u;
+				if (fill8 >= 64u) {
+					fill8 = flush(lit, 8u, fill8);
+				}
+				if (p >= pe) {
+					goto done;
+				}
+				code = pos.at(0);
+			}
 		}
-		fill8 = nf8;
-		if (p >= pe) {
-			break;
-		}
-		code = nxt;
+	}
+done:
+	if constexpr (!GLOBAL_IN) {
+		__syncwarp(); // every lane's full words are in the buffer: now the partial ones on top of them
 	}
 	uint8_t* ob = reinterpret_cast<uint8_t*>(ow);
 	for (uint32_t k = head; k < (fill8 >> 3); ++k) {

@@ -38,6 +38,25 @@ def all_reduce_partial(sum128, count, dist=None, device="cpu"):
     return unpack_partial(t.cpu())
 
 
+def limbs_of_results(res):
+    """uint8[k * 64] tensor of k flsgpu_agg_result structs (include/flsgpu.h: sum_lo, sum_hi, count, ...) -> int64[k, 5]
+    (four 32-bit limbs of the 128-bit SUM + COUNT), computed where the tensor lives: the partials of a query never visit
+    the host before the reduce."""
+    v = res.view(torch.int64).view(-1, 8)
+    lo, hi, m = v[:, 0], v[:, 1], 0xFFFFFFFF
+    return torch.stack([lo & m, (lo >> 32) & m, hi & m, (hi >> 32) & m, v[:, 2]], dim=1).contiguous()
+
+
+def all_reduce_results(res, dist=None):
+    """Combine the (SUM, COUNT) partials of k aggregates held in a device buffer of k flsgpu_agg_result structs: ONE
+    all_reduce(SUM) of k x 5 int64 lanes, then one D2H copy.  Returns [(sum128 as signed python int, count)] * k."""
+    limbs = limbs_of_results(res)
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(limbs, op=dist.ReduceOp.SUM)
+    host = limbs.cpu()
+    return [unpack_partial(host[i]) for i in range(host.shape[0])]
+
+
 def all_reduce_minmax(mn, mx, dist=None, device="cpu"):
     lo = torch.tensor([mn], dtype=torch.int64, device=device)
     hi = torch.tensor([mx], dtype=torch.int64, device=device)

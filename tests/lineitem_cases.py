@@ -67,8 +67,9 @@ def comments(n, r):
     return off, np.ascontiguousarray(data)
 
 
-def lineitem(n_rows, sf=1.0, seed=7, first_order=0):
-    """[(name, fls type, forced encoding (None = the writer's selection), data[, width, scale])] of n_rows lineitem rows."""
+def lineitem(n_rows, sf=1.0, seed=7, first_order=0, strings=True):
+    """[(name, fls type, forced encoding (None = the writer's selection), data[, width, scale])] of n_rows lineitem rows.
+    strings=False: the 11 integer / decimal / date columns only (what BASELINE config 5's SUM/COUNT scans read)."""
     r = np.random.default_rng(seed)
     # orders of 1..7 lines; order keys are sparse like dbgen's (8 used out of every 32), ascending
     n_orders = n_rows // 3 + 64  # 4 lines per order on average: comfortably more orders than the rows need
@@ -93,6 +94,20 @@ def lineitem(n_rows, sf=1.0, seed=7, first_order=0):
     today = 9298  # 1995-06-17: dbgen's CURRENTDATE
     returnflag = np.where(receiptdate <= today, r.integers(0, 2, n_rows), 2)  # R / A, else N
     linestatus = (shipdate > today).astype(np.int64)  # F / O
+    if not strings:
+        return [
+            ("l_orderkey", "INT64", None, orderkey),
+            ("l_partkey", "INT64", None, partkey),
+            ("l_suppkey", "INT64", None, suppkey),
+            ("l_linenumber", "INT32", None, linenumber),
+            ("l_quantity", "DECIMAL", None, quantity * 100, 15, 2),
+            ("l_extendedprice", "DECIMAL", None, extendedprice, 15, 2),
+            ("l_discount", "DECIMAL", None, discount, 15, 2),
+            ("l_tax", "DECIMAL", None, tax, 15, 2),
+            ("l_shipdate", "DATE", None, shipdate),
+            ("l_commitdate", "DATE", None, commitdate),
+            ("l_receiptdate", "DATE", None, receiptdate),
+        ]
     return [
         ("l_orderkey", "INT64", None, orderkey),
         ("l_partkey", "INT64", None, partkey),

@@ -32,6 +32,24 @@ def test_partial_pack_roundtrip_and_carries():
     assert sharding.unpack_partial(t) == (sum(vals), len(vals))
 
 
+def _results_buffer(partials):
+    """k (sum128, count) pairs as the device would hold them: k flsgpu_agg_result structs in one uint8 tensor."""
+    import flsgpu
+    raw = b""
+    for s, c in partials:
+        u = s & ((1 << 128) - 1)
+        raw += bytes(flsgpu.AggResult(sum_lo=u & (2 ** 64 - 1), sum_hi=u >> 64, count=c))
+    return torch.frombuffer(bytearray(raw), dtype=torch.uint8)
+
+
+def test_limbs_of_result_structs_match_pack_partial():
+    partials = [(0, 0), (1, 1), (-1, 7), (2 ** 64, 3), (-(2 ** 100), 2 ** 40), (2 ** 126 + 12345, 9), (-(2 ** 127), 1)]
+    limbs = sharding.limbs_of_results(_results_buffer(partials))
+    for row, (s, c) in zip(limbs, partials):
+        assert row.tolist() == sharding.pack_partial(s, c).tolist()
+    assert sharding.all_reduce_results(_results_buffer(partials)) == partials
+
+
 def _worker(rank, world, port, img_path, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -52,6 +70,13 @@ def _worker(rank, world, port, img_path, q):
         s, c = sharding.all_reduce_partial(part["sum"], part["count"], dist)
         mn, mx = sharding.all_reduce_minmax(part["min"], part["max"], dist)
         out[col] = (s, c, mn, mx)
+    # the same reduction with the partials left in a buffer of result structs: one all-reduce for every column
+    parts = []
+    for col in range(t.n_columns):
+        part = o.aggregate(col, b, e - b) if e > b else dict(sum=0, count=0)
+        parts.append((part["sum"], part["count"]))
+    batched = sharding.all_reduce_results(_results_buffer(parts), dist)
+    assert batched == [(out[col][0], out[col][1]) for col in range(t.n_columns)]
     if rank == 0:
         q.put(out)
     dist.barrier()
