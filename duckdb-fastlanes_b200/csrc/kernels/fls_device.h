@@ -80,6 +80,22 @@ struct FlsStrLaunch {
 	uint32_t fuse_rows;          // FSST chunks: the heap kernel also builds the string_t rows (the rows kernel skips them)
 };
 
+// Launch parameters of the string filter kernel (flsgpu_kernels_str.cu): a constant comparison over the decoded string_t
+// rows of a slab of row groups (FilterExecutor::Apply on a VARCHAR / BLOB column, reference filter_executor.cpp:19-60).
+struct FlsStrFilterLaunch {
+	const void* rows;          // string_t[n_rg * vec_per_rg * 1024]; pointers of non-inlined strings are device addresses
+	const uint32_t* n_tuples;  // tuples of every row group of the slab (rows beyond them never pass)
+	const uint8_t* rg_keep;    // per row group of the slab: 0 = pruned (selects nothing), or nullptr
+	const uint8_t* const_data; // the constant's bytes on the device
+	uint32_t const_len;
+	uint32_t const_prefix;     // its first 4 bytes, zero padded (string_t prefix layout)
+	uint32_t op;               // flsgpu_cmp
+	uint32_t and_into;         // 0: mask = cmp; 1: mask &= cmp
+	uint32_t* mask;            // [n_rg * vec_per_rg * 32] words of the slab
+	uint32_t n_rg;
+	uint32_t vec_per_rg;
+};
+
 // Per-warp shared memory holding the 32 vector descriptors of a batch (64 B each), in front of the pipeline slots.
 #define FLS_DESC_BYTES_PER_WARP 2048u
 

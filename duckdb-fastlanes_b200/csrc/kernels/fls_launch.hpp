@@ -26,6 +26,8 @@ cudaError_t fls_agg_reset(flsgpu_agg_acc* acc, cudaStream_t stream);
 cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream);
 cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream);
 cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t max_keys_per_chunk, cudaStream_t stream);
+// Constant comparison over decoded string_t rows -> selection mask words (one warp per vector).
+cudaError_t fls_str_launch_filter(FlsStrFilterLaunch L, cudaStream_t stream);
 #endif
 
 constexpr int kFlsWarpsPerCta = 8;

@@ -450,8 +450,11 @@ int check_filters(const flsgpu_table* t, const flsgpu_filter* f, uint32_t n, con
 			std::snprintf(msg, sizeof(msg), "%s: filter %u has a bad column or comparison", who, i);
 			return fls_set_error(FLSGPU_ERR_INVALID, msg);
 		}
-		if (t->columns[f[i].col].phys_bits == 128) {
-			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "filters on string columns are evaluated by the host after decode");
+		if (t->columns[f[i].col].phys_bits == 128 && !f[i].str_data && f[i].str_len) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "filter on a string column without the constant's bytes (str_data)");
+		}
+		if (t->columns[f[i].col].phys_bits == 128 && f[i].str_len > 0xffffffffull) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "string filter constant longer than a string_t can be");
 		}
 	}
 	return FLSGPU_OK;
@@ -1294,6 +1297,98 @@ int cmp_physical(const fls_column_desc& c, uint64_t a, uint64_t b) {
 	return a < b ? -1 : a > b ? 1 : 0;
 }
 
+// FilterExecutor::Apply on a VARCHAR / BLOB column: the reference decodes the chunk and hands the vector to
+// ColumnSegment::FilterSelection (filter_executor.cpp:42-48).  Here slabs of row groups are decoded to string_t rows + heap
+// in stream-ordered scratch memory (string pointers = device addresses of the heap) and compared by fls_str_filter_kernel;
+// the scratch (rows, heap, the constant's bytes, the slab's tuple counts) is one cudaMallocAsync block reused by every slab.
+int string_filter_pass(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg_begin, uint32_t n_rg, const uint8_t* rg_keep_dev,
+                       uint32_t* mask_dev, bool and_into, cudaStream_t s) {
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	const uint64_t rows_per_rg = (uint64_t)vpr * FLS_VEC_SZ * 16u;
+	const uint64_t budget = (uint64_t)env_u32("FLSGPU_STR_FILTER_SLAB_MB", 512) << 20;
+	// slabs: as many row groups as fit the budget (rows + heap), at least one
+	std::vector<std::pair<uint32_t, uint32_t>> slabs; // (first row group, count)
+	std::vector<uint64_t> slab_heap;
+	uint64_t max_rows = 0, max_heap = 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg;) {
+		uint64_t bytes = 0, heap = 0;
+		uint32_t n = 0;
+		while (r + n < rg_begin + n_rg) {
+			uint64_t h = 0;
+			const int hrc = flsgpu_string_heap_bytes(t, f.col, r + n, 1, &h);
+			if (hrc) {
+				return hrc;
+			}
+			if (n && bytes + rows_per_rg + h > budget) {
+				break;
+			}
+			bytes += rows_per_rg + h;
+			heap += h;
+			++n;
+		}
+		slabs.emplace_back(r, n);
+		slab_heap.push_back(heap);
+		max_rows = std::max(max_rows, (uint64_t)n * rows_per_rg);
+		max_heap = std::max(max_heap, heap);
+		r += n;
+	}
+	if (slabs.empty()) {
+		return FLSGPU_OK;
+	}
+	const uint64_t heap_cap = ((max_heap + 255u) & ~255ull) + 256u;
+	const uint64_t const_cap = ((f.str_len + 255u) & ~255ull) + 256u;
+	const uint64_t counts_cap = (((uint64_t)n_rg * 4u + 255u) & ~255ull);
+	uint8_t* scratch = nullptr;
+	FLS_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&scratch), max_rows + heap_cap + const_cap + counts_cap, s));
+	uint8_t* rows_dev = scratch;
+	uint8_t* heap_dev = rows_dev + max_rows;
+	uint8_t* const_dev = heap_dev + heap_cap;
+	uint32_t* counts_dev = reinterpret_cast<uint32_t*>(const_dev + const_cap);
+	std::vector<uint32_t> counts(n_rg);
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		counts[r] = t->rowgroups[rg_begin + r].n_tuples;
+	}
+	int rc = FLSGPU_OK;
+	cudaError_t ce = cudaMemcpyAsync(counts_dev, counts.data(), (size_t)n_rg * 4u, cudaMemcpyHostToDevice, s); // pageable source:
+	if (ce == cudaSuccess && f.str_len) { // staged before the call returns
+		ce = cudaMemcpyAsync(const_dev, f.str_data, f.str_len, cudaMemcpyHostToDevice, s);
+	}
+	if (ce != cudaSuccess) {
+		rc = fls_set_error(FLSGPU_ERR_CUDA, cudaGetErrorString(ce));
+	}
+	uint32_t prefix = 0;
+	if (f.str_len) {
+		std::memcpy(&prefix, f.str_data, (size_t)std::min<uint64_t>(4, f.str_len));
+	}
+	for (size_t i = 0; i < slabs.size() && rc == FLSGPU_OK; ++i) {
+		const uint32_t r0 = slabs[i].first, n = slabs[i].second;
+		rc = flsgpu_decode_strings(t, f.col, r0, n, rows_dev, (uint64_t)n * rows_per_rg, heap_dev, heap_cap,
+		                           reinterpret_cast<uint64_t>(heap_dev), s);
+		if (rc) {
+			break;
+		}
+		FlsStrFilterLaunch L {};
+		L.rows = rows_dev;
+		L.n_tuples = counts_dev + (r0 - rg_begin);
+		L.rg_keep = rg_keep_dev ? rg_keep_dev + (r0 - rg_begin) : nullptr;
+		L.const_data = const_dev;
+		L.const_len = (uint32_t)f.str_len;
+		L.const_prefix = prefix;
+		L.op = (uint32_t)f.op;
+		L.and_into = and_into ? 1u : 0u;
+		L.mask = mask_dev + (uint64_t)(r0 - rg_begin) * vpr * 32u;
+		L.n_rg = n;
+		L.vec_per_rg = vpr;
+		ce = fls_str_launch_filter(L, s);
+		if (ce != cudaSuccess) {
+			rc = fls_set_error(FLSGPU_ERR_CUDA, cudaGetErrorString(ce));
+		}
+		g_launches.fetch_add(1, std::memory_order_relaxed);
+	}
+	cudaFreeAsync(scratch, s);
+	return rc;
+}
+
 } // namespace
 
 int flsgpu_rowgroup_prune(const flsgpu_table* t, const flsgpu_filter* filters, uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg,
@@ -1313,7 +1408,7 @@ int flsgpu_rowgroup_prune(const flsgpu_table* t, const flsgpu_filter* filters, u
 		for (uint32_t i = 0; i < n_filters && keep; ++i) {
 			const fls_chunk_desc& ch = t->chunk(rg_begin + r, filters[i].col);
 			const fls_column_desc& col = t->columns[filters[i].col];
-			if (!ch.has_stats || col.is_float) {
+			if (!ch.has_stats || col.is_float || col.phys_bits == 128) {
 				continue; // no zone map: the row group may satisfy the filter (row_group_filter.cpp:157-160)
 			}
 			const int cmin = cmp_physical(col, ch.min_val, filters[i].constant), cmax = cmp_physical(col, ch.max_val, filters[i].constant);
@@ -1357,8 +1452,8 @@ int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n
 	std::vector<uint8_t> done(n_filters, 0);
 	bool first = true;
 	for (uint32_t i = 0; i < n_filters; ++i) {
-		if (done[i]) {
-			continue;
+		if (done[i] || t->columns[filters[i].col].phys_bits == 128) {
+			continue; // string filters run after the fused numeric passes
 		}
 		rc = check_resident(t, d, filters[i].col, rg_begin, n_rg);
 		if (rc) {
@@ -1385,6 +1480,15 @@ int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n
 		rc = decode_column_impl(t, d, filters[i].col, rg_begin, n_rg, os, nullptr, s, nullptr, &ms);
 		if (rc) {
 			return rc;
+		}
+	}
+	for (uint32_t i = 0; i < n_filters; ++i) {
+		if (t->columns[filters[i].col].phys_bits == 128) {
+			rc = string_filter_pass(t, filters[i], rg_begin, n_rg, rg_keep_dev, mask_dev, !first, s);
+			if (rc) {
+				return rc;
+			}
+			first = false;
 		}
 	}
 	return FLSGPU_OK;

@@ -562,7 +562,74 @@ __global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L)
 	}
 }
 
+// FilterExecutor::Apply on a string column (reference filter_executor.cpp:19-60 -> ColumnSegment::FilterSelection with a
+// ConstantFilter): compare every decoded string_t of the slab with the constant the way DuckDB does (string_type.hpp:155-217:
+// memcmp over the common length, the shorter string first on a tie) and emit the selection as mask words.  One warp per
+// vector: 32 coalesced 512-byte row loads; most rows are decided by the 4-byte prefix (zero padded in string_t, so a
+// big-endian integer comparison of two different prefixes is the bytewise order), the rest walk their bytes (inlined:
+// the row itself; longer: the heap the rows point into).
+__device__ __forceinline__ int compare_string_row(const uint4& s, const uint8_t* row_bytes, const FlsStrFilterLaunch& L) {
+	const uint32_t pa = __byte_perm(s.y, 0u, 0x0123), pb = __byte_perm(L.const_prefix, 0u, 0x0123);
+	if (pa != pb) {
+		return pa < pb ? -1 : 1;
+	}
+	const uint32_t la = s.x, lb = L.const_len, m = la < lb ? la : lb;
+	if (m > 4u) {
+		const uint8_t* p = la <= 12u ? row_bytes + 4 : reinterpret_cast<const uint8_t*>(((unsigned long long)s.w << 32) | s.z);
+		for (uint32_t k = 4; k < m; ++k) {
+			const uint32_t a = p[k], b = __ldg(L.const_data + k);
+			if (a != b) {
+				return a < b ? -1 : 1;
+			}
+		}
+	}
+	return la < lb ? -1 : la > lb ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(kWarps * 32) fls_str_filter_kernel(const FlsStrFilterLaunch L) {
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	const uint32_t v = blockIdx.x * kWarps + warp;
+	if (v >= L.n_rg * L.vec_per_rg) {
+		return;
+	}
+	const uint32_t rg = v / L.vec_per_rg, vi = v - rg * L.vec_per_rg;
+	const uint32_t nt = __ldg(L.n_tuples + rg);
+	const bool keep = L.rg_keep == nullptr || __ldg(L.rg_keep + rg) != 0;
+	const uint32_t first = vi * 1024u;
+	const uint32_t valid = !keep || nt <= first ? 0u : (nt - first < 1024u ? nt - first : 1024u);
+	const uint4* rows = static_cast<const uint4*>(L.rows) + (size_t)v * 1024u;
+	uint32_t mine = 0;
+	for (uint32_t it = 0; it * 32u < valid; ++it) {
+		const uint32_t row = it * 32u + lane;
+		bool pass = false;
+		if (row < valid) {
+			const uint4 s = __ldg(rows + row);
+			const int c = compare_string_row(s, reinterpret_cast<const uint8_t*>(rows + row), L);
+			switch (L.op) { // flsgpu_cmp: EQ NE LT LE GT GE
+			case 0: pass = c == 0; break;
+			case 1: pass = c != 0; break;
+			case 2: pass = c < 0; break;
+			case 3: pass = c <= 0; break;
+			case 4: pass = c > 0; break;
+			default: pass = c >= 0; break;
+			}
+		}
+		const uint32_t word = __ballot_sync(0xffffffffu, pass);
+		if (lane == it) {
+			mine = word;
+		}
+	}
+	uint32_t* mw = L.mask + (size_t)v * 32u + lane;
+	*mw = L.and_into ? (*mw & mine) : mine;
+}
+
 } // namespace
+
+cudaError_t fls_str_launch_filter(FlsStrFilterLaunch L, cudaStream_t stream) {
+	const uint32_t n_vec = L.n_rg * L.vec_per_rg;
+	fls_str_filter_kernel<<<(n_vec + kWarps - 1) / kWarps, kWarps * 32, 0, stream>>>(L);
+	return cudaGetLastError();
+}
 
 cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream) {
 	// 8 warp tiles of 32 * lane_strings strings per CTA; groups_per_rg (CTAs per chunk) comes from the launcher, which knows

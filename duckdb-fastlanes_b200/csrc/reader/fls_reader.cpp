@@ -282,6 +282,8 @@ std::vector<flsgpu_filter> FastLanesReader::PhysicalFilters() const {
 		p.col = (uint32_t)column_ids[f.column_index];
 		p.op = f.op;
 		p.constant = f.constant;
+		p.str_data = reinterpret_cast<const uint8_t*>(f.string_constant.data()); // owned by this->filters, alive for the scan
+		p.str_len = f.string_constant.size();
 		out.push_back(p);
 	}
 	return out;

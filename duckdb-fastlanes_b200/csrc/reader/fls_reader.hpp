@@ -99,11 +99,13 @@ struct DataChunk {
 };
 
 // ConstantFilter entry of a TableFilterSet (BaseFileReader::filters, base_file_reader.hpp:36-54): keyed by the position
-// of the column in column_ids; the constant is the physical value of the column's type (flsgpu_filter).
+// of the column in column_ids; the constant is the physical value of the column's type (flsgpu_filter), or the bytes of
+// a VARCHAR / BLOB constant (string_constant; compared like DuckDB's string_t, string_type.hpp:155-217).
 struct TableFilter {
 	idx_t column_index = 0; // index into column_ids
 	flsgpu_cmp op = FLSGPU_CMP_EQ;
 	uint64_t constant = 0;
+	std::string string_constant; // filters on string columns only
 };
 
 // FastLanesReaderProjectionPlan (fls_multi_file_info.hpp:48-55)

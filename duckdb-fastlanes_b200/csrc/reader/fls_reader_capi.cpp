@@ -117,6 +117,9 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 		f.column_index = filters[i].column_index;
 		f.op = (flsgpu_cmp)filters[i].op;
 		f.constant = filters[i].constant;
+		if (filters[i].str_data && filters[i].str_len) {
+			f.string_constant.assign(reinterpret_cast<const char*>(filters[i].str_data), filters[i].str_len);
+		}
 		reader.filters.push_back(f);
 	}
 	const auto& cols = reader.GetColumns();
@@ -304,6 +307,9 @@ int flsmulti_scan(flsmulti_handle* h, const uint64_t* column_ids, uint32_t n_col
 			f.column_index = filters[i].column_index;
 			f.op = (flsgpu_cmp)filters[i].op;
 			f.constant = filters[i].constant;
+			if (filters[i].str_data && filters[i].str_len) {
+				f.string_constant.assign(reinterpret_cast<const char*>(filters[i].str_data), filters[i].str_len);
+			}
 			info.filters.push_back(f);
 		}
 		const auto& cols = info.Columns();

@@ -40,6 +40,8 @@ typedef struct flsreader_filter {
 	uint64_t column_index;
 	int32_t op; /* flsgpu_cmp */
 	uint64_t constant;
+	const uint8_t* str_data; /* VARCHAR / BLOB columns: the constant's bytes (copied by the call), else NULL */
+	uint64_t str_len;
 } flsreader_filter;
 typedef struct flsreader_scan_stats {
 	uint64_t rows, chunks, max_chunk_rows;

@@ -50,12 +50,19 @@ CMP = dict(EQ=0, NE=1, LT=2, LE=3, GT=4, GE=5)
 
 
 class Filter(C.Structure):  # flsgpu_filter
-    _fields_ = [("col", C.c_uint32), ("op", C.c_int32), ("constant", C.c_uint64)]
+    _fields_ = [("col", C.c_uint32), ("op", C.c_int32), ("constant", C.c_uint64), ("str_data", C.c_char_p), ("str_len", C.c_uint64)]
 
 
 def make_filters(filters):
-    """[(col, 'GE', physical constant bits)] -> ctypes array."""
-    return (Filter * len(filters))(*[Filter(c, CMP[op] if isinstance(op, str) else op, k & 0xFFFFFFFFFFFFFFFF) for c, op, k in filters])
+    """[(col, 'GE', constant)] -> ctypes array; constant = physical bits (int) for numeric columns, bytes for VARCHAR / BLOB."""
+    out = []
+    for c, op, k in filters:
+        op = CMP[op] if isinstance(op, str) else op
+        if isinstance(k, (bytes, bytearray)):
+            out.append(Filter(c, op, 0, bytes(k), len(k)))
+        else:
+            out.append(Filter(c, op, int(k) & 0xFFFFFFFFFFFFFFFF, None, 0))
+    return (Filter * len(out))(*out)
 
 
 class StringColumn(C.Structure):

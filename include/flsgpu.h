@@ -166,10 +166,12 @@ int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, ui
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream);
 
 /* ---- filter pushdown: RowGroupFilter (row_group_filter.cpp:96-199) + FilterExecutor (filter_executor.cpp:19-60) ------ */
-/* Constant comparisons on numeric columns (DuckDB ConstantFilter), combined with AND like a TableFilterSet.  `constant` is
+/* Constant comparisons (DuckDB ConstantFilter), combined with AND like a TableFilterSet.  Numeric columns: `constant` is
  * the physical value of the column's type: integers sign- / zero-extended to 64 bits (DATE days, TIMESTAMP micros,
  * DECIMAL unscaled), FLOAT bits in the low word, DOUBLE bits.  Floating point follows DuckDB: NaN equals NaN and is
- * greater than every other value. */
+ * greater than every other value.  VARCHAR / BLOB columns: the constant is the str_len bytes at str_data (host memory,
+ * read during the call; `constant` is ignored), compared like DuckDB's string_t: bytewise over the common length, the
+ * shorter string first on a tie (string_type.hpp:155-217).  String chunks carry no zone maps: they never prune. */
 typedef enum flsgpu_cmp {
 	FLSGPU_CMP_EQ = 0, FLSGPU_CMP_NE = 1, FLSGPU_CMP_LT = 2, FLSGPU_CMP_LE = 3, FLSGPU_CMP_GT = 4, FLSGPU_CMP_GE = 5
 } flsgpu_cmp;
@@ -177,12 +179,15 @@ typedef struct flsgpu_filter {
 	uint32_t col;
 	int32_t op; /* flsgpu_cmp */
 	uint64_t constant;
+	const uint8_t* str_data; /* string columns only (may be NULL when str_len == 0) */
+	uint64_t str_len;
 } flsgpu_filter;
 /* RowGroupMaySatisfyFilters: keep_out[r] = 0 when the zone maps (fls_chunk_desc.min_val / max_val) of row group
  * rg_begin + r prove that no row passes.  Host only. */
 int flsgpu_rowgroup_prune(const flsgpu_table* t, const flsgpu_filter* filters, uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg,
                           uint8_t* keep_out);
-/* FilterExecutor::Apply on the device: decode each filter column (fused, nothing is written but the mask) and set bit i
+/* FilterExecutor::Apply on the device: decode each filter column (numeric: fused, nothing is written but the mask; string:
+ * slabs of row groups are decoded to string_t rows in stream-ordered scratch memory and compared there) and set bit i
  * of word w of vector v (mask_dev[v * 32 + w], vectors laid out as in flsgpu_decode_column) when row v*1024 + w*32 + i
  * passes every filter.  Padding rows never pass.  rg_keep_dev (device copy of flsgpu_rowgroup_prune's output, or NULL):
  * pruned row groups are not decoded and select nothing. */

@@ -71,6 +71,8 @@ typedef struct fls_oracle_filter {
 	uint32_t col;
 	int32_t op;
 	uint64_t constant; /* physical bits, integers extended to 64 */
+	const uint8_t* str_data; /* VARCHAR / BLOB columns: the constant's bytes (compared bytewise, then by length) */
+	uint64_t str_len;
 } fls_oracle_filter;
 int fls_oracle_filter_mask(const fls_oracle_table* t, const fls_oracle_filter* filters, uint32_t n_filters, uint32_t rg_begin,
                            uint32_t n_rg, uint32_t* mask /* n_rg * vec_per_rowgroup * 32 words */);

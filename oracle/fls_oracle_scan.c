@@ -428,6 +428,51 @@ static int passes(int op, int cmp) {
 	}
 }
 
+/* VARCHAR / BLOB constants: DuckDB compares string_t bytewise (memcmp over the common length), the shorter string first
+ * on a tie (duckdb/src/include/duckdb/common/types/string_type.hpp:155-217, StringComparisonOperators: GreaterThan is
+ * memcmp(left, right, min_len) > 0 || (== 0 && left_len > right_len); Equals compares length + bytes).  The filter column
+ * is decoded the way the scan decodes it (flat string_t rows of one row group) and every valid row is compared. */
+typedef struct ofilter_str {
+	uint32_t len;
+	uint8_t prefix[4];
+	union {
+		uint8_t inlined[8];
+		uint64_t ptr;
+	} v;
+} ofilter_str;
+
+static int cmp_string(const ofilter_str* s, const uint8_t* k, uint64_t klen) {
+	const uint8_t* p = s->len <= 12 ? s->prefix : (const uint8_t*)(uintptr_t)s->v.ptr;
+	const uint64_t m = s->len < klen ? s->len : klen;
+	const int c = m ? memcmp(p, k, m) : 0;
+	if (c) {
+		return c < 0 ? -1 : 1;
+	}
+	return s->len < klen ? -1 : s->len > klen ? 1 : 0;
+}
+
+static int filter_string_rowgroup(const fls_oracle_table* t, const fls_oracle_filter* f, uint32_t rg, uint32_t* mask_rg) {
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	uint64_t heap_bytes = 0;
+	if (fls_oracle_string_heap_bytes(t, f->col, rg, 1, &heap_bytes)) {
+		return -1;
+	}
+	ofilter_str* rows = (ofilter_str*)malloc((size_t)vpr * 1024 * sizeof(ofilter_str));
+	uint8_t* heap = (uint8_t*)malloc(heap_bytes + 16);
+	int rc = rows && heap ? fls_oracle_decode_strings(t, f->col, rg, 1, rows, heap, (uint64_t)(uintptr_t)heap) : -1;
+	if (!rc) {
+		const uint32_t n = t->rowgroups[rg].n_tuples;
+		for (uint32_t i = 0; i < n; ++i) {
+			if (!passes(f->op, cmp_string(&rows[i], f->str_data, f->str_len))) {
+				mask_rg[i >> 5] &= ~(1u << (i & 31));
+			}
+		}
+	}
+	free(rows);
+	free(heap);
+	return rc;
+}
+
 int fls_oracle_filter_mask(const fls_oracle_table* t, const fls_oracle_filter* filters, uint32_t n_filters, uint32_t rg_begin,
                            uint32_t n_rg, uint32_t* mask) {
 	if (rg_begin + n_rg > t->header.n_rowgroups) {
@@ -447,8 +492,11 @@ int fls_oracle_filter_mask(const fls_oracle_table* t, const fls_oracle_filter* f
 				mv[i >> 5] |= 1u << (i & 31);
 			}
 			for (uint32_t f = 0; f < n_filters; ++f) {
-				if (filters[f].col >= t->header.n_columns || t->columns[filters[f].col].phys_bits == 128) {
+				if (filters[f].col >= t->header.n_columns) {
 					return -1;
+				}
+				if (t->columns[filters[f].col].phys_bits == 128) {
+					continue; /* string filters: one pass per row group, below */
 				}
 				const fls_column_desc* c = &t->columns[filters[f].col];
 				int tr = 0;
@@ -468,6 +516,13 @@ int fls_oracle_filter_mask(const fls_oracle_table* t, const fls_oracle_filter* f
 				}
 			}
 		}
+		for (uint32_t f = 0; f < n_filters; ++f) {
+			if (t->columns[filters[f].col].phys_bits == 128) {
+				if ((!filters[f].str_data && filters[f].str_len) || filter_string_rowgroup(t, &filters[f], rg, mask + (size_t)r * vpr * 32)) {
+					return -1;
+				}
+			}
+		}
 	}
 	return 0;
 }
@@ -478,8 +533,8 @@ int fls_oracle_rowgroup_may_satisfy(const fls_oracle_table* t, const fls_oracle_
 	for (uint32_t f = 0; f < n_filters; ++f) {
 		const fls_column_desc* c = &t->columns[filters[f].col];
 		const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + filters[f].col];
-		if (!ch->has_stats || c->is_float) {
-			continue;
+		if (!ch->has_stats || c->is_float || c->phys_bits == 128) {
+			continue; /* no zone maps on floating point and string chunks */
 		}
 		const int cmin = cmp_values(c, ch->min_val, filters[f].constant), cmax = cmp_values(c, ch->max_val, filters[f].constant);
 		switch (filters[f].op) {

@@ -34,7 +34,18 @@ lib.fls_oracle_alp_decode_f32.argtypes = [C.c_int32, C.c_int, C.c_int]
 
 
 class OracleFilter(C.Structure):
-    _fields_ = [("col", C.c_uint32), ("op", C.c_int32), ("constant", C.c_uint64)]
+    _fields_ = [("col", C.c_uint32), ("op", C.c_int32), ("constant", C.c_uint64), ("str_data", C.c_char_p), ("str_len", C.c_uint64)]
+
+
+def _oracle_filters(filters):
+    """[(col, op, constant)]: an int (physical bits) for numeric columns, bytes for VARCHAR / BLOB columns."""
+    out = []
+    for c, op, k in filters:
+        if isinstance(k, (bytes, bytearray)):
+            out.append(OracleFilter(c, op, 0, bytes(k), len(k)))
+        else:
+            out.append(OracleFilter(c, op, int(k) & 0xFFFFFFFFFFFFFFFF, None, 0))
+    return (OracleFilter * len(out))(*out)
 
 
 class Oracle:
@@ -94,7 +105,7 @@ class Oracle:
 
     def filter_mask(self, filters, rg_begin, n_rg, vec_per_rg):
         """filters: [(col, op, constant_bits)] -> uint32 mask [n_rg * vec_per_rg * 32]."""
-        arr = (OracleFilter * len(filters))(*[OracleFilter(c, op, k & 0xFFFFFFFFFFFFFFFF) for c, op, k in filters])
+        arr = _oracle_filters(filters)
         mask = np.zeros(n_rg * vec_per_rg * 32, dtype=np.uint32)
         rc = lib.fls_oracle_filter_mask(C.byref(self.t), arr, len(filters), rg_begin, n_rg, C.c_void_p(mask.ctypes.data))
         if rc:
@@ -102,7 +113,7 @@ class Oracle:
         return mask
 
     def rowgroup_may_satisfy(self, filters, rg):
-        arr = (OracleFilter * len(filters))(*[OracleFilter(c, op, k & 0xFFFFFFFFFFFFFFFF) for c, op, k in filters])
+        arr = _oracle_filters(filters)
         return bool(lib.fls_oracle_rowgroup_may_satisfy(C.byref(self.t), arr, len(filters), rg))
 
     def aggregate_masked(self, col, rg_begin, n_rg, mask):

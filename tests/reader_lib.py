@@ -23,7 +23,19 @@ class StringSink(C.Structure):
 
 
 class ReaderFilter(C.Structure):
-    _fields_ = [("column_index", C.c_uint64), ("op", C.c_int32), ("constant", C.c_uint64)]
+    _fields_ = [("column_index", C.c_uint64), ("op", C.c_int32), ("constant", C.c_uint64), ("str_data", C.c_char_p),
+                ("str_len", C.c_uint64)]
+
+
+def reader_filters(filters):
+    """[(index into column_ids, op, constant)]: physical bits (int) or the bytes of a VARCHAR / BLOB constant."""
+    out = []
+    for ci, op, k in filters:
+        if isinstance(k, (bytes, bytearray)):
+            out.append(ReaderFilter(ci, op, 0, bytes(k), len(k)))
+        else:
+            out.append(ReaderFilter(ci, op, int(k) & 0xFFFFFFFFFFFFFFFF, None, 0))
+    return (ReaderFilter * max(1, len(out)))(*out)
 
 
 class ScanStats(C.Structure):
@@ -126,7 +138,7 @@ class Reader:
                 ptrs.append(a.ctypes.data)
         ia = (C.c_uint64 * len(ids))(*ids)
         pa = (C.c_void_p * len(ids))(*ptrs)
-        fa = (ReaderFilter * max(1, len(filters)))(*[ReaderFilter(ci, op, k & 0xFFFFFFFFFFFFFFFF) for ci, op, k in filters])
+        fa = reader_filters(filters)
         row_ids = np.zeros(n, dtype=np.int64)
         st = ScanStats()
         rc = lib.flsreader_scan(self._h, ia, len(ids), fa, len(filters), n_threads, pa, C.c_void_p(row_ids.ctypes.data), C.byref(st))
@@ -218,7 +230,7 @@ class MultiReader:
         ia = (C.c_uint64 * len(ids))(*ids)
         pa = (C.c_void_p * len(ids))(*ptrs)
         va = (C.c_void_p * len(ids))(*[v.ctypes.data for v in valids])
-        fa = (ReaderFilter * max(1, len(filters)))(*[ReaderFilter(ci, op, k & 0xFFFFFFFFFFFFFFFF) for ci, op, k in filters])
+        fa = reader_filters(filters)
         file_ids, row_ids = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.int64)
         st = ScanStats()
         rc = lib.flsmulti_scan(self._h, ia, len(ids), fa, len(filters), n_threads, pa, va, C.c_void_p(file_ids.ctypes.data),

@@ -1,0 +1,96 @@
+"""GPU: filters on VARCHAR / BLOB columns through the C ABI (flsgpu_filter_mask: slabs decoded to string_t rows in scratch
+memory, compared on the device) == oracle == plain Python, combined with numeric filters, with pruned row groups, through the
+host-to-host filtered scan and through the reader mirror."""
+import numpy as np
+import pytest
+
+import flsgpu
+import oracle_lib
+from str_filter_cases import COLUMNS, filter_sets, python_mask, table
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,vpr,slab_mb", [(3000, 2, None), (20000, 8, None), (70000, 4, "1")])
+def test_string_masks_match_oracle(n, vpr, slab_mb, monkeypatch):
+    import torch
+    if slab_mb:
+        monkeypatch.setenv("FLSGPU_STR_FILTER_SLAB_MB", slab_mb)  # many slabs per pass
+    specs, data = table(n)
+    img = flsgpu.write_table(specs, data, vec_per_rowgroup=vpr)
+    names = [s[0] for s in specs]
+    t = flsgpu.Table(img)
+    t.stage()
+    o = oracle_lib.Oracle(img)
+    n_words = t.n_rowgroups * t.vec_per_rowgroup * 32
+    res = torch.zeros(64, dtype=torch.uint8, device="cuda")
+    vi = names.index("v")
+    for fname, fs in filter_sets(data).items():
+        filt = [(names.index(c), flsgpu.CMP[op], k) for c, op, k in fs]
+        exp = o.filter_mask(filt, 0, t.n_rowgroups, t.vec_per_rowgroup)
+        want = python_mask(specs, data, fs)
+        assert int(np.unpackbits(exp.view(np.uint8)).sum()) == int(want.sum()), fname
+        mask = torch.full((n_words,), -1, dtype=torch.int32, device="cuda")
+        t.filter_mask(filt, mask.data_ptr(), n_words * 4)
+        flsgpu.sync()
+        got = mask.cpu().numpy().view(np.uint32)
+        assert got.tobytes() == exp.tobytes(), fname
+        # SELECT SUM(v), COUNT(*) WHERE <string filters>
+        flsgpu.agg_reset(res.data_ptr())
+        t.aggregate_column_masked(vi, mask.data_ptr(), res.data_ptr())
+        flsgpu.sync()
+        r = flsgpu.AggResult.from_buffer_copy(res.cpu().numpy().tobytes())
+        assert r.count == int(want.sum()) and r.sum_lo == int(np.asarray(data[vi])[want].sum()), fname
+    # pruned row groups select nothing, whatever the strings say
+    keep_host = (np.arange(t.n_rowgroups) % 2).astype(np.uint8)
+    keep = torch.from_numpy(keep_host).cuda()
+    filt = [(names.index("shipmode"), flsgpu.CMP["NE"], b"AIR")]
+    exp = o.filter_mask(filt, 0, t.n_rowgroups, t.vec_per_rowgroup).reshape(t.n_rowgroups, -1).copy()
+    exp[keep_host == 0] = 0
+    mask = torch.full((n_words,), -1, dtype=torch.int32, device="cuda")
+    t.filter_mask(filt, mask.data_ptr(), n_words * 4, keep.data_ptr())
+    flsgpu.sync()
+    assert mask.cpu().numpy().view(np.uint32).tobytes() == exp.tobytes()
+    # a sub-range of row groups
+    if t.n_rowgroups > 3:
+        filt = [(names.index("comment"), flsgpu.CMP["GE"], b"furiously"), (names.index("blob"), flsgpu.CMP["LT"], b"\x80")]
+        exp = o.filter_mask(filt, 1, t.n_rowgroups - 2, t.vec_per_rowgroup)
+        mask = torch.full((exp.size,), -1, dtype=torch.int32, device="cuda")
+        t.filter_mask(filt, mask.data_ptr(), exp.size * 4, 0, rg_begin=1, n_rg=t.n_rowgroups - 2)
+        flsgpu.sync()
+        assert mask.cpu().numpy().view(np.uint32).tobytes() == exp.tobytes()
+    t.close()
+
+
+@pytest.mark.parametrize("threads", [1, 3])
+def test_string_filters_through_reader(tmp_path, threads):
+    """WHERE l_shipmode = 'RAIL' AND ... pushed into the scan (read_fls.cpp:39-42 filter_pushdown = true; the reference
+    evaluates them in FilterExecutor::Apply after the decode): chunks come back sliced; result == plain Python."""
+    import reader_lib
+    n = 9 * 4096 + 55
+    specs, data = table(n)
+    names = [s[0] for s in specs]
+    img = flsgpu.write_table(specs, data, vec_per_rowgroup=4)
+    p = str(tmp_path / "sf.fls")
+    img.tofile(p)
+    r = reader_lib.Reader(p, rowgroups_per_batch=2)
+    proj = [names.index("v"), names.index("shipmode"), names.index("comment"), names.index("blob")]
+    sets = filter_sets(data)
+    for fname in ("dict_eq", "dict_range", "fsst_ge", "mixed", "two_strings", "blob_lt_empty", "blob_gt_ff"):
+        fs = sets[fname]
+        # filters address the projection; project the filter columns that are not in it
+        p2 = list(proj)
+        for c, _, _ in fs:
+            if names.index(c) not in p2:
+                p2.append(names.index(c))
+        filt = [(p2.index(names.index(c)), flsgpu.CMP[op], k) for c, op, k in fs]
+        got, row_ids, st = r.scan(p2, filt, n_threads=threads, stride=128)
+        want = python_mask(specs, data, fs)
+        idx = np.nonzero(want)[0]
+        assert st["rows"] == len(idx), fname
+        assert np.array_equal(row_ids, idx), fname
+        assert got[0].tobytes() == np.asarray(data[names.index("v")])[want].tobytes(), fname
+        for k, col in ((1, "shipmode"), (2, "comment"), (3, "blob")):
+            src = data[names.index(col)]
+            assert got[k] == [src[i] for i in idx], (fname, col)
+    r.close()
