@@ -78,6 +78,13 @@ struct FlsStrLaunch {
 	uint32_t cbuf_bytes;         // per-warp shared-memory staging of a tile's codes / decoded bytes (multiples of 16;
 	uint32_t dbuf_bytes;         //  tiles that do not fit are decoded straight to global memory)
 	uint32_t fuse_rows;          // FSST chunks: the heap kernel also builds the string_t rows (the rows kernel skips them)
+	// rows kernel, filter mode (dictionary-encoded chunks only): the comparison was evaluated once per dictionary key
+	// (key_flags, in key_prefix order), the rows only look their code's flag up -> selection mask words, nothing else written
+	const uint8_t* key_flags;    // nullptr: not a filter launch
+	const uint32_t* n_tuples;    // tuples of every row group of the range
+	const uint8_t* rg_keep;      // per row group: 0 = pruned (selects nothing), or nullptr
+	uint32_t* filter_mask;       // [n_rg * vec_per_rg * 32] words
+	uint32_t filter_and;         // 0: mask = flags; 1: mask &= flags
 };
 
 // Launch parameters of the string filter kernel (flsgpu_kernels_str.cu): a constant comparison over the decoded string_t
@@ -94,6 +101,9 @@ struct FlsStrFilterLaunch {
 	uint32_t* mask;            // [n_rg * vec_per_rg * 32] words of the slab
 	uint32_t n_rg;
 	uint32_t vec_per_rg;
+	// dictionary form: rows = the string_t of n_keys dictionary keys, one flag byte per key goes to key_flags_out
+	uint8_t* key_flags_out;
+	uint32_t n_keys;
 };
 
 // Per-warp shared memory holding the 32 vector descriptors of a batch (64 B each), in front of the pipeline slots.

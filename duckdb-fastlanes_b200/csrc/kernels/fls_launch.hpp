@@ -28,6 +28,8 @@ cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream);
 cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t max_keys_per_chunk, cudaStream_t stream);
 // Constant comparison over decoded string_t rows -> selection mask words (one warp per vector).
 cudaError_t fls_str_launch_filter(FlsStrFilterLaunch L, cudaStream_t stream);
+// The same comparison over the keys of dictionary chunks -> one flag byte per key (then fls_str_launch_rows in filter mode).
+cudaError_t fls_str_launch_key_flags(FlsStrFilterLaunch L, cudaStream_t stream);
 #endif
 
 constexpr int kFlsWarpsPerCta = 8;

@@ -1297,6 +1297,82 @@ int cmp_physical(const fls_column_desc& c, uint64_t a, uint64_t b) {
 	return a < b ? -1 : a > b ? 1 : 0;
 }
 
+// Dictionary-encoded ranges (DICT_STR / FSST_DICT / FSST12_DICT: l_shipmode, l_returnflag ...): the comparison is evaluated
+// once per dictionary key (keys + dictionary bytes decoded into scratch, one flag byte per key), then the rows kernel unpacks
+// the codes and looks the flags up: per row only the packed code is read and one mask bit written.
+int string_filter_pass_dict(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg_begin, uint32_t n_rg, const uint8_t* rg_keep_dev,
+                            uint32_t* mask_dev, bool and_into, cudaStream_t s) {
+	uint64_t n_keys = 0, heap_bytes = 0;
+	int rc = flsgpu_string_dict_keys(t, f.col, rg_begin, n_rg, &n_keys);
+	if (!rc) {
+		rc = flsgpu_string_heap_bytes(t, f.col, rg_begin, n_rg, &heap_bytes);
+	}
+	if (rc) {
+		return rc;
+	}
+	if (n_keys > 0xffffffffull) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "string filter: more than 2^32 dictionary keys in the range");
+	}
+	const uint64_t keys_cap = ((n_keys * 16u + 255u) & ~255ull) + 256u, heap_cap = ((heap_bytes + 255u) & ~255ull) + 256u;
+	const uint64_t flags_cap = ((n_keys + 255u) & ~255ull) + 256u, const_cap = ((f.str_len + 255u) & ~255ull) + 256u;
+	uint8_t* scratch = nullptr;
+	FLS_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&scratch), keys_cap + heap_cap + flags_cap + const_cap + (uint64_t)n_rg * 4u, s));
+	uint8_t* keys_dev = scratch;
+	uint8_t* heap_dev = keys_dev + keys_cap;
+	uint8_t* flags_dev = heap_dev + heap_cap;
+	uint8_t* const_dev = flags_dev + flags_cap;
+	uint32_t* counts_dev = reinterpret_cast<uint32_t*>(const_dev + const_cap);
+	std::vector<uint32_t> counts(n_rg);
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		counts[r] = t->rowgroups[rg_begin + r].n_tuples;
+	}
+	cudaError_t ce = cudaMemcpyAsync(counts_dev, counts.data(), (size_t)n_rg * 4u, cudaMemcpyHostToDevice, s); // pageable: staged
+	if (ce == cudaSuccess && f.str_len) {                                                                      // before the return
+		ce = cudaMemcpyAsync(const_dev, f.str_data, f.str_len, cudaMemcpyHostToDevice, s);
+	}
+	if (ce != cudaSuccess) {
+		rc = fls_set_error(FLSGPU_ERR_CUDA, cudaGetErrorString(ce));
+	}
+	if (!rc) {
+		rc = flsgpu_decode_string_dict(t, f.col, rg_begin, n_rg, keys_dev, keys_cap, heap_dev, heap_cap, reinterpret_cast<uint64_t>(heap_dev), s);
+	}
+	if (!rc) {
+		FlsStrFilterLaunch K {};
+		K.rows = keys_dev;
+		K.const_data = const_dev;
+		K.const_len = (uint32_t)f.str_len;
+		if (f.str_len) {
+			std::memcpy(&K.const_prefix, f.str_data, (size_t)std::min<uint64_t>(4, f.str_len));
+		}
+		K.op = (uint32_t)f.op;
+		K.key_flags_out = flags_dev;
+		K.n_keys = (uint32_t)n_keys;
+		ce = fls_str_launch_key_flags(K, s);
+		if (ce != cudaSuccess) {
+			rc = fls_set_error(FLSGPU_ERR_CUDA, cudaGetErrorString(ce));
+		}
+	}
+	if (!rc) {
+		FlsDeviceState* d = nullptr;
+		FlsStrLaunch L {};
+		rc = string_launch_setup(t, f.col, rg_begin, n_rg, "flsgpu_filter_mask", &d, &L);
+		if (!rc) {
+			L.key_flags = flags_dev;
+			L.n_tuples = counts_dev;
+			L.rg_keep = rg_keep_dev;
+			L.filter_mask = mask_dev;
+			L.filter_and = and_into ? 1u : 0u;
+			ce = fls_str_launch_rows(L, s);
+			if (ce != cudaSuccess) {
+				rc = fls_set_error(FLSGPU_ERR_CUDA, cudaGetErrorString(ce));
+			}
+			g_launches.fetch_add(2, std::memory_order_relaxed);
+		}
+	}
+	cudaFreeAsync(scratch, s);
+	return rc;
+}
+
 // FilterExecutor::Apply on a VARCHAR / BLOB column: the reference decodes the chunk and hands the vector to
 // ColumnSegment::FilterSelection (filter_executor.cpp:42-48).  Here slabs of row groups are decoded to string_t rows + heap
 // in stream-ordered scratch memory (string pointers = device addresses of the heap) and compared by fls_str_filter_kernel;
@@ -1304,6 +1380,13 @@ int cmp_physical(const fls_column_desc& c, uint64_t a, uint64_t b) {
 int string_filter_pass(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg_begin, uint32_t n_rg, const uint8_t* rg_keep_dev,
                        uint32_t* mask_dev, bool and_into, cudaStream_t s) {
 	const uint32_t vpr = t->header.vec_per_rowgroup;
+	bool all_dict = n_rg > 0 && env_u32("FLSGPU_STR_FILTER_DICT", 1) != 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg && all_dict; ++r) {
+		all_dict = is_dict_string_enc(t->chunk(r, f.col).encoding);
+	}
+	if (all_dict) {
+		return string_filter_pass_dict(t, f, rg_begin, n_rg, rg_keep_dev, mask_dev, and_into, s);
+	}
 	const uint64_t rows_per_rg = (uint64_t)vpr * FLS_VEC_SZ * 16u;
 	const uint64_t budget = (uint64_t)env_u32("FLSGPU_STR_FILTER_SLAB_MB", 512) << 20;
 	// slabs: as many row groups as fit the budget (rows + heap), at least one

@@ -494,6 +494,30 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrL
 	if (L.fuse_rows && FLS_ENC_IS_FSST_ROWS(enc)) {
 		return; // the heap kernel has built these rows from its staging buffer
 	}
+	if (L.key_flags) { // filter mode: code -> flag of its key -> selection mask (host: every chunk of the range is a dictionary)
+		if (!dict) {
+			return;
+		}
+		const uint32_t nt = __ldg(L.n_tuples + rg), first = vi * 1024u;
+		const bool keep = L.rg_keep == nullptr || __ldg(L.rg_keep + rg) != 0;
+		const uint32_t valid = !keep || nt <= first ? 0u : (nt - first < 1024u ? nt - first : 1024u);
+		uint32_t* tile = s_codes[warp];
+		vector_codes(ch, vi, lane, tile);
+		const uint8_t* fl = L.key_flags + (L.key_prefix[(size_t)rg * L.chunk_stride] - L.key_prefix0);
+		uint32_t mine = 0;
+#pragma unroll 4
+		for (uint32_t it = 0; it < 32u; ++it) {
+			const uint32_t row = it * 32u + lane;
+			const bool pass = row < valid && __ldg(fl + tile[row]) != 0;
+			const uint32_t word = __ballot_sync(0xffffffffu, pass);
+			if (lane == it) {
+				mine = word;
+			}
+		}
+		uint32_t* mw = L.filter_mask + (size_t)v * 32u + lane;
+		*mw = L.filter_and ? (*mw & mine) : mine;
+		return;
+	}
 	if (L.codes_only) {
 		if (dict) {
 			uint32_t* tile = s_codes[warp];
@@ -586,6 +610,17 @@ __device__ __forceinline__ int compare_string_row(const uint4& s, const uint8_t*
 	return la < lb ? -1 : la > lb ? 1 : 0;
 }
 
+__device__ __forceinline__ bool passes_cmp(uint32_t op, int c) { // flsgpu_cmp: EQ NE LT LE GT GE
+	switch (op) {
+	case 0: return c == 0;
+	case 1: return c != 0;
+	case 2: return c < 0;
+	case 3: return c <= 0;
+	case 4: return c > 0;
+	default: return c >= 0;
+	}
+}
+
 __global__ void __launch_bounds__(kWarps * 32) fls_str_filter_kernel(const FlsStrFilterLaunch L) {
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 	const uint32_t v = blockIdx.x * kWarps + warp;
@@ -604,15 +639,7 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_filter_kernel(const FlsSt
 		bool pass = false;
 		if (row < valid) {
 			const uint4 s = __ldg(rows + row);
-			const int c = compare_string_row(s, reinterpret_cast<const uint8_t*>(rows + row), L);
-			switch (L.op) { // flsgpu_cmp: EQ NE LT LE GT GE
-			case 0: pass = c == 0; break;
-			case 1: pass = c != 0; break;
-			case 2: pass = c < 0; break;
-			case 3: pass = c <= 0; break;
-			case 4: pass = c > 0; break;
-			default: pass = c >= 0; break;
-			}
+			pass = passes_cmp(L.op, compare_string_row(s, reinterpret_cast<const uint8_t*>(rows + row), L));
 		}
 		const uint32_t word = __ballot_sync(0xffffffffu, pass);
 		if (lane == it) {
@@ -623,7 +650,27 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_filter_kernel(const FlsSt
 	*mw = L.and_into ? (*mw & mine) : mine;
 }
 
+// dictionary form: the comparison once per key of the range's dictionaries (a few thousand keys instead of every row)
+__global__ void __launch_bounds__(256) fls_str_key_flags_kernel(const FlsStrFilterLaunch L) {
+	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= L.n_keys) {
+		return;
+	}
+	const uint4* rows = static_cast<const uint4*>(L.rows);
+	const uint4 s = __ldg(rows + k);
+	const int c = compare_string_row(s, reinterpret_cast<const uint8_t*>(rows + k), L);
+	L.key_flags_out[k] = passes_cmp(L.op, c) ? 1 : 0;
+}
+
 } // namespace
+
+cudaError_t fls_str_launch_key_flags(FlsStrFilterLaunch L, cudaStream_t stream) {
+	if (L.n_keys == 0) {
+		return cudaSuccess;
+	}
+	fls_str_key_flags_kernel<<<(L.n_keys + 255u) / 256u, 256, 0, stream>>>(L);
+	return cudaGetLastError();
+}
 
 cudaError_t fls_str_launch_filter(FlsStrFilterLaunch L, cudaStream_t stream) {
 	const uint32_t n_vec = L.n_rg * L.vec_per_rg;

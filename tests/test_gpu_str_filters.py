@@ -11,11 +11,13 @@ from str_filter_cases import COLUMNS, filter_sets, python_mask, table
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("n,vpr,slab_mb", [(3000, 2, None), (20000, 8, None), (70000, 4, "1")])
-def test_string_masks_match_oracle(n, vpr, slab_mb, monkeypatch):
+@pytest.mark.parametrize("n,vpr,slab_mb,dict_path", [(3000, 2, None, "1"), (20000, 8, None, "1"), (70000, 4, "1", "0"), (20000, 8, None, "0")])
+def test_string_masks_match_oracle(n, vpr, slab_mb, dict_path, monkeypatch):
     import torch
     if slab_mb:
         monkeypatch.setenv("FLSGPU_STR_FILTER_SLAB_MB", slab_mb)  # many slabs per pass
+    # dictionary-encoded ranges: "1" = comparison per key + flag lookup per row, "0" = the generic decode-and-compare path
+    monkeypatch.setenv("FLSGPU_STR_FILTER_DICT", dict_path)
     specs, data = table(n)
     img = flsgpu.write_table(specs, data, vec_per_rowgroup=vpr)
     names = [s[0] for s in specs]

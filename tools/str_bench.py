@@ -111,9 +111,26 @@ def main():
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / args.iters
         raw = int(off[-1])
+        # pushed-down string filter (flsgpu_filter_mask on the column): WHERE s >= / = constant -> selection mask
+        const, op = ((b"furiously regular", "GE") if col is comment else (bytes(data[int(off[1]):int(off[2])]), "EQ"))
+        n_words = t.n_rowgroups * t.vec_per_rowgroup * 32
+        mask = torch.empty(n_words, dtype=torch.int32, device="cuda")
+        filt = [(0, op, const)]
+        for _ in range(3):
+            t.filter_mask(filt, mask.data_ptr(), n_words * 4, stream=stream)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(args.iters):
+            t.filter_mask(filt, mask.data_ptr(), n_words * 4, stream=stream)
+        e1.record()
+        torch.cuda.synchronize()
+        fms = e0.elapsed_time(e1) / args.iters
+        selected = int(np.unpackbits(mask.cpu().numpy().view(np.uint8)).sum())
         print(json.dumps({"case": name, "encoding": enc, "form": form, "rows": n, "ms": round(ms, 4), "rows_per_s": round(n / ms * 1e3, 1),
                           "raw_string_MB": round(raw / 1e6, 1), "compressed_MB": round(comp / 1e6, 1),
-                          "string_GBps": round(raw / ms / 1e6, 1), "alg_GBps": round((comp + written) / ms / 1e6, 1)}), flush=True)
+                          "string_GBps": round(raw / ms / 1e6, 1), "alg_GBps": round((comp + written) / ms / 1e6, 1),
+                          "filter": {"op": op, "constant": const.decode(), "ms": round(fms, 4), "rows_per_s": round(n / fms * 1e3, 1),
+                                     "selected": selected}}), flush=True)
         t.close()
         w.close()
         del out, heap
