@@ -258,7 +258,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": gbps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     t.close()
     w.close()
 
@@ -528,7 +528,7 @@ def run_gpu(args, rank, world, local_rank):
                                                          "ms_per_gpu": round(agg_e2e_s * 1e3, 2),
                                                          "decoded_equivalent_GBps_per_gpu": round(agg_e2e_bytes / agg_e2e_s / 1e9, 1)}},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     for p in host_outs:
         flsgpu.host_free(p)
     t.close()
@@ -537,7 +537,31 @@ def run_gpu(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL's version banner, whatever the box's
+    NCCL_DEBUG says), so the real stdout is kept on a private descriptor for the JSON line and fd 1 is pointed at stderr."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        while data:
+            data = data[os.write(_JSON_FD, data):]
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
