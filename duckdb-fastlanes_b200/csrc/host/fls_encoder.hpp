@@ -11,6 +11,7 @@ namespace flshost {
 struct EncodedChunk {
 	fls_chunk_desc desc {};       // offset filled by the writer
 	std::vector<uint8_t> bytes;   // chunk image (segments 128-aligned inside)
+	int equal_to = -1;            // >= 0: EXP_EQUAL, the values are those of this earlier column of the same row group (no bytes)
 };
 
 struct ColumnType {

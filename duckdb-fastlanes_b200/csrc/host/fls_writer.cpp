@@ -11,6 +11,7 @@
 #include <cstring>
 #include <memory>
 #include <mutex>
+#include <cstdlib>
 #include <string>
 #include <thread>
 #include <vector>
@@ -31,6 +32,7 @@ struct flsgpu_writer {
 	uint64_t n_tuples = 0;
 	bool finished = false;
 	std::vector<uint8_t> image;
+	bool detect_equal = true; // FLSGPU_WRITER_EQUAL=0: never write EXP_EQUAL chunks
 };
 
 // Where the rows of one column start: fixed-width values, or (offsets, bytes) of a string column.
@@ -71,6 +73,23 @@ static int encode_rowgroups(flsgpu_writer* w, const std::vector<ColSrc>& col_ptr
 			const size_t esz = w->types[c].phys_bits / 8;
 			auto ch = std::make_unique<EncodedChunk>();
 			const char* err = "";
+			// EXP_EQUAL (FastLanes multi-column compression; the reference detects its use in HasMccEncoding, fls_reader.cpp:43-82):
+			// a numeric column whose row group repeats an earlier column of the same physical type is stored as a reference
+			if (w->detect_equal && !is_string(w->types[c]) && w->force[c] < 0) {
+				const uint8_t* mine = col_ptrs[c].data + r * w->rg_tuples * esz;
+				for (uint64_t a = 0; a < c; ++a) {
+					const ColumnType &ta = w->types[a], &tc = w->types[c];
+					if (ta.phys_bits == tc.phys_bits && ta.is_signed == tc.is_signed && ta.is_float == tc.is_float &&
+					    std::memcmp(col_ptrs[a].data + r * w->rg_tuples * esz, mine, (size_t)nt * esz) == 0) {
+						ch->equal_to = (int)a;
+						break;
+					}
+				}
+				if (ch->equal_to >= 0) {
+					w->chunks[first_chunk + task] = std::move(ch);
+					continue;
+				}
+			}
 			const bool ok = is_string(w->types[c])
 			                    ? encode_string_chunk(col_ptrs[c].offsets + r * w->rg_tuples, col_ptrs[c].data, nt, w->force[c], *ch, &err)
 			                    : encode_chunk(w->types[c], col_ptrs[c].data + r * w->rg_tuples * esz, nt, w->force[c], *ch, &err);
@@ -113,6 +132,9 @@ int flsgpu_writer_create(uint32_t n_columns, const flsgpu_column_spec* cols, uin
 	}
 	auto w = std::make_unique<flsgpu_writer>();
 	w->vec_per_rg = vec_per_rowgroup ? vec_per_rowgroup : FLS_DEFAULT_VEC_PER_RG;
+	if (const char* eq = std::getenv("FLSGPU_WRITER_EQUAL")) {
+		w->detect_equal = std::atoi(eq) != 0;
+	}
 	w->rg_tuples = (uint64_t)w->vec_per_rg * FLS_VEC_SZ;
 	for (uint32_t i = 0; i < n_columns; ++i) {
 		const ColumnType t = column_type_of(cols[i].data_type, cols[i].decimal_precision);
@@ -260,9 +282,21 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 	}
 	// lay out: header | chunks (128-aligned) | footer
 	uint64_t off = FLS_ALIGN; // header occupies the first 128 bytes
+	const size_t n_cols_all = w->cols.size();
 	for (auto& ch : w->chunks) {
-		ch->desc.offset = off;
-		off += ch->desc.size;
+		if (ch->equal_to < 0) {
+			ch->desc.offset = off;
+			off += ch->desc.size;
+		}
+	}
+	for (size_t i = 0; i < w->chunks.size(); ++i) { // EXP_EQUAL chunks: the descriptor of the column they repeat (never itself one)
+		EncodedChunk& ch = *w->chunks[i];
+		if (ch.equal_to >= 0) {
+			ch.desc = w->chunks[i - i % n_cols_all + (size_t)ch.equal_to]->desc;
+			ch.desc.is_equal = 1;
+			ch.desc.equal_col[0] = (uint8_t)(ch.equal_to & 0xff);
+			ch.desc.equal_col[1] = (uint8_t)((ch.equal_to >> 8) & 0xff);
+		}
 	}
 	const uint64_t footer_off = off;
 	const uint64_t footer_size = w->cols.size() * sizeof(fls_column_desc) + w->rgs.size() * sizeof(fls_rowgroup_desc) +

@@ -322,6 +322,12 @@ int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t 
 			}
 			d->chunk_resident[i] = 1;
 			const fls_chunk_desc& ch = t->chunks[i];
+			if (ch.is_equal) { // EXP_EQUAL: the bytes are those of another column's chunk; uploaded once
+				const uint64_t src = (uint64_t)r * n_cols + (ch.equal_col[0] | ((uint32_t)ch.equal_col[1] << 8));
+				if (src < i && (d->chunk_resident[src] || want[src - (uint64_t)r * n_cols])) {
+					continue; // resident already, or uploaded earlier in this very pass (source columns come first)
+				}
+			}
 			if (run_end > run_begin && ch.offset >= run_end && ch.offset - run_end <= kMergeGap) {
 				run_end = ch.offset + ch.size;
 			} else {

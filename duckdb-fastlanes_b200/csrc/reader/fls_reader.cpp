@@ -144,7 +144,9 @@ idx_t FastLanesReader::MaxThreads() const {
 }
 
 // FastLanesReader::BuildReaderProjectionPlan (fls_reader.cpp:560-613).  The multi-column-compression fallback
-// (HasMccEncoding, :43-82) has nothing to do here: this container has no cross-column encodings.
+// (HasMccEncoding, :43-82: the reference decodes EVERY column of a row group when a projected one is EXP_EQUAL / borrows a
+// dictionary) is not needed: an EXP_EQUAL chunk of this container carries a copy of its source chunk's descriptor (same
+// offset and segments, fls_chunk_desc.is_equal), so it stages and decodes like any other chunk, projected alone or not.
 FastLanesReaderProjectionPlan FastLanesReader::BuildReaderProjectionPlan() const {
 	FastLanesReaderProjectionPlan plan;
 	plan.output_to_reader_idx.assign(column_ids.size(), -1);

@@ -109,8 +109,13 @@ class ChunkDesc(C.Structure):
     _fields_ = [("offset", C.c_uint64), ("size", C.c_uint64), ("seg_off", C.c_uint64 * 4), ("seg_size", C.c_uint64 * 4),
                 ("const_val", C.c_uint64), ("min_val", C.c_uint64), ("max_val", C.c_uint64), ("n_vec", C.c_uint32),
                 ("n_tuples", C.c_uint32), ("aux_count", C.c_uint32), ("encoding", C.c_uint8), ("phys_bits", C.c_uint8),
-                ("idx_bits", C.c_uint8), ("max_width", C.c_uint8), ("has_stats", C.c_uint8), ("reserved8", C.c_uint8 * 3),
+                ("idx_bits", C.c_uint8), ("max_width", C.c_uint8), ("has_stats", C.c_uint8), ("is_equal", C.c_uint8), ("equal_col_bytes", C.c_uint8 * 2),
                 ("rd_dict", C.c_uint16 * 8), ("max_blob_bytes", C.c_uint32)]
+
+    @property
+    def equal_col(self):
+        """EXP_EQUAL chunks (is_equal): the column of the same row group whose values (and bytes) this chunk shares."""
+        return self.equal_col_bytes[0] | (self.equal_col_bytes[1] << 8)
 
 
 class TableInfo(C.Structure):

@@ -137,7 +137,10 @@ typedef struct fls_chunk_desc { /* 144 bytes */
 	uint8_t idx_bits;    /* DICT: lane width of the codes (8/16/32); RLE: 16 */
 	uint8_t max_width;   /* max fls_vec_meta.width(+width2) over the chunk: sizes the shared-memory stage */
 	uint8_t has_stats;
-	uint8_t reserved8[3];
+	uint8_t is_equal;     /* 1: EXP_EQUAL (multi-column compression, reference fls_reader.cpp:43-82): the chunk's values are those of
+	                         column equal_col's chunk of the same row group.  The descriptor is a copy of that chunk's (same offset
+	                         and segments: the bytes exist once), so every decoder reads it like any other chunk */
+	uint8_t equal_col[2]; /* little-endian u16 */
 	uint16_t rd_dict[8]; /* ALP_RD: left-part dictionary (alprd_constants.hpp MAX_DICTIONARY_SIZE = 8) */
 	uint32_t max_blob_bytes; /* largest per-vector blob of the chunk (packed data + exception tail): sizes the TMA slots */
 } fls_chunk_desc;
