@@ -500,6 +500,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 	AggPartial part;
 	(void)tile;
 
+	// Materialising launches of one stream are independent of each other (inputs: staged compressed bytes; outputs: the
+	// caller's column buffers), so the next one may fill the SMs as this one's CTAs retire instead of waiting for the
+	// slowest CTA and a launch latency: the tail of column k overlaps the ramp of column k+1.
+	if (!AGG && L.pdl) {
+		griddep_launch_dependents();
+	}
+
 	if (lane == 0) {
 		for (uint32_t s = 0; s < n_slots; ++s) {
 			mbar_init(bars + s, 1);
@@ -632,6 +639,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 		if (L.mask_mode == 0u || L.mask_mode == 3u) {
 			part.flush(L.agg, lane, L.agg_float);
 		}
+	} else if (L.pdl) {
+		// keep completion transitive: this grid must not be seen complete before the grid it was allowed to overtake
+		// (whatever follows in the stream waits for THIS grid only); at this point the predecessor has all but finished
+		griddep_wait();
 	}
 }
 

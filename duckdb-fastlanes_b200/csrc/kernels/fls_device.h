@@ -43,6 +43,8 @@ struct FlsLaunch {
 	uint32_t run_shift;        // log2 of the run of consecutive vectors a warp takes (0..5)
 	uint32_t idx_bits;         // DICT launches: only chunks whose codes sit in idx_bits-wide lanes (0: any)
 	uint32_t prefetch;         // 1: request a batch's 32 blobs into L2 at batch start (materialising launches)
+	uint32_t pdl;              // 1: materialising launch issued with programmatic stream serialization: let the next decode
+	                           //    launch of the stream start as this one's CTAs retire (griddepcontrol), see launch_family
 	void* out;
 	// fused aggregate launches (flsgpu_aggregate_column): out is unused, partials are folded into *agg
 	flsgpu_agg_acc* agg;

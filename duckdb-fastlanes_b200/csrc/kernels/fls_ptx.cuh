@@ -12,6 +12,16 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 	return (uint32_t)__cvta_generic_to_shared(p);
 }
 
+// Programmatic dependent launch (sm_90+): launch_dependents lets the next kernel of the stream (if it was launched with
+// programmatic stream serialization) begin once every CTA of this grid has executed it or exited; wait blocks until the
+// preceding grid has completed and its memory is visible.  Both are no-ops for ordinary launches.
+__device__ __forceinline__ void griddep_launch_dependents() {
+	asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void griddep_wait() {
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }

@@ -41,6 +41,7 @@ uint32_t env_u32(const char* name, uint32_t def) {
 }
 const uint32_t g_run_shift = std::min(5u, env_u32("FLSGPU_RUN_SHIFT", 0));
 const uint32_t g_prefetch = env_u32("FLSGPU_PREFETCH", 1);
+const uint32_t g_pdl = env_u32("FLSGPU_PDL", 1);                // programmatic dependent launch between materialising decode launches
 const uint32_t g_force_slots = env_u32("FLSGPU_NSLOTS", 0);     // experiments: pipeline depth override
 const uint32_t g_max_ctas = env_u32("FLSGPU_MAX_CTAS", 0);      // experiments: cap on resident CTAs per SM
 const uint32_t g_budget_kb = env_u32("FLSGPU_WARP_KB", 14);     // shared-memory budget per warp (KiB) the depth is sized for
@@ -440,8 +441,25 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 		occ = std::min<int>(occ, (int)g_max_ctas);
 	}
 	const uint32_t grid = (uint32_t)std::min<uint64_t>(want, (uint64_t)occ * g_n_sms);
+	// materialising launches (nothing but staged bytes read, nothing but the caller's column written): programmatic
+	// stream serialization, the kernel releases its successor at once and waits for its predecessor before it exits
+	L.pdl = (g_pdl && L.agg == nullptr && L.mask_mode == 0u) ? 1u : 0u;
 	void* args[] = {&L};
-	FLS_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(wpc * 32), args, smem, stream));
+	if (L.pdl) {
+		cudaLaunchConfig_t cfg {};
+		cfg.gridDim = dim3(grid);
+		cfg.blockDim = dim3(wpc * 32);
+		cfg.dynamicSmemBytes = smem;
+		cfg.stream = stream;
+		cudaLaunchAttribute attr {};
+		attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		attr.val.programmaticStreamSerializationAllowed = 1;
+		cfg.attrs = &attr;
+		cfg.numAttrs = 1;
+		FLS_CUDA(cudaLaunchKernelExC(&cfg, fn, args));
+	} else {
+		FLS_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(wpc * 32), args, smem, stream));
+	}
 	g_launches.fetch_add(1, std::memory_order_relaxed);
 	return FLSGPU_OK;
 }
