@@ -110,7 +110,10 @@ typedef enum flsgpu_out_type {
 /* Decode column `col` of row groups [rg_begin, rg_begin+n_rg) in ONE launch into out_dev (device memory,
  * 16-byte aligned).  Row group r's vector v lands at element ((r-rg_begin)*vec_per_rowgroup + v)*1024: whole
  * vectors are written, the caller exposes only n_tuples of each row group (fls_reader.cpp:429-431).
- * out_capacity_bytes must cover n_rg*vec_per_rowgroup*1024 elements. Asynchronous on `stream`. */
+ * out_capacity_bytes must cover n_rg*vec_per_rowgroup*1024 elements. Asynchronous on `stream`.
+ * Consecutive decode launches of one stream are chained by programmatic dependent launch (they may overlap each other:
+ * do not aim two back-to-back decodes at overlapping output ranges); anything else enqueued on the stream afterwards —
+ * copies, the caller's kernels, events — sees every earlier decode complete, as usual.  FLSGPU_PDL=0 turns the chaining off. */
 int flsgpu_decode_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, int32_t out_type,
                          void* out_dev, uint64_t out_capacity_bytes, void* cuda_stream);
 
