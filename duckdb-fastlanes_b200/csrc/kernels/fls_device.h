@@ -87,6 +87,7 @@ struct FlsStrLaunch {
 	const uint8_t* rg_keep;      // per row group: 0 = pruned (selects nothing), or nullptr
 	uint32_t* filter_mask;       // [n_rg * vec_per_rg * 32] words
 	uint32_t filter_and;         // 0: mask = flags; 1: mask &= flags
+	uint32_t pdl;                // 1: launch chaining (programmatic dependent launch) is on, see flsgpu_kernels_str.cu
 };
 
 // Launch parameters of the string filter kernel (flsgpu_kernels_str.cu): a constant comparison over the decoded string_t

@@ -1122,6 +1122,7 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	L->key_prefix0 = d->key_prefix[i0];
 	L->dict_only = 0;
 	L->fuse_rows = 0;
+	L->pdl = g_pdl ? 1u : 0u;
 	// FSST tiling: size a warp tile (32 * lane_strings strings) so that its codes + decoded bytes take <= 8 KiB of shared
 	// memory at twice the column's average string length: the decode is latency bound (dependent shared-memory lookups per
 	// code), so resident warps matter more than long per-lane runs (measured, 20 M l_comment-like strings: 26 KiB/warp

@@ -267,7 +267,7 @@ __device__ __forceinline__ void tile_rows(const uint8_t* hp, uint64_t haddr, con
 //      straight from the buffer, so the heap is written once and never read back.
 // Decoding lane-to-global directly (the fallback for tiles that do not fit the buffers) costs 2.8x the DRAM reads and 1.6x
 // the writes: 32 lanes x 8-byte stores hit 32 different sectors, partial sector writes make L2 fetch the rest.
-__global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrLaunch L) {
+__device__ __forceinline__ void str_heap_body(const FlsStrLaunch& L) {
 	__shared__ uint4 s_tab[256]; // FSST decoder table: {symbol lo, symbol hi, length in bits, 0}
 	__shared__ __align__(8) uint64_t s_bar[2 * kWarps]; // one per (warp, staging buffer)
 	extern __shared__ __align__(128) uint8_t s_dyn[];
@@ -477,7 +477,7 @@ __device__ __forceinline__ void vector_codes(const FlsChunkDev* ch, uint32_t vi,
 }
 
 // one warp per vector: 1024 string_t (flat form), or the u32 codes (selection vector) when L.codes_only
-__global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrLaunch L) {
+__device__ __forceinline__ void str_rows_body(const FlsStrLaunch& L) {
 	__shared__ uint32_t s_codes[kWarps][1024];
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
 	const uint32_t v = blockIdx.x * kWarps + warp;
@@ -569,7 +569,7 @@ __global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrL
 
 // dictionary form: string_t of every key of the dictionary chunks of the range (dictionary_kernel.hpp:60-78,
 // fsst_dict_kernel.hpp:54-80); chunk rg's keys start at key_prefix[rg] - key_prefix0.  grid: n_rg * groups_per_rg CTAs.
-__global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L) {
+__device__ __forceinline__ void str_keys_body(const FlsStrLaunch& L) {
 	const uint32_t rg = blockIdx.x / L.groups_per_rg, g = blockIdx.x - rg * L.groups_per_rg;
 	const FlsChunkDev* ch = L.chunks + (size_t)rg * L.chunk_stride;
 	const uint32_t enc = ch->encoding;
@@ -584,6 +584,37 @@ __global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L)
 		const uint32_t start = k ? __ldg(ends + k - 1) : 0u, end = __ldg(ends + k);
 		out[k] = make_string_t<false>(L.heap + hoff, L.heap_base_addr + hoff, start, end - start);
 	}
+}
+
+// The kernels proper.  With L.pdl (launch chaining, see launch_family in flsgpu_device.cu) a grid releases its successor at
+// once and waits for its predecessor before it exits: the heap kernel reads nothing but staged bytes, so it may overlap the
+// decode launch in front of it; the codes (selection vector) launch is independent of the heap / keys launches of the same
+// dictionary decode and overlaps them; the keys launch needs the heap complete and is an ordinary launch.
+__global__ void __launch_bounds__(kWarps * 32) fls_str_heap_kernel(const FlsStrLaunch L) {
+	if (L.pdl) {
+		griddep_launch_dependents();
+	}
+	str_heap_body(L);
+	if (L.pdl) {
+		griddep_wait();
+	}
+}
+
+__global__ void __launch_bounds__(kWarps * 32) fls_str_rows_kernel(const FlsStrLaunch L) {
+	if (L.pdl) {
+		griddep_launch_dependents();
+	}
+	str_rows_body(L);
+	if (L.pdl) {
+		griddep_wait();
+	}
+}
+
+__global__ void __launch_bounds__(256) fls_str_keys_kernel(const FlsStrLaunch L) {
+	if (L.pdl) {
+		griddep_launch_dependents();
+	}
+	str_keys_body(L);
 }
 
 // FilterExecutor::Apply on a string column (reference filter_executor.cpp:19-60 -> ColumnSegment::FilterSelection with a
@@ -662,6 +693,22 @@ __global__ void __launch_bounds__(256) fls_str_key_flags_kernel(const FlsStrFilt
 	L.key_flags_out[k] = passes_cmp(L.op, c) ? 1 : 0;
 }
 
+// <<<>>> with programmatic stream serialization when `chained` (the grid may start while its predecessor still runs)
+cudaError_t launch_chained(void (*kernel)(const FlsStrLaunch), const FlsStrLaunch& L, uint32_t grid, uint32_t block, uint32_t smem,
+                           cudaStream_t stream, bool chained) {
+	cudaLaunchConfig_t cfg {};
+	cfg.gridDim = dim3(grid);
+	cfg.blockDim = dim3(block);
+	cfg.dynamicSmemBytes = smem;
+	cfg.stream = stream;
+	cudaLaunchAttribute attr {};
+	attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr.val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = &attr;
+	cfg.numAttrs = chained ? 1 : 0;
+	return cudaLaunchKernelEx(&cfg, kernel, L);
+}
+
 } // namespace
 
 cudaError_t fls_str_launch_key_flags(FlsStrFilterLaunch L, cudaStream_t stream) {
@@ -697,14 +744,14 @@ cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream) {
 		}
 		attr_set = true;
 	}
-	fls_str_heap_kernel<<<L.n_rg * L.groups_per_rg, kWarps * 32, smem, stream>>>(L);
-	return cudaGetLastError();
+	return launch_chained(fls_str_heap_kernel, L, L.n_rg * L.groups_per_rg, kWarps * 32, smem, stream, L.pdl != 0);
 }
 
 cudaError_t fls_str_launch_rows(FlsStrLaunch L, cudaStream_t stream) {
 	const uint32_t n_vec = L.n_rg * L.vec_per_rg;
-	fls_str_rows_kernel<<<(n_vec + kWarps - 1) / kWarps, kWarps * 32, 0, stream>>>(L);
-	return cudaGetLastError();
+	// only the selection-vector form is independent of the launches in front of it (flat rows read the heap, filter mode the flags)
+	return launch_chained(fls_str_rows_kernel, L, (n_vec + kWarps - 1) / kWarps, kWarps * 32, 0, stream,
+	                      L.pdl != 0 && L.codes_only != 0 && L.key_flags == nullptr);
 }
 
 cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t max_keys_per_chunk, cudaStream_t stream) {
