@@ -167,9 +167,14 @@ int fls_table_parse(flsgpu_table* t) {
 	if (h.n_columns == 0 || h.vec_per_rowgroup == 0) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "container declares zero columns or zero vectors per row group");
 	}
+	// every count is bounded by the file size before it enters a product (a hostile header must not wrap the arithmetic)
+	const uint64_t max_chunks = t->size / sizeof(fls_chunk_desc);
+	if (h.n_columns > max_chunks || h.n_rowgroups > max_chunks || (h.n_rowgroups && h.n_columns > max_chunks / h.n_rowgroups)) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "footer out of bounds or of unexpected size");
+	}
 	const uint64_t need = (uint64_t)h.n_columns * sizeof(fls_column_desc) + (uint64_t)h.n_rowgroups * sizeof(fls_rowgroup_desc) +
 	                      (uint64_t)h.n_rowgroups * h.n_columns * sizeof(fls_chunk_desc);
-	if (h.footer_offset > t->size || h.footer_size != need || h.footer_offset + need > t->size || (h.footer_offset % 8)) {
+	if (h.footer_offset > t->size || h.footer_size != need || need > t->size - h.footer_offset || (h.footer_offset % 8)) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "footer out of bounds or of unexpected size");
 	}
 	const uint8_t* f = t->bytes + h.footer_offset;
@@ -179,6 +184,13 @@ int fls_table_parse(flsgpu_table* t) {
 	f += (uint64_t)h.n_rowgroups * sizeof(fls_rowgroup_desc);
 	t->chunks = reinterpret_cast<const fls_chunk_desc*>(f);
 
+	for (uint32_t c = 0; c < h.n_columns; ++c) {
+		const unsigned pb = t->columns[c].phys_bits;
+		if (pb != 8 && pb != 16 && pb != 32 && pb != 64 && pb != 128) {
+			std::snprintf(msg, sizeof(msg), "column %u: physical width must be 8, 16, 32, 64 or 128 (strings) bits", c);
+			return fls_set_error(FLSGPU_ERR_INVALID, msg);
+		}
+	}
 	uint64_t tuples = 0;
 	t->n_vectors = 0;
 	for (uint32_t r = 0; r < h.n_rowgroups; ++r) {
@@ -203,15 +215,31 @@ int fls_table_parse(flsgpu_table* t) {
 				std::snprintf(msg + ml, sizeof(msg) - ml, "%s", what);
 				return fls_set_error(FLSGPU_ERR_INVALID, msg);
 			};
-			if (ch.offset % FLS_ALIGN || ch.offset + ch.size > h.footer_offset || ch.offset + ch.size < ch.offset) {
+			if (ch.offset % FLS_ALIGN || ch.offset > h.footer_offset || ch.size > h.footer_offset - ch.offset) {
 				return fail("extent outside the data region");
 			}
 			if (ch.encoding >= FLS_ENC_COUNT || ch.phys_bits != col.phys_bits || ch.n_vec != rg.n_vec || ch.n_tuples != rg.n_tuples) {
 				return fail("descriptor disagrees with the row group / column");
 			}
 			for (int s = 0; s < FLS_SEG_COUNT; ++s) {
-				if (ch.seg_off[s] % FLS_ALIGN || ch.seg_off[s] + ch.seg_size[s] > ch.size) {
+				if (ch.seg_off[s] % FLS_ALIGN || ch.seg_off[s] > ch.size || ch.seg_size[s] > ch.size - ch.seg_off[s]) {
 					return fail("segment outside the chunk");
+				}
+			}
+			if (ch.is_equal) { // EXP_EQUAL: a copy of an EARLIER column's descriptor of the same row group, never a chain
+				const uint32_t src = ch.equal_col[0] | ((uint32_t)ch.equal_col[1] << 8);
+				if (src >= c || col.phys_bits == 128) {
+					return fail("EXP_EQUAL must refer to an earlier numeric column");
+				}
+				fls_chunk_desc want = t->chunk(r, src);
+				if (want.is_equal || t->columns[src].phys_bits != col.phys_bits) {
+					return fail("EXP_EQUAL source is itself a reference or has another physical width");
+				}
+				want.is_equal = 1;
+				want.equal_col[0] = ch.equal_col[0];
+				want.equal_col[1] = ch.equal_col[1];
+				if (std::memcmp(&want, &ch, sizeof(fls_chunk_desc)) != 0) {
+					return fail("EXP_EQUAL descriptor differs from its source chunk's");
 				}
 			}
 			if (ch.seg_size[FLS_SEG_META] != (uint64_t)ch.n_vec * sizeof(fls_vec_meta)) {
@@ -357,8 +385,28 @@ int flsgpu_table_open(const char* path, flsgpu_table** out) {
 	if (sz < 0 || n != (size_t)sz) {
 		return fls_set_error(FLSGPU_ERR_IO, (std::string("short read: ") + path).c_str());
 	}
+	// footer written beside the data (COPY ... (FORMAT fls, inline_footer false), reference fls_writer.cpp:229-230): append it
+	if (t->owned.size() >= sizeof(fls_file_header)) {
+		fls_file_header h;
+		std::memcpy(&h, t->owned.data(), sizeof(h));
+		if (std::memcmp(h.magic, FLS_MAGIC, 8) == 0 && h.reserved[0] == 1 && h.footer_offset == t->owned.size() &&
+		    h.footer_size <= (1ull << 40)) {
+			const std::string fpath = std::string(path) + ".footer";
+			FILE* ff = std::fopen(fpath.c_str(), "rb");
+			if (!ff) {
+				return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open footer file: ") + fpath).c_str());
+			}
+			const size_t at = t->owned.size();
+			t->owned.resize(at + (size_t)h.footer_size);
+			const size_t k = std::fread(t->owned.data() + at, 1, (size_t)h.footer_size, ff);
+			std::fclose(ff);
+			if (k != (size_t)h.footer_size) {
+				return fls_set_error(FLSGPU_ERR_IO, (std::string("short read: ") + fpath).c_str());
+			}
+		}
+	}
 	t->bytes = t->owned.data();
-	t->size = (uint64_t)sz;
+	t->size = t->owned.size();
 	const int rc = fls_table_parse(t.get());
 	if (rc) {
 		return rc;

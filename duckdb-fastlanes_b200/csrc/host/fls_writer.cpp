@@ -33,6 +33,15 @@ struct flsgpu_writer {
 	bool finished = false;
 	std::vector<uint8_t> image;
 	bool detect_equal = true; // FLSGPU_WRITER_EQUAL=0: never write EXP_EQUAL chunks
+	bool inline_footer = true; // WithInlinedFooter (fls_writer.cpp:278): false -> flsgpu_writer_save writes <path>.footer beside the data
+	std::mutex flush_mu;       // flsgpu_writer_flush_rowgroup may be called from any thread
+};
+
+// RowGroupWriter of the reference (fls_writer.cpp:306-330): one row group encoded off to the side by PrepareBatch, appended
+// to the file by FlushBatch.
+struct flsgpu_encoded_rowgroup {
+	uint32_t n_tuples = 0;
+	std::vector<std::unique_ptr<EncodedChunk>> chunks; // one per column
 };
 
 // Where the rows of one column start: fixed-width values, or (offsets, bytes) of a string column.
@@ -43,6 +52,34 @@ struct ColSrc {
 
 static bool is_string(const ColumnType& t) {
 	return t.phys_bits == 128;
+}
+
+// One column chunk: rows [first_row, first_row + nt) of column c.  EXP_EQUAL (FastLanes multi-column compression; the reference
+// detects its use in HasMccEncoding, fls_reader.cpp:43-82): a numeric column whose row group repeats an earlier column of the
+// same physical type is stored as a reference.
+static std::unique_ptr<EncodedChunk> encode_one(const flsgpu_writer* w, const std::vector<ColSrc>& col_ptrs, uint64_t first_row, uint32_t nt,
+                                                size_t c, std::string* err_out) {
+	const size_t esz = w->types[c].phys_bits / 8;
+	auto ch = std::make_unique<EncodedChunk>();
+	const char* err = "";
+	if (w->detect_equal && !is_string(w->types[c]) && w->force[c] < 0) {
+		const uint8_t* mine = col_ptrs[c].data + first_row * esz;
+		for (uint64_t a = 0; a < c; ++a) {
+			const ColumnType &ta = w->types[a], &tc = w->types[c];
+			if (ta.phys_bits == tc.phys_bits && ta.is_signed == tc.is_signed && ta.is_float == tc.is_float &&
+			    std::memcmp(col_ptrs[a].data + first_row * esz, mine, (size_t)nt * esz) == 0) {
+				ch->equal_to = (int)a;
+				return ch;
+			}
+		}
+	}
+	const bool ok = is_string(w->types[c]) ? encode_string_chunk(col_ptrs[c].offsets + first_row, col_ptrs[c].data, nt, w->force[c], *ch, &err)
+	                                       : encode_chunk(w->types[c], col_ptrs[c].data + first_row * esz, nt, w->force[c], *ch, &err);
+	if (!ok) {
+		*err_out = std::string("column '") + w->cols[c].name + "': " + err;
+		return nullptr;
+	}
+	return ch;
 }
 
 static int encode_rowgroups(flsgpu_writer* w, const std::vector<ColSrc>& col_ptrs, uint64_t n_rows, int n_threads) {
@@ -70,33 +107,12 @@ static int encode_rowgroups(flsgpu_writer* w, const std::vector<ColSrc>& col_ptr
 			}
 			const uint64_t r = task / n_cols, c = task % n_cols;
 			const uint32_t nt = (uint32_t)std::min<uint64_t>(w->rg_tuples, n_rows - r * w->rg_tuples);
-			const size_t esz = w->types[c].phys_bits / 8;
-			auto ch = std::make_unique<EncodedChunk>();
-			const char* err = "";
-			// EXP_EQUAL (FastLanes multi-column compression; the reference detects its use in HasMccEncoding, fls_reader.cpp:43-82):
-			// a numeric column whose row group repeats an earlier column of the same physical type is stored as a reference
-			if (w->detect_equal && !is_string(w->types[c]) && w->force[c] < 0) {
-				const uint8_t* mine = col_ptrs[c].data + r * w->rg_tuples * esz;
-				for (uint64_t a = 0; a < c; ++a) {
-					const ColumnType &ta = w->types[a], &tc = w->types[c];
-					if (ta.phys_bits == tc.phys_bits && ta.is_signed == tc.is_signed && ta.is_float == tc.is_float &&
-					    std::memcmp(col_ptrs[a].data + r * w->rg_tuples * esz, mine, (size_t)nt * esz) == 0) {
-						ch->equal_to = (int)a;
-						break;
-					}
-				}
-				if (ch->equal_to >= 0) {
-					w->chunks[first_chunk + task] = std::move(ch);
-					continue;
-				}
-			}
-			const bool ok = is_string(w->types[c])
-			                    ? encode_string_chunk(col_ptrs[c].offsets + r * w->rg_tuples, col_ptrs[c].data, nt, w->force[c], *ch, &err)
-			                    : encode_chunk(w->types[c], col_ptrs[c].data + r * w->rg_tuples * esz, nt, w->force[c], *ch, &err);
-			if (!ok) {
+			std::string err;
+			auto ch = encode_one(w, col_ptrs, r * w->rg_tuples, nt, (size_t)c, &err);
+			if (!ch) {
 				std::lock_guard<std::mutex> g(*mu);
 				failed = true;
-				fail_msg = std::string("column '") + w->cols[c].name + "': " + err;
+				fail_msg = err;
 				return;
 			}
 			w->chunks[first_chunk + task] = std::move(ch);
@@ -257,6 +273,88 @@ int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t 
 	return FLSGPU_OK;
 }
 
+// ---- row groups prepared out of order, flushed in order (PrepareBatch / FlushBatch, reference fls_writer.cpp:306-330) ----
+int flsgpu_writer_encode_rowgroup(const flsgpu_writer* w, const void* const* columns, uint64_t n_tuples, flsgpu_encoded_rowgroup** out) {
+	if (!w || !columns || !out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_encode_rowgroup: null argument");
+	}
+	if (n_tuples == 0 || n_tuples > w->rg_tuples) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_encode_rowgroup: a row group holds 1..row_group_size tuples");
+	}
+	const size_t n_cols = w->cols.size();
+	std::vector<ColSrc> ptrs(n_cols);
+	for (size_t c = 0; c < n_cols; ++c) {
+		if (!columns[c]) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_encode_rowgroup: null column pointer");
+		}
+		if (is_string(w->types[c])) {
+			const flsgpu_string_column* sc = static_cast<const flsgpu_string_column*>(columns[c]);
+			ptrs[c].data = sc->bytes;
+			ptrs[c].offsets = sc->offsets;
+		} else {
+			ptrs[c].data = static_cast<const uint8_t*>(columns[c]);
+		}
+	}
+	auto rg = std::make_unique<flsgpu_encoded_rowgroup>();
+	rg->n_tuples = (uint32_t)n_tuples;
+	for (size_t c = 0; c < n_cols; ++c) {
+		std::string err;
+		auto ch = encode_one(w, ptrs, 0, (uint32_t)n_tuples, c, &err);
+		if (!ch) {
+			return fls_set_error(FLSGPU_ERR_INVALID, err.c_str());
+		}
+		rg->chunks.push_back(std::move(ch));
+	}
+	*out = rg.release();
+	return FLSGPU_OK;
+}
+
+int flsgpu_writer_flush_rowgroup(flsgpu_writer* w, flsgpu_encoded_rowgroup* rg) {
+	if (!w || !rg) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_flush_rowgroup: null argument");
+	}
+	std::unique_ptr<flsgpu_encoded_rowgroup> own(rg);
+	std::lock_guard<std::mutex> g(w->flush_mu);
+	if (w->finished || w->pending_rows || rg->chunks.size() != w->cols.size()) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_flush_rowgroup: writer finished, rows pending from flsgpu_writer_append, or foreign row group");
+	}
+	fls_rowgroup_desc rd {};
+	rd.first_tuple = w->n_tuples;
+	rd.n_tuples = rg->n_tuples;
+	rd.n_vec = (rg->n_tuples + FLS_VEC_SZ - 1) / FLS_VEC_SZ;
+	w->rgs.push_back(rd);
+	for (auto& ch : rg->chunks) {
+		w->chunks.push_back(std::move(ch));
+	}
+	w->n_tuples += rg->n_tuples;
+	return FLSGPU_OK;
+}
+
+void flsgpu_encoded_rowgroup_free(flsgpu_encoded_rowgroup* rg) {
+	delete rg;
+}
+
+int flsgpu_writer_set_inline_footer(flsgpu_writer* w, int inline_footer) {
+	if (!w || w->finished) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_set_inline_footer: null or finished writer");
+	}
+	w->inline_footer = inline_footer != 0;
+	return FLSGPU_OK;
+}
+
+int flsgpu_writer_rowgroups(const flsgpu_writer* w, uint64_t* n_rowgroups, uint64_t* n_tuples) {
+	if (!w) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_rowgroups: null writer");
+	}
+	if (n_rowgroups) {
+		*n_rowgroups = w->rgs.size();
+	}
+	if (n_tuples) {
+		*n_tuples = w->n_tuples + w->pending_rows;
+	}
+	return FLSGPU_OK;
+}
+
 int flsgpu_writer_finish(flsgpu_writer* w) {
 	if (!w) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_finish: null writer");
@@ -311,6 +409,7 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 	h.n_tuples = w->n_tuples;
 	h.footer_offset = footer_off;
 	h.footer_size = footer_size;
+	h.reserved[0] = w->inline_footer ? 0 : 1; // 1: flsgpu_writer_save puts the footer into <path>.footer
 	std::memcpy(w->image.data(), &h, sizeof(h));
 	uint8_t* f = w->image.data() + footer_off;
 	std::memcpy(f, w->cols.data(), w->cols.size() * sizeof(fls_column_desc));
@@ -337,20 +436,33 @@ int flsgpu_writer_image(const flsgpu_writer* w, const void** bytes, uint64_t* si
 	return FLSGPU_OK;
 }
 
-int flsgpu_writer_save(const flsgpu_writer* w, const char* path) {
-	if (!w || !w->finished || !path) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_save: writer not finished");
-	}
+static int write_file(const char* path, const uint8_t* p, size_t n) {
 	FILE* fp = std::fopen(path, "wb");
 	if (!fp) {
 		return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open for writing: ") + path).c_str());
 	}
-	const size_t n = std::fwrite(w->image.data(), 1, w->image.size(), fp);
-	std::fclose(fp);
-	if (n != w->image.size()) {
-		return fls_set_error(FLSGPU_ERR_IO, "short write");
+	const size_t k = std::fwrite(p, 1, n, fp);
+	if (std::fclose(fp) != 0 || k != n) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("short write: ") + path).c_str());
 	}
 	return FLSGPU_OK;
+}
+
+int flsgpu_writer_save(const flsgpu_writer* w, const char* path) {
+	if (!w || !w->finished || !path) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_save: writer not finished");
+	}
+	if (w->inline_footer) {
+		return write_file(path, w->image.data(), w->image.size());
+	}
+	// WithInlinedFooter(false) (reference fls_writer.cpp:229-230,278): data file = header + chunks, footer beside it
+	fls_file_header h;
+	std::memcpy(&h, w->image.data(), sizeof(h));
+	const int rc = write_file(path, w->image.data(), (size_t)h.footer_offset);
+	if (rc) {
+		return rc;
+	}
+	return write_file((std::string(path) + ".footer").c_str(), w->image.data() + h.footer_offset, (size_t)h.footer_size);
 }
 
 void flsgpu_writer_destroy(flsgpu_writer* w) {

@@ -1,0 +1,248 @@
+// fls_file_reader.hpp — DuckDB-typed scan side of the B200 FastLanes extension.
+//
+// FastLanesReader : BaseFileReader and FastLanesMultiFileInfo : MultiFileReaderInterface are what
+// MultiFileFunction<FastLanesMultiFileInfo>("read_fls") drives (reference src/include/reader/fls_reader.hpp:27-104,
+// src/include/reader/fls_multi_file_info.hpp:16-150).  The reference decodes two 1024-value vectors per Scan call on the
+// worker's CPU through the FastLanes library + its materializer; here a worker is handed a BATCH of row groups, the batch is
+// staged, decoded and copied back by one pipelined call into libflsgpu (flsgpu_scan_filtered_to_host: H2D of the compressed
+// chunks, fused sm_100a decode kernels, D2H into pinned buffers) and Scan serves 2048-row chunks whose vectors point
+// straight into those pinned buffers (kept alive by the vectors themselves).
+#pragma once
+
+#include "duckdb.hpp"
+#include "duckdb/common/multi_file/base_file_reader.hpp"
+#include "duckdb/common/multi_file/multi_file_function.hpp"
+#include "duckdb/common/types/vector_buffer.hpp"
+#include "duckdb/function/partition_stats.hpp"
+#include "duckdb/planner/table_filter_state.hpp"
+
+#include "flsgpu.h"
+
+#include <atomic>
+#include <mutex>
+
+namespace duckdb {
+
+//! Status of a C-ABI call -> DuckDB exception (the reference throws InternalException / std::runtime_error /
+//! ConversionException from the same places: fls_reader.cpp:48,64,70,168,577,606, fls_kernel.hpp:26,32).
+void FlsCheck(int status, const char *where);
+
+class FastLanesFileReaderOptions : public BaseFileReaderOptions {
+public:
+	//! read_fls(..., explicit_cardinality := N) (reference read_fls.cpp:34)
+	idx_t explicit_cardinality = 0;
+	//! read_fls(..., file_row_number := true) (reference read_fls.cpp:35)
+	bool file_row_number = false;
+};
+
+struct FastLanesUnionData : public BaseUnionData {
+	explicit FastLanesUnionData(OpenFileInfo file_p) : BaseUnionData(std::move(file_p)) {
+	}
+	FastLanesFileReaderOptions options;
+};
+
+struct FastLanesReadBindData : public TableFunctionData {
+	idx_t initial_file_cardinality = 0;
+	idx_t initial_file_n_rowgroups = 0;
+	unique_ptr<FastLanesFileReaderOptions> options;
+};
+
+//! Pinned host memory the device copies decoded columns into.  It is a VectorBuffer so that every DuckDB vector that points
+//! into it holds a reference: the memory outlives the reader's own use of it for as long as a chunk is alive downstream.
+class FlsPinnedBuffer : public VectorBuffer {
+public:
+	explicit FlsPinnedBuffer(idx_t bytes);
+	~FlsPinnedBuffer() override;
+	data_ptr_t ptr = nullptr;
+	idx_t bytes = 0;
+};
+
+//! Output column -> decoder column of the row-group batch (reference FastLanesReaderProjectionPlan,
+//! fls_multi_file_info.hpp:48-55)
+struct FastLanesReaderProjectionPlan {
+	vector<uint32_t> reader_column_ids;
+	vector<optional_idx> output_to_reader_idx;
+	bool has_physical_columns = false;
+};
+
+//! A pushed-down filter the host evaluates after decode with DuckDB's own code, like the reference's FastLanesScanFilter
+//! (filter_executor.hpp:12-22): everything the device does not evaluate (IN lists, OR, dynamic and expression filters,
+//! filters on the virtual column or on columns that go through a conversion expression).
+struct FastLanesHostFilter {
+	FastLanesHostFilter(ClientContext &context, idx_t chunk_column, TableFilter &filter_p);
+	idx_t chunk_column;
+	TableFilter &filter;
+	unique_ptr<TableFilterState> filter_state;
+};
+
+//! Decoded rows of one reader column for the current batch
+struct FlsColumnStage {
+	bool is_string = false;
+	bool dictionary_form = false;
+	idx_t value_bytes = 0;
+	buffer_ptr<FlsPinnedBuffer> rows; // values | string_t | u32 selection entries
+	buffer_ptr<FlsPinnedBuffer> heap; // string bytes (flat form) / dictionary bytes (dictionary form)
+	buffer_ptr<FlsPinnedBuffer> keys; // dictionary form: string_t per key
+	vector<idx_t> key_offsets;        // dictionary form: first key of every row group of the batch (+ total)
+	vector<unique_ptr<Vector>> dictionaries; // dictionary form: the DuckDB dictionary of each row group, built on first use
+};
+
+struct FastLanesReadLocalState : public LocalTableFunctionState {
+	//! Tuples of the row group being served (reference fls_multi_file_info.hpp:57-77: same fields, same meaning)
+	idx_t n_tuples = 0;
+	idx_t cur_rowgroup = 0;
+	idx_t cur_vector = 0;
+	idx_t row_group_base = 0;
+	FastLanesReaderProjectionPlan projection;
+	//! Row groups [batch_begin, batch_end) handed to this worker by the last TryInitializeScan
+	idx_t batch_begin = 0;
+	idx_t batch_end = 0;
+	bool batch_decoded = false;
+	vector<unique_ptr<FlsColumnStage>> stage;
+	buffer_ptr<FlsPinnedBuffer> mask; // selection bit mask of the device-evaluated filters for the batch
+	bool has_mask = false;
+	//! Pushed-down filters, split once per file into what the device evaluates and what the host evaluates
+	bool filters_ready = false;
+	const BaseFileReader *filters_for = nullptr;
+	vector<flsgpu_filter> device_filters;
+	vector<string> device_filter_strings;
+	vector<FastLanesHostFilter> host_filters;
+	SelectionVector sel;
+	//! Conversion expressions the multi-file reader asked this reader to evaluate (BaseFileReader::expression_map)
+	unique_ptr<ExpressionExecutor> conversion_executor;
+	vector<optional_idx> conversion_of_output; // output column -> expression index in conversion_executor
+	DataChunk conversion_input;
+};
+
+struct FastLanesReadGlobalState : public GlobalTableFunctionState {
+	//! Next row group of the current file to hand out (reference fls_multi_file_info.hpp:79-86)
+	idx_t next_rowgroup = 0;
+};
+
+class FastLanesReader final : public BaseFileReader {
+public:
+	FastLanesReader(ClientContext &context, OpenFileInfo file_p, const FastLanesFileReaderOptions &options);
+	~FastLanesReader() override;
+
+	string GetReaderType() const override {
+		return "FastLanes";
+	}
+	bool TryInitializeScan(ClientContext &context, GlobalTableFunctionState &gstate,
+	                       LocalTableFunctionState &lstate) override;
+	void Scan(ClientContext &context, GlobalTableFunctionState &global_state, LocalTableFunctionState &local_state,
+	          DataChunk &chunk) override;
+	void FinishFile(ClientContext &context, GlobalTableFunctionState &gstate) override;
+	double GetProgressInFile(ClientContext &context) override;
+	unique_ptr<BaseStatistics> GetStatistics(ClientContext &context, const string &name) override;
+	shared_ptr<BaseUnionData> GetUnionData(idx_t file_idx) override;
+	void AddVirtualColumn(column_t virtual_column_id) override;
+
+	void GetPartitionStats(vector<PartitionStatistics> &result) const;
+	const FastLanesFileReaderOptions &GetOptions() const {
+		return reader_options;
+	}
+	idx_t GetNRowGroups() const {
+		return info.n_rowgroups;
+	}
+	idx_t GetNTuples(idx_t row_group_idx) const {
+		return row_groups[row_group_idx].n_tuples;
+	}
+	idx_t GetNVectors(idx_t row_group_idx) const {
+		return row_groups[row_group_idx].n_vec;
+	}
+	idx_t GetTotalTuples() const {
+		return total_tuples;
+	}
+	idx_t GetTotalVectors() const {
+		return total_vectors;
+	}
+	idx_t RowGroupsPerBatch() const {
+		return rowgroups_per_batch;
+	}
+	flsgpu_table *Table() const {
+		return table;
+	}
+
+private:
+	struct ScanBatch {
+		idx_t start_tuple = 0;
+		idx_t count = 0;
+		idx_t input_vector_count = 0;
+		bool IsValid() const {
+			return input_vector_count > 0;
+		}
+	};
+	void Initialize(ClientContext &context);
+	void EnsureFileRowNumberColumn();
+	bool IsFileRowNumberColumn(column_t column_id) const;
+	bool TryAssignNextRowGroup(FastLanesReadGlobalState &global_state, FastLanesReadLocalState &local_state, idx_t batch_limit);
+	void InitializeScanFilters(ClientContext &context, FastLanesReadLocalState &local_state);
+	void DecodeRowGroupBatch(FastLanesReadLocalState &local_state);
+	ScanBatch GetScanBatch(const FastLanesReadLocalState &local_state) const;
+	void DecodePhysicalColumns(FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t start_vector, idx_t count);
+	void PopulateVirtualColumns(const FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t row_start, idx_t count);
+	void ApplyFilters(FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t start_vector, idx_t count);
+	FastLanesReaderProjectionPlan BuildReaderProjectionPlan();
+	const vector<idx_t> &GetRowGroupsToScan(ClientContext &context, FastLanesReadLocalState &local_state);
+
+	flsgpu_table *table = nullptr;
+	flsgpu_table_info info {};
+	vector<fls_column_desc> column_descs;
+	vector<int32_t> column_out_types; // flsgpu_out_type per physical column
+	vector<fls_rowgroup_desc> row_groups;
+	vector<idx_t> row_group_offsets;
+	idx_t total_vectors = 0;
+	idx_t total_tuples = 0;
+	atomic<idx_t> vectors_read;
+	optional_idx file_row_number_local_idx;
+	FastLanesFileReaderOptions reader_options;
+	idx_t rowgroups_per_batch = 32;
+	//! RowGroupFilter of the reference (row_group_filter.cpp:62-94): row groups whose zone maps cannot satisfy the filters
+	//! are never handed out.  Built once per scan under rowgroup_filter_lock.
+	std::mutex rowgroup_filter_lock;
+	atomic<bool> rowgroup_filter_ready;
+	const TableFilterSet *rowgroup_filter_for = nullptr;
+	vector<idx_t> rowgroups_to_scan;
+};
+
+//! Splits BaseFileReader::filters into device filters (constant comparisons on physical columns, ANDed) and host filters.
+//! Returns false for a filter tree the device cannot evaluate completely (it then goes to the host as a whole).
+struct FastLanesFilterPushdown {
+	static void Split(ClientContext &context, BaseFileReader &reader, const vector<fls_column_desc> &column_descs,
+	                  idx_t n_physical_columns, FastLanesReadLocalState &local_state);
+	static bool ToDeviceFilter(const TableFilter &filter, const fls_column_desc &column, const LogicalType &type, uint32_t col,
+	                           vector<flsgpu_filter> &out, vector<string> &strings);
+};
+
+struct FastLanesMultiFileInfo : public MultiFileReaderInterface {
+	static unique_ptr<MultiFileReaderInterface> CreateInterface(ClientContext &context);
+
+	unique_ptr<BaseFileReaderOptions> InitializeOptions(ClientContext &context, optional_ptr<TableFunctionInfo> info) override;
+	bool ParseCopyOption(ClientContext &context, const string &key, const vector<Value> &values, BaseFileReaderOptions &options,
+	                     vector<string> &expected_names, vector<LogicalType> &expected_types) override;
+	bool ParseOption(ClientContext &context, const string &key, const Value &val, MultiFileOptions &file_options,
+	                 BaseFileReaderOptions &options) override;
+	unique_ptr<TableFunctionData> InitializeBindData(MultiFileBindData &multi_file_data,
+	                                                 unique_ptr<BaseFileReaderOptions> options) override;
+	void BindReader(ClientContext &context, vector<LogicalType> &return_types, vector<string> &names,
+	                MultiFileBindData &bind_data) override;
+	void FinalizeBindData(MultiFileBindData &multi_file_data) override;
+	void GetBindInfo(const TableFunctionData &bind_data, BindInfo &info) override;
+	optional_idx MaxThreads(const MultiFileBindData &bind_data_p, const MultiFileGlobalState &global_state,
+	                        FileExpandResult expand_result) override;
+	unique_ptr<GlobalTableFunctionState> InitializeGlobalState(ClientContext &context, MultiFileBindData &bind_data,
+	                                                           MultiFileGlobalState &global_state) override;
+	unique_ptr<LocalTableFunctionState> InitializeLocalState(ExecutionContext &, GlobalTableFunctionState &) override;
+	shared_ptr<BaseFileReader> CreateReader(ClientContext &context, GlobalTableFunctionState &gstate, BaseUnionData &union_data,
+	                                        const MultiFileBindData &bind_data_p) override;
+	shared_ptr<BaseFileReader> CreateReader(ClientContext &context, GlobalTableFunctionState &gstate, const OpenFileInfo &file,
+	                                        idx_t file_idx, const MultiFileBindData &bind_data) override;
+	shared_ptr<BaseFileReader> CreateReader(ClientContext &context, const OpenFileInfo &file, BaseFileReaderOptions &options,
+	                                        const MultiFileOptions &file_options) override;
+	void FinishReading(ClientContext &context, GlobalTableFunctionState &global_state,
+	                   LocalTableFunctionState &local_state) override;
+	unique_ptr<NodeStatistics> GetCardinality(const MultiFileBindData &bind_data, idx_t file_count) override;
+	void GetVirtualColumns(ClientContext &context, MultiFileBindData &bind_data, virtual_column_map_t &result) override;
+};
+
+} // namespace duckdb

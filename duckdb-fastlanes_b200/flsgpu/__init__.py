@@ -149,6 +149,8 @@ ABI_SYMBOLS = [
     "flsgpu_string_heap_bytes", "flsgpu_decode_strings", "flsgpu_decode_string_codes", "flsgpu_decode_string_dict",
     "flsgpu_string_dict_keys", "flsgpu_scan_strings_to_host", "flsgpu_scan_projection_to_host",
     "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked", "flsgpu_scan_filtered_to_host",
+    "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
+    "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups",
 ]
 
 

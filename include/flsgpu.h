@@ -64,6 +64,19 @@ int flsgpu_writer_create(uint32_t n_columns, const flsgpu_column_spec* cols, uin
 int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t n_tuples, int n_threads);
 /* Finalize (fls_writer.cpp:332-347): flush the tail row group and build the footer. */
 int flsgpu_writer_finish(flsgpu_writer* w);
+/* Row groups prepared out of order and appended in order: PrepareBatch / FlushBatch and the per-thread row-group writers of
+ * Sink / Combine (fls_writer.cpp:46-187,306-330: CreateRowGroupWriter + PrepareRowGroup, then rg_writer->Flush()).
+ * encode is thread safe (it only reads the writer's schema) and takes 1..row_group_size tuples, columns as for
+ * flsgpu_writer_append; flush appends the row group to the file in call order, takes ownership, and may be called from any
+ * thread.  Do not mix with flsgpu_writer_append while rows are pending there. */
+typedef struct flsgpu_encoded_rowgroup flsgpu_encoded_rowgroup;
+int flsgpu_writer_encode_rowgroup(const flsgpu_writer* w, const void* const* columns, uint64_t n_tuples, flsgpu_encoded_rowgroup** out);
+int flsgpu_writer_flush_rowgroup(flsgpu_writer* w, flsgpu_encoded_rowgroup* rg);
+void flsgpu_encoded_rowgroup_free(flsgpu_encoded_rowgroup* rg); /* only for row groups that were never flushed */
+/* WithInlinedFooter (fls_writer.cpp:229-230,278): 0 -> flsgpu_writer_save writes the footer to "<path>.footer". Default 1. */
+int flsgpu_writer_set_inline_footer(flsgpu_writer* w, int inline_footer);
+/* Row groups flushed so far / tuples accepted so far (num_row_groups of FastLanesWriteGlobalState: file rotation). */
+int flsgpu_writer_rowgroups(const flsgpu_writer* w, uint64_t* n_rowgroups, uint64_t* n_tuples);
 int flsgpu_writer_image(const flsgpu_writer* w, const void** bytes, uint64_t* size); /* valid until destroy */
 int flsgpu_writer_save(const flsgpu_writer* w, const char* path);
 void flsgpu_writer_destroy(flsgpu_writer* w);

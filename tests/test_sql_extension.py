@@ -1,0 +1,131 @@
+"""The real DuckDB `fastlanes` extension (duckdb-fastlanes_b200/extension): read_fls / COPY ... (FORMAT fls) linked into
+DuckDB v1.4.0 built from the reference tree's vendored sources.
+
+GPU tests shell out to DuckDB's own SQLLogicTest runner (extension/bin/unittest) on
+  * the REFERENCE's test files, unmodified (staged by `make -C oracle ref` into oracle/_ref/test: the reference's only
+    parity contract, test/all_types_{single,multi}_threaded.test), and their 1 M-row variants (BASELINE config 1);
+  * the extension's own tests (extension/test/sql/*.test).
+A run only counts when nothing was skipped: with the extension missing, `require fastlanes` turns a file into a skip that
+exits green.
+CPU tests cover what needs no device: the writer, bind/metadata, COUNT(*) from partition stats, and that a scan without a
+device fails loudly instead of falling back to the CPU.
+"""
+import os
+import re
+import shutil
+import subprocess
+import tempfile
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXT = os.path.join(ROOT, "duckdb-fastlanes_b200", "extension")
+BIN = os.path.join(EXT, "bin")
+REF_TESTS = os.path.join(ROOT, "oracle", "_ref")
+ENV = dict(os.environ, LD_LIBRARY_PATH=BIN + ":" + os.path.join(ROOT, "duckdb-fastlanes_b200") + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+
+needs_binaries = pytest.mark.skipif(not os.path.exists(os.path.join(BIN, "unittest")),
+                                    reason="extension binaries not built (make -C duckdb-fastlanes_b200/extension)")
+
+
+def run_sql(sql, threads=None):
+    pre = f"SET threads={threads};\n" if threads else ""
+    p = subprocess.run([os.path.join(BIN, "duckdb"), "-csv", "-noheader"], input=pre + sql, capture_output=True, text=True, env=ENV,
+                       timeout=600)
+    return p.returncode, p.stdout, p.stderr
+
+
+def run_unittest(test_dir, pattern, log_name):
+    tmp = tempfile.mkdtemp(prefix="fls_sqltest_")
+    shutil.rmtree(tmp)  # the runner insists on creating it
+    p = subprocess.run([os.path.join(BIN, "unittest"), "--test-dir", test_dir, "--test-temp-dir", tmp, pattern], capture_output=True,
+                       text=True, env=ENV, timeout=3000)
+    out = p.stdout + p.stderr
+    log_dir = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(log_dir, exist_ok=True)
+    with open(os.path.join(log_dir, log_name), "w") as f:
+        f.write(f"$ unittest --test-dir {os.path.relpath(test_dir, ROOT)} \"{pattern}\"\nexit code {p.returncode}\n{out}")
+    shutil.rmtree(tmp, ignore_errors=True)
+    return p.returncode, out
+
+
+def assert_all_passed(rc, out, n_files):
+    assert rc == 0, out[-4000:]
+    assert "skipped" not in out.lower() and "require fastlanes" not in out, "tests were SKIPPED, not passed:\n" + out[-2000:]
+    m = re.search(r"All tests passed \((\d+) assertions? in (\d+) test cases?\)", out)
+    assert m, out[-2000:]
+    assert int(m.group(2)) == n_files, f"expected {n_files} test files to run:\n" + out[-2000:]
+    return int(m.group(1))
+
+
+@needs_binaries
+def test_copy_and_bind_work_without_a_device_and_scans_fail_loudly(tmp_path):
+    path = str(tmp_path / "t.fls")
+    rc, out, err = run_sql(f"""
+        CREATE TABLE t AS SELECT i AS id, CAST(i * 10 AS BIGINT) AS col, 'Value ' || (i % 100) AS s, i / 1000.0 AS d,
+                                 CAST(i % 200 AS UTINYINT) AS u, CAST(i AS DECIMAL(9,2)) AS dec FROM range(1, 100001) tbl(i);
+        COPY t TO '{path}' (FORMAT fls);
+        SELECT column_name || ':' || column_type FROM (DESCRIBE SELECT * FROM read_fls('{path}'));
+        SELECT count(*) FROM read_fls('{path}');
+    """)
+    assert rc == 0, err
+    lines = out.replace('"', '').split()
+    assert lines[-7:-1] == ["id:BIGINT", "col:BIGINT", "s:VARCHAR", "d:DOUBLE", "u:UBIGINT", "dec:DECIMAL(9,2)"], out
+    assert lines[-1] == "100000"  # answered from the footer's partition statistics: no decode
+    assert os.path.getsize(path) > 1024
+    import torch
+    if not torch.cuda.is_available():
+        rc, out, err = run_sql(f"SELECT sum(col) FROM read_fls('{path}');")
+        assert rc != 0 and "no CUDA device" in err and "no CPU fallback" in err, (out, err)
+
+
+@needs_binaries
+def test_the_files_copy_writes_are_the_engines_container(tmp_path):
+    """COPY ... (FORMAT fls) goes through flsgpu_writer_*: the oracle (and the ctypes binding) read the file."""
+    import numpy as np
+
+    import flsgpu
+    import oracle_lib
+
+    path = str(tmp_path / "t.fls")
+    rc, out, err = run_sql(f"""
+        COPY (SELECT CAST(i AS BIGINT) * 7 AS a, CAST(i % 977 AS INTEGER) AS b, i / 8.0 AS c FROM range(0, 150000) t(i))
+        TO '{path}' (FORMAT fls, row_group_size 32768);
+    """)
+    assert rc == 0, err
+    img = np.fromfile(path, dtype=np.uint8)
+    t = flsgpu.Table(img)
+    assert (t.n_rowgroups, t.vec_per_rowgroup, t.n_tuples) == (5, 32, 150000)
+    oracle = oracle_lib.Oracle(img)
+    i = np.arange(150000)
+    for c, exp in enumerate(((i * 7).astype(np.int64), (i % 977).astype(np.int32), i / 8.0)):
+        got = oracle.decode_column(c, 0, t.n_rowgroups, 0, exp.dtype, t.vec_per_rowgroup)
+        flat = np.concatenate([got[a:b] for a, b in t.valid_mask_slices()])
+        assert flat.tobytes() == exp.tobytes()
+    t.close()
+
+
+@needs_binaries
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["all_types_single_threaded", "all_types_multi_threaded"])
+def test_reference_sqllogictests_unmodified(name):
+    path = os.path.join(REF_TESTS, "test", name + ".test")
+    assert os.path.exists(path), "reference tests not staged: make -C oracle ref (needs /root/reference)"
+    rc, out = run_unittest(REF_TESTS, f"test/{name}.test", f"sqltest_reference_{name}.log")
+    assert assert_all_passed(rc, out, 1) >= 13
+
+
+@needs_binaries
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["all_types_single_threaded_1m", "all_types_multi_threaded_1m"])
+def test_reference_sqllogictests_at_one_million_rows(name):
+    rc, out = run_unittest(REF_TESTS, f"test/{name}.test", f"sqltest_reference_{name}.log")
+    assert assert_all_passed(rc, out, 1) >= 13
+
+
+@needs_binaries
+@pytest.mark.gpu
+def test_extension_sqllogictests():
+    n_files = len([f for f in os.listdir(os.path.join(EXT, "test", "sql")) if f.endswith(".test")])
+    rc, out = run_unittest(EXT, "test/sql/*", "sqltest_extension.log")
+    assert_all_passed(rc, out, n_files)
