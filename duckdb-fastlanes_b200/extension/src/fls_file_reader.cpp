@@ -457,6 +457,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 					stage.key_offsets[r + 1] = stage.key_offsets[r] + chunk.aux_count;
 				}
 				stage.dictionaries.resize(n_rg);
+				stage.dictionary_ids.assign(n_rg, string());
 			}
 		} else {
 			stage.value_bytes = GetTypeIdSize(physical);
@@ -519,12 +520,16 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 				dictionary = make_uniq<Vector>(type, stage.keys->ptr + stage.key_offsets[rg_in_batch] * sizeof(string_t));
 				StringVector::AddBuffer(*dictionary, stage.keys);
 				StringVector::AddBuffer(*dictionary, stage.heap);
+				// operators cache work per dictionary id (hash tables, dictionary-aware functions): it must never repeat,
+				// not even when a later dictionary is allocated at the address of a freed one
+				static atomic<idx_t> next_dictionary_id {0};
+				stage.dictionary_ids[rg_in_batch] = "fls_dict_" + to_string(next_dictionary_id++);
 			}
 			// the selection entries of the chunk's rows: copied (8 KiB) so that the dictionary vector owns them
 			SelectionVector sel(STANDARD_VECTOR_SIZE);
 			std::memcpy(sel.data(), stage.rows->ptr + first_row * sizeof(sel_t), count * sizeof(sel_t));
 			target.Dictionary(*dictionary, dict_size, sel, count);
-			DictionaryVector::SetDictionaryId(target, to_string(CastPointerToValue(dictionary.get())));
+			DictionaryVector::SetDictionaryId(target, stage.dictionary_ids[rg_in_batch]);
 			continue;
 		}
 		Vector view(type, stage.rows->ptr + first_row * stage.value_bytes);
@@ -576,11 +581,11 @@ void FastLanesReader::ApplyFilters(FastLanesReadLocalState &ls, DataChunk &chunk
 	if (!ls.has_mask && ls.host_filters.empty()) {
 		return;
 	}
-	if (!ls.sel.data()) {
-		ls.sel.Initialize(STANDARD_VECTOR_SIZE);
-	}
+	// a fresh selection vector per chunk: the chunk's vectors share its buffer after Slice, and DuckDB's filter functions
+	// replace the vector they are handed by a smaller one (column_segment.cpp: sel.Initialize(new_sel))
+	SelectionVector selection(STANDARD_VECTOR_SIZE);
 	idx_t active = 0;
-	auto sel = ls.sel.data();
+	auto sel = selection.data();
 	if (ls.has_mask) {
 		const idx_t rg_in_batch = ls.cur_rowgroup - ls.batch_begin;
 		const auto words = reinterpret_cast<const uint32_t *>(ls.mask->ptr) + (rg_in_batch * info.vec_per_rowgroup + start_vector) * 32;
@@ -607,10 +612,10 @@ void FastLanesReader::ApplyFilters(FastLanesReadLocalState &ls, DataChunk &chunk
 		auto &vector = chunk.data[host_filter.chunk_column];
 		UnifiedVectorFormat unified;
 		vector.ToUnifiedFormat(count, unified);
-		ColumnSegment::FilterSelection(ls.sel, vector, unified, host_filter.filter, *host_filter.filter_state, count, active);
+		ColumnSegment::FilterSelection(selection, vector, unified, host_filter.filter, *host_filter.filter_state, count, active);
 	}
 	if (active != count) {
-		chunk.Slice(ls.sel, active);
+		chunk.Slice(selection, active);
 	}
 }
 

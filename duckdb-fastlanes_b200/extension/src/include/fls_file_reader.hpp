@@ -85,6 +85,7 @@ struct FlsColumnStage {
 	buffer_ptr<FlsPinnedBuffer> keys; // dictionary form: string_t per key
 	vector<idx_t> key_offsets;        // dictionary form: first key of every row group of the batch (+ total)
 	vector<unique_ptr<Vector>> dictionaries; // dictionary form: the DuckDB dictionary of each row group, built on first use
+	vector<string> dictionary_ids;           // ... and its process-wide unique dictionary id
 };
 
 struct FastLanesReadLocalState : public LocalTableFunctionState {
@@ -107,7 +108,6 @@ struct FastLanesReadLocalState : public LocalTableFunctionState {
 	vector<flsgpu_filter> device_filters;
 	vector<string> device_filter_strings;
 	vector<FastLanesHostFilter> host_filters;
-	SelectionVector sel;
 	//! Conversion expressions the multi-file reader asked this reader to evaluate (BaseFileReader::expression_map)
 	unique_ptr<ExpressionExecutor> conversion_executor;
 	vector<optional_idx> conversion_of_output; // output column -> expression index in conversion_executor

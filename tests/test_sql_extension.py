@@ -39,7 +39,7 @@ def run_unittest(test_dir, pattern, log_name):
     tmp = tempfile.mkdtemp(prefix="fls_sqltest_")
     shutil.rmtree(tmp)  # the runner insists on creating it
     p = subprocess.run([os.path.join(BIN, "unittest"), "--test-dir", test_dir, "--test-temp-dir", tmp, pattern], capture_output=True,
-                       text=True, env=ENV, timeout=3000)
+                       text=True, env=ENV, timeout=900)
     out = p.stdout + p.stderr
     log_dir = os.path.join(ROOT, "gpurun_out")
     os.makedirs(log_dir, exist_ok=True)
