@@ -227,6 +227,19 @@ void delta_encode_vector(const U* in, ChunkBuilder& b, fls_vec_meta& m) {
 	m.data_off16 = (uint32_t)(b.data.size() / 16);
 	m.base = (uint64_t)(U)dmin;
 	m.width = (uint8_t)W;
+	// Arithmetic sequence (fls_format.h FLS_VEC_FORM_SEQUENCE): every delta equals dmin and the lane chains continue each
+	// other, i.e. value(i) = value(0) + i * dmin for all 1024 positions (arithmetic modulo 2^T).  The blob is written as
+	// for any DELTA vector; the mark lets a reader hand the vector on as (start, increment) without decoding it.
+	if (W == 0) {
+		bool seq = true;
+		for (int i = 1; i < kVec && seq; ++i) {
+			seq = in[i] == (U)(in[0] + (U)((U)i * (U)dmin));
+		}
+		if (seq) {
+			m.e = FLS_VEC_FORM_SEQUENCE;
+			m.reserved = (uint64_t)in[0];
+		}
+	}
 	const size_t old = b.data.size();
 	b.data.resize(old + sizeof(bases));
 	std::memcpy(b.data.data() + old, bases, sizeof(bases));

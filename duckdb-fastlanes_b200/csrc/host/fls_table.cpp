@@ -4,6 +4,8 @@
 #include "fls_table.hpp"
 #include "fls_fsst.hpp"
 
+#include <climits>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -433,6 +435,75 @@ int flsgpu_table_info_get(const flsgpu_table* t, flsgpu_table_info* out) {
 	out->n_tuples = t->header.n_tuples;
 	out->n_vectors = t->n_vectors;
 	out->file_bytes = t->size;
+	return FLSGPU_OK;
+}
+
+// Vector forms (fls_format.h FLS_VEC_FORM_*): read off the entry points, no decode.
+int flsgpu_column_vector_forms(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, flsgpu_vector_form* out,
+                               uint64_t* n_flat) {
+	if (!t || !out || col >= t->header.n_columns || n_rg == 0 || rg_begin >= t->header.n_rowgroups ||
+	    n_rg > t->header.n_rowgroups - rg_begin) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_column_vector_forms: null argument, column or row-group range out of bounds");
+	}
+	const fls_column_desc& cd = t->columns[col];
+	const unsigned T = cd.phys_bits;
+	const uint32_t vpr = t->header.vec_per_rowgroup;
+	uint32_t flat = 0;
+	auto extend = [&](uint64_t word) -> int64_t { // physical word -> 64 bits by the column's signedness
+		if (T >= 64 || cd.is_float) {
+			return (int64_t)word;
+		}
+		const uint64_t m = (1ull << T) - 1;
+		word &= m;
+		return (cd.is_signed && (word >> (T - 1))) ? (int64_t)(word | ~m) : (int64_t)word;
+	};
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		const fls_chunk_desc& ch = t->chunk(rg_begin + r, col);
+		const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_META]);
+		for (uint32_t v = 0; v < vpr; ++v) {
+			flsgpu_vector_form& f = out[(uint64_t)r * vpr + v];
+			f.start = f.increment = 0;
+			f.form = FLS_VEC_FORM_CONSTANT;
+			f.flat_slot = 0xffffffffu;
+			if (v >= ch.n_vec) {
+				continue;
+			}
+			if (T != 128 && ch.encoding == FLS_ENC_CONSTANT) {
+				f.start = extend(ch.const_val);
+				continue;
+			}
+			const fls_vec_meta& m = meta[v];
+			if (T != 128 && ch.encoding == FLS_ENC_FFOR && m.width == 0 && m.aux_cnt == 0) {
+				f.start = extend(m.base);
+				continue;
+			}
+			if (T != 128 && !cd.is_float && ch.encoding == FLS_ENC_DELTA && m.width == 0 && m.e == FLS_VEC_FORM_SEQUENCE) {
+				// increment: the delta as a signed T-bit number (a decreasing unsigned column steps by -k, not by 2^T - k);
+				// the progression must stay inside the column's type and inside int64 (what DuckDB's Vector::Sequence takes)
+				const uint64_t mask = T >= 64 ? ~0ull : (1ull << T) - 1;
+				const uint64_t dw = m.base & mask;
+				const int64_t inc = (T < 64 && (dw >> (T - 1))) ? (int64_t)(dw | ~mask) : (int64_t)dw;
+				const __int128 start = cd.is_signed ? (__int128)extend(m.reserved) : (__int128)(m.reserved & mask);
+				const __int128 last = start + (__int128)inc * 1023;
+				const __int128 lo = cd.is_signed ? -((__int128)1 << (T - 1)) : 0;
+				__int128 hi = cd.is_signed ? ((__int128)1 << (T - 1)) - 1 : (__int128)mask;
+				if (hi > (__int128)INT64_MAX) {
+					hi = INT64_MAX;
+				}
+				if (start >= lo && start <= hi && last >= lo && last <= hi) {
+					f.start = (int64_t)start;
+					f.increment = inc;
+					f.form = inc == 0 ? FLS_VEC_FORM_CONSTANT : FLS_VEC_FORM_SEQUENCE;
+					continue;
+				}
+			}
+			f.form = FLS_VEC_FORM_FLAT;
+			f.flat_slot = flat++;
+		}
+	}
+	if (n_flat) {
+		*n_flat = flat;
+	}
 	return FLSGPU_OK;
 }
 

@@ -125,6 +125,9 @@ __device__ __forceinline__ VecDesc fetch_desc(const FlsLaunch& L, uint32_t v) {
 	d.aux_off = d.bytes = d.misc = d.misc2 = d.vec_in_chunk = d.aux_n = 0;
 	d.aux0 = d.aux1 = nullptr;
 	if (v < L.total_vecs) {
+		if (L.vec_map != nullptr) {
+			v = __ldg(L.vec_map + v);
+		}
 		const uint32_t r = v / L.vec_per_rg, vi = v - r * L.vec_per_rg;
 		const FlsChunkDev* ch = L.chunks + (size_t)r * L.chunk_stride;
 		const uint32_t enc = ch->encoding;

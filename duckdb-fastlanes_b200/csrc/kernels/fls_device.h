@@ -58,6 +58,9 @@ struct FlsLaunch {
 	uint64_t cmp_const2;
 	uint32_t* mask;      // [total_vecs * 32] words: bit i of word w of vector v = row v*1024 + w*32 + i
 	const uint8_t* rg_keep; // per row group of the range: 0 = pruned by its zone map (skipped), or nullptr
+	// compact scans (flsgpu_scan_column.compact): the launch walks total_vecs LISTED vectors, vec_map[k] = vector index inside
+	// the range of the k-th one, whose values land at slot k of the output; nullptr = every vector of the range, in place
+	const uint32_t* vec_map;
 };
 
 // Launch parameters of the string kernels (flsgpu_kernels_str.cu): column `col` of row groups [rg_begin, rg_begin + n_rg).

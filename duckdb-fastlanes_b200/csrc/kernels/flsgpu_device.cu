@@ -110,7 +110,15 @@ struct FlsDeviceState {
 	std::vector<uint64_t> heap_prefix; // host copy (n_chunks + n_columns entries: the last row holds the column totals)
 	uint64_t* d_key_prefix = nullptr;  // string columns: dictionary keys (DICT_STR / FSST_DICT aux_count) of the column's earlier chunks
 	std::vector<uint64_t> key_prefix;
-	std::vector<uint8_t> chunk_resident; // [rg * n_columns + col]
+	std::vector<uint8_t> chunk_resident; // [rg * n_columns + col]: the chunk's H2D copy has been ENQUEUED (see chunk_stage)
+	// Residency across streams: every staging pass records an event behind its copies (a ring of kStageEvents, a slot is
+	// synchronised before it is reused, so a ticket older than the ring is known complete); chunk_stage[i] = ticket of the
+	// pass that copied chunk i.  A consumer on another stream waits for the tickets of the chunks it reads (wait_resident).
+	static constexpr uint32_t kStageEvents = 64;
+	cudaEvent_t stage_events[kStageEvents] = {};
+	cudaStream_t stage_streams[kStageEvents] = {};
+	uint64_t stage_ticket = 0;           // tickets handed out so far (ticket k lives in ring slot k % kStageEvents)
+	std::vector<uint64_t> chunk_stage;   // [rg * n_columns + col]: ticket + 1, 0 = none
 	uint64_t resident_bytes = 0;
 	bool host_pinned_tried = false;
 	bool host_registered = false;
@@ -141,6 +149,11 @@ void fls_device_release(flsgpu_table* t) {
 	cudaFree(d->d_run_starts);
 	cudaFree(d->d_heap_prefix);
 	cudaFree(d->d_key_prefix);
+	for (cudaEvent_t e : d->stage_events) {
+		if (e) {
+			cudaEventDestroy(e);
+		}
+	}
 	if (d->host_registered) {
 		cudaHostUnregister(const_cast<uint8_t*>(t->bytes));
 	}
@@ -191,6 +204,7 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 	const uint64_t n_chunks = (uint64_t)h.n_rowgroups * h.n_columns;
 	d->image_bytes = h.footer_offset;
 	d->chunk_resident.assign(n_chunks, 0);
+	d->chunk_stage.assign(n_chunks, 0);
 	FLS_CUDA(cudaMalloc(&d->d_image, d->image_bytes + 256));
 
 	// CROSS_RLE run starts (reference cross_rle_kernel.hpp:8-21 rescans run lengths per vector; here the prefix sums
@@ -298,50 +312,79 @@ void pin_image(flsgpu_table* t, FlsDeviceState* d) {
 constexpr uint64_t kMergeGap = 256u << 10;
 
 int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t n_rg, const uint32_t* cols, uint32_t n_sel,
-                cudaStream_t stream) {
+                cudaStream_t stream, const uint8_t* need = nullptr) {
+	// need (optional): [(r - rg_begin) * n_columns + c] = 0 for chunks of the listed columns this pass may leave out
+	// (compact scans: chunks without a FLAT vector are never read on the device)
 	pin_image(t, d);
 	const uint32_t n_cols = t->header.n_columns;
 	std::vector<uint8_t> want(n_cols, cols ? 0 : 1);
 	for (uint32_t i = 0; cols && i < n_sel; ++i) {
 		want[cols[i]] = 1;
 	}
-	uint64_t run_begin = 0, run_end = 0; // pending merged copy [begin, end) in file offsets
+	std::vector<uint64_t> staged; // chunks whose copy this pass enqueues: marked resident only once every copy is enqueued
+	uint64_t run_begin = 0, run_end = 0, bytes = 0; // pending merged copy [begin, end) in file offsets
 	auto flush = [&]() -> int {
 		if (run_end > run_begin) {
 			FLS_CUDA(cudaMemcpyAsync(d->d_image + run_begin, t->bytes + run_begin, run_end - run_begin, cudaMemcpyHostToDevice,
 			                         stream));
-			d->resident_bytes += run_end - run_begin;
+			bytes += run_end - run_begin;
 		}
 		run_begin = run_end = 0;
 		return FLSGPU_OK;
 	};
-	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
-		for (uint32_t c = 0; c < n_cols; ++c) {
+	int rc = FLSGPU_OK;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg && rc == FLSGPU_OK; ++r) {
+		for (uint32_t c = 0; c < n_cols && rc == FLSGPU_OK; ++c) {
 			const uint64_t i = (uint64_t)r * n_cols + c;
-			if (!want[c] || d->chunk_resident[i]) {
+			if (!want[c] || d->chunk_resident[i] || (need && !need[(uint64_t)(r - rg_begin) * n_cols + c])) {
 				continue;
 			}
-			d->chunk_resident[i] = 1;
+			staged.push_back(i);
 			const fls_chunk_desc& ch = t->chunks[i];
 			if (ch.is_equal) { // EXP_EQUAL: the bytes are those of another column's chunk; uploaded once
-				const uint64_t src = (uint64_t)r * n_cols + (ch.equal_col[0] | ((uint32_t)ch.equal_col[1] << 8));
-				if (src < i && (d->chunk_resident[src] || want[src - (uint64_t)r * n_cols])) {
+				const uint32_t src_col = ch.equal_col[0] | ((uint32_t)ch.equal_col[1] << 8);
+				const uint64_t src = (uint64_t)r * n_cols + src_col;
+				const bool src_in_pass = src < i && want[src_col] && (!need || need[(uint64_t)(r - rg_begin) * n_cols + src_col]);
+				if (src < i && (d->chunk_resident[src] || src_in_pass)) {
+					if (d->chunk_resident[src] && !src_in_pass) {
+						staged.pop_back(); // copied by an earlier pass: inherit its ticket instead of this pass's
+						d->chunk_stage[i] = d->chunk_stage[src];
+						d->chunk_resident[i] = 1;
+					}
 					continue; // resident already, or uploaded earlier in this very pass (source columns come first)
 				}
 			}
 			if (run_end > run_begin && ch.offset >= run_end && ch.offset - run_end <= kMergeGap) {
 				run_end = ch.offset + ch.size;
 			} else {
-				const int rc = flush();
-				if (rc) {
-					return rc;
-				}
+				rc = flush();
 				run_begin = ch.offset;
 				run_end = ch.offset + ch.size;
 			}
 		}
 	}
-	return flush();
+	if (rc == FLSGPU_OK) {
+		rc = flush();
+	}
+	if (rc != FLSGPU_OK || staged.empty()) {
+		return rc; // nothing is marked: a failed pass leaves the chunks to the next one
+	}
+	// the event behind this pass's copies
+	const uint32_t slot = (uint32_t)(d->stage_ticket % FlsDeviceState::kStageEvents);
+	if (!d->stage_events[slot]) {
+		FLS_CUDA(cudaEventCreateWithFlags(&d->stage_events[slot], cudaEventDisableTiming));
+	} else {
+		FLS_CUDA(cudaEventSynchronize(d->stage_events[slot])); // kStageEvents passes old: long complete
+	}
+	FLS_CUDA(cudaEventRecord(d->stage_events[slot], stream));
+	d->stage_streams[slot] = stream;
+	const uint64_t ticket = d->stage_ticket++;
+	for (uint64_t i : staged) {
+		d->chunk_resident[i] = 1;
+		d->chunk_stage[i] = ticket + 1;
+	}
+	d->resident_bytes += bytes;
+	return FLSGPU_OK;
 }
 
 uint32_t blob_bytes_max(const fls_chunk_desc& c) {
@@ -535,7 +578,8 @@ struct MaskSpec { // filter pushdown on aggregate-family launches (FlsLaunch.mas
 };
 
 int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const OutSpec& os,
-                       void* out_dev, cudaStream_t stream, flsgpu_agg_acc* agg = nullptr, const MaskSpec* ms = nullptr) {
+                       void* out_dev, cudaStream_t stream, flsgpu_agg_acc* agg = nullptr, const MaskSpec* ms = nullptr,
+                       const uint32_t* vec_map_dev = nullptr, uint32_t n_mapped = 0) {
 	const fls_file_header& h = t->header;
 	const int T = t->columns[col].phys_bits;
 	if (T == 128) {
@@ -550,7 +594,8 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	L.chunks = d->d_chunks + (uint64_t)rg_begin * h.n_columns + col;
 	L.chunk_stride = h.n_columns;
 	L.vec_per_rg = h.vec_per_rowgroup;
-	L.total_vecs = n_rg * h.vec_per_rowgroup;
+	L.total_vecs = vec_map_dev ? n_mapped : n_rg * h.vec_per_rowgroup;
+	L.vec_map = vec_map_dev;
 	L.conv = os.conv;
 	L.out = out_dev;
 	L.run_shift = g_run_shift;
@@ -629,11 +674,27 @@ int check_range(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t
 	return FLSGPU_OK;
 }
 
-int check_resident(const flsgpu_table* t, const FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg) {
+// Every chunk of the column in the range must have been staged; `stream` is made to wait for staging passes that ran on
+// other streams and may still be in flight (flsgpu_table_stage on stream A followed by a decode on stream B; two
+// concurrent host-to-host scans over the same row groups).
+int check_resident(const flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_t rg_begin, uint32_t n_rg, cudaStream_t stream) {
+	std::lock_guard<std::mutex> g(d->mu);
+	uint64_t waited = 0; // bit per ring slot already waited for in this call
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
-		if (!d->chunk_resident[(uint64_t)r * t->header.n_columns + col]) {
+		const uint64_t i = (uint64_t)r * t->header.n_columns + col;
+		if (!d->chunk_resident[i]) {
 			return fls_set_error(FLSGPU_ERR_INVALID, "row group not staged: call flsgpu_table_stage first");
 		}
+		const uint64_t tk = d->chunk_stage[i];
+		if (tk == 0 || d->stage_ticket - (tk - 1) > FlsDeviceState::kStageEvents) {
+			continue; // the ring slot was reused since: that pass was synchronised
+		}
+		const uint32_t slot = (uint32_t)((tk - 1) % FlsDeviceState::kStageEvents);
+		if (d->stage_streams[slot] == stream || ((waited >> slot) & 1ull)) {
+			continue; // same stream: ordered already
+		}
+		waited |= 1ull << slot;
+		FLS_CUDA(cudaStreamWaitEvent(stream, d->stage_events[slot], 0));
 	}
 	return FLSGPU_OK;
 }
@@ -739,7 +800,7 @@ int flsgpu_decode_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint3
 	if (rc) {
 		return rc;
 	}
-	rc = check_resident(t, d, col, rg_begin, n_rg);
+	rc = check_resident(t, d, col, rg_begin, n_rg, static_cast<cudaStream_t>(cuda_stream));
 	if (rc) {
 		return rc;
 	}
@@ -771,7 +832,7 @@ int flsgpu_rowgroup_decode(flsgpu_table* t, uint32_t rg, const uint32_t* col_ids
 		return rc;
 	}
 	for (uint32_t i = 0; i < n_cols; ++i) {
-		rc = check_resident(t, d, col_ids[i], rg, 1);
+		rc = check_resident(t, d, col_ids[i], rg, 1, static_cast<cudaStream_t>(cuda_stream));
 		if (rc) {
 			return rc;
 		}
@@ -808,10 +869,12 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 	const fls_file_header& h = t->header;
 	struct ColPlan {
 		OutSpec os;
-		bool is_string = false, dict = false;
+		bool is_string = false, dict = false, compact = false;
 		uint64_t rg_bytes = 0;            // row bytes per row group (values, string_t or selection entries)
-		uint64_t dev_rows = 0, dev_heap = 0, dev_keys = 0; // offsets inside a slab's device scratch
+		uint64_t dev_rows = 0, dev_heap = 0, dev_keys = 0, dev_map = 0; // offsets inside a slab's device scratch
+		std::vector<flsgpu_vector_form> forms; // compact: form of every vector of the range
 	};
+	std::vector<std::vector<uint32_t>> vec_maps; // compact: the FLAT vectors of a (slab, column), alive until the streams drain
 	std::vector<ColPlan> cp(n_cols);
 	uint64_t rg_bytes_all = 0;
 	for (uint32_t i = 0; i < n_cols; ++i) {
@@ -842,9 +905,20 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 				return rc;
 			}
 			p.rg_bytes = (uint64_t)h.vec_per_rowgroup * FLS_VEC_SZ * p.os.ob;
+			p.compact = c.compact != 0;
 		}
 		rg_bytes_all += p.rg_bytes;
-		if (!c.out_host || c.out_capacity_bytes < p.rg_bytes * n_rg) {
+		uint64_t need_bytes = p.rg_bytes * n_rg;
+		if (p.compact) { // only the FLAT vectors of the range cross the link, packed
+			uint64_t n_flat = 0;
+			p.forms.resize((size_t)n_rg * h.vec_per_rowgroup);
+			rc = flsgpu_column_vector_forms(t, c.col, rg_begin, n_rg, p.forms.data(), &n_flat);
+			if (rc) {
+				return rc;
+			}
+			need_bytes = n_flat * FLS_VEC_SZ * p.os.ob;
+		}
+		if ((!c.out_host && need_bytes) || c.out_capacity_bytes < need_bytes) {
 			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_projection_to_host: output buffer null or too small");
 		}
 	}
@@ -890,6 +964,12 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 			slab_bytes += p.dict ? keys_max * 16u + 16u : 0u;
 		}
 	}
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		if (cp[i].compact) {
+			cp[i].dev_map = slab_bytes;
+			slab_bytes += (((uint64_t)slab_rg * h.vec_per_rowgroup * 4u) + 255u) & ~255ull;
+		}
+	}
 	const uint64_t dev_mask = slab_bytes, rg_mask_bytes = (uint64_t)h.vec_per_rowgroup * 128u;
 	slab_bytes += n_filters ? rg_mask_bytes * slab_rg : 0u;
 	FlsScanScratch* sc = nullptr;
@@ -912,9 +992,12 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		}
 	} ret {d, sc};
 	if (sc->out_bytes < slab_bytes) {
+		sc->out_bytes = 0; // a failed regrow must not leave the old size behind a freed or missing slab
 		for (int i = 0; i < 2; ++i) {
 			FLS_CUDA(cudaFree(sc->out[i]));
 			sc->out[i] = nullptr;
+		}
+		for (int i = 0; i < 2; ++i) {
 			FLS_CUDA(cudaMalloc(&sc->out[i], slab_bytes));
 		}
 		sc->out_bytes = slab_bytes;
@@ -943,9 +1026,45 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
 		const uint32_t n = std::min(slab_rg, n_rg - r);
 		cudaStream_t s = sc->streams[slab & 1];
+		// compact columns: the FLAT vectors of the slab (launch order = slot order) and the chunks that hold any
+		std::vector<uint8_t> need;
+		std::vector<uint32_t> map_of(n_cols, 0xffffffffu); // column -> index into vec_maps
+		for (uint32_t i = 0; i < n_cols; ++i) {
+			if (!cp[i].compact) {
+				continue;
+			}
+			if (need.empty()) {
+				need.assign((size_t)n * h.n_columns, 1);
+			}
+			vec_maps.emplace_back();
+			map_of[i] = (uint32_t)vec_maps.size() - 1;
+			std::vector<uint32_t>& vm = vec_maps.back();
+			bool filtered = false;
+			for (uint32_t k = 0; k < n_filters; ++k) {
+				filtered |= filters[k].col == cols[i].col;
+			}
+			for (uint32_t rr = 0; rr < n; ++rr) {
+				const size_t before = vm.size();
+				for (uint32_t v = 0; v < h.vec_per_rowgroup; ++v) {
+					if (cp[i].forms[(size_t)(r + rr) * h.vec_per_rowgroup + v].form == FLS_VEC_FORM_FLAT) {
+						vm.push_back(rr * h.vec_per_rowgroup + v);
+					}
+				}
+				if (vm.size() == before && !filtered) {
+					need[(size_t)rr * h.n_columns + cols[i].col] = 0;
+				}
+			}
+		}
+		for (uint32_t i = 0; i < n_cols && !need.empty(); ++i) { // a column listed twice, once in place: its chunks are needed
+			if (!cp[i].compact) {
+				for (uint32_t rr = 0; rr < n; ++rr) {
+					need[(size_t)rr * h.n_columns + cols[i].col] = 1;
+				}
+			}
+		}
 		{
 			std::lock_guard<std::mutex> g(d->mu);
-			status = stage_range(t, d, rg_begin + r, n, col_ids.data(), (uint32_t)col_ids.size(), s);
+			status = stage_range(t, d, rg_begin + r, n, col_ids.data(), (uint32_t)col_ids.size(), s, need.empty() ? nullptr : need.data());
 		}
 		uint8_t* base = static_cast<uint8_t*>(sc->out[slab & 1]);
 		if (n_filters && status == FLSGPU_OK) { // FilterExecutor::Apply for the slab: selection mask -> host
@@ -958,6 +1077,20 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 			const ColPlan& p = cp[i];
 			uint8_t* dev = base + p.dev_rows;
 			uint8_t* host_rows = static_cast<uint8_t*>(c.out_host) + (uint64_t)r * p.rg_bytes;
+			if (p.compact) {
+				const std::vector<uint32_t>& vm = vec_maps[map_of[i]];
+				const uint64_t slot0 = vm.empty() ? 0 : p.forms[(size_t)r * h.vec_per_rowgroup + vm[0]].flat_slot;
+				if (!vm.empty()) {
+					uint32_t* map_dev = reinterpret_cast<uint32_t*>(base + p.dev_map);
+					if (cudaMemcpyAsync(map_dev, vm.data(), vm.size() * 4u, cudaMemcpyHostToDevice, s) != cudaSuccess) {
+						status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(vector map)");
+						break;
+					}
+					status = decode_column_impl(t, d, c.col, rg_begin + r, n, p.os, dev, s, nullptr, nullptr, map_dev, (uint32_t)vm.size());
+					d2h(static_cast<uint8_t*>(c.out_host) + slot0 * FLS_VEC_SZ * p.os.ob, dev, (uint64_t)vm.size() * FLS_VEC_SZ * p.os.ob, s);
+				}
+				continue;
+			}
 			if (!p.is_string) {
 				status = decode_column_impl(t, d, c.col, rg_begin + r, n, p.os, dev, s);
 				d2h(host_rows, dev, p.rg_bytes * n, s);
@@ -1061,7 +1194,7 @@ int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, ui
 	if (rc) {
 		return rc;
 	}
-	rc = check_resident(t, d, col, rg_begin, n_rg);
+	rc = check_resident(t, d, col, rg_begin, n_rg, static_cast<cudaStream_t>(cuda_stream));
 	if (rc) {
 		return rc;
 	}
@@ -1095,7 +1228,7 @@ int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, ui
 namespace {
 
 int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const char* who, FlsDeviceState** dout,
-                        FlsStrLaunch* L) {
+                        FlsStrLaunch* L, cudaStream_t stream) {
 	int rc = check_range(t, col, rg_begin, n_rg, who);
 	if (rc) {
 		return rc;
@@ -1110,7 +1243,7 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	if (rc) {
 		return rc;
 	}
-	rc = check_resident(t, d, col, rg_begin, n_rg);
+	rc = check_resident(t, d, col, rg_begin, n_rg, stream);
 	if (rc) {
 		return rc;
 	}
@@ -1192,7 +1325,7 @@ int flsgpu_decode_strings(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint
                           void* cuda_stream) {
 	FlsDeviceState* d = nullptr;
 	FlsStrLaunch L {};
-	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_strings", &d, &L);
+	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_strings", &d, &L, static_cast<cudaStream_t>(cuda_stream));
 	if (rc) {
 		return rc;
 	}
@@ -1220,7 +1353,7 @@ int flsgpu_decode_string_codes(flsgpu_table* t, uint32_t col, uint32_t rg_begin,
                                uint64_t out_capacity_bytes, void* cuda_stream) {
 	FlsDeviceState* d = nullptr;
 	FlsStrLaunch L {};
-	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_string_codes", &d, &L);
+	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_string_codes", &d, &L, static_cast<cudaStream_t>(cuda_stream));
 	if (rc) {
 		return rc;
 	}
@@ -1245,7 +1378,7 @@ int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg_begin, 
                               void* cuda_stream) {
 	FlsDeviceState* d = nullptr;
 	FlsStrLaunch L {};
-	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_string_dict", &d, &L);
+	int rc = string_launch_setup(t, col, rg_begin, n_rg, "flsgpu_decode_string_dict", &d, &L, static_cast<cudaStream_t>(cuda_stream));
 	if (rc) {
 		return rc;
 	}
@@ -1413,7 +1546,7 @@ int string_filter_pass_dict(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg
 	if (!rc) {
 		FlsDeviceState* d = nullptr;
 		FlsStrLaunch L {};
-		rc = string_launch_setup(t, f.col, rg_begin, n_rg, "flsgpu_filter_mask", &d, &L);
+		rc = string_launch_setup(t, f.col, rg_begin, n_rg, "flsgpu_filter_mask", &d, &L, s);
 		if (!rc) {
 			L.key_flags = flags_dev;
 			L.n_tuples = counts_dev;
@@ -1596,7 +1729,7 @@ int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n
 		if (done[i] || t->columns[filters[i].col].phys_bits == 128) {
 			continue; // string filters run after the fused numeric passes
 		}
-		rc = check_resident(t, d, filters[i].col, rg_begin, n_rg);
+		rc = check_resident(t, d, filters[i].col, rg_begin, n_rg, s);
 		if (rc) {
 			return rc;
 		}
@@ -1649,7 +1782,7 @@ int flsgpu_aggregate_column_masked(flsgpu_table* t, uint32_t col, uint32_t rg_be
 	if (rc) {
 		return rc;
 	}
-	rc = check_resident(t, d, col, rg_begin, n_rg);
+	rc = check_resident(t, d, col, rg_begin, n_rg, static_cast<cudaStream_t>(cuda_stream));
 	if (rc) {
 		return rc;
 	}

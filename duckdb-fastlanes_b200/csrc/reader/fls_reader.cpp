@@ -210,6 +210,8 @@ bool FastLanesReader::TryInitializeScan(FastLanesReadGlobalState& gstate, FastLa
 	lstate.heaps.resize(n_reader_cols);
 	lstate.keys.resize(n_reader_cols);
 	lstate.dict_form.assign(n_reader_cols, 0);
+	lstate.forms.assign(n_reader_cols, {});
+	lstate.assembled.resize(n_reader_cols);
 	lstate.key_offsets.assign(n_reader_cols, {});
 	lstate.has_mask = false;
 	lstate.row_numbers.clear();
@@ -255,6 +257,13 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState& ls) {
 						ls.key_offsets[i][r + 1] = ls.key_offsets[i][r] + ch.aux_count;
 					}
 				}
+			} else if (reader_options.compressed_vectors) {
+				// only the FLAT vectors of the batch are decoded and cross PCIe, packed (flsgpu_scan_column.compact)
+				uint64_t n_flat = 0;
+				ls.forms[i].resize((size_t)n_rg * info.vec_per_rowgroup);
+				Check(flsgpu_column_vector_forms(table, ids[i], rg0, n_rg, ls.forms[i].data(), &n_flat), "flsgpu_column_vector_forms");
+				c.compact = 1;
+				ls.staging[i].Reserve(std::max<uint64_t>(16, n_flat * FLS_VEC_SZ * type.physical_bytes));
 			} else {
 				ls.staging[i].Reserve(rows * type.physical_bytes);
 			}
@@ -346,7 +355,7 @@ FastLanesReader::ScanBatch FastLanesReader::GetScanBatch(const FastLanesReadLoca
 
 // FastLanesReader::DecodePhysicalColumns (fls_reader.cpp:436-472): the values are already decoded; point the chunk's
 // vectors at rows [start_vector*1024, +count) of the current row group inside the staging buffers.
-void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState& ls, DataChunk& chunk, idx_t start_vector, idx_t) {
+void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState& ls, DataChunk& chunk, idx_t start_vector, idx_t count) {
 	const idx_t rg_in_batch = ls.cur_rowgroup - ls.batch_begin;
 	const idx_t first_elem = (rg_in_batch * info.vec_per_rowgroup + start_vector) * FLS_VEC_SZ;
 	for (size_t i = 0; i < column_ids.size(); ++i) {
@@ -363,10 +372,62 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState& ls, DataChu
 			v.sel = static_cast<const uint32_t*>(ls.staging[ri].ptr) + first_elem;
 			v.data = static_cast<const uint8_t*>(ls.keys[ri].ptr) + ls.key_offsets[ri][rg_in_batch] * 16;
 			v.dict_size = ls.key_offsets[ri][rg_in_batch + 1] - ls.key_offsets[ri][rg_in_batch];
+		} else if (!ls.forms[ri].empty()) {
+			FormedVector(ls, (size_t)ri, first_elem / FLS_VEC_SZ, count, v);
 		} else {
 			v.data = static_cast<const uint8_t*>(ls.staging[ri].ptr) + first_elem * def.type.physical_bytes;
 		}
 	}
+}
+
+namespace {
+template <class T>
+void FillForm(const flsgpu_vector_form& f, const uint8_t* flat, T* out, idx_t n) {
+	if (f.form == FLS_VEC_FORM_FLAT) {
+		std::memcpy(out, flat + (size_t)f.flat_slot * FLS_VEC_SZ * sizeof(T), n * sizeof(T));
+		return;
+	}
+	uint64_t value = (uint64_t)f.start;
+	const uint64_t step = f.form == FLS_VEC_FORM_SEQUENCE ? (uint64_t)f.increment : 0;
+	for (idx_t i = 0; i < n; ++i, value += step) {
+		out[i] = (T)value;
+	}
+}
+} // namespace
+
+// One chunk (at most two FastLanes vectors) of a column scanned in compact form: a zero-copy FLAT vector when both halves
+// sit side by side in the packed staging buffer, a CONSTANT / SEQUENCE vector when the halves continue each other
+// (constant_kernel.hpp:19-27 does the former for constant chunks), else the chunk is put together in a chunk-sized buffer.
+void FastLanesReader::FormedVector(FastLanesReadLocalState& ls, size_t ri, idx_t first_vector, idx_t count, Vector& v) const {
+	const flsgpu_vector_form& f0 = ls.forms[ri][first_vector];
+	const bool two = count > FLS_VEC_SZ;
+	const flsgpu_vector_form& f1 = ls.forms[ri][first_vector + (two ? 1 : 0)];
+	const uint8_t* flat = static_cast<const uint8_t*>(ls.staging[ri].ptr);
+	const uint32_t w = v.type.physical_bytes;
+	if (f0.form == FLS_VEC_FORM_FLAT && (!two || (f1.form == FLS_VEC_FORM_FLAT && f1.flat_slot == f0.flat_slot + 1))) {
+		v.data = flat + (size_t)f0.flat_slot * FLS_VEC_SZ * w;
+		return;
+	}
+	if (f0.form != FLS_VEC_FORM_FLAT && f1.form != FLS_VEC_FORM_FLAT) {
+		const int64_t inc0 = f0.form == FLS_VEC_FORM_SEQUENCE ? f0.increment : 0, inc1 = f1.form == FLS_VEC_FORM_SEQUENCE ? f1.increment : 0;
+		if (!two || (inc0 == inc1 && f1.start == f0.start + inc0 * (int64_t)FLS_VEC_SZ)) {
+			v.vector_type = inc0 == 0 ? VectorType::CONSTANT_VECTOR : VectorType::SEQUENCE_VECTOR;
+			v.seq_start = f0.start;
+			v.seq_increment = inc0;
+			return;
+		}
+	}
+	std::vector<uint64_t>& buf = ls.assembled[ri];
+	buf.resize(STANDARD_VECTOR_SIZE);
+	const idx_t n0 = std::min<idx_t>(count, FLS_VEC_SZ), n1 = count - n0;
+	switch (w) {
+	case 1: FillForm(f0, flat, reinterpret_cast<uint8_t*>(buf.data()), n0); FillForm(f1, flat, reinterpret_cast<uint8_t*>(buf.data()) + n0, n1); break;
+	case 2: FillForm(f0, flat, reinterpret_cast<uint16_t*>(buf.data()), n0); FillForm(f1, flat, reinterpret_cast<uint16_t*>(buf.data()) + n0, n1); break;
+	case 4: FillForm(f0, flat, reinterpret_cast<uint32_t*>(buf.data()), n0); FillForm(f1, flat, reinterpret_cast<uint32_t*>(buf.data()) + n0, n1); break;
+	default: FillForm(f0, flat, buf.data(), n0); FillForm(f1, flat, buf.data() + n0, n1); break;
+	}
+	v.data = buf.data();
+	ls.n_assembled++;
 }
 
 // FastLanesReader::PopulateVirtualColumns (fls_reader.cpp:474-495): file_row_number = row_group_base + start + i
@@ -412,7 +473,7 @@ void FastLanesReader::Scan(FastLanesReadGlobalState&, FastLanesReadLocalState& l
 			ls.cur_vector = 0;
 			continue;
 		}
-		DecodePhysicalColumns(ls, chunk, ls.cur_vector, batch.input_vector_count);
+		DecodePhysicalColumns(ls, chunk, ls.cur_vector, batch.count);
 		const idx_t row_start = ls.row_group_base + batch.start_tuple;
 		PopulateVirtualColumns(ls, chunk, row_start, batch.count);
 		chunk.SetCardinality(batch.count);

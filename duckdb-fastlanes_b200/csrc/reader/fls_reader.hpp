@@ -66,11 +66,14 @@ struct FastLanesFileReaderOptions {
 	bool file_row_number = false;
 	// GPU-side knobs (no reference counterpart)
 	idx_t rowgroups_per_batch = 32;
+	// hand vectors the file marks CONSTANT / arithmetic SEQUENCE on in that form (the reference does it for constant chunks:
+	// constant_kernel.hpp:19-27) instead of decoding and copying them; the extension's setting fastlanes_compressed_vectors
+	bool compressed_vectors = true;
 };
 
 // Stand-in for duckdb::Vector / DataChunk; data is owned by the reader's staging buffers (FlatVector::SetData /
 // Vector::Dictionary style hand-off, dictionary_kernel.hpp:80-101).
-enum class VectorType : uint8_t { FLAT_VECTOR, DICTIONARY_VECTOR };
+enum class VectorType : uint8_t { FLAT_VECTOR, DICTIONARY_VECTOR, CONSTANT_VECTOR, SEQUENCE_VECTOR };
 struct Vector {
 	LogicalType type;
 	VectorType vector_type = VectorType::FLAT_VECTOR;
@@ -78,10 +81,20 @@ struct Vector {
 	const uint32_t* sel = nullptr; // DICTIONARY: selection vector, one entry per row of the (unsliced) chunk
 	idx_t dict_size = 0;
 	bool all_null = false;         // CONSTANT NULL vector: a union_by_name column this file does not have
-	// value of (unsliced) row i as a pointer to its physical representation
+	int64_t seq_start = 0, seq_increment = 0; // CONSTANT: the value (physical word); SEQUENCE: start + i * increment
+	// value of (unsliced) row i as a pointer to its physical representation (FLAT / DICTIONARY vectors)
 	const void* Row(idx_t i) const {
 		const idx_t k = vector_type == VectorType::DICTIONARY_VECTOR ? sel[i] : i;
 		return static_cast<const uint8_t*>(data) + k * type.physical_bytes;
+	}
+	// value of (unsliced) row i copied to dst, whatever the vector type (numeric columns)
+	void CopyRow(idx_t i, void* dst) const {
+		if (vector_type == VectorType::CONSTANT_VECTOR || vector_type == VectorType::SEQUENCE_VECTOR) {
+			const uint64_t v = (uint64_t)seq_start + (uint64_t)seq_increment * (vector_type == VectorType::SEQUENCE_VECTOR ? i : 0);
+			__builtin_memcpy(dst, &v, type.physical_bytes); // little endian: the low bytes are the value
+		} else {
+			__builtin_memcpy(dst, Row(i), type.physical_bytes);
+		}
 	}
 };
 struct DataChunk {
@@ -139,6 +152,11 @@ struct FastLanesReadLocalState { // fls_multi_file_info.hpp:57-77
 	// string columns: string heap, dictionary keys (dictionary form) and the first key of every row group of the batch
 	std::vector<PinnedBuffer> heaps, keys;
 	std::vector<uint8_t> dict_form;
+	// compact scans: the form of every vector of the batch per reader column (empty: scanned in place), and a chunk-sized
+	// buffer per reader column for chunks whose two halves do not continue each other
+	std::vector<std::vector<flsgpu_vector_form>> forms;
+	std::vector<std::vector<uint64_t>> assembled;
+	idx_t n_assembled = 0; // chunks that had to be put together on the host (reported by the scan statistics)
 	std::vector<std::vector<idx_t>> key_offsets;
 	PinnedBuffer mask;                    // selection mask of the pushed-down filters for the batch
 	bool has_mask = false;
@@ -208,6 +226,9 @@ public:
 	flsgpu_table* Table() const {
 		return table;
 	}
+	void SetCompressedVectors(bool on) {
+		reader_options.compressed_vectors = on;
+	}
 
 private:
 	struct ScanBatch {
@@ -222,7 +243,8 @@ private:
 	bool TryAssignNextRowGroup(FastLanesReadGlobalState& global_state, FastLanesReadLocalState& local_state);
 	void DecodeRowGroupBatch(FastLanesReadLocalState& local_state);
 	ScanBatch GetScanBatch(const FastLanesReadLocalState& local_state) const;
-	void DecodePhysicalColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t input_vector_count);
+	void DecodePhysicalColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t count);
+	void FormedVector(FastLanesReadLocalState& local_state, size_t reader_column, idx_t first_vector, idx_t count, Vector& v) const;
 	void PopulateVirtualColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t row_start, idx_t count);
 	void ApplyFilters(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t count) const;
 	std::vector<flsgpu_filter> PhysicalFilters() const;

@@ -133,7 +133,7 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 		is_str[c] = cols[column_ids[c]].type.id == LogicalTypeId::VARCHAR || cols[column_ids[c]].type.id == LogicalTypeId::BLOB;
 	}
 	FastLanesReadGlobalState gstate;
-	std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0}, dict_vectors {0}, cursor {0};
+	std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0}, dict_vectors {0}, constant_vectors {0}, sequence_vectors {0}, assembled {0}, cursor {0};
 	std::mutex err_mu;
 	std::string err;
 	int err_status = 0;
@@ -155,10 +155,17 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 						break;
 					}
 					const int64_t* frn = static_cast<const int64_t*>(chunk.data[n_cols].data);
+					assembled += lstate.n_assembled;
+					lstate.n_assembled = 0;
 					const uint64_t base = row_ids_out ? cursor.fetch_add(chunk.count) : (uint64_t)frn[0];
 					for (uint32_t c = 0; c < n_cols; ++c) {
 						const Vector& v = chunk.data[c];
 						dict_vectors += v.vector_type == VectorType::DICTIONARY_VECTOR ? 1 : 0;
+						constant_vectors += v.vector_type == VectorType::CONSTANT_VECTOR ? 1 : 0;
+						sequence_vectors += v.vector_type == VectorType::SEQUENCE_VECTOR ? 1 : 0;
+						if (!out_cols || !out_cols[c]) {
+							continue; // the consumer takes the vector as it is (what DuckDB's operators do): nothing is copied
+						}
 						if (is_str[c]) {
 							const flsreader_string_sink* sink = static_cast<const flsreader_string_sink*>(out_cols[c]);
 							for (idx_t i = 0; i < chunk.count; ++i) {
@@ -173,7 +180,7 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 							std::memcpy(static_cast<uint8_t*>(out_cols[c]) + base * widths[c], v.data, chunk.count * widths[c]);
 						} else {
 							for (idx_t i = 0; i < chunk.count; ++i) {
-								std::memcpy(static_cast<uint8_t*>(out_cols[c]) + (base + i) * widths[c], v.Row(chunk.RowIndex(i)), widths[c]);
+								v.CopyRow(chunk.RowIndex(i), static_cast<uint8_t*>(out_cols[c]) + (base + i) * widths[c]);
 							}
 						}
 					}
@@ -211,6 +218,9 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 	stats->chunks = chunks;
 	stats->max_chunk_rows = maxrows;
 	stats->dictionary_vectors = dict_vectors;
+	stats->constant_vectors = constant_vectors;
+	stats->sequence_vectors = sequence_vectors;
+	stats->assembled_vectors = assembled;
 	stats->pruned_rowgroups = reader.GetNPrunedRowGroups();
 }
 
@@ -224,6 +234,17 @@ int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t
 		*rows_out = st.rows;
 		*chunks_out = st.chunks;
 		*max_chunk_rows = st.max_chunk_rows;
+	})
+}
+
+int flsreader_set_option(flsreader_handle* h, const char* key, uint64_t value) {
+	FLSR_TRY({
+		const std::string k = key ? key : "";
+		if (k == "compressed_vectors") {
+			h->reader->SetCompressedVectors(value != 0);
+		} else {
+			throw ReaderError(FLSGPU_ERR_INVALID, "unknown reader option: " + k);
+		}
 	})
 }
 
@@ -346,17 +367,16 @@ int flsmulti_scan(flsmulti_handle* h, const uint64_t* column_ids, uint32_t n_col
 							if (v.all_null) {
 								continue;
 							}
-							const void* src = v.Row(chunk.RowIndex(i));
 							if (is_str[c]) {
 								const flsreader_string_sink* sink = static_cast<const flsreader_string_sink*>(out_cols[c]);
-								const string_t* sv = static_cast<const string_t*>(src);
+								const string_t* sv = static_cast<const string_t*>(v.Row(chunk.RowIndex(i)));
 								if (sv->GetSize() > sink->stride) {
 									throw ReaderError(FLSGPU_ERR_INVALID, "string longer than the sink's stride");
 								}
 								std::memcpy(sink->bytes + (base + i) * sink->stride, sv->GetData(), sv->GetSize());
 								sink->lengths[base + i] = sv->GetSize();
 							} else {
-								std::memcpy(static_cast<uint8_t*>(out_cols[c]) + (base + i) * widths[c], src, widths[c]);
+								v.CopyRow(chunk.RowIndex(i), static_cast<uint8_t*>(out_cols[c]) + (base + i) * widths[c]);
 							}
 						}
 					}

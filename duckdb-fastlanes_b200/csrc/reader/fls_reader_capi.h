@@ -27,7 +27,9 @@ int flsreader_statistics(const flsreader_handle* h, const char* name, int* has_s
  * column id == n_columns (with file_row_number enabled) selects the virtual column. */
 int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, int n_threads, void* const* out_cols,
                        uint64_t* rows_out, uint64_t* chunks_out, uint64_t* max_chunk_rows);
-/* General form: string columns (VARCHAR / BLOB) are written through a fixed-stride sink (out_cols[c] points at a
+/* out_cols (or one of its entries) may be NULL: that column's chunks are produced and counted but not copied anywhere - the
+ * consumer takes each vector as it is, like a DuckDB operator (the bench's end-to-end scan).
+ * General form: string columns (VARCHAR / BLOB) are written through a fixed-stride sink (out_cols[c] points at a
  * flsreader_string_sink), optional pushed-down filters (column_index addresses column_ids, constants are physical values
  * as in flsgpu_filter).  With filters the passing rows are appended in arrival order and row_ids_out receives their file
  * row numbers; without, rows land at their file row number and row_ids_out is ignored. */
@@ -47,7 +49,12 @@ typedef struct flsreader_scan_stats {
 	uint64_t rows, chunks, max_chunk_rows;
 	uint64_t dictionary_vectors; /* vectors handed over as DICTIONARY_VECTOR (dictionary_kernel.hpp:80-101) */
 	uint64_t pruned_rowgroups;   /* row groups the zone maps ruled out (row_group_filter.cpp:80-94) */
+	uint64_t constant_vectors;   /* vectors handed over as CONSTANT_VECTOR (constant_kernel.hpp:19-27) */
+	uint64_t sequence_vectors;   /* ... as SEQUENCE_VECTOR (start + i * increment) */
+	uint64_t assembled_vectors;  /* chunks put together on the host because their two halves had different forms */
 } flsreader_scan_stats;
+/* Reader options without a named parameter of read_fls: "compressed_vectors" (default 1). */
+int flsreader_set_option(flsreader_handle* h, const char* key, uint64_t value);
 int flsreader_scan(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
                    int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats);
 /* ---- read_fls over several files: FastLanesMultiFileInfo + MultiFileReader semantics (csrc/reader/fls_multi_file.hpp) ---- */

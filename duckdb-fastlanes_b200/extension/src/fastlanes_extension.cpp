@@ -17,6 +17,10 @@ static void RegisterSettings(ExtensionLoader &loader) {
 	config.AddExtensionOption("fastlanes_rowgroups_per_batch",
 	                          "Row groups a read_fls worker decodes per GPU call (the reference hands out one at a time)",
 	                          LogicalType::UBIGINT, Value::UBIGINT(32));
+	config.AddExtensionOption("fastlanes_compressed_vectors",
+	                          "Hand vectors the file marks CONSTANT or arithmetic SEQUENCE to DuckDB as CONSTANT / SEQUENCE vectors "
+	                          "instead of decoding and copying them",
+	                          LogicalType::BOOLEAN, Value::BOOLEAN(true));
 	config.AddExtensionOption("fastlanes_gpu_devices",
 	                          "Comma separated CUDA device ordinals read_fls shards row groups over (empty: device 0)",
 	                          LogicalType::VARCHAR, Value(""));

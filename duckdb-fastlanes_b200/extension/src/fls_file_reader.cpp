@@ -130,6 +130,9 @@ void FastLanesReader::Initialize(ClientContext &context) {
 	if (context.TryGetCurrentSetting("fastlanes_rowgroups_per_batch", setting) && !setting.IsNull()) {
 		rowgroups_per_batch = MaxValue<idx_t>(1, setting.GetValue<uint64_t>());
 	}
+	if (context.TryGetCurrentSetting("fastlanes_compressed_vectors", setting) && !setting.IsNull()) {
+		compressed_vectors = setting.GetValue<bool>();
+	}
 }
 
 void FastLanesReader::EnsureFileRowNumberColumn() {
@@ -462,7 +465,18 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 		} else {
 			stage.value_bytes = GetTypeIdSize(physical);
 		}
-		ReservePinned(stage.rows, rows * stage.value_bytes);
+		stage.forms.clear();
+		idx_t stage_rows = rows;
+		if (!stage.is_string && compressed_vectors) {
+			// vectors the writer marked CONSTANT or arithmetic SEQUENCE are handed to DuckDB in that form (the reference
+			// does so for dec_constant_opr: constant_kernel.hpp:19-27): only the FLAT vectors are decoded and cross PCIe
+			uint64_t n_flat = 0;
+			stage.forms.resize(idx_t(n_rg) * info.vec_per_rowgroup);
+			FlsCheck(flsgpu_column_vector_forms(table, ids[i], rg0, n_rg, stage.forms.data(), &n_flat), "flsgpu_column_vector_forms");
+			sc.compact = 1;
+			stage_rows = n_flat * FLS_VEC_SZ;
+		}
+		ReservePinned(stage.rows, stage_rows * stage.value_bytes);
 		sc.out_host = stage.rows->ptr;
 		sc.out_capacity_bytes = stage.rows->bytes;
 	}
@@ -504,6 +518,9 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 	const idx_t rg_in_batch = ls.cur_rowgroup - ls.batch_begin;
 	const idx_t first_row = (rg_in_batch * info.vec_per_rowgroup + start_vector) * FLS_VEC_SZ;
 	idx_t n_conversions = 0;
+	if (ls.conversion_executor) {
+		ls.conversion_input.Reset(); // back to its own buffers: the last chunk left references to the staging memory
+	}
 	for (idx_t i = 0; i < column_ids.size(); i++) {
 		const auto reader_idx = ls.projection.output_to_reader_idx[i];
 		if (!reader_idx.IsValid()) {
@@ -532,6 +549,10 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 			DictionaryVector::SetDictionaryId(target, stage.dictionary_ids[rg_in_batch]);
 			continue;
 		}
+		if (!stage.forms.empty()) {
+			FormedVector(stage, type, (rg_in_batch * info.vec_per_rowgroup + start_vector), count, target);
+			continue;
+		}
 		Vector view(type, stage.rows->ptr + first_row * stage.value_bytes);
 		if (stage.is_string) {
 			StringVector::AddBuffer(view, stage.rows);
@@ -556,6 +577,74 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 				n_conversions++;
 			}
 		}
+	}
+}
+
+template <class T>
+static void FillForm(const flsgpu_vector_form &form, const data_ptr_t flat, T *out, idx_t n) {
+	if (form.form == FLS_VEC_FORM_FLAT) {
+		std::memcpy(out, flat + idx_t(form.flat_slot) * FLS_VEC_SZ * sizeof(T), n * sizeof(T));
+		return;
+	}
+	// CONSTANT / SEQUENCE: start + i * increment, exact in the column's type (flsgpu_column_vector_forms guarantees it)
+	uint64_t value = static_cast<uint64_t>(form.start);
+	const uint64_t step = form.form == FLS_VEC_FORM_SEQUENCE ? static_cast<uint64_t>(form.increment) : 0;
+	for (idx_t i = 0; i < n; i++, value += step) {
+		out[i] = static_cast<T>(value);
+	}
+}
+
+// One chunk (at most two FastLanes vectors) of a column scanned in compact form: zero-copy FLAT when both vectors sit side
+// by side in the packed buffer, CONSTANT_VECTOR / SEQUENCE_VECTOR when the forms of both halves continue each other, else the
+// chunk is put together in the vector's own buffer (a copy of the FLAT half, the other half generated).
+void FastLanesReader::FormedVector(FlsColumnStage &stage, const LogicalType &type, idx_t first_vector, idx_t count, Vector &target) {
+	const auto &f0 = stage.forms[first_vector];
+	const bool two = count > FLS_VEC_SZ;
+	const auto &f1 = stage.forms[first_vector + (two ? 1 : 0)];
+	if (f0.form == FLS_VEC_FORM_FLAT && (!two || (f1.form == FLS_VEC_FORM_FLAT && f1.flat_slot == f0.flat_slot + 1))) {
+		Vector view(type, stage.rows->ptr + idx_t(f0.flat_slot) * FLS_VEC_SZ * stage.value_bytes);
+		view.SetAuxiliary(stage.rows);
+		target.Reference(view);
+		return;
+	}
+	const auto physical = type.InternalType();
+	if (f0.form != FLS_VEC_FORM_FLAT && f1.form != FLS_VEC_FORM_FLAT) {
+		const int64_t inc0 = f0.form == FLS_VEC_FORM_SEQUENCE ? f0.increment : 0, inc1 = f1.form == FLS_VEC_FORM_SEQUENCE ? f1.increment : 0;
+		const bool continues = !two || (inc0 == inc1 && f1.start == f0.start + inc0 * int64_t(FLS_VEC_SZ));
+		if (continues && inc0 == 0) { // CONSTANT_VECTOR
+			target.SetVectorType(VectorType::CONSTANT_VECTOR);
+			ConstantVector::SetNull(target, false);
+			std::memcpy(ConstantVector::GetData(target), &f0.start, stage.value_bytes); // little endian: the low bytes are the value
+			return;
+		}
+		// DuckDB generates sequences for signed integer vectors only (generators.cpp:30-50)
+		const bool sequence_type = type.IsNumeric() && (physical == PhysicalType::INT8 || physical == PhysicalType::INT16 ||
+		                                                physical == PhysicalType::INT32 || physical == PhysicalType::INT64);
+		if (continues && sequence_type) {
+			target.Sequence(f0.start, inc0, count);
+			return;
+		}
+	}
+	target.SetVectorType(VectorType::FLAT_VECTOR);
+	const auto out = FlatVector::GetData(target);
+	const idx_t n0 = MinValue<idx_t>(count, FLS_VEC_SZ), n1 = count - n0;
+	switch (stage.value_bytes) {
+	case 1:
+		FillForm<uint8_t>(f0, stage.rows->ptr, reinterpret_cast<uint8_t *>(out), n0);
+		FillForm<uint8_t>(f1, stage.rows->ptr, reinterpret_cast<uint8_t *>(out) + n0, n1);
+		break;
+	case 2:
+		FillForm<uint16_t>(f0, stage.rows->ptr, reinterpret_cast<uint16_t *>(out), n0);
+		FillForm<uint16_t>(f1, stage.rows->ptr, reinterpret_cast<uint16_t *>(out) + n0, n1);
+		break;
+	case 4:
+		FillForm<uint32_t>(f0, stage.rows->ptr, reinterpret_cast<uint32_t *>(out), n0);
+		FillForm<uint32_t>(f1, stage.rows->ptr, reinterpret_cast<uint32_t *>(out) + n0, n1);
+		break;
+	default:
+		FillForm<uint64_t>(f0, stage.rows->ptr, reinterpret_cast<uint64_t *>(out), n0);
+		FillForm<uint64_t>(f1, stage.rows->ptr, reinterpret_cast<uint64_t *>(out) + n0, n1);
+		break;
 	}
 }
 
@@ -635,7 +724,7 @@ void FastLanesReader::Scan(ClientContext &, GlobalTableFunctionState &, LocalTab
 					input_types.push_back(columns[column_ids[MultiFileLocalIndex(i)].GetId()].type);
 				}
 			}
-			ls.conversion_input.InitializeEmpty(input_types);
+			ls.conversion_input.Initialize(Allocator::DefaultAllocator(), input_types);
 		}
 	}
 	while (true) {

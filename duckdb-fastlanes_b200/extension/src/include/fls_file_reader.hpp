@@ -86,6 +86,8 @@ struct FlsColumnStage {
 	vector<idx_t> key_offsets;        // dictionary form: first key of every row group of the batch (+ total)
 	vector<unique_ptr<Vector>> dictionaries; // dictionary form: the DuckDB dictionary of each row group, built on first use
 	vector<string> dictionary_ids;           // ... and its process-wide unique dictionary id
+	//! Compact scans: the form of every vector of the batch (flsgpu_column_vector_forms); `rows` then holds only the FLAT ones
+	vector<flsgpu_vector_form> forms;
 };
 
 struct FastLanesReadLocalState : public LocalTableFunctionState {
@@ -180,6 +182,7 @@ private:
 	void DecodeRowGroupBatch(FastLanesReadLocalState &local_state);
 	ScanBatch GetScanBatch(const FastLanesReadLocalState &local_state) const;
 	void DecodePhysicalColumns(FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t start_vector, idx_t count);
+	void FormedVector(FlsColumnStage &stage, const LogicalType &type, idx_t first_vector, idx_t count, Vector &target);
 	void PopulateVirtualColumns(const FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t row_start, idx_t count);
 	void ApplyFilters(FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t start_vector, idx_t count);
 	FastLanesReaderProjectionPlan BuildReaderProjectionPlan();
@@ -197,6 +200,8 @@ private:
 	optional_idx file_row_number_local_idx;
 	FastLanesFileReaderOptions reader_options;
 	idx_t rowgroups_per_batch = 32;
+	//! Hand CONSTANT / SEQUENCE vectors to DuckDB as such instead of decoding them (setting fastlanes_compressed_vectors)
+	bool compressed_vectors = true;
 	//! RowGroupFilter of the reference (row_group_filter.cpp:62-94): row groups whose zone maps cannot satisfy the filters
 	//! are never handed out.  Built once per scan under rowgroup_filter_lock.
 	std::mutex rowgroup_filter_lock;

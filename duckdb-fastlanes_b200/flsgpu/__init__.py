@@ -40,12 +40,14 @@ class ColumnSpec(C.Structure):
 
 
 class ScanColumn(C.Structure):  # flsgpu_scan_column
-    _fields_ = [("col", C.c_uint32), ("out_type", C.c_int32), ("string_form", C.c_int32), ("reserved", C.c_uint32),
+    _fields_ = [("col", C.c_uint32), ("out_type", C.c_int32), ("string_form", C.c_int32), ("compact", C.c_uint32),
                 ("out_host", C.c_void_p), ("out_capacity_bytes", C.c_uint64), ("heap_host", C.c_void_p),
                 ("heap_capacity_bytes", C.c_uint64), ("keys_host", C.c_void_p), ("keys_capacity_bytes", C.c_uint64)]
 
 
 STRING_FLAT, STRING_DICTIONARY = 0, 1
+FORM_FLAT, FORM_CONSTANT, FORM_SEQUENCE = 0, 1, 2
+VECTOR_FORM = np.dtype([("start", "<i8"), ("increment", "<i8"), ("form", "<u4"), ("flat_slot", "<u4")])  # flsgpu_vector_form
 CMP = dict(EQ=0, NE=1, LT=2, LE=3, GT=4, GE=5)
 
 
@@ -150,7 +152,7 @@ ABI_SYMBOLS = [
     "flsgpu_string_dict_keys", "flsgpu_scan_strings_to_host", "flsgpu_scan_projection_to_host",
     "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked", "flsgpu_scan_filtered_to_host",
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
-    "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups",
+    "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms",
 ]
 
 
@@ -379,6 +381,14 @@ class Table:
         arr = (ScanColumn * len(scan_columns))(*scan_columns)
         _check(lib.flsgpu_scan_filtered_to_host(self._h, arr, len(scan_columns), make_filters(filters), len(filters), rg_begin, n_rg,
                                                 _vp(mask_host_ptr), C.c_uint64(mask_bytes)), "scan_filtered_to_host")
+
+    def vector_forms(self, col, rg_begin=0, n_rg=None):
+        """(forms: structured array of VECTOR_FORM per vector of the range, n_flat)."""
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        out = np.zeros(n_rg * self.vec_per_rowgroup, dtype=VECTOR_FORM)
+        n_flat = C.c_uint64()
+        _check(lib.flsgpu_column_vector_forms(self._h, col, rg_begin, n_rg, _vp(out.ctypes.data), C.byref(n_flat)), "column_vector_forms")
+        return out, n_flat.value
 
     def scan_projection_to_host(self, scan_columns, rg_begin=0, n_rg=None):
         """scan_columns: list of ScanColumn."""

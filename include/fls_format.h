@@ -153,11 +153,21 @@ typedef struct fls_vec_meta { /* 32 bytes */
 	uint16_t aux_cnt;    /* #exceptions (stored in the blob's tail) | #runs of this vector */
 	uint8_t width;       /* packed bit width W in [0,T] */
 	uint8_t width2;      /* ALP_RD: bit width of the left-part codes */
-	uint8_t e;           /* ALP exponent */
+	uint8_t e;           /* ALP exponent; DELTA: vector form mark (FLS_VEC_FORM_*) */
 	uint8_t f;           /* ALP factor */
 	uint16_t n_valid;    /* tuples of this vector that exist (last vector of a row group may be partial) */
-	uint64_t reserved;
+	uint64_t reserved;   /* DELTA vectors marked FLS_VEC_FORM_SEQUENCE: value(0), zero-extended physical word */
 } fls_vec_meta;
+
+/* Vector forms a reader may hand on WITHOUT decoding, the way the reference hands a dec_constant_opr chunk to DuckDB as a
+ * CONSTANT_VECTOR (constant_kernel.hpp:19-27).  They are facts the writer established from the data and recorded in the
+ * entry point; the packed blob is complete either way, so every decoder may ignore them.
+ *   CONSTANT: chunk encoding CONSTANT, or an FFOR vector of width 0 without exceptions (every value = base)
+ *   SEQUENCE: a DELTA vector of width 0 whose fls_vec_meta.e == FLS_VEC_FORM_SEQUENCE:
+ *             value(i) = reserved + i * base in arithmetic modulo 2^T, i = 0..1023 (DuckDB SEQUENCE_VECTOR, vector_type.hpp:20) */
+#define FLS_VEC_FORM_FLAT 0u
+#define FLS_VEC_FORM_CONSTANT 1u
+#define FLS_VEC_FORM_SEQUENCE 2u
 
 /* Per-vector blob layout in the DATA segment (sizes in bytes, every blob is a multiple of 16 and starts 16-aligned):
  *   FFOR / SLPATCH / ALP / FREQUENCY(W=0): [128*W packed][exception tail]

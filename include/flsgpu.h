@@ -100,6 +100,25 @@ int flsgpu_table_column(const flsgpu_table* t, uint32_t col, fls_column_desc* ou
 int flsgpu_table_rowgroup(const flsgpu_table* t, uint32_t rg, fls_rowgroup_desc* out);         /* fls_reader.cpp:129-138 */
 int flsgpu_table_chunk(const flsgpu_table* t, uint32_t rg, uint32_t col, fls_chunk_desc* out); /* row_group_statistics.cpp:60-127 */
 
+/* ---- vector forms: what can be handed to DuckDB without decoding ---------------------------------------------------------- */
+/* The reference hands a dec_constant_opr chunk to DuckDB as a CONSTANT_VECTOR instead of 1024 copies (constant_kernel.hpp:
+ * 19-27).  This container records two such facts per vector (fls_format.h FLS_VEC_FORM_*): CONSTANT and arithmetic SEQUENCE
+ * (DuckDB SEQUENCE_VECTOR: start + i * increment).  Such vectors need no decode, no HBM traffic and - what matters for a
+ * host-fed scan - no PCIe transfer of decoded bytes.  Host only: reads entry points of the container image. */
+typedef struct flsgpu_vector_form { /* 24 bytes */
+	int64_t start;      /* CONSTANT: the value, SEQUENCE: value(0).  Integers sign- / zero-extended by the column's signedness
+	                       (like flsgpu_filter.constant), FLOAT bits in the low word, DOUBLE bits */
+	int64_t increment;  /* SEQUENCE: value(i) = start + i * increment for i = 0..1023, exact in the column's type: a vector whose
+	                       progression would wrap around inside the type, or leave int64, is reported FLAT */
+	uint32_t form;      /* FLS_VEC_FORM_FLAT / _CONSTANT / _SEQUENCE */
+	uint32_t flat_slot; /* FLAT: rank of the vector among the FLAT vectors of the range = its 1024-value slot in the output of
+	                       a compact scan (flsgpu_scan_column.compact); 0xffffffff otherwise */
+} flsgpu_vector_form;
+/* out[(r - rg_begin) * vec_per_rowgroup + v] for every vector of the range (vectors a short row group does not have:
+ * CONSTANT 0); *n_flat (may be NULL) = number of FLAT vectors.  String columns: every vector FLAT. */
+int flsgpu_column_vector_forms(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, flsgpu_vector_form* out,
+                               uint64_t* n_flat);
+
 /* ---- staging: get_rowgroup_reader (fls_reader.cpp:615-618) -------------------------------------------- */
 /* Copy the compressed image of row groups [rg_begin, rg_begin+n_rg) to HBM (pinned host -> device, async on
  * `stream`) and build the device descriptor tables.  No-op for row groups already resident. */
@@ -234,7 +253,9 @@ typedef struct flsgpu_scan_column {
 	uint32_t col;
 	int32_t out_type;           /* numeric columns: flsgpu_out_type */
 	int32_t string_form;        /* string columns: flsgpu_string_form */
-	uint32_t reserved;
+	uint32_t compact;           /* numeric columns, 1: only the FLAT vectors of flsgpu_column_vector_forms are decoded and copied;
+	                               vector k of them lands at element flat_slot * 1024 of out_host (CONSTANT / SEQUENCE vectors
+	                               cost nothing: the caller builds them from their form).  out_capacity_bytes >= n_flat * 1024 * width */
 	void* out_host;             /* rows of the column, layout of flsgpu_decode_column */
 	uint64_t out_capacity_bytes;
 	void* heap_host;            /* string columns: >= flsgpu_string_heap_bytes; string_t pointers point into it */

@@ -40,7 +40,8 @@ def reader_filters(filters):
 
 class ScanStats(C.Structure):
     _fields_ = [("rows", C.c_uint64), ("chunks", C.c_uint64), ("max_chunk_rows", C.c_uint64), ("dictionary_vectors", C.c_uint64),
-                ("pruned_rowgroups", C.c_uint64)]
+                ("pruned_rowgroups", C.c_uint64), ("constant_vectors", C.c_uint64), ("sequence_vectors", C.c_uint64),
+                ("assembled_vectors", C.c_uint64)]
 NP_OF = {"BOOLEAN": np.uint8, "TINYINT": np.int8, "SMALLINT": np.int16, "INTEGER": np.int32, "BIGINT": np.int64,
          "UBIGINT": np.uint64, "FLOAT": np.float32, "DOUBLE": np.float64, "DATE": np.int32, "TIMESTAMP": np.int64}
 
@@ -154,8 +155,24 @@ class Reader:
             else:
                 cols.append(o[:m][order] if filters else o)
         stats = dict(rows=st.rows, chunks=st.chunks, max_chunk_rows=st.max_chunk_rows, dictionary_vectors=st.dictionary_vectors,
-                     pruned_rowgroups=st.pruned_rowgroups)
+                     pruned_rowgroups=st.pruned_rowgroups, constant_vectors=st.constant_vectors, sequence_vectors=st.sequence_vectors,
+                     assembled_vectors=st.assembled_vectors)
         return cols, (row_ids[:m][order] if filters else None), stats
+
+    def set_option(self, key, value):
+        rc = lib.flsreader_set_option(self._h, key.encode(), C.c_uint64(int(value)))
+        if rc:
+            raise ReaderError(rc)
+
+    def consume(self, column_ids=None, n_threads=1):
+        """The scan with a consumer that takes every vector as it is (nothing copied): what the bench times end to end."""
+        ids = list(range(len(self.columns))) if column_ids is None else list(column_ids)
+        ia = (C.c_uint64 * len(ids))(*ids)
+        st = ScanStats()
+        rc = lib.flsreader_scan(self._h, ia, len(ids), reader_filters(()), 0, n_threads, None, None, C.byref(st))
+        if rc:
+            raise ReaderError(rc)
+        return {k: getattr(st, k) for k, _ in ScanStats._fields_}
 
     def close(self):
         if self._h:
