@@ -483,15 +483,22 @@ int flsgpu_column_vector_forms(const flsgpu_table* t, uint32_t col, uint32_t rg_
 				const uint64_t mask = T >= 64 ? ~0ull : (1ull << T) - 1;
 				const uint64_t dw = m.base & mask;
 				const int64_t inc = (T < 64 && (dw >> (T - 1))) ? (int64_t)(dw | ~mask) : (int64_t)dw;
-				const __int128 start = cd.is_signed ? (__int128)extend(m.reserved) : (__int128)(m.reserved & mask);
-				const __int128 last = start + (__int128)inc * 1023;
-				const __int128 lo = cd.is_signed ? -((__int128)1 << (T - 1)) : 0;
-				__int128 hi = cd.is_signed ? ((__int128)1 << (T - 1)) - 1 : (__int128)mask;
-				if (hi > (__int128)INT64_MAX) {
-					hi = INT64_MAX;
+				// last = start + 1023 * inc, all in 64 bits with overflow detection (an unsigned column's values are kept as
+				// int64 too, so anything beyond INT64_MAX is out: DuckDB's Vector::Sequence takes int64)
+				const uint64_t sw = m.reserved & mask;
+				int64_t start, span, last;
+				bool ok = cd.is_signed || sw <= (uint64_t)INT64_MAX;
+				start = cd.is_signed ? extend(m.reserved) : (int64_t)sw;
+				ok = ok && !__builtin_mul_overflow(inc, (int64_t)1023, &span) && !__builtin_add_overflow(start, span, &last);
+				if (ok && T < 64) {
+					const int64_t lo = cd.is_signed ? -((int64_t)1 << (T - 1)) : 0;
+					const int64_t hi = cd.is_signed ? ((int64_t)1 << (T - 1)) - 1 : (int64_t)mask;
+					ok = start >= lo && start <= hi && last >= lo && last <= hi;
+				} else if (ok && !cd.is_signed) {
+					ok = last >= 0;
 				}
-				if (start >= lo && start <= hi && last >= lo && last <= hi) {
-					f.start = (int64_t)start;
+				if (ok) {
+					f.start = start;
 					f.increment = inc;
 					f.form = inc == 0 ? FLS_VEC_FORM_CONSTANT : FLS_VEC_FORM_SEQUENCE;
 					continue;

@@ -26,6 +26,7 @@
 namespace {
 
 std::atomic<uint64_t> g_launches {0};
+std::atomic<uint64_t> g_h2d_bytes {0}, g_d2h_bytes {0}; // bytes this process asked the copy engines to move (flsgpu_transfer_bytes)
 std::mutex g_mu; // guards device selection + per-function attribute cache
 int g_device = -1;
 int g_n_sms = 0;
@@ -98,6 +99,10 @@ struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of
 	cudaStream_t streams[2] = {nullptr, nullptr};
 	void* out[2] = {nullptr, nullptr};
 	uint64_t out_bytes = 0;
+	// compact scans: the vector maps of a slab are put together in pinned memory (an asynchronous copy out of pageable
+	// memory would first synchronise the stream, i.e. wait for the previous column's D2H copy)
+	uint32_t* map_host[2] = {nullptr, nullptr};
+	uint64_t map_bytes = 0;
 };
 
 struct FlsDeviceState {
@@ -141,6 +146,7 @@ void fls_device_release(flsgpu_table* t) {
 				cudaStreamDestroy(sc->streams[i]);
 			}
 			cudaFree(sc->out[i]);
+			cudaFreeHost(sc->map_host[i]);
 		}
 		delete sc;
 	}
@@ -328,6 +334,7 @@ int stage_range(flsgpu_table* t, FlsDeviceState* d, uint32_t rg_begin, uint32_t 
 			FLS_CUDA(cudaMemcpyAsync(d->d_image + run_begin, t->bytes + run_begin, run_end - run_begin, cudaMemcpyHostToDevice,
 			                         stream));
 			bytes += run_end - run_begin;
+			g_h2d_bytes.fetch_add(run_end - run_begin, std::memory_order_relaxed);
 		}
 		run_begin = run_end = 0;
 		return FLSGPU_OK;
@@ -872,7 +879,8 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		bool is_string = false, dict = false, compact = false;
 		uint64_t rg_bytes = 0;            // row bytes per row group (values, string_t or selection entries)
 		uint64_t dev_rows = 0, dev_heap = 0, dev_keys = 0, dev_map = 0; // offsets inside a slab's device scratch
-		std::vector<flsgpu_vector_form> forms; // compact: form of every vector of the range
+		std::vector<flsgpu_vector_form> own_forms; // compact: form of every vector of the range, unless the caller handed them in
+		const flsgpu_vector_form* forms = nullptr;
 	};
 	std::vector<std::vector<uint32_t>> vec_maps; // compact: the FLAT vectors of a (slab, column), alive until the streams drain
 	std::vector<ColPlan> cp(n_cols);
@@ -911,10 +919,22 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		uint64_t need_bytes = p.rg_bytes * n_rg;
 		if (p.compact) { // only the FLAT vectors of the range cross the link, packed
 			uint64_t n_flat = 0;
-			p.forms.resize((size_t)n_rg * h.vec_per_rowgroup);
-			rc = flsgpu_column_vector_forms(t, c.col, rg_begin, n_rg, p.forms.data(), &n_flat);
-			if (rc) {
-				return rc;
+			const size_t n_vec_all = (size_t)n_rg * h.vec_per_rowgroup;
+			if (c.forms) {
+				p.forms = c.forms;
+				for (size_t v = n_vec_all; v-- > 0;) { // slots are ranks: the last FLAT vector tells how many there are
+					if (c.forms[v].form == FLS_VEC_FORM_FLAT) {
+						n_flat = (uint64_t)c.forms[v].flat_slot + 1;
+						break;
+					}
+				}
+			} else {
+				p.own_forms.resize(n_vec_all);
+				rc = flsgpu_column_vector_forms(t, c.col, rg_begin, n_rg, p.own_forms.data(), &n_flat);
+				if (rc) {
+					return rc;
+				}
+				p.forms = p.own_forms.data();
 			}
 			need_bytes = n_flat * FLS_VEC_SZ * p.os.ob;
 		}
@@ -1007,6 +1027,23 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
 		}
 	}
+	uint64_t n_compact = 0;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		n_compact += cp[i].compact ? 1 : 0;
+	}
+	const uint64_t map_need = n_compact * slab_rg * h.vec_per_rowgroup * 4u;
+	if (sc->map_bytes < map_need) {
+		sc->map_bytes = 0;
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaFreeHost(sc->map_host[i]));
+			sc->map_host[i] = nullptr;
+		}
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&sc->map_host[i]), map_need, cudaHostAllocDefault));
+		}
+		sc->map_bytes = map_need;
+	}
+	bool slab_used[2] = {false, false};
 	std::vector<uint32_t> col_ids(n_cols);
 	for (uint32_t i = 0; i < n_cols; ++i) {
 		col_ids[i] = cols[i].col;
@@ -1022,10 +1059,20 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		if (status == FLSGPU_OK && bytes && cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s) != cudaSuccess) {
 			status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
 		}
+		g_d2h_bytes.fetch_add(bytes, std::memory_order_relaxed);
 	};
 	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
 		const uint32_t n = std::min(slab_rg, n_rg - r);
 		cudaStream_t s = sc->streams[slab & 1];
+		if (slab_used[slab & 1] && n_compact) { // this slab's pinned map area was last read by the copies of slab - 2
+			const cudaError_t e = cudaStreamSynchronize(s);
+			if (e != cudaSuccess) {
+				status = cuda_fail(e, "cudaStreamSynchronize");
+				break;
+			}
+		}
+		slab_used[slab & 1] = true;
+		uint64_t map_used = 0; // entries of sc->map_host[slab & 1] taken so far
 		// compact columns: the FLAT vectors of the slab (launch order = slot order) and the chunks that hold any
 		std::vector<uint8_t> need;
 		std::vector<uint32_t> map_of(n_cols, 0xffffffffu); // column -> index into vec_maps
@@ -1082,10 +1129,14 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 				const uint64_t slot0 = vm.empty() ? 0 : p.forms[(size_t)r * h.vec_per_rowgroup + vm[0]].flat_slot;
 				if (!vm.empty()) {
 					uint32_t* map_dev = reinterpret_cast<uint32_t*>(base + p.dev_map);
-					if (cudaMemcpyAsync(map_dev, vm.data(), vm.size() * 4u, cudaMemcpyHostToDevice, s) != cudaSuccess) {
+					uint32_t* map_pinned = sc->map_host[slab & 1] + map_used;
+					map_used += vm.size();
+					std::memcpy(map_pinned, vm.data(), vm.size() * 4u);
+					if (cudaMemcpyAsync(map_dev, map_pinned, vm.size() * 4u, cudaMemcpyHostToDevice, s) != cudaSuccess) {
 						status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(vector map)");
 						break;
 					}
+					g_h2d_bytes.fetch_add(vm.size() * 4u, std::memory_order_relaxed);
 					status = decode_column_impl(t, d, c.col, rg_begin + r, n, p.os, dev, s, nullptr, nullptr, map_dev, (uint32_t)vm.size());
 					d2h(static_cast<uint8_t*>(c.out_host) + slot0 * FLS_VEC_SZ * p.os.ob, dev, (uint64_t)vm.size() * FLS_VEC_SZ * p.os.ob, s);
 				}
@@ -1157,6 +1208,22 @@ int flsgpu_sync(void* cuda_stream) {
 	return FLSGPU_OK;
 }
 
+// Pinned allocations are cached: page-locking costs ~0.3 ms per MiB, and every scan of every query wants staging buffers of
+// the same few sizes (a worker's batch of row groups).  Freed blocks go to a free list (up to FLSGPU_HOST_POOL_MB, default
+// 8192, in total) and are handed out again to requests they fit without wasting more than half of the block.
+namespace {
+struct HostPool {
+	std::mutex mu;
+	std::map<void*, uint64_t> live;                  // block -> its real size
+	std::multimap<uint64_t, void*> free_blocks;      // size -> block
+	uint64_t cached = 0;
+};
+HostPool& host_pool() {
+	static HostPool* p = new HostPool(); // never destroyed: blocks may be returned during static destruction
+	return *p;
+}
+} // namespace
+
 int flsgpu_host_alloc(uint64_t bytes, void** out) {
 	if (!out) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_host_alloc: null argument");
@@ -1165,15 +1232,53 @@ int flsgpu_host_alloc(uint64_t bytes, void** out) {
 	if (rc) {
 		return rc;
 	}
-	FLS_CUDA(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+	const uint64_t want = bytes ? bytes : 1;
+	HostPool& hp = host_pool();
+	{
+		std::lock_guard<std::mutex> g(hp.mu);
+		auto it = hp.free_blocks.lower_bound(want);
+		if (it != hp.free_blocks.end() && it->first <= std::max<uint64_t>(2 * want, 1u << 20)) {
+			*out = it->second;
+			hp.cached -= it->first;
+			hp.free_blocks.erase(it);
+			return FLSGPU_OK;
+		}
+	}
+	FLS_CUDA(cudaHostAlloc(out, want, cudaHostAllocDefault));
+	std::lock_guard<std::mutex> g(hp.mu);
+	hp.live[*out] = want;
 	return FLSGPU_OK;
 }
 
 int flsgpu_host_free(void* p) {
-	if (p) {
-		FLS_CUDA(cudaFreeHost(p));
+	if (!p) {
+		return FLSGPU_OK;
 	}
+	static const uint64_t limit = (uint64_t)env_u32("FLSGPU_HOST_POOL_MB", 8192) << 20;
+	HostPool& hp = host_pool();
+	{
+		std::lock_guard<std::mutex> g(hp.mu);
+		auto it = hp.live.find(p);
+		if (it != hp.live.end() && hp.cached + it->second <= limit) {
+			hp.free_blocks.emplace(it->second, p);
+			hp.cached += it->second;
+			return FLSGPU_OK;
+		}
+		if (it != hp.live.end()) {
+			hp.live.erase(it);
+		}
+	}
+	FLS_CUDA(cudaFreeHost(p));
 	return FLSGPU_OK;
+}
+
+void flsgpu_transfer_bytes(uint64_t* h2d, uint64_t* d2h) {
+	if (h2d) {
+		*h2d = g_h2d_bytes.load(std::memory_order_relaxed);
+	}
+	if (d2h) {
+		*d2h = g_d2h_bytes.load(std::memory_order_relaxed);
+	}
 }
 
 uint64_t flsgpu_launch_count(void) {

@@ -211,7 +211,6 @@ bool FastLanesReader::TryInitializeScan(FastLanesReadGlobalState& gstate, FastLa
 	lstate.keys.resize(n_reader_cols);
 	lstate.dict_form.assign(n_reader_cols, 0);
 	lstate.forms.assign(n_reader_cols, {});
-	lstate.assembled.resize(n_reader_cols);
 	lstate.key_offsets.assign(n_reader_cols, {});
 	lstate.has_mask = false;
 	lstate.row_numbers.clear();
@@ -263,6 +262,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState& ls) {
 				ls.forms[i].resize((size_t)n_rg * info.vec_per_rowgroup);
 				Check(flsgpu_column_vector_forms(table, ids[i], rg0, n_rg, ls.forms[i].data(), &n_flat), "flsgpu_column_vector_forms");
 				c.compact = 1;
+				c.forms = ls.forms[i].data();
 				ls.staging[i].Reserve(std::max<uint64_t>(16, n_flat * FLS_VEC_SZ * type.physical_bytes));
 			} else {
 				ls.staging[i].Reserve(rows * type.physical_bytes);
@@ -349,6 +349,10 @@ FastLanesReader::ScanBatch FastLanesReader::GetScanBatch(const FastLanesReadLoca
 	}
 	const idx_t tuples_left = local_state.n_tuples - batch.start_tuple;
 	batch.count = std::min<idx_t>(tuples_left, FLS_VEC_SZ * 2);
+	if (batch.count > FLS_VEC_SZ && local_state.cur_vector != ~0ull &&
+	    !VectorsJoin(local_state, (local_state.cur_rowgroup - local_state.batch_begin) * info.vec_per_rowgroup + local_state.cur_vector)) {
+		batch.count = FLS_VEC_SZ;
+	}
 	batch.input_vector_count = (batch.count + FLS_VEC_SZ - 1) / FLS_VEC_SZ;
 	return batch;
 }
@@ -380,54 +384,40 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState& ls, DataChu
 	}
 }
 
-namespace {
-template <class T>
-void FillForm(const flsgpu_vector_form& f, const uint8_t* flat, T* out, idx_t n) {
-	if (f.form == FLS_VEC_FORM_FLAT) {
-		std::memcpy(out, flat + (size_t)f.flat_slot * FLS_VEC_SZ * sizeof(T), n * sizeof(T));
-		return;
-	}
-	uint64_t value = (uint64_t)f.start;
-	const uint64_t step = f.form == FLS_VEC_FORM_SEQUENCE ? (uint64_t)f.increment : 0;
-	for (idx_t i = 0; i < n; ++i, value += step) {
-		out[i] = (T)value;
-	}
-}
-} // namespace
-
-// One chunk (at most two FastLanes vectors) of a column scanned in compact form: a zero-copy FLAT vector when both halves
-// sit side by side in the packed staging buffer, a CONSTANT / SEQUENCE vector when the halves continue each other
-// (constant_kernel.hpp:19-27 does the former for constant chunks), else the chunk is put together in a chunk-sized buffer.
-void FastLanesReader::FormedVector(FastLanesReadLocalState& ls, size_t ri, idx_t first_vector, idx_t count, Vector& v) const {
-	const flsgpu_vector_form& f0 = ls.forms[ri][first_vector];
-	const bool two = count > FLS_VEC_SZ;
-	const flsgpu_vector_form& f1 = ls.forms[ri][first_vector + (two ? 1 : 0)];
-	const uint8_t* flat = static_cast<const uint8_t*>(ls.staging[ri].ptr);
-	const uint32_t w = v.type.physical_bytes;
-	if (f0.form == FLS_VEC_FORM_FLAT && (!two || (f1.form == FLS_VEC_FORM_FLAT && f1.flat_slot == f0.flat_slot + 1))) {
-		v.data = flat + (size_t)f0.flat_slot * FLS_VEC_SZ * w;
-		return;
-	}
-	if (f0.form != FLS_VEC_FORM_FLAT && f1.form != FLS_VEC_FORM_FLAT) {
+// Do the two vectors of a would-be chunk continue each other in every compact column?  FLAT + FLAT side by side in the
+// packed buffer, or CONSTANT / SEQUENCE halves where the second takes up where the first ends.  If not, the chunk is cut
+// after its first vector (a chunk of 1024 rows, like the tail of a row group) so that every vector stays zero-copy.
+bool FastLanesReader::VectorsJoin(const FastLanesReadLocalState& ls, idx_t first_vector) const {
+	for (const auto& forms : ls.forms) {
+		if (forms.empty()) {
+			continue;
+		}
+		const flsgpu_vector_form &f0 = forms[first_vector], &f1 = forms[first_vector + 1];
+		if (f0.form == FLS_VEC_FORM_FLAT || f1.form == FLS_VEC_FORM_FLAT) {
+			if (f0.form != f1.form || f1.flat_slot != f0.flat_slot + 1) {
+				return false;
+			}
+			continue;
+		}
 		const int64_t inc0 = f0.form == FLS_VEC_FORM_SEQUENCE ? f0.increment : 0, inc1 = f1.form == FLS_VEC_FORM_SEQUENCE ? f1.increment : 0;
-		if (!two || (inc0 == inc1 && f1.start == f0.start + inc0 * (int64_t)FLS_VEC_SZ)) {
-			v.vector_type = inc0 == 0 ? VectorType::CONSTANT_VECTOR : VectorType::SEQUENCE_VECTOR;
-			v.seq_start = f0.start;
-			v.seq_increment = inc0;
-			return;
+		if (inc0 != inc1 || f1.start != f0.start + inc0 * (int64_t)FLS_VEC_SZ) {
+			return false;
 		}
 	}
-	std::vector<uint64_t>& buf = ls.assembled[ri];
-	buf.resize(STANDARD_VECTOR_SIZE);
-	const idx_t n0 = std::min<idx_t>(count, FLS_VEC_SZ), n1 = count - n0;
-	switch (w) {
-	case 1: FillForm(f0, flat, reinterpret_cast<uint8_t*>(buf.data()), n0); FillForm(f1, flat, reinterpret_cast<uint8_t*>(buf.data()) + n0, n1); break;
-	case 2: FillForm(f0, flat, reinterpret_cast<uint16_t*>(buf.data()), n0); FillForm(f1, flat, reinterpret_cast<uint16_t*>(buf.data()) + n0, n1); break;
-	case 4: FillForm(f0, flat, reinterpret_cast<uint32_t*>(buf.data()), n0); FillForm(f1, flat, reinterpret_cast<uint32_t*>(buf.data()) + n0, n1); break;
-	default: FillForm(f0, flat, buf.data(), n0); FillForm(f1, flat, buf.data() + n0, n1); break;
+	return true;
+}
+
+// One chunk of a column scanned in compact form (its vectors join, see VectorsJoin): a zero-copy FLAT slice of the packed
+// staging buffer, or a CONSTANT / SEQUENCE vector (constant_kernel.hpp:19-27 does the former for constant chunks).
+void FastLanesReader::FormedVector(FastLanesReadLocalState& ls, size_t ri, idx_t first_vector, idx_t, Vector& v) const {
+	const flsgpu_vector_form& f0 = ls.forms[ri][first_vector];
+	if (f0.form == FLS_VEC_FORM_FLAT) {
+		v.data = static_cast<const uint8_t*>(ls.staging[ri].ptr) + (size_t)f0.flat_slot * FLS_VEC_SZ * v.type.physical_bytes;
+		return;
 	}
-	v.data = buf.data();
-	ls.n_assembled++;
+	v.vector_type = f0.form == FLS_VEC_FORM_SEQUENCE ? VectorType::SEQUENCE_VECTOR : VectorType::CONSTANT_VECTOR;
+	v.seq_start = f0.start;
+	v.seq_increment = f0.form == FLS_VEC_FORM_SEQUENCE ? f0.increment : 0;
 }
 
 // FastLanesReader::PopulateVirtualColumns (fls_reader.cpp:474-495): file_row_number = row_group_base + start + i

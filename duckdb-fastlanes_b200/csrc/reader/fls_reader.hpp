@@ -152,11 +152,8 @@ struct FastLanesReadLocalState { // fls_multi_file_info.hpp:57-77
 	// string columns: string heap, dictionary keys (dictionary form) and the first key of every row group of the batch
 	std::vector<PinnedBuffer> heaps, keys;
 	std::vector<uint8_t> dict_form;
-	// compact scans: the form of every vector of the batch per reader column (empty: scanned in place), and a chunk-sized
-	// buffer per reader column for chunks whose two halves do not continue each other
+	// compact scans: the form of every vector of the batch per reader column (empty: scanned in place)
 	std::vector<std::vector<flsgpu_vector_form>> forms;
-	std::vector<std::vector<uint64_t>> assembled;
-	idx_t n_assembled = 0; // chunks that had to be put together on the host (reported by the scan statistics)
 	std::vector<std::vector<idx_t>> key_offsets;
 	PinnedBuffer mask;                    // selection mask of the pushed-down filters for the batch
 	bool has_mask = false;
@@ -244,6 +241,7 @@ private:
 	void DecodeRowGroupBatch(FastLanesReadLocalState& local_state);
 	ScanBatch GetScanBatch(const FastLanesReadLocalState& local_state) const;
 	void DecodePhysicalColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t count);
+	bool VectorsJoin(const FastLanesReadLocalState& local_state, idx_t first_vector) const;
 	void FormedVector(FastLanesReadLocalState& local_state, size_t reader_column, idx_t first_vector, idx_t count, Vector& v) const;
 	void PopulateVirtualColumns(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t row_start, idx_t count);
 	void ApplyFilters(FastLanesReadLocalState& local_state, DataChunk& chunk, idx_t start_vector, idx_t count) const;

@@ -109,7 +109,10 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 	FastLanesReader& reader = *h->reader;
 	// the driver appends file_row_number to the projection to know where each chunk belongs
 	reader.column_ids.assign(column_ids, column_ids + n_cols);
-	reader.column_ids.push_back(COLUMN_IDENTIFIER_FILE_ROW_NUMBER);
+	const bool place_rows = out_cols != nullptr || row_ids_out != nullptr; // a consumer that copies nothing needs no row numbers
+	if (place_rows) {
+		reader.column_ids.push_back(COLUMN_IDENTIFIER_FILE_ROW_NUMBER);
+	}
 	reader.filters.clear();
 	reader.ResetScan();
 	for (uint32_t i = 0; i < n_filters; ++i) {
@@ -133,7 +136,7 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 		is_str[c] = cols[column_ids[c]].type.id == LogicalTypeId::VARCHAR || cols[column_ids[c]].type.id == LogicalTypeId::BLOB;
 	}
 	FastLanesReadGlobalState gstate;
-	std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0}, dict_vectors {0}, constant_vectors {0}, sequence_vectors {0}, assembled {0}, cursor {0};
+	std::atomic<uint64_t> rows {0}, chunks {0}, maxrows {0}, dict_vectors {0}, constant_vectors {0}, sequence_vectors {0}, cursor {0};
 	std::mutex err_mu;
 	std::string err;
 	int err_status = 0;
@@ -142,6 +145,23 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 		try {
 			FastLanesReadLocalState lstate;
 			DataChunk chunk;
+			struct Tally { // folded into the shared counters once, when the worker is done
+				uint64_t rows = 0, chunks = 0, maxrows = 0, dict = 0, constant = 0, sequence = 0;
+			} tally;
+			struct Fold {
+				Tally& t;
+				std::atomic<uint64_t>&rows, &chunks, &maxrows, &dict, &constant, &sequence;
+				~Fold() {
+					rows += t.rows;
+					chunks += t.chunks;
+					dict += t.dict;
+					constant += t.constant;
+					sequence += t.sequence;
+					uint64_t m = maxrows.load();
+					while (t.maxrows > m && !maxrows.compare_exchange_weak(m, t.maxrows)) {
+					}
+				}
+			} fold {tally, rows, chunks, maxrows, dict_vectors, constant_vectors, sequence_vectors};
 			for (;;) {
 				{
 					std::lock_guard<std::mutex> g(gstate.lock);
@@ -154,15 +174,13 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 					if (chunk.count == 0) {
 						break;
 					}
-					const int64_t* frn = static_cast<const int64_t*>(chunk.data[n_cols].data);
-					assembled += lstate.n_assembled;
-					lstate.n_assembled = 0;
-					const uint64_t base = row_ids_out ? cursor.fetch_add(chunk.count) : (uint64_t)frn[0];
+					const int64_t* frn = place_rows ? static_cast<const int64_t*>(chunk.data[n_cols].data) : nullptr;
+					const uint64_t base = row_ids_out ? cursor.fetch_add(chunk.count) : frn ? (uint64_t)frn[0] : 0;
 					for (uint32_t c = 0; c < n_cols; ++c) {
 						const Vector& v = chunk.data[c];
-						dict_vectors += v.vector_type == VectorType::DICTIONARY_VECTOR ? 1 : 0;
-						constant_vectors += v.vector_type == VectorType::CONSTANT_VECTOR ? 1 : 0;
-						sequence_vectors += v.vector_type == VectorType::SEQUENCE_VECTOR ? 1 : 0;
+						tally.dict += v.vector_type == VectorType::DICTIONARY_VECTOR ? 1 : 0;
+						tally.constant += v.vector_type == VectorType::CONSTANT_VECTOR ? 1 : 0;
+						tally.sequence += v.vector_type == VectorType::SEQUENCE_VECTOR ? 1 : 0;
 						if (!out_cols || !out_cols[c]) {
 							continue; // the consumer takes the vector as it is (what DuckDB's operators do): nothing is copied
 						}
@@ -187,11 +205,9 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 					for (idx_t i = 0; row_ids_out && i < chunk.count; ++i) {
 						row_ids_out[base + i] = frn[chunk.RowIndex(i)];
 					}
-					rows += chunk.count;
-					chunks += 1;
-					uint64_t m = maxrows.load();
-					while (chunk.count > m && !maxrows.compare_exchange_weak(m, chunk.count)) {
-					}
+					tally.rows += chunk.count;
+					tally.chunks += 1;
+					tally.maxrows = std::max<uint64_t>(tally.maxrows, chunk.count);
 				}
 			}
 		} catch (const ReaderError& e) {
@@ -220,7 +236,7 @@ void scan_impl(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols,
 	stats->dictionary_vectors = dict_vectors;
 	stats->constant_vectors = constant_vectors;
 	stats->sequence_vectors = sequence_vectors;
-	stats->assembled_vectors = assembled;
+	stats->assembled_vectors = 0; // chunks are split where the forms of their halves differ: nothing is put together on the host
 	stats->pruned_rowgroups = reader.GetNPrunedRowGroups();
 }
 
@@ -234,6 +250,14 @@ int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t
 		*rows_out = st.rows;
 		*chunks_out = st.chunks;
 		*max_chunk_rows = st.max_chunk_rows;
+	})
+}
+
+int flsreader_evict(flsreader_handle* h) {
+	FLSR_TRY({
+		if (flsgpu_table_evict(h->reader->Table()) != FLSGPU_OK) {
+			throw ReaderError(FLSGPU_ERR_CUDA, flsgpu_last_error());
+		}
 	})
 }
 

@@ -55,6 +55,8 @@ typedef struct flsreader_scan_stats {
 } flsreader_scan_stats;
 /* Reader options without a named parameter of read_fls: "compressed_vectors" (default 1). */
 int flsreader_set_option(flsreader_handle* h, const char* key, uint64_t value);
+/* Forget which row groups are resident in HBM (the next scan stages them again): host-fed timing. */
+int flsreader_evict(flsreader_handle* h);
 int flsreader_scan(flsreader_handle* h, const uint64_t* column_ids, uint32_t n_cols, const flsreader_filter* filters, uint32_t n_filters,
                    int n_threads, void* const* out_cols, int64_t* row_ids_out, flsreader_scan_stats* stats);
 /* ---- read_fls over several files: FastLanesMultiFileInfo + MultiFileReader semantics (csrc/reader/fls_multi_file.hpp) ---- */

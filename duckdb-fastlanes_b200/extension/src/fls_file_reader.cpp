@@ -474,6 +474,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 			stage.forms.resize(idx_t(n_rg) * info.vec_per_rowgroup);
 			FlsCheck(flsgpu_column_vector_forms(table, ids[i], rg0, n_rg, stage.forms.data(), &n_flat), "flsgpu_column_vector_forms");
 			sc.compact = 1;
+			sc.forms = stage.forms.data();
 			stage_rows = n_flat * FLS_VEC_SZ;
 		}
 		ReservePinned(stage.rows, stage_rows * stage.value_bytes);
@@ -503,6 +504,10 @@ FastLanesReader::ScanBatch FastLanesReader::GetScanBatch(const FastLanesReadLoca
 		return batch;
 	}
 	batch.count = MinValue<idx_t>(local_state.n_tuples - batch.start_tuple, STANDARD_VECTOR_SIZE);
+	if (batch.count > FLS_VEC_SZ && local_state.batch_decoded &&
+	    !VectorsJoin(local_state, (local_state.cur_rowgroup - local_state.batch_begin) * info.vec_per_rowgroup + local_state.cur_vector)) {
+		batch.count = FLS_VEC_SZ;
+	}
 	batch.input_vector_count = (batch.count + FLS_VEC_SZ - 1) / FLS_VEC_SZ;
 	return batch;
 }
@@ -581,69 +586,74 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 }
 
 template <class T>
-static void FillForm(const flsgpu_vector_form &form, const data_ptr_t flat, T *out, idx_t n) {
-	if (form.form == FLS_VEC_FORM_FLAT) {
-		std::memcpy(out, flat + idx_t(form.flat_slot) * FLS_VEC_SZ * sizeof(T), n * sizeof(T));
-		return;
-	}
-	// CONSTANT / SEQUENCE: start + i * increment, exact in the column's type (flsgpu_column_vector_forms guarantees it)
-	uint64_t value = static_cast<uint64_t>(form.start);
-	const uint64_t step = form.form == FLS_VEC_FORM_SEQUENCE ? static_cast<uint64_t>(form.increment) : 0;
-	for (idx_t i = 0; i < n; i++, value += step) {
-		out[i] = static_cast<T>(value);
+static void GenerateSequence(int64_t start, int64_t increment, T *out, idx_t n) {
+	uint64_t value = static_cast<uint64_t>(start);
+	for (idx_t i = 0; i < n; i++, value += static_cast<uint64_t>(increment)) {
+		out[i] = static_cast<T>(value); // exact in the column's type: flsgpu_column_vector_forms guarantees it
 	}
 }
 
-// One chunk (at most two FastLanes vectors) of a column scanned in compact form: zero-copy FLAT when both vectors sit side
-// by side in the packed buffer, CONSTANT_VECTOR / SEQUENCE_VECTOR when the forms of both halves continue each other, else the
-// chunk is put together in the vector's own buffer (a copy of the FLAT half, the other half generated).
+// Do the two vectors of a would-be chunk continue each other in every compact column?  FLAT + FLAT side by side in the packed
+// buffer, or CONSTANT / SEQUENCE halves where the second takes up where the first ends.  If not, the chunk is cut after its
+// first vector (1024 rows, like the tail of a row group): every vector stays zero-copy, nothing is put together on the host.
+bool FastLanesReader::VectorsJoin(const FastLanesReadLocalState &ls, idx_t first_vector) const {
+	for (auto &stage : ls.stage) {
+		if (stage->forms.empty()) {
+			continue;
+		}
+		const auto &f0 = stage->forms[first_vector], &f1 = stage->forms[first_vector + 1];
+		if (f0.form == FLS_VEC_FORM_FLAT || f1.form == FLS_VEC_FORM_FLAT) {
+			if (f0.form != f1.form || f1.flat_slot != f0.flat_slot + 1) {
+				return false;
+			}
+			continue;
+		}
+		const int64_t inc0 = f0.form == FLS_VEC_FORM_SEQUENCE ? f0.increment : 0, inc1 = f1.form == FLS_VEC_FORM_SEQUENCE ? f1.increment : 0;
+		if (inc0 != inc1 || f1.start != f0.start + inc0 * int64_t(FLS_VEC_SZ)) {
+			return false;
+		}
+	}
+	return true;
+}
+
+// One chunk of a column scanned in compact form (its vectors join, see VectorsJoin): a zero-copy FLAT slice of the packed
+// staging buffer, a CONSTANT_VECTOR (what the reference emits for dec_constant_opr, constant_kernel.hpp:19-27) or a
+// SEQUENCE_VECTOR; types DuckDB has no sequence vectors for (unsigned, DATE, TIMESTAMP) get the sequence written out.
 void FastLanesReader::FormedVector(FlsColumnStage &stage, const LogicalType &type, idx_t first_vector, idx_t count, Vector &target) {
 	const auto &f0 = stage.forms[first_vector];
-	const bool two = count > FLS_VEC_SZ;
-	const auto &f1 = stage.forms[first_vector + (two ? 1 : 0)];
-	if (f0.form == FLS_VEC_FORM_FLAT && (!two || (f1.form == FLS_VEC_FORM_FLAT && f1.flat_slot == f0.flat_slot + 1))) {
+	if (f0.form == FLS_VEC_FORM_FLAT) {
 		Vector view(type, stage.rows->ptr + idx_t(f0.flat_slot) * FLS_VEC_SZ * stage.value_bytes);
 		view.SetAuxiliary(stage.rows);
 		target.Reference(view);
 		return;
 	}
 	const auto physical = type.InternalType();
-	if (f0.form != FLS_VEC_FORM_FLAT && f1.form != FLS_VEC_FORM_FLAT) {
-		const int64_t inc0 = f0.form == FLS_VEC_FORM_SEQUENCE ? f0.increment : 0, inc1 = f1.form == FLS_VEC_FORM_SEQUENCE ? f1.increment : 0;
-		const bool continues = !two || (inc0 == inc1 && f1.start == f0.start + inc0 * int64_t(FLS_VEC_SZ));
-		if (continues && inc0 == 0) { // CONSTANT_VECTOR
-			target.SetVectorType(VectorType::CONSTANT_VECTOR);
-			ConstantVector::SetNull(target, false);
-			std::memcpy(ConstantVector::GetData(target), &f0.start, stage.value_bytes); // little endian: the low bytes are the value
-			return;
-		}
-		// DuckDB generates sequences for signed integer vectors only (generators.cpp:30-50)
-		const bool sequence_type = type.IsNumeric() && (physical == PhysicalType::INT8 || physical == PhysicalType::INT16 ||
-		                                                physical == PhysicalType::INT32 || physical == PhysicalType::INT64);
-		if (continues && sequence_type) {
-			target.Sequence(f0.start, inc0, count);
-			return;
-		}
+	if (f0.form == FLS_VEC_FORM_CONSTANT) {
+		target.SetVectorType(VectorType::CONSTANT_VECTOR);
+		ConstantVector::SetNull(target, false);
+		std::memcpy(ConstantVector::GetData(target), &f0.start, stage.value_bytes); // little endian: the low bytes are the value
+		return;
+	}
+	// DuckDB generates sequences for signed integer vectors only (generators.cpp:30-50)
+	if (type.IsNumeric() && (physical == PhysicalType::INT8 || physical == PhysicalType::INT16 || physical == PhysicalType::INT32 ||
+	                         physical == PhysicalType::INT64)) {
+		target.Sequence(f0.start, f0.increment, count);
+		return;
 	}
 	target.SetVectorType(VectorType::FLAT_VECTOR);
 	const auto out = FlatVector::GetData(target);
-	const idx_t n0 = MinValue<idx_t>(count, FLS_VEC_SZ), n1 = count - n0;
 	switch (stage.value_bytes) {
 	case 1:
-		FillForm<uint8_t>(f0, stage.rows->ptr, reinterpret_cast<uint8_t *>(out), n0);
-		FillForm<uint8_t>(f1, stage.rows->ptr, reinterpret_cast<uint8_t *>(out) + n0, n1);
+		GenerateSequence(f0.start, f0.increment, reinterpret_cast<uint8_t *>(out), count);
 		break;
 	case 2:
-		FillForm<uint16_t>(f0, stage.rows->ptr, reinterpret_cast<uint16_t *>(out), n0);
-		FillForm<uint16_t>(f1, stage.rows->ptr, reinterpret_cast<uint16_t *>(out) + n0, n1);
+		GenerateSequence(f0.start, f0.increment, reinterpret_cast<uint16_t *>(out), count);
 		break;
 	case 4:
-		FillForm<uint32_t>(f0, stage.rows->ptr, reinterpret_cast<uint32_t *>(out), n0);
-		FillForm<uint32_t>(f1, stage.rows->ptr, reinterpret_cast<uint32_t *>(out) + n0, n1);
+		GenerateSequence(f0.start, f0.increment, reinterpret_cast<uint32_t *>(out), count);
 		break;
 	default:
-		FillForm<uint64_t>(f0, stage.rows->ptr, reinterpret_cast<uint64_t *>(out), n0);
-		FillForm<uint64_t>(f1, stage.rows->ptr, reinterpret_cast<uint64_t *>(out) + n0, n1);
+		GenerateSequence(f0.start, f0.increment, reinterpret_cast<uint64_t *>(out), count);
 		break;
 	}
 }

@@ -182,6 +182,7 @@ private:
 	void DecodeRowGroupBatch(FastLanesReadLocalState &local_state);
 	ScanBatch GetScanBatch(const FastLanesReadLocalState &local_state) const;
 	void DecodePhysicalColumns(FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t start_vector, idx_t count);
+	bool VectorsJoin(const FastLanesReadLocalState &local_state, idx_t first_vector) const;
 	void FormedVector(FlsColumnStage &stage, const LogicalType &type, idx_t first_vector, idx_t count, Vector &target);
 	void PopulateVirtualColumns(const FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t row_start, idx_t count);
 	void ApplyFilters(FastLanesReadLocalState &local_state, DataChunk &chunk, idx_t start_vector, idx_t count);

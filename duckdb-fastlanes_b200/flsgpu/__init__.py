@@ -42,7 +42,8 @@ class ColumnSpec(C.Structure):
 class ScanColumn(C.Structure):  # flsgpu_scan_column
     _fields_ = [("col", C.c_uint32), ("out_type", C.c_int32), ("string_form", C.c_int32), ("compact", C.c_uint32),
                 ("out_host", C.c_void_p), ("out_capacity_bytes", C.c_uint64), ("heap_host", C.c_void_p),
-                ("heap_capacity_bytes", C.c_uint64), ("keys_host", C.c_void_p), ("keys_capacity_bytes", C.c_uint64)]
+                ("heap_capacity_bytes", C.c_uint64), ("keys_host", C.c_void_p), ("keys_capacity_bytes", C.c_uint64),
+                ("forms", C.c_void_p)]
 
 
 STRING_FLAT, STRING_DICTIONARY = 0, 1
@@ -152,7 +153,7 @@ ABI_SYMBOLS = [
     "flsgpu_string_dict_keys", "flsgpu_scan_strings_to_host", "flsgpu_scan_projection_to_host",
     "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked", "flsgpu_scan_filtered_to_host",
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
-    "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms",
+    "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms", "flsgpu_transfer_bytes",
 ]
 
 
@@ -228,6 +229,13 @@ class Writer:
 
     def __del__(self):
         self.close()
+
+
+def transfer_bytes():
+    """(h2d, d2h) bytes handed to the copy engines by this process so far."""
+    a, b = C.c_uint64(), C.c_uint64()
+    lib.flsgpu_transfer_bytes(C.byref(a), C.byref(b))
+    return a.value, b.value
 
 
 def write_table(columns, arrays, vec_per_rowgroup=64, n_threads=None):

@@ -262,6 +262,8 @@ typedef struct flsgpu_scan_column {
 	uint64_t heap_capacity_bytes;
 	void* keys_host;            /* dictionary form: >= 16 * flsgpu_string_dict_keys */
 	uint64_t keys_capacity_bytes;
+	const flsgpu_vector_form* forms; /* compact: what flsgpu_column_vector_forms returned for this very range, when the caller has
+	                               it already (it needs it to read the result); NULL: the call works the forms out itself */
 } flsgpu_scan_column;
 int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, uint32_t rg_begin, uint32_t n_rg);
 /* The same scan with pushed-down filters (FastLanesReader::Scan -> FilterExecutor::Apply, fls_reader.cpp:516-547): every
@@ -275,6 +277,9 @@ int flsgpu_sync(void* cuda_stream);
 int flsgpu_host_alloc(uint64_t bytes, void** out);
 int flsgpu_host_free(void* p);
 
+/* Bytes this process has handed to the copy engines so far: staging of compressed chunks + vector maps (host to device) and
+ * the results of the host-to-host scans (device to host).  bench.py reports the per-step difference as e2e h2d / d2h bytes. */
+void flsgpu_transfer_bytes(uint64_t* h2d, uint64_t* d2h);
 /* Launch counter: number of decode/aggregate kernels this process has launched (bench.py gpu_launches). */
 uint64_t flsgpu_launch_count(void);
 

@@ -18,8 +18,25 @@ def build():
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
 
 
+def build_native():
+    """The oracle compiled for THIS machine's cores (-march=native) for the timed CPU baselines of bench.py: the library
+    that travels with the repo is built -march=x86-64-v3 so that it runs wherever the snapshot lands.  Returns the path, or
+    None when no compiler is at hand (the portable build is then timed, and the bench line says so)."""
+    out = os.path.join(ORACLE_DIR, "_ref", "liboracle_native.so")
+    try:
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["gcc", "-O3", "-march=native", "-ffp-contract=off", "-fPIC", "-std=gnu11", "-I" + os.path.join(ROOT, "include"),
+                               "-shared", "-o", out] + [os.path.join(ORACLE_DIR, f) for f in ("fls_oracle.c", "fls_oracle_scan.c", "fls_oracle_str.c")]
+                              + ["-lpthread"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        return out
+    except (OSError, subprocess.CalledProcessError):
+        return None
+
+
 build()
-lib = C.CDLL(LIB)
+NATIVE = build_native() if os.environ.get("FLS_ORACLE_NATIVE") == "1" else None
+lib = C.CDLL(NATIVE or LIB)
+MARCH = "native" if NATIVE else "x86-64-v3"
 
 
 class OracleTable(C.Structure):

@@ -118,6 +118,30 @@ class Reader:
             raise ReaderError(rc)
         return outs, dict(rows=rows.value, chunks=chunks.value, max_chunk_rows=mx.value)
 
+    def scan_raw(self, column_ids=None, n_threads=1, stride=16):
+        """Unfiltered scan into numpy buffers, strings left in their fixed-stride sinks: [array | (bytes[n, stride], lengths)]."""
+        ids = list(range(len(self.columns))) if column_ids is None else list(column_ids)
+        n = self.total_tuples
+        outs, keep, ptrs = [], [], []
+        for i in ids:
+            if self.columns[i]["type"] in ("VARCHAR", "BLOB"):
+                data, lens = np.zeros((n, stride), dtype=np.uint8), np.zeros(n, dtype=np.uint32)
+                sink = StringSink(data.ctypes.data, lens.ctypes.data, stride)
+                keep.append(sink)
+                outs.append((data, lens))
+                ptrs.append(C.addressof(sink))
+            else:
+                a = np.zeros(n, dtype=self.np_dtype(i))
+                outs.append(a)
+                ptrs.append(a.ctypes.data)
+        st = ScanStats()
+        rc = lib.flsreader_scan(self._h, (C.c_uint64 * len(ids))(*ids), len(ids), reader_filters(()), 0, n_threads,
+                                (C.c_void_p * len(ids))(*ptrs), None, C.byref(st))
+        if rc:
+            raise ReaderError(rc)
+        assert st.rows == n
+        return outs
+
     def scan(self, column_ids=None, filters=(), n_threads=1, stride=64):
         """SELECT cols FROM read_fls(path) WHERE filters.  filters: [(index into column_ids, op, physical constant)].
         Returns (columns, row ids or None, stats): string columns come back as lists of bytes; with filters the rows are
@@ -161,6 +185,11 @@ class Reader:
 
     def set_option(self, key, value):
         rc = lib.flsreader_set_option(self._h, key.encode(), C.c_uint64(int(value)))
+        if rc:
+            raise ReaderError(rc)
+
+    def evict(self):
+        rc = lib.flsreader_evict(self._h)
         if rc:
             raise ReaderError(rc)
 

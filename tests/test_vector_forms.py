@@ -143,7 +143,7 @@ def test_compact_scan_plus_forms_equals_full_scan(n, vpr):
 @pytest.mark.parametrize("threads", [1, 4])
 def test_reader_hands_constant_and_sequence_vectors_on(tmp_path, threads):
     """FastLanesReader::Scan over a compact scan: CONSTANT / SEQUENCE vectors, zero-copy FLAT slices, chunks put together
-    from halves of different forms — the rows a consumer reads are the input, with the forms on and off."""
+    cut where the forms of neighbouring vectors differ — the rows a consumer reads are the input, with the forms on and off."""
     import reader_lib
     n = 333333
     cols = columns(n)
@@ -158,9 +158,10 @@ def test_reader_hands_constant_and_sequence_vectors_on(tmp_path, threads):
             assert got[c].view(exp.dtype).tobytes() == exp.tobytes(), (col[0], on)
         assert stats["rows"] == n
         if on:
-            assert stats["sequence_vectors"] > 0 and stats["constant_vectors"] > 0 and stats["assembled_vectors"] > 0, stats
+            assert stats["sequence_vectors"] > 0 and stats["constant_vectors"] > 0 and stats["max_chunk_rows"] == 2048, stats
+            assert stats["chunks"] > (n + 2047) // 2048  # chunks are cut where the forms of two neighbouring vectors differ
         else:
-            assert stats["sequence_vectors"] == stats["constant_vectors"] == stats["assembled_vectors"] == 0, stats
+            assert stats["sequence_vectors"] == stats["constant_vectors"] == 0, stats
         st2 = r.consume(n_threads=threads)
         assert st2["rows"] == n and st2["chunks"] == stats["chunks"]
         r.close()
