@@ -355,8 +355,8 @@ int flsgpu_table_open_memory(const void* bytes, uint64_t size, int copy, flsgpu_
 	}
 	auto t = std::make_unique<flsgpu_table>();
 	if (copy) {
-		t->owned.assign(static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + size);
-		t->bytes = t->owned.data();
+		t->owned = std::make_shared<std::vector<uint8_t>>(static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + size);
+		t->bytes = t->owned->data();
 	} else {
 		t->bytes = static_cast<const uint8_t*>(bytes);
 	}
@@ -381,38 +381,58 @@ int flsgpu_table_open(const char* path, flsgpu_table** out) {
 	const long sz = std::ftell(fp);
 	std::fseek(fp, 0, SEEK_SET);
 	auto t = std::make_unique<flsgpu_table>();
-	t->owned.resize(sz > 0 ? (size_t)sz : 0);
-	const size_t n = sz > 0 ? std::fread(t->owned.data(), 1, (size_t)sz, fp) : 0;
+	t->owned = std::make_shared<std::vector<uint8_t>>(sz > 0 ? (size_t)sz : 0);
+	const size_t n = sz > 0 ? std::fread(t->owned->data(), 1, (size_t)sz, fp) : 0;
 	std::fclose(fp);
 	if (sz < 0 || n != (size_t)sz) {
 		return fls_set_error(FLSGPU_ERR_IO, (std::string("short read: ") + path).c_str());
 	}
 	// footer written beside the data (COPY ... (FORMAT fls, inline_footer false), reference fls_writer.cpp:229-230): append it
-	if (t->owned.size() >= sizeof(fls_file_header)) {
+	if (t->owned->size() >= sizeof(fls_file_header)) {
 		fls_file_header h;
-		std::memcpy(&h, t->owned.data(), sizeof(h));
-		if (std::memcmp(h.magic, FLS_MAGIC, 8) == 0 && h.reserved[0] == 1 && h.footer_offset == t->owned.size() &&
+		std::memcpy(&h, t->owned->data(), sizeof(h));
+		if (std::memcmp(h.magic, FLS_MAGIC, 8) == 0 && h.reserved[0] == 1 && h.footer_offset == t->owned->size() &&
 		    h.footer_size <= (1ull << 40)) {
 			const std::string fpath = std::string(path) + ".footer";
 			FILE* ff = std::fopen(fpath.c_str(), "rb");
 			if (!ff) {
 				return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open footer file: ") + fpath).c_str());
 			}
-			const size_t at = t->owned.size();
-			t->owned.resize(at + (size_t)h.footer_size);
-			const size_t k = std::fread(t->owned.data() + at, 1, (size_t)h.footer_size, ff);
+			const size_t at = t->owned->size();
+			t->owned->resize(at + (size_t)h.footer_size);
+			const size_t k = std::fread(t->owned->data() + at, 1, (size_t)h.footer_size, ff);
 			std::fclose(ff);
 			if (k != (size_t)h.footer_size) {
 				return fls_set_error(FLSGPU_ERR_IO, (std::string("short read: ") + fpath).c_str());
 			}
 		}
 	}
-	t->bytes = t->owned.data();
-	t->size = t->owned.size();
+	t->bytes = t->owned->data();
+	t->size = t->owned->size();
 	const int rc = fls_table_parse(t.get());
 	if (rc) {
 		return rc;
 	}
+	*out = t.release();
+	return FLSGPU_OK;
+}
+
+// Another handle over the same host image (no copy, no second validation pass): one handle per device of a single-process
+// multi-GPU scan.  The image lives as long as any handle that owns it does.
+int flsgpu_table_share(const flsgpu_table* src, flsgpu_table** out) {
+	if (!src || !out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_share: null argument");
+	}
+	auto t = std::make_unique<flsgpu_table>();
+	t->bytes = src->bytes;
+	t->size = src->size;
+	t->owned = src->owned;
+	t->header = src->header;
+	t->columns = src->columns;
+	t->rowgroups = src->rowgroups;
+	t->chunks = src->chunks;
+	t->n_vectors = src->n_vectors;
+	t->device_index = src->device_index;
 	*out = t.release();
 	return FLSGPU_OK;
 }

@@ -2,6 +2,7 @@
 // reference src/reader/table_metadata.cpp:13-35).
 #pragma once
 #include <cstdint>
+#include <memory>
 #include <vector>
 #include "fls_format.h"
 
@@ -10,7 +11,8 @@ struct FlsDeviceState; // defined by the CUDA side (flsgpu_device.cu)
 struct flsgpu_table {
 	const uint8_t* bytes = nullptr; // whole file image
 	uint64_t size = 0;
-	std::vector<uint8_t> owned;     // backing store when the table owns a copy
+	std::shared_ptr<std::vector<uint8_t>> owned; // backing store when the table owns a copy (shared by flsgpu_table_share handles)
+	int device_index = 0;           // which of flsgpu_init's devices this handle stages to and decodes on (flsgpu_table_bind_device)
 	void* pinned = nullptr;         // cudaHostAlloc'ed copy used for H2D staging (lazily created)
 	fls_file_header header {};
 	const fls_column_desc* columns = nullptr;

@@ -28,10 +28,13 @@ namespace {
 std::atomic<uint64_t> g_launches {0};
 std::atomic<uint64_t> g_h2d_bytes {0}, g_d2h_bytes {0}; // bytes this process asked the copy engines to move (flsgpu_transfer_bytes)
 std::mutex g_mu; // guards device selection + per-function attribute cache
-int g_device = -1;
-int g_n_sms = 0;
-std::map<const void*, int> g_func_ready;                  // fn -> 1 once the smem opt-in is set
-std::map<std::pair<const void*, uint32_t>, int> g_occ;    // (fn, smem) -> resident CTAs per SM
+// Devices of this process (flsgpu_init): CUDA ordinals, in the order given.  A table handle is bound to ONE of them
+// (flsgpu_table_bind_device; index 0 unless told otherwise); one process per GPU passes a single ordinal, a single-process
+// multi-GPU host (DuckDB: one process, N worker threads) opens one handle per device over the same image (flsgpu_table_share).
+std::vector<int> g_devices;
+std::map<int, int> g_n_sms_of;                                      // ordinal -> SM count
+std::map<std::pair<const void*, int>, int> g_func_ready;            // (fn, ordinal) -> 1 once the smem opt-in is set
+std::map<std::tuple<const void*, uint32_t, int>, int> g_occ;        // (fn, smem, ordinal) -> resident CTAs per SM
 
 constexpr uint32_t kMaxSmemPerCta = 227u * 1024u;
 
@@ -66,21 +69,50 @@ int cuda_fail(cudaError_t e, const char* where) {
 		}                                                                                                            \
 	} while (0)
 
-int ensure_device() {
+// Make device `index` of the process's list current for the calling thread (index 0: the default device).
+int ensure_device(int index = 0, int* ordinal_out = nullptr, int* n_sms_out = nullptr) {
 	std::lock_guard<std::mutex> g(g_mu);
-	if (g_device < 0) {
+	if (g_devices.empty()) {
 		int n = 0;
 		const cudaError_t e = cudaGetDeviceCount(&n);
 		if (e != cudaSuccess || n == 0) {
 			return fls_set_error(FLSGPU_ERR_CUDA, "no CUDA device available (flsgpu has no CPU fallback)");
 		}
-		g_device = 0;
+		g_devices.push_back(0);
 	}
-	FLS_CUDA(cudaSetDevice(g_device));
-	if (g_n_sms == 0) {
-		FLS_CUDA(cudaDeviceGetAttribute(&g_n_sms, cudaDevAttrMultiProcessorCount, g_device));
+	if (index < 0 || index >= (int)g_devices.size()) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "device index outside the list given to flsgpu_init");
+	}
+	const int ordinal = g_devices[index];
+	FLS_CUDA(cudaSetDevice(ordinal));
+	auto it = g_n_sms_of.find(ordinal);
+	if (it == g_n_sms_of.end()) {
+		int n_sms = 0;
+		FLS_CUDA(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, ordinal));
+		it = g_n_sms_of.emplace(ordinal, n_sms).first;
+	}
+	if (ordinal_out) {
+		*ordinal_out = ordinal;
+	}
+	if (n_sms_out) {
+		*n_sms_out = it->second;
 	}
 	return FLSGPU_OK;
+}
+
+// The device a raw device pointer / the caller's stream belongs to is the caller's business: entry points that take only
+// device pointers (flsgpu_agg_reset, flsgpu_sync) run on the device that owns the pointer when it can be told, else on the
+// thread's current device if it is one of ours, else on the default device.
+int ensure_device_of(const void* dev_ptr) {
+	if (dev_ptr) {
+		cudaPointerAttributes attr {};
+		if (cudaPointerGetAttributes(&attr, dev_ptr) == cudaSuccess && attr.type == cudaMemoryTypeDevice) {
+			FLS_CUDA(cudaSetDevice(attr.device));
+			return FLSGPU_OK;
+		}
+		cudaGetLastError();
+	}
+	return ensure_device();
 }
 
 } // namespace
@@ -106,7 +138,8 @@ struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of
 };
 
 struct FlsDeviceState {
-	int device = 0;
+	int device = 0; // CUDA ordinal
+	int n_sms = 0;
 	uint8_t* d_image = nullptr; // bytes [0, footer_offset) of the container, same offsets as the file
 	uint64_t image_bytes = 0;
 	FlsChunkDev* d_chunks = nullptr; // [rg * n_columns + col]
@@ -181,7 +214,8 @@ int device_state(flsgpu_table* t, FlsDeviceState** out) {
 		*out = t->dev;
 		return cudaSetDevice(t->dev->device) == cudaSuccess ? FLSGPU_OK : fls_set_error(FLSGPU_ERR_CUDA, "cudaSetDevice failed");
 	}
-	const int rc = ensure_device();
+	int ordinal = 0, n_sms = 0;
+	const int rc = ensure_device(t->device_index, &ordinal, &n_sms);
 	if (rc) {
 		return rc;
 	}
@@ -189,7 +223,8 @@ int device_state(flsgpu_table* t, FlsDeviceState** out) {
 		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "more than 65535 vectors per row group are not supported on the device");
 	}
 	auto d = new FlsDeviceState();
-	d->device = g_device;
+	d->device = ordinal;
+	d->n_sms = n_sms;
 	const int rc2 = device_state_create(t, d);
 	if (rc2) { // publish only fully built states
 		cudaFree(d->d_image);
@@ -304,7 +339,7 @@ void pin_image(flsgpu_table* t, FlsDeviceState* d) {
 		return; // already pinned
 	}
 	cudaGetLastError();
-	if (cudaHostRegister(const_cast<uint8_t*>(t->bytes), t->size, cudaHostRegisterDefault) == cudaSuccess) {
+	if (cudaHostRegister(const_cast<uint8_t*>(t->bytes), t->size, cudaHostRegisterPortable) == cudaSuccess) {
 		d->host_registered = true;
 	} else {
 		cudaGetLastError();
@@ -431,7 +466,7 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 }
 
 // Pick pipeline depth / grid for `fn` and launch it.
-int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t stage_bytes, cudaStream_t stream,
+int launch_family(const FlsDeviceState* d, const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t stage_bytes, cudaStream_t stream,
                   uint32_t tile_bytes = 0, uint32_t budget_kb = 0) {
 	if (!fn) {
 		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "no kernel instantiation for this (lane width, value width, output width)");
@@ -470,11 +505,11 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	int occ = 0;
 	{
 		std::lock_guard<std::mutex> g(g_mu);
-		if (!g_func_ready.count(fn)) {
+		if (!g_func_ready.count(std::make_pair(fn, d->device))) { // the opt-in is per device
 			FLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmemPerCta));
-			g_func_ready[fn] = 1;
+			g_func_ready[std::make_pair(fn, d->device)] = 1;
 		}
-		const auto key = std::make_pair(fn, smem ^ (wpc << 24));
+		const auto key = std::make_tuple(fn, smem ^ (wpc << 24), d->device);
 		auto it = g_occ.find(key);
 		if (it == g_occ.end()) {
 			FLS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, (int)wpc * 32, smem));
@@ -490,7 +525,7 @@ int launch_family(const void* fn, FlsLaunch L, uint32_t slot_bytes, uint32_t sta
 	if (g_max_ctas) {
 		occ = std::min<int>(occ, (int)g_max_ctas);
 	}
-	const uint32_t grid = (uint32_t)std::min<uint64_t>(want, (uint64_t)occ * g_n_sms);
+	const uint32_t grid = (uint32_t)std::min<uint64_t>(want, (uint64_t)occ * d->n_sms);
 	// materialising launches (nothing but staged bytes read, nothing but the caller's column written): programmatic
 	// stream serialization, the kernel releases its successor at once and waits for its predecessor before it exits
 	L.pdl = (g_pdl && L.agg == nullptr && L.mask_mode == 0u) ? 1u : 0u;
@@ -635,7 +670,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	if (fuse_alp) {
 		L.family_mask = fam_mask[1] | fam_mask[2];
 		L.idx_bits = 0;
-		rc = launch_family(fls_kernel_main(T, os.ob, 5), L, std::max(p.main_slot[1], p.main_slot[2]), 0u, stream, tile);
+		rc = launch_family(d, fls_kernel_main(T, os.ob, 5), L, std::max(p.main_slot[1], p.main_slot[2]), 0u, stream, tile);
 	}
 	for (int f = 0; f < 5 && rc == FLSGPU_OK; ++f) {
 		if (fuse_alp && (f == 1 || f == 2)) {
@@ -648,7 +683,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 			// DELTA needs the per-warp transposition area (+ 16 lane totals for T = 64); the SWAR kernel stores from registers
 			const bool stage = p.main_needs_stage && (f == 3 || (f == 0 && T != 64));
 			const uint32_t slot = fold4 ? std::max(p.main_slot[0], p.main_slot[4]) : p.main_slot[f];
-			rc = launch_family(agg_family ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, slot,
+			rc = launch_family(d, agg_family ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, slot,
 			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile, f == 4 ? g_swar8_kb : 0u);
 		}
 	}
@@ -658,7 +693,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 			L.family_mask = FLS_FAMILY_DICT;
 			L.idx_bits = (uint32_t)it;
 			L.run_shift = g_dict_run_shift;
-			rc = launch_family(agg_family ? fls_kernel_agg(1, it, T, 0) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile,
+			rc = launch_family(d, agg_family ? fls_kernel_agg(1, it, T, 0) : fls_kernel_dict(it, T, os.ob), L, p.dict_slot[k], 0, stream, tile,
 			                   g_dict_kb + tile / 1024u);
 		}
 	}
@@ -666,7 +701,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	if (p.has_rle && rc == FLSGPU_OK) {
 		L.family_mask = FLS_FAMILY_RLE;
 		L.idx_bits = 0;
-		rc = launch_family(agg_family ? fls_kernel_agg(2, 16, T, 0) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
+		rc = launch_family(d, agg_family ? fls_kernel_agg(2, 16, T, 0) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);
 	}
 	return rc;
 }
@@ -717,17 +752,47 @@ int flsgpu_init(int n_devices, const int* device_ids) {
 	if (e != cudaSuccess || n == 0) {
 		return fls_set_error(FLSGPU_ERR_CUDA, "flsgpu_init: no CUDA device available (flsgpu has no CPU fallback)");
 	}
-	// one process per GPU: the first listed device becomes this process's device
-	const int dev = (n_devices > 0 && device_ids) ? device_ids[0] : 0;
-	if (dev < 0 || dev >= n) {
-		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_init: device id out of range");
+	std::vector<int> devs;
+	for (int i = 0; i < n_devices && device_ids; ++i) {
+		if (device_ids[i] < 0 || device_ids[i] >= n) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_init: device id out of range");
+		}
+		devs.push_back(device_ids[i]); // an ordinal may be listed more than once (several handles of a table on one device)
+	}
+	if (devs.empty()) {
+		devs.push_back(0);
 	}
 	{
 		std::lock_guard<std::mutex> g(g_mu);
-		g_device = dev;
-		g_n_sms = 0;
+		g_devices = devs;
 	}
 	return ensure_device();
+}
+
+int flsgpu_n_devices(int* out) {
+	if (!out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_n_devices: null argument");
+	}
+	std::lock_guard<std::mutex> g(g_mu);
+	*out = g_devices.empty() ? 1 : (int)g_devices.size();
+	return FLSGPU_OK;
+}
+
+int flsgpu_table_bind_device(flsgpu_table* t, int device_index) {
+	if (!t) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_bind_device: null table");
+	}
+	if (t->dev) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_bind_device: the table already has device state (bind before the first staging)");
+	}
+	{
+		std::lock_guard<std::mutex> g(g_mu);
+		if (device_index < 0 || device_index >= (int)std::max<size_t>(1, g_devices.size())) {
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_table_bind_device: index outside the list given to flsgpu_init");
+		}
+	}
+	t->device_index = device_index;
+	return FLSGPU_OK;
 }
 
 int flsgpu_device_count(int* out) {
@@ -1200,9 +1265,14 @@ int flsgpu_scan_column_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin,
 }
 
 int flsgpu_sync(void* cuda_stream) {
-	const int rc = ensure_device();
-	if (rc) {
-		return rc;
+	if (cuda_stream == nullptr) { // the default stream is per device: the caller's current device, or our default
+		int cur = -1;
+		if (cudaGetDevice(&cur) != cudaSuccess) {
+			const int rc = ensure_device();
+			if (rc) {
+				return rc;
+			}
+		}
 	}
 	FLS_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(cuda_stream)));
 	return FLSGPU_OK;
@@ -1244,7 +1314,7 @@ int flsgpu_host_alloc(uint64_t bytes, void** out) {
 			return FLSGPU_OK;
 		}
 	}
-	FLS_CUDA(cudaHostAlloc(out, want, cudaHostAllocDefault));
+	FLS_CUDA(cudaHostAlloc(out, want, cudaHostAllocPortable));
 	std::lock_guard<std::mutex> g(hp.mu);
 	hp.live[*out] = want;
 	return FLSGPU_OK;
@@ -1906,7 +1976,7 @@ int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {
 	if (!result_dev) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_agg_reset: null argument");
 	}
-	const int rc = ensure_device();
+	const int rc = ensure_device_of(result_dev);
 	if (rc) {
 		return rc;
 	}

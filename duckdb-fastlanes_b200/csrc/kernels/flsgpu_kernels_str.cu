@@ -736,13 +736,17 @@ cudaError_t fls_str_launch_heap(FlsStrLaunch L, cudaStream_t stream) {
 		L.groups_per_rg = (L.vec_per_rg * 1024u + per_cta - 1u) / per_cta;
 	}
 	const uint32_t smem = kWarps * (2u * L.cbuf_bytes + L.dbuf_bytes); // two staging buffers for codes + one decode buffer per warp
-	static bool attr_set = false; // benign race: the attribute is idempotent
-	if (!attr_set) {
+	static bool attr_set[64] = {}; // per device; benign race: the attribute is idempotent
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (dev < 0 || dev >= 64 || !attr_set[dev]) {
 		const cudaError_t e = cudaFuncSetAttribute(fls_str_heap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
 		if (e != cudaSuccess) {
 			return e;
 		}
-		attr_set = true;
+		if (dev >= 0 && dev < 64) {
+			attr_set[dev] = true;
+		}
 	}
 	return launch_chained(fls_str_heap_kernel, L, L.n_rg * L.groups_per_rg, kWarps * 32, smem, stream, L.pdl != 0);
 }

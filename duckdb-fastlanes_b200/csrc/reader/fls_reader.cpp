@@ -80,12 +80,24 @@ FastLanesReader::FastLanesReader(const std::string& path, const FastLanesFileRea
 }
 
 FastLanesReader::~FastLanesReader() {
+	for (size_t i = 1; i < device_tables.size(); ++i) {
+		flsgpu_table_close(device_tables[i]);
+	}
 	flsgpu_table_close(table);
 }
 
 // FastLanesReader::Initialize (fls_reader.cpp:106-143): schema, per-row-group tuple offsets, totals.
 void FastLanesReader::Initialize() {
 	Check(flsgpu_table_info_get(table, &info), "flsgpu_table_info_get");
+	int n_devices = 1;
+	Check(flsgpu_n_devices(&n_devices), "flsgpu_n_devices");
+	device_tables.assign(1, table);
+	for (int g = 1; g < n_devices; ++g) {
+		flsgpu_table* shared = nullptr;
+		Check(flsgpu_table_share(table, &shared), "flsgpu_table_share");
+		device_tables.push_back(shared);
+		Check(flsgpu_table_bind_device(shared, g), "flsgpu_table_bind_device");
+	}
 	columns.clear();
 	column_out_types.clear();
 	for (uint32_t c = 0; c < info.n_columns; ++c) {
@@ -205,6 +217,7 @@ bool FastLanesReader::TryInitializeScan(FastLanesReadGlobalState& gstate, FastLa
 		return false;
 	}
 	gstate.next_rowgroup = lstate.batch_end; // mark the row groups as consumed (:511)
+	lstate.device_slot = gstate.next_batch++ % device_tables.size();
 	const size_t n_reader_cols = lstate.projection.reader_column_ids.size();
 	lstate.staging.resize(n_reader_cols);
 	lstate.heaps.resize(n_reader_cols);
@@ -274,7 +287,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState& ls) {
 			ls.mask.Reserve((uint64_t)n_rg * info.vec_per_rowgroup * 128u);
 			ls.has_mask = true;
 		}
-		Check(flsgpu_scan_filtered_to_host(table, sc.data(), (uint32_t)sc.size(), phys_filters.data(), (uint32_t)phys_filters.size(), rg0, n_rg,
+		Check(flsgpu_scan_filtered_to_host(device_tables[ls.device_slot], sc.data(), (uint32_t)sc.size(), phys_filters.data(), (uint32_t)phys_filters.size(), rg0, n_rg,
 		                                   static_cast<uint32_t*>(ls.mask.ptr), ls.mask.bytes),
 		      "flsgpu_scan_filtered_to_host");
 	}

@@ -130,6 +130,7 @@ struct FastLanesReaderProjectionPlan {
 
 struct FastLanesReadGlobalState { // fls_multi_file_info.hpp:79-86 (+ the multi-file lock TryInitializeScan runs under)
 	idx_t next_rowgroup = 0;
+	idx_t next_batch = 0; // batches handed out so far: batch k goes to device k mod G
 	std::mutex lock;
 };
 
@@ -148,6 +149,7 @@ struct FastLanesReadLocalState { // fls_multi_file_info.hpp:57-77
 	FastLanesReaderProjectionPlan projection;
 	// batch decoded by the last TryInitializeScan
 	idx_t batch_begin = 0, batch_end = 0; // row groups [begin, end)
+	idx_t device_slot = 0;                // which of the reader's per-device table handles decodes this batch
 	std::vector<PinnedBuffer> staging;    // one per reader column: batch_rowgroups * vec_per_rowgroup * 1024 values
 	// string columns: string heap, dictionary keys (dictionary form) and the first key of every row group of the batch
 	std::vector<PinnedBuffer> heaps, keys;
@@ -223,6 +225,9 @@ public:
 	flsgpu_table* Table() const {
 		return table;
 	}
+	const std::vector<flsgpu_table*>& DeviceTables() const {
+		return device_tables;
+	}
 	void SetCompressedVectors(bool on) {
 		reader_options.compressed_vectors = on;
 	}
@@ -251,6 +256,10 @@ private:
 	bool IsFileRowNumberColumn(idx_t column_id) const;
 
 	flsgpu_table* table = nullptr;
+	// Single-process multi-GPU (the reference runs one worker per row group inside one process,
+	// fls_multi_file_info.cpp:99-110): one handle per device of flsgpu_init's list over the same host image
+	// (device_tables[0] == table).  Row groups are independent, so a batch simply goes to the next device in turn.
+	std::vector<flsgpu_table*> device_tables;
 	flsgpu_table_info info {};
 	std::vector<ColumnDefinition> columns;
 	std::vector<int32_t> column_out_types;   // flsgpu_out_type per physical column

@@ -255,8 +255,10 @@ int flsreader_scan_all(flsreader_handle* h, const uint64_t* column_ids, uint32_t
 
 int flsreader_evict(flsreader_handle* h) {
 	FLSR_TRY({
-		if (flsgpu_table_evict(h->reader->Table()) != FLSGPU_OK) {
-			throw ReaderError(FLSGPU_ERR_CUDA, flsgpu_last_error());
+		for (flsgpu_table* t : h->reader->DeviceTables()) {
+			if (flsgpu_table_evict(t) != FLSGPU_OK) {
+				throw ReaderError(FLSGPU_ERR_CUDA, flsgpu_last_error());
+			}
 		}
 	})
 }

@@ -3,6 +3,7 @@
 #include "fls_file_reader.hpp"
 
 #include "duckdb/common/multi_file/multi_file_reader.hpp"
+#include "duckdb/common/string_util.hpp"
 #include "duckdb/common/types/selection_vector.hpp"
 #include "duckdb/execution/expression_executor.hpp"
 #include "duckdb/parallel/task_scheduler.hpp"
@@ -103,13 +104,55 @@ FastLanesReader::FastLanesReader(ClientContext &context, OpenFileInfo file_p, co
 }
 
 FastLanesReader::~FastLanesReader() {
+	for (idx_t i = 1; i < device_tables.size(); i++) {
+		flsgpu_table_close(device_tables[i]);
+	}
 	flsgpu_table_close(table);
+}
+
+// SET fastlanes_gpu_devices = '0,1,2,3': the process-wide device list of the engine (flsgpu_init); applied when it changes
+static void ApplyDeviceList(const string &list) {
+	static std::mutex lock;
+	static string applied;
+	std::lock_guard<std::mutex> guard(lock);
+	if (list == applied) {
+		return;
+	}
+	vector<int> ordinals;
+	for (auto &part : StringUtil::Split(list, ',')) {
+		auto text = part;
+		StringUtil::Trim(text);
+		if (text.empty()) {
+			continue;
+		}
+		for (auto ch : text) {
+			if (ch < '0' || ch > '9') {
+				throw InvalidInputException("fastlanes_gpu_devices: \"%s\" is not a list of CUDA device ordinals", list);
+			}
+		}
+		ordinals.push_back(std::stoi(text));
+	}
+	FlsCheck(flsgpu_init(NumericCast<int>(ordinals.size()), ordinals.data()), "fastlanes_gpu_devices");
+	applied = list;
 }
 
 // FastLanesReader::Initialize (fls_reader.cpp:106-143): footer -> schema, per-row-group tuple offsets, totals
 void FastLanesReader::Initialize(ClientContext &context) {
 	FlsCheck(flsgpu_table_open(file.path.c_str(), &table), "read_fls");
 	FlsCheck(flsgpu_table_info_get(table, &info), "flsgpu_table_info_get");
+	device_tables.assign(1, table);
+	Value devices;
+	if (context.TryGetCurrentSetting("fastlanes_gpu_devices", devices) && !devices.IsNull() && !devices.ToString().empty()) {
+		ApplyDeviceList(devices.ToString()); // fails here, at bind time, when there is no such device
+		int n_devices = 1;
+		FlsCheck(flsgpu_n_devices(&n_devices), "flsgpu_n_devices");
+		for (int g = 1; g < n_devices; g++) {
+			flsgpu_table *shared = nullptr;
+			FlsCheck(flsgpu_table_share(table, &shared), "flsgpu_table_share");
+			device_tables.push_back(shared);
+			FlsCheck(flsgpu_table_bind_device(shared, g), "flsgpu_table_bind_device");
+		}
+	}
 	columns.clear();
 	column_descs.resize(info.n_columns);
 	column_out_types.resize(info.n_columns);
@@ -343,6 +386,7 @@ bool FastLanesReader::TryAssignNextRowGroup(FastLanesReadGlobalState &global_sta
 	local_state.batch_begin = to_scan[global_state.next_rowgroup];
 	local_state.batch_end = local_state.batch_begin + n;
 	global_state.next_rowgroup += n; // mark the row groups as consumed (:511)
+	local_state.device_slot = global_state.next_batch++ % device_tables.size();
 	local_state.cur_rowgroup = local_state.batch_begin;
 	local_state.projection = BuildReaderProjectionPlan();
 	local_state.row_group_base = row_group_offsets[local_state.cur_rowgroup];
@@ -486,7 +530,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 		ReservePinned(ls.mask, idx_t(n_rg) * info.vec_per_rowgroup * 128);
 	}
 	if (!scan_columns.empty() || ls.has_mask) {
-		FlsCheck(flsgpu_scan_filtered_to_host(table, scan_columns.data(), NumericCast<uint32_t>(scan_columns.size()),
+		FlsCheck(flsgpu_scan_filtered_to_host(device_tables[ls.device_slot], scan_columns.data(), NumericCast<uint32_t>(scan_columns.size()),
 		                                      ls.device_filters.data(), NumericCast<uint32_t>(ls.device_filters.size()), rg0, n_rg,
 		                                      ls.has_mask ? reinterpret_cast<uint32_t *>(ls.mask->ptr) : nullptr,
 		                                      ls.has_mask ? ls.mask->bytes : 0),

@@ -101,6 +101,8 @@ struct FastLanesReadLocalState : public LocalTableFunctionState {
 	idx_t batch_begin = 0;
 	idx_t batch_end = 0;
 	bool batch_decoded = false;
+	//! Which of the reader's per-device table handles decodes this batch
+	idx_t device_slot = 0;
 	vector<unique_ptr<FlsColumnStage>> stage;
 	buffer_ptr<FlsPinnedBuffer> mask; // selection bit mask of the device-evaluated filters for the batch
 	bool has_mask = false;
@@ -119,6 +121,8 @@ struct FastLanesReadLocalState : public LocalTableFunctionState {
 struct FastLanesReadGlobalState : public GlobalTableFunctionState {
 	//! Next row group of the current file to hand out (reference fls_multi_file_info.hpp:79-86)
 	idx_t next_rowgroup = 0;
+	//! Batches handed out so far: batch k is decoded on device k mod G (setting fastlanes_gpu_devices)
+	idx_t next_batch = 0;
 };
 
 class FastLanesReader final : public BaseFileReader {
@@ -190,6 +194,10 @@ private:
 	const vector<idx_t> &GetRowGroupsToScan(ClientContext &context, FastLanesReadLocalState &local_state);
 
 	flsgpu_table *table = nullptr;
+	//! One handle per device of the fastlanes_gpu_devices list over the same host image (device_tables[0] == table): DuckDB
+	//! is ONE process with N worker threads (reference fls_multi_file_info.cpp:99-110), row groups are independent, so each
+	//! batch of row groups simply goes to the next device in turn and nothing is exchanged between devices.
+	vector<flsgpu_table *> device_tables;
 	flsgpu_table_info info {};
 	vector<fls_column_desc> column_descs;
 	vector<int32_t> column_out_types; // flsgpu_out_type per physical column

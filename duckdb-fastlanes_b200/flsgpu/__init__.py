@@ -154,6 +154,7 @@ ABI_SYMBOLS = [
     "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked", "flsgpu_scan_filtered_to_host",
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
     "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms", "flsgpu_transfer_bytes",
+    "flsgpu_n_devices", "flsgpu_table_share", "flsgpu_table_bind_device",
 ]
 
 
@@ -250,10 +251,14 @@ def write_table(columns, arrays, vec_per_rowgroup=64, n_threads=None):
 class Table:
     """TableMetadata + row-group readers: flsgpu_table_* (reference src/reader/table_metadata.cpp, fls_reader.cpp)."""
 
-    def __init__(self, image=None, path=None, copy=False):
+    def __init__(self, image=None, path=None, copy=False, share=None):
         self._h = C.c_void_p()
         self._image = None
-        if path is not None:
+        if share is not None:  # another handle over the same host image (one per device of a single-process scan)
+            self._image = share._image
+            self._parent = share
+            _check(lib.flsgpu_table_share(share._h, C.byref(self._h)), "table_share")
+        elif path is not None:
             _check(lib.flsgpu_table_open(os.fsencode(path), C.byref(self._h)), "table_open")
         else:
             self._image = np.ascontiguousarray(image, dtype=np.uint8)
@@ -264,6 +269,10 @@ class Table:
         self.info = info
         self.n_columns, self.n_rowgroups = info.n_columns, info.n_rowgroups
         self.vec_per_rowgroup, self.n_tuples = info.vec_per_rowgroup, info.n_tuples
+
+    def bind_device(self, index):
+        """Bind the handle to the index-th device of flsgpu.init's list (before its first staging / decode call)."""
+        _check(lib.flsgpu_table_bind_device(self._h, int(index)), "table_bind_device")
 
     def column(self, col):
         d = ColumnDesc()
@@ -422,6 +431,12 @@ class Table:
 def init(device_ids=(0,)):
     arr = (C.c_int * len(device_ids))(*device_ids)
     _check(lib.flsgpu_init(len(device_ids), arr), "init")
+
+
+def n_devices():
+    n = C.c_int()
+    _check(lib.flsgpu_n_devices(C.byref(n)), "n_devices")
+    return n.value
 
 
 def agg_reset(ptr, stream=0):

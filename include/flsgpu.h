@@ -35,9 +35,14 @@ const char* flsgpu_last_error(void);
 const char* flsgpu_version(void);
 
 /* ---- device ------------------------------------------------------------------------------------------ */
-/* Select the devices this process will use (one process per GPU: n_devices = 1).  No reference counterpart. */
+/* The CUDA devices this process uses, by ordinal (an ordinal may repeat).  One process per GPU (torchrun) passes one.  A
+ * single-process host with N worker threads - DuckDB (reference fls_multi_file_info.cpp:99-110: one worker per row group
+ * inside one process) - passes all of them, opens one handle per device over the same host image (flsgpu_table_share +
+ * flsgpu_table_bind_device) and sends each batch of row groups to one handle: row groups are independent, so nothing is
+ * exchanged between devices.  Not calling it = {0}.  No reference counterpart. */
 int flsgpu_init(int n_devices, const int* device_ids);
-int flsgpu_device_count(int* out);
+int flsgpu_device_count(int* out); /* CUDA devices visible to the process */
+int flsgpu_n_devices(int* out);    /* length of flsgpu_init's list */
 
 /* ---- writer: COPY ... (FORMAT fls), reference src/writer/fls_writer.cpp -------------------------------- */
 typedef struct flsgpu_column_spec {
@@ -85,6 +90,11 @@ void flsgpu_writer_destroy(flsgpu_writer* w);
 int flsgpu_table_open(const char* path, flsgpu_table** out);                         /* table_metadata.cpp:13-16 */
 int flsgpu_table_open_memory(const void* bytes, uint64_t size, int copy, flsgpu_table** out);
 void flsgpu_table_close(flsgpu_table* t);
+/* A second handle over the same host image (not copied, not validated again); every handle has its own device state. */
+int flsgpu_table_share(const flsgpu_table* src, flsgpu_table** out);
+/* Bind the handle to flsgpu_init's device_ids[device_index]: its HBM arena, staging copies and kernels live there.
+ * Before the first staging / decode call of the handle; default index 0. */
+int flsgpu_table_bind_device(flsgpu_table* t, int device_index);
 
 typedef struct flsgpu_table_info {
 	uint32_t n_columns;
