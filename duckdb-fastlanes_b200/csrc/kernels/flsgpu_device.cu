@@ -1985,3 +1985,165 @@ int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {
 }
 
 } // extern "C"
+
+// ---- allocation-free variant of the dictionary string filter ----------------------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+// the scratch string_filter_pass_dict takes from the stream-ordered pool lives here in a file-scope device array instead.
+// No counterpart in the reference.  Every device that loads the library holds
+// the array until the process exits.  The array's name is a host-side stand-in in host code: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current (static_scratch_of).
+#define FLS_STATIC_SCRATCH_BYTES FLSGPU_STATIC_SCRATCH_BYTES
+static __device__ __align__(256) uint8_t g_static_scratch[FLS_STATIC_SCRATCH_BYTES];
+
+// Device code names the array directly: the flag bytes of the keys start at zero on every call (the array keeps the last
+// call's contents).
+static __global__ void fls_static_scratch_clear_kernel(uint64_t offset, uint64_t bytes) {
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; // 16 bytes per thread; offset and bytes are multiples of 256
+	if (i * 16u < bytes) {
+		*reinterpret_cast<uint4*>(g_static_scratch + offset + i * 16u) = make_uint4(0u, 0u, 0u, 0u);
+	}
+}
+
+namespace {
+
+constexpr int kMaxStaticDevices = 64;
+constexpr uint32_t kStaticMaxRowgroups = 1024; // tuple counts of the range go through a stack array
+
+// Device address of g_static_scratch on CUDA ordinal `ordinal`, which must be the calling thread's current device.
+int static_scratch_of(int ordinal, uint8_t** out) {
+	static std::mutex mu;
+	static uint8_t* addr[kMaxStaticDevices] = {};
+	if (ordinal < 0 || ordinal >= kMaxStaticDevices) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "static scratch: device ordinal beyond 63");
+	}
+	std::lock_guard<std::mutex> g(mu);
+	if (!addr[ordinal]) {
+		int cur = -1;
+		FLS_CUDA(cudaGetDevice(&cur));
+		if (cur != ordinal) {
+			return fls_set_error(FLSGPU_ERR_CUDA, "static scratch: the table's device is not current");
+		}
+		uint8_t* p = nullptr;
+		FLS_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_scratch));
+		if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) {
+			return fls_set_error(FLSGPU_ERR_CUDA, "static scratch: cudaGetSymbolAddress returned a null or misaligned address");
+		}
+		addr[ordinal] = p;
+	}
+	*out = addr[ordinal];
+	return FLSGPU_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int flsgpu_filter_mask_string_dict_static(flsgpu_table* t, const flsgpu_filter* filter, uint32_t rg_begin, uint32_t n_rg,
+                                          const uint8_t* rg_keep_dev, uint32_t* mask_dev, uint64_t mask_capacity_bytes,
+                                          void* cuda_stream) {
+	const char* who = "flsgpu_filter_mask_string_dict_static";
+	int rc = check_range(t, 0, rg_begin, n_rg, who);
+	if (!rc) {
+		rc = check_filters(t, filter, filter ? 1u : 0u, who);
+	}
+	if (rc) {
+		return rc;
+	}
+	if (!filter || t->columns[filter->col].phys_bits != 128) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_filter_mask_string_dict_static: one filter on a VARCHAR / BLOB column is required");
+	}
+	if (!t->dev) { // creating the device state allocates the arena: that is flsgpu_table_stage's business, not this call's
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_filter_mask_string_dict_static: table not staged (this call allocates nothing: call flsgpu_table_stage first)");
+	}
+	if (n_rg > kStaticMaxRowgroups) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_filter_mask_string_dict_static: more than 1024 row groups in one call");
+	}
+	const uint64_t need = (uint64_t)n_rg * t->header.vec_per_rowgroup * 128u;
+	if (!mask_dev || (reinterpret_cast<uintptr_t>(mask_dev) & 15u) || mask_capacity_bytes < need) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_filter_mask_string_dict_static: mask buffer null, misaligned or too small");
+	}
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
+		if (!is_dict_string_enc(t->chunk(r, filter->col).encoding)) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_filter_mask_string_dict_static: a chunk of the range is not dictionary encoded (use flsgpu_filter_mask)");
+		}
+	}
+	uint64_t n_keys = 0, heap_bytes = 0;
+	rc = flsgpu_string_dict_keys(t, filter->col, rg_begin, n_rg, &n_keys);
+	if (!rc) {
+		rc = flsgpu_string_heap_bytes(t, filter->col, rg_begin, n_rg, &heap_bytes);
+	}
+	if (rc) {
+		return rc;
+	}
+	// layout inside the array, every part 256-byte aligned: keys (string_t) | dictionary bytes | flag per key | constant | tuple counts
+	const uint64_t keys_cap = ((n_keys * 16u + 255u) & ~255ull) + 256u, heap_cap = ((heap_bytes + 255u) & ~255ull) + 256u;
+	const uint64_t flags_cap = ((n_keys + 255u) & ~255ull) + 256u, const_cap = ((filter->str_len + 255u) & ~255ull) + 256u;
+	const uint64_t counts_cap = ((uint64_t)n_rg * 4u + 255u) & ~255ull;
+	const uint64_t total = keys_cap + heap_cap + flags_cap + const_cap + counts_cap;
+	if (n_keys > 0xffffffffull || total > (uint64_t)FLS_STATIC_SCRATCH_BYTES) {
+		char msg[256];
+		std::snprintf(msg, sizeof(msg),
+		              "flsgpu_filter_mask_string_dict_static: the range needs %llu bytes of scratch (%llu keys, %llu dictionary bytes), the "
+		              "static array holds %llu: use fewer row groups per call or flsgpu_filter_mask",
+		              (unsigned long long)total, (unsigned long long)n_keys, (unsigned long long)heap_bytes,
+		              (unsigned long long)FLS_STATIC_SCRATCH_BYTES);
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, msg);
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d); // makes the table's device current; t->dev exists, nothing is created
+	if (rc) {
+		return rc;
+	}
+	uint8_t* scratch = nullptr;
+	rc = static_scratch_of(d->device, &scratch);
+	if (rc) {
+		return rc;
+	}
+	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+	uint8_t* keys_dev = scratch;
+	uint8_t* heap_dev = keys_dev + keys_cap;
+	uint8_t* flags_dev = heap_dev + heap_cap;
+	uint8_t* const_dev = flags_dev + flags_cap;
+	uint32_t* counts_dev = reinterpret_cast<uint32_t*>(const_dev + const_cap);
+	uint32_t counts[kStaticMaxRowgroups];
+	for (uint32_t r = 0; r < n_rg; ++r) {
+		counts[r] = t->rowgroups[rg_begin + r].n_tuples;
+	}
+	FLS_CUDA(cudaMemsetAsync(mask_dev, 0, need, s)); // vectors nobody writes select nothing (as flsgpu_filter_mask)
+	fls_static_scratch_clear_kernel<<<(uint32_t)((flags_cap / 16u + 255u) / 256u), 256, 0, s>>>(keys_cap + heap_cap, flags_cap);
+	FLS_CUDA(cudaGetLastError());
+	FLS_CUDA(cudaMemcpyAsync(counts_dev, counts, (size_t)n_rg * 4u, cudaMemcpyHostToDevice, s)); // pageable sources: staged before
+	if (filter->str_len) {                                                                         // the call returns
+		FLS_CUDA(cudaMemcpyAsync(const_dev, filter->str_data, filter->str_len, cudaMemcpyHostToDevice, s));
+	}
+	rc = flsgpu_decode_string_dict(t, filter->col, rg_begin, n_rg, keys_dev, keys_cap, heap_dev, heap_cap, reinterpret_cast<uint64_t>(heap_dev), s);
+	if (rc) {
+		return rc;
+	}
+	FlsStrFilterLaunch K {};
+	K.rows = keys_dev;
+	K.const_data = const_dev;
+	K.const_len = (uint32_t)filter->str_len;
+	if (filter->str_len) {
+		std::memcpy(&K.const_prefix, filter->str_data, (size_t)std::min<uint64_t>(4, filter->str_len));
+	}
+	K.op = (uint32_t)filter->op;
+	K.key_flags_out = flags_dev;
+	K.n_keys = (uint32_t)n_keys;
+	FLS_CUDA(fls_str_launch_key_flags(K, s));
+	FlsStrLaunch L {};
+	rc = string_launch_setup(t, filter->col, rg_begin, n_rg, who, &d, &L, s);
+	if (rc) {
+		return rc;
+	}
+	L.key_flags = flags_dev;
+	L.n_tuples = counts_dev;
+	L.rg_keep = rg_keep_dev;
+	L.filter_mask = mask_dev;
+	L.filter_and = 0u;
+	FLS_CUDA(fls_str_launch_rows(L, s));
+	g_launches.fetch_add(3, std::memory_order_relaxed);
+	return FLSGPU_OK;
+}
+
+} // extern "C"

@@ -154,7 +154,7 @@ ABI_SYMBOLS = [
     "flsgpu_rowgroup_prune", "flsgpu_filter_mask", "flsgpu_aggregate_column_masked", "flsgpu_scan_filtered_to_host",
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
     "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms", "flsgpu_transfer_bytes",
-    "flsgpu_n_devices", "flsgpu_table_share", "flsgpu_table_bind_device",
+    "flsgpu_n_devices", "flsgpu_table_share", "flsgpu_table_bind_device", "flsgpu_filter_mask_string_dict_static",
 ]
 
 
@@ -387,6 +387,12 @@ class Table:
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_filter_mask(self._h, make_filters(filters), len(filters), rg_begin, n_rg, _vp(keep_ptr), _vp(mask_ptr),
                                       C.c_uint64(mask_bytes), _vp(stream)), "filter_mask")
+
+    def filter_mask_string_dict_static(self, filt, mask_ptr, mask_bytes, keep_ptr=0, rg_begin=0, n_rg=None, stream=0):
+        """One string filter over a dictionary-encoded range, scratch in the library's static device array (no allocation)."""
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        _check(lib.flsgpu_filter_mask_string_dict_static(self._h, make_filters([filt]), rg_begin, n_rg, _vp(keep_ptr), _vp(mask_ptr),
+                                                         C.c_uint64(mask_bytes), _vp(stream)), "filter_mask_string_dict_static")
 
     def aggregate_column_masked(self, col, mask_ptr, result_ptr, keep_ptr=0, rg_begin=0, n_rg=None, stream=0):
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg

@@ -242,6 +242,21 @@ int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n
  * *result_dev like flsgpu_aggregate_column; min_val / max_val are not produced. */
 int flsgpu_aggregate_column_masked(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const uint32_t* mask_dev,
                                    const uint8_t* rg_keep_dev, flsgpu_agg_result* result_dev, void* cuda_stream);
+/* Allocation-free variant of flsgpu_filter_mask for ONE constant comparison on a VARCHAR / BLOB column whose chunks in the
+ * range are all dictionary encoded (DICT_STR / FSST_DICT / FSST12_DICT).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The scratch flsgpu_filter_mask takes from a stream-ordered pool (string_t + bytes of
+ * the range's dictionary keys, one flag byte per key, the constant, the row groups' tuple counts) lives in a static device
+ * array of FLSGPU_STATIC_SCRATCH_BYTES that every device loading the library holds until exit; the call issues no
+ * cudaMalloc / cudaFree / pool allocation.  Requirements: the table is staged already (staging allocates the arena; a
+ * table without device state is refused), n_rg <= 1024, and the range's scratch need fits the array - otherwise
+ * FLSGPU_ERR_UNSUPPORTED with the sizes in the message (split the range, or use flsgpu_filter_mask).  Same mask layout and
+ * rg_keep_dev meaning as flsgpu_filter_mask; the mask is overwritten, not ANDed.  Asynchronous on cuda_stream.  All calls of
+ * a device share the one array: calls that overlap on the GPU (different streams, or threads) race - serialise them. */
+#define FLSGPU_STATIC_SCRATCH_BYTES (4u << 20)
+int flsgpu_filter_mask_string_dict_static(flsgpu_table* t, const flsgpu_filter* filter, uint32_t rg_begin, uint32_t n_rg,
+                                          const uint8_t* rg_keep_dev, uint32_t* mask_dev, uint64_t mask_capacity_bytes,
+                                          void* cuda_stream);
 
 /* ---- end to end from host buffers: what FastLanesReader::Scan hands to DuckDB -------------------------- */
 /* Stage (H2D) + decode + copy back (D2H) into pinned/pageable host memory `out_host`, pipelined in slabs of
