@@ -1,4 +1,5 @@
-// fls_strings.cpp — string column chunks (VARCHAR / BLOB): STR_CONSTANT, STR_UNCOMPRESSED, DICT_STR, FSST, FSST_DICT.
+// fls_strings.cpp — string column chunks (VARCHAR / BLOB): STR_CONSTANT, STR_UNCOMPRESSED, DICT_STR, FSST, FSST_DICT, FSST12,
+// FSST12_DICT, RLE_STR, CROSS_RLE_STR, FREQUENCY_STR.
 // Layouts: include/fls_format.h ("String columns").  Stands in for the string side of fastlanes::RowGroupWriter
 // (reference src/writer/fls_writer.cpp:14-39; fls_view_writer.cpp:61-94 hands VARCHAR/BLOB to the library as
 // offsets + bytes); which scheme a chunk gets is encoder policy (absent library), here: smallest estimated size.
@@ -219,6 +220,129 @@ void encode_str_dict(const StrChunk& c, const StrDict& dict, int enc_kind, Encod
 	b.finish(out, d);
 }
 
+// value strings of the VALUE encodings: bytes back to back + end offsets
+struct StrValues {
+	std::vector<uint8_t> bytes;
+	std::vector<uint32_t> ends;
+	void push(std::string_view s) {
+		bytes.insert(bytes.end(), s.begin(), s.end());
+		ends.push_back((uint32_t)bytes.size());
+	}
+	void into(ChunkBuilder& b, fls_chunk_desc& d) const {
+		b.aux0 = bytes;
+		append_u32(b.aux1, ends);
+		d.aux_count = (uint32_t)ends.size();
+		d.const_val = bytes.size();
+	}
+};
+
+// row i of the chunk, padding rows of the last vector repeat the last real string
+std::string_view padded_at(const StrChunk& c, uint32_t i) {
+	return c.at(std::min(i, c.n_tuples - 1));
+}
+
+// RLE_STR (dec_rle_map_opr<fls_string_t, u16>, rle_map_kernel.hpp:26-61): per vector its run strings and the run index of every
+// row, DELTA-coded like the numeric RLE index
+void encode_str_rle(const StrChunk& c, EncodedChunk& out) {
+	ChunkBuilder b;
+	fls_chunk_desc d = c.base_desc(FLS_ENC_RLE_STR);
+	d.idx_bits = 16;
+	StrValues vals;
+	unsigned maxw = 0;
+	uint16_t idxs[kVec];
+	for (uint32_t v = 0; v < c.n_vec; ++v) {
+		fls_vec_meta m {};
+		m.n_valid = c.valid_in(v);
+		m.aux_off = (uint32_t)vals.ends.size();
+		uint16_t run = 0;
+		std::string_view prev = padded_at(c, v * kVec);
+		vals.push(prev);
+		idxs[0] = 0;
+		for (int i = 1; i < kVec; ++i) {
+			const std::string_view cur = padded_at(c, v * kVec + i);
+			if (cur != prev) {
+				++run;
+				vals.push(cur);
+				prev = cur;
+			}
+			idxs[i] = run;
+		}
+		m.aux_cnt = (uint16_t)(run + 1u);
+		delta_encode_vector<uint16_t>(idxs, b, m);
+		maxw = std::max<unsigned>(maxw, m.width);
+		b.meta.push_back(m);
+	}
+	d.max_width = (uint8_t)maxw;
+	vals.into(b, d);
+	b.finish(out, d);
+}
+
+// CROSS_RLE_STR (dec_cross_rle_opr<fls_string_t>, cross_rle_kernel.hpp:55-97): runs over the whole chunk
+void encode_str_cross_rle(const StrChunk& c, EncodedChunk& out) {
+	ChunkBuilder b;
+	plain_meta(c, b);
+	fls_chunk_desc d = c.base_desc(FLS_ENC_CROSS_RLE_STR);
+	StrValues vals;
+	std::vector<uint32_t> lens;
+	const uint32_t total = c.n_vec * kVec;
+	for (uint32_t i = 0; i < total;) {
+		const std::string_view s = padded_at(c, i);
+		uint32_t j = i + 1;
+		while (j < total && padded_at(c, j) == s) {
+			++j;
+		}
+		vals.push(s);
+		lens.push_back(j - i);
+		i = j;
+	}
+	vals.into(b, d);
+	append_u32(b.aux1, lens);
+	b.finish(out, d);
+}
+
+// FREQUENCY_STR (dec_frequency_str_opr, frequency_kernel.hpp:23-69): per vector the most frequent string once, and the rows that
+// differ as (position, string) exceptions in position order
+void encode_str_frequency(const StrChunk& c, EncodedChunk& out) {
+	ChunkBuilder b;
+	fls_chunk_desc d = c.base_desc(FLS_ENC_FREQUENCY_STR);
+	StrValues vals;
+	for (uint32_t v = 0; v < c.n_vec; ++v) {
+		std::unordered_map<std::string_view, uint32_t> count;
+		std::string_view freq = padded_at(c, v * kVec);
+		uint32_t best = 0;
+		for (int i = 0; i < kVec; ++i) {
+			const std::string_view s = padded_at(c, v * kVec + i);
+			const uint32_t n = ++count[s];
+			if (n > best) { // first string to reach the highest count: deterministic
+				best = n;
+				freq = s;
+			}
+		}
+		fls_vec_meta m {};
+		m.n_valid = c.valid_in(v);
+		m.aux_off = (uint32_t)vals.ends.size();
+		m.data_off16 = (uint32_t)(b.data.size() / 16);
+		vals.push(freq);
+		std::vector<uint16_t> pos;
+		for (int i = 0; i < kVec; ++i) {
+			const std::string_view s = padded_at(c, v * kVec + i);
+			if (s != freq) {
+				pos.push_back((uint16_t)i);
+				vals.push(s);
+			}
+		}
+		m.aux_cnt = (uint16_t)pos.size();
+		const size_t o = b.data.size();
+		b.data.resize(o + FLS_PAD16(pos.size() * 2), 0);
+		if (!pos.empty()) {
+			std::memcpy(b.data.data() + o, pos.data(), pos.size() * 2);
+		}
+		b.meta.push_back(m);
+	}
+	vals.into(b, d);
+	b.finish(out, d);
+}
+
 } // namespace
 
 bool encode_string_chunk(const uint64_t* offsets, const uint8_t* bytes, uint32_t n_tuples, int force_encoding, EncodedChunk& out,
@@ -279,6 +403,9 @@ bool encode_string_chunk(const uint64_t* offsets, const uint8_t* bytes, uint32_t
 		}
 		encode_str_dict(c, dict, enc, out);
 		return true;
+	case FLS_ENC_RLE_STR: encode_str_rle(c, out); return true;
+	case FLS_ENC_CROSS_RLE_STR: encode_str_cross_rle(c, out); return true;
+	case FLS_ENC_FREQUENCY_STR: encode_str_frequency(c, out); return true;
 	default: *err = "encoding not applicable to a string column"; return false;
 	}
 }

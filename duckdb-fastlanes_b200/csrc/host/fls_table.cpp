@@ -39,7 +39,8 @@ static unsigned blob_bytes(const fls_chunk_desc& c, const fls_vec_meta& m) {
 }
 
 static bool is_string_enc(unsigned enc) {
-	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_STR_UNCOMPRESSED || enc == FLS_ENC_STR_CONSTANT || FLS_ENC_IS_FSST_ANY(enc);
+	return enc == FLS_ENC_DICT_STR || enc == FLS_ENC_STR_UNCOMPRESSED || enc == FLS_ENC_STR_CONSTANT || FLS_ENC_IS_FSST_ANY(enc) ||
+	       FLS_ENC_IS_STR_VALUES(enc);
 }
 
 // String chunk (fls_format.h "String columns"): every offset array must be monotone and end at its byte segment's size,
@@ -59,6 +60,61 @@ static const char* validate_string_chunk(const flsgpu_table* t, const fls_chunk_
 	}
 	if (ch.encoding == FLS_ENC_STR_CONSTANT) {
 		return (ch.seg_size[FLS_SEG_AUX0] == ch.aux_count && ch.const_val == ch.aux_count) ? nullptr : "constant string segment has the wrong size";
+	}
+	if (FLS_ENC_IS_STR_VALUES(ch.encoding)) {
+		// value strings: bytes in AUX0, monotone end offsets covering them in AUX1 (CROSS_RLE_STR: followed by the run lengths)
+		const uint64_t nv = ch.aux_count;
+		const bool cross = ch.encoding == FLS_ENC_CROSS_RLE_STR;
+		if (nv == 0 || ch.seg_size[FLS_SEG_AUX1] != nv * 4 * (cross ? 2 : 1)) {
+			return "value string offsets have the wrong size";
+		}
+		uint32_t prev = 0;
+		for (uint64_t i = 0; i < nv; ++i) {
+			if (aux1[i] < prev) {
+				return "string end offsets are not monotone";
+			}
+			prev = aux1[i];
+		}
+		if (prev != ch.seg_size[FLS_SEG_AUX0] || ch.const_val != prev) {
+			return "string end offsets do not cover the byte segment";
+		}
+		if (cross) {
+			uint64_t sum = 0;
+			for (uint64_t i = 0; i < nv; ++i) {
+				if (aux1[nv + i] == 0) {
+					return "CROSS_RLE_STR run of length zero";
+				}
+				sum += aux1[nv + i];
+			}
+			return sum == (uint64_t)ch.n_vec * FLS_VEC_SZ ? nullptr : "CROSS_RLE_STR run lengths do not cover the chunk";
+		}
+		const uint8_t* data_seg = base + ch.seg_off[FLS_SEG_DATA];
+		uint64_t next = 0; // the vectors' value ranges follow each other and cover the chunk's values
+		for (uint32_t v = 0; v < ch.n_vec; ++v) {
+			const fls_vec_meta& m = meta[v];
+			const bool rle = ch.encoding == FLS_ENC_RLE_STR;
+			const uint64_t n_vals = rle ? m.aux_cnt : (uint64_t)m.aux_cnt + 1u;
+			const uint64_t blob = rle ? 128u + 128u * m.width : FLS_PAD16((uint64_t)m.aux_cnt * 2u);
+			if (m.aux_off != next || n_vals == 0 || m.aux_cnt > FLS_VEC_SZ || m.aux_off + n_vals > nv) {
+				return "vector value range outside the chunk's value strings";
+			}
+			next += n_vals;
+			if ((rle && m.width > 16) || (uint64_t)m.data_off16 * 16 + blob > ch.seg_size[FLS_SEG_DATA] || blob > ch.max_blob_bytes) {
+				return "vector entry point or width out of range";
+			}
+			if (!rle) { // exception positions ascend strictly and stay inside the vector
+				const uint16_t* pos = reinterpret_cast<const uint16_t*>(data_seg + (uint64_t)m.data_off16 * 16);
+				for (uint32_t k = 0; k < m.aux_cnt; ++k) {
+					if (pos[k] >= FLS_VEC_SZ || (k && pos[k] <= pos[k - 1])) {
+						return "exception positions out of range or not ascending";
+					}
+				}
+			}
+		}
+		if (ch.encoding == FLS_ENC_RLE_STR && ch.idx_bits != 16) {
+			return "RLE_STR idx_bits must be 16";
+		}
+		return next == nv ? nullptr : "vector value ranges do not cover the chunk's value strings";
 	}
 	const uint64_t n = dict ? ch.aux_count : (uint64_t)ch.n_vec * FLS_VEC_SZ;
 	if (n == 0 || ch.aux_count != n) {

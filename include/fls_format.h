@@ -72,7 +72,10 @@ typedef enum fls_encoding {
 	FLS_ENC_FSST_DICT = 15,   /* dec_fsst_dict_opr<IDX>: dictionary whose strings are FSST-compressed + packed codes */
 	FLS_ENC_FSST12 = 16,      /* dec_fsst12_opr: FSST with 12-bit codes (4096 symbols, codes < 256 = the byte itself, no escapes) */
 	FLS_ENC_FSST12_DICT = 17, /* dec_fsst12_dict_opr<IDX> */
-	FLS_ENC_COUNT = 18
+	FLS_ENC_RLE_STR = 18,       /* dec_rle_map_opr<fls_string_t,u16> (rle_map_kernel.hpp:26-61): run strings + DELTA-coded run index */
+	FLS_ENC_CROSS_RLE_STR = 19, /* dec_cross_rle_opr<fls_string_t> (cross_rle_kernel.hpp:55-97,121-144): row-group wide (string,length) runs */
+	FLS_ENC_FREQUENCY_STR = 20, /* dec_frequency_str_opr (frequency_kernel.hpp:23-69): frequent string + exceptions */
+	FLS_ENC_COUNT = 21
 } fls_encoding;
 
 #define FLS_ENC_IS_FSST8(e) ((e) == FLS_ENC_FSST || (e) == FLS_ENC_FSST_DICT)
@@ -80,6 +83,9 @@ typedef enum fls_encoding {
 #define FLS_ENC_IS_FSST_ANY(e) (FLS_ENC_IS_FSST8(e) || FLS_ENC_IS_FSST12(e))
 #define FLS_ENC_IS_FSST_ROWS(e) ((e) == FLS_ENC_FSST || (e) == FLS_ENC_FSST12) /* one compressed string per row */
 #define FLS_ENC_IS_STR_DICT(e) ((e) == FLS_ENC_DICT_STR || (e) == FLS_ENC_FSST_DICT || (e) == FLS_ENC_FSST12_DICT)
+/* string encodings whose rows name one of aux_count VALUE strings (bytes in AUX0, u32 end[aux_count] in AUX1) by a rule of
+ * their own: run index, run position, exception list */
+#define FLS_ENC_IS_STR_VALUES(e) ((e) == FLS_ENC_RLE_STR || (e) == FLS_ENC_CROSS_RLE_STR || (e) == FLS_ENC_FREQUENCY_STR)
 
 /* Segment slots inside a column chunk. */
 enum {
@@ -188,6 +194,15 @@ typedef struct fls_vec_meta { /* 32 bytes */
  *   FSST:             AUX0 = fls_fsst_table | compressed bytes; AUX1 = u32 comp_end[n] | u32 dec_end[n]
  *   FSST_DICT:        META/DATA = packed codes; AUX0 = fls_fsst_table | compressed dictionary; AUX1 = comp_end[n_keys] | dec_end[n_keys]
  *   FSST12 / FSST12_DICT: the same with fls_fsst12_table and 12-bit code streams
+ *   RLE_STR:          per vector the strings of its runs + the run index of every row: META aux_off = first run of the vector
+ *                     among the chunk's runs, aux_cnt = its runs; DATA = [128 lane bases][128*W deltas] of the u16 run index
+ *                     (as numeric RLE); AUX0 = bytes of all run strings; AUX1 = u32 end[aux_count]; aux_count = runs of the chunk
+ *   CROSS_RLE_STR:    runs over the whole chunk (padding rows of the last vector extend the last run): AUX0 = bytes of the run
+ *                     strings; AUX1 = u32 end[aux_count] | u32 length[aux_count] (lengths sum to n_vec*1024)
+ *   FREQUENCY_STR:    per vector one frequent string and the rows that differ: META aux_off = index of the vector's frequent
+ *                     string among the chunk's value strings, aux_cnt = n exceptions, whose strings are values aux_off+1 ..
+ *                     aux_off+n in position order; DATA blob = u16 position[n] ascending, padded to 16 B; AUX0 = bytes of all
+ *                     value strings; AUX1 = u32 end[aux_count]; aux_count = value strings of the chunk (n_vec + all exceptions)
  * const_val = number of DECODED string bytes of the chunk (its share of the string heap); the per-string decoded end
  * offsets make every string's heap position known without decoding its predecessors (entry points, like PointTo). */
 typedef struct fls_fsst_table { /* fsst_decoder_t of duckdb/third_party/fsst/fsst.h:70-75 without its header bytes */
