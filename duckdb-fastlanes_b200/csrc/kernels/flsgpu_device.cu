@@ -253,7 +253,7 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 	std::vector<uint64_t> starts_off(n_chunks, ~0ull);
 	uint64_t n_starts = 0;
 	for (uint64_t i = 0; i < n_chunks; ++i) {
-		if (t->chunks[i].encoding == FLS_ENC_CROSS_RLE) {
+		if (t->chunks[i].encoding == FLS_ENC_CROSS_RLE || t->chunks[i].encoding == FLS_ENC_CROSS_RLE_STR) {
 			starts_off[i] = n_starts;
 			n_starts += (uint64_t)t->chunks[i].aux_count + 1;
 		}
@@ -265,7 +265,8 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 				continue;
 			}
 			const fls_chunk_desc& c = t->chunks[i];
-			const uint32_t* lens = reinterpret_cast<const uint32_t*>(t->bytes + c.offset + c.seg_off[FLS_SEG_AUX1]);
+			const uint32_t* lens = reinterpret_cast<const uint32_t*>(t->bytes + c.offset + c.seg_off[FLS_SEG_AUX1]) +
+			                       (c.encoding == FLS_ENC_CROSS_RLE_STR ? c.aux_count : 0u); // strings: the end offsets come first
 			uint32_t acc = 0;
 			uint32_t* s = starts.data() + starts_off[i];
 			for (uint32_t r = 0; r < c.aux_count; ++r) {
@@ -314,6 +315,9 @@ int device_state_create(flsgpu_table* t, FlsDeviceState* d) {
 		o.aux0 = base + c.seg_off[FLS_SEG_AUX0];
 		o.aux1 = c.encoding == FLS_ENC_CROSS_RLE ? reinterpret_cast<const uint8_t*>(d->d_run_starts + starts_off[i])
 		                                         : base + c.seg_off[FLS_SEG_AUX1];
+		if (c.encoding == FLS_ENC_CROSS_RLE_STR) { // no DATA segment: the slot carries the run starts, AUX1 keeps the end offsets
+			o.data = reinterpret_cast<const uint8_t*>(d->d_run_starts + starts_off[i]);
+		}
 		o.const_val = c.const_val;
 		o.aux_count = c.aux_count;
 		o.n_vec = (uint16_t)c.n_vec;

@@ -476,6 +476,78 @@ __device__ __forceinline__ void vector_codes(const FlsChunkDev* ch, uint32_t vi,
 	__syncwarp();
 }
 
+// VALUE encodings (fls_format.h FLS_ENC_IS_STR_VALUES): tile[row] = which of the chunk's value strings row `row` of vector vi is.
+//   RLE_STR (rle_map_kernel.hpp:26-61): the DELTA-coded u16 run index, unpacked and summed per FastLanes lane exactly like the
+//     numeric RLE index (process_rle): a thread owns lanes 2*lane, 2*lane + 1, whose 16 rows are 16 consecutive logical positions
+//     starting at chain_pos; value = first run of the vector + index
+//   CROSS_RLE_STR (cross_rle_kernel.hpp:55-97): binary search of the row's position in the run starts (prefix sums built at
+//     stage time) instead of the reference's rescan of the run lengths per vector
+//   FREQUENCY_STR (frequency_kernel.hpp:23-69): every row is the vector's frequent string, then the exceptions are patched in
+__device__ __forceinline__ int chain_pos(int fl_lane) { // logical start of the 16-row chain of 16-bit lane fl_lane
+	return (fl_lane & 15) * 64 + fl_order((fl_lane >> 4) & 7) * 8;
+}
+
+__device__ __forceinline__ void vector_value_index(const FlsChunkDev* ch, uint32_t enc, uint32_t vi, uint32_t lane, uint32_t* tile) {
+	const uint4* mp = reinterpret_cast<const uint4*>(ch->meta + vi);
+	const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1); // {base lo, base hi, data_off16, aux_off}, {aux_cnt | width << 16 ..}
+	const uint32_t first = m0.w, cnt = m1.x & 0xffffu, n_vals = ch->aux_count;
+	if (enc == FLS_ENC_RLE_STR) {
+		const uint32_t W = (m1.x >> 16) & 0xffu, dmin = m0.x;
+		const uint32_t* blob = reinterpret_cast<const uint32_t*>(ch->data + (size_t)m0.z * 16);
+		uint32_t v[32];
+		unpack_small_dispatch<16>((int)W, blob + 32, (int)lane, v);
+		const uint32_t bw = __ldg(blob + lane);
+#pragma unroll
+		for (int h = 0; h < 2; ++h) {
+			uint32_t acc = (bw >> (16 * h)) & 0xffffu;
+			const int p0 = chain_pos(2 * (int)lane + h);
+#pragma unroll
+			for (int row = 0; row < 16; ++row) {
+				acc += v[2 * row + h] + dmin;
+				tile[p0 + row] = min(first + min(acc & 0xffffu, cnt - 1u), n_vals - 1u); // clamped: never outside the value strings
+			}
+		}
+	} else if (enc == FLS_ENC_CROSS_RLE_STR) {
+		const uint32_t* starts = reinterpret_cast<const uint32_t*>(ch->data);
+		const uint32_t g0 = vi * 1024u;
+		uint32_t lo_r = 0, hi_r = n_vals; // first run of this vector: largest r with starts[r] <= g0
+		while (hi_r - lo_r > 1) {
+			const uint32_t mid = (lo_r + hi_r) >> 1;
+			if (__ldg(starts + mid) <= g0) {
+				lo_r = mid;
+			} else {
+				hi_r = mid;
+			}
+		}
+#pragma unroll 1
+		for (uint32_t it = 0; it < 32u; ++it) {
+			const uint32_t gi = g0 + it * 32u + lane;
+			uint32_t a = lo_r, b = min(n_vals, lo_r + 1025u);
+			while (b - a > 1) {
+				const uint32_t mid = (a + b) >> 1;
+				if (__ldg(starts + mid) <= gi) {
+					a = mid;
+				} else {
+					b = mid;
+				}
+			}
+			tile[it * 32u + lane] = a;
+		}
+	} else { // FREQUENCY_STR
+		const uint32_t freq = min(first, n_vals - 1u);
+#pragma unroll 4
+		for (uint32_t it = 0; it < 32u; ++it) {
+			tile[it * 32u + lane] = freq;
+		}
+		__syncwarp();
+		const uint16_t* pos = reinterpret_cast<const uint16_t*>(ch->data + (size_t)m0.z * 16);
+		for (uint32_t k = lane; k < cnt; k += 32u) {
+			tile[__ldg(pos + k) & 1023u] = min(first + 1u + k, n_vals - 1u);
+		}
+	}
+	__syncwarp();
+}
+
 // one warp per vector: 1024 string_t (flat form), or the u32 codes (selection vector) when L.codes_only
 __device__ __forceinline__ void str_rows_body(const FlsStrLaunch& L) {
 	__shared__ uint32_t s_codes[kWarps][1024];
@@ -542,9 +614,13 @@ __device__ __forceinline__ void str_rows_body(const FlsStrLaunch& L) {
 		for (int it = 0; it < 32; ++it) {
 			out[it * 32 + lane] = s;
 		}
-	} else if (dict) {
+	} else if (dict || FLS_ENC_IS_STR_VALUES(enc)) {
 		uint32_t* tile = s_codes[warp];
-		vector_codes(ch, vi, lane, tile);
+		if (dict) {
+			vector_codes(ch, vi, lane, tile);
+		} else {
+			vector_value_index(ch, enc, vi, lane, tile);
+		}
 #pragma unroll 2
 		for (int it = 0; it < 32; ++it) {
 			const uint32_t k = tile[it * 32 + lane];

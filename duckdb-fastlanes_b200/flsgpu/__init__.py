@@ -21,7 +21,8 @@ lib = C.CDLL(LIB_PATH)
 TYPE = dict(INT8=1, INT16=2, INT32=3, INT64=4, UINT8=5, UINT16=6, UINT32=7, UINT64=8, FLOAT=9, DOUBLE=10,
             BOOLEAN=11, DATE=12, TIMESTAMP=13, DECIMAL=14, VARCHAR=15, BLOB=16)
 ENC = dict(UNCOMPRESSED=0, CONSTANT=1, FFOR=2, DELTA=3, DICT=4, RLE=5, ALP=6, ALP_RD=7, CROSS_RLE=8, FREQUENCY=9,
-           SLPATCH=10, DICT_STR=11, STR_UNCOMPRESSED=12, STR_CONSTANT=13, FSST=14, FSST_DICT=15, FSST12=16, FSST12_DICT=17)
+           SLPATCH=10, DICT_STR=11, STR_UNCOMPRESSED=12, STR_CONSTANT=13, FSST=14, FSST_DICT=15, FSST12=16, FSST12_DICT=17,
+           RLE_STR=18, CROSS_RLE_STR=19, FREQUENCY_STR=20)
 STRING_TYPES = (15, 16)
 # DuckDB string_t (string_type.hpp:236-247): u32 length + 12 bytes (inlined | 4 prefix bytes + pointer)
 STRING_T = np.dtype([("length", "<u4"), ("body", "u1", 12)])

@@ -195,6 +195,15 @@ int fls_oracle_decode_vector(const fls_oracle_table* t, uint32_t rg, uint32_t co
 	}
 }
 
+/* Run index of one RLE vector (numeric RLE and RLE_STR share the blob): [128 lane bases][128*W deltas] in 16-bit lanes ->
+ * unffor + rsum (transposed) -> untranspose_i (rle_map_kernel.hpp:45-58). */
+void fls_oracle_rle_index(const uint8_t* blob, unsigned width, uint16_t dmin, uint16_t* idx) {
+	uint16_t d16[1024], t16[1024];
+	unpack_16((const uint16_t*)(blob + 128), width, d16);
+	rsum_16((const uint16_t*)blob, d16, dmin, t16);
+	untranspose_16(t16, idx);
+}
+
 /* Codes of one vector of a dictionary-encoded chunk (numeric DICT, DICT_STR, FSST_DICT): dec_dict_opr<KEY, IDX>::Index()
  * (reference dictionary_kernel.hpp:14-20,89-99): FFOR-packed in idx_bits lanes, base = smallest code of the vector. */
 int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, uint32_t* codes) {

@@ -81,6 +81,7 @@ int fls_oracle_aggregate_masked(const fls_oracle_table* t, uint32_t col, uint32_
                                 uint64_t* sum_lo, uint64_t* sum_hi, uint64_t* count, double* fsum);
 
 /* ---- string columns (fls_oracle_str.c) ---------------------------------------------------------------------------- */
+void fls_oracle_rle_index(const uint8_t* blob, unsigned width, uint16_t dmin, uint16_t* idx /* 1024 */);
 int fls_oracle_decode_codes(const fls_oracle_table* t, uint32_t rg, uint32_t col, uint32_t vec, uint32_t* codes /* 1024 */);
 uint64_t fls_oracle_fsst_decompress(const fls_fsst_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out);
 uint64_t fls_oracle_fsst12_decompress(const fls_fsst12_table* tab, const uint8_t* in, uint64_t len_in, uint8_t* out);

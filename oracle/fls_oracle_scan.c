@@ -160,7 +160,16 @@ static void* worker(void* arg) {
 				const fls_chunk_desc* ch = &t->chunks[(size_t)rg * t->header.n_columns + j->cols[ci]];
 				const int is_dict = FLS_ENC_IS_STR_DICT(ch->encoding);
 				const uint64_t need_keys = is_dict ? (uint64_t)ch->aux_count * 16 + 16 : 0;
-				const uint64_t need_heap = (is_dict ? ch->const_val : ch->encoding == FLS_ENC_STR_CONSTANT ? (uint64_t)ch->aux_count : ch->const_val) + 64;
+				uint64_t need_heap = (is_dict ? ch->const_val : ch->encoding == FLS_ENC_STR_CONSTANT ? (uint64_t)ch->aux_count : ch->const_val) + 64;
+				if (FLS_ENC_IS_STR_VALUES(ch->encoding)) { /* AddString per row: a vector's heap holds up to 1024 copies of the longest value */
+					const uint32_t* ends = (const uint32_t*)(t->bytes + ch->offset + ch->seg_off[FLS_SEG_AUX1]);
+					uint32_t longest = 0;
+					for (uint32_t k = 0; k < ch->aux_count; ++k) {
+						const uint32_t len = ends[k] - (k ? ends[k - 1] : 0);
+						longest = len > longest ? len : longest;
+					}
+					need_heap = (uint64_t)longest * FLS_VEC_SZ + 64;
+				}
 				if (str_cap[2 * ci] < need_keys) {
 					free(str_keys[ci]);
 					str_keys[ci] = (uint8_t*)malloc(need_keys);

@@ -9,6 +9,9 @@
  *                                                                 Decode: selection vector = the codes
  *   dec_fsst_opr                  fsst_kernel.hpp:19-57           per string: fsst_decompress(decoder, len, in, 8*len, buf)
  *   dec_fsst_dict_opr             fsst_dict_kernel.hpp:20-52,54-80 FSST-decoded dictionary + codes
+ *   dec_rle_map_opr<fls_string_t> rle_map_kernel.hpp:26-61        untranspose the run index, row i = run string idxs[i]
+ *   dec_cross_rle_opr<fls_string_t> cross_rle_kernel.hpp:55-97,121-144  row-group wide runs, vector v = rows [1024 v, 1024 v + 1024)
+ *   dec_frequency_str_opr         frequency_kernel.hpp:23-69      the frequent string, except at the exception positions
  * FSST decoding = duckdb/third_party/fsst/fsst.h:162-230 (in the reference tree): code < 255 -> symbol[code] (len[code]
  * bytes), 255 -> next byte literal.  The decoded element is DuckDB's string_t
  * (duckdb/src/include/duckdb/common/types/string_type.hpp:22-60,236-247): length <= 12 -> inlined, zero padded;
@@ -82,6 +85,65 @@ uint64_t fls_oracle_fsst12_decompress(const fls_fsst12_table* tab, const uint8_t
 static uint64_t fsst_any_decompress(unsigned enc, const uint8_t* aux0, const uint8_t* in, uint64_t len_in, uint8_t* out) {
 	return FLS_ENC_IS_FSST12(enc) ? fls_oracle_fsst12_decompress((const fls_fsst12_table*)aux0, in, len_in, out)
 	                              : fls_oracle_fsst_decompress((const fls_fsst_table*)aux0, in, len_in, out);
+}
+
+/* VALUE encodings (fls_format.h FLS_ENC_IS_STR_VALUES): which of the chunk's value strings every row of vector `vec` is.
+ *   RLE_STR        rle_map_kernel.hpp:45-58: unffor + rsum of the u16 run index (left transposed), untranspose_i, then
+ *                  value = first run of the vector + idxs[i]
+ *   CROSS_RLE_STR  cross_rle_kernel.hpp:55-97: find the run that covers row 1024 * vec, then walk the run lengths
+ *   FREQUENCY_STR  frequency_kernel.hpp:44-66: walk the rows with a cursor into the ascending exception positions */
+static int value_index_of_vector(const fls_oracle_table* t, const fls_chunk_desc* ch, uint32_t vec, uint32_t* keys) {
+	const uint8_t* base = t->bytes + ch->offset;
+	const fls_vec_meta* m = (const fls_vec_meta*)(base + ch->seg_off[FLS_SEG_META]) + vec;
+	const uint8_t* blob = base + ch->seg_off[FLS_SEG_DATA] + (size_t)m->data_off16 * 16;
+	const uint32_t* aux1 = (const uint32_t*)(base + ch->seg_off[FLS_SEG_AUX1]);
+	switch (ch->encoding) {
+	case FLS_ENC_RLE_STR: {
+		uint16_t idx[FLS_VEC_SZ];
+		fls_oracle_rle_index(blob, m->width, (uint16_t)m->base, idx);
+		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+			if (idx[i] >= m->aux_cnt) {
+				return -1;
+			}
+			keys[i] = m->aux_off + idx[i];
+		}
+		return 0;
+	}
+	case FLS_ENC_CROSS_RLE_STR: {
+		const uint32_t* lens = aux1 + ch->aux_count;
+		uint64_t target = (uint64_t)vec * FLS_VEC_SZ, pos = 0;
+		uint32_t run = 0, produced = 0;
+		while (run < ch->aux_count && pos + lens[run] <= target) {
+			pos += lens[run];
+			++run;
+		}
+		uint64_t offset = target - pos;
+		while (produced < FLS_VEC_SZ && run < ch->aux_count) {
+			uint64_t avail = lens[run] - offset;
+			uint32_t take = (uint32_t)(avail < FLS_VEC_SZ - produced ? avail : FLS_VEC_SZ - produced);
+			for (uint32_t k = 0; k < take; ++k) {
+				keys[produced++] = run;
+			}
+			offset = 0;
+			++run;
+		}
+		return produced == FLS_VEC_SZ ? 0 : -1;
+	}
+	case FLS_ENC_FREQUENCY_STR: {
+		const uint16_t* pos = (const uint16_t*)blob;
+		uint32_t e = 0;
+		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+			if (e < m->aux_cnt && pos[e] == i) {
+				keys[i] = m->aux_off + 1 + e;
+				++e;
+			} else {
+				keys[i] = m->aux_off;
+			}
+		}
+		return 0;
+	}
+	default: return -3;
+	}
 }
 
 int fls_oracle_string_heap_bytes(const fls_oracle_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, uint64_t* out) {
@@ -160,6 +222,20 @@ int fls_oracle_decode_strings(const fls_oracle_table* t, uint32_t col, uint32_t 
 				}
 			}
 			break;
+		case FLS_ENC_RLE_STR:
+		case FLS_ENC_CROSS_RLE_STR:
+		case FLS_ENC_FREQUENCY_STR:
+			for (uint32_t v = 0; v < ch->n_vec; ++v) {
+				if (value_index_of_vector(t, ch, v, codes)) {
+					return -2;
+				}
+				for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+					const uint32_t k = codes[i];
+					const uint32_t start = k ? ends[k - 1] : 0;
+					make_string(&out[(uint64_t)v * FLS_VEC_SZ + i], hp + start, ends[k] - start, haddr + start);
+				}
+			}
+			break;
 		default: return -3;
 		}
 		heap_off += pad16(ch->const_val);
@@ -230,6 +306,21 @@ int fls_oracle_decode_string_vector(const fls_oracle_table* t, uint32_t rg, uint
 			const uint32_t cstart = (i0 + i) ? aux1[i0 + i - 1] : 0;
 			const uint64_t len = fsst_any_decompress(ch->encoding, aux0, codes + cstart, aux1[i0 + i] - cstart, heap + pos);
 			make_string(&out[i], heap + pos, (uint32_t)len, heap_base_addr + pos);
+			pos += len;
+		}
+		break;
+	}
+	case FLS_ENC_RLE_STR:
+	case FLS_ENC_CROSS_RLE_STR:
+	case FLS_ENC_FREQUENCY_STR: { /* AddString per row, as the reference does: the vector's heap repeats the strings */
+		uint32_t keys[FLS_VEC_SZ];
+		if (value_index_of_vector(t, ch, vec, keys)) {
+			return -2;
+		}
+		for (uint32_t i = 0; i < FLS_VEC_SZ; ++i) {
+			const uint32_t start = keys[i] ? aux1[keys[i] - 1] : 0, len = aux1[keys[i]] - start;
+			memcpy(heap + pos, aux0 + start, len);
+			make_string(&out[i], heap + pos, len, heap_base_addr + pos);
 			pos += len;
 		}
 		break;

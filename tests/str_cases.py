@@ -16,6 +16,27 @@ def comment_like(n, seed=7):
     return out
 
 
+def runs_of(n, values, max_run, seed):
+    """n strings in runs of 1..max_run rows drawn from `values` (neighbouring runs differ)."""
+    rng = np.random.default_rng(seed)
+    out, prev = [], -1
+    while len(out) < n:
+        k = int(rng.integers(0, len(values)))
+        if k == prev:
+            k = (k + 1) % len(values)
+        prev = k
+        out += [values[k]] * int(rng.integers(1, max_run + 1))
+    return out[:n]
+
+
+def mostly(n, frequent, others, every, seed):
+    """`frequent` everywhere except about one row in `every`, which draws from `others`."""
+    rng = np.random.default_rng(seed)
+    hit = rng.integers(0, every, n) == 0
+    pick = rng.integers(0, len(others), n)
+    return [others[int(pick[i])] if hit[i] else frequent for i in range(n)]
+
+
 def cases(n):
     rng = np.random.default_rng(11)
     binary = [bytes(rng.integers(0, 256, int(rng.integers(0, 40)), dtype=np.uint8)) for _ in range(n)]  # includes 0xFF bytes
@@ -33,5 +54,12 @@ def cases(n):
         "blob12": ("BLOB", "FSST12", binary),                                                     # mostly literal codes (< 256)
         "instruct12": ("VARCHAR", "FSST12_DICT", [[b"DELIVER IN PERSON", b"COLLECT COD", b"NONE", b"TAKE BACK RETURN"][(i * 5) % 4] for i in range(n)]),
         "len_edges": ("VARCHAR", "FSST", [b"x" * (i % 30) for i in range(n)]),                   # lengths around the 12-byte inline limit
+        # the three VALUE encodings (rle_map_kernel.hpp:26-61, cross_rle_kernel.hpp:55-97, frequency_kernel.hpp:23-69)
+        "flag_runs": ("VARCHAR", "RLE_STR", runs_of(n, [b"A", b"N", b"R", b"RETURNED TO SENDER", b""], 200, 21)),
+        "rle_unique": ("VARCHAR", "RLE_STR", [b"Value %d" % i for i in range(n)]),               # 1024 runs per vector
+        "status_cross": ("VARCHAR", "CROSS_RLE_STR", runs_of(n, [b"F", b"O", b"P", b"PENDING REVIEW BY CLERK"], 5000, 22)),
+        "cross_short": ("BLOB", "CROSS_RLE_STR", runs_of(n, [b"\x00", b"\xff\xfe", b"abcdefghijklm", b""], 3, 23)),
+        "freq_none": ("VARCHAR", "FREQUENCY_STR", mostly(n, b"NONE", [b"DELIVER IN PERSON", b"COLLECT COD", b"", b"x"], 30, 24)),
+        "freq_const": ("VARCHAR", "FREQUENCY_STR", [b"TAKE BACK RETURN"] * n),                    # no exceptions at all
         "long": ("VARCHAR", "STR_UNCOMPRESSED", [b"%05d:" % i + b"abcdefghij" * (1 + i % 50) for i in range(n)]),
     }

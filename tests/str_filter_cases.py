@@ -8,7 +8,8 @@ import numpy as np
 from str_cases import cases
 
 PY_OP = dict(EQ=operator.eq, NE=operator.ne, LT=operator.lt, LE=operator.le, GT=operator.gt, GE=operator.ge)
-COLUMNS = ["shipmode", "instruct", "comment", "blob", "blob_plain", "len_edges", "long", "constant", "empty", "comment12", "instruct12"]
+COLUMNS = ["shipmode", "instruct", "comment", "blob", "blob_plain", "len_edges", "long", "constant", "empty", "comment12", "instruct12",
+           "flag_runs", "status_cross", "freq_none"]
 
 
 def table(n):
@@ -52,6 +53,10 @@ def filter_sets(data):
         "empty_gt": [("empty", "GT", b"")],
         "fsst12_ge": [("comment12", "GE", b"quickly")],
         "fsst12_dict_eq": [("instruct12", "EQ", b"NONE")],
+        "rle_str_eq_long": [("flag_runs", "EQ", b"RETURNED TO SENDER")],
+        "rle_str_lt": [("flag_runs", "LT", b"N")],
+        "cross_rle_str_ge": [("status_cross", "GE", b"P")],
+        "frequency_str_ne": [("freq_none", "NE", b"NONE")],
         "mixed": [("v", "GE", 100), ("shipmode", "EQ", b"RAIL"), ("v", "LT", 900), ("comment", "GE", b"c")],
         "two_strings": [("shipmode", "NE", b"FOB"), ("instruct", "NE", b"NONE")],
     }
