@@ -561,8 +561,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			for (uint32_t s = 0; s < n_slots && to_issue; ++s) {
 				const int k = __ffs(to_issue) - 1;
 				to_issue &= to_issue - 1;
-				const uint4 q0 = *reinterpret_cast<const uint4*>(descs + (size_t)k * kDescBytes);
-				const uint32_t bytes = *reinterpret_cast<const uint32_t*>(descs + (size_t)k * kDescBytes + 16);
+				const uint4 q0 = *reinterpret_cast<const uint4*>(descs + (size_t)k * kDescBytes + 16u * desc_quad(k, 0));
+				const uint32_t bytes = *reinterpret_cast<const uint32_t*>(descs + (size_t)k * kDescBytes + 16u * desc_quad(k, 1));
 				if (bytes) {
 					mbar_expect_tx(bars + slot_i, bytes);
 					tma_load_1d(slots + (size_t)slot_i * L.slot_bytes, (const void*)(((unsigned long long)q0.y << 32) | q0.x), bytes,
@@ -623,8 +623,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 				const int kn = __ffs(to_issue) - 1;
 				to_issue &= to_issue - 1;
 				if (lane == 0) {
-					const uint4 q0 = *reinterpret_cast<const uint4*>(descs + (size_t)kn * kDescBytes);
-					const uint32_t bytes = *reinterpret_cast<const uint32_t*>(descs + (size_t)kn * kDescBytes + 16);
+					const uint4 q0 = *reinterpret_cast<const uint4*>(descs + (size_t)kn * kDescBytes + 16u * desc_quad(kn, 0));
+					const uint32_t bytes = *reinterpret_cast<const uint32_t*>(descs + (size_t)kn * kDescBytes + 16u * desc_quad(kn, 1));
 					if (bytes) {
 						mbar_expect_tx(bars + slot, bytes);
 						tma_load_1d(slots + (size_t)slot * L.slot_bytes, (const void*)(((unsigned long long)q0.y << 32) | q0.x), bytes,

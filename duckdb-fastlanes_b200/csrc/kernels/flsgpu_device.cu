@@ -1976,6 +1976,163 @@ int flsgpu_aggregate_column_masked(flsgpu_table* t, uint32_t col, uint32_t rg_be
 	return decode_column_impl(t, d, col, rg_begin, n_rg, os, nullptr, static_cast<cudaStream_t>(cuda_stream), acc, &ms);
 }
 
+// SELECT SUM(c), COUNT(*), MIN(c), MAX(c) [... WHERE <filters>] from host memory to host memory: the row groups of the range
+// are worked through in slabs on two streams - H2D of the compressed chunks of the columns the query touches, (filter mask,)
+// fused decode + aggregate launches - so that the copy of slab k+1 overlaps the kernels of slab k; each stream folds into a
+// result set of its own, the two are added on the host.  Nothing decoded ever leaves the SMs; 64 bytes per column come back.
+int flsgpu_aggregate_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, const flsgpu_filter* filters, uint32_t n_filters,
+                             uint32_t rg_begin, uint32_t n_rg, flsgpu_agg_result* results_host) {
+	if (!t || !col_ids || n_cols == 0 || !results_host) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_aggregate_to_host: null argument");
+	}
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		const int rc = check_range(t, col_ids[i], rg_begin, n_rg, "flsgpu_aggregate_to_host");
+		if (rc) {
+			return rc;
+		}
+		if (t->columns[col_ids[i]].phys_bits == 128) {
+			return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_aggregate_to_host: aggregates over string columns are not supported");
+		}
+	}
+	int rc = check_filters(t, filters, n_filters, "flsgpu_aggregate_to_host");
+	if (rc) {
+		return rc;
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	const fls_file_header& h = t->header;
+	std::vector<uint32_t> need_cols(col_ids, col_ids + n_cols);
+	for (uint32_t i = 0; i < n_filters; ++i) {
+		if (std::find(need_cols.begin(), need_cols.end(), filters[i].col) == need_cols.end()) {
+			need_cols.push_back(filters[i].col);
+		}
+	}
+	std::vector<uint8_t> keep(n_rg, 1);
+	if (n_filters) {
+		rc = flsgpu_rowgroup_prune(t, filters, n_filters, rg_begin, n_rg, keep.data());
+		if (rc) {
+			return rc;
+		}
+	}
+	const uint32_t slab_rg = std::max(1u, std::min(n_rg, env_u32("FLSGPU_AGG_SLAB_RG", 64)));
+	const uint64_t res_bytes = ((uint64_t)n_cols * sizeof(flsgpu_agg_result) + 255u) & ~255ull;
+	const uint64_t mask_bytes = n_filters ? (uint64_t)slab_rg * h.vec_per_rowgroup * 128u : 0u;
+	const uint64_t keep_bytes = n_filters ? ((uint64_t)slab_rg + 255u) & ~255ull : 0u;
+	const uint64_t need_bytes = res_bytes + mask_bytes + keep_bytes;
+	FlsScanScratch* sc = nullptr;
+	{
+		std::lock_guard<std::mutex> g(d->mu);
+		if (!d->scratch_free.empty()) {
+			sc = d->scratch_free.back();
+			d->scratch_free.pop_back();
+		} else {
+			sc = new FlsScanScratch();
+			d->scratch_all.push_back(sc);
+		}
+	}
+	struct Return { // hand the scratch back on every exit path
+		FlsDeviceState* d;
+		FlsScanScratch* sc;
+		~Return() {
+			std::lock_guard<std::mutex> g(d->mu);
+			d->scratch_free.push_back(sc);
+		}
+	} ret {d, sc};
+	if (sc->out_bytes < need_bytes) {
+		sc->out_bytes = 0;
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaFree(sc->out[i]));
+			sc->out[i] = nullptr;
+		}
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaMalloc(&sc->out[i], need_bytes));
+		}
+		sc->out_bytes = need_bytes;
+	}
+	for (int i = 0; i < 2; ++i) {
+		if (!sc->streams[i]) {
+			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
+		}
+	}
+	int status = FLSGPU_OK;
+	for (int i = 0; i < 2 && status == FLSGPU_OK; ++i) {
+		for (uint32_t c = 0; c < n_cols && status == FLSGPU_OK; ++c) {
+			status = flsgpu_agg_reset(static_cast<flsgpu_agg_result*>(sc->out[i]) + c, sc->streams[i]);
+		}
+	}
+	uint32_t slab = 0;
+	for (uint32_t r0 = 0; r0 < n_rg && status == FLSGPU_OK; r0 += slab_rg, ++slab) {
+		const uint32_t n = std::min(slab_rg, n_rg - r0);
+		const int b = (int)(slab & 1u);
+		cudaStream_t st = sc->streams[b];
+		uint8_t* base = static_cast<uint8_t*>(sc->out[b]);
+		flsgpu_agg_result* res = reinterpret_cast<flsgpu_agg_result*>(base);
+		{
+			std::lock_guard<std::mutex> g(d->mu);
+			status = stage_range(t, d, rg_begin + r0, n, need_cols.data(), (uint32_t)need_cols.size(), st);
+		}
+		if (status != FLSGPU_OK) {
+			break;
+		}
+		if (n_filters) {
+			uint32_t* mask_dev = reinterpret_cast<uint32_t*>(base + res_bytes);
+			uint8_t* keep_dev = base + res_bytes + mask_bytes;
+			if (cudaMemcpyAsync(keep_dev, keep.data() + r0, n, cudaMemcpyHostToDevice, st) != cudaSuccess) { // pageable: staged before the call returns
+				status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(row-group keep flags)");
+				break;
+			}
+			status = flsgpu_filter_mask(t, filters, n_filters, rg_begin + r0, n, keep_dev, mask_dev, mask_bytes, st);
+			for (uint32_t c = 0; c < n_cols && status == FLSGPU_OK; ++c) {
+				status = flsgpu_aggregate_column_masked(t, col_ids[c], rg_begin + r0, n, mask_dev, keep_dev, res + c, st);
+			}
+		} else {
+			for (uint32_t c = 0; c < n_cols && status == FLSGPU_OK; ++c) {
+				status = flsgpu_aggregate_column(t, col_ids[c], rg_begin + r0, n, res + c, st);
+			}
+		}
+	}
+	std::vector<flsgpu_agg_result> part(2u * n_cols);
+	for (int i = 0; i < 2 && status == FLSGPU_OK; ++i) {
+		if (cudaMemcpyAsync(part.data() + (size_t)i * n_cols, sc->out[i], (size_t)n_cols * sizeof(flsgpu_agg_result), cudaMemcpyDeviceToHost,
+		                    sc->streams[i]) != cudaSuccess) {
+			status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H results)");
+		}
+	}
+	// always drain both streams before the scratch goes back to the pool
+	for (int i = 0; i < 2; ++i) {
+		const cudaError_t e = cudaStreamSynchronize(sc->streams[i]);
+		if (e != cudaSuccess && status == FLSGPU_OK) {
+			status = cuda_fail(e, "cudaStreamSynchronize");
+		}
+	}
+	if (status != FLSGPU_OK) {
+		return status;
+	}
+	g_d2h_bytes.fetch_add(2ull * n_cols * sizeof(flsgpu_agg_result), std::memory_order_relaxed);
+	for (uint32_t c = 0; c < n_cols; ++c) {
+		const flsgpu_agg_result &a = part[c], &b = part[n_cols + c];
+		flsgpu_agg_result& o = results_host[c];
+		o = flsgpu_agg_result {};
+		o.sum_lo = a.sum_lo + b.sum_lo;
+		o.sum_hi = a.sum_hi + b.sum_hi + (o.sum_lo < a.sum_lo ? 1u : 0u);
+		o.count = a.count + b.count;
+		o.fsum = a.fsum + b.fsum;
+		// order keys of the zone-map extremes (value ^ sign bit; ~0 / 0 when a stream saw none)
+		const uint64_t kmin = std::min(a.reserved[0], b.reserved[0]), kmax = std::max(a.reserved[1], b.reserved[1]);
+		o.reserved[0] = kmin;
+		o.reserved[1] = kmax;
+		if (!n_filters && o.count && kmin <= kmax && !t->columns[col_ids[c]].is_float) {
+			const uint64_t flip = t->columns[col_ids[c]].is_signed ? 0x8000000000000000ull : 0ull;
+			o.min_val = (int64_t)(kmin ^ flip);
+			o.max_val = (int64_t)(kmax ^ flip);
+		}
+	}
+	return FLSGPU_OK;
+}
+
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream) {
 	if (!result_dev) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_agg_reset: null argument");

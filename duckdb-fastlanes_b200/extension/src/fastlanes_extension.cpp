@@ -21,6 +21,10 @@ static void RegisterSettings(ExtensionLoader &loader) {
 	                          "Hand vectors the file marks CONSTANT or arithmetic SEQUENCE to DuckDB as CONSTANT / SEQUENCE vectors "
 	                          "instead of decoding and copying them",
 	                          LogicalType::BOOLEAN, Value::BOOLEAN(true));
+	config.AddExtensionOption("fastlanes_table_cache_mb",
+	                          "Opened .fls files stay open - container validated, image page-locked, compressed chunks resident in HBM - "
+	                          "for the next query until the cached files exceed this many MiB (0: no caching)",
+	                          LogicalType::UBIGINT, Value::UBIGINT(65536));
 	config.AddExtensionOption("fastlanes_gpu_devices",
 	                          "Comma separated CUDA device ordinals read_fls shards row groups over (empty: device 0)",
 	                          LogicalType::VARCHAR, Value(""));
@@ -30,6 +34,7 @@ static void LoadFastLanes(ExtensionLoader &loader) {
 	RegisterSettings(loader);
 	FastLanesScanFunction::Register(loader);
 	FastLanesCopyFunction::Register(loader);
+	FastLanesAggregatePushdown::Register(loader);
 }
 
 void FastlanesExtension::Load(ExtensionLoader &loader) {

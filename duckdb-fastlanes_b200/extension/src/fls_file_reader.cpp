@@ -13,6 +13,7 @@
 #include "duckdb/storage/table/row_group.hpp"
 
 #include <cstring>
+#include <sys/stat.h>
 
 namespace duckdb {
 
@@ -104,10 +105,7 @@ FastLanesReader::FastLanesReader(ClientContext &context, OpenFileInfo file_p, co
 }
 
 FastLanesReader::~FastLanesReader() {
-	for (idx_t i = 1; i < device_tables.size(); i++) {
-		flsgpu_table_close(device_tables[i]);
-	}
-	flsgpu_table_close(table);
+	// the handles belong to cached_table: closed when the last reader and the cache let go of the entry
 }
 
 // SET fastlanes_gpu_devices = '0,1,2,3': the process-wide device list of the engine (flsgpu_init); applied when it changes
@@ -136,23 +134,93 @@ static void ApplyDeviceList(const string &list) {
 	applied = list;
 }
 
-// FastLanesReader::Initialize (fls_reader.cpp:106-143): footer -> schema, per-row-group tuple offsets, totals
-void FastLanesReader::Initialize(ClientContext &context) {
-	FlsCheck(flsgpu_table_open(file.path.c_str(), &table), "read_fls");
+// ---- FlsTableCache ------------------------------------------------------------------------------------------------------
+FlsCachedTable::~FlsCachedTable() {
+	for (idx_t i = handles.size(); i-- > 1;) {
+		flsgpu_table_close(handles[i]);
+	}
+	if (!handles.empty()) {
+		flsgpu_table_close(handles[0]);
+	}
+}
+
+shared_ptr<FlsCachedTable> FlsTableCache::Open(const string &path, const string &key) {
+	auto entry = make_shared_ptr<FlsCachedTable>();
+	entry->key = key;
+	flsgpu_table *table = nullptr;
+	FlsCheck(flsgpu_table_open(path.c_str(), &table), "read_fls");
+	entry->handles.push_back(table);
+	flsgpu_table_info info {};
 	FlsCheck(flsgpu_table_info_get(table, &info), "flsgpu_table_info_get");
-	device_tables.assign(1, table);
-	Value devices;
-	if (context.TryGetCurrentSetting("fastlanes_gpu_devices", devices) && !devices.IsNull() && !devices.ToString().empty()) {
-		ApplyDeviceList(devices.ToString()); // fails here, at bind time, when there is no such device
-		int n_devices = 1;
-		FlsCheck(flsgpu_n_devices(&n_devices), "flsgpu_n_devices");
-		for (int g = 1; g < n_devices; g++) {
-			flsgpu_table *shared = nullptr;
-			FlsCheck(flsgpu_table_share(table, &shared), "flsgpu_table_share");
-			device_tables.push_back(shared);
-			FlsCheck(flsgpu_table_bind_device(shared, g), "flsgpu_table_bind_device");
+	entry->file_bytes = info.file_bytes;
+	int n_devices = 1;
+	FlsCheck(flsgpu_n_devices(&n_devices), "flsgpu_n_devices");
+	for (int g = 1; g < n_devices; g++) {
+		flsgpu_table *shared = nullptr;
+		FlsCheck(flsgpu_table_share(table, &shared), "flsgpu_table_share");
+		entry->handles.push_back(shared);
+		FlsCheck(flsgpu_table_bind_device(shared, g), "flsgpu_table_bind_device");
+	}
+	return entry;
+}
+
+shared_ptr<FlsCachedTable> FlsTableCache::Acquire(ClientContext &context, const string &path) {
+	static std::mutex lock;
+	// most recently used first; never destroyed: at process exit the CUDA runtime may be gone before static destructors run
+	static auto &entries = *new vector<shared_ptr<FlsCachedTable>>();
+	string device_list;
+	Value setting;
+	if (context.TryGetCurrentSetting("fastlanes_gpu_devices", setting) && !setting.IsNull()) {
+		device_list = setting.ToString();
+	}
+	ApplyDeviceList(device_list); // fails here, at bind time, when there is no such device
+	idx_t capacity_mb = 65536;
+	if (context.TryGetCurrentSetting("fastlanes_table_cache_mb", setting) && !setting.IsNull()) {
+		capacity_mb = setting.GetValue<uint64_t>();
+	}
+	struct stat st {};
+	if (capacity_mb == 0 || stat(path.c_str(), &st) != 0) {
+		return Open(path, string()); // not cached (or not a local file: flsgpu_table_open reports what is wrong with it)
+	}
+	const string key = path + "|" + to_string((uint64_t)st.st_size) + "|" + to_string((uint64_t)st.st_mtim.tv_sec) + "." +
+	                   to_string((uint64_t)st.st_mtim.tv_nsec) + "|" + device_list;
+	std::lock_guard<std::mutex> guard(lock);
+	for (idx_t i = 0; i < entries.size(); i++) {
+		if (entries[i]->key == key) {
+			auto hit = entries[i];
+			entries.erase(entries.begin() + NumericCast<int64_t>(i));
+			entries.insert(entries.begin(), hit);
+			return hit;
 		}
 	}
+	// an older version of the same file is of no use to anybody new
+	const string prefix = path + "|";
+	for (idx_t i = entries.size(); i-- > 0;) {
+		if (StringUtil::StartsWith(entries[i]->key, prefix)) {
+			entries.erase(entries.begin() + NumericCast<int64_t>(i));
+		}
+	}
+	auto entry = Open(path, key);
+	entries.insert(entries.begin(), entry);
+	idx_t total = 0;
+	for (auto &e : entries) {
+		total += e->file_bytes;
+	}
+	for (idx_t i = entries.size(); i-- > 1 && total > capacity_mb * 1024 * 1024;) {
+		if (entries[i].use_count() == 1) { // nobody scans it
+			total -= entries[i]->file_bytes;
+			entries.erase(entries.begin() + NumericCast<int64_t>(i));
+		}
+	}
+	return entry;
+}
+
+// FastLanesReader::Initialize (fls_reader.cpp:106-143): footer -> schema, per-row-group tuple offsets, totals
+void FastLanesReader::Initialize(ClientContext &context) {
+	cached_table = FlsTableCache::Acquire(context, file.path);
+	device_tables = cached_table->handles;
+	table = device_tables[0];
+	FlsCheck(flsgpu_table_info_get(table, &info), "flsgpu_table_info_get");
 	columns.clear();
 	column_descs.resize(info.n_columns);
 	column_out_types.resize(info.n_columns);

@@ -20,6 +20,10 @@ public:
 struct FastLanesScanFunction {
 	static void Register(ExtensionLoader &loader);
 };
+//! Ungrouped SUM / COUNT / MIN / MAX over read_fls answered by fused decode + aggregate kernels (no reference counterpart)
+struct FastLanesAggregatePushdown {
+	static void Register(ExtensionLoader &loader);
+};
 //! COPY ... (FORMAT fls) (reference src/write_fls.cpp:8-29)
 struct FastLanesCopyFunction {
 	static void Register(ExtensionLoader &loader);

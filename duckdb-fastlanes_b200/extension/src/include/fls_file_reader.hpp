@@ -47,6 +47,29 @@ struct FastLanesReadBindData : public TableFunctionData {
 	unique_ptr<FastLanesFileReaderOptions> options;
 };
 
+//! An opened .fls file and its handles in libflsgpu (one per device of the fastlanes_gpu_devices list over the same host
+//! image).  Entries are shared between the readers of every query of the process through FlsTableCache: what a query pays
+//! for once - reading and validating the container, page-locking its image, the HBM arena and the H2D copies of the
+//! compressed chunks it touched - the next query over the same file finds done.  180 GB of HBM hold the compressed image of
+//! every table of the BASELINE configs many times over, so compressed chunks simply stay resident;
+//! the reference re-opens the file and re-reads the row groups from the page cache for every scan (table_metadata.cpp:13-35).
+struct FlsCachedTable {
+	~FlsCachedTable();
+	string key;
+	idx_t file_bytes = 0;
+	vector<flsgpu_table *> handles; // [0] owns the image, the others share it
+};
+
+//! Process-wide cache of opened tables, keyed by (path, size, mtime, device list); least recently used entries nobody scans
+//! are closed once the cached files exceed the setting fastlanes_table_cache_mb (0: every reader opens its own).
+class FlsTableCache {
+public:
+	static shared_ptr<FlsCachedTable> Acquire(ClientContext &context, const string &path);
+
+private:
+	static shared_ptr<FlsCachedTable> Open(const string &path, const string &key);
+};
+
 //! Pinned host memory the device copies decoded columns into.  It is a VectorBuffer so that every DuckDB vector that points
 //! into it holds a reference: the memory outlives the reader's own use of it for as long as a chunk is alive downstream.
 class FlsPinnedBuffer : public VectorBuffer {
@@ -168,6 +191,12 @@ public:
 	flsgpu_table *Table() const {
 		return table;
 	}
+	const shared_ptr<FlsCachedTable> &CachedTable() const {
+		return cached_table;
+	}
+	const vector<fls_column_desc> &GetColumnDescs() const {
+		return column_descs;
+	}
 
 private:
 	struct ScanBatch {
@@ -193,6 +222,8 @@ private:
 	FastLanesReaderProjectionPlan BuildReaderProjectionPlan();
 	const vector<idx_t> &GetRowGroupsToScan(ClientContext &context, FastLanesReadLocalState &local_state);
 
+	//! Keeps the handles below alive (FlsTableCache)
+	shared_ptr<FlsCachedTable> cached_table;
 	flsgpu_table *table = nullptr;
 	//! One handle per device of the fastlanes_gpu_devices list over the same host image (device_tables[0] == table): DuckDB
 	//! is ONE process with N worker threads (reference fls_multi_file_info.cpp:99-110), row groups are independent, so each

@@ -156,6 +156,7 @@ ABI_SYMBOLS = [
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
     "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms", "flsgpu_transfer_bytes",
     "flsgpu_n_devices", "flsgpu_table_share", "flsgpu_table_bind_device", "flsgpu_filter_mask_string_dict_static",
+    "flsgpu_aggregate_to_host",
 ]
 
 
@@ -399,6 +400,15 @@ class Table:
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
         _check(lib.flsgpu_aggregate_column_masked(self._h, col, rg_begin, n_rg, _vp(mask_ptr), _vp(keep_ptr), _vp(result_ptr), _vp(stream)),
                "aggregate_column_masked")
+
+    def aggregate_to_host(self, cols, filters=(), rg_begin=0, n_rg=None):
+        """Fused SUM / COUNT / MIN / MAX of the listed numeric columns [WHERE filters], host to host -> list of AggResult."""
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        ids = (C.c_uint32 * len(cols))(*cols)
+        out = (AggResult * len(cols))()
+        _check(lib.flsgpu_aggregate_to_host(self._h, ids, len(cols), make_filters(filters) if filters else None, len(filters), rg_begin, n_rg, out),
+               "aggregate_to_host")
+        return list(out)
 
     def scan_filtered_to_host(self, scan_columns, filters, mask_host_ptr, mask_bytes, rg_begin=0, n_rg=None):
         n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg

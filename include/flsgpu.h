@@ -242,6 +242,15 @@ int flsgpu_filter_mask(flsgpu_table* t, const flsgpu_filter* filters, uint32_t n
  * *result_dev like flsgpu_aggregate_column; min_val / max_val are not produced. */
 int flsgpu_aggregate_column_masked(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, const uint32_t* mask_dev,
                                    const uint8_t* rg_keep_dev, flsgpu_agg_result* result_dev, void* cuda_stream);
+/* The host-to-host form of the fused aggregates - what a rewrite of SELECT SUM(c), COUNT(*), MIN(c), MAX(c) FROM read_fls(...)
+ * [WHERE <constant comparisons>] runs (the reference decodes every value into DuckDB vectors and lets DuckDB's
+ * aggregate operators consume them: fls_reader.cpp:436-472 -> ungrouped aggregate).  Stages the compressed chunks of the
+ * columns the query touches (slabs of row groups on two streams, H2D overlapping the kernels), evaluates the filters into a
+ * device mask, folds every listed numeric column and writes one flsgpu_agg_result per column to results_host[i].  With
+ * filters only sum_lo / sum_hi / count / fsum are produced (min_val / max_val stay 0); without, MIN / MAX come from the
+ * chunks' zone maps (integer columns whose chunks carry statistics).  Synchronous. */
+int flsgpu_aggregate_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t n_cols, const flsgpu_filter* filters, uint32_t n_filters,
+                             uint32_t rg_begin, uint32_t n_rg, flsgpu_agg_result* results_host);
 /* Allocation-free variant of flsgpu_filter_mask for ONE constant comparison on a VARCHAR / BLOB column whose chunks in the
  * range are all dictionary encoded (DICT_STR / FSST_DICT / FSST12_DICT).  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving

@@ -96,3 +96,49 @@ def test_subrange_and_q6_value():
     assert mask.cpu().numpy().view(np.uint32).tobytes() == o.filter_mask(filt, rg0, nrg, 2).tobytes()
     # string columns are not filtered on the device
     t.close()
+
+
+@pytest.mark.parametrize("n,vpr,slab", [(5000, 2, None), (300000, 4, "3"), (70000, 64, None)])
+def test_aggregate_to_host_matches_numpy(n, vpr, slab, monkeypatch):
+    """flsgpu_aggregate_to_host: SELECT SUM / COUNT / MIN / MAX [WHERE ...] from host memory to host memory (slabs of row
+    groups on two streams, nothing staged beforehand) == plain numpy over the input."""
+    if slab:
+        monkeypatch.setenv("FLSGPU_AGG_SLAB_RG", slab)  # many slabs: both streams' result sets get used
+    cols = table(n)
+    names = [c[0] for c in cols]
+    img = flsgpu.write_table([(c[0], c[1], c[2]) + tuple(c[4:6]) for c in cols], [c[3] for c in cols], vec_per_rowgroup=vpr)
+    by = {c[0]: c[3] for c in cols}
+    agg_names = ["price", "discount", "small", "u16", "runs", "dic", "shipdate", "dbl"]
+    ids = [names.index(c) for c in agg_names]
+
+    def check(res, rows, with_minmax):
+        for name, r in zip(agg_names, res):
+            v = by[name][rows]
+            assert r.count == len(v), name
+            if name == "dbl":
+                es = float(np.sum(v))
+                assert (np.isnan(r.fsum) and np.isnan(es)) or abs(r.fsum - es) <= 1e-9 * max(1.0, abs(es)), name
+                continue
+            s = (r.sum_hi << 64) | r.sum_lo
+            s -= (1 << 128) if s >= (1 << 127) else 0
+            assert s == int(v.astype(object).sum()) if len(v) else s == 0, name
+            if with_minmax and len(v):
+                mn, mx = (r.min_val, r.max_val) if v.dtype.kind == "i" else (r.min_val & (2 ** 64 - 1), r.max_val & (2 ** 64 - 1))
+                assert (mn, mx) == (int(v.min()), int(v.max())), name
+
+    t = flsgpu.Table(img)  # never staged by hand: the call stages what it needs
+    everything = np.ones(n, dtype=bool)
+    check(t.aggregate_to_host(ids), everything, True)
+    check(t.aggregate_to_host(ids), everything, True)  # resident now: same answer
+    for fname, fs in filter_sets().items():
+        filt = [(names.index(c), flsgpu.CMP[op], bits(k, k.dtype)) for c, op, k in fs]
+        check(t.aggregate_to_host(ids, filt), numpy_mask(cols, fs), False)
+    # a sub-range of row groups
+    if t.n_rowgroups > 3:
+        rows = np.zeros(n, dtype=bool)
+        stride = t.vec_per_rowgroup * 1024
+        rows[stride:min(n, (t.n_rowgroups - 1) * stride)] = True
+        check(t.aggregate_to_host(ids, rg_begin=1, n_rg=t.n_rowgroups - 2), rows, True)
+    with pytest.raises(flsgpu.FlsError):
+        t.aggregate_to_host([99])
+    t.close()

@@ -81,7 +81,32 @@ def main():
         done += n
     img = w.finish()
     build_s = time.perf_counter() - t0
+    doc = measure(img, want, n_rows, args.iters, args.cpu_seconds)
+    doc = dict({"workload": "TPC-H lineitem shape, SF%g (%d rows, %d row groups), writer's own encoding selection" % (args.sf, n_rows, doc["row_groups"]),
+                "raw_MB": round(raw_bytes / 1e6, 1), "build_s": round(build_s, 1)}, **doc)
+    print(json.dumps(doc, indent=1))
+    if args.out:
+        with open(args.out, "w") as f:
+            json.dump(doc, f, indent=1)
+    w.close()
+
+
+def measure(img, want, n_rows, iters, cpu_seconds):
+    """The resident measurements over a lineitem container image (numpy uint8): per-column scans, the whole scan as one
+    region, fused SUM/COUNT per numeric column, Q1 / Q6 filter scans - every result checked against `want` - and the
+    oracle's scan on the host cores.  Used with the numpy generator (main) and with dbgen's table (tools/lineitem_dbgen.py)."""
+    import torch
+    import flsgpu
+    import oracle_lib
+
+    class _A:
+        pass
+    args = _A()
+    args.iters, args.cpu_seconds = iters, cpu_seconds
+    flsgpu.init((0,))
+    threads = os.cpu_count() or 1
     t = flsgpu.Table(img)
+    names = [t.column(c).name.decode() for c in range(t.n_columns)]
     stream = torch.cuda.current_stream().cuda_stream
     t.stage(stream=stream)
     torch.cuda.synchronize()
@@ -191,8 +216,7 @@ def main():
         if time.perf_counter() - t0 >= args.cpu_seconds:
             break
     cpu_s = (time.perf_counter() - t0) / passes
-    doc = {"workload": "TPC-H lineitem shape, SF%g (%d rows, %d row groups), writer's own encoding selection" % (args.sf, n_rows, n_rg),
-           "raw_MB": round(raw_bytes / 1e6, 1), "container_MB": round(len(img) / 1e6, 1), "build_s": round(build_s, 1),
+    doc = {"rows": n_rows, "row_groups": n_rg, "container_MB": round(len(img) / 1e6, 1),
            "hbm_peak_GBps": peak, "per_column": per_column,
            "full_scan": {"ms": round(scan_ms, 4), "decoded_GBps": round(scan_bytes / scan_ms / 1e6, 1),
                          "rows_per_s": round(n_rows / scan_ms * 1e3, 1), "note": "sum of the per-column times above"},
@@ -202,12 +226,8 @@ def main():
            "sum_count_scans": sums, "queries": queries,
            "cpu_oracle_scan": {"threads": threads, "s_per_pass": round(cpu_s, 3), "decoded_GBps": round(scan_bytes / cpu_s / 1e9, 2),
                                "passes": passes}}
-    print(json.dumps(doc, indent=1))
-    if args.out:
-        with open(args.out, "w") as f:
-            json.dump(doc, f, indent=1)
     t.close()
-    w.close()
+    return doc
 
 
 if __name__ == "__main__":
