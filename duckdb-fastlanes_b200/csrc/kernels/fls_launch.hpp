@@ -30,6 +30,11 @@ cudaError_t fls_str_launch_keys(FlsStrLaunch L, uint32_t max_keys_per_chunk, cud
 cudaError_t fls_str_launch_filter(FlsStrFilterLaunch L, cudaStream_t stream);
 // The same comparison over the keys of dictionary chunks -> one flag byte per key (then fls_str_launch_rows in filter mode).
 cudaError_t fls_str_launch_key_flags(FlsStrFilterLaunch L, cudaStream_t stream);
+// Selected-rows-only scans (flsgpu_kernels_select.cu): where every vector's selected rows go (exclusive prefix sums of the mask
+// popcounts over n_vec vectors, total at [n_vec]), then the compaction of one decoded column (in == nullptr: row indexes).
+cudaError_t fls_select_launch_plan(const uint32_t* mask, uint32_t n_vec, uint32_t* vec_offsets, cudaStream_t stream);
+cudaError_t fls_select_launch_compact(const void* in, uint32_t elem_bytes, const uint32_t* mask, const uint32_t* vec_offsets, void* out,
+                                      uint32_t n_vec, uint32_t iota_base, cudaStream_t stream);
 #endif
 
 constexpr int kFlsWarpsPerCta = 8;

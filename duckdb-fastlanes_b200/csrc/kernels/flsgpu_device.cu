@@ -135,6 +135,7 @@ struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of
 	// memory would first synchronise the stream, i.e. wait for the previous column's D2H copy)
 	uint32_t* map_host[2] = {nullptr, nullptr};
 	uint64_t map_bytes = 0;
+	uint32_t* count_host = nullptr; // selected-rows scans: the slab's row count comes back here (pinned, one word per stream)
 };
 
 struct FlsDeviceState {
@@ -181,6 +182,7 @@ void fls_device_release(flsgpu_table* t) {
 			cudaFree(sc->out[i]);
 			cudaFreeHost(sc->map_host[i]);
 		}
+		cudaFreeHost(sc->count_host);
 		delete sc;
 	}
 	cudaFree(d->d_image);
@@ -1240,6 +1242,231 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 	const cudaError_t e0 = cudaStreamSynchronize(sc->streams[0]), e1 = cudaStreamSynchronize(sc->streams[1]);
 	if (status == FLSGPU_OK && (e0 != cudaSuccess || e1 != cudaSuccess)) {
 		status = cuda_fail(e0 != cudaSuccess ? e0 : e1, "cudaStreamSynchronize");
+	}
+	return status;
+}
+
+// The filtered scan with the selection applied ON THE DEVICE: per slab the filter mask is turned into per-vector output
+// offsets (fls_select_plan_kernel), the slab's row count comes back to the host (4 bytes, one stream synchronisation), then
+// every projected column is decoded in HBM, packed (fls_select_compact_kernel) and only the selected rows are copied out,
+// back to back over the whole range.  A Q6-shaped scan (2 % of the rows pass) moves 2 % of the bytes of the masked form.
+int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, const flsgpu_filter* filters,
+                                 uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg, uint32_t* row_index_host,
+                                 uint64_t row_index_capacity_bytes, uint64_t* n_selected_out) {
+	const char* who = "flsgpu_scan_selected_to_host";
+	if (!t || (!cols && n_cols) || !filters || n_filters == 0 || !n_selected_out) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_selected_to_host: null argument or no filters");
+	}
+	int rc = check_range(t, 0, rg_begin, n_rg, who);
+	if (!rc) {
+		rc = check_filters(t, filters, n_filters, who);
+	}
+	if (rc) {
+		return rc;
+	}
+	const fls_file_header& h = t->header;
+	const uint64_t rg_rows = (uint64_t)h.vec_per_rowgroup * FLS_VEC_SZ;
+	if (rg_rows * n_rg > 0xffffffffull) {
+		return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_scan_selected_to_host: more than 2^32 rows in one call");
+	}
+	if (row_index_host && row_index_capacity_bytes < rg_rows * n_rg * 4u) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_selected_to_host: row index buffer too small");
+	}
+	struct ColPlan {
+		OutSpec os;
+		bool is_string = false;
+		uint32_t ob = 0; // bytes per row
+	};
+	std::vector<ColPlan> cp(n_cols);
+	uint32_t ob_max = row_index_host ? 4u : 0u;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		const flsgpu_scan_column& c = cols[i];
+		rc = check_range(t, c.col, rg_begin, n_rg, who);
+		if (rc) {
+			return rc;
+		}
+		ColPlan& p = cp[i];
+		p.is_string = t->columns[c.col].phys_bits == 128;
+		if (p.is_string) {
+			if (c.string_form != FLSGPU_STRING_FLAT) {
+				return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_scan_selected_to_host: string columns come back flat (string_t rows + heap)");
+			}
+			uint64_t heap_need = 0;
+			flsgpu_string_heap_bytes(t, c.col, rg_begin, n_rg, &heap_need);
+			if (!c.heap_host || c.heap_capacity_bytes < heap_need) {
+				return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_selected_to_host: string heap buffer null or too small");
+			}
+			p.ob = 16;
+		} else {
+			rc = resolve_out(t->columns[c.col], c.out_type, &p.os);
+			if (rc) {
+				return rc;
+			}
+			p.ob = p.os.ob;
+		}
+		if (!c.out_host || c.out_capacity_bytes < rg_rows * n_rg * p.ob) { // how many rows pass is not known beforehand
+			return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_selected_to_host: output buffer null or smaller than the unfiltered column");
+		}
+		ob_max = std::max(ob_max, p.ob);
+	}
+	FlsDeviceState* d = nullptr;
+	rc = device_state(t, &d);
+	if (rc) {
+		return rc;
+	}
+	auto heap_off = [&](uint32_t col, uint32_t r) {
+		const uint64_t i0 = (uint64_t)rg_begin * h.n_columns + col;
+		return d->heap_prefix[i0 + (uint64_t)r * h.n_columns] - d->heap_prefix[i0];
+	};
+	// slab: decode area A + packed area B (the widest column each) + the largest string heap of a slab + mask + offsets
+	const uint64_t slab_target = (uint64_t)env_u32("FLSGPU_SLAB_MB", 256) << 20;
+	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, slab_target / std::max<uint64_t>(1, rg_rows * std::max(1u, ob_max) * 2u)));
+	uint64_t heap_max = 0;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		if (cp[i].is_string) {
+			for (uint32_t r = 0; r < n_rg; r += slab_rg) {
+				const uint32_t e = std::min(n_rg, r + slab_rg);
+				heap_max = std::max(heap_max, heap_off(cols[i].col, e) - heap_off(cols[i].col, r));
+			}
+		}
+	}
+	const uint64_t area = (rg_rows * slab_rg * std::max(1u, ob_max) + 255u) & ~255ull;
+	const uint64_t dev_a = 0, dev_b = area, dev_heap = 2u * area, dev_mask = dev_heap + ((heap_max + 16u + 255u) & ~255ull);
+	const uint64_t rg_mask_bytes = (uint64_t)h.vec_per_rowgroup * 128u;
+	const uint64_t dev_offsets = dev_mask + rg_mask_bytes * slab_rg;
+	const uint64_t slab_bytes = dev_offsets + ((((uint64_t)slab_rg * h.vec_per_rowgroup + 1u) * 4u + 255u) & ~255ull);
+	FlsScanScratch* sc = nullptr;
+	{
+		std::lock_guard<std::mutex> g(d->mu);
+		if (!d->scratch_free.empty()) {
+			sc = d->scratch_free.back();
+			d->scratch_free.pop_back();
+		} else {
+			sc = new FlsScanScratch();
+			d->scratch_all.push_back(sc);
+		}
+	}
+	struct Return { // hand the scratch back on every exit path
+		FlsDeviceState* d;
+		FlsScanScratch* sc;
+		~Return() {
+			std::lock_guard<std::mutex> g(d->mu);
+			d->scratch_free.push_back(sc);
+		}
+	} ret {d, sc};
+	if (sc->out_bytes < slab_bytes) {
+		sc->out_bytes = 0;
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaFree(sc->out[i]));
+			sc->out[i] = nullptr;
+		}
+		for (int i = 0; i < 2; ++i) {
+			FLS_CUDA(cudaMalloc(&sc->out[i], slab_bytes));
+		}
+		sc->out_bytes = slab_bytes;
+	}
+	for (int i = 0; i < 2; ++i) {
+		if (!sc->streams[i]) {
+			FLS_CUDA(cudaStreamCreateWithFlags(&sc->streams[i], cudaStreamNonBlocking));
+		}
+	}
+	if (!sc->count_host) {
+		FLS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&sc->count_host), 256, cudaHostAllocDefault));
+	}
+	std::vector<uint32_t> col_ids;
+	for (uint32_t i = 0; i < n_cols; ++i) {
+		if (std::find(col_ids.begin(), col_ids.end(), cols[i].col) == col_ids.end()) {
+			col_ids.push_back(cols[i].col);
+		}
+	}
+	for (uint32_t i = 0; i < n_filters; ++i) {
+		if (std::find(col_ids.begin(), col_ids.end(), filters[i].col) == col_ids.end()) {
+			col_ids.push_back(filters[i].col);
+		}
+	}
+	int status = FLSGPU_OK;
+	auto d2h = [&](void* dst, const void* src, uint64_t bytes, cudaStream_t s) {
+		if (status == FLSGPU_OK && bytes && cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, s) != cudaSuccess) {
+			status = cuda_fail(cudaGetLastError(), "cudaMemcpyAsync(D2H)");
+		}
+		g_d2h_bytes.fetch_add(bytes, std::memory_order_relaxed);
+	};
+	uint64_t written = 0; // selected rows of the slabs so far
+	uint32_t slab = 0;
+	for (uint32_t r = 0; r < n_rg && status == FLSGPU_OK; r += slab_rg, ++slab) {
+		const uint32_t n = std::min(slab_rg, n_rg - r), n_vec = n * h.vec_per_rowgroup;
+		cudaStream_t s = sc->streams[slab & 1];
+		uint8_t* base = static_cast<uint8_t*>(sc->out[slab & 1]);
+		uint32_t* mask_dev = reinterpret_cast<uint32_t*>(base + dev_mask);
+		uint32_t* offsets_dev = reinterpret_cast<uint32_t*>(base + dev_offsets);
+		{
+			std::lock_guard<std::mutex> g(d->mu);
+			status = stage_range(t, d, rg_begin + r, n, col_ids.data(), (uint32_t)col_ids.size(), s);
+		}
+		if (status == FLSGPU_OK) {
+			status = flsgpu_filter_mask(t, filters, n_filters, rg_begin + r, n, nullptr, mask_dev, rg_mask_bytes * n, s);
+		}
+		if (status != FLSGPU_OK) {
+			break;
+		}
+		cudaError_t ce = fls_select_launch_plan(mask_dev, n_vec, offsets_dev, s);
+		if (ce == cudaSuccess) {
+			ce = cudaMemcpyAsync(sc->count_host + (slab & 1), offsets_dev + n_vec, 4, cudaMemcpyDeviceToHost, s);
+		}
+		if (ce == cudaSuccess) {
+			ce = cudaStreamSynchronize(s); // the slab's row count decides the size of every copy below
+		}
+		if (ce != cudaSuccess) {
+			status = cuda_fail(ce, "selection plan");
+			break;
+		}
+		g_launches.fetch_add(1, std::memory_order_relaxed);
+		const uint64_t n_sel = sc->count_host[slab & 1];
+		if (n_sel == 0) {
+			continue; // nothing of this slab passes: no decode, no copy
+		}
+		for (uint32_t i = 0; i < n_cols && status == FLSGPU_OK; ++i) {
+			const flsgpu_scan_column& c = cols[i];
+			const ColPlan& p = cp[i];
+			uint8_t* dev = base + dev_a;
+			if (p.is_string) {
+				const uint64_t hoff = heap_off(c.col, r), hbytes = heap_off(c.col, r + n) - hoff;
+				uint8_t* host_heap = static_cast<uint8_t*>(c.heap_host) + hoff;
+				status = flsgpu_decode_strings(t, c.col, rg_begin + r, n, dev, rg_rows * n * 16u, base + dev_heap, hbytes + 16,
+				                               reinterpret_cast<uint64_t>(host_heap), s);
+				d2h(host_heap, base + dev_heap, hbytes, s);
+			} else {
+				status = decode_column_impl(t, d, c.col, rg_begin + r, n, p.os, dev, s);
+			}
+			if (status != FLSGPU_OK) {
+				break;
+			}
+			ce = fls_select_launch_compact(dev, p.ob, mask_dev, offsets_dev, base + dev_b, n_vec, 0, s);
+			if (ce != cudaSuccess) {
+				status = cuda_fail(ce, "fls_select_compact_kernel");
+				break;
+			}
+			g_launches.fetch_add(1, std::memory_order_relaxed);
+			d2h(static_cast<uint8_t*>(c.out_host) + written * p.ob, base + dev_b, n_sel * p.ob, s);
+		}
+		if (row_index_host && status == FLSGPU_OK) {
+			ce = fls_select_launch_compact(nullptr, 4, mask_dev, offsets_dev, base + dev_b, n_vec, (uint32_t)(r * rg_rows), s);
+			if (ce != cudaSuccess) {
+				status = cuda_fail(ce, "fls_select_compact_kernel(row index)");
+				break;
+			}
+			g_launches.fetch_add(1, std::memory_order_relaxed);
+			d2h(row_index_host + written, base + dev_b, n_sel * 4u, s);
+		}
+		written += n_sel;
+	}
+	// always drain both streams before the scratch goes back to the pool
+	const cudaError_t e0 = cudaStreamSynchronize(sc->streams[0]), e1 = cudaStreamSynchronize(sc->streams[1]);
+	if (status == FLSGPU_OK && (e0 != cudaSuccess || e1 != cudaSuccess)) {
+		status = cuda_fail(e0 != cudaSuccess ? e0 : e1, "cudaStreamSynchronize");
+	}
+	if (status == FLSGPU_OK) {
+		*n_selected_out = written;
 	}
 	return status;
 }

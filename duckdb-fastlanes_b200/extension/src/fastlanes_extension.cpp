@@ -21,6 +21,10 @@ static void RegisterSettings(ExtensionLoader &loader) {
 	                          "Hand vectors the file marks CONSTANT or arithmetic SEQUENCE to DuckDB as CONSTANT / SEQUENCE vectors "
 	                          "instead of decoding and copying them",
 	                          LogicalType::BOOLEAN, Value::BOOLEAN(true));
+	config.AddExtensionOption("fastlanes_select_on_device",
+	                          "Apply the filters the device evaluates on the device: only the rows that pass are copied to the host "
+	                          "(off: every row of the projected columns comes back with a selection mask)",
+	                          LogicalType::BOOLEAN, Value::BOOLEAN(true));
 	config.AddExtensionOption("fastlanes_table_cache_mb",
 	                          "Opened .fls files stay open - container validated, image page-locked, compressed chunks resident in HBM - "
 	                          "for the next query until the cached files exceed this many MiB (0: no caching)",

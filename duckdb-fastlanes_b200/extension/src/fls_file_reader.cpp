@@ -244,6 +244,9 @@ void FastLanesReader::Initialize(ClientContext &context) {
 	if (context.TryGetCurrentSetting("fastlanes_compressed_vectors", setting) && !setting.IsNull()) {
 		compressed_vectors = setting.GetValue<bool>();
 	}
+	if (context.TryGetCurrentSetting("fastlanes_select_on_device", setting) && !setting.IsNull()) {
+		select_on_device = setting.GetValue<bool>();
+	}
 }
 
 void FastLanesReader::EnsureFileRowNumberColumn() {
@@ -508,7 +511,7 @@ bool FastLanesReader::TryInitializeScan(ClientContext &context, GlobalTableFunct
 	InitializeScanFilters(context, local_state);
 	// batch size: the setting, but never so large that DuckDB's other workers are left without row groups
 	const idx_t n_threads = MaxValue<idx_t>(1, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
-	const idx_t fair_share = (rowgroups_to_scan.size() + 2 * n_threads - 1) / (2 * n_threads);
+	const idx_t fair_share = (rowgroups_to_scan.size() + 4 * n_threads - 1) / (4 * n_threads);
 	const idx_t batch_limit = MaxValue<idx_t>(1, MinValue<idx_t>(rowgroups_per_batch, fair_share));
 	if (!TryAssignNextRowGroup(global_state, local_state, batch_limit)) {
 		local_state.batch_begin = local_state.batch_end = 0;
@@ -538,6 +541,8 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 	while (ls.stage.size() < ids.size()) {
 		ls.stage.push_back(make_uniq<FlsColumnStage>());
 	}
+	// device filters: the selection is applied on the device, only the rows that pass come back (packed, flat)
+	const bool select = select_on_device && !ls.device_filters.empty();
 	vector<flsgpu_scan_column> scan_columns(ids.size());
 	for (idx_t i = 0; i < ids.size(); i++) {
 		auto &stage = *ls.stage[i];
@@ -554,7 +559,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 			// (dictionary_kernel.hpp:80-101, fsst_dict_kernel.hpp:54-80); taken when every chunk of the batch is
 			// dictionary encoded, else the batch is materialised flat
 			uint64_t n_keys = 0, heap_bytes = 0;
-			stage.dictionary_form = flsgpu_string_dict_keys(table, ids[i], rg0, n_rg, &n_keys) == FLSGPU_OK;
+			stage.dictionary_form = !select && flsgpu_string_dict_keys(table, ids[i], rg0, n_rg, &n_keys) == FLSGPU_OK;
 			FlsCheck(flsgpu_string_heap_bytes(table, ids[i], rg0, n_rg, &heap_bytes), "flsgpu_string_heap_bytes");
 			stage.value_bytes = stage.dictionary_form ? sizeof(sel_t) : sizeof(string_t);
 			sc.string_form = stage.dictionary_form ? FLSGPU_STRING_DICTIONARY : FLSGPU_STRING_FLAT;
@@ -579,7 +584,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 		}
 		stage.forms.clear();
 		idx_t stage_rows = rows;
-		if (!stage.is_string && compressed_vectors) {
+		if (!stage.is_string && compressed_vectors && !select) {
 			// vectors the writer marked CONSTANT or arithmetic SEQUENCE are handed to DuckDB in that form (the reference
 			// does so for dec_constant_opr: constant_kernel.hpp:19-27): only the FLAT vectors are decoded and cross PCIe
 			uint64_t n_flat = 0;
@@ -592,6 +597,27 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 		ReservePinned(stage.rows, stage_rows * stage.value_bytes);
 		sc.out_host = stage.rows->ptr;
 		sc.out_capacity_bytes = stage.rows->bytes;
+	}
+	ls.compacted = select;
+	ls.n_selected = ls.sel_cursor = 0;
+	if (select) {
+		bool need_row_index = false;
+		for (idx_t i = 0; i < column_ids.size(); i++) {
+			need_row_index |= IsFileRowNumberColumn(column_ids[MultiFileLocalIndex(i)].GetId());
+		}
+		if (need_row_index) {
+			ReservePinned(ls.row_index, rows * sizeof(uint32_t));
+		}
+		uint64_t n_selected = 0;
+		FlsCheck(flsgpu_scan_selected_to_host(device_tables[ls.device_slot], scan_columns.data(), NumericCast<uint32_t>(scan_columns.size()),
+		                                      ls.device_filters.data(), NumericCast<uint32_t>(ls.device_filters.size()), rg0, n_rg,
+		                                      need_row_index ? reinterpret_cast<uint32_t *>(ls.row_index->ptr) : nullptr,
+		                                      need_row_index ? ls.row_index->bytes : 0, &n_selected),
+		         "read_fls");
+		ls.n_selected = n_selected;
+		ls.has_mask = false;
+		ls.batch_decoded = true;
+		return;
 	}
 	ls.has_mask = !ls.device_filters.empty();
 	if (ls.has_mask) {
@@ -633,7 +659,7 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 		return;
 	}
 	const idx_t rg_in_batch = ls.cur_rowgroup - ls.batch_begin;
-	const idx_t first_row = (rg_in_batch * info.vec_per_rowgroup + start_vector) * FLS_VEC_SZ;
+	const idx_t first_row = ls.compacted ? ls.sel_cursor : (rg_in_batch * info.vec_per_rowgroup + start_vector) * FLS_VEC_SZ;
 	idx_t n_conversions = 0;
 	if (ls.conversion_executor) {
 		ls.conversion_input.Reset(); // back to its own buffers: the last chunk left references to the staging memory
@@ -771,7 +797,7 @@ void FastLanesReader::FormedVector(FlsColumnStage &stage, const LogicalType &typ
 }
 
 // FastLanesReader::PopulateVirtualColumns (fls_reader.cpp:474-495): file_row_number = row_group_base + start + i
-void FastLanesReader::PopulateVirtualColumns(const FastLanesReadLocalState &, DataChunk &chunk, idx_t row_start, idx_t count) {
+void FastLanesReader::PopulateVirtualColumns(const FastLanesReadLocalState &ls, DataChunk &chunk, idx_t row_start, idx_t count) {
 	for (idx_t i = 0; i < column_ids.size(); i++) {
 		if (!IsFileRowNumberColumn(column_ids[MultiFileLocalIndex(i)].GetId())) {
 			continue;
@@ -779,6 +805,14 @@ void FastLanesReader::PopulateVirtualColumns(const FastLanesReadLocalState &, Da
 		auto &target = chunk.data[i];
 		target.SetVectorType(VectorType::FLAT_VECTOR);
 		const auto data = FlatVector::GetData<int64_t>(target);
+		if (ls.compacted) { // packed rows: their positions inside the batch came back with them
+			const auto positions = reinterpret_cast<const uint32_t *>(ls.row_index->ptr) + ls.sel_cursor;
+			const idx_t rg_rows = idx_t(info.vec_per_rowgroup) * FLS_VEC_SZ;
+			for (idx_t row = 0; row < count; row++) {
+				data[row] = NumericCast<int64_t>(row_group_offsets[ls.batch_begin + positions[row] / rg_rows] + positions[row] % rg_rows);
+			}
+			continue;
+		}
 		for (idx_t row = 0; row < count; row++) {
 			data[row] = NumericCast<int64_t>(row_start + row);
 		}
@@ -848,6 +882,26 @@ void FastLanesReader::Scan(ClientContext &, GlobalTableFunctionState &, LocalTab
 			}
 			ls.conversion_input.Initialize(Allocator::DefaultAllocator(), input_types);
 		}
+	}
+	while (ls.compacted) { // the batch is a packed run of selected rows: hand out 2048-row slices of it
+		if (ls.sel_cursor >= ls.n_selected) {
+			for (idx_t r = ls.batch_begin; r < ls.batch_end; r++) {
+				vectors_read += GetNVectors(r);
+			}
+			ls.batch_begin = ls.batch_end; // batch exhausted
+			return;
+		}
+		const idx_t count = MinValue<idx_t>(STANDARD_VECTOR_SIZE, ls.n_selected - ls.sel_cursor);
+		DecodePhysicalColumns(ls, chunk, 0, count);
+		PopulateVirtualColumns(ls, chunk, 0, count);
+		chunk.SetCardinality(count);
+		ApplyFilters(ls, chunk, 0, count); // what the device did not evaluate
+		ls.sel_cursor += count;
+		if (chunk.size() == 0) {
+			chunk.Reset();
+			continue;
+		}
+		return;
 	}
 	while (true) {
 		const auto batch = GetScanBatch(ls);

@@ -129,6 +129,12 @@ struct FastLanesReadLocalState : public LocalTableFunctionState {
 	vector<unique_ptr<FlsColumnStage>> stage;
 	buffer_ptr<FlsPinnedBuffer> mask; // selection bit mask of the device-evaluated filters for the batch
 	bool has_mask = false;
+	//! Batches with device filters: the selection is applied on the device (flsgpu_scan_selected_to_host), the staging buffers
+	//! hold only the n_selected rows that passed, packed in row order; chunks are 2048-row slices of them from sel_cursor on
+	bool compacted = false;
+	idx_t n_selected = 0;
+	idx_t sel_cursor = 0;
+	buffer_ptr<FlsPinnedBuffer> row_index; // position of every selected row inside the batch (file_row_number)
 	//! Pushed-down filters, split once per file into what the device evaluates and what the host evaluates
 	bool filters_ready = false;
 	const BaseFileReader *filters_for = nullptr;
@@ -242,6 +248,8 @@ private:
 	idx_t rowgroups_per_batch = 32;
 	//! Hand CONSTANT / SEQUENCE vectors to DuckDB as such instead of decoding them (setting fastlanes_compressed_vectors)
 	bool compressed_vectors = true;
+	//! Apply device-evaluated filters on the device: only selected rows cross PCIe (setting fastlanes_select_on_device)
+	bool select_on_device = true;
 	//! RowGroupFilter of the reference (row_group_filter.cpp:62-94): row groups whose zone maps cannot satisfy the filters
 	//! are never handed out.  Built once per scan under rowgroup_filter_lock.
 	std::mutex rowgroup_filter_lock;

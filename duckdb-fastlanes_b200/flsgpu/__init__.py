@@ -156,7 +156,7 @@ ABI_SYMBOLS = [
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
     "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms", "flsgpu_transfer_bytes",
     "flsgpu_n_devices", "flsgpu_table_share", "flsgpu_table_bind_device", "flsgpu_filter_mask_string_dict_static",
-    "flsgpu_aggregate_to_host",
+    "flsgpu_aggregate_to_host", "flsgpu_scan_selected_to_host",
 ]
 
 
@@ -415,6 +415,15 @@ class Table:
         arr = (ScanColumn * len(scan_columns))(*scan_columns)
         _check(lib.flsgpu_scan_filtered_to_host(self._h, arr, len(scan_columns), make_filters(filters), len(filters), rg_begin, n_rg,
                                                 _vp(mask_host_ptr), C.c_uint64(mask_bytes)), "scan_filtered_to_host")
+
+    def scan_selected_to_host(self, scan_columns, filters, row_index_ptr=0, row_index_bytes=0, rg_begin=0, n_rg=None):
+        """Filtered scan, selection applied on the device: returns the number of selected rows (packed in every out_host)."""
+        n_rg = self.n_rowgroups - rg_begin if n_rg is None else n_rg
+        arr = (ScanColumn * len(scan_columns))(*scan_columns)
+        n_sel = C.c_uint64()
+        _check(lib.flsgpu_scan_selected_to_host(self._h, arr, len(scan_columns), make_filters(filters), len(filters), rg_begin, n_rg,
+                                                _vp(row_index_ptr), C.c_uint64(row_index_bytes), C.byref(n_sel)), "scan_selected_to_host")
+        return n_sel.value
 
     def vector_forms(self, col, rg_begin=0, n_rg=None):
         """(forms: structured array of VECTOR_FORM per vector of the range, n_flat)."""

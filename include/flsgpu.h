@@ -306,6 +306,17 @@ int flsgpu_scan_projection_to_host(flsgpu_table* t, const flsgpu_scan_column* co
 int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, const flsgpu_filter* filters,
                                  uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg, uint32_t* mask_host, uint64_t mask_capacity_bytes);
 
+/* The same scan with the selection applied on the device (chunk.Slice(sel, count) of filter_executor.cpp:57-59, done before the
+ * copy instead of after it): only the rows that pass every filter are copied to the host, packed back to back over the whole
+ * range in row order - out_host of column i holds *n_selected_out rows when the call returns (its capacity must be that of
+ * the unfiltered column: how many rows pass is not known beforehand).  String columns come back flat (string_form must be
+ * FLSGPU_STRING_FLAT; the heap is copied whole, the packed string_t rows point into it), `compact` / `forms` are ignored.
+ * row_index_host (optional): for every selected row its position (rg - rg_begin) * vec_per_rowgroup * 1024 + row inside the
+ * range, u32 - what a reader needs for file_row_number.  n_filters must be >= 1.  Synchronous. */
+int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, const flsgpu_filter* filters,
+                                 uint32_t n_filters, uint32_t rg_begin, uint32_t n_rg, uint32_t* row_index_host,
+                                 uint64_t row_index_capacity_bytes, uint64_t* n_selected_out);
+
 int flsgpu_sync(void* cuda_stream);
 /* Pinned host allocations for staging / results (cudaHostAlloc). */
 int flsgpu_host_alloc(uint64_t bytes, void** out);

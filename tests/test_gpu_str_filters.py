@@ -96,3 +96,54 @@ def test_string_filters_through_reader(tmp_path, threads):
             src = data[names.index(col)]
             assert got[k] == [src[i] for i in idx], (fname, col)
     r.close()
+
+
+@pytest.mark.parametrize("n,vpr,slab_mb", [(3000, 2, None), (9 * 4096 + 55, 4, "1"), (200000, 16, None)])
+def test_selected_rows_scan_matches_python(n, vpr, slab_mb, monkeypatch):
+    """flsgpu_scan_selected_to_host: the filter's selection applied on the device (fls_select_plan / fls_select_compact kernels),
+    only the rows that pass come back, packed in row order: == plain Python over the input, for numeric columns, flat strings of
+    every encoding (dictionary encoded ones included) and the row index."""
+    if slab_mb:
+        monkeypatch.setenv("FLSGPU_SLAB_MB", slab_mb)  # several slabs: both streams, offsets carried from slab to slab
+    specs, data = table(n)
+    names = [s[0] for s in specs]
+    img = flsgpu.write_table(specs, data, vec_per_rowgroup=vpr)
+    t = flsgpu.Table(img)  # not staged by hand
+    rows = t.out_elems(t.n_rowgroups)
+    proj = ["v", "shipmode", "comment", "blob", "flag_runs", "freq_none"]
+    sets = filter_sets(data)
+    for fname in ("mixed", "dict_eq", "fsst_ge", "blob_lt_empty", "blob_ge_empty", "two_strings", "rle_str_eq_long", "frequency_str_ne"):
+        fs = sets[fname]
+        filt = [(names.index(c), flsgpu.CMP[op], k) for c, op, k in fs]
+        bufs, cols = [], []
+        for name in proj:
+            c = names.index(name)
+            if t.column(c).phys_bits == 128:
+                out = np.zeros(rows * 16, dtype=np.uint8)
+                heap = np.zeros(max(16, t.string_heap_bytes(c)), dtype=np.uint8)
+                cols.append(flsgpu.ScanColumn(col=c, string_form=flsgpu.STRING_FLAT, out_host=out.ctypes.data, out_capacity_bytes=out.nbytes,
+                                              heap_host=heap.ctypes.data, heap_capacity_bytes=heap.nbytes))
+                bufs.append((out, heap))
+            else:
+                out = np.zeros(rows, dtype=np.int64)
+                cols.append(flsgpu.ScanColumn(col=c, out_host=out.ctypes.data, out_capacity_bytes=out.nbytes))
+                bufs.append((out, None))
+        row_index = np.full(rows, 0xFFFFFFFF, dtype=np.uint32)
+        n_sel = t.scan_selected_to_host(cols, filt, row_index.ctypes.data, row_index.nbytes)
+        want = python_mask(specs, data, fs)
+        idx = np.nonzero(want)[0]
+        assert n_sel == len(idx), fname
+        # row index: position inside the padded range layout -> row number of the table
+        stride = t.vec_per_rowgroup * 1024
+        got_rows = (row_index[:n_sel] // stride).astype(np.int64) * stride + row_index[:n_sel] % stride
+        assert np.array_equal(got_rows, idx), fname
+        for name, (out, heap) in zip(proj, bufs):
+            src = data[names.index(name)]
+            if heap is None:
+                assert out[:n_sel].tobytes() == np.asarray(src)[want].tobytes(), (fname, name)
+            else:
+                st = out[:n_sel * 16].view(flsgpu.STRING_T).reshape(-1)
+                assert flsgpu.strings_from(st, heap, heap.ctypes.data) == [bytes(src[i]) for i in idx], (fname, name)
+    with pytest.raises(flsgpu.FlsError):
+        t.scan_selected_to_host(cols, [])
+    t.close()
