@@ -35,6 +35,10 @@ cudaError_t fls_str_launch_key_flags(FlsStrFilterLaunch L, cudaStream_t stream);
 cudaError_t fls_select_launch_plan(const uint32_t* mask, uint32_t n_vec, uint32_t* vec_offsets, cudaStream_t stream);
 cudaError_t fls_select_launch_compact(const void* in, uint32_t elem_bytes, const uint32_t* mask, const uint32_t* vec_offsets, void* out,
                                       uint32_t n_vec, uint32_t iota_base, cudaStream_t stream);
+// dictionary codes: every code moved up by the keys in front of its row group (key_prefix as in FlsStrLaunch)
+cudaError_t fls_select_launch_compact_codes(const uint32_t* in, const uint32_t* mask, const uint32_t* vec_offsets, uint32_t* out, uint32_t n_vec,
+                                            const unsigned long long* key_prefix, unsigned long long key_prefix0, uint32_t stride,
+                                            uint32_t vec_per_rg, uint32_t first_rg, cudaStream_t stream);
 #endif
 
 constexpr int kFlsWarpsPerCta = 8;

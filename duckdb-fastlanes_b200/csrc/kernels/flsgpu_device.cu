@@ -1274,7 +1274,7 @@ int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 	}
 	struct ColPlan {
 		OutSpec os;
-		bool is_string = false;
+		bool is_string = false, dict = false;
 		uint32_t ob = 0; // bytes per row
 	};
 	std::vector<ColPlan> cp(n_cols);
@@ -1288,15 +1288,22 @@ int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		ColPlan& p = cp[i];
 		p.is_string = t->columns[c.col].phys_bits == 128;
 		if (p.is_string) {
-			if (c.string_form != FLSGPU_STRING_FLAT) {
-				return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_scan_selected_to_host: string columns come back flat (string_t rows + heap)");
-			}
-			uint64_t heap_need = 0;
+			p.dict = c.string_form == FLSGPU_STRING_DICTIONARY;
+			uint64_t heap_need = 0, keys_need = 0;
 			flsgpu_string_heap_bytes(t, c.col, rg_begin, n_rg, &heap_need);
-			if (!c.heap_host || c.heap_capacity_bytes < heap_need) {
-				return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_selected_to_host: string heap buffer null or too small");
+			if (p.dict) {
+				rc = flsgpu_string_dict_keys(t, c.col, rg_begin, n_rg, &keys_need); // fails unless every chunk is dictionary encoded
+				if (rc) {
+					return rc;
+				}
+				if (keys_need > 0xffffffffull) {
+					return fls_set_error(FLSGPU_ERR_UNSUPPORTED, "flsgpu_scan_selected_to_host: more than 2^32 dictionary keys in the range");
+				}
 			}
-			p.ob = 16;
+			if (!c.heap_host || c.heap_capacity_bytes < heap_need || (p.dict && (!c.keys_host || c.keys_capacity_bytes < keys_need * 16u))) {
+				return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_scan_selected_to_host: string heap / key buffer null or too small");
+			}
+			p.ob = p.dict ? 4 : 16;
 		} else {
 			rc = resolve_out(t->columns[c.col], c.out_type, &p.os);
 			if (rc) {
@@ -1321,17 +1328,25 @@ int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 	// slab: decode area A + packed area B (the widest column each) + the largest string heap of a slab + mask + offsets
 	const uint64_t slab_target = (uint64_t)env_u32("FLSGPU_SLAB_MB", 256) << 20;
 	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, slab_target / std::max<uint64_t>(1, rg_rows * std::max(1u, ob_max) * 2u)));
-	uint64_t heap_max = 0;
+	auto key_off = [&](uint32_t col, uint32_t r) {
+		const uint64_t i0 = (uint64_t)rg_begin * h.n_columns + col;
+		return d->key_prefix[i0 + (uint64_t)r * h.n_columns] - d->key_prefix[i0];
+	};
+	uint64_t heap_max = 0, keys_max = 0;
 	for (uint32_t i = 0; i < n_cols; ++i) {
 		if (cp[i].is_string) {
 			for (uint32_t r = 0; r < n_rg; r += slab_rg) {
 				const uint32_t e = std::min(n_rg, r + slab_rg);
 				heap_max = std::max(heap_max, heap_off(cols[i].col, e) - heap_off(cols[i].col, r));
+				if (cp[i].dict) {
+					keys_max = std::max(keys_max, key_off(cols[i].col, e) - key_off(cols[i].col, r));
+				}
 			}
 		}
 	}
 	const uint64_t area = (rg_rows * slab_rg * std::max(1u, ob_max) + 255u) & ~255ull;
-	const uint64_t dev_a = 0, dev_b = area, dev_heap = 2u * area, dev_mask = dev_heap + ((heap_max + 16u + 255u) & ~255ull);
+	const uint64_t dev_a = 0, dev_b = area, dev_heap = 2u * area, dev_keys = dev_heap + ((heap_max + 16u + 255u) & ~255ull);
+	const uint64_t dev_mask = dev_keys + ((keys_max * 16u + 16u + 255u) & ~255ull);
 	const uint64_t rg_mask_bytes = (uint64_t)h.vec_per_rowgroup * 128u;
 	const uint64_t dev_offsets = dev_mask + rg_mask_bytes * slab_rg;
 	const uint64_t slab_bytes = dev_offsets + ((((uint64_t)slab_rg * h.vec_per_rowgroup + 1u) * 4u + 255u) & ~255ull);
@@ -1422,13 +1437,45 @@ int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		}
 		g_launches.fetch_add(1, std::memory_order_relaxed);
 		const uint64_t n_sel = sc->count_host[slab & 1];
-		if (n_sel == 0) {
-			continue; // nothing of this slab passes: no decode, no copy
-		}
 		for (uint32_t i = 0; i < n_cols && status == FLSGPU_OK; ++i) {
 			const flsgpu_scan_column& c = cols[i];
 			const ColPlan& p = cp[i];
 			uint8_t* dev = base + dev_a;
+			if (n_sel == 0 && !(p.is_string && p.dict)) {
+				continue; // nothing of this slab passes: no decode, no copy (dictionaries are still delivered whole)
+			}
+			if (p.is_string && p.dict) {
+				// keys + dictionary bytes of the slab's row groups go to their places in the range-wide dictionary; the packed
+				// codes count from the start of that dictionary
+				const uint64_t hoff = heap_off(c.col, r), hbytes = heap_off(c.col, r + n) - hoff;
+				const uint64_t koff = key_off(c.col, r), kbytes = (key_off(c.col, r + n) - koff) * 16u;
+				uint8_t* host_heap = static_cast<uint8_t*>(c.heap_host) + hoff;
+				status = flsgpu_decode_string_dict(t, c.col, rg_begin + r, n, base + dev_keys, kbytes + 16, base + dev_heap, hbytes + 16,
+				                                   reinterpret_cast<uint64_t>(host_heap), s);
+				if (status == FLSGPU_OK && n_sel) {
+					status = flsgpu_decode_string_codes(t, c.col, rg_begin + r, n, reinterpret_cast<uint32_t*>(dev), rg_rows * n * 4u, s);
+				}
+				if (status != FLSGPU_OK) {
+					break;
+				}
+				d2h(static_cast<uint8_t*>(c.keys_host) + koff * 16u, base + dev_keys, kbytes, s);
+				d2h(host_heap, base + dev_heap, hbytes, s);
+				if (n_sel == 0) {
+					continue;
+				}
+				const uint64_t i0 = (uint64_t)rg_begin * h.n_columns + c.col;
+				ce = fls_select_launch_compact_codes(reinterpret_cast<const uint32_t*>(dev), mask_dev, offsets_dev,
+				                                     reinterpret_cast<uint32_t*>(base + dev_b), n_vec,
+				                                     reinterpret_cast<const unsigned long long*>(d->d_key_prefix + i0), d->key_prefix[i0],
+				                                     h.n_columns, h.vec_per_rowgroup, r, s);
+				if (ce != cudaSuccess) {
+					status = cuda_fail(ce, "fls_select_compact_kernel(codes)");
+					break;
+				}
+				g_launches.fetch_add(1, std::memory_order_relaxed);
+				d2h(static_cast<uint8_t*>(c.out_host) + written * 4u, base + dev_b, n_sel * 4u, s);
+				continue;
+			}
 			if (p.is_string) {
 				const uint64_t hoff = heap_off(c.col, r), hbytes = heap_off(c.col, r + n) - hoff;
 				uint8_t* host_heap = static_cast<uint8_t*>(c.heap_host) + hoff;
@@ -1449,7 +1496,7 @@ int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 			g_launches.fetch_add(1, std::memory_order_relaxed);
 			d2h(static_cast<uint8_t*>(c.out_host) + written * p.ob, base + dev_b, n_sel * p.ob, s);
 		}
-		if (row_index_host && status == FLSGPU_OK) {
+		if (row_index_host && n_sel && status == FLSGPU_OK) {
 			ce = fls_select_launch_compact(nullptr, 4, mask_dev, offsets_dev, base + dev_b, n_vec, (uint32_t)(r * rg_rows), s);
 			if (ce != cudaSuccess) {
 				status = cuda_fail(ce, "fls_select_compact_kernel(row index)");

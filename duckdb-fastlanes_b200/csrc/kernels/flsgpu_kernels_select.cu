@@ -83,9 +83,18 @@ __global__ void __launch_bounds__(kPlanThreads) fls_select_plan_kernel(const uin
 	}
 }
 
-template <typename T, bool IOTA>
+// dictionary codes: the codes of a row group count from its own dictionary; packed rows of several row groups share ONE
+// dictionary (all keys of the range back to back), so every code is moved up by the number of keys in front of its row group
+struct FlsKeyBase {
+	const unsigned long long* key_prefix; // per chunk of the column (stride entries apart), or nullptr
+	unsigned long long key_prefix0;       // keys in front of the range
+	uint32_t stride, vec_per_rg, first_rg; // first_rg: row group of vector 0 inside the range
+};
+
+template <typename T, bool IOTA, bool CODES>
 __global__ void __launch_bounds__(256) fls_select_compact_kernel(const T* __restrict__ in, const uint32_t* __restrict__ mask,
-                                                                 const uint32_t* __restrict__ vec_offsets, T* __restrict__ out, uint32_t n_vec, uint32_t iota_base) {
+                                                                 const uint32_t* __restrict__ vec_offsets, T* __restrict__ out, uint32_t n_vec, uint32_t iota_base,
+                                                                 const FlsKeyBase kb) {
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t v = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (v >= n_vec) {
@@ -108,6 +117,10 @@ __global__ void __launch_bounds__(256) fls_select_compact_kernel(const T* __rest
 	const uint32_t base = __ldg(vec_offsets + v);
 	const T* src = in + (size_t)v * 1024u;
 	const uint32_t below = (1u << lane) - 1u;
+	uint32_t key_add = 0;
+	if constexpr (CODES) {
+		key_add = (uint32_t)(__ldg(kb.key_prefix + (size_t)(kb.first_rg + v / kb.vec_per_rg) * kb.stride) - kb.key_prefix0);
+	}
 #pragma unroll 4
 	for (int it = 0; it < 32; ++it) {
 		const uint32_t w = __shfl_sync(0xffffffffu, word, it);
@@ -116,6 +129,8 @@ __global__ void __launch_bounds__(256) fls_select_compact_kernel(const T* __rest
 			const uint32_t pos = base + off + __popc(w & below);
 			if constexpr (IOTA) {
 				out[pos] = (T)(iota_base + v * 1024u + (uint32_t)it * 32u + lane);
+			} else if constexpr (CODES) {
+				out[pos] = src[it * 32 + lane] + key_add;
 			} else {
 				out[pos] = src[it * 32 + lane];
 			}
@@ -131,31 +146,43 @@ cudaError_t fls_select_launch_plan(const uint32_t* mask, uint32_t n_vec, uint32_
 }
 
 // elem_bytes 1 / 2 / 4 / 8 / 16; in == nullptr: the rows' indexes inside the range (u32) are written instead of values
+cudaError_t fls_select_launch_compact_codes(const uint32_t* in, const uint32_t* mask, const uint32_t* vec_offsets, uint32_t* out, uint32_t n_vec,
+                                            const unsigned long long* key_prefix, unsigned long long key_prefix0, uint32_t stride,
+                                            uint32_t vec_per_rg, uint32_t first_rg, cudaStream_t stream) {
+	if (!n_vec) {
+		return cudaSuccess;
+	}
+	const FlsKeyBase kb {key_prefix, key_prefix0, stride, vec_per_rg, first_rg};
+	fls_select_compact_kernel<uint32_t, false, true><<<(n_vec + 7u) / 8u, 256, 0, stream>>>(in, mask, vec_offsets, out, n_vec, 0u, kb);
+	return cudaGetLastError();
+}
+
 cudaError_t fls_select_launch_compact(const void* in, uint32_t elem_bytes, const uint32_t* mask, const uint32_t* vec_offsets, void* out,
                                       uint32_t n_vec, uint32_t iota_base, cudaStream_t stream) {
 	const uint32_t grid = (n_vec + 7u) / 8u;
 	if (!n_vec) {
 		return cudaSuccess;
 	}
+	const FlsKeyBase kb {nullptr, 0ull, 0u, 1u, 0u};
 	if (!in) {
-		fls_select_compact_kernel<uint32_t, true><<<grid, 256, 0, stream>>>(nullptr, mask, vec_offsets, static_cast<uint32_t*>(out), n_vec, iota_base);
+		fls_select_compact_kernel<uint32_t, true, false><<<grid, 256, 0, stream>>>(nullptr, mask, vec_offsets, static_cast<uint32_t*>(out), n_vec, iota_base, kb);
 		return cudaGetLastError();
 	}
 	switch (elem_bytes) {
 	case 1:
-		fls_select_compact_kernel<uint8_t, false><<<grid, 256, 0, stream>>>(static_cast<const uint8_t*>(in), mask, vec_offsets, static_cast<uint8_t*>(out), n_vec, 0u);
+		fls_select_compact_kernel<uint8_t, false, false><<<grid, 256, 0, stream>>>(static_cast<const uint8_t*>(in), mask, vec_offsets, static_cast<uint8_t*>(out), n_vec, 0u, kb);
 		break;
 	case 2:
-		fls_select_compact_kernel<uint16_t, false><<<grid, 256, 0, stream>>>(static_cast<const uint16_t*>(in), mask, vec_offsets, static_cast<uint16_t*>(out), n_vec, 0u);
+		fls_select_compact_kernel<uint16_t, false, false><<<grid, 256, 0, stream>>>(static_cast<const uint16_t*>(in), mask, vec_offsets, static_cast<uint16_t*>(out), n_vec, 0u, kb);
 		break;
 	case 4:
-		fls_select_compact_kernel<uint32_t, false><<<grid, 256, 0, stream>>>(static_cast<const uint32_t*>(in), mask, vec_offsets, static_cast<uint32_t*>(out), n_vec, 0u);
+		fls_select_compact_kernel<uint32_t, false, false><<<grid, 256, 0, stream>>>(static_cast<const uint32_t*>(in), mask, vec_offsets, static_cast<uint32_t*>(out), n_vec, 0u, kb);
 		break;
 	case 8:
-		fls_select_compact_kernel<unsigned long long, false><<<grid, 256, 0, stream>>>(static_cast<const unsigned long long*>(in), mask, vec_offsets, static_cast<unsigned long long*>(out), n_vec, 0u);
+		fls_select_compact_kernel<unsigned long long, false, false><<<grid, 256, 0, stream>>>(static_cast<const unsigned long long*>(in), mask, vec_offsets, static_cast<unsigned long long*>(out), n_vec, 0u, kb);
 		break;
 	case 16:
-		fls_select_compact_kernel<uint4, false><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(in), mask, vec_offsets, static_cast<uint4*>(out), n_vec, 0u);
+		fls_select_compact_kernel<uint4, false, false><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(in), mask, vec_offsets, static_cast<uint4*>(out), n_vec, 0u, kb);
 		break;
 	default: return cudaErrorInvalidValue;
 	}

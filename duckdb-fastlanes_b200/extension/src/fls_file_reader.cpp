@@ -559,7 +559,7 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 			// (dictionary_kernel.hpp:80-101, fsst_dict_kernel.hpp:54-80); taken when every chunk of the batch is
 			// dictionary encoded, else the batch is materialised flat
 			uint64_t n_keys = 0, heap_bytes = 0;
-			stage.dictionary_form = !select && flsgpu_string_dict_keys(table, ids[i], rg0, n_rg, &n_keys) == FLSGPU_OK;
+			stage.dictionary_form = flsgpu_string_dict_keys(table, ids[i], rg0, n_rg, &n_keys) == FLSGPU_OK;
 			FlsCheck(flsgpu_string_heap_bytes(table, ids[i], rg0, n_rg, &heap_bytes), "flsgpu_string_heap_bytes");
 			stage.value_bytes = stage.dictionary_form ? sizeof(sel_t) : sizeof(string_t);
 			sc.string_form = stage.dictionary_form ? FLSGPU_STRING_DICTIONARY : FLSGPU_STRING_FLAT;
@@ -576,8 +576,9 @@ void FastLanesReader::DecodeRowGroupBatch(FastLanesReadLocalState &ls) {
 					FlsCheck(flsgpu_table_chunk(table, rg0 + r, ids[i], &chunk), "flsgpu_table_chunk");
 					stage.key_offsets[r + 1] = stage.key_offsets[r] + chunk.aux_count;
 				}
-				stage.dictionaries.resize(n_rg);
-				stage.dictionary_ids.assign(n_rg, string());
+				// packed batches (select): one dictionary over the keys of all row groups of the batch, the entries index it
+				stage.dictionaries.resize(select ? 1 : n_rg);
+				stage.dictionary_ids.assign(select ? 1 : n_rg, string());
 			}
 		} else {
 			stage.value_bytes = GetTypeIdSize(physical);
@@ -674,22 +675,24 @@ void FastLanesReader::DecodePhysicalColumns(FastLanesReadLocalState &ls, DataChu
 		const bool converted = ls.conversion_of_output[i].IsValid();
 		auto &target = converted ? ls.conversion_input.data[n_conversions++] : chunk.data[i];
 		if (stage.dictionary_form) {
-			auto &dictionary = stage.dictionaries[rg_in_batch];
-			const idx_t dict_size = stage.key_offsets[rg_in_batch + 1] - stage.key_offsets[rg_in_batch];
+			const idx_t dict_slot = ls.compacted ? 0 : rg_in_batch;
+			const idx_t first_key = ls.compacted ? 0 : stage.key_offsets[rg_in_batch];
+			auto &dictionary = stage.dictionaries[dict_slot];
+			const idx_t dict_size = (ls.compacted ? stage.key_offsets.back() : stage.key_offsets[rg_in_batch + 1]) - first_key;
 			if (!dictionary) { // once per row group, like KernelTraits<dec_dict_opr<fls_string_t>>::Prepare
-				dictionary = make_uniq<Vector>(type, stage.keys->ptr + stage.key_offsets[rg_in_batch] * sizeof(string_t));
+				dictionary = make_uniq<Vector>(type, stage.keys->ptr + first_key * sizeof(string_t));
 				StringVector::AddBuffer(*dictionary, stage.keys);
 				StringVector::AddBuffer(*dictionary, stage.heap);
 				// operators cache work per dictionary id (hash tables, dictionary-aware functions): it must never repeat,
 				// not even when a later dictionary is allocated at the address of a freed one
 				static atomic<idx_t> next_dictionary_id {0};
-				stage.dictionary_ids[rg_in_batch] = "fls_dict_" + to_string(next_dictionary_id++);
+				stage.dictionary_ids[dict_slot] = "fls_dict_" + to_string(next_dictionary_id++);
 			}
 			// the selection entries of the chunk's rows: copied (8 KiB) so that the dictionary vector owns them
 			SelectionVector sel(STANDARD_VECTOR_SIZE);
 			std::memcpy(sel.data(), stage.rows->ptr + first_row * sizeof(sel_t), count * sizeof(sel_t));
 			target.Dictionary(*dictionary, dict_size, sel, count);
-			DictionaryVector::SetDictionaryId(target, stage.dictionary_ids[rg_in_batch]);
+			DictionaryVector::SetDictionaryId(target, stage.dictionary_ids[dict_slot]);
 			continue;
 		}
 		if (!stage.forms.empty()) {

@@ -309,8 +309,11 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 /* The same scan with the selection applied on the device (chunk.Slice(sel, count) of filter_executor.cpp:57-59, done before the
  * copy instead of after it): only the rows that pass every filter are copied to the host, packed back to back over the whole
  * range in row order - out_host of column i holds *n_selected_out rows when the call returns (its capacity must be that of
- * the unfiltered column: how many rows pass is not known beforehand).  String columns come back flat (string_form must be
- * FLSGPU_STRING_FLAT; the heap is copied whole, the packed string_t rows point into it), `compact` / `forms` are ignored.
+ * the unfiltered column: how many rows pass is not known beforehand).  String columns: flat (packed string_t rows, the heap
+ * copied whole), or dictionary form when every chunk of the range is dictionary encoded - then keys_host / heap_host receive
+ * the keys and dictionary bytes of ALL row groups of the range back to back (as flsgpu_decode_string_dict lays them out) and
+ * the packed u32 entries index that one range-wide dictionary, so that rows of different row groups can share a DuckDB
+ * DICTIONARY_VECTOR.  `compact` / `forms` are ignored.
  * row_index_host (optional): for every selected row its position (rg - rg_begin) * vec_per_rowgroup * 1024 + row inside the
  * range, u32 - what a reader needs for file_row_number.  n_filters must be >= 1.  Synchronous. */
 int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols, uint32_t n_cols, const flsgpu_filter* filters,

@@ -128,6 +128,17 @@ def test_selected_rows_scan_matches_python(n, vpr, slab_mb, monkeypatch):
                 out = np.zeros(rows, dtype=np.int64)
                 cols.append(flsgpu.ScanColumn(col=c, out_host=out.ctypes.data, out_capacity_bytes=out.nbytes))
                 bufs.append((out, None))
+        # dictionary form of dictionary-encoded columns: packed entries into ONE dictionary over all row groups of the range
+        dict_bufs = []
+        for name in ("shipmode", "instruct"):
+            c = names.index(name)
+            codes = np.zeros(rows, dtype=np.uint32)
+            keys = np.zeros(max(1, t.string_dict_keys(c)) * 16, dtype=np.uint8)
+            heap = np.zeros(max(16, t.string_heap_bytes(c)), dtype=np.uint8)
+            cols.append(flsgpu.ScanColumn(col=c, string_form=flsgpu.STRING_DICTIONARY, out_host=codes.ctypes.data, out_capacity_bytes=codes.nbytes,
+                                          heap_host=heap.ctypes.data, heap_capacity_bytes=heap.nbytes, keys_host=keys.ctypes.data,
+                                          keys_capacity_bytes=keys.nbytes))
+            dict_bufs.append((name, codes, keys, heap))
         row_index = np.full(rows, 0xFFFFFFFF, dtype=np.uint32)
         n_sel = t.scan_selected_to_host(cols, filt, row_index.ctypes.data, row_index.nbytes)
         want = python_mask(specs, data, fs)
@@ -144,6 +155,15 @@ def test_selected_rows_scan_matches_python(n, vpr, slab_mb, monkeypatch):
             else:
                 st = out[:n_sel * 16].view(flsgpu.STRING_T).reshape(-1)
                 assert flsgpu.strings_from(st, heap, heap.ctypes.data) == [bytes(src[i]) for i in idx], (fname, name)
+        for name, codes, keys, heap in dict_bufs:
+            src = data[names.index(name)]
+            all_keys = flsgpu.strings_from(keys.view(flsgpu.STRING_T).reshape(-1), heap, heap.ctypes.data)
+            assert [all_keys[k] for k in codes[:n_sel]] == [bytes(src[i]) for i in idx], (fname, name, "dictionary form")
     with pytest.raises(flsgpu.FlsError):
         t.scan_selected_to_host(cols, [])
+    with pytest.raises(flsgpu.FlsError):  # dictionary form of a column that is not dictionary encoded
+        c = names.index("comment")
+        t.scan_selected_to_host([flsgpu.ScanColumn(col=c, string_form=flsgpu.STRING_DICTIONARY, out_host=codes.ctypes.data,
+                                                   out_capacity_bytes=codes.nbytes, heap_host=heap.ctypes.data, heap_capacity_bytes=1 << 40,
+                                                   keys_host=keys.ctypes.data, keys_capacity_bytes=keys.nbytes)], filt)
     t.close()

@@ -1,4 +1,4 @@
 set -x
-python -m pytest tests/test_gpu_str_filters.py tests/test_sql_extension.py tests/test_gpu_filters.py -m gpu -x -q > gpurun_out/sel_suite.log 2>&1; echo suite=$?; tail -30 gpurun_out/sel_suite.log
-tail -15 gpurun_out/sqltest_extension.log
-python tools/lineitem_dbgen.py --sf 10 --parity-sf 1 --sql-runs 5 --out gpurun_out/r02_lineitem_dbgen_sf10.json > gpurun_out/dbgen_sf10.log 2>&1; echo dbgen=$?; tail -5 gpurun_out/dbgen_sf10.log
+python -m pytest tests/test_gpu_str_filters.py tests/test_sql_extension.py -m gpu -x -q > gpurun_out/sel_suite.log 2>&1; echo suite=$?; tail -30 gpurun_out/sel_suite.log
+tail -8 gpurun_out/sqltest_extension.log
+python tools/lineitem_dbgen.py --sf 10 --parity-sf 1 --sql-runs 5 --out gpurun_out/r02_lineitem_dbgen_sf10.json > gpurun_out/dbgen_sf10.log 2>&1; echo dbgen=$?; tail -3 gpurun_out/dbgen_sf10.log
