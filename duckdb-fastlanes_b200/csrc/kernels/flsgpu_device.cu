@@ -39,22 +39,39 @@ std::map<std::tuple<const void*, uint32_t, int>, int> g_occ;        // (fn, smem
 constexpr uint32_t kMaxSmemPerCta = 227u * 1024u;
 
 // tuning knobs (environment overrides are for experiments; defaults are the measured best)
-uint32_t env_u32(const char* name, uint32_t def) {
+// A value that is not a plain decimal number inside [lo, hi] is reported once on stderr and ignored: a typo in an experiment
+// knob must not turn into a zero-sized slab or a 4 GiB shared-memory request.
+uint32_t env_u32(const char* name, uint32_t def, uint32_t lo = 0, uint32_t hi = 0xffffffffu) {
 	const char* v = std::getenv(name);
-	return v ? (uint32_t)std::strtoul(v, nullptr, 10) : def;
+	if (!v) {
+		return def;
+	}
+	char* end = nullptr;
+	const unsigned long long x = std::strtoull(v, &end, 10);
+	if (end == v || *end != '\0' || x < lo || x > hi) {
+		static std::mutex mu;
+		static std::vector<std::string> reported;
+		std::lock_guard<std::mutex> g(mu);
+		if (std::find(reported.begin(), reported.end(), name) == reported.end()) {
+			reported.push_back(name);
+			std::fprintf(stderr, "flsgpu: ignoring %s=\"%s\" (expected an integer in [%u, %u]); using %u\n", name, v, lo, hi, def);
+		}
+		return def;
+	}
+	return (uint32_t)x;
 }
-const uint32_t g_run_shift = std::min(5u, env_u32("FLSGPU_RUN_SHIFT", 0));
-const uint32_t g_prefetch = env_u32("FLSGPU_PREFETCH", 1);
-const uint32_t g_pdl = env_u32("FLSGPU_PDL", 1);                // programmatic dependent launch between materialising decode launches
-const uint32_t g_force_slots = env_u32("FLSGPU_NSLOTS", 0);     // experiments: pipeline depth override
-const uint32_t g_max_ctas = env_u32("FLSGPU_MAX_CTAS", 0);      // experiments: cap on resident CTAs per SM
-const uint32_t g_budget_kb = env_u32("FLSGPU_WARP_KB", 18);     // shared-memory budget per warp (KiB) the depth is sized for (14 -> 18 with chained launches: equal or up to +2.5 % across widths, all_types step 1.162 -> 1.149 ms)
+const uint32_t g_run_shift = std::min(5u, env_u32("FLSGPU_RUN_SHIFT", 0, 0, 5));
+const uint32_t g_prefetch = env_u32("FLSGPU_PREFETCH", 1, 0, 1);
+const uint32_t g_pdl = env_u32("FLSGPU_PDL", 1, 0, 1);                // programmatic dependent launch between materialising decode launches
+const uint32_t g_force_slots = env_u32("FLSGPU_NSLOTS", 0, 0, 16);     // experiments: pipeline depth override
+const uint32_t g_max_ctas = env_u32("FLSGPU_MAX_CTAS", 0, 0, 32);      // experiments: cap on resident CTAs per SM
+const uint32_t g_budget_kb = env_u32("FLSGPU_WARP_KB", 18, 4, 27);     // shared-memory budget per warp (KiB) the depth is sized for (14 -> 18 with chained launches: equal or up to +2.5 % across widths, all_types step 1.162 -> 1.149 ms)
 // DICT launches: a warp takes runs of 8 consecutive vectors (so a CTA works through one row group = one dictionary) and
 // the pipeline is kept shallow, which leaves most of the SM's L1 to the dictionary: 4096 x 8-byte keys 0.82 -> 0.26 ms
 // per 128 M values (measured; low-cardinality dictionaries are unaffected)
-const uint32_t g_dict_run_shift = std::min(5u, env_u32("FLSGPU_DICT_RUN_SHIFT", 3));
-const uint32_t g_dict_kb = env_u32("FLSGPU_DICT_KB", 6);
-const uint32_t g_swar8_kb = env_u32("FLSGPU_SWAR8_KB", 8);      // same for the 8-bit SWAR kernel (48 registers: up to five resident CTAs per SM)
+const uint32_t g_dict_run_shift = std::min(5u, env_u32("FLSGPU_DICT_RUN_SHIFT", 3, 0, 5));
+const uint32_t g_dict_kb = env_u32("FLSGPU_DICT_KB", 6, 2, 27);
+const uint32_t g_swar8_kb = env_u32("FLSGPU_SWAR8_KB", 8, 2, 27);      // same for the 8-bit SWAR kernel (48 registers: up to five resident CTAs per SM)
 
 int cuda_fail(cudaError_t e, const char* where) {
 	char msg[256];
@@ -1035,7 +1052,7 @@ int flsgpu_scan_filtered_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 			rg_avg += heap_off(cols[i].col, n_rg) / n_rg;
 		}
 	}
-	const uint64_t slab_target = (uint64_t)env_u32("FLSGPU_SLAB_MB", 256) << 20;
+	const uint64_t slab_target = (uint64_t)env_u32("FLSGPU_SLAB_MB", 256, 1, 65536) << 20;
 	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, slab_target / std::max<uint64_t>(1, rg_avg)));
 	uint64_t slab_bytes = 0;
 	for (uint32_t i = 0; i < n_cols; ++i) {
@@ -1326,7 +1343,7 @@ int flsgpu_scan_selected_to_host(flsgpu_table* t, const flsgpu_scan_column* cols
 		return d->heap_prefix[i0 + (uint64_t)r * h.n_columns] - d->heap_prefix[i0];
 	};
 	// slab: decode area A + packed area B (the widest column each) + the largest string heap of a slab + mask + offsets
-	const uint64_t slab_target = (uint64_t)env_u32("FLSGPU_SLAB_MB", 256) << 20;
+	const uint64_t slab_target = (uint64_t)env_u32("FLSGPU_SLAB_MB", 256, 1, 65536) << 20;
 	const uint32_t slab_rg = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_rg, slab_target / std::max<uint64_t>(1, rg_rows * std::max(1u, ob_max) * 2u)));
 	auto key_off = [&](uint32_t col, uint32_t r) {
 		const uint64_t i0 = (uint64_t)rg_begin * h.n_columns + col;
@@ -1602,7 +1619,7 @@ int flsgpu_host_free(void* p) {
 	if (!p) {
 		return FLSGPU_OK;
 	}
-	static const uint64_t limit = (uint64_t)env_u32("FLSGPU_HOST_POOL_MB", 8192) << 20;
+	static const uint64_t limit = (uint64_t)env_u32("FLSGPU_HOST_POOL_MB", 8192, 0, 1u << 20) << 20;
 	HostPool& hp = host_pool();
 	{
 		std::lock_guard<std::mutex> g(hp.mu);
@@ -1736,8 +1753,8 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	}
 	if (n_str) {
 		const double avg_dec = (double)dec_bytes / (double)n_str, avg_comp = (double)comp_bytes / (double)n_str;
-		const uint32_t budget = env_u32("FLSGPU_STR_WARP_KB", 10) * 1024u, cap = 26u * 1024u;
-		uint32_t ls = std::min(16u, env_u32("FLSGPU_STR_LANE_STRINGS", 16));
+		const uint32_t budget = env_u32("FLSGPU_STR_WARP_KB", 10, 2, 26) * 1024u, cap = 26u * 1024u;
+		uint32_t ls = std::min(16u, env_u32("FLSGPU_STR_LANE_STRINGS", 16, 1, 16));
 		for (;; ls >>= 1) {
 			const uint32_t db = ((uint32_t)(2.0 * 32.0 * ls * avg_dec) + 64u + 255u) & ~255u;
 			const uint32_t cb = ((uint32_t)(2.0 * 32.0 * ls * avg_comp) + 64u + 255u) & ~255u;
@@ -1756,7 +1773,7 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 	// CTAs per chunk of the heap kernel: enough 8-warp CTAs for the largest FSST chunk's tiles, and one CTA per 32 KiB of
 	// plain bytes (a 9 KiB dictionary is one CTA's work, not 32 CTAs copying 280 bytes each)
 	// (a warp of the heap kernel walks FLSGPU_STR_TILES tiles of the largest chunk as a software pipeline)
-	const uint32_t per_cta = 8u * 32u * L->lane_strings * std::max(1u, env_u32("FLSGPU_STR_TILES", 8));
+	const uint32_t per_cta = 8u * 32u * L->lane_strings * std::max(1u, env_u32("FLSGPU_STR_TILES", 8, 1, 1024));
 	L->groups_per_rg = std::max<uint32_t>(1u, std::max<uint32_t>((max_fsst_strings + per_cta - 1u) / per_cta,
 	                                                            (uint32_t)((max_plain_bytes + 32767u) >> 15)));
 	L->chunk_stride = t->header.n_columns;
@@ -1794,7 +1811,7 @@ int flsgpu_decode_strings(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint
 	L.heap = static_cast<uint8_t*>(heap_dev);
 	L.heap_base_addr = heap_base_addr;
 	L.out = out_strings_dev;
-	L.fuse_rows = env_u32("FLSGPU_STR_FUSE_ROWS", 1);
+	L.fuse_rows = env_u32("FLSGPU_STR_FUSE_ROWS", 1, 0, 1);
 	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
 	FLS_CUDA(fls_str_launch_heap(L, s));
 	FLS_CUDA(fls_str_launch_rows(L, s));
@@ -1934,7 +1951,7 @@ cudaError_t scratch_alloc(void** out, uint64_t bytes, cudaStream_t s) {
 			if (e != cudaSuccess) {
 				return e;
 			}
-			uint64_t keep = (uint64_t)env_u32("FLSGPU_SCRATCH_POOL_MB", 2048) << 20;
+			uint64_t keep = (uint64_t)env_u32("FLSGPU_SCRATCH_POOL_MB", 2048, 0, 1u << 20) << 20;
 			cudaMemPoolSetAttribute(pools[dev], cudaMemPoolAttrReleaseThreshold, &keep);
 		}
 	}
@@ -2024,7 +2041,7 @@ int string_filter_pass_dict(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg
 int string_filter_pass(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg_begin, uint32_t n_rg, const uint8_t* rg_keep_dev,
                        uint32_t* mask_dev, bool and_into, cudaStream_t s) {
 	const uint32_t vpr = t->header.vec_per_rowgroup;
-	bool all_dict = n_rg > 0 && env_u32("FLSGPU_STR_FILTER_DICT", 1) != 0;
+	bool all_dict = n_rg > 0 && env_u32("FLSGPU_STR_FILTER_DICT", 1, 0, 1) != 0;
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg && all_dict; ++r) {
 		all_dict = is_dict_string_enc(t->chunk(r, f.col).encoding);
 	}
@@ -2032,7 +2049,7 @@ int string_filter_pass(flsgpu_table* t, const flsgpu_filter& f, uint32_t rg_begi
 		return string_filter_pass_dict(t, f, rg_begin, n_rg, rg_keep_dev, mask_dev, and_into, s);
 	}
 	const uint64_t rows_per_rg = (uint64_t)vpr * FLS_VEC_SZ * 16u;
-	const uint64_t budget = (uint64_t)env_u32("FLSGPU_STR_FILTER_SLAB_MB", 512) << 20;
+	const uint64_t budget = (uint64_t)env_u32("FLSGPU_STR_FILTER_SLAB_MB", 512, 1, 65536) << 20;
 	// slabs: as many row groups as fit the budget (rows + heap), at least one
 	std::vector<std::pair<uint32_t, uint32_t>> slabs; // (first row group, count)
 	std::vector<uint64_t> slab_heap;
@@ -2291,7 +2308,7 @@ int flsgpu_aggregate_to_host(flsgpu_table* t, const uint32_t* col_ids, uint32_t 
 			return rc;
 		}
 	}
-	const uint32_t slab_rg = std::max(1u, std::min(n_rg, env_u32("FLSGPU_AGG_SLAB_RG", 64)));
+	const uint32_t slab_rg = std::max(1u, std::min(n_rg, env_u32("FLSGPU_AGG_SLAB_RG", 64, 1, 65535)));
 	const uint64_t res_bytes = ((uint64_t)n_cols * sizeof(flsgpu_agg_result) + 255u) & ~255ull;
 	const uint64_t mask_bytes = n_filters ? (uint64_t)slab_rg * h.vec_per_rowgroup * 128u : 0u;
 	const uint64_t keep_bytes = n_filters ? ((uint64_t)slab_rg + 255u) & ~255ull : 0u;

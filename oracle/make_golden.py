@@ -31,10 +31,9 @@ def load_ref():
     l.ref_alp_encode_f32.argtypes = [C.c_float, C.c_int, C.c_int]
     l.ref_alp_impossible_f64.argtypes = [C.c_double]
     l.ref_alp_impossible_f32.argtypes = [C.c_float]
-    l.ref_alprd_glue_u64.restype = C.c_uint64
-    l.ref_alprd_glue_u64.argtypes = [C.c_uint16, C.c_uint64, C.c_int]
-    l.ref_alprd_glue_u32.restype = C.c_uint32
-    l.ref_alprd_glue_u32.argtypes = [C.c_uint16, C.c_uint32, C.c_int]
+    for name in ("ref_alprd_decompress_u64", "ref_alprd_decompress_u32"):
+        getattr(l, name).restype = None
+        getattr(l, name).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
     return l
 
 
@@ -86,7 +85,8 @@ def alprd_container(l, bits, seed):
     ch = t.chunk(0, 0)
     meta = np.frombuffer(img, dtype=META_DT, count=ch.n_vec, offset=ch.offset + ch.seg_off[0])
     data0 = ch.offset + ch.seg_off[1]
-    glue = l.ref_alprd_glue_u64 if bits == 64 else l.ref_alprd_glue_u32
+    decompress = l.ref_alprd_decompress_u64 if bits == 64 else l.ref_alprd_decompress_u32
+    rd_dict = np.array([int(k) for k in ch.rd_dict], dtype=np.uint16)
     expected = np.zeros(2048, dtype=udt)
     for v in range(ch.n_vec):
         m = meta[v]
@@ -94,12 +94,21 @@ def alprd_container(l, bits, seed):
         right = oracle_lib.unpack(np.frombuffer(img, dtype=np.uint8, count=128 * int(m["width"]), offset=blob), bits, int(m["width"]))
         left = oracle_lib.unpack(np.frombuffer(img, dtype=np.uint8, count=128 * int(m["width2"]), offset=blob + 128 * int(m["width"])),
                                  bits, int(m["width2"]))
-        out = np.array([glue(int(ch.rd_dict[int(c) & 7]), int(rt), int(m["width"])) for c, rt in zip(left, right)], dtype=udt)
         n = int(m["aux_cnt"])  # exception tail of the blob: [n whole words, padded to 16 B][n u16 positions]
         tail = blob + 128 * (int(m["width"]) + int(m["width2"]))
         exc_vals = np.frombuffer(img, dtype=udt, count=n, offset=tail)
-        exc_pos = np.frombuffer(img, dtype=np.uint16, count=n, offset=tail + (n * (bits // 8) + 15) // 16 * 16)
-        out[exc_pos] = exc_vals
+        exc_pos = np.ascontiguousarray(np.frombuffer(img, dtype=np.uint16, count=n, offset=tail + (n * (bits // 8) + 15) // 16 * 16))
+        # the reference keeps an exception's LEFT part (alprd.hpp:229-234); the container keeps the whole word, whose right
+        # part is the packed one: the left part is what sits above right_bit_width
+        assert np.array_equal(exc_vals & udt((1 << int(m["width"])) - 1), np.asarray(right, dtype=udt)[exc_pos])
+        exc_left = np.ascontiguousarray((exc_vals >> udt(int(m["width"]))).astype(np.uint16))
+        left16 = np.ascontiguousarray((np.asarray(left) & 7).astype(np.uint16))
+        right_u = np.ascontiguousarray(np.asarray(right, dtype=udt))
+        out = np.zeros(1024, dtype=udt)
+        # AlpRDDecompression<T>::Decompress of the reference tree, unchanged (oracle/ref_alp.cpp packs the parts with DuckDB's
+        # BitpackingPrimitives first: that is the layout it unpacks)
+        decompress(left16.ctypes.data, right_u.ctypes.data, 1024, rd_dict.ctypes.data, exc_left.ctypes.data, exc_pos.ctypes.data, n,
+                   int(m["width2"]), int(m["width"]), out.ctypes.data)
         expected[v * 1024:(v + 1) * 1024] = out
     t.close()
     assert expected.tobytes() == x.tobytes(), "reference glue over the container's parts must reproduce the input"

@@ -29,6 +29,19 @@ bool Value::IsFinite(double input) {
 }
 } // namespace duckdb
 
+// AlpRDDecompression<T>::Decompress itself (alprd.hpp:203-236) over one vector: the left codes and right parts are packed
+// with DuckDB's own BitpackingPrimitives (the layout Decompress unpacks), then the reference's decompression runs unchanged:
+// bit-unpacking, dictionary lookup, glue, exception patching.  exc_left = the exceptions' left parts (alprd.hpp:229-234).
+template <class T, class EXACT>
+static void alprd_decompress(const uint16_t* left_codes, const EXACT* right_parts, int n, const uint16_t* dict, const uint16_t* exc_left,
+                             const uint16_t* exc_pos, int n_exc, int left_bw, int right_bw, EXACT* out) {
+	std::vector<uint8_t> left_packed(AlpRDConstants::ALP_VECTOR_SIZE * 8 + 1024, 0), right_packed(AlpRDConstants::ALP_VECTOR_SIZE * 8 + 1024, 0);
+	BitpackingPrimitives::PackBuffer<uint16_t>(left_packed.data(), const_cast<uint16_t*>(left_codes), (idx_t)n, (bitpacking_width_t)left_bw);
+	BitpackingPrimitives::PackBuffer<EXACT>(right_packed.data(), const_cast<EXACT*>(right_parts), (idx_t)n, (bitpacking_width_t)right_bw);
+	alp::AlpRDDecompression<T>::Decompress(left_packed.data(), right_packed.data(), dict, out, (idx_t)n, (uint16_t)n_exc, exc_left, exc_pos,
+	                                       (uint8_t)left_bw, (uint8_t)right_bw);
+}
+
 extern "C" {
 
 // alp.hpp:129-134
@@ -51,12 +64,13 @@ int ref_alp_impossible_f64(double v) {
 int ref_alp_impossible_f32(float v) {
 	return alp::AlpCompression<float, true>::IsImpossibleToEncode(v);
 }
-// alprd.hpp:222-226: (left << right_bit_width) | right
-uint64_t ref_alprd_glue_u64(uint16_t left, uint64_t right, int right_bw) {
-	return (static_cast<uint64_t>(left) << right_bw) | right;
+void ref_alprd_decompress_u64(const uint16_t* left_codes, const uint64_t* right_parts, int n, const uint16_t* dict, const uint16_t* exc_left,
+                              const uint16_t* exc_pos, int n_exc, int left_bw, int right_bw, uint64_t* out) {
+	alprd_decompress<double, uint64_t>(left_codes, right_parts, n, dict, exc_left, exc_pos, n_exc, left_bw, right_bw, out);
 }
-uint32_t ref_alprd_glue_u32(uint16_t left, uint32_t right, int right_bw) {
-	return (static_cast<uint32_t>(left) << right_bw) | right;
+void ref_alprd_decompress_u32(const uint16_t* left_codes, const uint32_t* right_parts, int n, const uint16_t* dict, const uint16_t* exc_left,
+                              const uint16_t* exc_pos, int n_exc, int left_bw, int right_bw, uint32_t* out) {
+	alprd_decompress<float, uint32_t>(left_codes, right_parts, n, dict, exc_left, exc_pos, n_exc, left_bw, right_bw, out);
 }
 int ref_alprd_max_dict_size() {
 	return AlpRDConstants::MAX_DICTIONARY_SIZE;
