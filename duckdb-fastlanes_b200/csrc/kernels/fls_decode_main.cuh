@@ -586,6 +586,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, min_ctas_per_sm<MODE, T, AG
 			const uint32_t voff = ((((uint32_t)k >> cs) * n_warps) << cs) + ((uint32_t)k & cmask);
 			const uint64_t vk = vbase + voff;
 			uint8_t* out_vec = AGG ? tile : out_batch + (size_t)voff * (1024u * OB);
+			if constexpr (!AGG) {
+				if (L.map_in_place) { // a family's vector list: the vector lands where it belongs in the column
+					const uint32_t r = (uint32_t)(d.ch - L.chunks) / L.chunk_stride;
+					out_vec = out + ((size_t)r * L.vec_per_rg + (d.vec_in_chunk & 0xffffu)) * (1024u * OB);
+				}
+			}
 			(void)vk;
 			const uint8_t* sp = slots + (size_t)slot * L.slot_bytes;
 			// aggregate fast path: complete vector, no exceptions, an encoding whose values end up in registers

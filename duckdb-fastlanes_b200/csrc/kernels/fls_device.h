@@ -61,6 +61,9 @@ struct FlsLaunch {
 	// compact scans (flsgpu_scan_column.compact): the launch walks total_vecs LISTED vectors, vec_map[k] = vector index inside
 	// the range of the k-th one, whose values land at slot k of the output; nullptr = every vector of the range, in place
 	const uint32_t* vec_map;
+	// 1: the listed vectors are decoded IN PLACE (output position = the vector's own index inside the range, not its slot in the
+	// list): launches of a column whose chunks fall into several kernel families walk only their own family's vectors
+	uint32_t map_in_place;
 };
 
 // Launch parameters of the string kernels (flsgpu_kernels_str.cu): column `col` of row groups [rg_begin, rg_begin + n_rg).

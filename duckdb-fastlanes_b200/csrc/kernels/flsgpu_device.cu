@@ -71,6 +71,7 @@ const uint32_t g_budget_kb = env_u32("FLSGPU_WARP_KB", 18, 4, 27);     // shared
 // per 128 M values (measured; low-cardinality dictionaries are unaffected)
 const uint32_t g_dict_run_shift = std::min(5u, env_u32("FLSGPU_DICT_RUN_SHIFT", 3, 0, 5));
 const uint32_t g_dict_kb = env_u32("FLSGPU_DICT_KB", 6, 2, 27);
+const uint32_t g_kind_maps = env_u32("FLSGPU_KIND_MAPS", 1, 0, 1); // per-kind vector lists for columns that mix kernel families
 const uint32_t g_swar8_kb = env_u32("FLSGPU_SWAR8_KB", 8, 2, 27);      // same for the 8-bit SWAR kernel (48 registers: up to five resident CTAs per SM)
 
 int cuda_fail(cudaError_t e, const char* where) {
@@ -142,6 +143,12 @@ struct FlsColumnPlan { // what a decode launch over (col, rg range) needs to kno
 	bool has_rle = false, has_dict[3] = {false, false, false};
 	bool main_needs_stage = false;
 	uint32_t main_slot[5] = {0, 0, 0, 0, 0}, rle_slot = 0, dict_slot[3] = {0, 0, 0};
+	// Columns whose chunks fall into several launch kinds (main families 0..4, DICT by code width 5..7, RLE 8): the vectors of
+	// every kind, listed on the device, so that a kind's launch walks its own vectors only (a launch over the whole range spends
+	// a descriptor fetch on every vector of the other kinds: the ALP_RD launch of the bench's DOUBLE column took 20 us to write
+	// 0.07 MB).  nullptr: the launch walks the range.
+	const uint32_t* kind_map[9] = {};
+	uint32_t kind_n[9] = {};
 };
 
 struct FlsScanScratch { // two streams + two device slabs: H2D / decode / D2H of neighbouring slabs overlap
@@ -179,6 +186,8 @@ struct FlsDeviceState {
 	bool host_pinned_tried = false;
 	bool host_registered = false;
 	std::map<std::tuple<uint32_t, uint32_t, uint32_t>, FlsColumnPlan> plans;
+	std::vector<void*> plan_maps; // device blocks behind FlsColumnPlan::kind_map: freed with the table (launches may be in flight)
+	uint64_t plan_map_bytes = 0;
 	// pipelined scans (flsgpu_scan_columns_to_host): one scratch per concurrent caller, recycled through a free list
 	std::vector<FlsScanScratch*> scratch_all, scratch_free;
 	std::mutex mu;
@@ -201,6 +210,9 @@ void fls_device_release(flsgpu_table* t) {
 		}
 		cudaFreeHost(sc->count_host);
 		delete sc;
+	}
+	for (void* p : d->plan_maps) {
+		cudaFree(p);
 	}
 	cudaFree(d->d_image);
 	cudaFree(d->d_chunks);
@@ -463,16 +475,21 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 		return it->second;
 	}
 	FlsColumnPlan p;
+	std::vector<uint8_t> kind_of(n_rg); // launch kind of every row group's chunk
+	uint32_t kinds_seen = 0;
 	for (uint32_t r = rg_begin; r < rg_begin + n_rg; ++r) {
 		const fls_chunk_desc& c = t->chunk(r, col);
 		const uint32_t bytes = blob_bytes_max(c);
+		int kind;
 		if (c.encoding == FLS_ENC_DICT) {
 			const int k = c.idx_bits == 8 ? 0 : c.idx_bits == 16 ? 1 : 2;
 			p.has_dict[k] = true;
 			p.dict_slot[k] = std::max(p.dict_slot[k], bytes);
+			kind = 5 + k;
 		} else if (c.encoding == FLS_ENC_RLE) {
 			p.has_rle = true;
 			p.rle_slot = std::max(p.rle_slot, bytes);
+			kind = 8;
 		} else {
 			const int f = c.encoding == FLS_ENC_ALP ? 1 : c.encoding == FLS_ENC_ALP_RD ? 2
 			              : (c.encoding == FLS_ENC_DELTA && c.phys_bits == 64) ? 3
@@ -480,10 +497,45 @@ const FlsColumnPlan& plan_for(flsgpu_table* t, FlsDeviceState* d, uint32_t col, 
 			p.has_main[f] = true;
 			p.main_slot[f] = std::max(p.main_slot[f], bytes);
 			p.main_needs_stage |= c.encoding == FLS_ENC_DELTA;
+			kind = f;
+		}
+		kind_of[r - rg_begin] = (uint8_t)kind;
+		kinds_seen |= 1u << kind;
+	}
+	// several kinds in the range: list every kind's vectors on the device (one block; bounded per table: past the bound the
+	// launches simply walk the whole range as before)
+	const uint64_t map_bytes = (uint64_t)n_rg * t->header.vec_per_rowgroup * 4u;
+	if ((kinds_seen & (kinds_seen - 1u)) != 0 && g_kind_maps && d->plan_map_bytes + map_bytes <= (256ull << 20)) {
+		std::vector<uint32_t> all;
+		all.reserve((size_t)n_rg * t->header.vec_per_rowgroup);
+		uint32_t first[9] = {};
+		for (int k = 0; k < 9; ++k) {
+			first[k] = (uint32_t)all.size();
+			for (uint32_t r = 0; r < n_rg && ((kinds_seen >> k) & 1u); ++r) {
+				if (kind_of[r] == k) {
+					const uint32_t nv = t->chunk(rg_begin + r, col).n_vec;
+					for (uint32_t v = 0; v < nv; ++v) {
+						all.push_back(r * t->header.vec_per_rowgroup + v);
+					}
+				}
+			}
+			p.kind_n[k] = (uint32_t)all.size() - first[k];
+		}
+		void* block = nullptr;
+		if (!all.empty() && cudaMalloc(&block, all.size() * 4u) == cudaSuccess &&
+		    cudaMemcpy(block, all.data(), all.size() * 4u, cudaMemcpyHostToDevice) == cudaSuccess) {
+			d->plan_maps.push_back(block);
+			d->plan_map_bytes += all.size() * 4u;
+			for (int k = 0; k < 9; ++k) {
+				p.kind_map[k] = p.kind_n[k] ? static_cast<const uint32_t*>(block) + first[k] : nullptr;
+			}
+		} else {
+			cudaGetLastError();
+			cudaFree(block);
 		}
 	}
 	if (d->plans.size() > 4096) {
-		d->plans.clear();
+		d->plans.clear(); // the device blocks of the dropped plans stay until the table closes: launches may still read them
 	}
 	return d->plans.emplace(key, p).first->second;
 }
@@ -690,7 +742,17 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	// FLOAT columns that mix ALP and ALP_RD chunks: one launch of the instantiation that carries both (same 128-register
 	// budget as the ALP_RD kernel alone) instead of two launches with their ramp and tail
 	const bool fuse_alp = T == 32 && !agg_family && p.has_main[1] && p.has_main[2];
+	// a column that mixes launch kinds: every launch walks the list of its own vectors and decodes them in place
+	const uint32_t range_vecs = L.total_vecs;
+	const bool use_maps = !vec_map_dev && !agg_family;
+	auto walk = [&](int kind) {
+		const bool mapped = use_maps && kind >= 0 && p.kind_map[kind] != nullptr;
+		L.vec_map = mapped ? p.kind_map[kind] : vec_map_dev;
+		L.total_vecs = mapped ? p.kind_n[kind] : range_vecs;
+		L.map_in_place = mapped ? 1u : 0u;
+	};
 	if (fuse_alp) {
+		walk(-1);
 		L.family_mask = fam_mask[1] | fam_mask[2];
 		L.idx_bits = 0;
 		rc = launch_family(d, fls_kernel_main(T, os.ob, 5), L, std::max(p.main_slot[1], p.main_slot[2]), 0u, stream, tile);
@@ -701,6 +763,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 		}
 		const bool fold4 = f == 0 && p.has_main[4] && !use_swar8;
 		if ((f == 4 ? use_swar8 : p.has_main[f]) || fold4) {
+			walk(fold4 ? -1 : f); // a launch that also takes the 8-bit family's chunks walks the range
 			L.family_mask = fam_mask[f];
 			L.idx_bits = 0;
 			// DELTA needs the per-warp transposition area (+ 16 lane totals for T = 64); the SWAR kernel stores from registers
@@ -713,6 +776,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {
 		if (p.has_dict[k]) {
 			const int it = 8 << k;
+			walk(5 + k);
 			L.family_mask = FLS_FAMILY_DICT;
 			L.idx_bits = (uint32_t)it;
 			L.run_shift = g_dict_run_shift;
@@ -722,6 +786,7 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 	}
 	L.run_shift = g_run_shift;
 	if (p.has_rle && rc == FLSGPU_OK) {
+		walk(8);
 		L.family_mask = FLS_FAMILY_RLE;
 		L.idx_bits = 0;
 		rc = launch_family(d, agg_family ? fls_kernel_agg(2, 16, T, 0) : fls_kernel_rle(T, os.ob), L, p.rle_slot, 2048u, stream, tile);

@@ -205,7 +205,10 @@ typedef struct flsgpu_agg_result { /* written to device memory, 64 bytes */
 	double fsum;      /* FLOAT/DOUBLE columns: sum in double (not order-stable, reported only) */
 	uint64_t reserved[2];
 } flsgpu_agg_result;
-/* Accumulates into *result_dev (caller zero-initialises with flsgpu_agg_reset). Asynchronous. */
+/* Accumulates into *result_dev (caller zero-initialises with flsgpu_agg_reset). Asynchronous.  SUM / COUNT are folded by the
+ * kernels; min_val / max_val are merged from the zone maps of the chunks in the range (fls_chunk_desc.has_stats, min_val,
+ * max_val: exact, written from the data; integer columns): they cover the chunks that carry statistics - a caller that needs
+ * MIN / MAX of the whole range checks has_stats of its chunks first (the aggregate pushdown of the extension does). */
 int flsgpu_aggregate_column(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg,
                             flsgpu_agg_result* result_dev, void* cuda_stream);
 int flsgpu_agg_reset(flsgpu_agg_result* result_dev, void* cuda_stream);

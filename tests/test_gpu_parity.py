@@ -229,3 +229,44 @@ def test_alp_golden_vectors_on_gpu():
         got = gpu_decode(t, 0, 0, udt)
         assert got[:2048].tobytes() == g[f"rd{bits}_expected"].tobytes()
         t.close()
+
+
+@pytest.mark.parametrize("dtype,tname", [(np.int64, "INT64"), (np.int32, "INT32"), (np.int16, "INT16"), (np.int8, "INT8"), (np.float64, "DOUBLE"),
+                                         (np.float32, "FLOAT")])
+def test_columns_that_mix_kernel_families(dtype, tname):
+    """A column whose row groups fall into several launch kinds (light, 64-bit DELTA, DICT by code width, RLE, ALP, ALP_RD): every
+    kind's launch walks the device list of its own vectors and decodes them in place (FlsColumnPlan::kind_map) - whole range,
+    sub-ranges, widened output: always the input, always the oracle."""
+    vpr, rows = 4, 4 * 1024
+    r = np.random.default_rng(3)
+    info = np.iinfo(dtype) if np.dtype(dtype).kind == "i" else None
+    parts = []
+    for rg in range(14):
+        k = rg % 7
+        if np.dtype(dtype).kind == "f":
+            x = [np.round(r.random(rows) * 100, 2), r.random(rows) * 2 - 1, np.repeat(r.random(rows // 64), 64), np.full(rows, 2.5),
+                 np.round(r.random(rows) * 1e6, 1), (r.random(rows) - 0.5) * 1e30, np.repeat(np.round(r.random(rows // 256), 3), 256)][k]
+        else:
+            hi = min(int(info.max), 1 << 40)
+            x = [r.integers(0, hi, rows), np.sort(r.integers(0, hi, rows)), np.repeat(r.integers(0, hi, rows // 128), 128),
+                 r.integers(0, 3, rows) * (hi // 3), np.full(rows, 7), np.arange(rows) * 3 % 100, r.choice(r.integers(0, hi, 300), rows)][k]
+        parts.append(np.asarray(x).astype(dtype))
+    col = np.concatenate(parts)[:14 * rows - 700]  # partial last row group
+    img = flsgpu.write_table([("x", tname, None)], [col], vec_per_rowgroup=vpr)
+    t = flsgpu.Table(img)
+    kinds = {flsgpu.ENC_NAME[t.chunk(rg, 0).encoding] for rg in range(t.n_rowgroups)}
+    assert len(kinds) >= 3, kinds
+    o = oracle_lib.Oracle(img)
+    dt = np.dtype(dtype)
+    wide = np.dtype(np.float64) if dt.kind == "f" else np.dtype(np.int64)
+    t.stage()
+    for rg_begin, n_rg in ((0, t.n_rowgroups), (3, 6), (5, 1), (t.n_rowgroups - 2, 2)):
+        for out_type, odt in ((0, dt), (flsgpu.OUT[_NAME_OF[wide]], wide)):
+            exp = o.decode_column(0, rg_begin, n_rg, out_type, odt, t.vec_per_rowgroup)
+            got = gpu_decode(t, 0, out_type, odt, rg_begin, n_rg)
+            for a, b in t.valid_mask_slices(rg_begin, n_rg):
+                assert got[a:b].tobytes() == exp[a:b].tobytes(), (kinds, rg_begin, n_rg, out_type)
+    got = gpu_decode(t, 0, 0, dt)
+    flat = np.concatenate([got[a:b] for a, b in t.valid_mask_slices()])
+    assert flat.tobytes() == col.tobytes()
+    t.close()
