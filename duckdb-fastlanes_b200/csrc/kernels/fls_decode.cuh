@@ -74,7 +74,12 @@ static_assert(kDescBytesPerWarp == FLS_DESC_BYTES_PER_WARP, "launcher and kernel
 
 // where quad j of descriptor k sits inside the descriptor's 64 bytes (see store_desc)
 __device__ __forceinline__ uint32_t desc_quad(int k, int j) {
+#ifdef FLS_DESC_PLAIN
+	(void)k;
+	return (uint32_t)j;
+#else
 	return (uint32_t)(j ^ ((k >> 1) & 3));
+#endif
 }
 
 __device__ __forceinline__ void store_desc(uint8_t* descs, int lane, const VecDesc& d) {
@@ -84,7 +89,7 @@ __device__ __forceinline__ void store_desc(uint8_t* descs, int lane, const VecDe
 	// quad j of lane's descriptor sits at quad j ^ x, x = (lane >> 1) & 3: the 8 lanes of a quarter warp (the unit a 128-bit
 	// shared store is checked in) then hit 8 different 16-byte bank groups instead of two (stride 64 B: 4-way conflicts, ncu
 	// 12 excessive wavefronts per store)
-	const int x = (lane >> 1) & 3;
+	const int x = (int)desc_quad(lane, 0);
 	p[0 ^ x] = make_uint4((uint32_t)blob, (uint32_t)(blob >> 32), (uint32_t)d.base, (uint32_t)(d.base >> 32));
 	p[1 ^ x] = make_uint4(d.bytes, d.misc, d.misc2, d.vec_in_chunk);
 	p[2 ^ x] = make_uint4((uint32_t)a0, (uint32_t)(a0 >> 32), (uint32_t)a1, (uint32_t)(a1 >> 32));
@@ -93,7 +98,7 @@ __device__ __forceinline__ void store_desc(uint8_t* descs, int lane, const VecDe
 
 __device__ __forceinline__ VecDesc load_desc(const uint8_t* descs, int k) {
 	const uint4* p = reinterpret_cast<const uint4*>(descs + (size_t)k * kDescBytes);
-	const int x = (k >> 1) & 3;
+	const int x = (int)desc_quad(k, 0);
 	const uint4 q0 = p[0 ^ x], q1 = p[1 ^ x], q2 = p[2 ^ x], q3 = p[3 ^ x];
 	VecDesc r;
 	r.blob = (const uint8_t*)(((unsigned long long)q0.y << 32) | q0.x);
