@@ -514,6 +514,62 @@ int flsgpu_table_info_get(const flsgpu_table* t, flsgpu_table_info* out) {
 	return FLSGPU_OK;
 }
 
+// Statistics of a string column for the host database's optimizer, where they come cheap: chunks whose distinct strings sit
+// uncompressed in AUX0 (DICT_STR dictionaries, STR_CONSTANT, the value strings of RLE_STR / CROSS_RLE_STR / FREQUENCY_STR) are
+// summarised from those few strings; any other chunk (one string per row, or an FSST-compressed dictionary) makes the
+// statistics unavailable rather than costing a decode of the column.
+int flsgpu_column_string_stats(const flsgpu_table* t, uint32_t col, flsgpu_string_stats* out) {
+	if (!t || !out || col >= t->header.n_columns || t->columns[col].phys_bits != 128) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_column_string_stats: null argument or not a string column");
+	}
+	flsgpu_string_stats st {};
+	const uint8_t *min_p = nullptr, *max_p = nullptr;
+	uint32_t min_n = 0, max_n = 0;
+	auto less = [](const uint8_t* a, uint32_t an, const uint8_t* b, uint32_t bn) { // bytewise, the shorter first on a tie
+		const int c = std::memcmp(a, b, std::min(an, bn));
+		return c < 0 || (c == 0 && an < bn);
+	};
+	auto take = [&](const uint8_t* p, uint32_t n) {
+		st.max_length = std::max(st.max_length, n);
+		for (uint32_t i = 0; i < n && !st.has_non_ascii; ++i) {
+			st.has_non_ascii = p[i] >= 0x80u;
+		}
+		if (!min_p || less(p, n, min_p, min_n)) {
+			min_p = p;
+			min_n = n;
+		}
+		if (!max_p || less(max_p, max_n, p, n)) {
+			max_p = p;
+			max_n = n;
+		}
+	};
+	for (uint32_t r = 0; r < t->header.n_rowgroups; ++r) {
+		const fls_chunk_desc& ch = t->chunk(r, col);
+		const uint8_t* aux0 = t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX0];
+		const uint32_t* ends = reinterpret_cast<const uint32_t*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX1]);
+		if (ch.encoding == FLS_ENC_STR_CONSTANT) {
+			take(aux0, ch.aux_count);
+		} else if (ch.encoding == FLS_ENC_DICT_STR || FLS_ENC_IS_STR_VALUES(ch.encoding)) {
+			for (uint32_t k = 0; k < ch.aux_count; ++k) {
+				const uint32_t start = k ? ends[k - 1] : 0u;
+				take(aux0 + start, ends[k] - start);
+			}
+		} else {
+			*out = flsgpu_string_stats {};
+			return FLSGPU_OK; // available = 0
+		}
+	}
+	if (min_p) {
+		st.available = 1;
+		st.min_length = std::min(min_n, 8u);
+		st.max_value_length = std::min(max_n, 8u);
+		std::memcpy(st.min_value, min_p, st.min_length);
+		std::memcpy(st.max_value, max_p, st.max_value_length);
+	}
+	*out = st;
+	return FLSGPU_OK;
+}
+
 // Vector forms (fls_format.h FLS_VEC_FORM_*): read off the entry points, no decode.
 int flsgpu_column_vector_forms(const flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32_t n_rg, flsgpu_vector_form* out,
                                uint64_t* n_flat) {

@@ -329,6 +329,22 @@ unique_ptr<BaseStatistics> FastLanesReader::GetStatistics(ClientContext &, const
 		return stats.ToUnique();
 	}
 	if (type.id() == LogicalTypeId::VARCHAR) {
+		// dictionary-encoded columns: longest string, min / max prefix and the ASCII flag come from the dictionaries (a few
+		// strings per row group) - what DuckDB's compressed materialization needs to turn GROUP BY l_returnflag, l_linestatus
+		// into a perfect hash aggregate over one-byte keys, as it does over its own tables
+		flsgpu_string_stats summary {};
+		if (file_col_idx < info.n_columns && flsgpu_column_string_stats(table, NumericCast<uint32_t>(file_col_idx), &summary) == FLSGPU_OK &&
+		    summary.available) {
+			auto stats = StringStats::CreateEmpty(type);
+			StringStats::Update(stats, string_t(const_char_ptr_cast(summary.min_value), summary.min_length));
+			StringStats::Update(stats, string_t(const_char_ptr_cast(summary.max_value), summary.max_value_length));
+			StringStats::SetMaxStringLength(stats, summary.max_length);
+			if (summary.has_non_ascii) {
+				StringStats::SetContainsUnicode(stats);
+			}
+			stats.Set(StatsInfo::CANNOT_HAVE_NULL_VALUES);
+			return stats.ToUnique();
+		}
 		auto stats = StringStats::CreateUnknown(type);
 		stats.Set(StatsInfo::CANNOT_HAVE_NULL_VALUES);
 		return stats.ToUnique();

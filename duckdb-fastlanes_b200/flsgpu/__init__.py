@@ -127,6 +127,11 @@ class TableInfo(C.Structure):
                 ("reserved", C.c_uint32), ("n_tuples", C.c_uint64), ("n_vectors", C.c_uint64), ("file_bytes", C.c_uint64)]
 
 
+class StringStats(C.Structure):  # flsgpu_string_stats
+    _fields_ = [("available", C.c_uint32), ("max_length", C.c_uint32), ("has_non_ascii", C.c_uint32), ("min_length", C.c_uint32),
+                ("max_value_length", C.c_uint32), ("min_value", C.c_uint8 * 8), ("max_value", C.c_uint8 * 8), ("reserved", C.c_uint32)]
+
+
 class AggResult(C.Structure):
     _fields_ = [("sum_lo", C.c_uint64), ("sum_hi", C.c_uint64), ("count", C.c_uint64), ("min_val", C.c_int64),
                 ("max_val", C.c_int64), ("fsum", C.c_double), ("reserved", C.c_uint64 * 2)]
@@ -156,7 +161,7 @@ ABI_SYMBOLS = [
     "flsgpu_writer_encode_rowgroup", "flsgpu_writer_flush_rowgroup", "flsgpu_encoded_rowgroup_free",
     "flsgpu_writer_set_inline_footer", "flsgpu_writer_rowgroups", "flsgpu_column_vector_forms", "flsgpu_transfer_bytes",
     "flsgpu_n_devices", "flsgpu_table_share", "flsgpu_table_bind_device", "flsgpu_filter_mask_string_dict_static",
-    "flsgpu_aggregate_to_host", "flsgpu_scan_selected_to_host",
+    "flsgpu_aggregate_to_host", "flsgpu_scan_selected_to_host", "flsgpu_column_string_stats",
 ]
 
 
@@ -424,6 +429,14 @@ class Table:
         _check(lib.flsgpu_scan_selected_to_host(self._h, arr, len(scan_columns), make_filters(filters), len(filters), rg_begin, n_rg,
                                                 _vp(row_index_ptr), C.c_uint64(row_index_bytes), C.byref(n_sel)), "scan_selected_to_host")
         return n_sel.value
+
+    def string_stats(self, col):
+        """None, or (max_length, has_non_ascii, min prefix, max prefix) of a string column whose distinct strings sit uncompressed."""
+        st = StringStats()
+        _check(lib.flsgpu_column_string_stats(self._h, col, C.byref(st)), "column_string_stats")
+        if not st.available:
+            return None
+        return st.max_length, bool(st.has_non_ascii), bytes(st.min_value[:st.min_length]), bytes(st.max_value[:st.max_value_length])
 
     def vector_forms(self, col, rg_begin=0, n_rg=None):
         """(forms: structured array of VECTOR_FORM per vector of the range, n_flat)."""

@@ -110,6 +110,23 @@ int flsgpu_table_column(const flsgpu_table* t, uint32_t col, fls_column_desc* ou
 int flsgpu_table_rowgroup(const flsgpu_table* t, uint32_t rg, fls_rowgroup_desc* out);         /* fls_reader.cpp:129-138 */
 int flsgpu_table_chunk(const flsgpu_table* t, uint32_t rg, uint32_t col, fls_chunk_desc* out); /* row_group_statistics.cpp:60-127 */
 
+/* String statistics for the host database's optimizer (DuckDB StringStats: the reference reports none for VARCHAR columns,
+ * row_group_statistics.cpp:60-127 covers numeric types): longest string, whether any byte is >= 0x80, and the first 8 bytes of
+ * the smallest / greatest string (bytewise order, the shorter first on a tie).  available = 0 unless every chunk of the column
+ * keeps its distinct strings uncompressed (DICT_STR, STR_CONSTANT, RLE_STR, CROSS_RLE_STR, FREQUENCY_STR): the summary then
+ * costs a walk over those few strings, never a decode.  Host only. */
+typedef struct flsgpu_string_stats {
+	uint32_t available;
+	uint32_t max_length;       /* bytes of the longest string */
+	uint32_t has_non_ascii;
+	uint32_t min_length;       /* bytes of min_value that are valid (<= 8) */
+	uint32_t max_value_length; /* bytes of max_value that are valid (<= 8) */
+	uint8_t min_value[8];
+	uint8_t max_value[8];
+	uint32_t reserved;
+} flsgpu_string_stats;
+int flsgpu_column_string_stats(const flsgpu_table* t, uint32_t col, flsgpu_string_stats* out);
+
 /* ---- vector forms: what can be handed to DuckDB without decoding ---------------------------------------------------------- */
 /* The reference hands a dec_constant_opr chunk to DuckDB as a CONSTANT_VECTOR instead of 1024 copies (constant_kernel.hpp:
  * 19-27).  This container records two such facts per vector (fls_format.h FLS_VEC_FORM_*): CONSTANT and arithmetic SEQUENCE
