@@ -82,3 +82,26 @@ def test_writer_buffers_string_rows_across_appends():
         got += flsgpu.strings_from(st[a:b], heap)
     assert got == vals
     t.close()
+
+
+def test_string_statistics_come_from_the_dictionaries():
+    """flsgpu_column_string_stats (host only): longest string, ASCII flag and min / max prefix of columns whose distinct strings
+    sit uncompressed in the container; unavailable - not wrong - for per-row and FSST-compressed encodings."""
+    cs = str_cases.cases(5000)
+    names = list(cs)
+    img = flsgpu.write_table([(k, cs[k][0], cs[k][1]) for k in names], [cs[k][2] for k in names], vec_per_rowgroup=2)
+    t = flsgpu.Table(img)
+    seen = 0
+    for c, k in enumerate(names):
+        encs = {flsgpu.ENC_NAME[t.chunk(r, c).encoding] for r in range(t.n_rowgroups)}
+        st = t.string_stats(c)
+        if encs <= {"DICT_STR", "STR_CONSTANT", "RLE_STR", "CROSS_RLE_STR", "FREQUENCY_STR"}:
+            vals = [bytes(v) for v in cs[k][2]]
+            assert st == (max(len(v) for v in vals), any(b >= 0x80 for v in vals for b in v), min(vals)[:8], max(vals)[:8]), k
+            seen += 1
+        else:
+            assert st is None, (k, encs)
+    assert seen >= 6
+    with pytest.raises(flsgpu.FlsError):
+        flsgpu.Table(flsgpu.write_table([("v", "INT64", None)], [np.arange(10, dtype=np.int64)])).string_stats(0)
+    t.close()
