@@ -9,7 +9,14 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <algorithm>
+#include <atomic>
+#include <unistd.h>
+#include <chrono>
+#include <cstdlib>
 #include <string>
+#include <thread>
+#include <vector>
 
 static thread_local std::string g_last_error;
 
@@ -209,6 +216,131 @@ static const char* validate_string_chunk(const flsgpu_table* t, const fls_chunk_
 	return ch.const_val == dprev ? nullptr : "decoded byte count disagrees with the decoded end offsets";
 }
 
+// Everything about one chunk that opening a table checks: extents, descriptor consistency, per-vector entry points, exception
+// positions, string offsets / FSST streams.  Reads the image only: chunks are validated in parallel (fls_table_parse).
+static const char* validate_chunk(const flsgpu_table* t, uint32_t r, uint32_t c) {
+	const fls_file_header& h = t->header;
+	const fls_rowgroup_desc& rg = t->rowgroups[r];
+	const fls_chunk_desc& ch = t->chunk(r, c);
+	const fls_column_desc& col = t->columns[c];
+	if (ch.offset % FLS_ALIGN || ch.offset > h.footer_offset || ch.size > h.footer_offset - ch.offset) {
+		return "extent outside the data region";
+	}
+	if (ch.encoding >= FLS_ENC_COUNT || ch.phys_bits != col.phys_bits || ch.n_vec != rg.n_vec || ch.n_tuples != rg.n_tuples) {
+		return "descriptor disagrees with the row group / column";
+	}
+	for (int s = 0; s < FLS_SEG_COUNT; ++s) {
+		if (ch.seg_off[s] % FLS_ALIGN || ch.seg_off[s] > ch.size || ch.seg_size[s] > ch.size - ch.seg_off[s]) {
+			return "segment outside the chunk";
+		}
+	}
+	if (ch.is_equal) { // EXP_EQUAL: a copy of an EARLIER column's descriptor of the same row group, never a chain
+		const uint32_t src = ch.equal_col[0] | ((uint32_t)ch.equal_col[1] << 8);
+		if (src >= c || col.phys_bits == 128) {
+			return "EXP_EQUAL must refer to an earlier numeric column";
+		}
+		fls_chunk_desc want = t->chunk(r, src);
+		if (want.is_equal || t->columns[src].phys_bits != col.phys_bits) {
+			return "EXP_EQUAL source is itself a reference or has another physical width";
+		}
+		want.is_equal = 1;
+		want.equal_col[0] = ch.equal_col[0];
+		want.equal_col[1] = ch.equal_col[1];
+		if (std::memcmp(&want, &ch, sizeof(fls_chunk_desc)) != 0) {
+			return "EXP_EQUAL descriptor differs from its source chunk's";
+		}
+	}
+	if (ch.seg_size[FLS_SEG_META] != (uint64_t)ch.n_vec * sizeof(fls_vec_meta)) {
+		return "meta segment has the wrong size";
+	}
+	if (is_string_enc(ch.encoding) != (col.phys_bits == 128)) {
+		return "string encoding on a numeric column or vice versa";
+	}
+	if (col.phys_bits == 128) {
+		const char* why = validate_string_chunk(t, ch);
+		if (why) {
+			return why;
+		}
+		return nullptr;
+	}
+	const unsigned T = ch.phys_bits, esz = T / 8;
+	const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_META]);
+	const bool patched = is_patched(ch.encoding);
+	unsigned lanes_T = T;
+	if (ch.encoding == FLS_ENC_DICT) {
+		lanes_T = ch.idx_bits;
+		if (lanes_T != 8 && lanes_T != 16 && lanes_T != 32) {
+			return "DICT idx_bits must be 8, 16 or 32";
+		}
+		if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.aux_count == 0) {
+			return "dictionary segment has the wrong size";
+		}
+	} else if (ch.encoding == FLS_ENC_RLE) {
+		lanes_T = 16;
+		if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz) {
+			return "run value segment has the wrong size";
+		}
+	} else if (ch.encoding == FLS_ENC_CROSS_RLE) {
+		if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.seg_size[FLS_SEG_AUX1] != (uint64_t)ch.aux_count * 4) {
+			return "CROSS_RLE segments have the wrong size";
+		}
+		const uint32_t* lens = reinterpret_cast<const uint32_t*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX1]);
+		uint64_t sum = 0;
+		for (uint32_t i = 0; i < ch.aux_count; ++i) {
+			sum += lens[i];
+		}
+		if (sum != (uint64_t)ch.n_vec * FLS_VEC_SZ) {
+			return "CROSS_RLE run lengths do not cover the chunk";
+		}
+	}
+	if ((ch.encoding == FLS_ENC_ALP || ch.encoding == FLS_ENC_ALP_RD) && !(col.is_float && T >= 32)) {
+		return "ALP encodings need a FLOAT/DOUBLE column";
+	}
+	const uint8_t* data_seg = t->bytes + ch.offset + ch.seg_off[FLS_SEG_DATA];
+	uint64_t n_exc_seen = 0;
+	for (uint32_t v = 0; v < ch.n_vec; ++v) {
+		const fls_vec_meta& m = meta[v];
+		if (m.width > lanes_T || (ch.encoding == FLS_ENC_ALP_RD && (m.width2 == 0 || m.width2 > 3 || m.width + m.width2 > 64 + 3))) {
+			return "vector bit width out of range";
+		}
+		if ((uint64_t)m.data_off16 * 16 + blob_bytes(ch, m) > ch.seg_size[FLS_SEG_DATA]) {
+			return "vector entry point outside the data segment";
+		}
+		if (blob_bytes(ch, m) > ch.max_blob_bytes) {
+			return "vector blob larger than the chunk's max_blob_bytes";
+		}
+		if (m.n_valid == 0 || m.n_valid > FLS_VEC_SZ) {
+			return "vector n_valid out of range";
+		}
+		if (m.aux_cnt > FLS_VEC_SZ || (!patched && ch.encoding != FLS_ENC_RLE && m.aux_cnt != 0)) {
+			return "vector exception/run count out of range";
+		}
+		if (ch.encoding == FLS_ENC_RLE && (uint64_t)m.aux_off + m.aux_cnt > ch.aux_count) {
+			return "vector run range outside the run value segment";
+		}
+		if (patched && m.aux_cnt) {
+			const uint16_t* exc_pos = reinterpret_cast<const uint16_t*>(data_seg + (uint64_t)m.data_off16 * 16 + packed_bytes(ch, m) +
+			                                                            FLS_PAD16((uint32_t)m.aux_cnt * esz));
+			for (uint32_t k = 0; k < m.aux_cnt; ++k) {
+				if (exc_pos[k] >= FLS_VEC_SZ) {
+					return "exception position out of range";
+				}
+			}
+			n_exc_seen += m.aux_cnt;
+		}
+		if (ch.encoding == FLS_ENC_ALP && (m.e > (T == 64 ? 18 : 10) || m.f > m.e)) {
+			return "ALP exponent/factor out of range";
+		}
+		if (ch.encoding == FLS_ENC_RLE && m.aux_cnt == 0) {
+			return "RLE vector without runs";
+		}
+	}
+	if (patched && n_exc_seen != ch.aux_count) {
+		return "exception count disagrees with the chunk descriptor";
+	}
+	return nullptr;
+}
+
 int fls_table_parse(flsgpu_table* t) {
 	char msg[256];
 	if (t->size < sizeof(fls_file_header)) {
@@ -264,129 +396,59 @@ int fls_table_parse(flsgpu_table* t) {
 		}
 		tuples += rg.n_tuples;
 		t->n_vectors += rg.n_vec;
-		for (uint32_t c = 0; c < h.n_columns; ++c) {
-			const fls_chunk_desc& ch = t->chunk(r, c);
-			const fls_column_desc& col = t->columns[c];
-			std::snprintf(msg, sizeof(msg), "chunk (rg %u, col %u): ", r, c);
-			const size_t ml = std::strlen(msg);
-			auto fail = [&](const char* what) {
-				std::snprintf(msg + ml, sizeof(msg) - ml, "%s", what);
-				return fls_set_error(FLSGPU_ERR_INVALID, msg);
-			};
-			if (ch.offset % FLS_ALIGN || ch.offset > h.footer_offset || ch.size > h.footer_offset - ch.offset) {
-				return fail("extent outside the data region");
-			}
-			if (ch.encoding >= FLS_ENC_COUNT || ch.phys_bits != col.phys_bits || ch.n_vec != rg.n_vec || ch.n_tuples != rg.n_tuples) {
-				return fail("descriptor disagrees with the row group / column");
-			}
-			for (int s = 0; s < FLS_SEG_COUNT; ++s) {
-				if (ch.seg_off[s] % FLS_ALIGN || ch.seg_off[s] > ch.size || ch.seg_size[s] > ch.size - ch.seg_off[s]) {
-					return fail("segment outside the chunk");
+	}
+	// The per-chunk checks walk every entry point, exception list and FSST code stream - O(compressed bytes): 0.29 s for a
+	// 196 MB SF1 lineitem on one core.  Row groups are independent, so they are spread over the host's cores; the first
+	// failure in (row group, column) order is the one reported.
+	{
+		const unsigned n_threads = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>({(uint64_t)std::thread::hardware_concurrency(), 32u,
+		                                                                                 (uint64_t)h.n_rowgroups, h.footer_offset >> 22}));
+		std::atomic<uint32_t> next {0};
+		std::atomic<uint64_t> first_bad {~0ull};
+		std::vector<const char*> why(n_threads, nullptr);
+		std::vector<uint64_t> where(n_threads, ~0ull);
+		auto work = [&](unsigned k) {
+			for (;;) {
+				const uint32_t r = next.fetch_add(1, std::memory_order_relaxed);
+				if (r >= h.n_rowgroups || (uint64_t)r * h.n_columns > first_bad.load(std::memory_order_relaxed)) {
+					return;
 				}
-			}
-			if (ch.is_equal) { // EXP_EQUAL: a copy of an EARLIER column's descriptor of the same row group, never a chain
-				const uint32_t src = ch.equal_col[0] | ((uint32_t)ch.equal_col[1] << 8);
-				if (src >= c || col.phys_bits == 128) {
-					return fail("EXP_EQUAL must refer to an earlier numeric column");
-				}
-				fls_chunk_desc want = t->chunk(r, src);
-				if (want.is_equal || t->columns[src].phys_bits != col.phys_bits) {
-					return fail("EXP_EQUAL source is itself a reference or has another physical width");
-				}
-				want.is_equal = 1;
-				want.equal_col[0] = ch.equal_col[0];
-				want.equal_col[1] = ch.equal_col[1];
-				if (std::memcmp(&want, &ch, sizeof(fls_chunk_desc)) != 0) {
-					return fail("EXP_EQUAL descriptor differs from its source chunk's");
-				}
-			}
-			if (ch.seg_size[FLS_SEG_META] != (uint64_t)ch.n_vec * sizeof(fls_vec_meta)) {
-				return fail("meta segment has the wrong size");
-			}
-			if (is_string_enc(ch.encoding) != (col.phys_bits == 128)) {
-				return fail("string encoding on a numeric column or vice versa");
-			}
-			if (col.phys_bits == 128) {
-				const char* why = validate_string_chunk(t, ch);
-				if (why) {
-					return fail(why);
-				}
-				continue;
-			}
-			const unsigned T = ch.phys_bits, esz = T / 8;
-			const fls_vec_meta* meta = reinterpret_cast<const fls_vec_meta*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_META]);
-			const bool patched = is_patched(ch.encoding);
-			unsigned lanes_T = T;
-			if (ch.encoding == FLS_ENC_DICT) {
-				lanes_T = ch.idx_bits;
-				if (lanes_T != 8 && lanes_T != 16 && lanes_T != 32) {
-					return fail("DICT idx_bits must be 8, 16 or 32");
-				}
-				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.aux_count == 0) {
-					return fail("dictionary segment has the wrong size");
-				}
-			} else if (ch.encoding == FLS_ENC_RLE) {
-				lanes_T = 16;
-				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz) {
-					return fail("run value segment has the wrong size");
-				}
-			} else if (ch.encoding == FLS_ENC_CROSS_RLE) {
-				if (ch.seg_size[FLS_SEG_AUX0] != (uint64_t)ch.aux_count * esz || ch.seg_size[FLS_SEG_AUX1] != (uint64_t)ch.aux_count * 4) {
-					return fail("CROSS_RLE segments have the wrong size");
-				}
-				const uint32_t* lens = reinterpret_cast<const uint32_t*>(t->bytes + ch.offset + ch.seg_off[FLS_SEG_AUX1]);
-				uint64_t sum = 0;
-				for (uint32_t i = 0; i < ch.aux_count; ++i) {
-					sum += lens[i];
-				}
-				if (sum != (uint64_t)ch.n_vec * FLS_VEC_SZ) {
-					return fail("CROSS_RLE run lengths do not cover the chunk");
-				}
-			}
-			if ((ch.encoding == FLS_ENC_ALP || ch.encoding == FLS_ENC_ALP_RD) && !(col.is_float && T >= 32)) {
-				return fail("ALP encodings need a FLOAT/DOUBLE column");
-			}
-			const uint8_t* data_seg = t->bytes + ch.offset + ch.seg_off[FLS_SEG_DATA];
-			uint64_t n_exc_seen = 0;
-			for (uint32_t v = 0; v < ch.n_vec; ++v) {
-				const fls_vec_meta& m = meta[v];
-				if (m.width > lanes_T || (ch.encoding == FLS_ENC_ALP_RD && (m.width2 == 0 || m.width2 > 3 || m.width + m.width2 > 64 + 3))) {
-					return fail("vector bit width out of range");
-				}
-				if ((uint64_t)m.data_off16 * 16 + blob_bytes(ch, m) > ch.seg_size[FLS_SEG_DATA]) {
-					return fail("vector entry point outside the data segment");
-				}
-				if (blob_bytes(ch, m) > ch.max_blob_bytes) {
-					return fail("vector blob larger than the chunk's max_blob_bytes");
-				}
-				if (m.n_valid == 0 || m.n_valid > FLS_VEC_SZ) {
-					return fail("vector n_valid out of range");
-				}
-				if (m.aux_cnt > FLS_VEC_SZ || (!patched && ch.encoding != FLS_ENC_RLE && m.aux_cnt != 0)) {
-					return fail("vector exception/run count out of range");
-				}
-				if (ch.encoding == FLS_ENC_RLE && (uint64_t)m.aux_off + m.aux_cnt > ch.aux_count) {
-					return fail("vector run range outside the run value segment");
-				}
-				if (patched && m.aux_cnt) {
-					const uint16_t* exc_pos = reinterpret_cast<const uint16_t*>(data_seg + (uint64_t)m.data_off16 * 16 + packed_bytes(ch, m) +
-					                                                            FLS_PAD16((uint32_t)m.aux_cnt * esz));
-					for (uint32_t k = 0; k < m.aux_cnt; ++k) {
-						if (exc_pos[k] >= FLS_VEC_SZ) {
-							return fail("exception position out of range");
+				for (uint32_t c = 0; c < h.n_columns; ++c) {
+					const char* w = validate_chunk(t, r, c);
+					if (w) {
+						const uint64_t at = (uint64_t)r * h.n_columns + c;
+						if (at < where[k]) {
+							where[k] = at;
+							why[k] = w;
 						}
+						uint64_t cur = first_bad.load(std::memory_order_relaxed);
+						while (at < cur && !first_bad.compare_exchange_weak(cur, at)) {
+						}
+						break;
 					}
-					n_exc_seen += m.aux_cnt;
-				}
-				if (ch.encoding == FLS_ENC_ALP && (m.e > (T == 64 ? 18 : 10) || m.f > m.e)) {
-					return fail("ALP exponent/factor out of range");
-				}
-				if (ch.encoding == FLS_ENC_RLE && m.aux_cnt == 0) {
-					return fail("RLE vector without runs");
 				}
 			}
-			if (patched && n_exc_seen != ch.aux_count) {
-				return fail("exception count disagrees with the chunk descriptor");
+		};
+		const auto t_dbg0 = std::chrono::steady_clock::now();
+		std::vector<std::thread> pool;
+		for (unsigned k = 1; k < n_threads; ++k) {
+			pool.emplace_back(work, k);
+		}
+		work(0);
+		for (auto& th : pool) {
+			th.join();
+		}
+		if (std::getenv("FLSGPU_TRACE_OPEN")) {
+			std::fprintf(stderr, "flsgpu: validated %u row groups on %u threads in %.3f s\n", h.n_rowgroups, n_threads,
+			             std::chrono::duration<double>(std::chrono::steady_clock::now() - t_dbg0).count());
+		}
+		const uint64_t bad = first_bad.load();
+		if (bad != ~0ull) {
+			for (unsigned k = 0; k < n_threads; ++k) {
+				if (where[k] == bad) {
+					std::snprintf(msg, sizeof(msg), "chunk (rg %u, col %u): %s", (unsigned)(bad / h.n_columns), (unsigned)(bad % h.n_columns), why[k]);
+					return fls_set_error(FLSGPU_ERR_INVALID, msg);
+				}
 			}
 		}
 	}
@@ -411,7 +473,7 @@ int flsgpu_table_open_memory(const void* bytes, uint64_t size, int copy, flsgpu_
 	}
 	auto t = std::make_unique<flsgpu_table>();
 	if (copy) {
-		t->owned = std::make_shared<std::vector<uint8_t>>(static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + size);
+		t->owned = std::make_shared<FlsImage>(static_cast<const uint8_t*>(bytes), static_cast<const uint8_t*>(bytes) + size);
 		t->bytes = t->owned->data();
 	} else {
 		t->bytes = static_cast<const uint8_t*>(bytes);
@@ -437,8 +499,40 @@ int flsgpu_table_open(const char* path, flsgpu_table** out) {
 	const long sz = std::ftell(fp);
 	std::fseek(fp, 0, SEEK_SET);
 	auto t = std::make_unique<flsgpu_table>();
-	t->owned = std::make_shared<std::vector<uint8_t>>(sz > 0 ? (size_t)sz : 0);
-	const size_t n = sz > 0 ? std::fread(t->owned->data(), 1, (size_t)sz, fp) : 0;
+	t->owned = std::make_shared<FlsImage>(sz > 0 ? (size_t)sz : 0);
+	// the image is read by several threads at once (pread of disjoint pieces): out of the page cache a single reader is bound
+	// by its own page faults and copies, 0.13 s for a 196 MB file
+	size_t n = 0;
+	if (sz > 0) {
+		const int fd = fileno(fp);
+		const size_t total = (size_t)sz;
+		const unsigned n_readers = (unsigned)std::max<size_t>(1, std::min<size_t>({(size_t)std::thread::hardware_concurrency(), 16u, total >> 24}));
+		const size_t piece = (total + n_readers - 1) / n_readers;
+		std::vector<size_t> got(n_readers, 0);
+		auto read_piece = [&](unsigned k) {
+			const size_t begin = std::min(total, (size_t)k * piece), end = std::min(total, begin + piece);
+			size_t at = begin;
+			while (at < end) {
+				const ssize_t r = pread(fd, t->owned->data() + at, end - at, (off_t)at);
+				if (r <= 0) {
+					break;
+				}
+				at += (size_t)r;
+			}
+			got[k] = at - begin;
+		};
+		std::vector<std::thread> readers;
+		for (unsigned k = 1; k < n_readers; ++k) {
+			readers.emplace_back(read_piece, k);
+		}
+		read_piece(0);
+		for (auto& th : readers) {
+			th.join();
+		}
+		for (size_t g : got) {
+			n += g;
+		}
+	}
 	std::fclose(fp);
 	if (sz < 0 || n != (size_t)sz) {
 		return fls_set_error(FLSGPU_ERR_IO, (std::string("short read: ") + path).c_str());
