@@ -1963,7 +1963,8 @@ int flsgpu_scan_strings_to_host(flsgpu_table* t, uint32_t col, uint32_t rg_begin
 // ---- filter pushdown ---------------------------------------------------------------------------------------------------
 namespace {
 
-// order of two physical values of a column (integers in their signedness; floats with DuckDB's NaN rules)
+// order of two physical values of a column (integers in their signedness; floats with DuckDB's NaN rules).  Zone maps of
+// float columns are NOT physical words (they are doubles, fls_format.h): pruning skips float columns and never comes here with one.
 int cmp_physical(const fls_column_desc& c, uint64_t a, uint64_t b) {
 	if (c.is_float) {
 		double x, y;

@@ -133,7 +133,8 @@ typedef struct fls_chunk_desc { /* 144 bytes */
 	uint64_t seg_off[FLS_SEG_COUNT]; /* from chunk start, 128-aligned */
 	uint64_t seg_size[FLS_SEG_COUNT];
 	uint64_t const_val; /* CONSTANT: the value (zero-extended physical word) */
-	uint64_t min_val;   /* zone map, physical word (sign-extended to 64 for signed, raw IEEE for floats) */
+	uint64_t min_val;   /* zone map: integers as the physical word sign- / zero-extended to 64 bits; FLOAT and DOUBLE columns as the bits
+	                       of an IEEE double (FLOAT values widened; NaNs are left out, has_stats = 0 when the chunk holds nothing else) */
 	uint64_t max_val;
 	uint32_t n_vec;
 	uint32_t n_tuples;

@@ -217,7 +217,7 @@ typedef struct flsgpu_agg_result { /* written to device memory, 64 bytes */
 	uint64_t sum_lo;  /* 128-bit two's complement sum (HUGEINT / DECIMAL(38) semantics, sum.cpp:161-210) */
 	uint64_t sum_hi;
 	uint64_t count;
-	int64_t min_val;  /* physical order of the column (signed or unsigned 64, raw IEEE for floats) */
+	int64_t min_val;  /* integer columns: the column's physical value, signed or unsigned 64 bits; not produced for FLOAT / DOUBLE */
 	int64_t max_val;
 	double fsum;      /* FLOAT/DOUBLE columns: sum in double (not order-stable, reported only) */
 	uint64_t reserved[2];
