@@ -357,7 +357,8 @@ def kernel_name(t, col):
     T = t.column(col).phys_bits
     fams = sorted(fams)  # "delta": 64-bit DELTA chunks have their own instantiation
     if fams == ["str_dict"]:
-        return "fls_str_kernels<dictionary form>", sorted(encs), 3  # heap fill + keys + codes
+        # heap fill (+ keys' string_t in the same launch for plain DICT_STR dictionaries, else a keys launch) + codes
+        return "fls_str_kernels<dictionary form>", sorted(encs), 2 if encs == {"DICT_STR"} else 3
     if len(fams) == 1:
         return f"fls_decode_kernel<{fams[0]},T={T}>", sorted(encs), 1
     fused = T == 32 and "alp" in fams and "alprd" in fams  # FLOAT: ALP and ALP_RD chunks share one launch

@@ -1938,10 +1938,19 @@ int flsgpu_decode_string_dict(flsgpu_table* t, uint32_t col, uint32_t rg_begin, 
 	L.heap_base_addr = heap_base_addr;
 	L.out = out_keys_dev;
 	L.dict_only = 1;
+	// plain dictionaries (DICT_STR): the heap launch builds the keys' string_t as well - one launch instead of two (the keys
+	// launch had to wait for the whole heap; FSST-compressed dictionaries still need it: their keys exist only decoded)
+	bool plain = env_u32("FLSGPU_STR_FUSE_KEYS", 1, 0, 1) != 0;
+	for (uint32_t r = rg_begin; r < rg_begin + n_rg && plain; ++r) {
+		plain = t->chunk(r, col).encoding == FLS_ENC_DICT_STR;
+	}
+	L.fuse_keys = plain ? 1u : 0u;
 	cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
 	FLS_CUDA(fls_str_launch_heap(L, s));
-	FLS_CUDA(fls_str_launch_keys(L, max_keys, s));
-	g_launches.fetch_add(2, std::memory_order_relaxed);
+	if (!plain) {
+		FLS_CUDA(fls_str_launch_keys(L, max_keys, s));
+	}
+	g_launches.fetch_add(plain ? 1 : 2, std::memory_order_relaxed);
 	return FLSGPU_OK;
 }
 

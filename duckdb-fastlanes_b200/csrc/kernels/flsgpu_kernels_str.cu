@@ -447,6 +447,15 @@ __device__ __forceinline__ void str_heap_body(const FlsStrLaunch& L) {
 	for (uint64_t i = g0 + threadIdx.x; i < g1; i += blockDim.x) {
 		dst[i] = __ldg(src + i);
 	}
+	if (L.fuse_keys && enc == FLS_ENC_DICT_STR) { // the keys' string_t: built from the source bytes the slice is a copy of
+		const uint32_t n = ch->aux_count;
+		const uint32_t* ends = reinterpret_cast<const uint32_t*>(ch->aux1);
+		uint4* out = static_cast<uint4*>(L.out) + (L.key_prefix[(size_t)rg * L.chunk_stride] - L.key_prefix0);
+		for (uint32_t k = g * blockDim.x + threadIdx.x; k < n; k += L.groups_per_rg * blockDim.x) {
+			const uint32_t start = k ? __ldg(ends + k - 1) : 0u, end = __ldg(ends + k);
+			out[k] = make_string_t<false>(ch->aux0, L.heap_base_addr + hoff, start, end - start);
+		}
+	}
 }
 
 template <int IT>
