@@ -86,6 +86,7 @@ struct FlsStrLaunch {
 	uint32_t cbuf_bytes;         // per-warp shared-memory staging of a tile's codes / decoded bytes (multiples of 16;
 	uint32_t dbuf_bytes;         //  tiles that do not fit are decoded straight to global memory)
 	uint32_t fuse_rows;          // FSST chunks: the heap kernel also builds the string_t rows (the rows kernel skips them)
+	uint32_t balance;            // FSST decode: lanes split a tile by code bytes (cut at string boundaries), not by string count
 	uint32_t fuse_keys;          // dictionary decode of plain DICT_STR chunks: the heap kernel also builds the keys' string_t (from the
 	                             // source bytes, which the heap slice copies verbatim), the keys launch is not issued
 	// rows kernel, filter mode (dictionary-encoded chunks only): the comparison was evaluated once per dictionary key

@@ -1805,6 +1805,9 @@ int string_launch_setup(flsgpu_table* t, uint32_t col, uint32_t rg_begin, uint32
 		}
 	}
 	L->lane_strings = 8;
+	// experiment, off: lanes splitting a tile by code bytes instead of by strings evens out the lanes' work but costs a lower-bound
+	// search per lane and tile; measured slower (dbgen l_comment SF3 0.645 -> 0.698 ms, synthetic text 0.523 -> 0.631 ms)
+	L->balance = env_u32("FLSGPU_STR_BALANCE", 0, 0, 1);
 	L->cbuf_bytes = L->dbuf_bytes = 0;
 	uint32_t max_fsst_strings = 0;
 	uint64_t max_plain_bytes = 0;

@@ -337,6 +337,36 @@ __device__ __forceinline__ void str_heap_body(const FlsStrLaunch& L) {
 			t.d0 = t.s0 ? __ldg(dec_end + t.s0 - 1) : 0u;
 			t.c1 = __ldg(comp_end + t.s1 - 1);
 			t.d1 = __ldg(dec_end + t.s1 - 1);
+			if (L.balance && !twelve) {
+				// (experiment, off by default: measured 8-20 % SLOWER than the equal-strings split, the search outweighs the balance)
+				// Lanes take equal shares of the tile's CODE BYTES, cut at string boundaries, instead of equal numbers of strings: a
+				// lane's work is its code count, and with lane_strings strings apiece the slowest of 32 lanes carried ~25 % more
+				// codes than the mean (21.5 active lanes per instruction).  Lane i starts at the first string that begins at or
+				// after byte c0 + i * (c1 - c0) / 32 (lower bound over the tile's compressed end offsets: ~10 probes, all but the
+				// first few out of L1); its neighbour's start is where it ends.  The heap is one contiguous stream, so any
+				// string-aligned cut decodes to the same bytes.
+				const uint32_t target = t.c0 + (uint32_t)(((uint64_t)(t.c1 - t.c0) * lane) >> 5);
+				uint32_t lo = t.s0, hi = t.s1;
+				while (lo < hi) {
+					const uint32_t mid = (lo + hi) >> 1;
+					const uint32_t start = mid ? __ldg(comp_end + mid - 1) : 0u;
+					if (start >= target) {
+						hi = mid;
+					} else {
+						lo = mid + 1u;
+					}
+				}
+				uint32_t nxt = __shfl_down_sync(0xffffffffu, lo, 1);
+				if (lane == 31u) {
+					nxt = t.s1;
+				}
+				t.first = lo;
+				t.last = nxt ? nxt - 1u : 0u; // unused by the FSST8 decoder
+				t.cbeg = lo ? __ldg(comp_end + lo - 1) : 0u;
+				t.dbeg = lo ? __ldg(dec_end + lo - 1) : 0u;
+				t.cend = nxt ? __ldg(comp_end + nxt - 1) : 0u;
+				return t;
+			}
 			t.first = t.s0 + lane * L.lane_strings;
 			t.last = t.first;
 			t.cbeg = t.cend = t.dbeg = 0;
