@@ -64,7 +64,8 @@ def main():
     ap.add_argument("--sql-runs", type=int, default=3)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--cpu-seconds", type=float, default=8.0)
-    ap.add_argument("--gpu-devices", type=int, default=1)
+    ap.add_argument("--gpu-devices", type=int, default=1, help="read_fls shards its batches of row groups over this many devices of the one DuckDB process")
+    ap.add_argument("--no-resident", action="store_true", help="SQL part only")
     ap.add_argument("--out", default=None)
     args = ap.parse_args()
     tmp = tempfile.mkdtemp(prefix="fls_dbgen_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
@@ -95,14 +96,14 @@ def main():
         doc["fls_MB"], doc["duckdb_file_MB"] = round(os.path.getsize(fls) / 1e6, 1), round(os.path.getsize(db) / 1e6, 1)
 
         # ---- SQL timings: the native table on the host cores vs read_fls on the GPU
-        setup = "SET fastlanes_gpu_devices=%d;\n" % args.gpu_devices if args.gpu_devices > 1 else ""
+        setup = "SET fastlanes_gpu_devices='%s';\n" % ",".join(str(g) for g in range(args.gpu_devices)) if args.gpu_devices > 1 else ""
         sql = {}
         for name, stmt in SQL.items():
             cpu_s, cpu_rows = timed_sql(db, stmt.format(src="lineitem"), args.sql_runs)
             gpu_s, gpu_rows = timed_sql(db, stmt.format(src="read_fls('%s')" % fls), args.sql_runs, setup)
             assert cpu_rows[1:] == gpu_rows[1:], "%s: read_fls result differs from the native table:\n%s\n%s" % (name, cpu_rows, gpu_rows)
             sql[name] = {"duckdb_native_table_s": cpu_s, "read_fls_gpu_s": gpu_s, "speedup": round(cpu_s / gpu_s, 2), "result_rows": len(cpu_rows) - 1}
-        doc["sql"] = {"host_threads": os.cpu_count(), "runs": args.sql_runs, "timing": "the shell's .timer, best run; results equal as text", "queries": sql}
+        doc["sql"] = {"host_threads": os.cpu_count(), "gpu_devices": args.gpu_devices, "runs": args.sql_runs, "timing": "the shell's .timer, best run; results equal as text", "queries": sql}
 
         # ---- answers for the resident bench from DuckDB itself (dates as days since 1970, decimals unscaled)
         want_csv = os.path.join(tmp, "want.csv")
@@ -121,6 +122,13 @@ def main():
         n_rows = int(row["n"])
         os.remove(db)
 
+        if args.no_resident:
+            os.remove(fls)
+            print(json.dumps(doc, indent=1))
+            if args.out:
+                with open(args.out, "w") as f:
+                    json.dump(doc, f, indent=1)
+            return
         # ---- resident scans of the same file (tools/lineitem_bench.py)
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import lineitem_bench
