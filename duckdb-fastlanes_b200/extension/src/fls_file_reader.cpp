@@ -184,14 +184,28 @@ shared_ptr<FlsCachedTable> FlsTableCache::Acquire(ClientContext &context, const 
 	}
 	const string key = path + "|" + to_string((uint64_t)st.st_size) + "|" + to_string((uint64_t)st.st_mtim.tv_sec) + "." +
 	                   to_string((uint64_t)st.st_mtim.tv_nsec) + "|" + device_list;
-	std::lock_guard<std::mutex> guard(lock);
-	for (idx_t i = 0; i < entries.size(); i++) {
-		if (entries[i]->key == key) {
-			auto hit = entries[i];
-			entries.erase(entries.begin() + NumericCast<int64_t>(i));
-			entries.insert(entries.begin(), hit);
+	auto lookup = [&]() -> shared_ptr<FlsCachedTable> {
+		for (idx_t i = 0; i < entries.size(); i++) {
+			if (entries[i]->key == key) {
+				auto hit = entries[i];
+				entries.erase(entries.begin() + NumericCast<int64_t>(i));
+				entries.insert(entries.begin(), hit);
+				return hit;
+			}
+		}
+		return nullptr;
+	};
+	{
+		std::lock_guard<std::mutex> guard(lock);
+		if (auto hit = lookup()) {
 			return hit;
 		}
+	}
+	// reading and validating a file takes its time (0.08 s per 200 MB): not under the lock, the files of a glob open in parallel
+	auto entry = Open(path, key);
+	std::lock_guard<std::mutex> guard(lock);
+	if (auto hit = lookup()) {
+		return hit; // another thread opened the same file meanwhile: one copy is enough
 	}
 	// an older version of the same file is of no use to anybody new
 	const string prefix = path + "|";
@@ -200,7 +214,6 @@ shared_ptr<FlsCachedTable> FlsTableCache::Acquire(ClientContext &context, const 
 			entries.erase(entries.begin() + NumericCast<int64_t>(i));
 		}
 	}
-	auto entry = Open(path, key);
 	entries.insert(entries.begin(), entry);
 	idx_t total = 0;
 	for (auto &e : entries) {
