@@ -73,6 +73,10 @@ const uint32_t g_dict_run_shift = std::min(5u, env_u32("FLSGPU_DICT_RUN_SHIFT", 
 const uint32_t g_dict_kb = env_u32("FLSGPU_DICT_KB", 6, 2, 27);
 const uint32_t g_kind_maps = env_u32("FLSGPU_KIND_MAPS", 1, 0, 1); // per-kind vector lists for columns that mix kernel families
 const uint32_t g_swar8_kb = env_u32("FLSGPU_SWAR8_KB", 8, 2, 27);      // same for the 8-bit SWAR kernel (48 registers: up to five resident CTAs per SM)
+// 8 / 16-bit columns decode more values per staged byte: resident warps matter more than pipeline depth (measured on 32 M
+// SMALLINT values, 18 -> 8 KiB: FFOR w=16 26.5 -> 17.5 us, DELTA w=10/12 27 -> 18 us, w <= 8 unchanged or 12 % faster;
+// profiles/r02_sweep_knobs.txt)
+const uint32_t g_narrow_kb = env_u32("FLSGPU_NARROW_KB", 8, 2, 27);
 
 int cuda_fail(cudaError_t e, const char* where) {
 	char msg[256];
@@ -770,7 +774,8 @@ int decode_column_impl(flsgpu_table* t, FlsDeviceState* d, uint32_t col, uint32_
 			const bool stage = p.main_needs_stage && (f == 3 || (f == 0 && T != 64));
 			const uint32_t slot = fold4 ? std::max(p.main_slot[0], p.main_slot[4]) : p.main_slot[f];
 			rc = launch_family(d, agg_family ? fls_kernel_agg(0, T, T, f == 3 ? 0 : f) : fls_kernel_main(T, os.ob, f), L, slot,
-			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile, f == 4 ? g_swar8_kb : 0u);
+			                   stage ? 128u * T + (T == 64 ? 128u : 0u) : 0u, stream, tile,
+			                   f == 4 ? g_swar8_kb : (T <= 16 && !agg_family) ? g_narrow_kb : 0u);
 		}
 	}
 	for (int k = 0; k < 3 && rc == FLSGPU_OK; ++k) {
