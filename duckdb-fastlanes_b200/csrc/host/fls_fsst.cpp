@@ -3,13 +3,10 @@
 
 #include <algorithm>
 #include <cstring>
-#include <unordered_map>
 
 namespace flshost {
 
 namespace {
-
-constexpr uint32_t kSlots = 1u << 12; // lookup slots (255 symbols: load factor 6 %)
 
 inline uint64_t load_prefix(const uint8_t* s, uint32_t len) { // first `len` (<= 8) bytes, little endian, zero padded
 	uint64_t v = 0;
@@ -17,10 +14,15 @@ inline uint64_t load_prefix(const uint8_t* s, uint32_t len) { // first `len` (<=
 	return v;
 }
 
-inline uint32_t hash_sym(uint64_t v, uint32_t len) {
-	const uint64_t h = (v ^ ((uint64_t)len << 59)) * 0x9E3779B97F4A7C15ull;
-	return (uint32_t)(h >> 40) & (kSlots - 1);
-}
+constexpr uint64_t kLenMask[9] = {0ull,
+                                  0xffull,
+                                  0xffffull,
+                                  0xffffffull,
+                                  0xffffffffull,
+                                  0xffffffffffull,
+                                  0xffffffffffffull,
+                                  0xffffffffffffffull,
+                                  ~0ull};
 
 struct Cand {
 	uint64_t value;
@@ -28,47 +30,165 @@ struct Cand {
 	uint64_t gain;
 };
 
-struct KeyHash {
-	size_t operator()(const std::pair<uint64_t, uint32_t>& k) const {
-		return (size_t)((k.first ^ ((uint64_t)k.second << 59)) * 0x9E3779B97F4A7C15ull);
+// (bytes, length) -> occurrences, for the trainers: open addressing, grows at half load.  The order candidates come out in
+// does not matter: the selection below sorts them by a total order.
+struct SymbolCounts {
+	std::vector<uint64_t> value, count;
+	std::vector<uint8_t> len; // 0 = empty slot
+	uint64_t used = 0;
+
+	explicit SymbolCounts(uint32_t log2_slots) : value(1ull << log2_slots), count(1ull << log2_slots), len(1ull << log2_slots) {
+	}
+	void clear() {
+		std::fill(len.begin(), len.end(), (uint8_t)0);
+		used = 0;
+	}
+	static uint64_t hash(uint64_t v, uint32_t l) {
+		return ((v ^ ((uint64_t)l << 59)) * 0x9E3779B97F4A7C15ull) >> 24;
+	}
+	void add(uint64_t v, uint32_t l) {
+		const uint64_t mask = len.size() - 1;
+		uint64_t h = hash(v, l) & mask;
+		while (len[h]) {
+			if (len[h] == l && value[h] == v) {
+				++count[h];
+				return;
+			}
+			h = (h + 1) & mask;
+		}
+		value[h] = v;
+		len[h] = (uint8_t)l;
+		count[h] = 1;
+		if (++used * 2 > len.size()) {
+			grow();
+		}
+	}
+	void grow() {
+		SymbolCounts bigger(0);
+		bigger.value.assign(len.size() * 2, 0);
+		bigger.count.assign(len.size() * 2, 0);
+		bigger.len.assign(len.size() * 2, 0);
+		const uint64_t mask = bigger.len.size() - 1;
+		for (size_t i = 0; i < len.size(); ++i) {
+			if (len[i]) {
+				uint64_t h = hash(value[i], len[i]) & mask;
+				while (bigger.len[h]) {
+					h = (h + 1) & mask;
+				}
+				bigger.value[h] = value[i];
+				bigger.len[h] = len[i];
+				bigger.count[h] = count[i];
+			}
+		}
+		bigger.used = used;
+		*this = std::move(bigger);
 	}
 };
 
 } // namespace
 
-void FsstEncoder::rebuild_lookup() {
-	slots.assign(kSlots, 0);
-	std::memset(byte_code, 0, sizeof(byte_code));
+// Symbols of two or more bytes, grouped by their first two bytes and ordered longest first inside a group: the longest
+// symbol that matches at a position is the first hit of one short list (a handful of entries on text), where probing a hash
+// per candidate length cost up to seven lookups per position.
+void FsstPrefixIndex::build(const uint64_t* symbol, const uint8_t* len, uint32_t first_code, uint32_t n_codes) {
+	bucket.assign(1u << 16, 0u);
+	order.clear();
 	max_len = 0;
-	for (uint32_t c = 0; c < n_symbols; ++c) {
-		const uint32_t len = table.len[c];
-		max_len = std::max<uint8_t>(max_len, (uint8_t)len);
-		if (len == 1) {
-			byte_code[table.symbol[c] & 0xff] = (uint16_t)(c + 1);
-			continue;
+	std::vector<uint32_t> fill(1u << 16, 0u);
+	uint32_t n_mid = 0, n_full = 0;
+	for (uint32_t c = first_code; c < first_code + n_codes; ++c) {
+		max_len = std::max<uint8_t>(max_len, len[c]);
+		if (len[c] >= 2 && len[c] < 8) {
+			++fill[symbol[c] & 0xffffu];
+			++n_mid;
 		}
-		uint32_t h = hash_sym(table.symbol[c], len);
-		while (slots[h]) {
-			h = (h + 1) & (kSlots - 1);
-		}
-		slots[h] = c + 1;
+		n_full += len[c] == 8;
 	}
+	// 8-byte symbols (half of a table trained on text): one probe with the whole word
+	uint32_t log2 = 4;
+	while ((1u << log2) < 4 * n_full) {
+		++log2;
+	}
+	full.assign(1u << log2, 0);
+	full_shift = 64 - log2;
+	for (uint32_t c = first_code; c < first_code + n_codes; ++c) {
+		if (len[c] == 8) {
+			uint32_t h = (uint32_t)((symbol[c] * 0x9E3779B97F4A7C15ull) >> full_shift);
+			while (full[h]) {
+				h = (h + 1) & ((uint32_t)full.size() - 1);
+			}
+			full[h] = (uint16_t)(c + 1);
+		}
+	}
+	order.resize(n_mid);
+	uint32_t start = 0;
+	for (uint32_t k = 0; k < (1u << 16); ++k) {
+		if (fill[k]) {
+			bucket[k] = (start << 16) | fill[k];
+			start += fill[k];
+			fill[k] = 0;
+		}
+	}
+	for (uint32_t c = first_code; c < first_code + n_codes; ++c) {
+		if (len[c] >= 2 && len[c] < 8) {
+			const uint32_t k = (uint32_t)(symbol[c] & 0xffffu);
+			order[(bucket[k] >> 16) + fill[k]++] = (uint16_t)c;
+		}
+	}
+	for (uint32_t k = 0; k < (1u << 16); ++k) {
+		if ((bucket[k] & 0xffffu) > 1) {
+			uint16_t* o = order.data() + (bucket[k] >> 16);
+			std::sort(o, o + (bucket[k] & 0xffffu), [&](uint16_t a, uint16_t b) { return len[a] != len[b] ? len[a] > len[b] : a < b; });
+		}
+	}
+}
+
+int FsstPrefixIndex::find(const uint64_t* symbol, const uint8_t* len, const uint8_t* s, uint64_t remaining, uint32_t* len_out) const {
+	if (remaining < 2) {
+		return -1;
+	}
+	uint64_t w = 0;
+	if (remaining >= 8) {
+		std::memcpy(&w, s, 8);
+		for (uint32_t h = (uint32_t)((w * 0x9E3779B97F4A7C15ull) >> full_shift); full[h]; h = (h + 1) & ((uint32_t)full.size() - 1)) {
+			if (symbol[full[h] - 1u] == w) {
+				*len_out = 8;
+				return (int)full[h] - 1;
+			}
+		}
+	} else {
+		std::memcpy(&w, s, remaining);
+	}
+	const uint32_t e = bucket[(uint32_t)(w & 0xffffu)];
+	if (!e) {
+		return -1;
+	}
+	const uint16_t* o = order.data() + (e >> 16);
+	for (uint32_t k = 0, n = e & 0xffffu; k < n; ++k) {
+		const uint32_t c = o[k], l = len[c];
+		if (l <= remaining && (w & kLenMask[l]) == symbol[c]) {
+			*len_out = l;
+			return (int)c;
+		}
+	}
+	return -1;
+}
+
+void FsstEncoder::rebuild_lookup() {
+	std::memset(byte_code, 0, sizeof(byte_code));
+	for (uint32_t c = 0; c < n_symbols; ++c) {
+		if (table.len[c] == 1) {
+			byte_code[table.symbol[c] & 0xff] = (uint16_t)(c + 1);
+		}
+	}
+	index.build(table.symbol, table.len, 0, n_symbols);
 }
 
 // longest symbol matching at s; returns its code or -1
 int FsstEncoder::find(const uint8_t* s, uint64_t remaining, uint32_t* len_out) const {
-	const uint32_t top = (uint32_t)std::min<uint64_t>(max_len, remaining);
-	for (uint32_t len = top; len >= 2; --len) {
-		const uint64_t v = load_prefix(s, len);
-		uint32_t h = hash_sym(v, len);
-		while (slots[h]) {
-			const uint32_t c = slots[h] - 1;
-			if (table.len[c] == len && table.symbol[c] == v) {
-				*len_out = len;
-				return (int)c;
-			}
-			h = (h + 1) & (kSlots - 1);
-		}
+	const int c = index.find(table.symbol, table.len, s, remaining, len_out);
+	if (c >= 0) {
+		return c;
 	}
 	if (remaining && byte_code[s[0]]) {
 		*len_out = 1;
@@ -94,9 +214,9 @@ void FsstEncoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_t 
 	n_symbols = 0;
 	std::memset(&table, 0, sizeof(table));
 	rebuild_lookup();
+	SymbolCounts count(15);
 	for (int round = 0; round < 5; ++round) {
-		std::unordered_map<std::pair<uint64_t, uint32_t>, uint64_t, KeyHash> count;
-		count.reserve(1 << 14);
+		count.clear();
 		for (const auto& sv : sample) {
 			const uint8_t* s = sv.first;
 			const uint64_t len = sv.second;
@@ -109,9 +229,9 @@ void FsstEncoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_t 
 					l = 1;
 				}
 				const uint64_t v = load_prefix(s + p, l);
-				++count[{v, l}];
+				count.add(v, l);
 				if (prev_len && prev_len + l <= 8) { // candidate: the two adjacent symbols glued together
-					++count[{prev_v | (v << (8 * prev_len)), prev_len + l}];
+					count.add(prev_v | (v << (8 * prev_len)), prev_len + l);
 				}
 				prev_v = v;
 				prev_len = l;
@@ -119,12 +239,16 @@ void FsstEncoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_t 
 			}
 		}
 		std::vector<Cand> cands;
-		cands.reserve(count.size());
-		for (const auto& kv : count) {
+		cands.reserve(count.used);
+		for (size_t i = 0; i < count.len.size(); ++i) {
+			if (!count.len[i]) {
+				continue;
+			}
 			// a single byte that is not a symbol costs 2 output bytes (escape), so a 1-byte symbol saves 1 per use like a
 			// 2-byte symbol does; longer symbols save len - 1
-			const uint64_t gain = kv.second * (kv.first.second == 1 ? 1 : kv.first.second - 1) + (kv.first.second == 1 ? kv.second / 2 : 0);
-			cands.push_back({kv.first.first, kv.first.second, gain});
+			const uint64_t n = count.count[i], l = count.len[i];
+			const uint64_t gain = n * (l == 1 ? 1 : l - 1) + (l == 1 ? n / 2 : 0);
+			cands.push_back({count.value[i], (uint32_t)l, gain});
 		}
 		const size_t keep = std::min<size_t>(255, cands.size());
 		std::partial_sort(cands.begin(), cands.begin() + keep, cands.end(), [](const Cand& a, const Cand& b) {
@@ -175,43 +299,12 @@ uint64_t fsst_decoded_length(const fls_fsst_table& table, const uint8_t* codes, 
 }
 
 // ---- FSST12 -----------------------------------------------------------------------------------------------------------
-namespace {
-constexpr uint32_t kSlots12 = 1u << 14;
-inline uint32_t hash_sym12(uint64_t v, uint32_t len) {
-	const uint64_t h = (v ^ ((uint64_t)len << 59)) * 0x9E3779B97F4A7C15ull;
-	return (uint32_t)(h >> 40) & (kSlots12 - 1);
-}
-} // namespace
-
 void Fsst12Encoder::rebuild_lookup() {
-	slots.assign(kSlots12, 0);
-	max_len = 0;
-	for (uint32_t i = 0; i < n_symbols; ++i) {
-		const uint32_t c = 256 + i, len = table.len[c];
-		max_len = std::max<uint8_t>(max_len, (uint8_t)len);
-		uint32_t h = hash_sym12(table.symbol[c], len);
-		while (slots[h]) {
-			h = (h + 1) & (kSlots12 - 1);
-		}
-		slots[h] = c;
-	}
+	index.build(table.symbol, table.len, 256, n_symbols);
 }
 
 int Fsst12Encoder::find(const uint8_t* s, uint64_t remaining, uint32_t* len_out) const {
-	const uint32_t top = (uint32_t)std::min<uint64_t>(max_len, remaining);
-	for (uint32_t len = top; len >= 2; --len) {
-		const uint64_t v = load_prefix(s, len);
-		uint32_t h = hash_sym12(v, len);
-		while (slots[h]) {
-			const uint32_t c = slots[h];
-			if (table.len[c] == len && table.symbol[c] == v) {
-				*len_out = len;
-				return (int)c;
-			}
-			h = (h + 1) & (kSlots12 - 1);
-		}
-	}
-	return -1;
+	return index.find(table.symbol, table.len, s, remaining, len_out);
 }
 
 void Fsst12Encoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_t n) {
@@ -234,9 +327,9 @@ void Fsst12Encoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_
 		table.len[c] = 1;
 	}
 	rebuild_lookup();
+	SymbolCounts count(17);
 	for (int round = 0; round < 5; ++round) {
-		std::unordered_map<std::pair<uint64_t, uint32_t>, uint64_t, KeyHash> count;
-		count.reserve(1 << 16);
+		count.clear();
 		for (const auto& sv : sample) {
 			const uint8_t* s = sv.first;
 			const uint64_t len = sv.second;
@@ -249,10 +342,10 @@ void Fsst12Encoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_
 				}
 				const uint64_t v = load_prefix(s + p, l);
 				if (l >= 2) {
-					++count[{v, l}];
+					count.add(v, l);
 				}
 				if (prev_len && prev_len + l <= 8) {
-					++count[{prev_v | (v << (8 * prev_len)), prev_len + l}];
+					count.add(prev_v | (v << (8 * prev_len)), prev_len + l);
 				}
 				prev_v = v;
 				prev_len = l;
@@ -260,10 +353,10 @@ void Fsst12Encoder::train(const uint64_t* offsets, const uint8_t* bytes, uint64_
 			}
 		}
 		std::vector<Cand> cands;
-		cands.reserve(count.size());
-		for (const auto& kv : count) {
-			if (kv.second >= 2) { // a symbol seen once saves nothing worth a table slot
-				cands.push_back({kv.first.first, kv.first.second, kv.second * (kv.first.second - 1)});
+		cands.reserve(count.used);
+		for (size_t i = 0; i < count.len.size(); ++i) {
+			if (count.len[i] && count.count[i] >= 2) { // a symbol seen once saves nothing worth a table slot
+				cands.push_back({count.value[i], (uint32_t)count.len[i], count.count[i] * (count.len[i] - 1u)});
 			}
 		}
 		const size_t keep = std::min<size_t>(4096 - 256, cands.size());

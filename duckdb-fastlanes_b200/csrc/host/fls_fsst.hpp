@@ -13,12 +13,24 @@
 
 namespace flshost {
 
+// longest-match lookup shared by both encoders: 8-byte symbols in a hash of the whole word, symbols of 2..7 bytes grouped by
+// their first two bytes, longest first
+struct FsstPrefixIndex {
+	std::vector<uint16_t> full;   // open addressing, code + 1 (0 = empty)
+	uint32_t full_shift = 60;
+	std::vector<uint32_t> bucket; // 65536 entries: (first entry in `order`) << 16 | entries
+	std::vector<uint16_t> order;  // codes
+	uint8_t max_len = 0;
+
+	void build(const uint64_t* symbol, const uint8_t* len, uint32_t first_code, uint32_t n_codes);
+	// code of the longest symbol (>= 2 bytes) that matches at s, or -1
+	int find(const uint64_t* symbol, const uint8_t* len, const uint8_t* s, uint64_t remaining, uint32_t* len_out) const;
+};
+
 struct FsstEncoder {
 	fls_fsst_table table {};
 	uint32_t n_symbols = 0;
-	// lookup: open-addressed hash of (length, bytes) -> code, probed from the longest length down
-	std::vector<uint32_t> slots; // code + 1, 0 = empty
-	uint8_t max_len = 0;
+	FsstPrefixIndex index;
 	// single-byte symbols: direct table (code + 1)
 	uint16_t byte_code[256] = {};
 
@@ -37,8 +49,7 @@ struct FsstEncoder {
 struct Fsst12Encoder {
 	fls_fsst12_table table {};
 	uint32_t n_symbols = 0; // trained symbols: codes 256 .. 256 + n_symbols - 1
-	std::vector<uint32_t> slots;
-	uint8_t max_len = 0;
+	FsstPrefixIndex index;
 
 	void train(const uint64_t* offsets, const uint8_t* bytes, uint64_t n);
 	// appends the packed 12-bit code stream of one string to out

@@ -6,7 +6,11 @@
 #include "fls_encoder.hpp"
 #include "fls_error.hpp"
 
+#include <fcntl.h>
+#include <unistd.h>
+
 #include <atomic>
+#include <cerrno>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -35,7 +39,69 @@ struct flsgpu_writer {
 	bool detect_equal = true; // FLSGPU_WRITER_EQUAL=0: never write EXP_EQUAL chunks
 	bool inline_footer = true; // WithInlinedFooter (fls_writer.cpp:278): false -> flsgpu_writer_save writes <path>.footer beside the data
 	std::mutex flush_mu;       // flsgpu_writer_flush_rowgroup may be called from any thread
+	// flsgpu_writer_stream_to: chunks go to the file as their row group is flushed / encoded and only their descriptors stay
+	int fd = -1;
+	std::string stream_path;
+	uint64_t stream_off = FLS_ALIGN; // where the next chunk goes (the header takes the first 128 bytes)
+	size_t streamed_chunks = 0;      // chunks[0 .. streamed_chunks) are in the file
+
+	~flsgpu_writer() {
+		if (fd >= 0) {
+			::close(fd);
+		}
+	}
 };
+
+static int write_file(const char* path, const uint8_t* p, size_t n) {
+	FILE* fp = std::fopen(path, "wb");
+	if (!fp) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open for writing: ") + path).c_str());
+	}
+	const size_t k = std::fwrite(p, 1, n, fp);
+	if (std::fclose(fp) != 0 || k != n) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("short write: ") + path).c_str());
+	}
+	return FLSGPU_OK;
+}
+
+static int pwrite_all(int fd, const uint8_t* p, size_t n, uint64_t off, const std::string& path) {
+	while (n) {
+		const ssize_t k = ::pwrite(fd, p, n, (off_t)off);
+		if (k < 0) {
+			if (errno == EINTR) {
+				continue;
+			}
+			return fls_set_error(FLSGPU_ERR_IO, ("write failed: " + path + ": " + std::strerror(errno)).c_str());
+		}
+		p += k;
+		n -= (size_t)k;
+		off += (uint64_t)k;
+	}
+	return FLSGPU_OK;
+}
+
+// streaming writers: put the chunks that arrived since the last call into the file (same offsets as flsgpu_writer_finish lays
+// an in-memory image out with) and drop their bytes
+static int stream_new_chunks(flsgpu_writer* w) {
+	if (w->fd < 0) {
+		return FLSGPU_OK;
+	}
+	for (; w->streamed_chunks < w->chunks.size(); ++w->streamed_chunks) {
+		EncodedChunk& ch = *w->chunks[w->streamed_chunks];
+		if (ch.equal_to >= 0) {
+			continue; // EXP_EQUAL: a descriptor only
+		}
+		ch.desc.offset = w->stream_off;
+		const int rc = pwrite_all(w->fd, ch.bytes.data(), ch.bytes.size(), w->stream_off, w->stream_path);
+		if (rc) {
+			return rc;
+		}
+		w->stream_off += ch.desc.size;
+		ch.bytes.clear();
+		ch.bytes.shrink_to_fit();
+	}
+	return FLSGPU_OK;
+}
 
 // RowGroupWriter of the reference (fls_writer.cpp:306-330): one row group encoded off to the side by PrepareBatch, appended
 // to the file by FlushBatch.
@@ -236,7 +302,10 @@ int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t 
 		w->pending_rows += take;
 		consumed = take;
 		if (w->pending_rows == w->rg_tuples) {
-			const int rc = encode_rowgroups(w, pending_src(), w->rg_tuples, n_threads);
+			int rc = encode_rowgroups(w, pending_src(), w->rg_tuples, n_threads);
+			if (!rc) {
+				rc = stream_new_chunks(w);
+			}
 			if (rc) {
 				return rc;
 			}
@@ -256,7 +325,10 @@ int flsgpu_writer_append(flsgpu_writer* w, const void* const* columns, uint64_t 
 				ptrs[c].data = static_cast<const uint8_t*>(columns[c]) + consumed * (w->types[c].phys_bits / 8);
 			}
 		}
-		const int rc = encode_rowgroups(w, ptrs, full, n_threads);
+		int rc = encode_rowgroups(w, ptrs, full, n_threads);
+		if (!rc) {
+			rc = stream_new_chunks(w);
+		}
 		if (rc) {
 			return rc;
 		}
@@ -327,6 +399,23 @@ int flsgpu_writer_flush_rowgroup(flsgpu_writer* w, flsgpu_encoded_rowgroup* rg) 
 		w->chunks.push_back(std::move(ch));
 	}
 	w->n_tuples += rg->n_tuples;
+	return stream_new_chunks(w);
+}
+
+int flsgpu_writer_stream_to(flsgpu_writer* w, const char* path) {
+	if (!w || !path) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_stream_to: null argument");
+	}
+	std::lock_guard<std::mutex> g(w->flush_mu);
+	if (w->finished || w->fd >= 0 || !w->chunks.empty()) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_stream_to: call once, before the first row group");
+	}
+	const int fd = ::open(path, O_CREAT | O_TRUNC | O_WRONLY | O_CLOEXEC, 0644);
+	if (fd < 0) {
+		return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open for writing: ") + path + ": " + std::strerror(errno)).c_str());
+	}
+	w->fd = fd;
+	w->stream_path = path;
 	return FLSGPU_OK;
 }
 
@@ -368,7 +457,10 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 			ptrs[c].data = w->pending[c].data();
 			ptrs[c].offsets = is_string(w->types[c]) ? w->pending_off[c].data() : nullptr;
 		}
-		const int rc = encode_rowgroups(w, ptrs, w->pending_rows, 1);
+		int rc = encode_rowgroups(w, ptrs, w->pending_rows, 1);
+		if (!rc) {
+			rc = stream_new_chunks(w);
+		}
 		if (rc) {
 			return rc;
 		}
@@ -399,7 +491,6 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 	const uint64_t footer_off = off;
 	const uint64_t footer_size = w->cols.size() * sizeof(fls_column_desc) + w->rgs.size() * sizeof(fls_rowgroup_desc) +
 	                             w->chunks.size() * sizeof(fls_chunk_desc);
-	w->image.assign(footer_off + footer_size, 0);
 	fls_file_header h {};
 	std::memcpy(h.magic, FLS_MAGIC, 8);
 	h.version = FLS_VERSION;
@@ -410,18 +501,54 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 	h.footer_offset = footer_off;
 	h.footer_size = footer_size;
 	h.reserved[0] = w->inline_footer ? 0 : 1; // 1: flsgpu_writer_save puts the footer into <path>.footer
-	std::memcpy(w->image.data(), &h, sizeof(h));
-	uint8_t* f = w->image.data() + footer_off;
+	const bool streaming = w->fd >= 0;
+	// streaming writers hold the header + footer only: the chunks are in the file already, at these very offsets
+	std::vector<uint8_t> tail;
+	uint8_t* f;
+	if (streaming) {
+		if (w->streamed_chunks != w->chunks.size() || w->stream_off != footer_off) {
+			return fls_set_error(FLSGPU_ERR_IO, "flsgpu_writer_finish: streamed chunks disagree with the final layout");
+		}
+		tail.assign(footer_size, 0);
+		f = tail.data();
+	} else {
+		w->image.assign(footer_off + footer_size, 0);
+		std::memcpy(w->image.data(), &h, sizeof(h));
+		f = w->image.data() + footer_off;
+	}
 	std::memcpy(f, w->cols.data(), w->cols.size() * sizeof(fls_column_desc));
 	f += w->cols.size() * sizeof(fls_column_desc);
 	std::memcpy(f, w->rgs.data(), w->rgs.size() * sizeof(fls_rowgroup_desc));
 	f += w->rgs.size() * sizeof(fls_rowgroup_desc);
 	for (auto& ch : w->chunks) {
-		std::memcpy(w->image.data() + ch->desc.offset, ch->bytes.data(), ch->bytes.size());
+		if (!streaming) {
+			std::memcpy(w->image.data() + ch->desc.offset, ch->bytes.data(), ch->bytes.size());
+		}
 		std::memcpy(f, &ch->desc, sizeof(fls_chunk_desc));
 		f += sizeof(fls_chunk_desc);
 		ch->bytes.clear();
 		ch->bytes.shrink_to_fit();
+	}
+	if (streaming) {
+		uint8_t head[FLS_ALIGN] = {};
+		std::memcpy(head, &h, sizeof(h));
+		int rc = pwrite_all(w->fd, head, sizeof(head), 0, w->stream_path);
+		if (!rc && ::ftruncate(w->fd, (off_t)(w->inline_footer ? footer_off + footer_size : footer_off)) != 0) {
+			rc = fls_set_error(FLSGPU_ERR_IO, ("cannot size " + w->stream_path + ": " + std::strerror(errno)).c_str());
+		}
+		if (!rc && w->inline_footer) {
+			rc = pwrite_all(w->fd, tail.data(), tail.size(), footer_off, w->stream_path);
+		}
+		if (::close(w->fd) != 0 && !rc) {
+			rc = fls_set_error(FLSGPU_ERR_IO, ("close failed: " + w->stream_path).c_str());
+		}
+		w->fd = -1;
+		if (!rc && !w->inline_footer) {
+			rc = write_file((w->stream_path + ".footer").c_str(), tail.data(), tail.size());
+		}
+		if (rc) {
+			return rc;
+		}
 	}
 	w->finished = true;
 	return FLSGPU_OK;
@@ -431,26 +558,21 @@ int flsgpu_writer_image(const flsgpu_writer* w, const void** bytes, uint64_t* si
 	if (!w || !w->finished || !bytes || !size) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_image: writer not finished");
 	}
+	if (!w->stream_path.empty()) {
+		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_image: a streaming writer keeps no image (flsgpu_writer_stream_to)");
+	}
 	*bytes = w->image.data();
 	*size = w->image.size();
-	return FLSGPU_OK;
-}
-
-static int write_file(const char* path, const uint8_t* p, size_t n) {
-	FILE* fp = std::fopen(path, "wb");
-	if (!fp) {
-		return fls_set_error(FLSGPU_ERR_IO, (std::string("cannot open for writing: ") + path).c_str());
-	}
-	const size_t k = std::fwrite(p, 1, n, fp);
-	if (std::fclose(fp) != 0 || k != n) {
-		return fls_set_error(FLSGPU_ERR_IO, (std::string("short write: ") + path).c_str());
-	}
 	return FLSGPU_OK;
 }
 
 int flsgpu_writer_save(const flsgpu_writer* w, const char* path) {
 	if (!w || !w->finished || !path) {
 		return fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_save: writer not finished");
+	}
+	if (!w->stream_path.empty()) { // the file was complete when flsgpu_writer_finish returned
+		return w->stream_path == path ? FLSGPU_OK
+		                              : fls_set_error(FLSGPU_ERR_INVALID, "flsgpu_writer_save: a streaming writer saves to the path it streams to");
 	}
 	if (w->inline_footer) {
 		return write_file(path, w->image.data(), w->image.size());

@@ -328,6 +328,8 @@ unique_ptr<GlobalFunctionData> FlsWriteInitGlobal(ClientContext &, FunctionData 
 	                              &global_state->writer),
 	         "COPY (FORMAT fls)");
 	FlsCheck(flsgpu_writer_set_inline_footer(global_state->writer, bind_data.inline_footer ? 1 : 0), "COPY (FORMAT fls)");
+	// row groups go to the file as they are flushed (rg_writer->Flush(), fls_writer.cpp:70,94): the writer keeps descriptors only
+	FlsCheck(flsgpu_writer_stream_to(global_state->writer, file_path.c_str()), "COPY (FORMAT fls)");
 	return std::move(global_state);
 }
 

@@ -149,7 +149,7 @@ for _n in ("flsgpu_table_close", "flsgpu_writer_destroy"):
 # every symbol include/flsgpu.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "flsgpu_last_error", "flsgpu_version", "flsgpu_init", "flsgpu_device_count", "flsgpu_writer_create",
-    "flsgpu_writer_append", "flsgpu_writer_finish", "flsgpu_writer_image", "flsgpu_writer_save",
+    "flsgpu_writer_append", "flsgpu_writer_finish", "flsgpu_writer_image", "flsgpu_writer_save", "flsgpu_writer_stream_to",
     "flsgpu_writer_destroy", "flsgpu_table_open", "flsgpu_table_open_memory", "flsgpu_table_close",
     "flsgpu_table_info_get", "flsgpu_table_column", "flsgpu_table_rowgroup", "flsgpu_table_chunk",
     "flsgpu_table_stage", "flsgpu_table_evict", "flsgpu_table_unstage", "flsgpu_table_resident_bytes", "flsgpu_decode_column",
@@ -229,6 +229,13 @@ class Writer:
 
     def save(self, path):
         _check(lib.flsgpu_writer_save(self._h, os.fsencode(path)), "writer_save")
+
+    def stream_to(self, path):
+        """Row groups go to `path` as they fill; finish_stream() completes the file (no in-memory image)."""
+        _check(lib.flsgpu_writer_stream_to(self._h, os.fsencode(path)), "writer_stream_to")
+
+    def finish_stream(self):
+        _check(lib.flsgpu_writer_finish(self._h), "writer_finish")
 
     def close(self):
         if self._h:

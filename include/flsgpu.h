@@ -82,6 +82,13 @@ void flsgpu_encoded_rowgroup_free(flsgpu_encoded_rowgroup* rg); /* only for row 
 int flsgpu_writer_set_inline_footer(flsgpu_writer* w, int inline_footer);
 /* Row groups flushed so far / tuples accepted so far (num_row_groups of FastLanesWriteGlobalState: file rotation). */
 int flsgpu_writer_rowgroups(const flsgpu_writer* w, uint64_t* n_rowgroups, uint64_t* n_tuples);
+/* Streaming: call once, before the first row group.  Every row group then goes to `path` as it is flushed (or, with
+ * flsgpu_writer_append, as it fills) and only its descriptors stay in memory; flsgpu_writer_finish writes the footer and the
+ * header and closes the file, which is byte for byte what flsgpu_writer_save would have written from an in-memory image.
+ * The reference's FileWriter writes row groups as they are flushed too (rg_writer->Flush(), fls_writer.cpp:70,94,130,161,325);
+ * without this call the container is assembled in memory (flsgpu_writer_image) - what tests and benchmarks want.
+ * After it flsgpu_writer_image fails and flsgpu_writer_save accepts the same path only (a no-op). */
+int flsgpu_writer_stream_to(flsgpu_writer* w, const char* path);
 int flsgpu_writer_image(const flsgpu_writer* w, const void** bytes, uint64_t* size); /* valid until destroy */
 int flsgpu_writer_save(const flsgpu_writer* w, const char* path);
 void flsgpu_writer_destroy(flsgpu_writer* w);

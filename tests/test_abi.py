@@ -85,3 +85,67 @@ def test_writer_rejects_bad_input():
         flsgpu.write_table([("a", "INT32", "CONSTANT")], [np.arange(10, dtype=np.int32)])
     with pytest.raises(flsgpu.FlsError):
         flsgpu.write_table([("a", "INT32", "ALP")], [np.arange(10, dtype=np.int32)])
+
+
+def test_streaming_writer_writes_the_same_bytes_as_the_image(tmp_path):
+    """flsgpu_writer_stream_to: row groups reach the file as they fill, the finished file is byte for byte the in-memory
+    container (inline footer), or data file + '<path>.footer' (reference WithInlinedFooter(false), fls_writer.cpp:229-230)."""
+    import fls_cases
+    import str_cases
+    n = 5 * 2048 + 333
+    cs = fls_cases.standard_cases(n=n)
+    sc = str_cases.cases(n)
+    cols = [fls_cases.column_spec(c) for c in cs] + [(k, sc[k][0], sc[k][1]) for k in sc]
+    arrs = [c[3] for c in cs] + [sc[k][2] for k in sc]
+    img = flsgpu.write_table(cols, arrs, vec_per_rowgroup=2)
+    path = str(tmp_path / "s.fls")
+    w = flsgpu.Writer(cols, 2)
+    w.stream_to(path)
+    cut = [0, 100, 2048, 2049, 7000, n]  # uneven pieces: pending rows, several row groups at once, a partial tail
+    for a, b in zip(cut, cut[1:]):
+        w.append([x[a:b] for x in arrs])
+    w.finish_stream()
+    w.save(path)  # the path it streams to: accepted, nothing left to do
+    with pytest.raises(flsgpu.FlsError):
+        w.save(path + ".elsewhere")
+    with pytest.raises(flsgpu.FlsError):
+        w.finish()  # a streaming writer keeps no image
+    w.close()
+    assert np.array_equal(np.fromfile(path, dtype=np.uint8), img)
+    t = flsgpu.Table(path=path)
+    assert t.n_rowgroups == (n + 2047) // 2048
+    t.close()
+
+    # footer beside the data file
+    a = np.arange(10_000, dtype=np.int64)
+    w = flsgpu.Writer([("a", "INT64", None)], 2)
+    _check = flsgpu._check
+    _check(flsgpu.lib.flsgpu_writer_set_inline_footer(w._h, 0), "set_inline_footer")
+    split = str(tmp_path / "split.fls")
+    w.stream_to(split)
+    w.append([a])
+    w.finish_stream()
+    w.close()
+    ref = flsgpu.Writer([("a", "INT64", None)], 2)
+    _check(flsgpu.lib.flsgpu_writer_set_inline_footer(ref._h, 0), "set_inline_footer")
+    ref.append([a])
+    ref.finish()
+    ref.save(str(tmp_path / "ref.fls"))
+    ref.close()
+    for suffix in ("", ".footer"):
+        assert open(split + suffix, "rb").read() == open(str(tmp_path / "ref.fls") + suffix, "rb").read(), suffix
+
+    # misuse: after the first row group, twice, unwritable path
+    w = flsgpu.Writer([("a", "INT64", None)], 2)
+    with pytest.raises(flsgpu.FlsError) as e:
+        w.stream_to(str(tmp_path / "no_such_dir" / "x.fls"))
+    assert e.value.status == -2
+    w.append([a])
+    with pytest.raises(flsgpu.FlsError):
+        w.stream_to(str(tmp_path / "late.fls"))
+    w.close()
+    w = flsgpu.Writer([("a", "INT64", None)], 2)
+    w.stream_to(str(tmp_path / "once.fls"))
+    with pytest.raises(flsgpu.FlsError):
+        w.stream_to(str(tmp_path / "twice.fls"))
+    w.close()
