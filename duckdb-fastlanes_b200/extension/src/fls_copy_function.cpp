@@ -262,6 +262,28 @@ struct FastLanesWriteGlobalState : public GlobalFunctionData {
 	unique_ptr<RowGroupBuffer> combine_buffer;
 	atomic<idx_t> num_row_groups {0};
 
+	//! batch mode: PrepareBatch runs on any thread and has no local state; its row-group buffers are recycled here so that
+	//! every batch does not fault a few megabytes of fresh pages in
+	std::mutex pool_lock;
+	vector<unique_ptr<RowGroupBuffer>> pool;
+
+	unique_ptr<RowGroupBuffer> AcquireBuffer(const vector<ColumnPlan> &plans) {
+		{
+			std::lock_guard<std::mutex> guard(pool_lock);
+			if (!pool.empty()) {
+				auto buffer = std::move(pool.back());
+				pool.pop_back();
+				return buffer;
+			}
+		}
+		return make_uniq<RowGroupBuffer>(plans);
+	}
+	void ReleaseBuffer(unique_ptr<RowGroupBuffer> buffer) {
+		buffer->Reset();
+		std::lock_guard<std::mutex> guard(pool_lock);
+		pool.push_back(std::move(buffer));
+	}
+
 	//! rg_writer->Flush() (fls_writer.cpp:70,94,130,161,325)
 	void Flush(flsgpu_encoded_rowgroup *encoded) {
 		FlsCheck(flsgpu_writer_flush_rowgroup(writer, encoded), "COPY (FORMAT fls)");
@@ -413,7 +435,8 @@ unique_ptr<PreparedBatchData> FlsWritePrepareBatch(ClientContext &, FunctionData
 	auto &bind_data = bind_data_p.Cast<FastLanesWriteBindData>();
 	auto &global_state = global_state_p.Cast<FastLanesWriteGlobalState>();
 	auto batch = make_uniq<FastLanesWriteBatchData>();
-	RowGroupBuffer buffer(bind_data.plans);
+	auto buffer_p = global_state.AcquireBuffer(bind_data.plans);
+	auto &buffer = *buffer_p;
 	for (auto &chunk : collection->Chunks()) {
 		idx_t consumed = 0;
 		while (consumed < chunk.size()) {
@@ -429,6 +452,7 @@ unique_ptr<PreparedBatchData> FlsWritePrepareBatch(ClientContext &, FunctionData
 	if (buffer.count) {
 		batch->row_groups.push_back(buffer.Encode(global_state.writer));
 	}
+	global_state.ReleaseBuffer(std::move(buffer_p));
 	return std::move(batch);
 }
 
