@@ -106,6 +106,67 @@ def test_the_files_copy_writes_are_the_engines_container(tmp_path):
 
 
 @needs_binaries
+def test_copy_modes_and_options_write_the_source_rows(tmp_path):
+    """Every COPY path of extension/test/sql/fls_copy_options.test (row_group_size, sidecar footer, file rotation, parallel and
+    ordered batch copy, overwriting an existing file, an empty result) checked on the CPU: the streamed files open and the
+    oracle decodes them to the source table."""
+    import glob
+
+    import numpy as np
+
+    import flsgpu
+    import oracle_lib
+
+    d = str(tmp_path)
+    rc, out, err = run_sql(f"""
+        CREATE TABLE src AS SELECT i AS id, CAST(i * 3 AS INTEGER) AS v, 'row ' || i AS s FROM range(0, 100000) t(i);
+        COPY src TO '{d}/rg2048.fls' (FORMAT fls, row_group_size 2048);
+        COPY src TO '{d}/sidecar.fls' (FORMAT fls, inline_footer false);
+        COPY src TO '{d}/rotated' (FORMAT fls, row_group_size 8192, row_groups_per_file 2);
+        SET preserve_insertion_order = false;
+        COPY src TO '{d}/parallel.fls' (FORMAT fls, row_group_size 4096);
+        SET preserve_insertion_order = true;
+        COPY src TO '{d}/batch.fls' (FORMAT fls, row_group_size 4096);
+        COPY src TO '{d}/batch.fls' (FORMAT fls, row_group_size 4096);
+        COPY (SELECT i AS id, i * 2 AS v FROM range(0, 10) t(i) WHERE i > 100) TO '{d}/empty.fls' (FORMAT fls);
+    """, threads=4)
+    assert rc == 0, err
+
+    def rows_of(paths):
+        ids, vs, strs = [], [], []
+        for p in paths:
+            img = np.fromfile(p, dtype=np.uint8)
+            if os.path.exists(p + ".footer"):
+                img = np.concatenate([img, np.fromfile(p + ".footer", dtype=np.uint8)])
+            t = flsgpu.Table(path=p)
+            o = oracle_lib.Oracle(img)
+            a = o.decode_column(0, 0, t.n_rowgroups, 0, np.int64, t.vec_per_rowgroup)
+            b = o.decode_column(1, 0, t.n_rowgroups, 0, np.int32, t.vec_per_rowgroup)
+            st, heap = o.decode_strings(2, 0, t.n_rowgroups, t.vec_per_rowgroup, 0x7F0000001000)
+            st = st.view(flsgpu.STRING_T).reshape(-1)
+            for x, y in t.valid_mask_slices():
+                ids.append(a[x:y])
+                vs.append(b[x:y])
+                strs += flsgpu.strings_from(st[x:y], heap, 0x7F0000001000)
+            t.close()
+        return np.concatenate(ids), np.concatenate(vs), strs
+
+    want = np.arange(100000)
+    for name, ordered in (("rg2048", True), ("sidecar", True), ("batch", True), ("parallel", False)):
+        ids, vs, strs = rows_of([f"{d}/{name}.fls"])
+        order = np.arange(len(ids)) if ordered else np.argsort(ids, kind="stable")
+        assert np.array_equal(ids[order], want) and np.array_equal(vs[order], want * 3), name
+        assert [strs[k] for k in order[:3000]] == [b"row %d" % k for k in range(3000)], name
+    files = sorted(glob.glob(f"{d}/rotated/*.fls"))
+    assert len(files) == 7  # 13 row groups of 8192 rows, two per file
+    ids, vs, _ = rows_of(files)
+    assert np.array_equal(np.sort(ids), want) and np.array_equal(vs, ids * 3)
+    t = flsgpu.Table(path=f"{d}/empty.fls")
+    assert (t.n_rowgroups, t.n_columns, t.n_tuples) == (0, 2, 0)
+    t.close()
+
+
+@needs_binaries
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["all_types_single_threaded", "all_types_multi_threaded"])
 def test_reference_sqllogictests_unmodified(name):
