@@ -1,5 +1,7 @@
 """GPU: random tables (tests/random_tables.py) go writer -> container -> CUDA decode through the C ABI and come back bit for
 bit (and equal the oracle's decode of the same bytes on every row of every existing vector)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -13,7 +15,8 @@ HEAP_BASE = 0x7F0000001000
 
 def test_random_tables_roundtrip_through_cuda():
     import torch
-    for seed in range(1000, 1150):
+    first, last = (int(v) for v in os.environ.get("FLS_RANDOM_SEEDS", "1000:1150").split(":"))  # a longer soak by hand
+    for seed in range(first, last):
         cols, arrs, vpr = random_tables.table(seed)
         img = flsgpu.write_table(cols, arrs, vec_per_rowgroup=vpr, n_threads=1)
         t = flsgpu.Table(img)
