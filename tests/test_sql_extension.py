@@ -106,6 +106,31 @@ def test_the_files_copy_writes_are_the_engines_container(tmp_path):
 
 
 @needs_binaries
+def test_aggregate_pushdown_plans_without_a_device(tmp_path):
+    """The optimizer rewrite is host logic: EXPLAIN shows FLS_AGGREGATE_SCAN for the supported shape and the ordinary scan for
+    everything else (extension/test/sql/fls_aggregate_pushdown.test holds the executed twin of this, on the GPU)."""
+    path = str(tmp_path / "p.fls")
+    rc, out, err = run_sql(f"""
+        COPY (SELECT i AS id, CAST(i % 100 AS INTEGER) AS k, i / 4.0 AS x, 'm' || (i % 4) AS mode FROM range(0, 50000) t(i))
+        TO '{path}' (FORMAT fls, row_group_size 8192);
+    """)
+    assert rc == 0, err
+
+    def plan(sql, pre=""):
+        rc, out, err = run_sql(f"{pre}EXPLAIN {sql};")
+        assert rc == 0, err
+        return out
+
+    src = f"read_fls('{path}')"
+    assert "FLS_AGGREGATE_SCAN" in plan(f"SELECT sum(id), count(*), min(k), max(k) FROM {src}")
+    assert "FLS_AGGREGATE_SCAN" in plan(f"SELECT sum(id), count(*) FROM {src} WHERE k < 10 AND mode = 'm1'")
+    for sql in (f"SELECT mode, sum(id) FROM {src} GROUP BY mode", f"SELECT sum(id * 2) FROM {src}", f"SELECT sum(x) FROM {src}",
+                f"SELECT count(DISTINCT k) FROM {src}", f"SELECT min(id) FROM {src} WHERE k > 3", f"SELECT avg(id) FROM {src}"):
+        assert "FLS_AGGREGATE_SCAN" not in plan(sql), sql
+    assert "FLS_AGGREGATE_SCAN" not in plan(f"SELECT sum(id) FROM {src}", "SET fastlanes_aggregate_pushdown = false;\n")
+
+
+@needs_binaries
 def test_copy_modes_and_options_write_the_source_rows(tmp_path):
     """Every COPY path of extension/test/sql/fls_copy_options.test (row_group_size, sidecar footer, file rotation, parallel and
     ordered batch copy, overwriting an existing file, an empty result) checked on the CPU: the streamed files open and the
