@@ -518,10 +518,12 @@ int flsgpu_writer_finish(flsgpu_writer* w) {
 	}
 	std::memcpy(f, w->cols.data(), w->cols.size() * sizeof(fls_column_desc));
 	f += w->cols.size() * sizeof(fls_column_desc);
-	std::memcpy(f, w->rgs.data(), w->rgs.size() * sizeof(fls_rowgroup_desc));
+	if (!w->rgs.empty()) { // an empty table has columns only
+		std::memcpy(f, w->rgs.data(), w->rgs.size() * sizeof(fls_rowgroup_desc));
+	}
 	f += w->rgs.size() * sizeof(fls_rowgroup_desc);
 	for (auto& ch : w->chunks) {
-		if (!streaming) {
+		if (!streaming && !ch->bytes.empty()) { // EXP_EQUAL chunks have a descriptor only
 			std::memcpy(w->image.data() + ch->desc.offset, ch->bytes.data(), ch->bytes.size());
 		}
 		std::memcpy(f, &ch->desc, sizeof(fls_chunk_desc));

@@ -35,7 +35,8 @@ def build_native():
 
 build()
 NATIVE = build_native() if os.environ.get("FLS_ORACLE_NATIVE") == "1" else None
-lib = C.CDLL(NATIVE or LIB)
+# FLS_ORACLE_LIB: another build of the same sources (tools/sanitize.sh: AddressSanitizer / UBSan)
+lib = C.CDLL(os.environ.get("FLS_ORACLE_LIB") or NATIVE or LIB)
 MARCH = "native" if NATIVE else "x86-64-v3"
 
 
