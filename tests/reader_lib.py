@@ -6,7 +6,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "duckdb-fastlanes_b200", "libflsreader.so")
-lib = C.CDLL(LIB)
+lib = C.CDLL(os.environ.get("FLSREADER_LIB", LIB))  # FLSREADER_LIB: tools/sanitize.sh
 lib.flsreader_last_error.restype = C.c_char_p
 lib.flsreader_close.restype = None
 lib.flsreader_cardinality.restype = C.c_uint64
