@@ -151,3 +151,37 @@ def test_reference_string_tables_roundtrip(n):
             got += flsgpu.strings_from(st[a:b], heap)
         assert got == vals, name
         t.close()
+
+
+def test_committed_container_still_decodes():
+    """tests/golden/container_v1.npz (oracle/make_golden_container.py): a container written at format version 1 - every numeric
+    encoding on INT32 / DOUBLE columns, one column per string encoding - with the rows it was written from.  Today's validator
+    must accept the committed bytes and today's oracle must decode them to those rows: the on-disk format stays readable."""
+    import flsgpu
+    import oracle_lib
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "container_v1.npz"))
+    img = np.ascontiguousarray(g["image"])
+    t = flsgpu.Table(img)
+    o = oracle_lib.Oracle(img)
+    assert t.n_columns == int(g["n_columns"]) == 35 and t.vec_per_rowgroup == 1 and t.n_tuples == 1124
+    seen = set()
+    for c in range(t.n_columns):
+        seen |= {flsgpu.ENC_NAME[t.chunk(r, c).encoding] for r in range(t.n_rowgroups)}
+        if str(g["types"][c]) in ("VARCHAR", "BLOB"):
+            off, data = g[f"off{c}"], g[f"col{c}"].tobytes()
+            want = [data[int(off[i]):int(off[i + 1])] for i in range(len(off) - 1)]
+            st, heap = o.decode_strings(c, 0, t.n_rowgroups, t.vec_per_rowgroup, 0x7F0000001000)
+            st = st.view(flsgpu.STRING_T).reshape(-1)
+            got = []
+            for a, b in t.valid_mask_slices():
+                got += flsgpu.strings_from(st[a:b], heap, 0x7F0000001000)
+            assert got == want, str(g["names"][c])
+        else:
+            want = g[f"col{c}"]
+            out = o.decode_column(c, 0, t.n_rowgroups, 0, want.dtype, t.vec_per_rowgroup)
+            got = np.concatenate([out[a:b] for a, b in t.valid_mask_slices()])
+            assert got.tobytes() == want.tobytes(), str(g["names"][c])
+    t.close()
+    assert {"UNCOMPRESSED", "CONSTANT", "FFOR", "DELTA", "DICT", "RLE", "ALP", "ALP_RD", "CROSS_RLE", "FREQUENCY", "SLPATCH", "DICT_STR",
+            "STR_UNCOMPRESSED", "STR_CONSTANT", "FSST", "FSST_DICT", "FSST12", "FSST12_DICT", "RLE_STR", "CROSS_RLE_STR",
+            "FREQUENCY_STR"} <= seen, seen
