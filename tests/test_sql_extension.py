@@ -125,7 +125,10 @@ def test_aggregate_pushdown_plans_without_a_device(tmp_path):
     assert "FLS_AGGREGATE_SCAN" in plan(f"SELECT sum(id), count(*), min(k), max(k) FROM {src}")
     assert "FLS_AGGREGATE_SCAN" in plan(f"SELECT sum(id), count(*) FROM {src} WHERE k < 10 AND mode = 'm1'")
     for sql in (f"SELECT mode, sum(id) FROM {src} GROUP BY mode", f"SELECT sum(id * 2) FROM {src}", f"SELECT sum(x) FROM {src}",
-                f"SELECT count(DISTINCT k) FROM {src}", f"SELECT min(id) FROM {src} WHERE k > 3", f"SELECT avg(id) FROM {src}"):
+                f"SELECT count(DISTINCT k) FROM {src}", f"SELECT min(id) FROM {src} WHERE k > 3", f"SELECT avg(id) FROM {src}",
+                f"SELECT sum(id) FILTER (WHERE k > 3) FROM {src}", f"SELECT sum(id) FROM (SELECT id FROM {src} LIMIT 10)",
+                f"SELECT sum(id) FROM read_fls(['{path}', '{path}'])", f"SELECT sum(id) FROM {src} WHERE k IN (1, 5, 7) OR id = 3",
+                f"SELECT sum(a.id), count(*) FROM {src} a, {src} b WHERE a.id = b.id"):
         assert "FLS_AGGREGATE_SCAN" not in plan(sql), sql
     assert "FLS_AGGREGATE_SCAN" not in plan(f"SELECT sum(id) FROM {src}", "SET fastlanes_aggregate_pushdown = false;\n")
 
