@@ -109,7 +109,21 @@ def mutate(rng, image, regs):
     what = []
     for _ in range(int(rng.choice([1, 1, 1, 2, 3]))):
         off, size, _ = regs[int(rng.choice(len(regs), p=weights))]
-        kind = int(rng.integers(0, 6))
+        kind = int(rng.integers(0, 8))
+        if kind == 6:  # a block of metadata from elsewhere lands here (a descriptor of another chunk, another vector's entry)
+            src_off, src_size, _ = regs[int(rng.choice(len(regs), p=weights))]
+            ln = int(min(rng.choice([8, 16, 32, 64, 144]), size, src_size))
+            a = src_off + (int(rng.integers(0, src_size - ln + 1)) & ~7)
+            b = off + (int(rng.integers(0, size - ln + 1)) & ~7)
+            a, b = min(a, src_off + src_size - ln), min(b, off + size - ln)
+            img[b:b + ln] = image[a:a + ln]
+            what.append((b, -ln, a))
+            continue
+        if kind == 7:  # the file ends early (or a few bytes of the tail are gone)
+            cut = int(rng.choice([int(rng.integers(0, len(img))), len(img) - int(rng.integers(1, 300))]))
+            img = img[:max(0, cut)].copy()
+            what.append((len(img), 0, 0))
+            break
         if kind <= 2:  # an aligned little-endian field takes an interesting value
             width = int(rng.choice([1, 2, 4, 8]))
             if size < width:
